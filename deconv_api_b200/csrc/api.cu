@@ -1,0 +1,701 @@
+// C-ABI of the dcv library (include/dcv.h): context, network description, forward tape,
+// projection chain and the standalone operators.  Host-side orchestration only; kernels live in
+// kernels_stream.cu, conv_fp32.cu and conv_tc.cu.
+#include "common.cuh"
+#include "internal.cuh"
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+
+using namespace dcv;
+
+namespace {
+thread_local std::string g_create_error;
+}
+
+// ---- error helpers ------------------------------------------------------------------------------
+int dcv_ctx::fail(int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  err = buf;
+  return code;
+}
+
+#define CU(ctx, expr)                                                                              \
+  do {                                                                                             \
+    cudaError_t e_ = (expr);                                                                       \
+    if (e_ != cudaSuccess)                                                                         \
+      return (ctx)->fail(e_ == cudaErrorMemoryAllocation ? DCV_ERR_NOMEM : DCV_ERR_CUDA, "%s: %s", #expr, \
+                         cudaGetErrorString(e_));                                                  \
+  } while (0)
+
+#define CHECK_LAUNCH(ctx) CU(ctx, cudaGetLastError())
+
+int DevBuf::ensure(dcv_ctx* ctx, size_t bytes) {
+  if (bytes <= cap) return 0;
+  if (p) { cudaFree(p); p = nullptr; cap = 0; }
+  size_t want = bytes + bytes / 8;       // slack so a slightly larger request does not reallocate
+  cudaError_t e = cudaMalloc(&p, want);
+  if (e != cudaSuccess) {
+    p = nullptr;
+    return ctx->fail(DCV_ERR_NOMEM, "cudaMalloc(%zu bytes): %s", want, cudaGetErrorString(e));
+  }
+  cap = want;
+  return 0;
+}
+
+void DevBuf::release() {
+  if (p) cudaFree(p);
+  p = nullptr;
+  cap = 0;
+}
+
+static int set_device(dcv_ctx* ctx) {
+  CU(ctx, cudaSetDevice(ctx->device));
+  return 0;
+}
+
+#define ENTER(ctx)                                   \
+  if (!(ctx)) return DCV_ERR_ARG;                    \
+  { int r_ = set_device(ctx); if (r_) return r_; }
+
+#define TRY(expr) do { int r_ = (expr); if (r_) return r_; } while (0)
+
+// ---- life cycle ---------------------------------------------------------------------------------
+extern "C" int dcv_version(void) { return 100; }
+
+extern "C" int dcv_create(int device, dcv_ctx** out) {
+  if (!out) return DCV_ERR_ARG;
+  *out = nullptr;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0) {
+    g_create_error = std::string("no CUDA device: ") + cudaGetErrorString(e);
+    return DCV_ERR_CUDA;
+  }
+  if (device < 0 || device >= ndev) { g_create_error = "device index out of range"; return DCV_ERR_ARG; }
+  e = cudaSetDevice(device);
+  if (e != cudaSuccess) { g_create_error = cudaGetErrorString(e); return DCV_ERR_CUDA; }
+  cudaDeviceProp prop;
+  e = cudaGetDeviceProperties(&prop, device);
+  if (e != cudaSuccess) { g_create_error = cudaGetErrorString(e); return DCV_ERR_CUDA; }
+  if (prop.major != 10) {
+    g_create_error = "this library is built for sm_100a (B200) only; device is sm_" + std::to_string(prop.major) +
+                     std::to_string(prop.minor);
+    return DCV_ERR_UNSUPPORTED;
+  }
+  dcv_ctx* ctx = new (std::nothrow) dcv_ctx();
+  if (!ctx) return DCV_ERR_NOMEM;
+  ctx->device = device;
+  ctx->num_sms = prop.multiProcessorCount;
+  e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
+  if (e != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete ctx; return DCV_ERR_CUDA; }
+  const char* ws = getenv("DCV_WORKSPACE_MB");
+  ctx->workspace_budget = (ws ? (size_t)atoll(ws) : (size_t)12288) << 20;
+  *out = ctx;
+  return DCV_OK;
+}
+
+static void free_layer(Layer& l) {
+  if (l.w) cudaFree(l.w);
+  if (l.bias) cudaFree(l.bias);
+  if (l.wd) cudaFree(l.wd);
+  tc_free_layer(l);
+  l.act.release();
+  l.sw.release();
+}
+
+extern "C" void dcv_destroy(dcv_ctx* ctx) {
+  if (!ctx) return;
+  cudaSetDevice(ctx->device);
+  cudaStreamSynchronize(ctx->stream);
+  for (auto& l : ctx->net) free_layer(l);
+  ctx->input.release();
+  for (auto& b : ctx->ws) b.release();
+  ctx->feat_dev.release();
+  ctx->scratch.release();
+  ctx->stage.release();
+  cudaStreamDestroy(ctx->stream);
+  delete ctx;
+}
+
+extern "C" const char* dcv_last_error(const dcv_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+extern "C" int dcv_device(const dcv_ctx* ctx) { return ctx ? ctx->device : DCV_ERR_ARG; }
+extern "C" long long dcv_launch_count(const dcv_ctx* ctx) { return ctx ? ctx->launches : 0; }
+extern "C" void* dcv_stream(const dcv_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+
+extern "C" int dcv_sync(dcv_ctx* ctx) {
+  ENTER(ctx);
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+// ---- network description --------------------------------------------------------------------------
+extern "C" int dcv_net_clear(dcv_ctx* ctx) {
+  ENTER(ctx);
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  for (auto& l : ctx->net) free_layer(l);
+  ctx->net.clear();
+  ctx->tape_upto = -1;
+  return 0;
+}
+
+static int upload(dcv_ctx* ctx, float** dst, const float* src, size_t n) {
+  CU(ctx, cudaMalloc(dst, std::max<size_t>(n, 1) * sizeof(float)));
+  if (src) CU(ctx, cudaMemcpyAsync(*dst, src, n * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+  else CU(ctx, cudaMemsetAsync(*dst, 0, n * sizeof(float), ctx->stream));
+  return 0;
+}
+
+extern "C" int dcv_net_add_conv(dcv_ctx* ctx, const float* w_hwio, const float* bias, int cin, int cout, int relu) {
+  ENTER(ctx);
+  if (!w_hwio || cin <= 0 || cout <= 0) return ctx->fail(DCV_ERR_ARG, "dcv_net_add_conv: bad arguments");
+  Layer l;
+  l.kind = LK_CONV; l.cin = cin; l.cout = cout; l.relu = relu ? 1 : 0;
+  const size_t nw = (size_t)9 * cin * cout;
+  TRY(upload(ctx, &l.w, w_hwio, nw));
+  TRY(upload(ctx, &l.bias, bias, cout));
+  CU(ctx, cudaMalloc(&l.wd, nw * sizeof(float)));
+  launch_flip_transpose(l.w, cin, cout, l.wd, ctx->stream); ctx->launches++;
+  CHECK_LAUNCH(ctx);
+  TRY(tc_prepare_layer(ctx, l));
+  CU(ctx, cudaStreamSynchronize(ctx->stream));      // host pointers are borrowed for the call only
+  ctx->net.push_back(l);
+  return (int)ctx->net.size() - 1;
+}
+
+extern "C" int dcv_net_add_pool(dcv_ctx* ctx) {
+  ENTER(ctx);
+  Layer l;
+  l.kind = LK_POOL;
+  ctx->net.push_back(l);
+  return (int)ctx->net.size() - 1;
+}
+
+extern "C" int dcv_net_add_flatten(dcv_ctx* ctx) {
+  ENTER(ctx);
+  Layer l;
+  l.kind = LK_FLATTEN;
+  ctx->net.push_back(l);
+  return (int)ctx->net.size() - 1;
+}
+
+extern "C" int dcv_net_add_dense(dcv_ctx* ctx, const float* w, const float* bias, int nin, int nout, int act) {
+  ENTER(ctx);
+  if (!w || nin <= 0 || nout <= 0 || act < 0 || act > 2) return ctx->fail(DCV_ERR_ARG, "dcv_net_add_dense: bad arguments");
+  Layer l;
+  l.kind = LK_DENSE; l.cin = nin; l.cout = nout; l.act_kind = act;
+  TRY(upload(ctx, &l.w, w, (size_t)nin * nout));
+  TRY(upload(ctx, &l.bias, bias, nout));
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  ctx->net.push_back(l);
+  return (int)ctx->net.size() - 1;
+}
+
+extern "C" int dcv_net_num_layers(const dcv_ctx* ctx) { return ctx ? (int)ctx->net.size() : DCV_ERR_ARG; }
+
+// ---- forward tape -----------------------------------------------------------------------------------
+static int forward_impl(dcv_ctx* ctx, const float* img, bool on_device, int B, int H, int W, int upto) {
+  if (!img || B <= 0 || H <= 0 || W <= 0) return ctx->fail(DCV_ERR_ARG, "dcv_forward: bad arguments");
+  if (ctx->net.empty()) return ctx->fail(DCV_ERR_STATE, "dcv_forward: empty network");
+  if (upto < 0 || upto >= (int)ctx->net.size()) return ctx->fail(DCV_ERR_ARG, "dcv_forward: layer %d out of range", upto);
+  int C = -1;
+  for (auto& l : ctx->net) if (l.kind == LK_CONV) { C = l.cin; break; }
+  if (C < 0) return ctx->fail(DCV_ERR_UNSUPPORTED, "dcv_forward: network has no conv layer to define the input channels");
+  ctx->tape_upto = -1;
+  const size_t n_in = (size_t)B * H * W * C;
+  TRY(ctx->input.ensure(ctx, n_in * sizeof(float)));
+  CU(ctx, cudaMemcpyAsync(ctx->input.p, img, n_in * sizeof(float),
+                          on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, ctx->stream));
+  ctx->in_B = B; ctx->in_H = H; ctx->in_W = W; ctx->in_C = C;
+  const float* cur = (const float*)ctx->input.p;
+  int cb = B, ch = H, cw = W, cc = C;
+  bool flat = false;
+  for (int j = 0; j <= upto; ++j) {
+    Layer& l = ctx->net[j];
+    switch (l.kind) {
+      case LK_CONV: {
+        if (flat) return ctx->fail(DCV_ERR_UNSUPPORTED, "conv after flatten");
+        if (l.cin != cc) return ctx->fail(DCV_ERR_ARG, "layer %d: expects %d input channels, got %d", j, l.cin, cc);
+        TRY(l.act.ensure(ctx, (size_t)cb * ch * cw * l.cout * sizeof(float)));
+        ConvEpilogue e; e.bias = l.bias; e.relu = l.relu;
+        launch_conv3x3_fp32(cur, l.w, cb, ch, cw, l.cin, l.cout, e, (float*)l.act.p, ctx->stream); ctx->launches++;
+        cc = l.cout;
+        break;
+      }
+      case LK_POOL: {
+        if (flat) return ctx->fail(DCV_ERR_UNSUPPORTED, "pool after flatten");
+        const int oh = ch / 2, ow = cw / 2;
+        if (oh == 0 || ow == 0) return ctx->fail(DCV_ERR_ARG, "layer %d: input %dx%d too small to pool", j, ch, cw);
+        TRY(l.act.ensure(ctx, (size_t)cb * oh * ow * cc * sizeof(float)));
+        TRY(l.sw.ensure(ctx, (size_t)cb * oh * ow * cc));
+        launch_maxpool_switch(cur, cb, ch, cw, cc, (float*)l.act.p, (uint8_t*)l.sw.p, ctx->stream); ctx->launches++;
+        l.in_H = ch; l.in_W = cw;
+        ch = oh; cw = ow;
+        break;
+      }
+      case LK_FLATTEN: {
+        // NHWC row-major flatten is a no-op on the data (DFlatten.up, deepdream.py:342-352)
+        l.in_H = ch; l.in_W = cw; l.in_C = cc;
+        TRY(l.act.ensure(ctx, (size_t)cb * ch * cw * cc * sizeof(float)));
+        CU(ctx, cudaMemcpyAsync(l.act.p, cur, (size_t)cb * ch * cw * cc * sizeof(float), cudaMemcpyDeviceToDevice, ctx->stream));
+        cc = ch * cw * cc; ch = 1; cw = 1;
+        flat = true;
+        break;
+      }
+      case LK_DENSE: {
+        if (!flat && !(ch == 1 && cw == 1)) return ctx->fail(DCV_ERR_UNSUPPORTED, "dense needs a flattened input");
+        if (l.cin != cc) return ctx->fail(DCV_ERR_ARG, "layer %d: dense expects %d inputs, got %d", j, l.cin, cc);
+        TRY(l.act.ensure(ctx, (size_t)cb * l.cout * sizeof(float)));
+        TRY(ctx->scratch.ensure(ctx, (size_t)dense_splits(l.cin) * cb * l.cout * sizeof(float)));
+        launch_dense_fwd(cur, l.w, l.bias, cb, l.cin, l.cout, l.act_kind, (float*)ctx->scratch.p, (float*)l.act.p, ctx->stream);
+        ctx->launches += 2;
+        if (l.act_kind == DCV_ACT_SOFTMAX) {
+          launch_softmax_rows((float*)l.act.p, cb, l.cout, (float*)l.act.p, ctx->stream); ctx->launches++;
+        }
+        cc = l.cout;
+        break;
+      }
+    }
+    l.B = cb; l.H = ch; l.W = cw; l.C = cc;
+    cur = (const float*)l.act.p;
+  }
+  CHECK_LAUNCH(ctx);
+  ctx->tape_upto = upto;
+  return 0;
+}
+
+extern "C" int dcv_forward(dcv_ctx* ctx, const float* img, int B, int H, int W, int upto) {
+  ENTER(ctx);
+  TRY(forward_impl(ctx, img, false, B, H, W, upto));
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+extern "C" int dcv_forward_dev(dcv_ctx* ctx, const float* img, int B, int H, int W, int upto) {
+  ENTER(ctx);
+  return forward_impl(ctx, img, true, B, H, W, upto);
+}
+
+static int check_tape(const dcv_ctx* c, dcv_ctx* ctx, int layer, const char* who) {
+  (void)c;
+  if (layer < 0 || layer >= (int)ctx->net.size()) return ctx->fail(DCV_ERR_ARG, "%s: layer %d out of range", who, layer);
+  if (layer > ctx->tape_upto) return ctx->fail(DCV_ERR_STATE, "%s: layer %d is not in the current tape (run dcv_forward first)", who, layer);
+  return 0;
+}
+
+extern "C" int dcv_layer_shape(const dcv_ctx* ctx, int layer, int dims[4]) {
+  if (!ctx || !dims) return DCV_ERR_ARG;
+  dcv_ctx* m = const_cast<dcv_ctx*>(ctx);
+  TRY(check_tape(ctx, m, layer, "dcv_layer_shape"));
+  const Layer& l = ctx->net[layer];
+  dims[0] = l.B; dims[1] = l.H; dims[2] = l.W; dims[3] = l.C;
+  return 0;
+}
+
+extern "C" int dcv_read_activation(dcv_ctx* ctx, int layer, float* out) {
+  ENTER(ctx);
+  if (!out) return ctx->fail(DCV_ERR_ARG, "dcv_read_activation: null output");
+  TRY(check_tape(ctx, ctx, layer, "dcv_read_activation"));
+  const Layer& l = ctx->net[layer];
+  CU(ctx, cudaMemcpyAsync(out, l.act.p, (size_t)l.B * l.H * l.W * l.C * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+extern "C" int dcv_read_switch(dcv_ctx* ctx, int layer, uint8_t* out) {
+  ENTER(ctx);
+  if (!out) return ctx->fail(DCV_ERR_ARG, "dcv_read_switch: null output");
+  TRY(check_tape(ctx, ctx, layer, "dcv_read_switch"));
+  const Layer& l = ctx->net[layer];
+  if (l.kind != LK_POOL) return ctx->fail(DCV_ERR_ARG, "dcv_read_switch: layer %d is not a pool layer", layer);
+  CU(ctx, cudaMemcpyAsync(out, l.sw.p, (size_t)l.B * l.H * l.W * l.C, cudaMemcpyDeviceToHost, ctx->stream));
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+extern "C" int dcv_channel_sums(dcv_ctx* ctx, int layer, double* out) {
+  ENTER(ctx);
+  if (!out) return ctx->fail(DCV_ERR_ARG, "dcv_channel_sums: null output");
+  TRY(check_tape(ctx, ctx, layer, "dcv_channel_sums"));
+  const Layer& l = ctx->net[layer];
+  const size_t rows = (size_t)l.B * l.H * l.W;
+  const int np = channel_sums_partials(rows, l.C);
+  TRY(ctx->scratch.ensure(ctx, ((size_t)np + 1) * l.C * sizeof(double)));
+  double* partial = (double*)ctx->scratch.p;
+  double* res = partial + (size_t)np * l.C;
+  launch_channel_sums((const float*)l.act.p, rows, l.C, partial, np, res, ctx->stream); ctx->launches += 2;
+  CHECK_LAUNCH(ctx);
+  CU(ctx, cudaMemcpyAsync(out, res, (size_t)l.C * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+extern "C" int dcv_channel_sums_buf(dcv_ctx* ctx, const float* x, size_t rows, int C, double* out) {
+  ENTER(ctx);
+  if (!x || !out || C <= 0) return ctx->fail(DCV_ERR_ARG, "dcv_channel_sums_buf: bad arguments");
+  if (rows == 0) { memset(out, 0, (size_t)C * sizeof(double)); return 0; }
+  const size_t nbytes = (rows * C * sizeof(float) + 255) & ~(size_t)255;
+  TRY(ctx->stage.ensure(ctx, nbytes));
+  CU(ctx, cudaMemcpyAsync(ctx->stage.p, x, rows * C * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+  const int np = channel_sums_partials(rows, C);
+  TRY(ctx->scratch.ensure(ctx, ((size_t)np + 1) * C * sizeof(double)));
+  double* partial = (double*)ctx->scratch.p;
+  double* res = partial + (size_t)np * C;
+  launch_channel_sums((const float*)ctx->stage.p, rows, C, partial, np, res, ctx->stream); ctx->launches += 2;
+  CHECK_LAUNCH(ctx);
+  CU(ctx, cudaMemcpyAsync(out, res, (size_t)C * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+// ---- projection chain -------------------------------------------------------------------------------
+// Largest per-item fp32 element count any intermediate of a chain starting at `layer` can have.
+static size_t chain_max_elems(const dcv_ctx* ctx, int layer) {
+  size_t m = (size_t)ctx->in_H * ctx->in_W * ctx->in_C;
+  for (int j = 0; j <= layer; ++j) {
+    const Layer& l = ctx->net[j];
+    m = std::max(m, (size_t)l.H * l.W * l.C);
+  }
+  return m;
+}
+
+static int ensure_nonneg(dcv_ctx* ctx, bool& nonneg, float* data, size_t n) {
+  if (nonneg) return 0;
+  launch_relu(data, n, data, ctx->stream); ctx->launches++;
+  nonneg = true;
+  return 0;
+}
+
+// Runs the chain for `n` feature maps (already on the device in ctx->feat_dev at `foff`) and leaves the
+// result, (n*B, H0, W0, C0) fp32, at *result (a pointer into the workspace).
+// The data is in one of three forms while it travels down:
+//   MAP    one single-channel map per item (the projected tensor has ONE non-zero channel, so it is
+//          never materialised; pools unpool the map, the first conv below runs as a rank-1 update)
+//   TENSOR full (P,h,w,C) NHWC tensors
+//   VEC    (P,C) rows, above a Flatten (dense layers)
+static int project_chunk(dcv_ctx* ctx, int layer, int foff, int n, int vis_mode, int precision, float** result) {
+  enum { M_MAP, M_TENSOR, M_VEC };
+  const int B = ctx->in_B;
+  const int P = n * B;
+  const int* feat = (const int*)ctx->feat_dev.p + foff;
+  const Layer& top = ctx->net[layer];
+  float* bufs[2] = {(float*)ctx->ws[0].p, (float*)ctx->ws[1].p};
+  int cur = 0;                       // bufs[cur] holds the current data
+  float* maps = (float*)ctx->ws[2].p;
+  float* maps2 = (float*)ctx->ws[3].p;
+
+  // seed (deepdream.py:450-465): feature map feat[k] of the layer's output, all other maps zero
+  int h = top.H, w = top.W, C = top.C;
+  launch_gather_map((const float*)top.act.p, B, h, w, C, feat, n, maps, ctx->stream); ctx->launches++;
+  if (vis_mode == DCV_VIS_MAX) {
+    launch_keep_max(maps, n, (size_t)B * h * w, nullptr, ctx->stream); ctx->launches++;
+  }
+  int mode = M_MAP;
+  if (top.kind == LK_DENSE || top.kind == LK_FLATTEN) {
+    launch_scatter_map(maps, n, B, 1, 1, C, feat, bufs[cur], ctx->stream); ctx->launches++;
+    mode = M_VEC;
+  }
+  // Data is non-negative whenever the op that produced it ended in a ReLU; tracking this lets the
+  // '<name>_activation'.down ReLUs (deepdream.py:260) run only where they can change a value.
+  bool nonneg = false;
+  for (int j = layer; j >= 0; --j) {
+    const Layer& l = ctx->net[j];
+    if (l.kind == LK_CONV) { nonneg = l.relu != 0; break; }
+    if (l.kind == LK_DENSE) { nonneg = l.act_kind != DCV_ACT_LINEAR; break; }
+  }
+
+  for (int j = layer; j >= 0; --j) {
+    const Layer& l = ctx->net[j];
+    if (l.kind == LK_DENSE) {
+      if (mode != M_VEC) return ctx->fail(DCV_ERR_STATE, "chain: dense layer %d below a spatial layer", j);
+      if (l.cout != C) return ctx->fail(DCV_ERR_STATE, "chain: dense layer %d has %d outputs, data has %d", j, l.cout, C);
+      if (j != layer) {              // '<name>_activation'.down of this layer comes first
+        if (l.act_kind == DCV_ACT_RELU) TRY(ensure_nonneg(ctx, nonneg, bufs[cur], (size_t)P * C));
+        if (l.act_kind == DCV_ACT_SOFTMAX) {
+          launch_softmax_rows(bufs[cur], P, C, bufs[cur], ctx->stream); ctx->launches++;
+        }
+      }
+      launch_dense_bwd(bufs[cur], l.w, P, l.cin, l.cout, bufs[cur ^ 1], ctx->stream); ctx->launches++;
+      cur ^= 1;
+      C = l.cin;
+      nonneg = false;
+    } else if (l.kind == LK_FLATTEN) {
+      if (mode != M_VEC) return ctx->fail(DCV_ERR_STATE, "chain: flatten layer %d below a spatial layer", j);
+      h = l.in_H; w = l.in_W; C = l.in_C;      // DFlatten.down is a reshape (deepdream.py:355-366)
+      mode = M_TENSOR;
+    } else if (l.kind == LK_POOL) {
+      if (mode == M_VEC) return ctx->fail(DCV_ERR_STATE, "chain: pool layer %d above a flatten", j);
+      if ((l.in_H & 1) || (l.in_W & 1))
+        return ctx->fail(DCV_ERR_ARG, "unpool of layer %d: odd input size %dx%d (the reference raises here too)", j, l.in_H, l.in_W);
+      if (mode == M_MAP) {
+        launch_unpool_map(maps, (const uint8_t*)l.sw.p, B, h, w, C, feat, n, maps2, ctx->stream); ctx->launches++;
+        std::swap(maps, maps2);
+      } else {
+        launch_unpool_switch_items(bufs[cur], (const uint8_t*)l.sw.p, P, B, l.in_H, l.in_W, C, 0, bufs[cur ^ 1], ctx->stream);
+        ctx->launches++;
+        cur ^= 1;
+      }
+      h = l.in_H; w = l.in_W;
+    } else {   // LK_CONV
+      if (mode == M_VEC) return ctx->fail(DCV_ERR_STATE, "chain: conv layer %d above a flatten", j);
+      if (l.cout != C) return ctx->fail(DCV_ERR_STATE, "chain: layer %d has %d outputs, data has %d channels", j, l.cout, C);
+      if (mode == M_MAP) {
+        if (j != layer && l.relu) TRY(ensure_nonneg(ctx, nonneg, maps, (size_t)P * h * w));
+        launch_rank1_deconv(maps, l.wd, l.cout, l.cin, feat, n, B, h, w, l.relu, bufs[cur], ctx->stream); ctx->launches++;
+        mode = M_TENSOR;
+      } else {
+        if (j != layer && l.relu) TRY(ensure_nonneg(ctx, nonneg, bufs[cur], (size_t)P * h * w * C));
+        if (precision == DCV_BF16) {
+          TRY(tc_deconv(ctx, l, bufs[cur], P, h, w, bufs[cur ^ 1]));
+        } else {
+          ConvEpilogue e; e.relu = l.relu;
+          // backward conv: input channels = l.cout, output channels = l.cin, weights wd [9][cout][cin]
+          launch_conv3x3_fp32(bufs[cur], l.wd, P, h, w, l.cout, l.cin, e, bufs[cur ^ 1], ctx->stream); ctx->launches++;
+        }
+        cur ^= 1;
+      }
+      nonneg = l.relu != 0;
+      C = l.cin;
+    }
+  }
+  if (mode == M_MAP) {   // no conv below the projected layer: the result is the map in channel f of zeros
+    launch_scatter_map(maps, n, B, h, w, C, feat, bufs[cur], ctx->stream); ctx->launches++;
+  }
+  CHECK_LAUNCH(ctx);
+  *result = bufs[cur];
+  return 0;
+}
+
+static int project_impl(dcv_ctx* ctx, int layer, const int* feat, int n, int vis_mode, int precision, float* out,
+                        bool out_on_device) {
+  if (!feat || !out || n < 0) return ctx->fail(DCV_ERR_ARG, "dcv_project: bad arguments");
+  if (vis_mode != DCV_VIS_ALL && vis_mode != DCV_VIS_MAX) return ctx->fail(DCV_ERR_ARG, "Illegal visualize mode");
+  if (precision != DCV_FP32 && precision != DCV_BF16) return ctx->fail(DCV_ERR_ARG, "dcv_project: unknown precision");
+  TRY(check_tape(ctx, ctx, layer, "dcv_project"));
+  const Layer& top = ctx->net[layer];
+  for (int k = 0; k < n; ++k)
+    if (feat[k] < 0 || feat[k] >= top.C) return ctx->fail(DCV_ERR_ARG, "dcv_project: feature %d out of range [0,%d)", feat[k], top.C);
+  if (n == 0) return 0;
+  const int B = ctx->in_B;
+  const size_t out_elems = (size_t)B * ctx->in_H * ctx->in_W * ctx->in_C;   // per feature
+  const size_t max_elems = chain_max_elems(ctx, layer);                     // per item
+  // chunk so that the two ping-pong buffers fit the workspace budget
+  size_t per_feat = 2 * (size_t)B * max_elems * sizeof(float);
+  int chunk = (int)std::max<size_t>(1, ctx->workspace_budget / per_feat);
+  chunk = std::min(chunk, n);
+  TRY(ctx->ws[0].ensure(ctx, (size_t)chunk * B * max_elems * sizeof(float)));
+  TRY(ctx->ws[1].ensure(ctx, (size_t)chunk * B * max_elems * sizeof(float)));
+  size_t map_elems = 0;
+  for (int j = 0; j <= layer; ++j) map_elems = std::max(map_elems, (size_t)ctx->net[j].H * ctx->net[j].W);
+  map_elems = std::max(map_elems, (size_t)ctx->in_H * ctx->in_W);
+  TRY(ctx->ws[2].ensure(ctx, (size_t)chunk * B * map_elems * sizeof(float)));
+  TRY(ctx->ws[3].ensure(ctx, (size_t)chunk * B * map_elems * sizeof(float)));
+  TRY(ctx->feat_dev.ensure(ctx, (size_t)n * sizeof(int)));
+  CU(ctx, cudaMemcpyAsync(ctx->feat_dev.p, feat, (size_t)n * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+  for (int f0 = 0; f0 < n; f0 += chunk) {
+    const int nf = std::min(chunk, n - f0);
+    float* res = nullptr;
+    TRY(project_chunk(ctx, layer, f0, nf, vis_mode, precision, &res));
+    CU(ctx, cudaMemcpyAsync(out + (size_t)f0 * out_elems, res, (size_t)nf * out_elems * sizeof(float),
+                            out_on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, ctx->stream));
+  }
+  return 0;
+}
+
+extern "C" int dcv_project(dcv_ctx* ctx, int layer, const int* feat, int n, int vis_mode, int precision, float* out) {
+  ENTER(ctx);
+  TRY(project_impl(ctx, layer, feat, n, vis_mode, precision, out, false));
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+extern "C" int dcv_project_dev(dcv_ctx* ctx, int layer, const int* feat, int n, int vis_mode, int precision, float* out_dev) {
+  ENTER(ctx);
+  return project_impl(ctx, layer, feat, n, vis_mode, precision, out_dev, true);
+}
+
+// ---- de-process -------------------------------------------------------------------------------------
+extern "C" int dcv_deprocess_dev(dcv_ctx* ctx, const float* x_dev, size_t n, uint8_t* out_dev) {
+  ENTER(ctx);
+  if (!x_dev || !out_dev) return ctx->fail(DCV_ERR_ARG, "dcv_deprocess: null pointer");
+  if (n == 0) return 0;
+  if (((uintptr_t)x_dev & 15) || ((uintptr_t)out_dev & 3)) return ctx->fail(DCV_ERR_ARG, "dcv_deprocess_dev: x must be 16-byte and out 4-byte aligned");
+  const int np = deprocess_partials(n);
+  TRY(ctx->scratch.ensure(ctx, (size_t)np * 2 * sizeof(double)));
+  launch_deprocess(x_dev, n, (double*)ctx->scratch.p, np, out_dev, nullptr, ctx->stream); ctx->launches += 2;
+  CHECK_LAUNCH(ctx);
+  return 0;
+}
+
+extern "C" int dcv_deprocess(dcv_ctx* ctx, float* x, size_t n, uint8_t* out, int mutate) {
+  ENTER(ctx);
+  if (!x || !out) return ctx->fail(DCV_ERR_ARG, "dcv_deprocess: null pointer");
+  if (n == 0) return 0;
+  const size_t in_bytes = (n * sizeof(float) + 255) & ~(size_t)255;
+  const size_t out_bytes = (n + 255) & ~(size_t)255;
+  TRY(ctx->stage.ensure(ctx, in_bytes + out_bytes + (mutate ? in_bytes : 0)));
+  float* xd = (float*)ctx->stage.p;
+  uint8_t* od = (uint8_t*)ctx->stage.p + in_bytes;
+  float* nd = mutate ? (float*)((char*)ctx->stage.p + in_bytes + out_bytes) : nullptr;
+  CU(ctx, cudaMemcpyAsync(xd, x, n * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+  const int np = deprocess_partials(n);
+  TRY(ctx->scratch.ensure(ctx, (size_t)np * 2 * sizeof(double)));
+  launch_deprocess(xd, n, (double*)ctx->scratch.p, np, od, nd, ctx->stream); ctx->launches += 2;
+  CHECK_LAUNCH(ctx);
+  CU(ctx, cudaMemcpyAsync(out, od, n, cudaMemcpyDeviceToHost, ctx->stream));
+  if (mutate) CU(ctx, cudaMemcpyAsync(x, nd, n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+// ---- standalone operators on host buffers -----------------------------------------------------------
+static size_t align256(size_t b) { return (b + 255) & ~(size_t)255; }
+
+extern "C" int dcv_maxpool_switch(dcv_ctx* ctx, const float* x, int B, int H, int W, int C, float* pooled, uint8_t* sw) {
+  ENTER(ctx);
+  if (!x || !pooled || !sw || B < 0 || H < 0 || W < 0 || C < 0) return ctx->fail(DCV_ERR_ARG, "dcv_maxpool_switch: bad arguments");
+  const size_t nin = (size_t)B * H * W * C, nout = (size_t)B * (H / 2) * (W / 2) * C;
+  if (nout == 0) return 0;
+  const size_t o1 = align256(nin * 4), o2 = o1 + align256(nout * 4);
+  TRY(ctx->stage.ensure(ctx, o2 + nout));
+  char* base = (char*)ctx->stage.p;
+  CU(ctx, cudaMemcpyAsync(base, x, nin * 4, cudaMemcpyHostToDevice, ctx->stream));
+  launch_maxpool_switch((const float*)base, B, H, W, C, (float*)(base + o1), (uint8_t*)(base + o2), ctx->stream); ctx->launches++;
+  CHECK_LAUNCH(ctx);
+  CU(ctx, cudaMemcpyAsync(pooled, base + o1, nout * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  CU(ctx, cudaMemcpyAsync(sw, base + o2, nout, cudaMemcpyDeviceToHost, ctx->stream));
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+extern "C" int dcv_unpool_switch(dcv_ctx* ctx, const float* x, const uint8_t* sw, int B, int H, int W, int C, float* out) {
+  ENTER(ctx);
+  if (!x || !sw || !out || B < 0 || H < 0 || W < 0 || C < 0) return ctx->fail(DCV_ERR_ARG, "dcv_unpool_switch: bad arguments");
+  if ((H & 1) || (W & 1)) return ctx->fail(DCV_ERR_ARG, "dcv_unpool_switch: output size %dx%d must be even (the reference raises on odd sizes)", H, W);
+  const size_t nout = (size_t)B * H * W * C, nin = nout / 4;
+  if (nout == 0) return 0;
+  const size_t o1 = align256(nin * 4), o2 = o1 + align256(nin);
+  TRY(ctx->stage.ensure(ctx, o2 + nout * 4));
+  char* base = (char*)ctx->stage.p;
+  CU(ctx, cudaMemcpyAsync(base, x, nin * 4, cudaMemcpyHostToDevice, ctx->stream));
+  CU(ctx, cudaMemcpyAsync(base + o1, sw, nin, cudaMemcpyHostToDevice, ctx->stream));
+  launch_unpool_switch((const float*)base, (const uint8_t*)(base + o1), B, H, W, C, 0, (float*)(base + o2), ctx->stream); ctx->launches++;
+  CHECK_LAUNCH(ctx);
+  CU(ctx, cudaMemcpyAsync(out, base + o2, nout * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+extern "C" int dcv_conv3x3(dcv_ctx* ctx, const float* x, const float* w_hwio, const float* bias, int B, int H, int W,
+                           int cin, int cout, int relu, float* out) {
+  ENTER(ctx);
+  if (!x || !w_hwio || !out || B <= 0 || H <= 0 || W <= 0 || cin <= 0 || cout <= 0) return ctx->fail(DCV_ERR_ARG, "dcv_conv3x3: bad arguments");
+  const size_t nin = (size_t)B * H * W * cin, nout = (size_t)B * H * W * cout, nw = (size_t)9 * cin * cout;
+  const size_t o1 = align256(nin * 4), o2 = o1 + align256(nw * 4), o3 = o2 + align256((size_t)cout * 4);
+  TRY(ctx->stage.ensure(ctx, o3 + nout * 4));
+  char* base = (char*)ctx->stage.p;
+  CU(ctx, cudaMemcpyAsync(base, x, nin * 4, cudaMemcpyHostToDevice, ctx->stream));
+  CU(ctx, cudaMemcpyAsync(base + o1, w_hwio, nw * 4, cudaMemcpyHostToDevice, ctx->stream));
+  if (bias) CU(ctx, cudaMemcpyAsync(base + o2, bias, (size_t)cout * 4, cudaMemcpyHostToDevice, ctx->stream));
+  ConvEpilogue e; e.bias = bias ? (const float*)(base + o2) : nullptr; e.relu = relu;
+  launch_conv3x3_fp32((const float*)base, (const float*)(base + o1), B, H, W, cin, cout, e, (float*)(base + o3), ctx->stream);
+  ctx->launches++;
+  CHECK_LAUNCH(ctx);
+  CU(ctx, cudaMemcpyAsync(out, base + o3, nout * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+extern "C" int dcv_deconv3x3(dcv_ctx* ctx, const float* x, const float* w_hwio, int B, int H, int W, int cin, int cout,
+                             int relu, int precision, float* out) {
+  ENTER(ctx);
+  if (!x || !w_hwio || !out || B <= 0 || H <= 0 || W <= 0 || cin <= 0 || cout <= 0) return ctx->fail(DCV_ERR_ARG, "dcv_deconv3x3: bad arguments");
+  if (precision != DCV_FP32 && precision != DCV_BF16) return ctx->fail(DCV_ERR_ARG, "dcv_deconv3x3: unknown precision");
+  const size_t nin = (size_t)B * H * W * cout, nout = (size_t)B * H * W * cin, nw = (size_t)9 * cin * cout;
+  const size_t o1 = align256(nin * 4), o2 = o1 + align256(nw * 4), o3 = o2 + align256(nw * 4);
+  TRY(ctx->stage.ensure(ctx, o3 + nout * 4));
+  char* base = (char*)ctx->stage.p;
+  CU(ctx, cudaMemcpyAsync(base, x, nin * 4, cudaMemcpyHostToDevice, ctx->stream));
+  CU(ctx, cudaMemcpyAsync(base + o1, w_hwio, nw * 4, cudaMemcpyHostToDevice, ctx->stream));
+  launch_flip_transpose((const float*)(base + o1), cin, cout, (float*)(base + o2), ctx->stream); ctx->launches++;
+  if (precision == DCV_BF16) {
+    Layer tmp;
+    tmp.kind = LK_CONV; tmp.cin = cin; tmp.cout = cout; tmp.relu = relu ? 1 : 0;
+    tmp.wd = (float*)(base + o2);
+    int r = tc_prepare_layer(ctx, tmp);
+    if (!r) r = tc_deconv(ctx, tmp, (const float*)base, B, H, W, (float*)(base + o3));
+    if (!r && cudaStreamSynchronize(ctx->stream) != cudaSuccess) r = ctx->fail(DCV_ERR_CUDA, "dcv_deconv3x3: kernel failed");
+    tc_free_layer(tmp);
+    if (r) return r;
+  } else {
+    ConvEpilogue e; e.relu = relu;
+    launch_conv3x3_fp32((const float*)base, (const float*)(base + o2), B, H, W, cout, cin, e, (float*)(base + o3), ctx->stream);
+    ctx->launches++;
+  }
+  CHECK_LAUNCH(ctx);
+  CU(ctx, cudaMemcpyAsync(out, base + o3, nout * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+extern "C" int dcv_activation(dcv_ctx* ctx, const float* x, int rows, int n, int act, float* out) {
+  ENTER(ctx);
+  if (!x || !out || rows < 0 || n < 0 || act < 0 || act > 2) return ctx->fail(DCV_ERR_ARG, "dcv_activation: bad arguments");
+  const size_t total = (size_t)rows * n;
+  if (total == 0) return 0;
+  TRY(ctx->stage.ensure(ctx, total * 4));
+  float* d = (float*)ctx->stage.p;
+  CU(ctx, cudaMemcpyAsync(d, x, total * 4, cudaMemcpyHostToDevice, ctx->stream));
+  if (act == DCV_ACT_RELU) { launch_relu(d, total, d, ctx->stream); ctx->launches++; }
+  if (act == DCV_ACT_SOFTMAX) { launch_softmax_rows(d, rows, n, d, ctx->stream); ctx->launches++; }
+  CHECK_LAUNCH(ctx);
+  CU(ctx, cudaMemcpyAsync(out, d, total * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+extern "C" int dcv_dense(dcv_ctx* ctx, const float* x, const float* w, const float* bias, int B, int nin, int nout,
+                         int act, float* out) {
+  ENTER(ctx);
+  if (!x || !w || !out || B <= 0 || nin <= 0 || nout <= 0 || act < 0 || act > 2) return ctx->fail(DCV_ERR_ARG, "dcv_dense: bad arguments");
+  const size_t o1 = align256((size_t)B * nin * 4), o2 = o1 + align256((size_t)nin * nout * 4);
+  const size_t o3 = o2 + align256((size_t)nout * 4), o4 = o3 + align256((size_t)dense_splits(nin) * B * nout * 4);
+  TRY(ctx->stage.ensure(ctx, o4 + (size_t)B * nout * 4));
+  char* base = (char*)ctx->stage.p;
+  CU(ctx, cudaMemcpyAsync(base, x, (size_t)B * nin * 4, cudaMemcpyHostToDevice, ctx->stream));
+  CU(ctx, cudaMemcpyAsync(base + o1, w, (size_t)nin * nout * 4, cudaMemcpyHostToDevice, ctx->stream));
+  if (bias) CU(ctx, cudaMemcpyAsync(base + o2, bias, (size_t)nout * 4, cudaMemcpyHostToDevice, ctx->stream));
+  float* od = (float*)(base + o4);
+  launch_dense_fwd((const float*)base, (const float*)(base + o1), bias ? (const float*)(base + o2) : nullptr, B, nin, nout,
+                   act, (float*)(base + o3), od, ctx->stream);
+  ctx->launches += 2;
+  if (act == DCV_ACT_SOFTMAX) { launch_softmax_rows(od, B, nout, od, ctx->stream); ctx->launches++; }
+  CHECK_LAUNCH(ctx);
+  CU(ctx, cudaMemcpyAsync(out, od, (size_t)B * nout * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+extern "C" int dcv_dense_transpose(dcv_ctx* ctx, const float* x, const float* w, int B, int nin, int nout, float* out) {
+  ENTER(ctx);
+  if (!x || !w || !out || B <= 0 || nin <= 0 || nout <= 0) return ctx->fail(DCV_ERR_ARG, "dcv_dense_transpose: bad arguments");
+  const size_t o1 = align256((size_t)B * nout * 4), o2 = o1 + align256((size_t)nin * nout * 4);
+  TRY(ctx->stage.ensure(ctx, o2 + (size_t)B * nin * 4));
+  char* base = (char*)ctx->stage.p;
+  CU(ctx, cudaMemcpyAsync(base, x, (size_t)B * nout * 4, cudaMemcpyHostToDevice, ctx->stream));
+  CU(ctx, cudaMemcpyAsync(base + o1, w, (size_t)nin * nout * 4, cudaMemcpyHostToDevice, ctx->stream));
+  launch_dense_bwd((const float*)base, (const float*)(base + o1), B, nin, nout, (float*)(base + o2), ctx->stream);
+  ctx->launches++;
+  CHECK_LAUNCH(ctx);
+  CU(ctx, cudaMemcpyAsync(out, base + o2, (size_t)B * nin * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  return 0;
+}

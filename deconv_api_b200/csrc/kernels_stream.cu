@@ -1,0 +1,581 @@
+// HBM-streaming kernels of the deconvnet path: max-pool with switches, switch-driven unpool,
+// per-channel sums, de-process, seed-map handling and the rank-1 first backward conv.
+// All of them are bandwidth-bound: 128-bit accesses along the NHWC channel axis, grids sized in
+// multiples of the SM count, no shared-memory staging (no reuse to exploit).
+#include "common.cuh"
+
+namespace dcv {
+
+static inline int grid_for(size_t work_items, int block, int max_waves = 16) {
+  size_t blocks = (work_items + block - 1) / block;
+  size_t cap = (size_t)kNumSMs * max_waves;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  return (int)blocks;
+}
+
+// ------------------------------------------------------------------------------------------------
+// 2x2/2 max-pool + switch (DPooling.up, deepdream.py:152-188).
+// One thread = VEC channels of one pooled pixel.  Strict '>' scan in the order (0,0),(0,1),(1,0),(1,1)
+// reproduces "first maximum in row-major order" (deepdream.py:180-183); an all-equal patch gives 0.
+// Algorithmic bytes per pooled element: 16 read + 4 written + 1 switch byte.
+template <int VEC>
+__global__ void __launch_bounds__(256) maxpool_switch_kernel(const float* __restrict__ x, int B, int H, int W, int C,
+                                                             float* __restrict__ pooled, uint8_t* __restrict__ sw) {
+  const int OH = H >> 1, OW = W >> 1;
+  const int CV = C / VEC;
+  const size_t total = (size_t)B * OH * OW * CV;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int cv = (int)(i % CV);
+    size_t p = i / CV;
+    const int ow = (int)(p % OW); p /= OW;
+    const int oh = (int)(p % OH);
+    const int b = (int)(p / OH);
+    const float* base = x + (((size_t)b * H + 2 * oh) * W + 2 * ow) * C + (size_t)cv * VEC;
+    float v[4][VEC];
+    if constexpr (VEC == 4) {
+      const float4 a0 = __ldg(reinterpret_cast<const float4*>(base));
+      const float4 a1 = __ldg(reinterpret_cast<const float4*>(base + C));
+      const float4 a2 = __ldg(reinterpret_cast<const float4*>(base + (size_t)W * C));
+      const float4 a3 = __ldg(reinterpret_cast<const float4*>(base + (size_t)W * C + C));
+      v[0][0] = a0.x; v[0][1] = a0.y; v[0][2] = a0.z; v[0][3] = a0.w;
+      v[1][0] = a1.x; v[1][1] = a1.y; v[1][2] = a1.z; v[1][3] = a1.w;
+      v[2][0] = a2.x; v[2][1] = a2.y; v[2][2] = a2.z; v[2][3] = a2.w;
+      v[3][0] = a3.x; v[3][1] = a3.y; v[3][2] = a3.z; v[3][3] = a3.w;
+    } else {
+#pragma unroll
+      for (int k = 0; k < VEC; ++k) {
+        v[0][k] = __ldg(base + k);
+        v[1][k] = __ldg(base + C + k);
+        v[2][k] = __ldg(base + (size_t)W * C + k);
+        v[3][k] = __ldg(base + (size_t)W * C + C + k);
+      }
+    }
+    float m[VEC];
+    uint8_t s[VEC];
+#pragma unroll
+    for (int k = 0; k < VEC; ++k) {
+      float best = v[0][k];
+      int idx = 0;
+      if (v[1][k] > best) { best = v[1][k]; idx = 1; }
+      if (v[2][k] > best) { best = v[2][k]; idx = 2; }
+      if (v[3][k] > best) { best = v[3][k]; idx = 3; }
+      m[k] = best;
+      s[k] = (uint8_t)idx;
+    }
+    const size_t o = (((size_t)b * OH + oh) * OW + ow) * C + (size_t)cv * VEC;
+    if constexpr (VEC == 4) {
+      *reinterpret_cast<float4*>(pooled + o) = make_float4(m[0], m[1], m[2], m[3]);
+      *reinterpret_cast<uchar4*>(sw + o) = make_uchar4(s[0], s[1], s[2], s[3]);
+    } else {
+#pragma unroll
+      for (int k = 0; k < VEC; ++k) { pooled[o + k] = m[k]; sw[o + k] = s[k]; }
+    }
+  }
+}
+
+void launch_maxpool_switch(const float* x, int B, int H, int W, int C, float* pooled, uint8_t* sw, cudaStream_t s) {
+  const size_t outs = (size_t)B * (H / 2) * (W / 2);
+  if (outs == 0 || C == 0) return;
+  if (C % 4 == 0) {
+    maxpool_switch_kernel<4><<<grid_for(outs * (C / 4), 256), 256, 0, s>>>(x, B, H, W, C, pooled, sw);
+  } else {
+    maxpool_switch_kernel<1><<<grid_for(outs * C, 256), 256, 0, s>>>(x, B, H, W, C, pooled, sw);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Switch-driven unpool (DPooling.down, deepdream.py:191-209) as a gather: one thread owns VEC
+// channels of one pooled pixel and writes its whole 2x2 output quad (value at the switch position,
+// zeros elsewhere) with coalesced 128-bit stores, so there are no atomics and no pre-zeroing.
+// (H,W) is the OUTPUT size; rows/cols beyond 2*(H/2), 2*(W/2) (odd sizes, DeepDream only) are zeroed.
+// `item % Bsw` selects the switch image, so P = n*B projection items can share B switch tensors.
+template <int VEC>
+__global__ void __launch_bounds__(256) unpool_switch_kernel(const float* __restrict__ x, const uint8_t* __restrict__ sw,
+                                                            int P, int Bsw, int H, int W, int C, int relu,
+                                                            float* __restrict__ out) {
+  const int OH = (H + 1) >> 1, OW = (W + 1) >> 1;   // quads incl. the partial ones at odd borders
+  const int PH = H >> 1, PW = W >> 1;               // pooled size
+  const int CV = C / VEC;
+  const size_t total = (size_t)P * OH * OW * CV;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int cv = (int)(i % CV);
+    size_t p = i / CV;
+    const int ow = (int)(p % OW); p /= OW;
+    const int oh = (int)(p % OH);
+    const int item = (int)(p / OH);
+    float v[VEC];
+    int sidx[VEC];
+    const bool inside = (oh < PH) && (ow < PW);
+    if (inside) {
+      const size_t pi = (((size_t)item * PH + oh) * PW + ow) * C + (size_t)cv * VEC;
+      const size_t si = (((size_t)(item % Bsw) * PH + oh) * PW + ow) * C + (size_t)cv * VEC;
+      if constexpr (VEC == 4) {
+        const float4 a = __ldg(reinterpret_cast<const float4*>(x + pi));
+        const uchar4 q = __ldg(reinterpret_cast<const uchar4*>(sw + si));
+        v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
+        sidx[0] = q.x; sidx[1] = q.y; sidx[2] = q.z; sidx[3] = q.w;
+      } else {
+#pragma unroll
+        for (int k = 0; k < VEC; ++k) { v[k] = __ldg(x + pi + k); sidx[k] = __ldg(sw + si + k); }
+      }
+      if (relu) {
+#pragma unroll
+        for (int k = 0; k < VEC; ++k) v[k] = fmaxf(v[k], 0.f);
+      }
+    } else {
+#pragma unroll
+      for (int k = 0; k < VEC; ++k) { v[k] = 0.f; sidx[k] = -1; }
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int y = 2 * oh + (q >> 1), xx = 2 * ow + (q & 1);
+      if (y >= H || xx >= W) continue;
+      const size_t o = (((size_t)item * H + y) * W + xx) * C + (size_t)cv * VEC;
+      float r[VEC];
+#pragma unroll
+      for (int k = 0; k < VEC; ++k) r[k] = (sidx[k] == q) ? v[k] : 0.f;
+      if constexpr (VEC == 4) {
+        *reinterpret_cast<float4*>(out + o) = make_float4(r[0], r[1], r[2], r[3]);
+      } else {
+#pragma unroll
+        for (int k = 0; k < VEC; ++k) out[o + k] = r[k];
+      }
+    }
+  }
+}
+
+// P items, switches of B images (item % B)
+void launch_unpool_switch_items(const float* x, const uint8_t* sw, int P, int Bsw, int H, int W, int C, int relu,
+                                float* out, cudaStream_t s) {
+  const size_t quads = (size_t)P * ((H + 1) / 2) * ((W + 1) / 2);
+  if (quads == 0 || C == 0) return;
+  if (C % 4 == 0) {
+    unpool_switch_kernel<4><<<grid_for(quads * (C / 4), 256), 256, 0, s>>>(x, sw, P, Bsw, H, W, C, relu, out);
+  } else {
+    unpool_switch_kernel<1><<<grid_for(quads * C, 256), 256, 0, s>>>(x, sw, P, Bsw, H, W, C, relu, out);
+  }
+}
+
+void launch_unpool_switch(const float* x, const uint8_t* sw, int B, int H, int W, int C, int relu, float* out,
+                          cudaStream_t s) {
+  launch_unpool_switch_items(x, sw, B, B, H, W, C, relu, out, s);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Per-channel fp64 sums of a (rows, C) fp32 matrix (find_top_filters, deepdream.py:369-380).
+// Stage 1: block (32 x 8) strides over rows; thread x = channel lane (coalesced), 8 row lanes;
+// partial[blockIdx.y][c].  Stage 2: one thread per channel adds the partials in fixed order, so
+// the result is deterministic.
+__global__ void __launch_bounds__(256) channel_sums_stage1(const float* __restrict__ x, size_t rows, int C,
+                                                           double* __restrict__ partial) {
+  __shared__ double red[8][33];
+  const int c = blockIdx.x * 32 + threadIdx.x;
+  double acc = 0.0;
+  if (c < C) {
+    for (size_t r = (size_t)blockIdx.y * 8 + threadIdx.y; r < rows; r += (size_t)gridDim.y * 8)
+      acc += (double)__ldg(x + r * C + c);
+  }
+  red[threadIdx.y][threadIdx.x] = acc;
+  __syncthreads();
+  if (threadIdx.y == 0 && c < C) {
+    double t = 0.0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) t += red[k][threadIdx.x];
+    partial[(size_t)blockIdx.y * C + c] = t;
+  }
+}
+
+__global__ void channel_sums_stage2(const double* __restrict__ partial, int npartial, int C, double* __restrict__ out) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  double t = 0.0;
+  for (int k = 0; k < npartial; ++k) t += partial[(size_t)k * C + c];
+  out[c] = t;
+}
+
+int channel_sums_partials(size_t rows, int C) {
+  const int xb = (C + 31) / 32;
+  size_t want = (size_t)(4 * kNumSMs + xb - 1) / xb;          // ~4 blocks per SM in total
+  size_t maxy = (rows + 7) / 8;
+  if (want > maxy) want = maxy;
+  if (want < 1) want = 1;
+  return (int)want;
+}
+
+void launch_channel_sums(const float* x, size_t rows, int C, double* partial, int npartial, double* out, cudaStream_t s) {
+  dim3 grid((C + 31) / 32, npartial), block(32, 8);
+  channel_sums_stage1<<<grid, block, 0, s>>>(x, rows, C, partial);
+  channel_sums_stage2<<<(C + 127) / 128, 128, 0, s>>>(partial, npartial, C, out);
+}
+
+// ------------------------------------------------------------------------------------------------
+// De-process (deprocess_image, deepdream.py:483-498).  Pass 1: fp64 sum and sum of squares (block
+// partials in scratch, fixed-order final reduce inside pass 2's prologue).  Pass 2: the elementwise
+// map in fp32, op by op in the reference's order.
+__global__ void __launch_bounds__(256) deprocess_stats_kernel(const float* __restrict__ x, size_t n,
+                                                              double* __restrict__ partial) {
+  double s = 0.0, q = 0.0;
+  const size_t n4 = n / 4;
+  const float4* x4 = reinterpret_cast<const float4*>(x);
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
+    const float4 a = __ldg(x4 + i);
+    s += (double)a.x + (double)a.y + (double)a.z + (double)a.w;
+    q += (double)a.x * a.x + (double)a.y * a.y + (double)a.z * a.z + (double)a.w * a.w;
+  }
+  if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {
+    const float a = x[n4 * 4 + threadIdx.x];
+    s += a; q += (double)a * a;
+  }
+  __shared__ double rs[8], rq[8];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    s += __shfl_xor_sync(0xffffffffu, s, o);
+    q += __shfl_xor_sync(0xffffffffu, q, o);
+  }
+  if ((threadIdx.x & 31) == 0) { rs[threadIdx.x >> 5] = s; rq[threadIdx.x >> 5] = q; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double ts = 0.0, tq = 0.0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) { ts += rs[k]; tq += rq[k]; }
+    partial[2 * blockIdx.x] = ts;
+    partial[2 * blockIdx.x + 1] = tq;
+  }
+}
+
+__device__ __forceinline__ float deprocess_norm(float v, float mean, float denom) {
+  v = v - mean;            // x -= x.mean()
+  v = v / denom;           // x /= (x.std() + epsilon)
+  v = v * 0.1f;            // x *= 0.1
+  v = v + 0.5f;            // x += 0.5
+  return v;
+}
+
+__device__ __forceinline__ uint8_t deprocess_one(float v, float mean, float denom) {
+  v = deprocess_norm(v, mean, denom);
+  v = fminf(fmaxf(v, 0.f), 1.f);
+  v = v * 255.f;
+  v = fminf(fmaxf(v, 0.f), 255.f);
+  return (uint8_t)v;       // astype('uint8') truncates
+}
+
+__global__ void __launch_bounds__(256) deprocess_map_kernel(const float* __restrict__ x, size_t n,
+                                                            const double* __restrict__ partial, int npartial,
+                                                            uint8_t* __restrict__ out, float* __restrict__ norm) {
+  __shared__ float sh[2];
+  if (threadIdx.x == 0) {
+    double ts = 0.0, tq = 0.0;
+    for (int k = 0; k < npartial; ++k) { ts += partial[2 * k]; tq += partial[2 * k + 1]; }
+    const double mean = ts / (double)n;
+    double var = tq / (double)n - mean * mean;      // population variance (ddof = 0)
+    if (var < 0.0) var = 0.0;
+    // std of the CENTRED data equals std of x; the reference adds K.epsilon() = 1e-7 to it
+    sh[0] = (float)mean;
+    sh[1] = (float)(sqrt(var) + 1e-7);
+  }
+  __syncthreads();
+  const float mean = sh[0], denom = sh[1];
+  const size_t n4 = n / 4;
+  const float4* x4 = reinterpret_cast<const float4*>(x);
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
+    const float4 a = __ldg(x4 + i);
+    uchar4 r;
+    r.x = deprocess_one(a.x, mean, denom);
+    r.y = deprocess_one(a.y, mean, denom);
+    r.z = deprocess_one(a.z, mean, denom);
+    r.w = deprocess_one(a.w, mean, denom);
+    reinterpret_cast<uchar4*>(out)[i] = r;
+    if (norm)
+      reinterpret_cast<float4*>(norm)[i] = make_float4(deprocess_norm(a.x, mean, denom), deprocess_norm(a.y, mean, denom),
+                                                       deprocess_norm(a.z, mean, denom), deprocess_norm(a.w, mean, denom));
+  }
+  if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {
+    const size_t j = n4 * 4 + threadIdx.x;
+    out[j] = deprocess_one(x[j], mean, denom);
+    if (norm) norm[j] = deprocess_norm(x[j], mean, denom);
+  }
+}
+
+int deprocess_partials(size_t n) {
+  return grid_for((n + 3) / 4, 256, 4);
+}
+
+void launch_deprocess(const float* x, size_t n, double* partial, int npartial, uint8_t* out, float* norm,
+                      cudaStream_t s) {
+  deprocess_stats_kernel<<<npartial, 256, 0, s>>>(x, n, partial);
+  deprocess_map_kernel<<<grid_for((n + 3) / 4, 256, 8), 256, 0, s>>>(x, n, partial, npartial, out, norm);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Seed maps of the projections (deepdream.py:450-465): map[(k*B+b), y, x] = act[b, y, x, feat[k]].
+__global__ void gather_map_kernel(const float* __restrict__ act, int B, size_t HW, int C,
+                                  const int* __restrict__ feat, int n, float* __restrict__ maps) {
+  const size_t total = (size_t)n * B * HW;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const size_t pix = i % HW;
+    const size_t item = i / HW;
+    const int b = (int)(item % B), k = (int)(item / B);
+    maps[i] = __ldg(act + ((size_t)b * HW + pix) * C + feat[k]);
+  }
+}
+
+void launch_gather_map(const float* act, int B, int H, int W, int C, const int* feat_dev, int n, float* maps,
+                       cudaStream_t s) {
+  const size_t total = (size_t)n * B * H * W;
+  if (!total) return;
+  gather_map_kernel<<<grid_for(total, 256), 256, 0, s>>>(act, B, (size_t)H * W, C, feat_dev, n, maps);
+}
+
+// 'max' visualize mode (deepdream.py:454-457): keep the entries equal to the map maximum.  One
+// block per map; activations are >= 0 so the int-ordered max of the float bits would do, but a plain
+// float reduction keeps it general.
+__global__ void __launch_bounds__(256) keep_max_kernel(float* __restrict__ maps, size_t len) {
+  float* m = maps + (size_t)blockIdx.x * len;
+  float best = -INFINITY;
+  for (size_t i = threadIdx.x; i < len; i += blockDim.x) best = fmaxf(best, m[i]);
+  __shared__ float red[8];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) best = fmaxf(best, __shfl_xor_sync(0xffffffffu, best, o));
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = best;
+  __syncthreads();
+  best = red[0];
+#pragma unroll
+  for (int k = 1; k < 8; ++k) best = fmaxf(best, red[k]);
+  for (size_t i = threadIdx.x; i < len; i += blockDim.x) {
+    const float v = m[i];
+    m[i] = (v == best) ? v : 0.f;
+  }
+}
+
+void launch_keep_max(float* maps, int n, size_t len, float*, cudaStream_t s) {
+  if (n <= 0 || len == 0) return;
+  keep_max_kernel<<<n, 256, 0, s>>>(maps, len);
+}
+
+// Unpool of single-channel maps with channel feat[k] of the switches: (n*B, h, w) -> (n*B, H, W).
+__global__ void unpool_map_kernel(const float* __restrict__ maps, const uint8_t* __restrict__ sw, int B, int h, int w,
+                                  int H, int W, int C, const int* __restrict__ feat, int n, float* __restrict__ out) {
+  const size_t total = (size_t)n * B * H * W;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int x = (int)(i % W);
+    size_t p = i / W;
+    const int y = (int)(p % H);
+    const size_t item = p / H;
+    const int b = (int)(item % B), k = (int)(item / B);
+    const int py = y >> 1, px = x >> 1;
+    float r = 0.f;
+    if (py < h && px < w) {
+      const int q = ((y & 1) << 1) | (x & 1);
+      const uint8_t sidx = __ldg(sw + (((size_t)b * h + py) * w + px) * C + feat[k]);
+      if (sidx == q) r = __ldg(maps + (item * h + py) * w + px);
+    }
+    out[i] = r;
+  }
+}
+
+void launch_unpool_map(const float* maps, const uint8_t* sw, int B, int h, int w, int C, const int* feat_dev, int n,
+                       float* out, cudaStream_t s) {
+  // output size is exactly (2h, 2w): the deconvnet path only sees even sizes
+  const size_t total = (size_t)n * B * (2 * h) * (2 * w);
+  if (!total) return;
+  unpool_map_kernel<<<grid_for(total, 256), 256, 0, s>>>(maps, sw, B, h, w, 2 * h, 2 * w, C, feat_dev, n, out);
+}
+
+// Expand maps into channel feat[k] of an otherwise zero (n*B, H, W, C) tensor (only needed when the
+// projected layer has no conv below it).
+__global__ void scatter_map_kernel(const float* __restrict__ maps, size_t HW, int C, int B, const int* __restrict__ feat,
+                                   size_t total, float* __restrict__ out) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C);
+    const size_t pi = i / C;              // item*HW + pix
+    const int k = (int)((pi / HW) / B);
+    out[i] = (c == feat[k]) ? maps[pi] : 0.f;
+  }
+}
+
+void launch_scatter_map(const float* maps, int n, int B, int H, int W, int C, const int* feat_dev, float* out,
+                        cudaStream_t s) {
+  const size_t total = (size_t)n * B * H * W * C;
+  if (!total) return;
+  scatter_map_kernel<<<grid_for(total, 256), 256, 0, s>>>(maps, (size_t)H * W, C, B, feat_dev, total, out);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Rank-1 first backward conv (a3 in SURVEY.md §8a): the projected tensor has ONE non-zero channel f,
+// so relu(conv3x3_same(x, flipT(W)))[p, ci] = relu(sum_tap map[p + tap] * wd[tap][f][ci]).
+// One block = 64 pixels of one item; the 9 x cin weight slice sits in shared memory; thread layout
+// (cin lane, pixel lane) keeps the NHWC stores coalesced.  9*H*W*cin MACs instead of 9*H*W*cin*cout.
+__global__ void __launch_bounds__(256) rank1_deconv_kernel(const float* __restrict__ maps, const float* __restrict__ wd,
+                                                           int cout, int cin, const int* __restrict__ feat, int B,
+                                                           int H, int W, int relu, float* __restrict__ out) {
+  extern __shared__ float smem[];
+  float* wsl = smem;                 // [9][cin]
+  float* tap = smem + 9 * cin;       // [64][9] map values around each pixel
+  const int item = blockIdx.y;
+  const int f = feat[item / B];
+  for (int i = threadIdx.x; i < 9 * cin; i += blockDim.x) {
+    const int t = i / cin, ci = i % cin;
+    wsl[i] = __ldg(wd + ((size_t)t * cout + f) * cin + ci);
+  }
+  const int HW = H * W;
+  const int p0 = blockIdx.x * 64;
+  const float* m = maps + (size_t)item * HW;
+  for (int i = threadIdx.x; i < 64 * 9; i += blockDim.x) {
+    const int pp = i / 9, t = i % 9;
+    const int p = p0 + pp;
+    float v = 0.f;
+    if (p < HW) {
+      const int y = p / W + t / 3 - 1, x = p % W + t % 3 - 1;
+      if (y >= 0 && y < H && x >= 0 && x < W) v = __ldg(m + y * W + x);
+    }
+    tap[i] = v;
+  }
+  __syncthreads();
+  const size_t obase = ((size_t)item * HW + p0) * cin;
+  const int total = 64 * cin;
+  for (int i = threadIdx.x; i < total; i += blockDim.x) {
+    const int pp = i / cin, ci = i % cin;
+    if (p0 + pp >= HW) break;
+    float acc = 0.f;
+#pragma unroll
+    for (int t = 0; t < 9; ++t) acc = fmaf(tap[pp * 9 + t], wsl[t * cin + ci], acc);
+    if (relu) acc = fmaxf(acc, 0.f);
+    out[obase + i] = acc;
+  }
+}
+
+void launch_rank1_deconv(const float* maps, const float* wd, int cout, int cin, const int* feat_dev, int n, int B,
+                         int H, int W, int relu, float* out, cudaStream_t s) {
+  if (n * B == 0) return;
+  dim3 grid((H * W + 63) / 64, n * B);
+  const size_t smem = (size_t)(9 * cin + 64 * 9) * sizeof(float);
+  rank1_deconv_kernel<<<grid, 256, smem, s>>>(maps, wd, cout, cin, feat_dev, B, H, W, relu, out);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Weight preparation (DConvolution2D.__init__, deepdream.py:80-81): W (3,3,cin,cout) HWIO ->
+// wd[kh][kw][co][ci] = W[2-kh][2-kw][ci][co], i.e. transpose(0,1,3,2) then flip both spatial axes.
+__global__ void flip_transpose_kernel(const float* __restrict__ w, int cin, int cout, float* __restrict__ wd) {
+  const size_t total = (size_t)9 * cin * cout;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int ci = (int)(i % cin);
+    size_t p = i / cin;
+    const int co = (int)(p % cout);
+    const int t = (int)(p / cout);
+    wd[i] = __ldg(w + ((size_t)(8 - t) * cin + ci) * cout + co);
+  }
+}
+
+void launch_flip_transpose(const float* w_hwio, int cin, int cout, float* wd, cudaStream_t s) {
+  flip_transpose_kernel<<<grid_for((size_t)9 * cin * cout, 256), 256, 0, s>>>(w_hwio, cin, cout, wd);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Dense layers (DDense, deepdream.py:264-321).  Batch is 1 in the API, so both directions are
+// matrix-vector products bound by reading W once from HBM.
+// forward: out[b][j] = act(sum_i x[b][i] W[i][j] + bias[j]); W rows are contiguous in j, so lanes
+// run along j and blockIdx.y splits i; partials are reduced in a fixed order by stage 2.
+__global__ void __launch_bounds__(256) dense_fwd_stage1(const float* __restrict__ x, const float* __restrict__ w,
+                                                        int nin, int nout, int chunk, float* __restrict__ partial) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  const int b = blockIdx.z;
+  const int i0 = blockIdx.y * chunk;
+  const int i1 = min(nin, i0 + chunk);
+  if (j >= nout) return;
+  float acc = 0.f;
+  const float* xb = x + (size_t)b * nin;
+  for (int i = i0; i < i1; ++i) acc = fmaf(__ldg(xb + i), __ldg(w + (size_t)i * nout + j), acc);
+  partial[((size_t)blockIdx.y * gridDim.z + b) * nout + j] = acc;
+}
+
+__global__ void dense_fwd_stage2(const float* __restrict__ partial, int nsplit, int B, int nout,
+                                 const float* __restrict__ bias, int act, float* __restrict__ out) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  const int b = blockIdx.y;
+  if (j >= nout) return;
+  float acc = 0.f;
+  for (int k = 0; k < nsplit; ++k) acc += partial[((size_t)k * B + b) * nout + j];
+  if (bias) acc += bias[j];
+  if (act == DCV_ACT_RELU) acc = fmaxf(acc, 0.f);
+  out[(size_t)b * nout + j] = acc;
+}
+
+int dense_splits(int nin) {
+  int s = (nin + 255) / 256;
+  if (s > 128) s = 128;
+  return s < 1 ? 1 : s;
+}
+
+void launch_dense_fwd(const float* x, const float* w, const float* bias, int B, int nin, int nout, int act,
+                      float* partial, float* out, cudaStream_t s) {
+  const int ns = dense_splits(nin);
+  const int chunk = (nin + ns - 1) / ns;
+  dim3 g1((nout + 255) / 256, ns, B);
+  dense_fwd_stage1<<<g1, 256, 0, s>>>(x, w, nin, nout, chunk, partial);
+  dim3 g2((nout + 255) / 256, B);
+  dense_fwd_stage2<<<g2, 256, 0, s>>>(partial, ns, B, nout, bias, act, out);
+}
+
+// backward: out[b][i] = sum_j x[b][j] W[i][j]  (x W^T, deepdream.py:289-297).  One warp per row i.
+__global__ void __launch_bounds__(256) dense_bwd_kernel(const float* __restrict__ x, const float* __restrict__ w,
+                                                        int nin, int nout, float* __restrict__ out) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  const int b = blockIdx.y;
+  if (warp >= nin) return;
+  const float* wr = w + (size_t)warp * nout;
+  const float* xb = x + (size_t)b * nout;
+  float acc = 0.f;
+  for (int j = lane; j < nout; j += 32) acc = fmaf(__ldg(xb + j), __ldg(wr + j), acc);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if (lane == 0) out[(size_t)b * nin + warp] = acc;
+}
+
+void launch_dense_bwd(const float* x, const float* w, int B, int nin, int nout, float* out, cudaStream_t s) {
+  dim3 g((nin + 7) / 8, B);
+  dense_bwd_kernel<<<g, 256, 0, s>>>(x, w, nin, nout, out);
+}
+
+// row softmax (one block per row), used for 'predictions' in both directions (deepdream.py:226-235)
+__global__ void __launch_bounds__(256) softmax_rows_kernel(const float* __restrict__ x, int n, float* __restrict__ out) {
+  const float* r = x + (size_t)blockIdx.x * n;
+  float* o = out + (size_t)blockIdx.x * n;
+  __shared__ float red[8];
+  float m = -INFINITY;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) m = fmaxf(m, r[i]);
+#pragma unroll
+  for (int k = 16; k > 0; k >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, k));
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = m;
+  __syncthreads();
+  m = red[0];
+#pragma unroll
+  for (int k = 1; k < 8; ++k) m = fmaxf(m, red[k]);
+  __syncthreads();
+  float sum = 0.f;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) sum += expf(r[i] - m);
+#pragma unroll
+  for (int k = 16; k > 0; k >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, k);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = sum;
+  __syncthreads();
+  sum = 0.f;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) sum += red[k];
+  for (int i = threadIdx.x; i < n; i += blockDim.x) o[i] = expf(r[i] - m) / sum;
+}
+
+void launch_softmax_rows(const float* x, int B, int n, float* out, cudaStream_t s) {
+  if (B > 0) softmax_rows_kernel<<<B, 256, 0, s>>>(x, n, out);
+}
+
+__global__ void relu_kernel(const float* __restrict__ x, size_t n, float* __restrict__ out) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    out[i] = fmaxf(x[i], 0.f);
+}
+
+void launch_relu(const float* x, size_t n, float* out, cudaStream_t s) {
+  if (n) relu_kernel<<<grid_for(n, 256), 256, 0, s>>>(x, n, out);
+}
+
+}  // namespace dcv

