@@ -137,6 +137,48 @@ extern "C" int dcv_sync(dcv_ctx* ctx) {
   return 0;
 }
 
+// ---- per-class kernel timing -------------------------------------------------------------------------
+void dcv_ctx::prof_begin(int cat, double flops, double bytes) {
+  ProfRec r;
+  r.cat = cat; r.flops = flops; r.bytes = bytes;
+  for (cudaEvent_t* e : {&r.a, &r.b}) {
+    if (!ev_pool.empty()) { *e = ev_pool.back(); ev_pool.pop_back(); }
+    else cudaEventCreate(e);
+  }
+  cudaEventRecord(r.a, stream);
+  prof.push_back(r);
+}
+
+void dcv_ctx::prof_end() { cudaEventRecord(prof.back().b, stream); }
+
+extern "C" int dcv_profile(dcv_ctx* ctx, int enable) {
+  ENTER(ctx);
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  for (auto& r : ctx->prof) { ctx->ev_pool.push_back(r.a); ctx->ev_pool.push_back(r.b); }
+  ctx->prof.clear();
+  ctx->prof_on = enable != 0;
+  return 0;
+}
+
+extern "C" int dcv_profile_read(dcv_ctx* ctx, int cat, double* ms, long long* launches, double* flops, double* bytes) {
+  ENTER(ctx);
+  if (cat < 0 || cat >= DCV_K_NUM) return ctx->fail(DCV_ERR_ARG, "dcv_profile_read: unknown kernel class %d", cat);
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  double t = 0, f = 0, by = 0;
+  long long n = 0;
+  for (auto& r : ctx->prof) {
+    if (r.cat != cat) continue;
+    float e = 0.f;
+    CU(ctx, cudaEventElapsedTime(&e, r.a, r.b));
+    t += e; f += r.flops; by += r.bytes; ++n;
+  }
+  if (ms) *ms = t;
+  if (launches) *launches = n;
+  if (flops) *flops = f;
+  if (bytes) *bytes = by;
+  return 0;
+}
+
 // ---- network description --------------------------------------------------------------------------
 extern "C" int dcv_net_clear(dcv_ctx* ctx) {
   ENTER(ctx);
@@ -226,7 +268,11 @@ static int forward_impl(dcv_ctx* ctx, const float* img, bool on_device, int B, i
         if (l.cin != cc) return ctx->fail(DCV_ERR_ARG, "layer %d: expects %d input channels, got %d", j, l.cin, cc);
         TRY(l.act.ensure(ctx, (size_t)cb * ch * cw * l.cout * sizeof(float)));
         ConvEpilogue e; e.bias = l.bias; e.relu = l.relu;
-        launch_conv3x3_fp32(cur, l.w, cb, ch, cw, l.cin, l.cout, e, (float*)l.act.p, ctx->stream); ctx->launches++;
+        {
+          ProfScope ps(ctx, DCV_K_CONV_FP32, 2.0 * 9 * cb * ch * cw * (double)l.cin * l.cout,
+                       4.0 * cb * ch * cw * ((double)l.cin + l.cout));
+          launch_conv3x3_fp32(cur, l.w, cb, ch, cw, l.cin, l.cout, e, (float*)l.act.p, ctx->stream); ctx->launches++;
+        }
         cc = l.cout;
         break;
       }
@@ -236,7 +282,11 @@ static int forward_impl(dcv_ctx* ctx, const float* img, bool on_device, int B, i
         if (oh == 0 || ow == 0) return ctx->fail(DCV_ERR_ARG, "layer %d: input %dx%d too small to pool", j, ch, cw);
         TRY(l.act.ensure(ctx, (size_t)cb * oh * ow * cc * sizeof(float)));
         TRY(l.sw.ensure(ctx, (size_t)cb * oh * ow * cc));
-        launch_maxpool_switch(cur, cb, ch, cw, cc, (float*)l.act.p, (uint8_t*)l.sw.p, ctx->stream); ctx->launches++;
+        {
+          // algorithmic bytes: 4*HWC read + 5*HWC/4 written
+          ProfScope ps(ctx, DCV_K_POOL, 0.0, (double)cb * ch * cw * cc * (4.0 + 5.0 / 4.0));
+          launch_maxpool_switch(cur, cb, ch, cw, cc, (float*)l.act.p, (uint8_t*)l.sw.p, ctx->stream); ctx->launches++;
+        }
         l.in_H = ch; l.in_W = cw;
         ch = oh; cw = ow;
         break;
@@ -436,9 +486,12 @@ static int project_chunk(dcv_ctx* ctx, int layer, int foff, int n, int vis_mode,
       if ((l.in_H & 1) || (l.in_W & 1))
         return ctx->fail(DCV_ERR_ARG, "unpool of layer %d: odd input size %dx%d (the reference raises here too)", j, l.in_H, l.in_W);
       if (mode == M_MAP) {
+        ProfScope ps(ctx, DCV_K_UNPOOL, 0.0, (double)P * h * w * (5.0 + 16.0));
         launch_unpool_map(maps, (const uint8_t*)l.sw.p, B, h, w, C, feat, n, maps2, ctx->stream); ctx->launches++;
         std::swap(maps, maps2);
       } else {
+        // algorithmic bytes: 5*HWC/4 read + 4*HWC written, (H,W) = unpooled size
+        ProfScope ps(ctx, DCV_K_UNPOOL, 0.0, (double)P * l.in_H * l.in_W * C * (4.0 + 5.0 / 4.0));
         launch_unpool_switch_items(bufs[cur], (const uint8_t*)l.sw.p, P, B, l.in_H, l.in_W, C, 0, bufs[cur ^ 1], ctx->stream);
         ctx->launches++;
         cur ^= 1;
@@ -449,14 +502,19 @@ static int project_chunk(dcv_ctx* ctx, int layer, int foff, int n, int vis_mode,
       if (l.cout != C) return ctx->fail(DCV_ERR_STATE, "chain: layer %d has %d outputs, data has %d channels", j, l.cout, C);
       if (mode == M_MAP) {
         if (j != layer && l.relu) TRY(ensure_nonneg(ctx, nonneg, maps, (size_t)P * h * w));
-        launch_rank1_deconv(maps, l.wd, l.cout, l.cin, feat, n, B, h, w, l.relu, bufs[cur], ctx->stream); ctx->launches++;
+        {
+          ProfScope ps(ctx, DCV_K_RANK1, 2.0 * 9 * P * h * w * (double)l.cin, 4.0 * P * h * w * (1.0 + l.cin));
+          launch_rank1_deconv(maps, l.wd, l.cout, l.cin, feat, n, B, h, w, l.relu, bufs[cur], ctx->stream); ctx->launches++;
+        }
         mode = M_TENSOR;
       } else {
         if (j != layer && l.relu) TRY(ensure_nonneg(ctx, nonneg, bufs[cur], (size_t)P * h * w * C));
+        const double fl = 2.0 * 9 * P * h * w * (double)l.cin * l.cout;
         if (precision == DCV_BF16) {
           TRY(tc_deconv(ctx, l, bufs[cur], P, h, w, bufs[cur ^ 1]));
         } else {
           ConvEpilogue e; e.relu = l.relu;
+          ProfScope ps(ctx, DCV_K_CONV_FP32, fl, 4.0 * P * h * w * ((double)l.cin + l.cout));
           // backward conv: input channels = l.cout, output channels = l.cin, weights wd [9][cout][cin]
           launch_conv3x3_fp32(bufs[cur], l.wd, P, h, w, l.cout, l.cin, e, bufs[cur ^ 1], ctx->stream); ctx->launches++;
         }

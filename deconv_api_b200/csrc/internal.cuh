@@ -33,6 +33,12 @@ struct Layer {
   DevBuf sw;                           // pool: switches, 1 byte per pooled element
 };
 
+struct ProfRec {
+  cudaEvent_t a, b;
+  int cat;
+  double flops, bytes;
+};
+
 struct dcv_ctx {
   int device = 0;
   int num_sms = dcv::kNumSMs;
@@ -48,7 +54,19 @@ struct dcv_ctx {
   DevBuf feat_dev;
   DevBuf scratch;      // reduction partials
   DevBuf stage;        // staging for host-buffer entry points
+  // optional per-kernel-class timing (dcv_profile): CUDA events around every launch of a class
+  bool prof_on = false;
+  std::vector<ProfRec> prof;
+  std::vector<cudaEvent_t> ev_pool;
+  void prof_begin(int cat, double flops, double bytes);
+  void prof_end();
   int fail(int code, const char* fmt, ...);
+};
+
+struct ProfScope {
+  dcv_ctx* c;
+  ProfScope(dcv_ctx* ctx, int cat, double flops, double bytes) : c(ctx) { if (c->prof_on) c->prof_begin(cat, flops, bytes); }
+  ~ProfScope() { if (c->prof_on) c->prof_end(); }
 };
 
 // conv_tc.cu

@@ -311,6 +311,8 @@ def visualize_all_layers(model, data, layer_name='predictions', visualize_mode='
     # the reference's stacking loop stops AFTER the layer called layer_name; an unknown name never
     # breaks, so every layer is stacked and visualised
     last = names.index(layer_name) if layer_name in names else len(names) - 1
+    if last == 0:
+        return dict()            # only the input layer was stacked; it is popped (deepdream.py:437)
     eng = m.bound_engine(device, upto=names[last])
     data = np.ascontiguousarray(data, dtype=np.float32)
     prec = precision or DEFAULT_PRECISION

@@ -75,6 +75,22 @@ class Engine(object):
     def stream(self):
         return self.lib.dcv_stream(self.ctx)
 
+    # -- per-kernel-class timing
+    KERNEL_CLASSES = ("conv_fp32", "conv_tc", "pool", "unpool", "rank1", "other")
+
+    def profile(self, enable=True):
+        self._ck(self.lib.dcv_profile(self.ctx, 1 if enable else 0))
+
+    def profile_read(self):
+        """-> {class: dict(ms, launches, flops, bytes)} for the launches since profile(True)."""
+        out = {}
+        for i, name in enumerate(self.KERNEL_CLASSES):
+            ms, fl, by = ctypes.c_double(), ctypes.c_double(), ctypes.c_double()
+            n = ctypes.c_longlong()
+            self._ck(self.lib.dcv_profile_read(self.ctx, i, ctypes.byref(ms), ctypes.byref(n), ctypes.byref(fl), ctypes.byref(by)))
+            out[name] = dict(ms=ms.value, launches=n.value, flops=fl.value, bytes=by.value)
+        return out
+
     # -- network
     def clear(self):
         self._ck(self.lib.dcv_net_clear(self.ctx))

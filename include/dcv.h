@@ -67,6 +67,22 @@ DCV_API long long dcv_launch_count(const dcv_ctx* ctx);
 /* The context's cudaStream_t, as an opaque pointer (for event timing by the caller). */
 DCV_API void* dcv_stream(const dcv_ctx* ctx);
 
+/* Kernel classes for dcv_profile_read. */
+enum dcv_kernel_class {
+  DCV_K_CONV_FP32 = 0,  /* FFMA 3x3 conv / backward conv */
+  DCV_K_CONV_TC = 1,    /* tcgen05 implicit-GEMM backward conv */
+  DCV_K_POOL = 2,       /* max-pool + switch */
+  DCV_K_UNPOOL = 3,     /* switch-driven unpool (tensor and single-map forms) */
+  DCV_K_RANK1 = 4,      /* rank-1 first backward conv */
+  DCV_K_OTHER = 5,      /* seed gather, layout/precision conversion, sums, de-process, dense */
+  DCV_K_NUM = 6
+};
+/* enable != 0: record a CUDA event pair on the context's stream around every kernel launch (cleared on
+ * every call).  dcv_profile_read synchronises and returns, for one class, the summed device time in
+ * ms, the number of launches and the algorithmic flops / bytes those launches were given. */
+DCV_API int dcv_profile(dcv_ctx* ctx, int enable);
+DCV_API int dcv_profile_read(dcv_ctx* ctx, int kernel_class, double* ms, long long* launches, double* flops, double* bytes);
+
 /* ---- network description: replaces the wrapper stack of visualize_all_layers (deepdream.py:401-423)
  * and DConvolution2D.__init__ (deepdream.py:58-89), which the reference rebuilds on every request.
  * Layers are appended in model order; the returned value (>= 0) is the layer index. ------------- */

@@ -251,3 +251,48 @@ def visualize_all_layers(model, data, layer_name="predictions", visualize_mode="
             lst.append(backward(entries, i, seed))
         out[e.name] = lst
     return out
+
+
+# ----------------------------------------------------------------------------- strong CPU baseline
+class FastTape(object):
+    """Vectorised torch-CPU form of the same algorithm (F.conv2d / F.max_pool2d(return_indices) /
+    F.conv_transpose2d / F.max_unpool2d), used as the timed CPU baseline and for large-size checks.
+    tests/test_oracle.py proves it equal to the faithful restatement above (switches included)."""
+
+    def __init__(self, model, layer_name, data):
+        self.ops = []          # ("conv", W_oihw, b) / ("pool", indices, in_hw)
+        x = _nchw(data)
+        for layer in model.layers:
+            k = _kind(layer)
+            if k == "conv":
+                W, b = layer.get_weights()
+                wt = torch.from_numpy(np.ascontiguousarray(W, np.float32)).permute(3, 2, 0, 1).contiguous()
+                x = F.conv2d(x, wt, torch.from_numpy(np.ascontiguousarray(b, np.float32)), padding=1)
+                if _act_name(layer) == "relu":
+                    x = F.relu(x)
+                self.ops.append(("conv", wt, _act_name(layer) == "relu"))
+            elif k == "pool":
+                hw = x.shape[2:]
+                x, idx = F.max_pool2d(x, 2, 2, return_indices=True)
+                self.ops.append(("pool", idx, hw))
+            elif k != "input":
+                raise NotImplementedError(k)
+            if layer.name == layer_name:
+                break
+        self.top = x
+
+    def project(self, feats):
+        """-> (n, H, W, C0) float32 projections of the top layer's feature maps `feats` (image 0)."""
+        n = len(feats)
+        g = torch.zeros((n,) + tuple(self.top.shape[1:]))
+        for k, f in enumerate(feats):
+            g[k, f] = self.top[0, f]
+        for op in reversed(self.ops):
+            if op[0] == "conv":
+                g = F.conv_transpose2d(g, op[1], padding=1)
+                if op[2]:
+                    g = F.relu(g)
+            else:
+                idx = op[1].expand(n, -1, -1, -1)
+                g = F.max_unpool2d(g, idx, 2, 2, output_size=list(op[2]))
+        return _nhwc(g)

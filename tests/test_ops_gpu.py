@@ -1,0 +1,170 @@
+"""GPU parity of the individual operators, called through the C-ABI (ctypes) and checked against the
+oracle restatement and the reference-generated golden vectors.  Bit-exact for switches, pooled values,
+unpool placement; rel-L2 <= 1e-5 for fp32 conv arithmetic (north_star's stated tolerance)."""
+import numpy as np
+import pytest
+
+from oracle import restatement as rs
+from conftest import rel_l2
+
+pytestmark = pytest.mark.gpu
+
+FP32_TOL = 1e-5
+
+
+def _relu_quant(rng, shape, q=4.0):
+    x = np.maximum(rng.normal(0, 1, shape), 0).astype(np.float32)
+    return np.round(x * q) / q
+
+
+def test_pool_golden_bit_exact(engine, golden):
+    g = golden("pool_reference.npz")
+    pooled, idx = engine.maxpool_switch(g["x"])
+    assert np.array_equal(pooled.astype(np.float64), g["pooled"])
+    assert np.array_equal(idx, g["idx"])
+    un = engine.unpool_switch(g["g"], idx)
+    assert np.array_equal(un.astype(np.float64), g["unpooled"])
+
+
+@pytest.mark.parametrize("shape", [(1, 224, 224, 64), (2, 28, 28, 512), (3, 14, 10, 6), (1, 8, 8, 3), (1, 2, 2, 1),
+                                   (1, 9, 7, 5), (2, 16, 16, 130)])
+def test_pool_unpool_vs_oracle(engine, shape):
+    rng = np.random.default_rng(sum(shape))
+    x = _relu_quant(rng, shape)                       # ties and all-zero patches everywhere
+    pooled, idx = engine.maxpool_switch(x)
+    p_ref, sw_ref, idx_ref = rs.maxpool_with_switch(x)
+    assert np.array_equal(idx, idx_ref)
+    assert np.array_equal(pooled, p_ref.astype(np.float32))
+    if shape[1] % 2 == 0 and shape[2] % 2 == 0:
+        g = rng.normal(0, 1, pooled.shape).astype(np.float32)
+        un = engine.unpool_switch(g, idx)
+        assert np.array_equal(un.astype(np.float64), rs.unpool_with_switch(g, sw_ref))
+        # scatter positions: exactly one non-zero candidate per patch, at the switch
+        assert np.count_nonzero(un) <= g.size
+
+
+def test_pool_empty_and_odd(engine):
+    pooled, idx = engine.maxpool_switch(np.zeros((1, 1, 1, 4), np.float32))
+    assert pooled.shape == (1, 0, 0, 4)
+    from deconv_api_b200 import _native
+    import ctypes
+    out = np.zeros((1, 5, 4, 2), np.float32)
+    x = np.zeros((1, 2, 2, 2), np.float32)
+    sw = np.zeros((1, 2, 2, 2), np.uint8)
+    rc = engine.lib.dcv_unpool_switch(engine.ctx, x.ctypes.data, sw.ctypes.data, 1, 5, 4, 2, out.ctypes.data)
+    assert rc == -1 and b"even" in engine.lib.dcv_last_error(engine.ctx)
+
+
+@pytest.mark.parametrize("B,H,W,cin,cout,bias,relu", [
+    (1, 16, 16, 3, 64, True, True),        # first layer: K = 27
+    (2, 20, 12, 64, 64, True, True),
+    (1, 14, 14, 512, 512, False, True),    # block5 shape
+    (1, 9, 11, 8, 5, True, False),         # odd sizes, ragged channels, linear
+    (1, 33, 17, 16, 24, False, True),
+    (1, 224, 224, 3, 64, True, True),
+])
+def test_conv3x3_vs_oracle(engine, B, H, W, cin, cout, bias, relu):
+    rng = np.random.default_rng(B * 1000 + H + cin + cout)
+    x = rng.normal(0, 1, (B, H, W, cin)).astype(np.float32)
+    lim = np.sqrt(6.0 / (9 * cin + 9 * cout))
+    Wt = rng.uniform(-lim, lim, (3, 3, cin, cout)).astype(np.float32)
+    b = rng.uniform(-0.1, 0.1, (cout,)).astype(np.float32) if bias else np.zeros((cout,), np.float32)
+    out = engine.conv3x3(x, Wt, b, relu=relu)
+    ref = rs.conv_up(x, Wt, b, relu=relu)
+    assert out.shape == ref.shape
+    assert rel_l2(out, ref) < FP32_TOL
+
+
+@pytest.mark.parametrize("B,H,W,cin,cout,relu", [
+    (1, 16, 16, 3, 64, True),              # last backward layer: 64 -> 3 channels
+    (2, 12, 20, 64, 128, True),
+    (1, 14, 14, 512, 512, True),
+    (1, 7, 9, 5, 8, False),
+])
+def test_deconv3x3_fp32_vs_oracle(engine, B, H, W, cin, cout, relu):
+    rng = np.random.default_rng(B * 1000 + H + cin + cout + 1)
+    x = np.maximum(rng.normal(0, 1, (B, H, W, cout)), 0).astype(np.float32)
+    lim = np.sqrt(6.0 / (9 * cin + 9 * cout))
+    Wt = rng.uniform(-lim, lim, (3, 3, cin, cout)).astype(np.float32)
+    out = engine.deconv3x3(x, Wt, relu=relu, precision="fp32")
+    ref = rs.conv_down(x, Wt, relu=relu)
+    assert out.shape == (B, H, W, cin)
+    assert rel_l2(out, ref) < FP32_TOL
+    if relu:
+        assert out.min() >= 0
+
+
+def test_channel_sums_and_top_filters(engine):
+    from deconv_api_b200 import deepdream as dd
+    rng = np.random.default_rng(9)
+    out = rng.normal(0.05, 1, (1, 28, 28, 512)).astype(np.float32)
+    sums = engine.channel_sums_array(out.reshape(-1, 512))
+    ref = out.astype(np.float64).sum(axis=(0, 1, 2))
+    assert np.allclose(sums, ref, rtol=1e-12, atol=1e-9)
+    top = dd.find_top_filters(out)
+    top_ref = rs.find_top_filters(out)
+    assert [t[0] for t in top] == [t[0] for t in top_ref]
+    assert np.allclose([t[1] for t in top], [t[1] for t in top_ref], rtol=1e-5)
+    assert isinstance(top[0][0], int) and len(top) == 8
+    # 2-D (dense) outputs and the s > 0 rule
+    o2 = np.array([[1.0, -2.0, 0.0, 3.0]], np.float32)
+    assert [t[0] for t in dd.find_top_filters(o2)] == [3, 0]
+
+
+def test_deprocess_golden(engine, golden):
+    from deconv_api_b200 import deepdream as dd
+    g = golden("deprocess_reference.npz")
+    x = g["small_in"].copy()
+    out = dd.deprocess_image(x)
+    assert out.dtype == np.uint8 and out.shape == x.shape
+    d = np.abs(out.astype(np.int16) - g["small_u8"].astype(np.int16))
+    assert d.max() <= 1 and np.count_nonzero(d) <= out.size // 1000      # truncation boundary cases only
+    assert np.allclose(x, g["small_mutated"], rtol=0, atol=2e-6)         # in-place side effect reproduced
+    # large, odd length, constant input (std = 0 -> epsilon path)
+    big = np.random.default_rng(1).normal(2.0, 3.0, (448 * 448 * 3 + 3,)).astype(np.float32)
+    ref = rs.deprocess_image(big.copy())
+    got = engine.deprocess(big.copy(), mutate=False)
+    d = np.abs(got.astype(np.int16) - ref.astype(np.int16))
+    assert d.max() <= 1 and np.count_nonzero(d) <= got.size // 1000
+    const = np.full((64,), 3.0, np.float32)
+    assert np.array_equal(engine.deprocess(const.copy()), rs.deprocess_image(const.copy()))
+
+
+def test_dense_and_activation_ops(engine):
+    rng = np.random.default_rng(4)
+    x = rng.normal(0, 1, (2, 300)).astype(np.float32)
+    W = rng.normal(0, 0.1, (300, 70)).astype(np.float32)
+    b = rng.normal(0, 0.1, (70,)).astype(np.float32)
+    y = engine.dense(x, W, b, "relu")
+    assert rel_l2(y, np.maximum(x @ W + b, 0)) < FP32_TOL
+    s = engine.dense(x, W, b, "softmax")
+    assert rel_l2(s, rs.softmax(x @ W + b)) < FP32_TOL
+    g = rng.normal(0, 1, (2, 70)).astype(np.float32)
+    assert rel_l2(engine.dense_transpose(g, W), g @ W.T) < FP32_TOL
+    assert np.array_equal(engine.relu(x), np.maximum(x, 0))
+
+
+def test_wrapper_classes_mirror_reference(engine, golden):
+    """The D* classes keep the reference's contract: ctor takes a layer, .up/.down, up_data/down_data/switch."""
+    from deconv_api_b200 import deepdream as dd, layers
+    g = golden("pool_reference.npz")
+    p = dd.DPooling(layers.MaxPooling2D((2, 2), name="p"))
+    up = p.up(g["x"])
+    assert up.dtype == np.float64 and np.array_equal(up, g["pooled"])
+    assert p.switch.dtype == np.float64 and np.array_equal(p.switch.astype(np.uint8), g["switch"])
+    down = p.down(g["g"])
+    assert np.array_equal(down, g["unpooled"]) and np.array_equal(p.down_data, down)
+    conv = layers.Convolution2D(8, (3, 3), activation="relu", padding="same", name="c")
+    conv._build((None, 10, 10, 4))
+    rng = np.random.default_rng(0)
+    Wt = rng.normal(0, 0.2, (3, 3, 4, 8)).astype(np.float32)
+    b = rng.normal(0, 0.1, (8,)).astype(np.float32)
+    conv.set_weights([Wt, b])
+    c = dd.DConvolution2D(conv)
+    x = rng.normal(0, 1, (1, 10, 10, 4)).astype(np.float32)
+    assert rel_l2(c.up(x), rs.conv_up(x, Wt, b)) < FP32_TOL
+    assert rel_l2(c.down(c.up_data), rs.conv_down(c.up_data, Wt)) < FP32_TOL
+    a = dd.DActivation(conv)
+    assert np.array_equal(a.up(x), np.maximum(x, 0)) and np.array_equal(a.down(-x), np.maximum(-x, 0))
+    i = dd.DInput(layers.InputLayer((10, 10, 4)))
+    assert i.up(x) is x and i.down(x) is x

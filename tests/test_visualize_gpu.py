@@ -1,0 +1,129 @@
+"""End-to-end GPU parity of the drop-in ``visualize_all_layers`` (through the C-ABI) against the
+reference-generated golden vectors and the oracle restatement, fp32 mode (rel-L2 <= 1e-5)."""
+import numpy as np
+import pytest
+
+from oracle import keras_shim, restatement as rs
+from deconv_api_b200 import deepdream as dd, synth, vgg16
+from conftest import rel_l2, unpack2
+
+pytestmark = pytest.mark.gpu
+
+FP32_TOL = 1e-5
+
+
+def test_mini_model_all_targets_vs_reference_golden(golden):
+    g = golden("mini_reference.npz")
+    mini = keras_shim.mini_model(seed=7)          # a foreign (Keras-shaped) model object is adopted as is
+    for mode in ("all", "max"):
+        for tgt in ("predictions", "block2_pool", "block1_conv2"):
+            res = dd.visualize_all_layers(mini, g["x"].copy(), tgt, mode)
+            keys = [k.split("|")[2] for k in g.files if k.startswith("%s|%s|" % (mode, tgt))]
+            assert list(res.keys()) == keys, (mode, tgt)
+            for name, lst in res.items():
+                ref = g["%s|%s|%s" % (mode, tgt, name)]
+                assert len(lst) == len(ref), (mode, tgt, name)
+                for a, b in zip(lst, ref):
+                    assert a.shape == b.shape and a.dtype == np.float32
+                    assert rel_l2(a, b) < FP32_TOL, (mode, tgt, name)
+
+
+def test_mini_model_batch2(golden):
+    g = golden("mini_reference.npz")
+    mini = keras_shim.mini_model(seed=7)
+    res = dd.visualize_all_layers(mini, g["x2"].copy(), "block2_conv1", "all")
+    for name, lst in res.items():
+        ref = g["all|b2|%s" % name]
+        assert np.stack(lst).shape == ref.shape
+        assert rel_l2(np.stack(lst), ref) < FP32_TOL, name
+
+
+def test_illegal_mode_and_unknown_layer():
+    mini = keras_shim.mini_model(seed=7)
+    x = np.zeros((1, 16, 16, 3), np.float32)
+    with pytest.raises(SystemExit):
+        dd.visualize_all_layers(mini, x, "block1_conv1", "bogus")
+    # unknown layer name: the reference stacks and visualises every layer (then main.py raises KeyError)
+    res = dd.visualize_all_layers(mini, np.random.default_rng(0).normal(0, 50, (1, 16, 16, 3)).astype(np.float32), "nope")
+    assert "nope" not in res and "predictions" in res
+
+
+@pytest.fixture(scope="module")
+def vgg_run():
+    model = vgg16.VGG16(weights="imagenet", include_top=True)
+    img = synth.image_batch(1)
+    res = dd.visualize_all_layers(model, img, "block5_conv3", "all")
+    return model, img, res
+
+
+def test_vgg16_block5_conv3_vs_reference_golden(vgg_run, golden):
+    g = golden("vgg16_block5_conv3_reference.npz")
+    model, img, res = vgg_run
+    assert list(res.keys()) == list(g["layers"])
+    assert [len(res[k]) for k in res] == g["counts"].tolist()
+    assert sum(len(v) for v in res.values()) == 136
+    for key in g.files:
+        if key.startswith("proj|"):
+            _, name, k = key.split("|")
+            a = res[name][int(k)]
+            assert a.shape == (224, 224, 3) and a.dtype == np.float32 and a.min() >= 0
+            assert rel_l2(a, g[key]) < FP32_TOL, key
+    for name in res:     # every one of the 136 projections, through its checksums
+        st = np.array([[a.astype(np.float64).sum(), (a.astype(np.float64) ** 2).sum(), a.max()] for a in res[name]])
+        assert np.allclose(st, g["stats|%s" % name], rtol=2e-4), name
+
+
+def test_vgg16_switches_and_top_filters_vs_reference(vgg_run, golden):
+    g = golden("vgg16_block5_conv3_reference.npz")
+    model, img, _ = vgg_run
+    eng = model.bound_engine()
+    total = mism = 0
+    for name in ("block1_pool", "block2_pool", "block3_pool", "block4_pool"):
+        idx = eng.switch_index(eng.index[name])
+        ref = unpack2(g["switch|%s" % name], idx.size).reshape(idx.shape)
+        bad = np.argwhere(idx != ref)
+        total += idx.size
+        mism += len(bad)
+        if len(bad):
+            # a mismatch is only acceptable as a near-tie of the fp32 conv below (last-ulp differences)
+            act = eng.activation(eng.index[name] - 1)
+            for b, y, x, c in bad[:50]:
+                patch = act[b, 2 * y:2 * y + 2, 2 * x:2 * x + 2, c].reshape(-1)
+                va, vb = patch[idx[b, y, x, c]], patch[ref[b, y, x, c]]
+                assert abs(va - vb) <= 1e-5 * max(abs(va), abs(vb), 1e-30), (name, b, y, x, c, patch)
+    assert mism <= max(3, total // 100000), "switch mismatch rate %d / %d" % (mism, total)
+    for name in [n for n in g["layers"]]:
+        sums = eng.channel_sums(eng.index[name])
+        top = dd._top_from_sums(sums, 8, np.float64)
+        assert [t[0] for t in top] == g["top_idx|%s" % name].tolist(), name
+        assert np.allclose([t[1] for t in top], g["top_sum|%s" % name], rtol=1e-4), name
+
+
+def test_api_mosaic_and_deprocess_vs_reference(vgg_run, golden):
+    g = golden("deprocess_reference.npz")
+    _, _, res = vgg_run
+    l = res["block5_conv3"]
+    mosaic = np.concatenate((np.concatenate((l[0], l[1]), axis=1), np.concatenate((l[2], l[3]), axis=1)), axis=0)
+    out = dd.deprocess_image(np.ascontiguousarray(mosaic))
+    assert out.shape == (448, 448, 3) and out.dtype == np.uint8
+    d = np.abs(out.astype(np.int16) - g["mosaic_u8"].astype(np.int16))
+    assert d.max() <= 1 and np.count_nonzero(d) <= out.size // 500
+
+
+def test_vgg16_only_layers_and_vs_oracle_bias():
+    """Second weight set (non-zero biases) and the additive only_layers/top knobs, against the oracle."""
+    model = vgg16.VGG16(weights=None, include_top=False, input_shape=(64, 64, 3), seed=77, bias=True)
+    ref_model = keras_shim.VGG16(include_top=False, input_shape=(64, 64, 3), seed=77, bias=True)
+    img = synth.caffe_preprocess(synth.smooth_image_u8(3, 64, 64))
+    layers = ["block4_conv3", "block3_pool", "block2_conv2"]
+    got = dd.visualize_all_layers(model, img, "block4_conv3", "all", only_layers=layers, top=3)
+    ref = rs.visualize_all_layers(ref_model, img, "block4_conv3", "all", top=3, only_layers=layers)
+    assert list(got.keys()) == list(ref.keys()) == layers
+    for name in layers:
+        assert len(got[name]) == len(ref[name]) == 3
+        for a, b in zip(got[name], ref[name]):
+            assert rel_l2(a, b) < FP32_TOL, name
+    got = dd.visualize_all_layers(model, img, "block3_conv1", "max", only_layers=["block3_conv1"], top=2)
+    ref = rs.visualize_all_layers(ref_model, img, "block3_conv1", "max", top=2, only_layers=["block3_conv1"])
+    for a, b in zip(got["block3_conv1"], ref["block3_conv1"]):
+        assert rel_l2(a, b) < FP32_TOL
