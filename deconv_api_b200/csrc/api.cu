@@ -431,8 +431,18 @@ static int ensure_nonneg(dcv_ctx* ctx, bool& nonneg, float* data, size_t n) {
 //          never materialised; pools unpool the map, the first conv below runs as a rank-1 update)
 //   TENSOR full (P,h,w,C) NHWC tensors
 //   VEC    (P,C) rows, above a Flatten (dense layers)
-static int project_chunk(dcv_ctx* ctx, int layer, int foff, int n, int vis_mode, int precision, float** result) {
+//
+// With DCV_BF16 the TENSOR form lives in the padded-flat bf16 layout of conv_tc.cu between the first
+// (rank-1) and the last backward conv; only that last conv writes fp32 again.  `final_dst`, when not
+// null, is where the last kernel of the chain writes directly (saves a device-to-device copy).
+static int project_chunk(dcv_ctx* ctx, int layer, int foff, int n, int vis_mode, int precision, float* final_dst,
+                         float** result) {
   enum { M_MAP, M_TENSOR, M_VEC };
+  __nv_bfloat16* hb[2] = {(__nv_bfloat16*)ctx->ws[4].p, (__nv_bfloat16*)ctx->ws[5].p};
+  int hcur = 0;
+  bool rep_bf16 = false;             // TENSOR data currently lives in hb[hcur] (padded-flat bf16)
+  int lowest_conv = -1;
+  for (int j = 0; j <= layer; ++j) if (ctx->net[j].kind == LK_CONV) { lowest_conv = j; break; }
   const int B = ctx->in_B;
   const int P = n * B;
   const int* feat = (const int*)ctx->feat_dev.p + foff;
@@ -489,6 +499,9 @@ static int project_chunk(dcv_ctx* ctx, int layer, int foff, int n, int vis_mode,
         ProfScope ps(ctx, DCV_K_UNPOOL, 0.0, (double)P * h * w * (5.0 + 16.0));
         launch_unpool_map(maps, (const uint8_t*)l.sw.p, B, h, w, C, feat, n, maps2, ctx->stream); ctx->launches++;
         std::swap(maps, maps2);
+      } else if (rep_bf16) {
+        TRY(tc_unpool(ctx, hb[hcur], (const uint8_t*)l.sw.p, P, B, h, w, C, hb[hcur ^ 1]));
+        hcur ^= 1;
       } else {
         // algorithmic bytes: 5*HWC/4 read + 4*HWC written, (H,W) = unpooled size
         ProfScope ps(ctx, DCV_K_UNPOOL, 0.0, (double)P * l.in_H * l.in_W * C * (4.0 + 5.0 / 4.0));
@@ -500,19 +513,41 @@ static int project_chunk(dcv_ctx* ctx, int layer, int foff, int n, int vis_mode,
     } else {   // LK_CONV
       if (mode == M_VEC) return ctx->fail(DCV_ERR_STATE, "chain: conv layer %d above a flatten", j);
       if (l.cout != C) return ctx->fail(DCV_ERR_STATE, "chain: layer %d has %d outputs, data has %d channels", j, l.cout, C);
+      const bool more_convs = j > lowest_conv;      // another backward conv follows
+      float* fdst = (j == 0 && final_dst) ? final_dst : nullptr;
       if (mode == M_MAP) {
         if (j != layer && l.relu) TRY(ensure_nonneg(ctx, nonneg, maps, (size_t)P * h * w));
-        {
+        if (precision == DCV_BF16 && more_convs) {
+          TRY(tc_rank1(ctx, maps, l, feat, n, B, h, w, hb[hcur]));
+          rep_bf16 = true;
+        } else {
+          if (fdst) { bufs[cur] = fdst; }
           ProfScope ps(ctx, DCV_K_RANK1, 2.0 * 9 * P * h * w * (double)l.cin, 4.0 * P * h * w * (1.0 + l.cin));
           launch_rank1_deconv(maps, l.wd, l.cout, l.cin, feat, n, B, h, w, l.relu, bufs[cur], ctx->stream); ctx->launches++;
         }
         mode = M_TENSOR;
       } else {
-        if (j != layer && l.relu) TRY(ensure_nonneg(ctx, nonneg, bufs[cur], (size_t)P * h * w * C));
+        if (j != layer && l.relu && !nonneg) {
+          if (rep_bf16) return ctx->fail(DCV_ERR_UNSUPPORTED, "DCV_BF16 chain: a linear conv above a ReLU conv is not supported");
+          TRY(ensure_nonneg(ctx, nonneg, bufs[cur], (size_t)P * h * w * C));
+        }
         const double fl = 2.0 * 9 * P * h * w * (double)l.cin * l.cout;
         if (precision == DCV_BF16) {
-          TRY(tc_deconv(ctx, l, bufs[cur], P, h, w, bufs[cur ^ 1]));
+          if (!rep_bf16) {              // entering from the fp32 side (below a Flatten)
+            TRY(tc_pad_convert(ctx, bufs[cur], P, h, w, C, hb[hcur]));
+            rep_bf16 = true;
+          }
+          if (more_convs) {
+            TRY(tc_conv(ctx, l, hb[hcur], P, h, w, hb[hcur ^ 1], nullptr));
+            hcur ^= 1;
+            cur ^= 1;                   // keeps the fp32 ping-pong bookkeeping below uniform
+          } else {
+            if (fdst) bufs[cur ^ 1] = fdst;
+            TRY(tc_conv(ctx, l, hb[hcur], P, h, w, nullptr, bufs[cur ^ 1]));
+            rep_bf16 = false;
+          }
         } else {
+          if (fdst) bufs[cur ^ 1] = fdst;
           ConvEpilogue e; e.relu = l.relu;
           ProfScope ps(ctx, DCV_K_CONV_FP32, fl, 4.0 * P * h * w * ((double)l.cin + l.cout));
           // backward conv: input channels = l.cout, output channels = l.cin, weights wd [9][cout][cin]
@@ -544,13 +579,38 @@ static int project_impl(dcv_ctx* ctx, int layer, const int* feat, int n, int vis
   if (n == 0) return 0;
   const int B = ctx->in_B;
   const size_t out_elems = (size_t)B * ctx->in_H * ctx->in_W * ctx->in_C;   // per feature
-  const size_t max_elems = chain_max_elems(ctx, layer);                     // per item
-  // chunk so that the two ping-pong buffers fit the workspace budget
-  size_t per_feat = 2 * (size_t)B * max_elems * sizeof(float);
+  size_t max_elems = chain_max_elems(ctx, layer);                           // fp32 elements per item
+  if (precision == DCV_BF16 && (top.kind == LK_CONV || top.kind == LK_POOL)) {
+    // between the first and the last backward conv the data is bf16 (ws[4], ws[5]); fp32 buffers only
+    // hold what the last conv (or anything below it) writes
+    int lowest_conv = -1;
+    for (int j = 0; j <= layer; ++j) if (ctx->net[j].kind == LK_CONV) { lowest_conv = j; break; }
+    if (lowest_conv >= 0) {
+      max_elems = (size_t)ctx->in_H * ctx->in_W * ctx->in_C;
+      for (int j = 0; j < lowest_conv; ++j) max_elems = std::max(max_elems, (size_t)ctx->net[j].H * ctx->net[j].W * ctx->net[j].C);
+      const Layer& lc = ctx->net[lowest_conv];
+      max_elems = std::max(max_elems, (size_t)lc.H * lc.W * lc.cin);
+    }
+  }
+  // padded-flat bf16 elements per item (DCV_BF16 only)
+  size_t max_pad = 0;
+  if (precision == DCV_BF16) {
+    max_pad = tc_padded_elems(ctx->in_H, ctx->in_W, ctx->in_C);
+    for (int j = 0; j <= layer; ++j) {
+      const Layer& l = ctx->net[j];
+      if (l.kind == LK_CONV || l.kind == LK_POOL) max_pad = std::max(max_pad, tc_padded_elems(l.H, l.W, l.C));
+    }
+  }
+  // chunk so that the ping-pong buffers fit the workspace budget
+  size_t per_feat = 2 * (size_t)B * (max_elems * sizeof(float) + max_pad * sizeof(__nv_bfloat16));
   int chunk = (int)std::max<size_t>(1, ctx->workspace_budget / per_feat);
   chunk = std::min(chunk, n);
   TRY(ctx->ws[0].ensure(ctx, (size_t)chunk * B * max_elems * sizeof(float)));
   TRY(ctx->ws[1].ensure(ctx, (size_t)chunk * B * max_elems * sizeof(float)));
+  if (max_pad) {
+    TRY(ctx->ws[4].ensure(ctx, (size_t)chunk * B * max_pad * sizeof(__nv_bfloat16)));
+    TRY(ctx->ws[5].ensure(ctx, (size_t)chunk * B * max_pad * sizeof(__nv_bfloat16)));
+  }
   size_t map_elems = 0;
   for (int j = 0; j <= layer; ++j) map_elems = std::max(map_elems, (size_t)ctx->net[j].H * ctx->net[j].W);
   map_elems = std::max(map_elems, (size_t)ctx->in_H * ctx->in_W);
@@ -561,9 +621,11 @@ static int project_impl(dcv_ctx* ctx, int layer, const int* feat, int n, int vis
   for (int f0 = 0; f0 < n; f0 += chunk) {
     const int nf = std::min(chunk, n - f0);
     float* res = nullptr;
-    TRY(project_chunk(ctx, layer, f0, nf, vis_mode, precision, &res));
-    CU(ctx, cudaMemcpyAsync(out + (size_t)f0 * out_elems, res, (size_t)nf * out_elems * sizeof(float),
-                            out_on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, ctx->stream));
+    float* dst = out + (size_t)f0 * out_elems;
+    TRY(project_chunk(ctx, layer, f0, nf, vis_mode, precision, out_on_device ? dst : nullptr, &res));
+    if (res != dst)
+      CU(ctx, cudaMemcpyAsync(dst, res, (size_t)nf * out_elems * sizeof(float),
+                              out_on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, ctx->stream));
   }
   return 0;
 }

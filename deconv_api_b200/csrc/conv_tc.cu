@@ -1,10 +1,516 @@
-// placeholder until the tcgen05 kernel lands (next milestone): the BF16 precision is refused loudly,
-// never routed to another implementation.
+// Tensor-core backward conv (a3 in SURVEY.md §8a): relu(conv3x3_same(x, flipT(W))) as an implicit GEMM
+// on tcgen05 with TMEM accumulators, operands staged by TMA — hand-written for sm_100a.
+//
+// Layout ("padded-flat"): an activation of P items x (h,w) x C is stored as a 2-D bf16 matrix
+//   rows = P*(h+1)*(w+1), cols = C_pad (multiple of 64); pixel (p,y,x) is row p*(h+1)*(w+1)+y*(w+1)+x,
+// with one zero column (x == w) per image row and one zero row (y == h) per image.  In that layout the
+// input a 3x3 tap (dy,dx) needs for output row r is simply row r + dy*(w+1) + dx: the halo of a 'same'
+// convolution is the shared zero row/column, or an out-of-range row that TMA zero-fills.  So the A tile
+// of every (tap, 64-channel block) is ONE plain 2-D TMA box of 128 consecutive rows at a shifted row
+// coordinate, landing in shared memory already in the 128-byte-swizzled K-major form UMMA reads.
+//   GEMM view:  M = padded rows, N = output channels, K = 9 taps x C_pad;
+//   A tile 128 x 64 (16 KB), B tile BLOCK_N x 64 from weights packed [tap][N_pad][K_pad] bf16.
+// Output rows at pad positions are garbage by construction and are written as zeros (bf16 output, so
+// the next layer's halo stays zero) or skipped (fp32 compact output of the last layer).
+//
+// One persistent CTA per SM, 6 warps: warp 0 = TMA producer, warp 1 = MMA issuer (one thread) and TMEM
+// owner, warps 2-5 = epilogue (TMEM -> registers -> ReLU/mask -> global).  Pipelines: smem ring
+// (full/empty mbarriers, 4-8 stages) and a 2-deep TMEM accumulator ring so the epilogue of tile i
+// overlaps the MMAs of tile i+1.
 #include "common.cuh"
 #include "internal.cuh"
+#include "tc_ptx.cuh"
 
-int tc_prepare_layer(dcv_ctx*, Layer&) { return 0; }
-void tc_free_layer(Layer&) {}
-int tc_deconv(dcv_ctx* ctx, const Layer&, const float*, int, int, int, float*) {
-  return ctx->fail(DCV_ERR_UNSUPPORTED, "DCV_BF16: tensor-core kernel not built into this library yet");
+#include <algorithm>
+
+using namespace dcv;
+using namespace dcv::tc;
+
+namespace {
+
+constexpr int BLOCK_M = 128;
+constexpr int BLOCK_K = 64;                 // bf16 elements = 128 bytes = one swizzle row
+constexpr int A_TILE_BYTES = BLOCK_M * 128;
+constexpr int NUM_THREADS = 192;
+constexpr int SMEM_BUDGET = 200 * 1024;
+
+struct TcParams {
+  int rows;          // P * (h+1) * (w+1)
+  int h, w;          // image size (unpadded)
+  int k_blocks;      // K_pad / 64
+  int n_pad;         // padded output channels (weights / bf16 output pitch)
+  int n_real;        // real output channels (fp32 compact output)
+  int m_tiles, n_tiles;
+  int relu;
+  __nv_bfloat16* out_bf16;   // padded-flat (rows, n_pad), or null
+  float* out_f32;            // compact (P,h,w,n_real), or null
+};
+
+template <int BLOCK_N>
+struct TcCfg {
+  static constexpr int B_TILE_BYTES = BLOCK_N * 128;
+  static constexpr int STAGE_BYTES = A_TILE_BYTES + B_TILE_BYTES;
+  static constexpr int STAGES = (SMEM_BUDGET / STAGE_BYTES) > 8 ? 8 : (SMEM_BUDGET / STAGE_BYTES);
+  static constexpr int TMEM_COLS = (2 * BLOCK_N) < 32 ? 32 : (2 * BLOCK_N);     // power of two for 16/64/128/256
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+};
+
+template <int BLOCK_N>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, TcParams p) {
+  using Cfg = TcCfg<BLOCK_N>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::STAGES * Cfg::STAGE_BYTES);
+  uint64_t* empty_bar = full_bar + Cfg::STAGES;
+  uint64_t* tfull_bar = empty_bar + Cfg::STAGES;      // [2] accumulator ready
+  uint64_t* tempty_bar = tfull_bar + 2;               // [2] accumulator drained
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap_a);
+    tma_prefetch_desc(&tmap_b);
+    for (int s = 0; s < Cfg::STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    for (int b = 0; b < 2; ++b) { mbar_init(&tfull_bar[b], 1); mbar_init(&tempty_bar[b], 4); }
+    fence_barrier_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int total_tiles = p.m_tiles * p.n_tiles;
+  const int wp = p.w + 1;
+  const int total_kb = 9 * p.k_blocks;
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int m0 = (tile / p.n_tiles) * BLOCK_M;
+        const int n0 = (tile % p.n_tiles) * BLOCK_N;
+        for (int kb = 0; kb < total_kb; ++kb) {
+          const int tap = kb / p.k_blocks, kc = kb % p.k_blocks;
+          const int shift = (tap / 3 - 1) * wp + (tap % 3 - 1);
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* a_dst = smem + stage * Cfg::STAGE_BYTES;
+          uint8_t* b_dst = a_dst + A_TILE_BYTES;
+          mbar_arrive_expect_tx(&full_bar[stage], Cfg::STAGE_BYTES);
+          tma_load_2d(a_dst, &tmap_a, &full_bar[stage], kc * BLOCK_K, m0 + shift);
+          tma_load_2d(b_dst, &tmap_b, &full_bar[stage], kc * BLOCK_K, tap * p.n_pad + n0);
+          if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer (single thread) =====
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(BLOCK_M, BLOCK_N);
+      int stage = 0;
+      uint32_t phase = 0;
+      int local = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++local) {
+        const int buf = local & 1;
+        const uint32_t use = (uint32_t)(local >> 1);          // how many times this buffer was used before
+        mbar_wait(&tempty_bar[buf], (use & 1) ^ 1);           // epilogue has drained it
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(buf * BLOCK_N);
+        for (int kb = 0; kb < total_kb; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t a_addr = smem_u32(smem + stage * Cfg::STAGE_BYTES);
+          const uint64_t a_desc = make_sw128_kmajor_desc(a_addr);
+          const uint64_t b_desc = make_sw128_kmajor_desc(a_addr + A_TILE_BYTES);
+#pragma unroll
+          for (int k = 0; k < BLOCK_K / 16; ++k) {
+            // +32 bytes along K inside the swizzle atom = +2 in the (addr >> 4) field
+            umma_bf16(d_tmem, a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc, (kb | k) != 0);
+          }
+          umma_commit(&empty_bar[stage]);                     // smem slot free once these MMAs retire
+          if (kb == total_kb - 1) umma_commit(&tfull_bar[buf]);
+          if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else {
+    // ===== epilogue warps 2..5: TMEM lane group = warp % 4 =====
+    const int lg = warp & 3;
+    const int rp = (p.h + 1) * wp;
+    int local = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++local) {
+      const int m0 = (tile / p.n_tiles) * BLOCK_M;
+      const int n0 = (tile % p.n_tiles) * BLOCK_N;
+      const int buf = local & 1;
+      const uint32_t use = (uint32_t)(local >> 1);
+      mbar_wait(&tfull_bar[buf], use & 1);
+      tc_fence_after();
+      const int r = m0 + lg * 32 + lane;                      // this thread's output row
+      const int q = r % rp;
+      const int y = q / wp, x = q % wp;
+      const bool in_range = r < p.rows;
+      const bool is_pixel = in_range && (x < p.w) && (y < p.h);
+      const uint32_t t_row = tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(buf * BLOCK_N);
+      constexpr int CHUNK = BLOCK_N >= 32 ? 32 : 16;
+#pragma unroll 1
+      for (int c0 = 0; c0 < BLOCK_N; c0 += CHUNK) {
+        uint32_t v[32];
+        if constexpr (CHUNK == 32) tmem_ld32(t_row + (uint32_t)c0, v);
+        else tmem_ld16(t_row + (uint32_t)c0, v);
+        tmem_ld_wait();
+        if (p.out_bf16) {
+          if (in_range) {
+            uint32_t packed[CHUNK / 2];
+#pragma unroll
+            for (int i = 0; i < CHUNK / 2; ++i) {
+              float a = __uint_as_float(v[2 * i]), b = __uint_as_float(v[2 * i + 1]);
+              if (p.relu) { a = fmaxf(a, 0.f); b = fmaxf(b, 0.f); }
+              if (!is_pixel) { a = 0.f; b = 0.f; }
+              __nv_bfloat162 h2 = __floats2bfloat162_rn(a, b);
+              packed[i] = *reinterpret_cast<uint32_t*>(&h2);
+            }
+            uint4* dst = reinterpret_cast<uint4*>(p.out_bf16 + (size_t)r * p.n_pad + n0 + c0);
+#pragma unroll
+            for (int i = 0; i < CHUNK / 8; ++i)
+              dst[i] = make_uint4(packed[4 * i], packed[4 * i + 1], packed[4 * i + 2], packed[4 * i + 3]);
+          }
+        } else if (is_pixel) {
+          const int item = r / rp;
+          float* dst = p.out_f32 + (((size_t)item * p.h + y) * p.w + x) * p.n_real;
+#pragma unroll
+          for (int i = 0; i < CHUNK; ++i) {
+            const int c = n0 + c0 + i;
+            if (c < p.n_real) {
+              float a = __uint_as_float(v[i]);
+              if (p.relu) a = fmaxf(a, 0.f);
+              dst[c] = a;
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty_bar[buf]);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+}
+
+}  // namespace
+
+// =====================================================================================================
+// Supporting kernels of the bf16 chain (HBM-streaming, 128-bit accesses along the channel axis).
+namespace {
+
+static inline int grid_for(size_t work, int block, int waves = 16) {
+  size_t b = (work + block - 1) / block, cap = (size_t)kNumSMs * waves;
+  if (b > cap) b = cap;
+  return (int)(b < 1 ? 1 : b);
+}
+
+// Weights of the backward conv for UMMA: wd fp32 [9][K=cout][N=cin]  ->  bf16 [9][n_pad][k_pad] (K-major rows).
+__global__ void pack_weights_tc_kernel(const float* __restrict__ wd, int kdim, int ndim, int k_pad, int n_pad,
+                                       __nv_bfloat16* __restrict__ out) {
+  const size_t total = (size_t)9 * n_pad * k_pad;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int k = (int)(i % k_pad);
+    const int n = (int)((i / k_pad) % n_pad);
+    const int t = (int)(i / ((size_t)k_pad * n_pad));
+    float v = 0.f;
+    if (k < kdim && n < ndim) v = __ldg(wd + ((size_t)t * kdim + k) * ndim + n);
+    out[i] = __float2bfloat16_rn(v);
+  }
+}
+
+// fp32 compact (P,h,w,C) -> bf16 padded-flat (P*(h+1)*(w+1), c_pad); one thread = 8 channels of one padded row.
+__global__ void pad_convert_kernel(const float* __restrict__ x, int P, int h, int w, int C, int c_pad,
+                                   __nv_bfloat16* __restrict__ out) {
+  const int wp = w + 1, rp = (h + 1) * wp, cg = c_pad / 8;
+  const size_t total = (size_t)P * rp * cg;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int g = (int)(i % cg);
+    const size_t r = i / cg;
+    const int q = (int)(r % rp);
+    const int item = (int)(r / rp);
+    const int y = q / wp, xx = q % wp;
+    float v[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) v[k] = 0.f;
+    if (y < h && xx < w) {
+      const float* src = x + (((size_t)item * h + y) * w + xx) * C + g * 8;
+#pragma unroll
+      for (int k = 0; k < 8; ++k)
+        if (g * 8 + k < C) v[k] = __ldg(src + k);
+    }
+    uint32_t pk[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      __nv_bfloat162 h2 = __floats2bfloat162_rn(v[2 * k], v[2 * k + 1]);
+      pk[k] = *reinterpret_cast<uint32_t*>(&h2);
+    }
+    *reinterpret_cast<uint4*>(out + r * c_pad + g * 8) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+  }
+}
+
+// Switch-driven unpool in the padded-flat bf16 layout (DPooling.down): in (P,(ph+1),(pw+1),c_pad) at the
+// pooled size, switches (Bsw, ph, pw, C) bytes, out (P,(2ph+1),(2pw+1),c_pad).  One thread = 8 channels of
+// one 2x2 output quad; quads with index ph / pw are the zero pad row / column of the output.
+__global__ void __launch_bounds__(256)
+unpool_pad_kernel(const __nv_bfloat16* __restrict__ x, const uint8_t* __restrict__ sw, int P, int Bsw, int ph, int pw,
+                  int C, int c_pad, __nv_bfloat16* __restrict__ out) {
+  const int h = 2 * ph, w = 2 * pw;
+  const int iwp = pw + 1, irp = (ph + 1) * iwp;
+  const int owp = w + 1, orp = (h + 1) * owp;
+  const int cg = c_pad / 8;
+  const size_t total = (size_t)P * (ph + 1) * (pw + 1) * cg;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int g = (int)(i % cg);
+    size_t t = i / cg;
+    const int ox = (int)(t % (pw + 1)); t /= (pw + 1);
+    const int oy = (int)(t % (ph + 1));
+    const int item = (int)(t / (ph + 1));
+    uint4 val = make_uint4(0u, 0u, 0u, 0u);
+    uint32_t sidx[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) sidx[k] = 0xFFu;
+    if (oy < ph && ox < pw) {
+      val = __ldg(reinterpret_cast<const uint4*>(x + ((size_t)item * irp + oy * iwp + ox) * c_pad + g * 8));
+      const uint8_t* sp = sw + (((size_t)(item % Bsw) * ph + oy) * pw + ox) * C + g * 8;
+      if (g * 8 + 8 <= C && (C & 7) == 0) {
+        const uint2 s2 = __ldg(reinterpret_cast<const uint2*>(sp));
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { sidx[k] = (s2.x >> (8 * k)) & 0xFFu; sidx[4 + k] = (s2.y >> (8 * k)) & 0xFFu; }
+      } else {
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+          if (g * 8 + k < C) sidx[k] = __ldg(sp + k);
+      }
+    }
+    const uint32_t vv[4] = {val.x, val.y, val.z, val.w};
+#pragma unroll
+    for (int qd = 0; qd < 4; ++qd) {
+      const int y = 2 * oy + (qd >> 1), xx = 2 * ox + (qd & 1);
+      if (y > h || xx > w) continue;
+      uint32_t o[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const uint32_t lo = (sidx[2 * k] == (uint32_t)qd) ? (vv[k] & 0xFFFFu) : 0u;
+        const uint32_t hi = (sidx[2 * k + 1] == (uint32_t)qd) ? (vv[k] & 0xFFFF0000u) : 0u;
+        o[k] = lo | hi;
+      }
+      *reinterpret_cast<uint4*>(out + ((size_t)item * orp + y * owp + xx) * c_pad + g * 8) = make_uint4(o[0], o[1], o[2], o[3]);
+    }
+  }
+}
+
+// Rank-1 first backward conv writing the padded-flat bf16 layout: out[r][ci] = relu(sum_tap map[p+tap] * wd[tap][f][ci]).
+__global__ void __launch_bounds__(256)
+rank1_pad_kernel(const float* __restrict__ maps, const float* __restrict__ wd, int cout, int cin, int c_pad,
+                 const int* __restrict__ feat, int B, int h, int w, int relu, __nv_bfloat16* __restrict__ out) {
+  extern __shared__ float sm[];
+  float* wsl = sm;                 // [9][c_pad]
+  float* tap = sm + 9 * c_pad;     // [64][9]
+  const int item = blockIdx.y;
+  const int f = feat[item / B];
+  const int wp = w + 1, rp = (h + 1) * wp;
+  for (int i = threadIdx.x; i < 9 * c_pad; i += blockDim.x) {
+    const int t = i / c_pad, ci = i % c_pad;
+    wsl[i] = ci < cin ? __ldg(wd + ((size_t)t * cout + f) * cin + ci) : 0.f;
+  }
+  const int q0 = blockIdx.x * 64;
+  const float* m = maps + (size_t)item * h * w;
+  for (int i = threadIdx.x; i < 64 * 9; i += blockDim.x) {
+    const int pp = i / 9, t = i % 9;
+    const int q = q0 + pp;
+    float v = 0.f;
+    if (q < rp) {
+      const int yc = q / wp, xc = q % wp;
+      const int y = yc + t / 3 - 1, x = xc + t % 3 - 1;
+      if (yc < h && xc < w && y >= 0 && y < h && x >= 0 && x < w) v = __ldg(m + y * w + x);
+    }
+    tap[i] = v;                     // all-zero taps at pad positions -> relu(0) = 0 is written there
+  }
+  __syncthreads();
+  const int cg = c_pad / 2;
+  for (int i = threadIdx.x; i < 64 * cg; i += blockDim.x) {
+    const int pp = i / cg, c2 = (i % cg) * 2;
+    if (q0 + pp >= rp) break;
+    float a = 0.f, b = 0.f;
+#pragma unroll
+    for (int t = 0; t < 9; ++t) {
+      const float tv = tap[pp * 9 + t];
+      a = fmaf(tv, wsl[t * c_pad + c2], a);
+      b = fmaf(tv, wsl[t * c_pad + c2 + 1], b);
+    }
+    if (relu) { a = fmaxf(a, 0.f); b = fmaxf(b, 0.f); }
+    *reinterpret_cast<__nv_bfloat162*>(out + ((size_t)item * rp + q0 + pp) * c_pad + c2) = __floats2bfloat162_rn(a, b);
+  }
+}
+
+}  // namespace
+
+// =====================================================================================================
+// Host side.
+namespace {
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+// 2-D bf16 row-major matrix (rows x cols), box = (box_rows x 64 cols), 128-byte swizzle, zero OOB fill.
+int make_tmap(dcv_ctx* ctx, CUtensorMap* m, const void* base, uint64_t rows, uint64_t cols, uint32_t box_rows) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) return ctx->fail(DCV_ERR_CUDA, "cuTensorMapEncodeTiled is not available from the driver");
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {cols * sizeof(__nv_bfloat16)};
+  cuuint32_t box[2] = {64, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return ctx->fail(DCV_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+  return 0;
+}
+
+template <int BLOCK_N>
+int launch_tc(dcv_ctx* ctx, const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p) {
+  using Cfg = TcCfg<BLOCK_N>;
+  static bool attr_set[64] = {};
+  if (!attr_set[ctx->device & 63]) {
+    cudaError_t e = cudaFuncSetAttribute(deconv_tc_kernel<BLOCK_N>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
+    if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "cudaFuncSetAttribute(smem %d): %s", Cfg::SMEM_BYTES, cudaGetErrorString(e));
+    attr_set[ctx->device & 63] = true;
+  }
+  const int tiles = p.m_tiles * p.n_tiles;
+  const int grid = std::min(tiles, ctx->num_sms);
+  deconv_tc_kernel<BLOCK_N><<<grid, NUM_THREADS, Cfg::SMEM_BYTES, ctx->stream>>>(ta, tb, p);
+  ctx->launches++;
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "deconv_tc_kernel<%d> launch: %s", BLOCK_N, cudaGetErrorString(e));
+  return 0;
+}
+
+inline int round_up(int v, int m) { return (v + m - 1) / m * m; }
+
+}  // namespace
+
+int tc_cpad(int c) { return round_up(c, 64); }
+
+size_t tc_padded_elems(int h, int w, int c) { return (size_t)(h + 1) * (w + 1) * tc_cpad(c); }
+
+int tc_prepare_layer(dcv_ctx* ctx, Layer& l) {
+  // backward conv: K = l.cout (input channels of the backward pass), N = l.cin
+  l.tc.k_pad = tc_cpad(l.cout);
+  l.tc.n_pad = tc_cpad(l.cin);
+  const size_t n = (size_t)9 * l.tc.n_pad * l.tc.k_pad;
+  cudaError_t e = cudaMalloc(&l.tc.wd_bf16, n * sizeof(__nv_bfloat16));
+  if (e != cudaSuccess) return ctx->fail(DCV_ERR_NOMEM, "cudaMalloc(bf16 weights): %s", cudaGetErrorString(e));
+  pack_weights_tc_kernel<<<grid_for(n, 256), 256, 0, ctx->stream>>>(l.wd, l.cout, l.cin, l.tc.k_pad, l.tc.n_pad, l.tc.wd_bf16);
+  ctx->launches++;
+  e = cudaGetLastError();
+  if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "pack_weights_tc_kernel: %s", cudaGetErrorString(e));
+  return 0;
+}
+
+void tc_free_layer(Layer& l) {
+  if (l.tc.wd_bf16) cudaFree(l.tc.wd_bf16);
+  l.tc.wd_bf16 = nullptr;
+}
+
+int tc_pad_convert(dcv_ctx* ctx, const float* x, int P, int h, int w, int C, __nv_bfloat16* out) {
+  const int c_pad = tc_cpad(C);
+  const size_t work = (size_t)P * (h + 1) * (w + 1) * (c_pad / 8);
+  ProfScope ps(ctx, DCV_K_OTHER, 0.0, 4.0 * P * h * w * C + 2.0 * P * (h + 1) * (w + 1) * c_pad);
+  pad_convert_kernel<<<grid_for(work, 256), 256, 0, ctx->stream>>>(x, P, h, w, C, c_pad, out);
+  ctx->launches++;
+  return 0;
+}
+
+int tc_rank1(dcv_ctx* ctx, const float* maps, const Layer& l, const int* feat, int n, int B, int h, int w,
+             __nv_bfloat16* out) {
+  const int c_pad = l.tc.n_pad;
+  const int rp = (h + 1) * (w + 1);
+  dim3 grid((rp + 63) / 64, n * B);
+  const size_t smem = (size_t)(9 * c_pad + 64 * 9) * sizeof(float);
+  ProfScope ps(ctx, DCV_K_RANK1, 2.0 * 9 * n * B * h * w * (double)l.cin, (double)n * B * h * w * (4.0 + 2.0 * l.cin));
+  rank1_pad_kernel<<<grid, 256, smem, ctx->stream>>>(maps, l.wd, l.cout, l.cin, c_pad, feat, B, h, w, l.relu, out);
+  ctx->launches++;
+  return 0;
+}
+
+int tc_unpool(dcv_ctx* ctx, const __nv_bfloat16* x, const uint8_t* sw, int P, int Bsw, int ph, int pw, int C,
+              __nv_bfloat16* out) {
+  const int c_pad = tc_cpad(C);
+  const size_t work = (size_t)P * (ph + 1) * (pw + 1) * (c_pad / 8);
+  // algorithmic bytes in this layout: 2 B/elem read at pooled size + 1 B switch, 2 B/elem written at full size
+  ProfScope ps(ctx, DCV_K_UNPOOL, 0.0, (double)P * ph * pw * C * (2.0 + 1.0 + 8.0));
+  unpool_pad_kernel<<<grid_for(work, 256), 256, 0, ctx->stream>>>(x, sw, P, Bsw, ph, pw, C, c_pad, out);
+  ctx->launches++;
+  return 0;
+}
+
+int tc_conv(dcv_ctx* ctx, const Layer& l, const __nv_bfloat16* in, int P, int h, int w, __nv_bfloat16* out_bf16,
+            float* out_f32) {
+  if (!l.tc.wd_bf16) return ctx->fail(DCV_ERR_STATE, "tensor-core weights were not prepared for this layer");
+  const long long rows_ll = (long long)P * (h + 1) * (w + 1);
+  if (rows_ll > 0x7FFFFF00LL) return ctx->fail(DCV_ERR_ARG, "tc_conv: %lld padded rows exceed the TMA coordinate range", rows_ll);
+  TcParams p;
+  p.rows = (int)rows_ll; p.h = h; p.w = w;
+  p.k_blocks = l.tc.k_pad / 64;
+  p.n_pad = l.tc.n_pad; p.n_real = l.cin;
+  p.relu = l.relu;
+  p.out_bf16 = out_bf16; p.out_f32 = out_f32;
+  p.m_tiles = (p.rows + BLOCK_M - 1) / BLOCK_M;
+  int bn;
+  if (out_f32 && l.cin <= 16) bn = 16;
+  else if (l.tc.n_pad % 256 == 0) bn = 256;
+  else if (l.tc.n_pad % 128 == 0) bn = 128;
+  else bn = 64;
+  p.n_tiles = bn == 16 ? 1 : l.tc.n_pad / bn;
+  CUtensorMap ta, tb;
+  int r = make_tmap(ctx, &ta, in, (uint64_t)p.rows, (uint64_t)l.tc.k_pad, BLOCK_M);
+  if (r) return r;
+  r = make_tmap(ctx, &tb, l.tc.wd_bf16, (uint64_t)9 * l.tc.n_pad, (uint64_t)l.tc.k_pad, (uint32_t)bn);
+  if (r) return r;
+  ProfScope ps(ctx, DCV_K_CONV_TC, 2.0 * 9 * P * h * w * (double)l.cin * l.cout,
+               2.0 * P * h * w * ((double)l.cout + (out_f32 ? 2.0 * l.cin : (double)l.cin)));
+  switch (bn) {
+    case 16: return launch_tc<16>(ctx, ta, tb, p);
+    case 64: return launch_tc<64>(ctx, ta, tb, p);
+    case 128: return launch_tc<128>(ctx, ta, tb, p);
+    default: return launch_tc<256>(ctx, ta, tb, p);
+  }
+}
+
+// Stand-alone operator (dcv_deconv3x3 with DCV_BF16): fp32 compact in -> fp32 compact out.
+int tc_deconv(dcv_ctx* ctx, const Layer& l, const float* in, int P, int h, int w, float* out) {
+  const size_t elems = (size_t)P * tc_padded_elems(h, w, l.cout);
+  int r = ctx->ws[4].ensure(ctx, elems * sizeof(__nv_bfloat16));
+  if (r) return r;
+  r = tc_pad_convert(ctx, in, P, h, w, l.cout, (__nv_bfloat16*)ctx->ws[4].p);
+  if (r) return r;
+  return tc_conv(ctx, l, (const __nv_bfloat16*)ctx->ws[4].p, P, h, w, nullptr, out);
 }

@@ -13,9 +13,8 @@ struct DevBuf {
 
 // tensor-core side of a conv layer (conv_tc.cu)
 struct TcWeights {
-  __nv_bfloat16* wd_bf16 = nullptr;   // backward weights packed [9][cin_pad(N)][cout_pad(K)] K-major bf16
-  int n_pad = 0, k_pad = 0;
-  void* tmap = nullptr;               // host copy of the CUtensorMap for the weights (128 B, 64 B aligned)
+  __nv_bfloat16* wd_bf16 = nullptr;   // backward weights packed [9][n_pad][k_pad] bf16 (K-major rows)
+  int n_pad = 0, k_pad = 0;           // N = cin, K = cout of the forward layer, rounded up to 64
 };
 
 struct Layer {
@@ -69,8 +68,14 @@ struct ProfScope {
   ~ProfScope() { if (c->prof_on) c->prof_end(); }
 };
 
-// conv_tc.cu
+// conv_tc.cu — bf16 tensor-core chain in the padded-flat layout (see the header comment there)
 int tc_prepare_layer(dcv_ctx* ctx, Layer& l);
 void tc_free_layer(Layer& l);
-// backward conv of layer l on P items of (h, w, l.cout) fp32 -> (h, w, l.cin) fp32 with the tensor-core kernel
+int tc_cpad(int c);
+size_t tc_padded_elems(int h, int w, int c);         // bf16 elements of one padded item
+int tc_pad_convert(dcv_ctx* ctx, const float* x, int P, int h, int w, int C, __nv_bfloat16* out);
+int tc_rank1(dcv_ctx* ctx, const float* maps, const Layer& l, const int* feat, int n, int B, int h, int w, __nv_bfloat16* out);
+int tc_unpool(dcv_ctx* ctx, const __nv_bfloat16* x, const uint8_t* sw, int P, int Bsw, int ph, int pw, int C, __nv_bfloat16* out);
+// exactly one of out_bf16 (padded-flat, pitch l.tc.n_pad) / out_f32 (compact (P,h,w,l.cin)) is non-null
+int tc_conv(dcv_ctx* ctx, const Layer& l, const __nv_bfloat16* in, int P, int h, int w, __nv_bfloat16* out_bf16, float* out_f32);
 int tc_deconv(dcv_ctx* ctx, const Layer& l, const float* in, int P, int h, int w, float* out);

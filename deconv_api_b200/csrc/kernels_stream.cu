@@ -483,10 +483,12 @@ __global__ void __launch_bounds__(256) dense_fwd_stage1(const float* __restrict_
   const int i0 = blockIdx.y * chunk;
   const int i1 = min(nin, i0 + chunk);
   if (j >= nout) return;
-  float acc = 0.f;
+  // fp64 accumulation is free here (the kernel waits on HBM) and keeps the cancellation-heavy dense
+  // chains within the fp32 parity tolerance
+  double acc = 0.0;
   const float* xb = x + (size_t)b * nin;
-  for (int i = i0; i < i1; ++i) acc = fmaf(__ldg(xb + i), __ldg(w + (size_t)i * nout + j), acc);
-  partial[((size_t)blockIdx.y * gridDim.z + b) * nout + j] = acc;
+  for (int i = i0; i < i1; ++i) acc += (double)__ldg(xb + i) * (double)__ldg(w + (size_t)i * nout + j);
+  partial[((size_t)blockIdx.y * gridDim.z + b) * nout + j] = (float)acc;
 }
 
 __global__ void dense_fwd_stage2(const float* __restrict__ partial, int nsplit, int B, int nout,
@@ -494,9 +496,10 @@ __global__ void dense_fwd_stage2(const float* __restrict__ partial, int nsplit, 
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
   const int b = blockIdx.y;
   if (j >= nout) return;
-  float acc = 0.f;
-  for (int k = 0; k < nsplit; ++k) acc += partial[((size_t)k * B + b) * nout + j];
-  if (bias) acc += bias[j];
+  double accd = 0.0;
+  for (int k = 0; k < nsplit; ++k) accd += (double)partial[((size_t)k * B + b) * nout + j];
+  if (bias) accd += (double)bias[j];
+  float acc = (float)accd;
   if (act == DCV_ACT_RELU) acc = fmaxf(acc, 0.f);
   out[(size_t)b * nout + j] = acc;
 }
@@ -526,11 +529,11 @@ __global__ void __launch_bounds__(256) dense_bwd_kernel(const float* __restrict_
   if (warp >= nin) return;
   const float* wr = w + (size_t)warp * nout;
   const float* xb = x + (size_t)b * nout;
-  float acc = 0.f;
-  for (int j = lane; j < nout; j += 32) acc = fmaf(__ldg(xb + j), __ldg(wr + j), acc);
+  double acc = 0.0;
+  for (int j = lane; j < nout; j += 32) acc += (double)__ldg(xb + j) * (double)__ldg(wr + j);
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-  if (lane == 0) out[(size_t)b * nin + warp] = acc;
+  if (lane == 0) out[(size_t)b * nin + warp] = (float)acc;
 }
 
 void launch_dense_bwd(const float* x, const float* w, int B, int nin, int nout, float* out, cudaStream_t s) {
