@@ -29,6 +29,7 @@ SIGNATURES = {
     "dcv_stream": (_c.c_void_p, [_c.c_void_p]),
     "dcv_profile": (_c.c_int, [_c.c_void_p, _c.c_int]),
     "dcv_profile_read": (_c.c_int, [_c.c_void_p, _c.c_int, P_F64, _c.POINTER(_c.c_longlong), P_F64, P_F64]),
+    "dcv_profile_launch": (_c.c_int, [_c.c_void_p, _c.c_int, P_I32, P_F64, P_F64, P_F64]),
     "dcv_net_clear": (_c.c_int, [_c.c_void_p]),
     "dcv_net_add_conv": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_void_p, _c.c_int, _c.c_int, _c.c_int]),
     "dcv_net_add_pool": (_c.c_int, [_c.c_void_p]),

@@ -179,6 +179,20 @@ extern "C" int dcv_profile_read(dcv_ctx* ctx, int cat, double* ms, long long* la
   return 0;
 }
 
+extern "C" int dcv_profile_launch(dcv_ctx* ctx, int index, int* cat, double* ms, double* flops, double* bytes) {
+  ENTER(ctx);
+  if (index < 0 || index >= (int)ctx->prof.size()) return DCV_ERR_ARG;      // end of the list (no error text)
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  const ProfRec& r = ctx->prof[index];
+  float e = 0.f;
+  CU(ctx, cudaEventElapsedTime(&e, r.a, r.b));
+  if (cat) *cat = r.cat;
+  if (ms) *ms = e;
+  if (flops) *flops = r.flops;
+  if (bytes) *bytes = r.bytes;
+  return 0;
+}
+
 // ---- network description --------------------------------------------------------------------------
 extern "C" int dcv_net_clear(dcv_ctx* ctx) {
   ENTER(ctx);

@@ -20,194 +20,13 @@
 #include "common.cuh"
 #include "internal.cuh"
 #include "tc_ptx.cuh"
+#include "tc_kernel.cuh"
 
 #include <algorithm>
+#include <cstdlib>
 
 using namespace dcv;
 using namespace dcv::tc;
-
-namespace {
-
-constexpr int BLOCK_M = 128;
-constexpr int BLOCK_K = 64;                 // bf16 elements = 128 bytes = one swizzle row
-constexpr int A_TILE_BYTES = BLOCK_M * 128;
-constexpr int NUM_THREADS = 192;
-constexpr int SMEM_BUDGET = 200 * 1024;
-
-struct TcParams {
-  int rows;          // P * (h+1) * (w+1)
-  int h, w;          // image size (unpadded)
-  int k_blocks;      // K_pad / 64
-  int n_pad;         // padded output channels (weights / bf16 output pitch)
-  int n_real;        // real output channels (fp32 compact output)
-  int m_tiles, n_tiles;
-  int relu;
-  __nv_bfloat16* out_bf16;   // padded-flat (rows, n_pad), or null
-  float* out_f32;            // compact (P,h,w,n_real), or null
-};
-
-template <int BLOCK_N>
-struct TcCfg {
-  static constexpr int B_TILE_BYTES = BLOCK_N * 128;
-  static constexpr int STAGE_BYTES = A_TILE_BYTES + B_TILE_BYTES;
-  static constexpr int STAGES = (SMEM_BUDGET / STAGE_BYTES) > 8 ? 8 : (SMEM_BUDGET / STAGE_BYTES);
-  static constexpr int TMEM_COLS = (2 * BLOCK_N) < 32 ? 32 : (2 * BLOCK_N);     // power of two for 16/64/128/256
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
-};
-
-template <int BLOCK_N>
-__global__ void __launch_bounds__(NUM_THREADS, 1)
-deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, TcParams p) {
-  using Cfg = TcCfg<BLOCK_N>;
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::STAGES * Cfg::STAGE_BYTES);
-  uint64_t* empty_bar = full_bar + Cfg::STAGES;
-  uint64_t* tfull_bar = empty_bar + Cfg::STAGES;      // [2] accumulator ready
-  uint64_t* tempty_bar = tfull_bar + 2;               // [2] accumulator drained
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
-
-  const int warp = threadIdx.x >> 5;
-  const int lane = threadIdx.x & 31;
-
-  if (warp == 0 && lane == 0) {
-    tma_prefetch_desc(&tmap_a);
-    tma_prefetch_desc(&tmap_b);
-    for (int s = 0; s < Cfg::STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-    for (int b = 0; b < 2; ++b) { mbar_init(&tfull_bar[b], 1); mbar_init(&tempty_bar[b], 4); }
-    fence_barrier_init();
-  }
-  if (warp == 1) {
-    tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
-    tmem_relinquish();
-  }
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem_base = *tmem_slot;
-
-  const int total_tiles = p.m_tiles * p.n_tiles;
-  const int wp = p.w + 1;
-  const int total_kb = 9 * p.k_blocks;
-
-  if (warp == 0) {
-    // ===== TMA producer =====
-    if (lane == 0) {
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        const int m0 = (tile / p.n_tiles) * BLOCK_M;
-        const int n0 = (tile % p.n_tiles) * BLOCK_N;
-        for (int kb = 0; kb < total_kb; ++kb) {
-          const int tap = kb / p.k_blocks, kc = kb % p.k_blocks;
-          const int shift = (tap / 3 - 1) * wp + (tap % 3 - 1);
-          mbar_wait(&empty_bar[stage], phase ^ 1);
-          uint8_t* a_dst = smem + stage * Cfg::STAGE_BYTES;
-          uint8_t* b_dst = a_dst + A_TILE_BYTES;
-          mbar_arrive_expect_tx(&full_bar[stage], Cfg::STAGE_BYTES);
-          tma_load_2d(a_dst, &tmap_a, &full_bar[stage], kc * BLOCK_K, m0 + shift);
-          tma_load_2d(b_dst, &tmap_b, &full_bar[stage], kc * BLOCK_K, tap * p.n_pad + n0);
-          if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
-        }
-      }
-    }
-  } else if (warp == 1) {
-    // ===== MMA issuer (single thread) =====
-    if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_bf16(BLOCK_M, BLOCK_N);
-      int stage = 0;
-      uint32_t phase = 0;
-      int local = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++local) {
-        const int buf = local & 1;
-        const uint32_t use = (uint32_t)(local >> 1);          // how many times this buffer was used before
-        mbar_wait(&tempty_bar[buf], (use & 1) ^ 1);           // epilogue has drained it
-        tc_fence_after();
-        const uint32_t d_tmem = tmem_base + (uint32_t)(buf * BLOCK_N);
-        for (int kb = 0; kb < total_kb; ++kb) {
-          mbar_wait(&full_bar[stage], phase);
-          tc_fence_after();
-          const uint32_t a_addr = smem_u32(smem + stage * Cfg::STAGE_BYTES);
-          const uint64_t a_desc = make_sw128_kmajor_desc(a_addr);
-          const uint64_t b_desc = make_sw128_kmajor_desc(a_addr + A_TILE_BYTES);
-#pragma unroll
-          for (int k = 0; k < BLOCK_K / 16; ++k) {
-            // +32 bytes along K inside the swizzle atom = +2 in the (addr >> 4) field
-            umma_bf16(d_tmem, a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc, (kb | k) != 0);
-          }
-          umma_commit(&empty_bar[stage]);                     // smem slot free once these MMAs retire
-          if (kb == total_kb - 1) umma_commit(&tfull_bar[buf]);
-          if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
-        }
-      }
-    }
-  } else {
-    // ===== epilogue warps 2..5: TMEM lane group = warp % 4 =====
-    const int lg = warp & 3;
-    const int rp = (p.h + 1) * wp;
-    int local = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++local) {
-      const int m0 = (tile / p.n_tiles) * BLOCK_M;
-      const int n0 = (tile % p.n_tiles) * BLOCK_N;
-      const int buf = local & 1;
-      const uint32_t use = (uint32_t)(local >> 1);
-      mbar_wait(&tfull_bar[buf], use & 1);
-      tc_fence_after();
-      const int r = m0 + lg * 32 + lane;                      // this thread's output row
-      const int q = r % rp;
-      const int y = q / wp, x = q % wp;
-      const bool in_range = r < p.rows;
-      const bool is_pixel = in_range && (x < p.w) && (y < p.h);
-      const uint32_t t_row = tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(buf * BLOCK_N);
-      constexpr int CHUNK = BLOCK_N >= 32 ? 32 : 16;
-#pragma unroll 1
-      for (int c0 = 0; c0 < BLOCK_N; c0 += CHUNK) {
-        uint32_t v[32];
-        if constexpr (CHUNK == 32) tmem_ld32(t_row + (uint32_t)c0, v);
-        else tmem_ld16(t_row + (uint32_t)c0, v);
-        tmem_ld_wait();
-        if (p.out_bf16) {
-          if (in_range) {
-            uint32_t packed[CHUNK / 2];
-#pragma unroll
-            for (int i = 0; i < CHUNK / 2; ++i) {
-              float a = __uint_as_float(v[2 * i]), b = __uint_as_float(v[2 * i + 1]);
-              if (p.relu) { a = fmaxf(a, 0.f); b = fmaxf(b, 0.f); }
-              if (!is_pixel) { a = 0.f; b = 0.f; }
-              __nv_bfloat162 h2 = __floats2bfloat162_rn(a, b);
-              packed[i] = *reinterpret_cast<uint32_t*>(&h2);
-            }
-            uint4* dst = reinterpret_cast<uint4*>(p.out_bf16 + (size_t)r * p.n_pad + n0 + c0);
-#pragma unroll
-            for (int i = 0; i < CHUNK / 8; ++i)
-              dst[i] = make_uint4(packed[4 * i], packed[4 * i + 1], packed[4 * i + 2], packed[4 * i + 3]);
-          }
-        } else if (is_pixel) {
-          const int item = r / rp;
-          float* dst = p.out_f32 + (((size_t)item * p.h + y) * p.w + x) * p.n_real;
-#pragma unroll
-          for (int i = 0; i < CHUNK; ++i) {
-            const int c = n0 + c0 + i;
-            if (c < p.n_real) {
-              float a = __uint_as_float(v[i]);
-              if (p.relu) a = fmaxf(a, 0.f);
-              dst[c] = a;
-            }
-          }
-        }
-      }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&tempty_bar[buf]);
-    }
-  }
-
-  tc_fence_before();
-  __syncthreads();
-  if (warp == 1) tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
-}
-
-}  // namespace
 
 // =====================================================================================================
 // Supporting kernels of the bf16 chain (HBM-streaming, 128-bit accesses along the channel axis).
@@ -395,21 +214,23 @@ int make_tmap(dcv_ctx* ctx, CUtensorMap* m, const void* base, uint64_t rows, uin
   return 0;
 }
 
-template <int BLOCK_N>
-int launch_tc(dcv_ctx* ctx, const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p) {
-  using Cfg = TcCfg<BLOCK_N>;
-  static bool attr_set[64] = {};
-  if (!attr_set[ctx->device & 63]) {
-    cudaError_t e = cudaFuncSetAttribute(deconv_tc_kernel<BLOCK_N>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
-    if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "cudaFuncSetAttribute(smem %d): %s", Cfg::SMEM_BYTES, cudaGetErrorString(e));
-    attr_set[ctx->device & 63] = true;
-  }
+template <int BLOCK_N, int MODE>
+int launch_tc(dcv_ctx* ctx, const CUtensorMap& ta, const CUtensorMap& tb, TcParams p) {
+  const int stage_bytes = tc_stage_bytes(MODE, BLOCK_N);
+  const int res_bytes = tc_resident_bytes(MODE, BLOCK_N, p.k_blocks);
+  int stages = (SMEM_BUDGET - res_bytes) / stage_bytes;
+  if (stages > 8) stages = 8;
+  if (stages < 2) return ctx->fail(DCV_ERR_UNSUPPORTED, "tc kernel: %d resident bytes leave no room for the pipeline", res_bytes);
+  p.stages = stages;
+  const int smem = res_bytes + stages * stage_bytes + 1024 /*align slack*/ + 256 /*barriers*/;
+  cudaError_t e = cudaFuncSetAttribute(deconv_tc_kernel<BLOCK_N, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "cudaFuncSetAttribute(smem %d): %s", smem, cudaGetErrorString(e));
   const int tiles = p.m_tiles * p.n_tiles;
   const int grid = std::min(tiles, ctx->num_sms);
-  deconv_tc_kernel<BLOCK_N><<<grid, NUM_THREADS, Cfg::SMEM_BYTES, ctx->stream>>>(ta, tb, p);
+  deconv_tc_kernel<BLOCK_N, MODE><<<grid, NUM_THREADS, smem, ctx->stream>>>(ta, tb, p);
   ctx->launches++;
-  cudaError_t e = cudaGetLastError();
-  if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "deconv_tc_kernel<%d> launch: %s", BLOCK_N, cudaGetErrorString(e));
+  e = cudaGetLastError();
+  if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "deconv_tc_kernel<%d,%d> launch: %s", BLOCK_N, MODE, cudaGetErrorString(e));
   return 0;
 }
 
@@ -490,19 +311,39 @@ int tc_conv(dcv_ctx* ctx, const Layer& l, const __nv_bfloat16* in, int P, int h,
   else if (l.tc.n_pad % 128 == 0) bn = 128;
   else bn = 64;
   p.n_tiles = bn == 16 ? 1 : l.tc.n_pad / bn;
+  // operand staging mode (tc_kernel.cuh): bands for narrow N, resident weights when they fit beside >= 4 stages
+  static const int force_mode = getenv("DCV_TC_MODE") ? atoi(getenv("DCV_TC_MODE")) : -1;
+  // Measured on B200: the 128-byte swizzle is applied to the absolute shared-memory address, so an operand
+  // that starts 1-2 rows into a TMA box needs base offset 0 (1 gives wrong results; tests/test_tc_gpu.py).
+  static const int base_off = getenv("DCV_TC_BASEOFF") ? atoi(getenv("DCV_TC_BASEOFF")) : 0;
+  int mode = MODE_TAP;
+  if (bn <= 128) {
+    mode = MODE_BAND;
+    if (p.n_tiles == 1 && tc_resident_bytes(MODE_BAND_RES, bn, p.k_blocks) + 4 * A_BAND_BYTES <= SMEM_BUDGET) mode = MODE_BAND_RES;
+  }
+  if (force_mode >= 0 && bn <= 128) mode = force_mode;
+  if (mode == MODE_BAND_RES && p.n_tiles != 1) mode = MODE_BAND;
+  p.base_off = base_off;
   CUtensorMap ta, tb;
-  int r = make_tmap(ctx, &ta, in, (uint64_t)p.rows, (uint64_t)l.tc.k_pad, BLOCK_M);
+  int r = make_tmap(ctx, &ta, in, (uint64_t)p.rows, (uint64_t)l.tc.k_pad, mode == MODE_TAP ? BLOCK_M : BAND_ROWS);
   if (r) return r;
   r = make_tmap(ctx, &tb, l.tc.wd_bf16, (uint64_t)9 * l.tc.n_pad, (uint64_t)l.tc.k_pad, (uint32_t)bn);
   if (r) return r;
   ProfScope ps(ctx, DCV_K_CONV_TC, 2.0 * 9 * P * h * w * (double)l.cin * l.cout,
                2.0 * P * h * w * ((double)l.cout + (out_f32 ? 2.0 * l.cin : (double)l.cin)));
-  switch (bn) {
-    case 16: return launch_tc<16>(ctx, ta, tb, p);
-    case 64: return launch_tc<64>(ctx, ta, tb, p);
-    case 128: return launch_tc<128>(ctx, ta, tb, p);
-    default: return launch_tc<256>(ctx, ta, tb, p);
+#define TC_DISPATCH(BN)                                                    \
+  switch (mode) {                                                          \
+    case MODE_BAND: return launch_tc<BN, MODE_BAND>(ctx, ta, tb, p);       \
+    case MODE_BAND_RES: return launch_tc<BN, MODE_BAND_RES>(ctx, ta, tb, p); \
+    default: return launch_tc<BN, MODE_TAP>(ctx, ta, tb, p);               \
   }
+  switch (bn) {
+    case 16: TC_DISPATCH(16)
+    case 64: TC_DISPATCH(64)
+    case 128: TC_DISPATCH(128)
+    default: return launch_tc<256, MODE_TAP>(ctx, ta, tb, p);
+  }
+#undef TC_DISPATCH
 }
 
 // Stand-alone operator (dcv_deconv3x3 with DCV_BF16): fp32 compact in -> fp32 compact out.

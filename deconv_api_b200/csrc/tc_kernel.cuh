@@ -1,0 +1,248 @@
+// The tcgen05 implicit-GEMM kernel of the backward conv (included by conv_tc.cu only).
+//
+// Three operand-staging modes share one pipeline and one epilogue:
+//   MODE_TAP       one smem stage = (tap, 64-channel block): A box of 128 rows at row m0 + dy*(w+1) + dx,
+//                  B box of BLOCK_N weight rows.  Best when N is large (N tile 256: block3/block4 layers).
+//   MODE_BAND      one smem stage = (dy, 64-channel block): ONE A box of 136 rows starting at
+//                  m0 + dy*(w+1) - 1 serves the three dx taps (UMMA descriptors start 0, 1, 2 rows into
+//                  the box), plus the three B boxes.  Cuts the A traffic from L2 by 2.8x; for N <= 128.
+//   MODE_BAND_RES  as MODE_BAND, but ALL weights of the layer (9 x K x N) are loaded into shared memory
+//                  once per persistent CTA and stay resident; stages then hold only A bands.  For the
+//                  64-channel block1 layers, which are otherwise bound by the L2 -> SM operand stream.
+#pragma once
+#include "common.cuh"
+#include "tc_ptx.cuh"
+
+namespace dcv {
+namespace tc {
+
+constexpr int BLOCK_M = 128;
+constexpr int BLOCK_K = 64;                 // bf16 elements = 128 bytes = one swizzle row
+constexpr int A_TILE_BYTES = BLOCK_M * 128;
+constexpr int BAND_ROWS = 136;              // 128 + 2 halo rows, rounded up to the 8-row swizzle atom
+constexpr int A_BAND_BYTES = BAND_ROWS * 128;
+constexpr int NUM_THREADS = 192;
+constexpr int SMEM_BUDGET = 200 * 1024;
+
+enum { MODE_TAP = 0, MODE_BAND = 1, MODE_BAND_RES = 2 };
+
+struct TcParams {
+  int rows;          // P * (h+1) * (w+1)
+  int h, w;          // image size (unpadded)
+  int k_blocks;      // K_pad / 64
+  int n_pad;         // padded output channels (weights / bf16 output pitch)
+  int n_real;        // real output channels (fp32 compact output)
+  int m_tiles, n_tiles;
+  int relu;
+  int stages;        // smem ring depth (host-computed from the budget)
+  int base_off;      // 1: put (start_addr >> 7) & 7 into the descriptor's base-offset field
+  __nv_bfloat16* out_bf16;   // padded-flat (rows, n_pad), or null
+  float* out_f32;            // compact (P,h,w,n_real), or null
+};
+
+__host__ __device__ inline int tc_stage_bytes(int mode, int block_n) {
+  if (mode == MODE_TAP) return A_TILE_BYTES + block_n * 128;
+  if (mode == MODE_BAND) return A_BAND_BYTES + 3 * block_n * 128;
+  return A_BAND_BYTES;
+}
+__host__ __device__ inline int tc_resident_bytes(int mode, int block_n, int k_blocks) {
+  return mode == MODE_BAND_RES ? 9 * k_blocks * block_n * 128 : 0;
+}
+
+template <int BLOCK_N, int MODE>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, TcParams p) {
+  constexpr int B_TILE_BYTES = BLOCK_N * 128;
+  constexpr int TMEM_COLS = (2 * BLOCK_N) < 32 ? 32 : (2 * BLOCK_N);
+  constexpr int MAX_STAGES = 8;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  const int stage_bytes = tc_stage_bytes(MODE, BLOCK_N);
+  const int res_bytes = tc_resident_bytes(MODE, BLOCK_N, p.k_blocks);
+  uint8_t* wres = smem;                               // resident weights (MODE_BAND_RES)
+  uint8_t* ring = smem + res_bytes;                   // stage ring
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(ring + p.stages * stage_bytes);
+  uint64_t* empty_bar = full_bar + MAX_STAGES;
+  uint64_t* tfull_bar = empty_bar + MAX_STAGES;       // [2] accumulator ready
+  uint64_t* tempty_bar = tfull_bar + 2;               // [2] accumulator drained
+  uint64_t* wres_bar = tempty_bar + 2;                // resident weights landed
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(wres_bar + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap_a);
+    tma_prefetch_desc(&tmap_b);
+    for (int s = 0; s < p.stages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    for (int b = 0; b < 2; ++b) { mbar_init(&tfull_bar[b], 1); mbar_init(&tempty_bar[b], 4); }
+    mbar_init(wres_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, TMEM_COLS);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int total_tiles = p.m_tiles * p.n_tiles;
+  const int wp = p.w + 1;
+  const int groups = (MODE == MODE_TAP) ? 9 : 3;      // stages per 64-channel block
+  const int total_st = groups * p.k_blocks;           // stages per tile
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (lane == 0) {
+      if constexpr (MODE == MODE_BAND_RES) {
+        // all 9 x k_blocks weight tiles, once; n_tiles == 1 in this mode
+        mbar_arrive_expect_tx(wres_bar, (uint32_t)res_bytes);
+        for (int t = 0; t < 9; ++t)
+          for (int kc = 0; kc < p.k_blocks; ++kc)
+            tma_load_2d(wres + (t * p.k_blocks + kc) * B_TILE_BYTES, &tmap_b, wres_bar, kc * BLOCK_K, t * p.n_pad);
+      }
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int m0 = (tile / p.n_tiles) * BLOCK_M;
+        const int n0 = (tile % p.n_tiles) * BLOCK_N;
+        for (int st = 0; st < total_st; ++st) {
+          const int g = st / p.k_blocks, kc = st % p.k_blocks;
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* a_dst = ring + stage * stage_bytes;
+          mbar_arrive_expect_tx(&full_bar[stage], (uint32_t)stage_bytes);
+          if constexpr (MODE == MODE_TAP) {
+            const int shift = (g / 3 - 1) * wp + (g % 3 - 1);
+            tma_load_2d(a_dst, &tmap_a, &full_bar[stage], kc * BLOCK_K, m0 + shift);
+            tma_load_2d(a_dst + A_TILE_BYTES, &tmap_b, &full_bar[stage], kc * BLOCK_K, g * p.n_pad + n0);
+          } else {
+            tma_load_2d(a_dst, &tmap_a, &full_bar[stage], kc * BLOCK_K, m0 + (g - 1) * wp - 1);
+            if constexpr (MODE == MODE_BAND) {
+#pragma unroll
+              for (int dx = 0; dx < 3; ++dx)
+                tma_load_2d(a_dst + A_BAND_BYTES + dx * B_TILE_BYTES, &tmap_b, &full_bar[stage], kc * BLOCK_K,
+                            (g * 3 + dx) * p.n_pad + n0);
+            }
+          }
+          if (++stage == p.stages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer (single thread) =====
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(BLOCK_M, BLOCK_N);
+      if constexpr (MODE == MODE_BAND_RES) {
+        mbar_wait(wres_bar, 0);
+        tc_fence_after();
+      }
+      int stage = 0;
+      uint32_t phase = 0;
+      int local = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++local) {
+        const int buf = local & 1;
+        const uint32_t use = (uint32_t)(local >> 1);          // how many times this buffer was used before
+        mbar_wait(&tempty_bar[buf], (use & 1) ^ 1);           // epilogue has drained it
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(buf * BLOCK_N);
+        for (int st = 0; st < total_st; ++st) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t a_addr = smem_u32(ring + stage * stage_bytes);
+          if constexpr (MODE == MODE_TAP) {
+            const uint64_t a_desc = make_sw128_kmajor_desc(a_addr, 0);
+            const uint64_t b_desc = make_sw128_kmajor_desc(a_addr + A_TILE_BYTES, 0);
+#pragma unroll
+            for (int k = 0; k < BLOCK_K / 16; ++k)   // +32 bytes along K inside the swizzle atom = +2 in addr>>4
+              umma_bf16(d_tmem, a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc, (st | k) != 0);
+          } else {
+            const int g = st / p.k_blocks, kc = st % p.k_blocks;
+#pragma unroll
+            for (int dx = 0; dx < 3; ++dx) {
+              // tap (g-1, dx-1): the A operand starts dx rows (dx * 128 bytes) into the band
+              const uint64_t a_desc = make_sw128_kmajor_desc(a_addr + dx * 128, p.base_off ? (uint32_t)dx : 0u);
+              uint32_t b_addr;
+              if constexpr (MODE == MODE_BAND) b_addr = a_addr + A_BAND_BYTES + dx * B_TILE_BYTES;
+              else b_addr = smem_u32(wres + ((g * 3 + dx) * p.k_blocks + kc) * B_TILE_BYTES);
+              const uint64_t b_desc = make_sw128_kmajor_desc(b_addr, 0);
+#pragma unroll
+              for (int k = 0; k < BLOCK_K / 16; ++k)
+                umma_bf16(d_tmem, a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc, (st | dx | k) != 0);
+            }
+          }
+          umma_commit(&empty_bar[stage]);                     // smem slot free once these MMAs retire
+          if (st == total_st - 1) umma_commit(&tfull_bar[buf]);
+          if (++stage == p.stages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else {
+    // ===== epilogue warps 2..5: TMEM lane group = warp % 4 =====
+    const int lg = warp & 3;
+    const int rp = (p.h + 1) * wp;
+    int local = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++local) {
+      const int m0 = (tile / p.n_tiles) * BLOCK_M;
+      const int n0 = (tile % p.n_tiles) * BLOCK_N;
+      const int buf = local & 1;
+      const uint32_t use = (uint32_t)(local >> 1);
+      mbar_wait(&tfull_bar[buf], use & 1);
+      tc_fence_after();
+      const int r = m0 + lg * 32 + lane;                      // this thread's output row
+      const int q = r % rp;
+      const int y = q / wp, x = q % wp;
+      const bool in_range = r < p.rows;
+      const bool is_pixel = in_range && (x < p.w) && (y < p.h);
+      const uint32_t t_row = tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(buf * BLOCK_N);
+      constexpr int CHUNK = BLOCK_N >= 32 ? 32 : 16;
+#pragma unroll 1
+      for (int c0 = 0; c0 < BLOCK_N; c0 += CHUNK) {
+        uint32_t v[32];
+        if constexpr (CHUNK == 32) tmem_ld32(t_row + (uint32_t)c0, v);
+        else tmem_ld16(t_row + (uint32_t)c0, v);
+        tmem_ld_wait();
+        if (p.out_bf16) {
+          if (in_range) {
+            uint32_t packed[CHUNK / 2];
+#pragma unroll
+            for (int i = 0; i < CHUNK / 2; ++i) {
+              float a = __uint_as_float(v[2 * i]), b = __uint_as_float(v[2 * i + 1]);
+              if (p.relu) { a = fmaxf(a, 0.f); b = fmaxf(b, 0.f); }
+              if (!is_pixel) { a = 0.f; b = 0.f; }
+              __nv_bfloat162 h2 = __floats2bfloat162_rn(a, b);
+              packed[i] = *reinterpret_cast<uint32_t*>(&h2);
+            }
+            uint4* dst = reinterpret_cast<uint4*>(p.out_bf16 + (size_t)r * p.n_pad + n0 + c0);
+#pragma unroll
+            for (int i = 0; i < CHUNK / 8; ++i)
+              dst[i] = make_uint4(packed[4 * i], packed[4 * i + 1], packed[4 * i + 2], packed[4 * i + 3]);
+          }
+        } else if (is_pixel) {
+          const int item = r / rp;
+          float* dst = p.out_f32 + (((size_t)item * p.h + y) * p.w + x) * p.n_real;
+#pragma unroll
+          for (int i = 0; i < CHUNK; ++i) {
+            const int c = n0 + c0 + i;
+            if (c < p.n_real) {
+              float a = __uint_as_float(v[i]);
+              if (p.relu) a = fmaxf(a, 0.f);
+              dst[c] = a;
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty_bar[buf]);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, TMEM_COLS);
+}
+
+}  // namespace tc
+}  // namespace dcv

@@ -110,8 +110,11 @@ __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.
 // 8-row swizzle atoms are 1024 B apart (SBO); LBO is unused because one MMA's K extent (32 B) stays
 // inside one atom.  bits [0,14) addr>>4 | [16,30) LBO>>4 | [32,46) SBO>>4 | [46,48) version=1 |
 // [61,64) layout: 2 = SWIZZLE_128B.
-__device__ __forceinline__ uint64_t make_sw128_kmajor_desc(uint32_t smem_addr) {
+// base_off (bits [49,52)): (start address >> 7) & 7 when the operand does not start on a 1024-byte
+// swizzle-pattern boundary (an operand that begins a few rows into a TMA box).
+__device__ __forceinline__ uint64_t make_sw128_kmajor_desc(uint32_t smem_addr, uint32_t base_off) {
   uint64_t d = 0;
+  d |= (uint64_t)(base_off & 7u) << 49;
   d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);
   d |= (uint64_t)((1024u >> 4) & 0x3FFF) << 32;
   d |= (uint64_t)1 << 46;

@@ -91,6 +91,17 @@ class Engine(object):
             out[name] = dict(ms=ms.value, launches=n.value, flops=fl.value, bytes=by.value)
         return out
 
+    def profile_launches(self):
+        """-> [(class, ms, flops, bytes)] per recorded launch, in launch order."""
+        out, i = [], 0
+        while True:
+            cat = ctypes.c_int()
+            ms, fl, by = ctypes.c_double(), ctypes.c_double(), ctypes.c_double()
+            if self.lib.dcv_profile_launch(self.ctx, i, ctypes.byref(cat), ctypes.byref(ms), ctypes.byref(fl), ctypes.byref(by)) < 0:
+                return out
+            out.append((self.KERNEL_CLASSES[cat.value], ms.value, fl.value, by.value))
+            i += 1
+
     # -- network
     def clear(self):
         self._ck(self.lib.dcv_net_clear(self.ctx))

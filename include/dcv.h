@@ -82,6 +82,8 @@ enum dcv_kernel_class {
  * ms, the number of launches and the algorithmic flops / bytes those launches were given. */
 DCV_API int dcv_profile(dcv_ctx* ctx, int enable);
 DCV_API int dcv_profile_read(dcv_ctx* ctx, int kernel_class, double* ms, long long* launches, double* flops, double* bytes);
+/* The index-th recorded launch since dcv_profile(ctx, 1), in launch order; DCV_ERR_ARG past the end. */
+DCV_API int dcv_profile_launch(dcv_ctx* ctx, int index, int* kernel_class, double* ms, double* flops, double* bytes);
 
 /* ---- network description: replaces the wrapper stack of visualize_all_layers (deepdream.py:401-423)
  * and DConvolution2D.__init__ (deepdream.py:58-89), which the reference rebuilds on every request.
