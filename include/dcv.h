@@ -142,6 +142,23 @@ DCV_API int dcv_project_dev(dcv_ctx* ctx, int layer, const int* feat, int n, int
 DCV_API int dcv_deprocess(dcv_ctx* ctx, float* x, size_t n, uint8_t* out, int mutate);
 DCV_API int dcv_deprocess_dev(dcv_ctx* ctx, const float* x_dev, size_t n, uint8_t* out_dev);
 
+/* De-process without any GPU allocation (no counterpart in the reference, which never touches a GPU).
+ * For callers that cannot call cudaMalloc: a server whose memory pool owns the whole device, a request
+ * path that cannot afford the device-wide synchronisation cudaMalloc/cudaFree imply, a sandbox that only
+ * admits pre-declared buffers.  Same arithmetic and same result as dcv_deprocess_dev, but the reduction
+ * partials live in a fixed 16 KiB array inside the library image (one copy per GPU, held until the
+ * process exits) instead of the context's growable scratch buffer.
+ *   - x_dev (16-byte aligned) and out_dev (4-byte aligned) are device pointers supplied by the caller;
+ *     n <= DCV_DEPROCESS_NOALLOC_MAX_ELEMS, larger inputs are refused with DCV_ERR_ARG;
+ *   - the first call on each device looks up the array's device address; make that call before any
+ *     stream capture begins;
+ *   - all calls (from every context on that device) share the one array: two calls whose kernels can
+ *     overlap on the GPU race on it — issue them on one stream or order them with events;
+ *   - the call is asynchronous on the context's stream, like dcv_deprocess_dev. */
+#define DCV_DEPROCESS_NOALLOC_MAX_PARTIALS 1024
+#define DCV_DEPROCESS_NOALLOC_MAX_ELEMS (1ull << 28)
+DCV_API int dcv_deprocess_dev_noalloc(dcv_ctx* ctx, const float* x_dev, size_t n, uint8_t* out_dev);
+
 /* ---- standalone layer operators on host buffers (unit parity; used by the D* wrapper classes) --- */
 /* DPooling.up (deepdream.py:129-139,152-188).  x (B,H,W,C) -> pooled (B,H/2,W/2,C) float32 (the
  * reference's float64 holds the same values), sw (B,H/2,W/2,C) bytes as in dcv_read_switch. */
