@@ -122,6 +122,7 @@ extern "C" void dcv_destroy(dcv_ctx* ctx) {
   ctx->feat_dev.release();
   ctx->scratch.release();
   ctx->stage.release();
+  for (auto& b : ctx->dream) b.release();
   cudaStreamDestroy(ctx->stream);
   delete ctx;
 }
@@ -258,7 +259,7 @@ extern "C" int dcv_net_add_dense(dcv_ctx* ctx, const float* w, const float* bias
 extern "C" int dcv_net_num_layers(const dcv_ctx* ctx) { return ctx ? (int)ctx->net.size() : DCV_ERR_ARG; }
 
 // ---- forward tape -----------------------------------------------------------------------------------
-static int forward_impl(dcv_ctx* ctx, const float* img, bool on_device, int B, int H, int W, int upto) {
+int forward_impl(dcv_ctx* ctx, const float* img, bool on_device, int B, int H, int W, int upto) {
   if (!img || B <= 0 || H <= 0 || W <= 0) return ctx->fail(DCV_ERR_ARG, "dcv_forward: bad arguments");
   if (ctx->net.empty()) return ctx->fail(DCV_ERR_STATE, "dcv_forward: empty network");
   if (upto < 0 || upto >= (int)ctx->net.size()) return ctx->fail(DCV_ERR_ARG, "dcv_forward: layer %d out of range", upto);

@@ -35,6 +35,7 @@ int channel_sums_partials(size_t rows, int C);
 // norm (optional): the normalised floats the reference leaves in its argument (deepdream.py:485-490)
 void launch_deprocess(const float* x, size_t n, double* partial, int npartial, uint8_t* out, float* norm, cudaStream_t s);
 int deprocess_partials(size_t n);
+void launch_sum_stats(const float* x, size_t n, double* partial, int npartial, cudaStream_t s);
 // seed maps: maps[(k*B+b), y, x] = act[b, y, x, feat[k]]
 void launch_gather_map(const float* act, int B, int H, int W, int C, const int* feat_dev, int n, float* maps, cudaStream_t s);
 // DCV_VIS_MAX: maps (n, len) -> keep only the entries equal to the map maximum
@@ -58,5 +59,10 @@ void launch_dense_fwd(const float* x, const float* w, const float* bias, int B, 
 void launch_dense_bwd(const float* x, const float* w, int B, int nin, int nout, float* out, cudaStream_t s);
 void launch_softmax_rows(const float* x, int B, int n, float* out, cudaStream_t s);
 void launch_relu(const float* x, size_t n, float* out, cudaStream_t s);
+}  // namespace dcv
+// dream.cu
+void launch_resize_bilinear(const float* x, int B, int H, int W, int C, int OH, int OW, float* out, cudaStream_t s);
+void launch_roll(const float* x, int B, int H, int W, int C, int oy, int ox, float* out, cudaStream_t s);
+namespace dcv {
 
 }  // namespace dcv

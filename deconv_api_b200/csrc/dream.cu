@@ -1,0 +1,355 @@
+// DeepDream gradient-ascent loop (a12 in SURVEY.md §8a).  The reference has NO such code (its
+// app/deepdream.py is deconvnet-only); the algorithm is the derived spec of SURVEY.md Appendix A:
+//   per octave (small -> large): img = resize_bilinear(img, shape); `iterations` times:
+//       x = roll(img, (oy,ox)); loss = sum_l coeff_l * mean(act_l(x)^2); g = dloss/dx (true backprop: ReLU
+//       masks by forward sign, max-pool routes by switch, conv backward = flipped-filter conv, no ReLU);
+//       img += step * unroll(g) / max(sqrt(mean(g^2)), 1e-7)        (per image)
+//     then img += resize(orig, shape) - resize(orig at the previous octave's shape, shape).
+// Forward = the fp32 tape of dcv_forward; backward re-uses the backward-conv and unpool kernels of the
+// projection path.  Streaming kernels here: bilinear resize (half-pixel centres, no antialias), jitter
+// roll, gradient prep (seed + ReLU mask), RMS partials, fused normalise + un-roll + update.
+#include "common.cuh"
+#include "internal.cuh"
+
+#include <algorithm>
+#include <vector>
+
+using namespace dcv;
+
+namespace {
+
+inline int grid_for(size_t work, int block, int waves = 16) {
+  size_t b = (work + block - 1) / block, cap = (size_t)kNumSMs * waves;
+  if (b > cap) b = cap;
+  return (int)(b < 1 ? 1 : b);
+}
+
+// Bilinear resize, NHWC, align_corners = false: src = (dst + 0.5) * (in/out) - 0.5 clamped at 0,
+// neighbours x0 = floor(src), x1 = min(x0 + 1, in - 1).  One thread = one output element.
+__global__ void resize_bilinear_kernel(const float* __restrict__ x, int B, int H, int W, int C, int OH, int OW,
+                                       float* __restrict__ out) {
+  const float sh = (float)H / (float)OH, sw = (float)W / (float)OW;
+  const size_t total = (size_t)B * OH * OW * C;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C);
+    size_t p = i / C;
+    const int ox = (int)(p % OW); p /= OW;
+    const int oy = (int)(p % OH);
+    const int b = (int)(p / OH);
+    float fy = sh * ((float)oy + 0.5f) - 0.5f; if (fy < 0.f) fy = 0.f;
+    float fx = sw * ((float)ox + 0.5f) - 0.5f; if (fx < 0.f) fx = 0.f;
+    int y0 = (int)fy, x0 = (int)fx;
+    if (y0 > H - 1) y0 = H - 1;
+    if (x0 > W - 1) x0 = W - 1;
+    const int y1 = y0 + (y0 < H - 1 ? 1 : 0), x1 = x0 + (x0 < W - 1 ? 1 : 0);
+    const float ly = fy - (float)y0, lx = fx - (float)x0;
+    const float hy = 1.f - ly, hx = 1.f - lx;
+    const float* base = x + (size_t)b * H * W * C + c;
+    const float v00 = __ldg(base + ((size_t)y0 * W + x0) * C), v01 = __ldg(base + ((size_t)y0 * W + x1) * C);
+    const float v10 = __ldg(base + ((size_t)y1 * W + x0) * C), v11 = __ldg(base + ((size_t)y1 * W + x1) * C);
+    out[i] = hy * (hx * v00 + lx * v01) + ly * (hx * v10 + lx * v11);
+  }
+}
+
+// out[b, y, x] = in[b, (y - oy) mod H, (x - ox) mod W]   (numpy.roll over the two spatial axes)
+__global__ void roll_kernel(const float* __restrict__ x, int B, int H, int W, int C, int oy, int ox, float* __restrict__ out) {
+  const size_t total = (size_t)B * H * W * C;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C);
+    size_t p = i / C;
+    const int xx = (int)(p % W); p /= W;
+    const int y = (int)(p % H);
+    const int b = (int)(p / H);
+    int sy = (y - oy) % H; if (sy < 0) sy += H;
+    int sx = (xx - ox) % W; if (sx < 0) sx += W;
+    out[i] = __ldg(x + (((size_t)b * H + sy) * W + sx) * C + c);
+  }
+}
+
+// gradient w.r.t. a layer's pre-activation: g = mask(act > 0) * (g_above + scale * act).  g_above may be absent.
+__global__ void dream_prep_kernel(float* __restrict__ g, const float* __restrict__ act, size_t n, float scale, int has_g, int relu) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const float a = __ldg(act + i);
+    float v = (has_g ? g[i] : 0.f) + scale * a;
+    if (relu && !(a > 0.f)) v = 0.f;
+    g[i] = v;
+  }
+}
+
+// img[b,y,x,c] += step / max(rms_b, 1e-7) * g[b,(y+oy) mod H,(x+ox) mod W,c]; rms from the fp64 block partials
+__global__ void __launch_bounds__(256)
+dream_update_kernel(float* __restrict__ img, const float* __restrict__ g, const double* __restrict__ partial, int np,
+                    int H, int W, int C, float step, int oy, int ox) {
+  __shared__ float s_scale;
+  const size_t n = (size_t)H * W * C;
+  if (threadIdx.x == 0) {
+    double q = 0.0;
+    for (int k = 0; k < np; ++k) q += partial[2 * k + 1];
+    const float rms = (float)sqrt(q / (double)n);
+    s_scale = step / fmaxf(rms, 1e-7f);
+  }
+  __syncthreads();
+  const float sc = s_scale;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C);
+    size_t p = i / C;
+    const int xx = (int)(p % W);
+    const int y = (int)(p / W);
+    int sy = (y + oy) % H; if (sy < 0) sy += H;
+    int sx = (xx + ox) % W; if (sx < 0) sx += W;
+    img[i] = fmaf(sc, __ldg(g + ((size_t)sy * W + sx) * C + c), img[i]);
+  }
+}
+
+__global__ void add_diff_kernel(float* __restrict__ img, const float* __restrict__ a, const float* __restrict__ b, size_t n) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    img[i] += a[i] - b[i];
+}
+
+}  // namespace
+
+void launch_resize_bilinear(const float* x, int B, int H, int W, int C, int OH, int OW, float* out, cudaStream_t s) {
+  const size_t total = (size_t)B * OH * OW * C;
+  if (total) resize_bilinear_kernel<<<grid_for(total, 256), 256, 0, s>>>(x, B, H, W, C, OH, OW, out);
+}
+
+void launch_roll(const float* x, int B, int H, int W, int C, int oy, int ox, float* out, cudaStream_t s) {
+  const size_t total = (size_t)B * H * W * C;
+  if (total) roll_kernel<<<grid_for(total, 256), 256, 0, s>>>(x, B, H, W, C, oy, ox, out);
+}
+
+// ---- host side ----------------------------------------------------------------------------------------
+#define CUD(ctx, expr)                                                                            \
+  do {                                                                                            \
+    cudaError_t e_ = (expr);                                                                      \
+    if (e_ != cudaSuccess) return (ctx)->fail(DCV_ERR_CUDA, "%s: %s", #expr, cudaGetErrorString(e_)); \
+  } while (0)
+#define TRYD(expr) do { int r_ = (expr); if (r_) return r_; } while (0)
+
+namespace {
+
+struct LossSpec {
+  std::vector<float> coeff;      // per net layer, 0 = not a loss layer
+  int deepest = -1;
+};
+
+int parse_losses(dcv_ctx* ctx, const int* layers, const float* coeffs, int nl, LossSpec* out) {
+  if (!layers || !coeffs || nl <= 0) return ctx->fail(DCV_ERR_ARG, "dream: no loss layers given");
+  out->coeff.assign(ctx->net.size(), 0.f);
+  for (int k = 0; k < nl; ++k) {
+    if (layers[k] < 0 || layers[k] >= (int)ctx->net.size()) return ctx->fail(DCV_ERR_ARG, "dream: loss layer %d out of range", layers[k]);
+    if (ctx->net[layers[k]].kind != LK_CONV && ctx->net[layers[k]].kind != LK_POOL)
+      return ctx->fail(DCV_ERR_UNSUPPORTED, "dream: loss layers must be conv or pool layers");
+    out->coeff[layers[k]] += coeffs[k];
+    out->deepest = std::max(out->deepest, layers[k]);
+  }
+  return 0;
+}
+
+// Backward pass of loss = sum_l coeff_l * mean(act_l^2) through the current tape; leaves dloss/dinput
+// (B,H,W,C0) in *grad (one of ctx->dream[4], ctx->dream[5]).  If loss_out != null the loss value is computed too.
+int dream_backward(dcv_ctx* ctx, const LossSpec& ls, float** grad, double* loss_out) {
+  const int B = ctx->in_B;
+  size_t max_elems = (size_t)B * ctx->in_H * ctx->in_W * ctx->in_C;
+  for (int j = 0; j <= ls.deepest; ++j) max_elems = std::max(max_elems, (size_t)ctx->net[j].B * ctx->net[j].H * ctx->net[j].W * ctx->net[j].C);
+  TRYD(ctx->dream[4].ensure(ctx, max_elems * sizeof(float)));
+  TRYD(ctx->dream[5].ensure(ctx, max_elems * sizeof(float)));
+  float* bufs[2] = {(float*)ctx->dream[4].p, (float*)ctx->dream[5].p};
+  int cur = 0;
+  bool has_g = false;
+  double loss = 0.0;
+  for (int j = ls.deepest; j >= 0; --j) {
+    const Layer& l = ctx->net[j];
+    const size_t n = (size_t)l.B * l.H * l.W * l.C;
+    const float coeff = ls.coeff[j];
+    if (coeff != 0.f && loss_out) {
+      const int np = deprocess_partials(n);
+      TRYD(ctx->scratch.ensure(ctx, (size_t)np * 2 * sizeof(double)));
+      launch_sum_stats((const float*)l.act.p, n, (double*)ctx->scratch.p, np, ctx->stream); ctx->launches++;
+      std::vector<double> h((size_t)np * 2);
+      CUD(ctx, cudaMemcpyAsync(h.data(), ctx->scratch.p, h.size() * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+      CUD(ctx, cudaStreamSynchronize(ctx->stream));
+      double q = 0.0;
+      for (int k = 0; k < np; ++k) q += h[2 * k + 1];
+      loss += (double)coeff * q / (double)n;
+    }
+    const float scale = coeff != 0.f ? 2.f * coeff / (float)n : 0.f;
+    if (l.kind == LK_CONV) {
+      if (!has_g && scale == 0.f) continue;          // nothing flows yet (layers above the deepest loss)
+      {
+        ProfScope ps(ctx, DCV_K_OTHER, 0.0, 12.0 * n);
+        dream_prep_kernel<<<grid_for(n, 256), 256, 0, ctx->stream>>>(bufs[cur], (const float*)l.act.p, n, scale, has_g ? 1 : 0, l.relu);
+        ctx->launches++;
+      }
+      ConvEpilogue e;                                  // conv backward-data: no bias, no ReLU
+      ProfScope ps(ctx, DCV_K_CONV_FP32, 2.0 * 9 * l.B * l.H * l.W * (double)l.cin * l.cout, 4.0 * l.B * l.H * l.W * ((double)l.cin + l.cout));
+      launch_conv3x3_fp32(bufs[cur], l.wd, l.B, l.H, l.W, l.cout, l.cin, e, bufs[cur ^ 1], ctx->stream); ctx->launches++;
+      cur ^= 1;
+      has_g = true;
+    } else if (l.kind == LK_POOL) {
+      if (!has_g && scale == 0.f) continue;
+      {
+        ProfScope ps(ctx, DCV_K_OTHER, 0.0, 12.0 * n);
+        dream_prep_kernel<<<grid_for(n, 256), 256, 0, ctx->stream>>>(bufs[cur], (const float*)l.act.p, n, scale, has_g ? 1 : 0, 0);
+        ctx->launches++;
+      }
+      // max-pool backward = unpool by switch; trailing row/column of an odd input gets zero gradient
+      ProfScope ps(ctx, DCV_K_UNPOOL, 0.0, (double)l.B * l.in_H * l.in_W * l.C * (4.0 + 5.0 / 4.0));
+      launch_unpool_switch_items(bufs[cur], (const uint8_t*)l.sw.p, l.B, l.B, l.in_H, l.in_W, l.C, 0, bufs[cur ^ 1], ctx->stream);
+      ctx->launches++;
+      cur ^= 1;
+      has_g = true;
+    } else {
+      return ctx->fail(DCV_ERR_UNSUPPORTED, "dream: only conv/pool layers are supported below the loss layers");
+    }
+  }
+  if (!has_g) return ctx->fail(DCV_ERR_ARG, "dream: all loss coefficients are zero");
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "dream backward: %s", cudaGetErrorString(e));
+  *grad = bufs[cur];
+  if (loss_out) *loss_out = loss;
+  return 0;
+}
+
+// one jittered ascent step on the device image img (B,H,W,C)
+int dream_iter(dcv_ctx* ctx, float* img, int B, int H, int W, int C, const LossSpec& ls, float step, int oy, int ox, double* loss_out) {
+  const size_t n = (size_t)B * H * W * C;
+  TRYD(ctx->dream[3].ensure(ctx, n * sizeof(float)));
+  float* x = (float*)ctx->dream[3].p;
+  {
+    ProfScope ps(ctx, DCV_K_OTHER, 0.0, 8.0 * n);
+    launch_roll(img, B, H, W, C, oy, ox, x, ctx->stream); ctx->launches++;
+  }
+  TRYD(forward_impl(ctx, x, true, B, H, W, ls.deepest));
+  float* g = nullptr;
+  TRYD(dream_backward(ctx, ls, &g, loss_out));
+  const size_t per = (size_t)H * W * C;
+  const int np = deprocess_partials(per);
+  TRYD(ctx->scratch.ensure(ctx, (size_t)np * 2 * sizeof(double)));
+  for (int b = 0; b < B; ++b) {          // the RMS normalisation is per image
+    ProfScope ps(ctx, DCV_K_OTHER, 0.0, 16.0 * per);
+    launch_sum_stats(g + b * per, per, (double*)ctx->scratch.p, np, ctx->stream);
+    dream_update_kernel<<<grid_for(per, 256, 8), 256, 0, ctx->stream>>>(img + b * per, g + b * per, (const double*)ctx->scratch.p, np,
+                                                                         H, W, C, step, oy, ox);
+    ctx->launches += 2;
+  }
+  return 0;
+}
+
+int dream_impl(dcv_ctx* ctx, const float* img_in, bool on_device, int B, int H, int W, const int* loss_layers, const float* coeffs,
+               int nl, const int* shapes, int n_oct, int iterations, float step, const int* jitter, float* out, double* losses) {
+  if (!img_in || !out || B <= 0 || H <= 0 || W <= 0 || !shapes || n_oct <= 0 || iterations < 0 || (iterations > 0 && !jitter))
+    return ctx->fail(DCV_ERR_ARG, "dcv_dream: bad arguments");
+  if (ctx->net.empty() || ctx->net[0].kind != LK_CONV) return ctx->fail(DCV_ERR_STATE, "dcv_dream: network must start with a conv layer");
+  LossSpec ls;
+  TRYD(parse_losses(ctx, loss_layers, coeffs, nl, &ls));
+  const int C = ctx->net[0].cin;
+  if (shapes[2 * (n_oct - 1)] != H || shapes[2 * (n_oct - 1) + 1] != W)
+    return ctx->fail(DCV_ERR_ARG, "dcv_dream: the last octave shape must be the image size %dx%d", H, W);
+  size_t max_px = 0;
+  for (int k = 0; k < n_oct; ++k) {
+    if (shapes[2 * k] < 8 || shapes[2 * k + 1] < 8) return ctx->fail(DCV_ERR_ARG, "dcv_dream: octave %d is smaller than 8x8", k);
+    max_px = std::max(max_px, (size_t)shapes[2 * k] * shapes[2 * k + 1]);
+  }
+  const size_t full = (size_t)B * H * W * C, maxn = (size_t)B * max_px * C;
+  for (int k = 0; k < 3; ++k) TRYD(ctx->dream[k].ensure(ctx, std::max(full, maxn) * sizeof(float)));
+  TRYD(ctx->stage.ensure(ctx, 2 * maxn * sizeof(float)));
+  float* img = (float*)ctx->dream[0].p;
+  float* orig = (float*)ctx->dream[1].p;
+  float* shrunk = (float*)ctx->dream[2].p;
+  float* tmp_a = (float*)ctx->stage.p;
+  float* tmp_b = tmp_a + maxn;
+  CUD(ctx, cudaMemcpyAsync(orig, img_in, full * sizeof(float), on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, ctx->stream));
+  CUD(ctx, cudaMemcpyAsync(img, orig, full * sizeof(float), cudaMemcpyDeviceToDevice, ctx->stream));
+  int ch = H, cw = W;                       // current size of img
+  int sh = shapes[0], sw = shapes[1];       // size of `shrunk`
+  launch_resize_bilinear(orig, B, H, W, C, sh, sw, shrunk, ctx->stream); ctx->launches++;
+  for (int k = 0; k < n_oct; ++k) {
+    const int oh = shapes[2 * k], ow = shapes[2 * k + 1];
+    const size_t n = (size_t)B * oh * ow * C;
+    if (oh != ch || ow != cw) {
+      ProfScope ps(ctx, DCV_K_OTHER, 0.0, 4.0 * ((double)B * ch * cw * C + n));
+      launch_resize_bilinear(img, B, ch, cw, C, oh, ow, tmp_a, ctx->stream); ctx->launches++;
+      CUD(ctx, cudaMemcpyAsync(img, tmp_a, n * sizeof(float), cudaMemcpyDeviceToDevice, ctx->stream));
+      ch = oh; cw = ow;
+    }
+    for (int it = 0; it < iterations; ++it) {
+      const int* j = jitter + 2 * ((size_t)k * iterations + it);
+      TRYD(dream_iter(ctx, img, B, oh, ow, C, ls, step, j[0], j[1], losses ? losses + (size_t)k * iterations + it : nullptr));
+    }
+    // re-inject the detail lost by having worked at a lower resolution
+    launch_resize_bilinear(shrunk, B, sh, sw, C, oh, ow, tmp_a, ctx->stream);          // upscaled shrunk original
+    launch_resize_bilinear(orig, B, H, W, C, oh, ow, tmp_b, ctx->stream);              // original at this size
+    add_diff_kernel<<<grid_for(n, 256), 256, 0, ctx->stream>>>(img, tmp_b, tmp_a, n);
+    ctx->launches += 3;
+    CUD(ctx, cudaMemcpyAsync(shrunk, tmp_b, n * sizeof(float), cudaMemcpyDeviceToDevice, ctx->stream));
+    sh = oh; sw = ow;
+  }
+  CUD(ctx, cudaGetLastError());
+  CUD(ctx, cudaMemcpyAsync(out, img, full * sizeof(float), on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, ctx->stream));
+  return 0;
+}
+
+}  // namespace
+
+#define ENTERD(ctx)                                                       \
+  if (!(ctx)) return DCV_ERR_ARG;                                          \
+  CUD(ctx, cudaSetDevice((ctx)->device));
+
+extern "C" int dcv_dream(dcv_ctx* ctx, const float* img, int B, int H, int W, const int* loss_layers, const float* coeffs, int nl,
+                         const int* shapes, int n_oct, int iterations, float step, const int* jitter, float* out, double* losses) {
+  ENTERD(ctx);
+  TRYD(dream_impl(ctx, img, false, B, H, W, loss_layers, coeffs, nl, shapes, n_oct, iterations, step, jitter, out, losses));
+  CUD(ctx, cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+extern "C" int dcv_dream_dev(dcv_ctx* ctx, const float* img_dev, int B, int H, int W, const int* loss_layers, const float* coeffs,
+                             int nl, const int* shapes, int n_oct, int iterations, float step, const int* jitter, float* out_dev) {
+  ENTERD(ctx);
+  return dream_impl(ctx, img_dev, true, B, H, W, loss_layers, coeffs, nl, shapes, n_oct, iterations, step, jitter, out_dev, nullptr);
+}
+
+extern "C" int dcv_dream_gradient(dcv_ctx* ctx, const float* img, int B, int H, int W, const int* loss_layers, const float* coeffs,
+                                  int nl, float* grad_out, double* loss_out) {
+  ENTERD(ctx);
+  if (!img || !grad_out || B <= 0 || H <= 0 || W <= 0) return ctx->fail(DCV_ERR_ARG, "dcv_dream_gradient: bad arguments");
+  LossSpec ls;
+  TRYD(parse_losses(ctx, loss_layers, coeffs, nl, &ls));
+  TRYD(forward_impl(ctx, img, false, B, H, W, ls.deepest));
+  float* g = nullptr;
+  TRYD(dream_backward(ctx, ls, &g, loss_out));
+  CUD(ctx, cudaMemcpyAsync(grad_out, g, (size_t)B * H * W * ctx->in_C * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+  CUD(ctx, cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+extern "C" int dcv_resize_bilinear(dcv_ctx* ctx, const float* x, int B, int H, int W, int C, int OH, int OW, float* out) {
+  ENTERD(ctx);
+  if (!x || !out || B <= 0 || H <= 0 || W <= 0 || C <= 0 || OH <= 0 || OW <= 0) return ctx->fail(DCV_ERR_ARG, "dcv_resize_bilinear: bad arguments");
+  const size_t nin = (size_t)B * H * W * C, nout = (size_t)B * OH * OW * C;
+  const size_t o1 = (nin * 4 + 255) & ~(size_t)255;
+  TRYD(ctx->stage.ensure(ctx, o1 + nout * 4));
+  char* base = (char*)ctx->stage.p;
+  CUD(ctx, cudaMemcpyAsync(base, x, nin * 4, cudaMemcpyHostToDevice, ctx->stream));
+  launch_resize_bilinear((const float*)base, B, H, W, C, OH, OW, (float*)(base + o1), ctx->stream); ctx->launches++;
+  CUD(ctx, cudaGetLastError());
+  CUD(ctx, cudaMemcpyAsync(out, base + o1, nout * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  CUD(ctx, cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+extern "C" int dcv_roll(dcv_ctx* ctx, const float* x, int B, int H, int W, int C, int oy, int ox, float* out) {
+  ENTERD(ctx);
+  if (!x || !out || B <= 0 || H <= 0 || W <= 0 || C <= 0) return ctx->fail(DCV_ERR_ARG, "dcv_roll: bad arguments");
+  const size_t n = (size_t)B * H * W * C;
+  const size_t o1 = (n * 4 + 255) & ~(size_t)255;
+  TRYD(ctx->stage.ensure(ctx, o1 + n * 4));
+  char* base = (char*)ctx->stage.p;
+  CUD(ctx, cudaMemcpyAsync(base, x, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+  launch_roll((const float*)base, B, H, W, C, oy, ox, (float*)(base + o1), ctx->stream); ctx->launches++;
+  CUD(ctx, cudaGetLastError());
+  CUD(ctx, cudaMemcpyAsync(out, base + o1, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  CUD(ctx, cudaStreamSynchronize(ctx->stream));
+  return 0;
+}

@@ -53,6 +53,7 @@ struct dcv_ctx {
   DevBuf feat_dev;
   DevBuf scratch;      // reduction partials
   DevBuf stage;        // staging for host-buffer entry points
+  DevBuf dream[6];     // DeepDream: image, original, shrunk original, rolled input / resize temp, 2 gradient buffers
   // optional per-kernel-class timing (dcv_profile): CUDA events around every launch of a class
   bool prof_on = false;
   std::vector<ProfRec> prof;
@@ -67,6 +68,9 @@ struct ProfScope {
   ProfScope(dcv_ctx* ctx, int cat, double flops, double bytes) : c(ctx) { if (c->prof_on) c->prof_begin(cat, flops, bytes); }
   ~ProfScope() { if (c->prof_on) c->prof_end(); }
 };
+
+// api.cu
+int forward_impl(dcv_ctx* ctx, const float* img, bool on_device, int B, int H, int W, int upto);
 
 // conv_tc.cu — bf16 tensor-core chain in the padded-flat layout (see the header comment there)
 int tc_prepare_layer(dcv_ctx* ctx, Layer& l);

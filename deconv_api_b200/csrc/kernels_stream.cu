@@ -307,6 +307,11 @@ void launch_deprocess(const float* x, size_t n, double* partial, int npartial, u
   deprocess_map_kernel<<<grid_for((n + 3) / 4, 256, 8), 256, 0, s>>>(x, n, partial, npartial, out, norm);
 }
 
+// fp64 (sum, sum of squares) block partials of x[0..n): partial[2*b], partial[2*b+1]; x 16-byte aligned
+void launch_sum_stats(const float* x, size_t n, double* partial, int npartial, cudaStream_t s) {
+  deprocess_stats_kernel<<<npartial, 256, 0, s>>>(x, n, partial);
+}
+
 // ------------------------------------------------------------------------------------------------
 // Seed maps of the projections (deepdream.py:450-465): map[(k*B+b), y, x] = act[b, y, x, feat[k]].
 __global__ void gather_map_kernel(const float* __restrict__ act, int B, size_t HW, int C,

@@ -281,6 +281,56 @@ class Engine(object):
         return out
 
 
+    # -- DeepDream (derived spec)
+    def resize_bilinear(self, x, out_hw):
+        x = _f32(x)
+        B, H, W, C = x.shape
+        out = np.empty((B, int(out_hw[0]), int(out_hw[1]), C), np.float32)
+        self._ck(self.lib.dcv_resize_bilinear(self.ctx, _ptr(x), B, H, W, C, int(out_hw[0]), int(out_hw[1]), _ptr(out)))
+        return out
+
+    def roll(self, x, oy, ox):
+        x = _f32(x)
+        B, H, W, C = x.shape
+        out = np.empty_like(x)
+        self._ck(self.lib.dcv_roll(self.ctx, _ptr(x), B, H, W, C, int(oy), int(ox), _ptr(out)))
+        return out
+
+    def dream_gradient(self, img, loss_layers, coeffs):
+        """-> (dloss/dimg (B,H,W,C) float32, loss float)"""
+        img = _f32(img)
+        B, H, W, _ = img.shape
+        ll = np.ascontiguousarray(loss_layers, np.int32)
+        cf = np.ascontiguousarray(coeffs, np.float32)
+        g = np.empty_like(img)
+        loss = ctypes.c_double()
+        self._ck(self.lib.dcv_dream_gradient(self.ctx, _ptr(img), B, H, W, _ptr(ll), _ptr(cf), int(ll.size), _ptr(g), ctypes.byref(loss)))
+        return g, loss.value
+
+    def dream(self, img, loss_layers, coeffs, shapes, iterations, step, jitter, want_losses=False):
+        img = _f32(img)
+        B, H, W, _ = img.shape
+        ll = np.ascontiguousarray(loss_layers, np.int32)
+        cf = np.ascontiguousarray(coeffs, np.float32)
+        sh = np.ascontiguousarray(shapes, np.int32).reshape(-1, 2)
+        jt = np.ascontiguousarray(jitter, np.int32).reshape(-1, 2)
+        assert jt.shape[0] == sh.shape[0] * iterations, "need one (oy, ox) pair per iteration"
+        out = np.empty_like(img)
+        losses = np.zeros((sh.shape[0] * iterations,), np.float64) if want_losses else None
+        self._ck(self.lib.dcv_dream(self.ctx, _ptr(img), B, H, W, _ptr(ll), _ptr(cf), int(ll.size), _ptr(sh), int(sh.shape[0]),
+                                    int(iterations), ctypes.c_float(step), _ptr(jt), _ptr(out),
+                                    _ptr(losses) if losses is not None else None))
+        return (out, losses) if want_losses else out
+
+    def dream_dev(self, img_dev_ptr, B, H, W, loss_layers, coeffs, shapes, iterations, step, jitter, out_dev_ptr):
+        ll = np.ascontiguousarray(loss_layers, np.int32)
+        cf = np.ascontiguousarray(coeffs, np.float32)
+        sh = np.ascontiguousarray(shapes, np.int32).reshape(-1, 2)
+        jt = np.ascontiguousarray(jitter, np.int32).reshape(-1, 2)
+        self._ck(self.lib.dcv_dream_dev(self.ctx, ctypes.c_void_p(img_dev_ptr), B, H, W, _ptr(ll), _ptr(cf), int(ll.size), _ptr(sh),
+                                        int(sh.shape[0]), int(iterations), ctypes.c_float(step), _ptr(jt), ctypes.c_void_p(out_dev_ptr)))
+
+
 def default_engine(device=None):
     """Process-wide engine for `device` (default: LOCAL_RANK or 0), created on first use."""
     import os

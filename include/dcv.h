@@ -184,6 +184,27 @@ DCV_API int dcv_dense(dcv_ctx* ctx, const float* x, const float* w, const float*
  * (deepdream.py:289-297). */
 DCV_API int dcv_dense_transpose(dcv_ctx* ctx, const float* x, const float* w, int B, int nin, int nout, float* out);
 
+/* ---- DeepDream (BASELINE.json north_star; NO counterpart in the reference: app/deepdream.py holds only
+ * deconvnet code).  Algorithm = the derived spec of SURVEY.md Appendix A, restated in
+ * csrc/dream.cu.  The network must consist of conv/pool layers (include_top = False), any image size.
+ *   loss = sum_k coeffs[k] * mean(act_{loss_layers[k]}^2);   per iteration: x = roll(img, (oy,ox)),
+ *   g = dloss/dx, img += step * unroll(g) / max(rms(g), 1e-7)  (rms per image).
+ * shapes: n_oct (h,w) pairs, smallest first, the last one equal to (H,W); jitter: n_oct*iterations (oy,ox)
+ * pairs drawn by the caller (so that an oracle can use the same stream); losses (optional, host):
+ * n_oct*iterations loss values BEFORE each update (costs a device sync per iteration). ------------ */
+DCV_API int dcv_dream(dcv_ctx* ctx, const float* img, int B, int H, int W, const int* loss_layers, const float* coeffs, int nl,
+                      const int* shapes, int n_oct, int iterations, float step, const int* jitter, float* out, double* losses);
+/* Same on device buffers, asynchronous on the context's stream. */
+DCV_API int dcv_dream_dev(dcv_ctx* ctx, const float* img_dev, int B, int H, int W, const int* loss_layers, const float* coeffs,
+                          int nl, const int* shapes, int n_oct, int iterations, float step, const int* jitter, float* out_dev);
+/* One forward + backward: grad_out (B,H,W,C0) = dloss/dimg (un-normalised), loss_out (optional) = loss. */
+DCV_API int dcv_dream_gradient(dcv_ctx* ctx, const float* img, int B, int H, int W, const int* loss_layers, const float* coeffs,
+                               int nl, float* grad_out, double* loss_out);
+/* Bilinear resize NHWC, half-pixel centres (align_corners = False), no antialiasing: the octave resize. */
+DCV_API int dcv_resize_bilinear(dcv_ctx* ctx, const float* x, int B, int H, int W, int C, int OH, int OW, float* out);
+/* numpy.roll over the two spatial axes by (oy, ox): the jitter. */
+DCV_API int dcv_roll(dcv_ctx* ctx, const float* x, int B, int H, int W, int C, int oy, int ox, float* out);
+
 #ifdef __cplusplus
 }
 #endif

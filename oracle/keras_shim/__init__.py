@@ -212,7 +212,7 @@ class MaxPooling2D(Layer):
         self.padding = padding
 
     def compute_output_shape(self, s):
-        return (s[0], s[1] // self.pool_size[0], s[2] // self.pool_size[1], s[3])
+        return (s[0], None if s[1] is None else s[1] // self.pool_size[0], None if s[2] is None else s[2] // self.pool_size[1], s[3])
 
     def call(self, x):
         xt = torch.from_numpy(np.ascontiguousarray(np.asarray(x, np.float32))).permute(0, 3, 1, 2)

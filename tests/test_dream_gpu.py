@@ -1,0 +1,56 @@
+"""GPU parity of the DeepDream row (a12).  No reference implementation exists: the oracle is
+oracle/dream_oracle.py (torch autograd on the Appendix-A spec) — parity against the reference is unpinned."""
+import numpy as np
+import pytest
+
+from oracle import dream_oracle as do, keras_shim
+from deconv_api_b200 import dream as dm, engine as E, synth, vgg16
+from conftest import rel_l2
+
+pytestmark = pytest.mark.gpu
+
+
+def test_resize_and_roll_vs_oracle(engine):
+    rng = np.random.default_rng(0)
+    for (h, w), (oh, ow) in (((37, 53), (61, 44)), ((64, 64), (45, 45)), ((365, 365), (512, 512)), ((20, 30), (20, 30))):
+        x = rng.normal(0, 50, (2, h, w, 3)).astype(np.float32)
+        got = engine.resize_bilinear(x, (oh, ow))
+        assert rel_l2(got, do.resize(x, (oh, ow))) < 1e-6
+    x = rng.normal(0, 1, (2, 17, 23, 3)).astype(np.float32)
+    for oy, ox in ((0, 0), (5, -7), (-32, 32), (17, 23), (40, -50)):
+        assert np.array_equal(engine.roll(x, oy, ox), np.roll(x, (oy, ox), axis=(1, 2)))
+
+
+@pytest.mark.parametrize("hw", [(64, 64), (45, 61)])          # odd sizes: pools floor, trailing row/col get zero gradient
+def test_gradient_vs_autograd(hw):
+    model = vgg16.VGG16(weights=None, include_top=False, input_shape=(None, None, 3), seed=9, bias=True)
+    ref = keras_shim.VGG16(include_top=False, input_shape=(None, None, 3), seed=9, bias=True)
+    layers = {"block2_conv2": 0.7, "block3_pool": 1.0, "block4_conv2": 2.0}
+    img = np.concatenate([synth.caffe_preprocess(synth.smooth_image_u8(s, *hw)) for s in (1, 2)], axis=0)
+    eng = model.bound_engine(upto="block4_conv2")
+    g, loss = eng.dream_gradient(img, [eng.index[n] for n in layers], list(layers.values()))
+    loss_ref, g_ref = do.loss_and_grad(do._convs(ref, "block4_conv2"), img, layers)
+    assert abs(loss - loss_ref) <= 1e-5 * abs(loss_ref)
+    assert rel_l2(g, g_ref) < 1e-5
+
+
+def test_dream_loop_vs_oracle():
+    model = vgg16.VGG16(weights=None, include_top=False, input_shape=(None, None, 3), seed=9)
+    ref = keras_shim.VGG16(include_top=False, input_shape=(None, None, 3), seed=9)
+    layers = {"block2_conv2": 0.5, "block3_conv3": 2.0}
+    img = synth.caffe_preprocess(synth.smooth_image_u8(4, 96, 80))
+    out, losses = dm.dream(model, img, layers=layers, num_octave=3, octave_scale=1.4, iterations=4, step=1.0, jitter=8,
+                           seed=3, return_losses=True)
+    shapes = dm.octave_shapes(96, 80, 3, 1.4)
+    assert shapes == [(48, 40), (68, 57), (96, 80)]
+    jt = dm.jitter_offsets(12, 8, 3)
+    out_ref, losses_ref = do.dream(ref, img, layers, shapes, 4, 1.0, jt)
+    assert out.shape == img.shape
+    assert np.allclose(losses, losses_ref, rtol=1e-4)
+    delta, delta_ref = out - img, out_ref - img
+    assert np.linalg.norm(delta_ref) > 1.0                      # the loop really changed the image
+    assert rel_l2(out, out_ref) < 1e-5
+    assert rel_l2(delta, delta_ref) < 1e-3                      # gradient ascent amplifies fp32 noise; stated tolerance
+    # single (H,W,3) image in, same shape out
+    o1 = dm.dream(model, img[0], layers=layers, num_octave=2, iterations=1, jitter=0)
+    assert o1.shape == img.shape[1:]
