@@ -45,6 +45,8 @@ def parse():
     ap.add_argument("--nfeat", type=int, default=NFEAT)
     ap.add_argument("--cpu-sample", type=int, default=48, help="projections in the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-dream", action="store_true", help="skip the secondary DeepDream measurement")
+    ap.add_argument("--dream-size", type=int, default=512)
     return ap.parse_args()
 
 
@@ -272,6 +274,10 @@ def run_ours(args, rank, world, local_rank):
                    "gbs": (v["bytes"] / (v["ms"] / 1e3) / 1e9) if v["ms"] > 0 and v["bytes"] else None}
                for k, v in prof.items() if v["launches"]}
 
+    dream = None
+    if not args.no_dream:
+        dream = bench_dream(args, local_rank)
+
     cpu = None
     if not args.no_cpu_baseline:
         r, s, cores = cpu_projection_rate(args.layer, min(args.cpu_sample, args.nfeat))
@@ -296,10 +302,52 @@ def run_ours(args, rank, world, local_rank):
         "kernel_classes": classes,
         "cpu_baseline": cpu,
         "clocks": clocks,
+        "deepdream": dream,
     }
     print(json.dumps(line), flush=True)
     if dist is not None:
         dist.destroy_process_group()
+
+
+def bench_dream(args, local_rank):
+    """Secondary BASELINE metric (configs[2]): DeepDream iterations/s on a SxS synthetic image, 3 octaves x 20
+    iterations, mixed-layer loss (block3_conv3, block4_conv3, block5_conv3).  No reference implementation exists
+    (derived spec); fp32 arithmetic in round 1."""
+    import torch
+    from deconv_api_b200 import dream as dm, synth, vgg16
+    S = args.dream_size
+    model = vgg16.VGG16(weights=None, include_top=False, input_shape=(None, None, 3))
+    eng = model.bound_engine(local_rank, upto="block5_conv3")
+    layers = dm.DEFAULT_LAYERS
+    idx = [eng.index[n] for n in layers]
+    coeffs = [layers[n] for n in layers]
+    shapes = dm.octave_shapes(S, S, 3, 1.4)
+    iters = 20
+    jt = dm.jitter_offsets(3 * iters, 32, 0)
+    img = synth.caffe_preprocess(synth.smooth_image_u8(0, S, S))
+    img_dev = torch.from_numpy(img).cuda()
+    out_dev = torch.empty_like(img_dev)
+    stream = torch.cuda.ExternalStream(eng.stream, device=local_rank)
+    eng.dream_dev(img_dev.data_ptr(), 1, S, S, idx, coeffs, shapes, iters, 1.0, jt, out_dev.data_ptr())   # warm-up
+    eng.sync()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    reps = 2
+    l0 = eng.launch_count
+    e0.record(stream)
+    for _ in range(reps):
+        eng.dream_dev(img_dev.data_ptr(), 1, S, S, idx, coeffs, shapes, iters, 1.0, jt, out_dev.data_ptr())
+    e1.record(stream)
+    eng.sync()
+    ms = e0.elapsed_time(e1) / reps
+    t0 = time.perf_counter()
+    eng.dream(img, idx, coeffs, shapes, iters, 1.0, jt)
+    ms_e2e = (time.perf_counter() - t0) * 1e3
+    fwd_gmac = sum(15.347 * (h * w) / (224.0 * 224.0) for h, w in shapes)          # conv stack to block5_conv3
+    return {"metric": "deepdream_iters_per_sec", "value": 3 * iters / (ms / 1e3), "unit": "iterations/s",
+            "e2e_value": 3 * iters / (ms_e2e / 1e3), "ms_per_dream": ms, "dtype": "f32",
+            "config": {"workload": "DeepDream %dx%d, octaves %s x %d iterations, loss on block3_conv3/block4_conv3/block5_conv3 "
+                                   "(BASELINE configs[2]; derived spec, no reference implementation)" % (S, S, shapes, iters)},
+            "tflops": 2 * 2 * fwd_gmac * iters / (ms / 1e3) / 1e3, "gpu_launches": (eng.launch_count - l0) // reps}
 
 
 def main():
