@@ -312,7 +312,7 @@ def run_ours(args, rank, world, local_rank):
 def bench_dream(args, local_rank):
     """Secondary BASELINE metric (configs[2]): DeepDream iterations/s on a SxS synthetic image, 3 octaves x 20
     iterations, mixed-layer loss (block3_conv3, block4_conv3, block5_conv3).  No reference implementation exists
-    (derived spec); fp32 arithmetic in round 1."""
+    (derived spec); --precision bf16 = tcgen05 forward and backward on a bf16 tape."""
     import torch
     from deconv_api_b200 import dream as dm, synth, vgg16
     S = args.dream_size
@@ -328,23 +328,23 @@ def bench_dream(args, local_rank):
     img_dev = torch.from_numpy(img).cuda()
     out_dev = torch.empty_like(img_dev)
     stream = torch.cuda.ExternalStream(eng.stream, device=local_rank)
-    eng.dream_dev(img_dev.data_ptr(), 1, S, S, idx, coeffs, shapes, iters, 1.0, jt, out_dev.data_ptr())   # warm-up
+    eng.dream_dev(img_dev.data_ptr(), 1, S, S, idx, coeffs, shapes, iters, 1.0, jt, out_dev.data_ptr(), precision=args.precision)   # warm-up
     eng.sync()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     reps = 2
     l0 = eng.launch_count
     e0.record(stream)
     for _ in range(reps):
-        eng.dream_dev(img_dev.data_ptr(), 1, S, S, idx, coeffs, shapes, iters, 1.0, jt, out_dev.data_ptr())
+        eng.dream_dev(img_dev.data_ptr(), 1, S, S, idx, coeffs, shapes, iters, 1.0, jt, out_dev.data_ptr(), precision=args.precision)
     e1.record(stream)
     eng.sync()
     ms = e0.elapsed_time(e1) / reps
     t0 = time.perf_counter()
-    eng.dream(img, idx, coeffs, shapes, iters, 1.0, jt)
+    eng.dream(img, idx, coeffs, shapes, iters, 1.0, jt, precision=args.precision)
     ms_e2e = (time.perf_counter() - t0) * 1e3
     fwd_gmac = sum(15.347 * (h * w) / (224.0 * 224.0) for h, w in shapes)          # conv stack to block5_conv3
     return {"metric": "deepdream_iters_per_sec", "value": 3 * iters / (ms / 1e3), "unit": "iterations/s",
-            "e2e_value": 3 * iters / (ms_e2e / 1e3), "ms_per_dream": ms, "dtype": "f32",
+            "e2e_value": 3 * iters / (ms_e2e / 1e3), "ms_per_dream": ms, "dtype": "bf16" if args.precision == "bf16" else "f32",
             "config": {"workload": "DeepDream %dx%d, octaves %s x %d iterations, loss on block3_conv3/block4_conv3/block5_conv3 "
                                    "(BASELINE configs[2]; derived spec, no reference implementation)" % (S, S, shapes, iters)},
             "tflops": 2 * 2 * fwd_gmac * iters / (ms / 1e3) / 1e3, "gpu_launches": (eng.launch_count - l0) // reps}

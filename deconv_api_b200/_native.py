@@ -59,11 +59,11 @@ SIGNATURES = {
                              _c.c_int, _c.c_void_p]),
     "dcv_dense_transpose": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_void_p, _c.c_int, _c.c_int, _c.c_int, _c.c_void_p]),
     "dcv_dream": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_int, _c.c_int, _c.c_int, _c.c_void_p, _c.c_void_p, _c.c_int,
-                             _c.c_void_p, _c.c_int, _c.c_int, _c.c_float, _c.c_void_p, _c.c_void_p, _c.c_void_p]),
+                             _c.c_void_p, _c.c_int, _c.c_int, _c.c_float, _c.c_void_p, _c.c_int, _c.c_void_p, _c.c_void_p]),
     "dcv_dream_dev": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_int, _c.c_int, _c.c_int, _c.c_void_p, _c.c_void_p, _c.c_int,
-                                 _c.c_void_p, _c.c_int, _c.c_int, _c.c_float, _c.c_void_p, _c.c_void_p]),
+                                 _c.c_void_p, _c.c_int, _c.c_int, _c.c_float, _c.c_void_p, _c.c_int, _c.c_void_p]),
     "dcv_dream_gradient": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_int, _c.c_int, _c.c_int, _c.c_void_p, _c.c_void_p,
-                                      _c.c_int, _c.c_void_p, _c.c_void_p]),
+                                      _c.c_int, _c.c_int, _c.c_void_p, _c.c_void_p]),
     "dcv_resize_bilinear": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_void_p]),
     "dcv_roll": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_void_p]),
 }

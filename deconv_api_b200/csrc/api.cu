@@ -97,6 +97,12 @@ extern "C" int dcv_create(int device, dcv_ctx** out) {
   ctx->num_sms = prop.multiProcessorCount;
   e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
   if (e != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete ctx; return DCV_ERR_CUDA; }
+  e = cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking);
+  for (int i = 0; i < 2 && e == cudaSuccess; ++i) {
+    e = cudaEventCreateWithFlags(&ctx->ev_ready[i], cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ctx->ev_copied[i], cudaEventDisableTiming);
+  }
+  if (e != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete ctx; return DCV_ERR_CUDA; }
   const char* ws = getenv("DCV_WORKSPACE_MB");
   ctx->workspace_budget = (ws ? (size_t)atoll(ws) : (size_t)12288) << 20;
   *out = ctx;
@@ -110,6 +116,7 @@ static void free_layer(Layer& l) {
   tc_free_layer(l);
   l.act.release();
   l.sw.release();
+  l.act_h.release();
 }
 
 extern "C" void dcv_destroy(dcv_ctx* ctx) {
@@ -123,6 +130,10 @@ extern "C" void dcv_destroy(dcv_ctx* ctx) {
   ctx->scratch.release();
   ctx->stage.release();
   for (auto& b : ctx->dream) b.release();
+  for (auto& b : ctx->out_stage) b.release();
+  cudaStreamSynchronize(ctx->copy_stream);
+  for (int i = 0; i < 2; ++i) { cudaEventDestroy(ctx->ev_ready[i]); cudaEventDestroy(ctx->ev_copied[i]); }
+  cudaStreamDestroy(ctx->copy_stream);
   cudaStreamDestroy(ctx->stream);
   delete ctx;
 }
@@ -515,7 +526,7 @@ static int project_chunk(dcv_ctx* ctx, int layer, int foff, int n, int vis_mode,
         launch_unpool_map(maps, (const uint8_t*)l.sw.p, B, h, w, C, feat, n, maps2, ctx->stream); ctx->launches++;
         std::swap(maps, maps2);
       } else if (rep_bf16) {
-        TRY(tc_unpool(ctx, hb[hcur], (const uint8_t*)l.sw.p, P, B, h, w, C, hb[hcur ^ 1]));
+        TRY(tc_unpool(ctx, hb[hcur], (const uint8_t*)l.sw.p, P, B, h, w, l.in_H, l.in_W, C, hb[hcur ^ 1]));
         hcur ^= 1;
       } else {
         // algorithmic bytes: 5*HWC/4 read + 4*HWC written, (H,W) = unpooled size
@@ -553,12 +564,12 @@ static int project_chunk(dcv_ctx* ctx, int layer, int foff, int n, int vis_mode,
             rep_bf16 = true;
           }
           if (more_convs) {
-            TRY(tc_conv(ctx, l, hb[hcur], P, h, w, hb[hcur ^ 1], nullptr));
+            TRY(tc_conv(ctx, l, hb[hcur], P, h, w, hb[hcur ^ 1], nullptr, -1));
             hcur ^= 1;
             cur ^= 1;                   // keeps the fp32 ping-pong bookkeeping below uniform
           } else {
             if (fdst) bufs[cur ^ 1] = fdst;
-            TRY(tc_conv(ctx, l, hb[hcur], P, h, w, nullptr, bufs[cur ^ 1]));
+            TRY(tc_conv(ctx, l, hb[hcur], P, h, w, nullptr, bufs[cur ^ 1], -1));
             rep_bf16 = false;
           }
         } else {
@@ -620,6 +631,10 @@ static int project_impl(dcv_ctx* ctx, int layer, const int* feat, int n, int vis
   size_t per_feat = 2 * (size_t)B * (max_elems * sizeof(float) + max_pad * sizeof(__nv_bfloat16));
   int chunk = (int)std::max<size_t>(1, ctx->workspace_budget / per_feat);
   chunk = std::min(chunk, n);
+  // Host output: split into >= 4 chunks so that the device-to-host copy of chunk i (second stream) overlaps
+  // the kernels of chunk i+1; each chunk still carries >= 32 feature maps, far more rows than the GPU needs.
+  const bool pipelined = !out_on_device && n >= 64;
+  if (pipelined) chunk = std::min(chunk, std::max(32, (n + 3) / 4));
   TRY(ctx->ws[0].ensure(ctx, (size_t)chunk * B * max_elems * sizeof(float)));
   TRY(ctx->ws[1].ensure(ctx, (size_t)chunk * B * max_elems * sizeof(float)));
   if (max_pad) {
@@ -633,14 +648,34 @@ static int project_impl(dcv_ctx* ctx, int layer, const int* feat, int n, int vis
   TRY(ctx->ws[3].ensure(ctx, (size_t)chunk * B * map_elems * sizeof(float)));
   TRY(ctx->feat_dev.ensure(ctx, (size_t)n * sizeof(int)));
   CU(ctx, cudaMemcpyAsync(ctx->feat_dev.p, feat, (size_t)n * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
-  for (int f0 = 0; f0 < n; f0 += chunk) {
+  if (pipelined) {
+    for (int i = 0; i < 2; ++i) TRY(ctx->out_stage[i].ensure(ctx, (size_t)chunk * out_elems * sizeof(float)));
+  }
+  int ci = 0;
+  for (int f0 = 0; f0 < n; f0 += chunk, ++ci) {
     const int nf = std::min(chunk, n - f0);
     float* res = nullptr;
     float* dst = out + (size_t)f0 * out_elems;
+    if (pipelined) {
+      const int s = ci & 1;
+      float* stage = (float*)ctx->out_stage[s].p;
+      if (ci >= 2) CU(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_copied[s], 0));    // stage buffer is free again
+      TRY(project_chunk(ctx, layer, f0, nf, vis_mode, precision, stage, &res));
+      if (res != stage)
+        CU(ctx, cudaMemcpyAsync(stage, res, (size_t)nf * out_elems * sizeof(float), cudaMemcpyDeviceToDevice, ctx->stream));
+      CU(ctx, cudaEventRecord(ctx->ev_ready[s], ctx->stream));
+      CU(ctx, cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_ready[s], 0));
+      CU(ctx, cudaMemcpyAsync(dst, stage, (size_t)nf * out_elems * sizeof(float), cudaMemcpyDeviceToHost, ctx->copy_stream));
+      CU(ctx, cudaEventRecord(ctx->ev_copied[s], ctx->copy_stream));
+      continue;
+    }
     TRY(project_chunk(ctx, layer, f0, nf, vis_mode, precision, out_on_device ? dst : nullptr, &res));
     if (res != dst)
       CU(ctx, cudaMemcpyAsync(dst, res, (size_t)nf * out_elems * sizeof(float),
                               out_on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, ctx->stream));
+  }
+  if (pipelined) {      // the context's stream completes only after the last copies have landed
+    for (int s = 0; s < 2 && s < ci; ++s) CU(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_copied[s], 0));
   }
   return 0;
 }

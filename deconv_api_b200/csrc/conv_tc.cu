@@ -82,23 +82,24 @@ __global__ void pad_convert_kernel(const float* __restrict__ x, int P, int h, in
   }
 }
 
-// Switch-driven unpool in the padded-flat bf16 layout (DPooling.down): in (P,(ph+1),(pw+1),c_pad) at the
-// pooled size, switches (Bsw, ph, pw, C) bytes, out (P,(2ph+1),(2pw+1),c_pad).  One thread = 8 channels of
-// one 2x2 output quad; quads with index ph / pw are the zero pad row / column of the output.
+// Switch-driven unpool in the padded-flat bf16 layout (DPooling.down / max-pool backward): in
+// (P,(ph+1),(pw+1),c_pad) at the pooled size, switches (Bsw, ph, pw, C) bytes, out (P,(h+1),(w+1),c_pad) with
+// h in {2ph, 2ph+1}, w likewise (odd sizes only occur in DeepDream: the trailing row/column gets zeros).
+// One thread = 8 channels of one 2x2 output quad; quads beyond the pooled grid are zero rows / columns.
 __global__ void __launch_bounds__(256)
 unpool_pad_kernel(const __nv_bfloat16* __restrict__ x, const uint8_t* __restrict__ sw, int P, int Bsw, int ph, int pw,
-                  int C, int c_pad, __nv_bfloat16* __restrict__ out) {
-  const int h = 2 * ph, w = 2 * pw;
+                  int h, int w, int C, int c_pad, __nv_bfloat16* __restrict__ out) {
   const int iwp = pw + 1, irp = (ph + 1) * iwp;
   const int owp = w + 1, orp = (h + 1) * owp;
+  const int qh = (h + 2) / 2, qw = (w + 2) / 2;          // quads covering y in [0,h], x in [0,w]
   const int cg = c_pad / 8;
-  const size_t total = (size_t)P * (ph + 1) * (pw + 1) * cg;
+  const size_t total = (size_t)P * qh * qw * cg;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
     const int g = (int)(i % cg);
     size_t t = i / cg;
-    const int ox = (int)(t % (pw + 1)); t /= (pw + 1);
-    const int oy = (int)(t % (ph + 1));
-    const int item = (int)(t / (ph + 1));
+    const int ox = (int)(t % qw); t /= qw;
+    const int oy = (int)(t % qh);
+    const int item = (int)(t / qh);
     uint4 val = make_uint4(0u, 0u, 0u, 0u);
     uint32_t sidx[8];
 #pragma unroll
@@ -130,6 +131,91 @@ unpool_pad_kernel(const __nv_bfloat16* __restrict__ x, const uint8_t* __restrict
       }
       *reinterpret_cast<uint4*>(out + ((size_t)item * orp + y * owp + xx) * c_pad + g * 8) = make_uint4(o[0], o[1], o[2], o[3]);
     }
+  }
+}
+
+// 2x2/2 max-pool + switch in the padded-flat bf16 layout (DeepDream forward in bf16): in (P,(h+1),(w+1),c_pad),
+// out (P,(ph+1),(pw+1),c_pad) with ph = h/2, pw = w/2 (floor), switches (P,ph,pw,C).  Same tie rule as the fp32
+// kernel (strict '>' in row-major order).  One thread = 8 channels of one pooled position (incl. the zero pads).
+__global__ void __launch_bounds__(256)
+pool_pad_kernel(const __nv_bfloat16* __restrict__ x, int P, int h, int w, int C, int c_pad,
+                __nv_bfloat16* __restrict__ out, uint8_t* __restrict__ sw) {
+  const int ph = h / 2, pw = w / 2;
+  const int iwp = w + 1, irp = (h + 1) * iwp;
+  const int owp = pw + 1, orp = (ph + 1) * owp;
+  const int cg = c_pad / 8;
+  const size_t total = (size_t)P * orp * cg;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int g = (int)(i % cg);
+    const size_t r = i / cg;
+    const int q = (int)(r % orp);
+    const int item = (int)(r / orp);
+    const int oy = q / owp, ox = q % owp;
+    uint4 res = make_uint4(0u, 0u, 0u, 0u);
+    if (oy < ph && ox < pw) {
+      const __nv_bfloat16* base = x + ((size_t)item * irp + (2 * oy) * iwp + 2 * ox) * c_pad + g * 8;
+      uint4 q4[4];
+      q4[0] = __ldg(reinterpret_cast<const uint4*>(base));
+      q4[1] = __ldg(reinterpret_cast<const uint4*>(base + c_pad));
+      q4[2] = __ldg(reinterpret_cast<const uint4*>(base + (size_t)iwp * c_pad));
+      q4[3] = __ldg(reinterpret_cast<const uint4*>(base + (size_t)iwp * c_pad + c_pad));
+      uint16_t best[8];
+      uint8_t idx[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        float bv = 0.f;
+#pragma unroll
+        for (int qd = 0; qd < 4; ++qd) {
+          const uint32_t word = (&q4[qd].x)[k >> 1];
+          const uint16_t bits = (k & 1) ? (uint16_t)(word >> 16) : (uint16_t)(word & 0xFFFFu);
+          const float v = __uint_as_float((uint32_t)bits << 16);
+          if (qd == 0 || v > bv) { bv = v; best[k] = bits; idx[k] = (uint8_t)qd; }
+        }
+      }
+      res = make_uint4((uint32_t)best[0] | ((uint32_t)best[1] << 16), (uint32_t)best[2] | ((uint32_t)best[3] << 16),
+                       (uint32_t)best[4] | ((uint32_t)best[5] << 16), (uint32_t)best[6] | ((uint32_t)best[7] << 16));
+      uint8_t* sp = sw + (((size_t)item * ph + oy) * pw + ox) * C + g * 8;
+#pragma unroll
+      for (int k = 0; k < 8; ++k)
+        if (g * 8 + k < C) sp[k] = idx[k];
+    }
+    *reinterpret_cast<uint4*>(out + r * c_pad + g * 8) = res;
+  }
+}
+
+// DeepDream backward, padded-flat bf16: g = mask(act > 0) * (g_above + scale * act); g_above may be absent.
+__global__ void dream_prep_pad_kernel(__nv_bfloat16* __restrict__ g, const __nv_bfloat16* __restrict__ act, size_t n2,
+                                      float scale, int has_g, int relu) {
+  __nv_bfloat162* g2 = reinterpret_cast<__nv_bfloat162*>(g);
+  const __nv_bfloat162* a2 = reinterpret_cast<const __nv_bfloat162*>(act);
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n2; i += (size_t)gridDim.x * blockDim.x) {
+    const float2 a = __bfloat1622float2(a2[i]);
+    float2 v = has_g ? __bfloat1622float2(g2[i]) : make_float2(0.f, 0.f);
+    v.x += scale * a.x; v.y += scale * a.y;
+    if (relu) { if (!(a.x > 0.f)) v.x = 0.f; if (!(a.y > 0.f)) v.y = 0.f; }
+    g2[i] = __floats2bfloat162_rn(v.x, v.y);
+  }
+}
+
+// fp64 block partials of sum(x^2) over a bf16 array (pads are zero, so padded-flat tensors sum correctly)
+__global__ void __launch_bounds__(256) sumsq_bf16_kernel(const __nv_bfloat16* __restrict__ x, size_t n2, double* __restrict__ partial) {
+  const __nv_bfloat162* x2 = reinterpret_cast<const __nv_bfloat162*>(x);
+  double q = 0.0;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n2; i += (size_t)gridDim.x * blockDim.x) {
+    const float2 a = __bfloat1622float2(x2[i]);
+    q += (double)a.x * a.x + (double)a.y * a.y;
+  }
+  __shared__ double rq[8];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
+  if ((threadIdx.x & 31) == 0) rq[threadIdx.x >> 5] = q;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = 0.0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) t += rq[k];
+    partial[2 * blockIdx.x] = 0.0;
+    partial[2 * blockIdx.x + 1] = t;
   }
 }
 
@@ -258,7 +344,8 @@ int tc_prepare_layer(dcv_ctx* ctx, Layer& l) {
 
 void tc_free_layer(Layer& l) {
   if (l.tc.wd_bf16) cudaFree(l.tc.wd_bf16);
-  l.tc.wd_bf16 = nullptr;
+  if (l.tc.wf_bf16) cudaFree(l.tc.wf_bf16);
+  l.tc.wd_bf16 = l.tc.wf_bf16 = nullptr;
 }
 
 int tc_pad_convert(dcv_ctx* ctx, const float* x, int P, int h, int w, int C, __nv_bfloat16* out) {
@@ -282,35 +369,96 @@ int tc_rank1(dcv_ctx* ctx, const float* maps, const Layer& l, const int* feat, i
   return 0;
 }
 
-int tc_unpool(dcv_ctx* ctx, const __nv_bfloat16* x, const uint8_t* sw, int P, int Bsw, int ph, int pw, int C,
-              __nv_bfloat16* out) {
+int tc_unpool(dcv_ctx* ctx, const __nv_bfloat16* x, const uint8_t* sw, int P, int Bsw, int ph, int pw, int h, int w,
+              int C, __nv_bfloat16* out) {
   const int c_pad = tc_cpad(C);
-  const size_t work = (size_t)P * (ph + 1) * (pw + 1) * (c_pad / 8);
+  const size_t work = (size_t)P * ((h + 2) / 2) * ((w + 2) / 2) * (c_pad / 8);
   // algorithmic bytes in this layout: 2 B/elem read at pooled size + 1 B switch, 2 B/elem written at full size
   ProfScope ps(ctx, DCV_K_UNPOOL, 0.0, (double)P * ph * pw * C * (2.0 + 1.0 + 8.0));
-  unpool_pad_kernel<<<grid_for(work, 256), 256, 0, ctx->stream>>>(x, sw, P, Bsw, ph, pw, C, c_pad, out);
+  unpool_pad_kernel<<<grid_for(work, 256), 256, 0, ctx->stream>>>(x, sw, P, Bsw, ph, pw, h, w, C, c_pad, out);
   ctx->launches++;
   return 0;
 }
 
+int tc_pool(dcv_ctx* ctx, const __nv_bfloat16* x, int P, int h, int w, int C, __nv_bfloat16* out, uint8_t* sw) {
+  const int c_pad = tc_cpad(C);
+  const size_t work = (size_t)P * (h / 2 + 1) * (w / 2 + 1) * (c_pad / 8);
+  ProfScope ps(ctx, DCV_K_POOL, 0.0, (double)P * h * w * C * (2.0 + 3.0 / 4.0));
+  pool_pad_kernel<<<grid_for(work, 256), 256, 0, ctx->stream>>>(x, P, h, w, C, c_pad, out, sw);
+  ctx->launches++;
+  return 0;
+}
+
+int tc_dream_prep(dcv_ctx* ctx, __nv_bfloat16* g, const __nv_bfloat16* act, size_t elems, float scale, int has_g, int relu) {
+  ProfScope ps(ctx, DCV_K_OTHER, 0.0, 6.0 * elems);
+  dream_prep_pad_kernel<<<grid_for(elems / 2, 256), 256, 0, ctx->stream>>>(g, act, elems / 2, scale, has_g, relu);
+  ctx->launches++;
+  return 0;
+}
+
+int tc_sumsq_partials(size_t elems) { return grid_for(elems / 2, 256, 4); }
+
+int tc_sumsq(dcv_ctx* ctx, const __nv_bfloat16* x, size_t elems, double* partial, int np) {
+  sumsq_bf16_kernel<<<np, 256, 0, ctx->stream>>>(x, elems / 2, partial);
+  ctx->launches++;
+  return 0;
+}
+
+int tc_prepare_forward(dcv_ctx* ctx, Layer& l) {
+  if (l.tc.wf_bf16) return 0;
+  l.tc.fk_pad = tc_cpad(l.cin);
+  l.tc.fn_pad = tc_cpad(l.cout);
+  const size_t n = (size_t)9 * l.tc.fn_pad * l.tc.fk_pad;
+  cudaError_t e = cudaMalloc(&l.tc.wf_bf16, n * sizeof(__nv_bfloat16));
+  if (e != cudaSuccess) return ctx->fail(DCV_ERR_NOMEM, "cudaMalloc(bf16 forward weights): %s", cudaGetErrorString(e));
+  // forward conv: K = cin, N = cout; l.w is [9][cin][cout] = [tap][k][n]
+  pack_weights_tc_kernel<<<grid_for(n, 256), 256, 0, ctx->stream>>>(l.w, l.cin, l.cout, l.tc.fk_pad, l.tc.fn_pad, l.tc.wf_bf16);
+  ctx->launches++;
+  return 0;
+}
+
+struct TcConvArgs {
+  const __nv_bfloat16* w;   // [9][n_pad][k_pad]
+  int k_pad, n_pad;
+  int k_real, n_real;
+  int relu;
+  const float* bias;
+};
+
+static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& a, const __nv_bfloat16* in, int P, int h, int w,
+                       __nv_bfloat16* out_bf16, float* out_f32);
+
 int tc_conv(dcv_ctx* ctx, const Layer& l, const __nv_bfloat16* in, int P, int h, int w, __nv_bfloat16* out_bf16,
-            float* out_f32) {
+            float* out_f32, int relu) {
   if (!l.tc.wd_bf16) return ctx->fail(DCV_ERR_STATE, "tensor-core weights were not prepared for this layer");
+  TcConvArgs a{l.tc.wd_bf16, l.tc.k_pad, l.tc.n_pad, l.cout, l.cin, relu < 0 ? l.relu : relu, nullptr};
+  return tc_conv_run(ctx, a, in, P, h, w, out_bf16, out_f32);
+}
+
+int tc_conv_fwd(dcv_ctx* ctx, const Layer& l, const __nv_bfloat16* in, int P, int h, int w, __nv_bfloat16* out_bf16) {
+  if (!l.tc.wf_bf16) return ctx->fail(DCV_ERR_STATE, "tensor-core forward weights were not prepared for this layer");
+  TcConvArgs a{l.tc.wf_bf16, l.tc.fk_pad, l.tc.fn_pad, l.cin, l.cout, l.relu, l.bias};
+  return tc_conv_run(ctx, a, in, P, h, w, out_bf16, nullptr);
+}
+
+static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* in, int P, int h, int w,
+                       __nv_bfloat16* out_bf16, float* out_f32) {
   const long long rows_ll = (long long)P * (h + 1) * (w + 1);
   if (rows_ll > 0x7FFFFF00LL) return ctx->fail(DCV_ERR_ARG, "tc_conv: %lld padded rows exceed the TMA coordinate range", rows_ll);
   TcParams p;
   p.rows = (int)rows_ll; p.h = h; p.w = w;
-  p.k_blocks = l.tc.k_pad / 64;
-  p.n_pad = l.tc.n_pad; p.n_real = l.cin;
+  p.k_blocks = l.k_pad / 64;
+  p.n_pad = l.n_pad; p.n_real = l.n_real;
   p.relu = l.relu;
+  p.bias = l.bias;
   p.out_bf16 = out_bf16; p.out_f32 = out_f32;
   p.m_tiles = (p.rows + BLOCK_M - 1) / BLOCK_M;
   int bn;
-  if (out_f32 && l.cin <= 16) bn = 16;
-  else if (l.tc.n_pad % 256 == 0) bn = 256;
-  else if (l.tc.n_pad % 128 == 0) bn = 128;
+  if (out_f32 && l.n_real <= 16) bn = 16;
+  else if (l.n_pad % 256 == 0) bn = 256;
+  else if (l.n_pad % 128 == 0) bn = 128;
   else bn = 64;
-  p.n_tiles = bn == 16 ? 1 : l.tc.n_pad / bn;
+  p.n_tiles = bn == 16 ? 1 : l.n_pad / bn;
   // operand staging mode (tc_kernel.cuh): bands for narrow N, resident weights when they fit beside >= 4 stages
   static const int force_mode = getenv("DCV_TC_MODE") ? atoi(getenv("DCV_TC_MODE")) : -1;
   // Measured on B200: the 128-byte swizzle is applied to the absolute shared-memory address, so an operand
@@ -325,12 +473,12 @@ int tc_conv(dcv_ctx* ctx, const Layer& l, const __nv_bfloat16* in, int P, int h,
   if (mode == MODE_BAND_RES && p.n_tiles != 1) mode = MODE_BAND;
   p.base_off = base_off;
   CUtensorMap ta, tb;
-  int r = make_tmap(ctx, &ta, in, (uint64_t)p.rows, (uint64_t)l.tc.k_pad, mode == MODE_TAP ? BLOCK_M : BAND_ROWS);
+  int r = make_tmap(ctx, &ta, in, (uint64_t)p.rows, (uint64_t)l.k_pad, mode == MODE_TAP ? BLOCK_M : BAND_ROWS);
   if (r) return r;
-  r = make_tmap(ctx, &tb, l.tc.wd_bf16, (uint64_t)9 * l.tc.n_pad, (uint64_t)l.tc.k_pad, (uint32_t)bn);
+  r = make_tmap(ctx, &tb, l.w, (uint64_t)9 * l.n_pad, (uint64_t)l.k_pad, (uint32_t)bn);
   if (r) return r;
-  ProfScope ps(ctx, DCV_K_CONV_TC, 2.0 * 9 * P * h * w * (double)l.cin * l.cout,
-               2.0 * P * h * w * ((double)l.cout + (out_f32 ? 2.0 * l.cin : (double)l.cin)));
+  ProfScope ps(ctx, DCV_K_CONV_TC, 2.0 * 9 * P * h * w * (double)l.k_real * l.n_real,
+               2.0 * P * h * w * ((double)l.k_real + (out_f32 ? 2.0 * l.n_real : (double)l.n_real)));
 #define TC_DISPATCH(BN)                                                    \
   switch (mode) {                                                          \
     case MODE_BAND: return launch_tc<BN, MODE_BAND>(ctx, ta, tb, p);       \
@@ -353,5 +501,5 @@ int tc_deconv(dcv_ctx* ctx, const Layer& l, const float* in, int P, int h, int w
   if (r) return r;
   r = tc_pad_convert(ctx, in, P, h, w, l.cout, (__nv_bfloat16*)ctx->ws[4].p);
   if (r) return r;
-  return tc_conv(ctx, l, (const __nv_bfloat16*)ctx->ws[4].p, P, h, w, nullptr, out);
+  return tc_conv(ctx, l, (const __nv_bfloat16*)ctx->ws[4].p, P, h, w, nullptr, out, -1);
 }

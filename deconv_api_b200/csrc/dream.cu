@@ -211,8 +211,103 @@ int dream_backward(dcv_ctx* ctx, const LossSpec& ls, float** grad, double* loss_
   return 0;
 }
 
+// ---- bf16 / tensor-core variant: the tape lives in the padded-flat bf16 layout of conv_tc.cu -------------
+// Forward: layer 0 (3 input channels, K = 27) stays on the FFMA kernel and is converted; every other conv is
+// tc_conv_fwd (tcgen05, bias + ReLU epilogue), pools are tc_pool.  x is a device pointer (B,H,W,C0) fp32.
+int dream_forward_bf16(dcv_ctx* ctx, const float* x, int B, int H, int W, int upto) {
+  if (ctx->net.empty() || ctx->net[0].kind != LK_CONV) return ctx->fail(DCV_ERR_STATE, "dream: network must start with a conv layer");
+  ctx->tape_upto = -1;                      // the fp32 projection tape is not valid after this
+  Layer& l0 = ctx->net[0];
+  ctx->in_B = B; ctx->in_H = H; ctx->in_W = W; ctx->in_C = l0.cin;
+  TRYD(l0.act.ensure(ctx, (size_t)B * H * W * l0.cout * sizeof(float)));
+  TRYD(l0.act_h.ensure(ctx, (size_t)B * tc_padded_elems(H, W, l0.cout) * sizeof(__nv_bfloat16)));
+  {
+    ConvEpilogue e; e.bias = l0.bias; e.relu = l0.relu;
+    ProfScope ps(ctx, DCV_K_CONV_FP32, 2.0 * 9 * B * H * W * (double)l0.cin * l0.cout, 4.0 * B * H * W * ((double)l0.cin + l0.cout));
+    launch_conv3x3_fp32(x, l0.w, B, H, W, l0.cin, l0.cout, e, (float*)l0.act.p, ctx->stream); ctx->launches++;
+  }
+  TRYD(tc_pad_convert(ctx, (const float*)l0.act.p, B, H, W, l0.cout, (__nv_bfloat16*)l0.act_h.p));
+  l0.B = B; l0.H = H; l0.W = W; l0.C = l0.cout;
+  int ch = H, cw = W, cc = l0.cout;
+  for (int j = 1; j <= upto; ++j) {
+    Layer& l = ctx->net[j];
+    const __nv_bfloat16* prev = (const __nv_bfloat16*)ctx->net[j - 1].act_h.p;
+    if (l.kind == LK_CONV) {
+      if (l.cin != cc) return ctx->fail(DCV_ERR_ARG, "layer %d: expects %d input channels, got %d", j, l.cin, cc);
+      TRYD(tc_prepare_forward(ctx, l));
+      TRYD(l.act_h.ensure(ctx, (size_t)B * tc_padded_elems(ch, cw, l.cout) * sizeof(__nv_bfloat16)));
+      TRYD(tc_conv_fwd(ctx, l, prev, B, ch, cw, (__nv_bfloat16*)l.act_h.p));
+      cc = l.cout;
+    } else if (l.kind == LK_POOL) {
+      const int oh = ch / 2, ow = cw / 2;
+      if (oh == 0 || ow == 0) return ctx->fail(DCV_ERR_ARG, "layer %d: input %dx%d too small to pool", j, ch, cw);
+      TRYD(l.act_h.ensure(ctx, (size_t)B * tc_padded_elems(oh, ow, cc) * sizeof(__nv_bfloat16)));
+      TRYD(l.sw.ensure(ctx, (size_t)B * oh * ow * cc));
+      TRYD(tc_pool(ctx, prev, B, ch, cw, cc, (__nv_bfloat16*)l.act_h.p, (uint8_t*)l.sw.p));
+      l.in_H = ch; l.in_W = cw;
+      ch = oh; cw = ow;
+    } else {
+      return ctx->fail(DCV_ERR_UNSUPPORTED, "dream: only conv/pool layers are supported");
+    }
+    l.B = B; l.H = ch; l.W = cw; l.C = cc;
+  }
+  return 0;
+}
+
+int dream_backward_bf16(dcv_ctx* ctx, const LossSpec& ls, float** grad, double* loss_out) {
+  const int B = ctx->in_B;
+  size_t max_pad = (size_t)B * tc_padded_elems(ctx->in_H, ctx->in_W, ctx->in_C);
+  for (int j = 0; j <= ls.deepest; ++j) max_pad = std::max(max_pad, (size_t)B * tc_padded_elems(ctx->net[j].H, ctx->net[j].W, ctx->net[j].C));
+  TRYD(ctx->dream[4].ensure(ctx, max_pad * sizeof(__nv_bfloat16)));
+  TRYD(ctx->dream[5].ensure(ctx, max_pad * sizeof(__nv_bfloat16)));
+  TRYD(ctx->ws[0].ensure(ctx, (size_t)B * ctx->in_H * ctx->in_W * ctx->in_C * sizeof(float)));
+  __nv_bfloat16* hb[2] = {(__nv_bfloat16*)ctx->dream[4].p, (__nv_bfloat16*)ctx->dream[5].p};
+  int cur = 0;
+  bool has_g = false;
+  double loss = 0.0;
+  for (int j = ls.deepest; j >= 0; --j) {
+    const Layer& l = ctx->net[j];
+    const size_t n = (size_t)l.B * l.H * l.W * l.C;                          // real elements
+    const size_t elems = (size_t)l.B * tc_padded_elems(l.H, l.W, l.C);      // padded bf16 elements
+    const float coeff = ls.coeff[j];
+    if (coeff != 0.f && loss_out) {
+      const int np = tc_sumsq_partials(elems);
+      TRYD(ctx->scratch.ensure(ctx, (size_t)np * 2 * sizeof(double)));
+      TRYD(tc_sumsq(ctx, (const __nv_bfloat16*)l.act_h.p, elems, (double*)ctx->scratch.p, np));
+      std::vector<double> h((size_t)np * 2);
+      CUD(ctx, cudaMemcpyAsync(h.data(), ctx->scratch.p, h.size() * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+      CUD(ctx, cudaStreamSynchronize(ctx->stream));
+      double q = 0.0;
+      for (int k = 0; k < np; ++k) q += h[2 * k + 1];
+      loss += (double)coeff * q / (double)n;
+    }
+    const float scale = coeff != 0.f ? 2.f * coeff / (float)n : 0.f;
+    if (!has_g && scale == 0.f) continue;
+    TRYD(tc_dream_prep(ctx, hb[cur], (const __nv_bfloat16*)l.act_h.p, elems, scale, has_g ? 1 : 0, l.kind == LK_CONV ? l.relu : 0));
+    if (l.kind == LK_CONV) {
+      if (j == 0) {
+        TRYD(tc_conv(ctx, l, hb[cur], l.B, l.H, l.W, nullptr, (float*)ctx->ws[0].p, 0));
+      } else {
+        TRYD(tc_conv(ctx, l, hb[cur], l.B, l.H, l.W, hb[cur ^ 1], nullptr, 0));
+        cur ^= 1;
+      }
+    } else {
+      TRYD(tc_unpool(ctx, hb[cur], (const uint8_t*)l.sw.p, l.B, l.B, l.H, l.W, l.in_H, l.in_W, l.C, hb[cur ^ 1]));
+      cur ^= 1;
+    }
+    has_g = true;
+  }
+  if (!has_g) return ctx->fail(DCV_ERR_ARG, "dream: all loss coefficients are zero");
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "dream backward (bf16): %s", cudaGetErrorString(e));
+  *grad = (float*)ctx->ws[0].p;
+  if (loss_out) *loss_out = loss;
+  return 0;
+}
+
 // one jittered ascent step on the device image img (B,H,W,C)
-int dream_iter(dcv_ctx* ctx, float* img, int B, int H, int W, int C, const LossSpec& ls, float step, int oy, int ox, double* loss_out) {
+int dream_iter(dcv_ctx* ctx, float* img, int B, int H, int W, int C, const LossSpec& ls, float step, int oy, int ox, double* loss_out,
+               int precision) {
   const size_t n = (size_t)B * H * W * C;
   TRYD(ctx->dream[3].ensure(ctx, n * sizeof(float)));
   float* x = (float*)ctx->dream[3].p;
@@ -220,9 +315,14 @@ int dream_iter(dcv_ctx* ctx, float* img, int B, int H, int W, int C, const LossS
     ProfScope ps(ctx, DCV_K_OTHER, 0.0, 8.0 * n);
     launch_roll(img, B, H, W, C, oy, ox, x, ctx->stream); ctx->launches++;
   }
-  TRYD(forward_impl(ctx, x, true, B, H, W, ls.deepest));
   float* g = nullptr;
-  TRYD(dream_backward(ctx, ls, &g, loss_out));
+  if (precision == DCV_BF16) {
+    TRYD(dream_forward_bf16(ctx, x, B, H, W, ls.deepest));
+    TRYD(dream_backward_bf16(ctx, ls, &g, loss_out));
+  } else {
+    TRYD(forward_impl(ctx, x, true, B, H, W, ls.deepest));
+    TRYD(dream_backward(ctx, ls, &g, loss_out));
+  }
   const size_t per = (size_t)H * W * C;
   const int np = deprocess_partials(per);
   TRYD(ctx->scratch.ensure(ctx, (size_t)np * 2 * sizeof(double)));
@@ -237,7 +337,9 @@ int dream_iter(dcv_ctx* ctx, float* img, int B, int H, int W, int C, const LossS
 }
 
 int dream_impl(dcv_ctx* ctx, const float* img_in, bool on_device, int B, int H, int W, const int* loss_layers, const float* coeffs,
-               int nl, const int* shapes, int n_oct, int iterations, float step, const int* jitter, float* out, double* losses) {
+               int nl, const int* shapes, int n_oct, int iterations, float step, const int* jitter, int precision, float* out,
+               double* losses) {
+  if (precision != DCV_FP32 && precision != DCV_BF16) return ctx->fail(DCV_ERR_ARG, "dcv_dream: unknown precision");
   if (!img_in || !out || B <= 0 || H <= 0 || W <= 0 || !shapes || n_oct <= 0 || iterations < 0 || (iterations > 0 && !jitter))
     return ctx->fail(DCV_ERR_ARG, "dcv_dream: bad arguments");
   if (ctx->net.empty() || ctx->net[0].kind != LK_CONV) return ctx->fail(DCV_ERR_STATE, "dcv_dream: network must start with a conv layer");
@@ -275,7 +377,7 @@ int dream_impl(dcv_ctx* ctx, const float* img_in, bool on_device, int B, int H, 
     }
     for (int it = 0; it < iterations; ++it) {
       const int* j = jitter + 2 * ((size_t)k * iterations + it);
-      TRYD(dream_iter(ctx, img, B, oh, ow, C, ls, step, j[0], j[1], losses ? losses + (size_t)k * iterations + it : nullptr));
+      TRYD(dream_iter(ctx, img, B, oh, ow, C, ls, step, j[0], j[1], losses ? losses + (size_t)k * iterations + it : nullptr, precision));
     }
     // re-inject the detail lost by having worked at a lower resolution
     launch_resize_bilinear(shrunk, B, sh, sw, C, oh, ow, tmp_a, ctx->stream);          // upscaled shrunk original
@@ -297,28 +399,40 @@ int dream_impl(dcv_ctx* ctx, const float* img_in, bool on_device, int B, int H, 
   CUD(ctx, cudaSetDevice((ctx)->device));
 
 extern "C" int dcv_dream(dcv_ctx* ctx, const float* img, int B, int H, int W, const int* loss_layers, const float* coeffs, int nl,
-                         const int* shapes, int n_oct, int iterations, float step, const int* jitter, float* out, double* losses) {
+                         const int* shapes, int n_oct, int iterations, float step, const int* jitter, int precision, float* out,
+                         double* losses) {
   ENTERD(ctx);
-  TRYD(dream_impl(ctx, img, false, B, H, W, loss_layers, coeffs, nl, shapes, n_oct, iterations, step, jitter, out, losses));
+  TRYD(dream_impl(ctx, img, false, B, H, W, loss_layers, coeffs, nl, shapes, n_oct, iterations, step, jitter, precision, out, losses));
   CUD(ctx, cudaStreamSynchronize(ctx->stream));
   return 0;
 }
 
 extern "C" int dcv_dream_dev(dcv_ctx* ctx, const float* img_dev, int B, int H, int W, const int* loss_layers, const float* coeffs,
-                             int nl, const int* shapes, int n_oct, int iterations, float step, const int* jitter, float* out_dev) {
+                             int nl, const int* shapes, int n_oct, int iterations, float step, const int* jitter, int precision,
+                             float* out_dev) {
   ENTERD(ctx);
-  return dream_impl(ctx, img_dev, true, B, H, W, loss_layers, coeffs, nl, shapes, n_oct, iterations, step, jitter, out_dev, nullptr);
+  return dream_impl(ctx, img_dev, true, B, H, W, loss_layers, coeffs, nl, shapes, n_oct, iterations, step, jitter, precision, out_dev, nullptr);
 }
 
 extern "C" int dcv_dream_gradient(dcv_ctx* ctx, const float* img, int B, int H, int W, const int* loss_layers, const float* coeffs,
-                                  int nl, float* grad_out, double* loss_out) {
+                                  int nl, int precision, float* grad_out, double* loss_out) {
   ENTERD(ctx);
   if (!img || !grad_out || B <= 0 || H <= 0 || W <= 0) return ctx->fail(DCV_ERR_ARG, "dcv_dream_gradient: bad arguments");
+  if (precision != DCV_FP32 && precision != DCV_BF16) return ctx->fail(DCV_ERR_ARG, "dcv_dream_gradient: unknown precision");
   LossSpec ls;
   TRYD(parse_losses(ctx, loss_layers, coeffs, nl, &ls));
-  TRYD(forward_impl(ctx, img, false, B, H, W, ls.deepest));
   float* g = nullptr;
-  TRYD(dream_backward(ctx, ls, &g, loss_out));
+  if (precision == DCV_BF16) {
+    if (ctx->net.empty() || ctx->net[0].kind != LK_CONV) return ctx->fail(DCV_ERR_STATE, "dream: network must start with a conv layer");
+    const size_t nimg = (size_t)B * H * W * ctx->net[0].cin;
+    TRYD(ctx->dream[3].ensure(ctx, nimg * sizeof(float)));
+    CUD(ctx, cudaMemcpyAsync(ctx->dream[3].p, img, nimg * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+    TRYD(dream_forward_bf16(ctx, (const float*)ctx->dream[3].p, B, H, W, ls.deepest));
+    TRYD(dream_backward_bf16(ctx, ls, &g, loss_out));
+  } else {
+    TRYD(forward_impl(ctx, img, false, B, H, W, ls.deepest));
+    TRYD(dream_backward(ctx, ls, &g, loss_out));
+  }
   CUD(ctx, cudaMemcpyAsync(grad_out, g, (size_t)B * H * W * ctx->in_C * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
   CUD(ctx, cudaStreamSynchronize(ctx->stream));
   return 0;

@@ -15,6 +15,8 @@ struct DevBuf {
 struct TcWeights {
   __nv_bfloat16* wd_bf16 = nullptr;   // backward weights packed [9][n_pad][k_pad] bf16 (K-major rows)
   int n_pad = 0, k_pad = 0;           // N = cin, K = cout of the forward layer, rounded up to 64
+  __nv_bfloat16* wf_bf16 = nullptr;   // forward weights [9][fn_pad][fk_pad] (N = cout, K = cin); built on first bf16 DeepDream
+  int fn_pad = 0, fk_pad = 0;
 };
 
 struct Layer {
@@ -30,6 +32,7 @@ struct Layer {
   int in_H = 0, in_W = 0, in_C = 0;    // pool / flatten: input shape
   DevBuf act;                          // output, fp32
   DevBuf sw;                           // pool: switches, 1 byte per pooled element
+  DevBuf act_h;                        // bf16 padded-flat copy of the output (bf16 DeepDream tape)
 };
 
 struct ProfRec {
@@ -53,6 +56,10 @@ struct dcv_ctx {
   DevBuf feat_dev;
   DevBuf scratch;      // reduction partials
   DevBuf stage;        // staging for host-buffer entry points
+  // host-output projections: chunks are copied back on a second stream while the next chunk computes
+  cudaStream_t copy_stream = nullptr;
+  cudaEvent_t ev_ready[2] = {nullptr, nullptr}, ev_copied[2] = {nullptr, nullptr};
+  DevBuf out_stage[2];
   DevBuf dream[6];     // DeepDream: image, original, shrunk original, rolled input / resize temp, 2 gradient buffers
   // optional per-kernel-class timing (dcv_profile): CUDA events around every launch of a class
   bool prof_on = false;
@@ -79,7 +86,18 @@ int tc_cpad(int c);
 size_t tc_padded_elems(int h, int w, int c);         // bf16 elements of one padded item
 int tc_pad_convert(dcv_ctx* ctx, const float* x, int P, int h, int w, int C, __nv_bfloat16* out);
 int tc_rank1(dcv_ctx* ctx, const float* maps, const Layer& l, const int* feat, int n, int B, int h, int w, __nv_bfloat16* out);
-int tc_unpool(dcv_ctx* ctx, const __nv_bfloat16* x, const uint8_t* sw, int P, int Bsw, int ph, int pw, int C, __nv_bfloat16* out);
-// exactly one of out_bf16 (padded-flat, pitch l.tc.n_pad) / out_f32 (compact (P,h,w,l.cin)) is non-null
-int tc_conv(dcv_ctx* ctx, const Layer& l, const __nv_bfloat16* in, int P, int h, int w, __nv_bfloat16* out_bf16, float* out_f32);
+// (ph,pw) pooled size, (h,w) unpooled size with h in {2ph, 2ph+1}
+int tc_unpool(dcv_ctx* ctx, const __nv_bfloat16* x, const uint8_t* sw, int P, int Bsw, int ph, int pw, int h, int w, int C,
+              __nv_bfloat16* out);
+int tc_pool(dcv_ctx* ctx, const __nv_bfloat16* x, int P, int h, int w, int C, __nv_bfloat16* out, uint8_t* sw);
+int tc_dream_prep(dcv_ctx* ctx, __nv_bfloat16* g, const __nv_bfloat16* act, size_t elems, float scale, int has_g, int relu);
+int tc_sumsq_partials(size_t elems);
+int tc_sumsq(dcv_ctx* ctx, const __nv_bfloat16* x, size_t elems, double* partial, int np);
+int tc_prepare_forward(dcv_ctx* ctx, Layer& l);
+// backward conv; exactly one of out_bf16 (padded-flat, pitch l.tc.n_pad) / out_f32 (compact (P,h,w,l.cin)) is
+// non-null; relu < 0: the layer's own activation (deconvnet rule), 0/1: explicit (DeepDream uses 0)
+int tc_conv(dcv_ctx* ctx, const Layer& l, const __nv_bfloat16* in, int P, int h, int w, __nv_bfloat16* out_bf16, float* out_f32,
+            int relu);
+// forward conv + bias + activation, bf16 padded-flat in and out
+int tc_conv_fwd(dcv_ctx* ctx, const Layer& l, const __nv_bfloat16* in, int P, int h, int w, __nv_bfloat16* out_bf16);
 int tc_deconv(dcv_ctx* ctx, const Layer& l, const float* in, int P, int h, int w, float* out);

@@ -36,6 +36,7 @@ struct TcParams {
   int relu;
   int stages;        // smem ring depth (host-computed from the budget)
   int base_off;      // 1: put (start_addr >> 7) & 7 into the descriptor's base-offset field
+  const float* bias;         // n_real entries added before the ReLU (forward conv), or null
   __nv_bfloat16* out_bf16;   // padded-flat (rows, n_pad), or null
   float* out_f32;            // compact (P,h,w,n_real), or null
 };
@@ -209,6 +210,11 @@ deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 #pragma unroll
             for (int i = 0; i < CHUNK / 2; ++i) {
               float a = __uint_as_float(v[2 * i]), b = __uint_as_float(v[2 * i + 1]);
+              if (p.bias) {
+                const int c = n0 + c0 + 2 * i;
+                if (c < p.n_real) a += __ldg(p.bias + c);
+                if (c + 1 < p.n_real) b += __ldg(p.bias + c + 1);
+              }
               if (p.relu) { a = fmaxf(a, 0.f); b = fmaxf(b, 0.f); }
               if (!is_pixel) { a = 0.f; b = 0.f; }
               __nv_bfloat162 h2 = __floats2bfloat162_rn(a, b);
@@ -227,6 +233,7 @@ deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             const int c = n0 + c0 + i;
             if (c < p.n_real) {
               float a = __uint_as_float(v[i]);
+              if (p.bias) a += __ldg(p.bias + c);
               if (p.relu) a = fmaxf(a, 0.f);
               dst[c] = a;
             }

@@ -27,7 +27,7 @@ def jitter_offsets(n, jitter=32, seed=0):
 
 
 def dream(model, image, layers=None, num_octave=3, octave_scale=1.4, iterations=20, step=1.0, jitter=32, seed=0,
-          device=None, return_losses=False):
+          device=None, return_losses=False, precision="fp32"):
     layers = dict(DEFAULT_LAYERS if layers is None else layers)
     m = _dd.adopt(model)
     names = [l.name for l in m.layers]
@@ -45,7 +45,7 @@ def dream(model, image, layers=None, num_octave=3, octave_scale=1.4, iterations=
     jt = jitter_offsets(num_octave * iterations, jitter, seed)
     idx = [eng.index[n] for n in layers]
     coeffs = [float(layers[n]) for n in layers]
-    res = eng.dream(img, idx, coeffs, shapes, iterations, step, jt, want_losses=return_losses)
+    res = eng.dream(img, idx, coeffs, shapes, iterations, step, jt, want_losses=return_losses, precision=precision)
     out, losses = res if return_losses else (res, None)
     out = out[0] if squeeze else out
     return (out, losses) if return_losses else out

@@ -296,7 +296,7 @@ class Engine(object):
         self._ck(self.lib.dcv_roll(self.ctx, _ptr(x), B, H, W, C, int(oy), int(ox), _ptr(out)))
         return out
 
-    def dream_gradient(self, img, loss_layers, coeffs):
+    def dream_gradient(self, img, loss_layers, coeffs, precision="fp32"):
         """-> (dloss/dimg (B,H,W,C) float32, loss float)"""
         img = _f32(img)
         B, H, W, _ = img.shape
@@ -304,10 +304,11 @@ class Engine(object):
         cf = np.ascontiguousarray(coeffs, np.float32)
         g = np.empty_like(img)
         loss = ctypes.c_double()
-        self._ck(self.lib.dcv_dream_gradient(self.ctx, _ptr(img), B, H, W, _ptr(ll), _ptr(cf), int(ll.size), _ptr(g), ctypes.byref(loss)))
+        self._ck(self.lib.dcv_dream_gradient(self.ctx, _ptr(img), B, H, W, _ptr(ll), _ptr(cf), int(ll.size), precision_id(precision),
+                                             _ptr(g), ctypes.byref(loss)))
         return g, loss.value
 
-    def dream(self, img, loss_layers, coeffs, shapes, iterations, step, jitter, want_losses=False):
+    def dream(self, img, loss_layers, coeffs, shapes, iterations, step, jitter, want_losses=False, precision="fp32"):
         img = _f32(img)
         B, H, W, _ = img.shape
         ll = np.ascontiguousarray(loss_layers, np.int32)
@@ -318,17 +319,18 @@ class Engine(object):
         out = np.empty_like(img)
         losses = np.zeros((sh.shape[0] * iterations,), np.float64) if want_losses else None
         self._ck(self.lib.dcv_dream(self.ctx, _ptr(img), B, H, W, _ptr(ll), _ptr(cf), int(ll.size), _ptr(sh), int(sh.shape[0]),
-                                    int(iterations), ctypes.c_float(step), _ptr(jt), _ptr(out),
+                                    int(iterations), ctypes.c_float(step), _ptr(jt), precision_id(precision), _ptr(out),
                                     _ptr(losses) if losses is not None else None))
         return (out, losses) if want_losses else out
 
-    def dream_dev(self, img_dev_ptr, B, H, W, loss_layers, coeffs, shapes, iterations, step, jitter, out_dev_ptr):
+    def dream_dev(self, img_dev_ptr, B, H, W, loss_layers, coeffs, shapes, iterations, step, jitter, out_dev_ptr, precision="fp32"):
         ll = np.ascontiguousarray(loss_layers, np.int32)
         cf = np.ascontiguousarray(coeffs, np.float32)
         sh = np.ascontiguousarray(shapes, np.int32).reshape(-1, 2)
         jt = np.ascontiguousarray(jitter, np.int32).reshape(-1, 2)
         self._ck(self.lib.dcv_dream_dev(self.ctx, ctypes.c_void_p(img_dev_ptr), B, H, W, _ptr(ll), _ptr(cf), int(ll.size), _ptr(sh),
-                                        int(sh.shape[0]), int(iterations), ctypes.c_float(step), _ptr(jt), ctypes.c_void_p(out_dev_ptr)))
+                                        int(sh.shape[0]), int(iterations), ctypes.c_float(step), _ptr(jt), precision_id(precision),
+                                        ctypes.c_void_p(out_dev_ptr)))
 
 
 def default_engine(device=None):

@@ -191,15 +191,19 @@ DCV_API int dcv_dense_transpose(dcv_ctx* ctx, const float* x, const float* w, in
  *   g = dloss/dx, img += step * unroll(g) / max(rms(g), 1e-7)  (rms per image).
  * shapes: n_oct (h,w) pairs, smallest first, the last one equal to (H,W); jitter: n_oct*iterations (oy,ox)
  * pairs drawn by the caller (so that an oracle can use the same stream); losses (optional, host):
- * n_oct*iterations loss values BEFORE each update (costs a device sync per iteration). ------------ */
+ * n_oct*iterations loss values BEFORE each update (costs a device sync per iteration).
+ * precision: DCV_FP32 = FFMA forward and backward; DCV_BF16 = forward AND backward on tcgen05 with a bf16
+ * tape in the padded-flat layout (layer 0, K = 27, stays FFMA); the image and its update stay fp32. ---- */
 DCV_API int dcv_dream(dcv_ctx* ctx, const float* img, int B, int H, int W, const int* loss_layers, const float* coeffs, int nl,
-                      const int* shapes, int n_oct, int iterations, float step, const int* jitter, float* out, double* losses);
+                      const int* shapes, int n_oct, int iterations, float step, const int* jitter, int precision, float* out,
+                      double* losses);
 /* Same on device buffers, asynchronous on the context's stream. */
 DCV_API int dcv_dream_dev(dcv_ctx* ctx, const float* img_dev, int B, int H, int W, const int* loss_layers, const float* coeffs,
-                          int nl, const int* shapes, int n_oct, int iterations, float step, const int* jitter, float* out_dev);
+                          int nl, const int* shapes, int n_oct, int iterations, float step, const int* jitter, int precision,
+                          float* out_dev);
 /* One forward + backward: grad_out (B,H,W,C0) = dloss/dimg (un-normalised), loss_out (optional) = loss. */
 DCV_API int dcv_dream_gradient(dcv_ctx* ctx, const float* img, int B, int H, int W, const int* loss_layers, const float* coeffs,
-                               int nl, float* grad_out, double* loss_out);
+                               int nl, int precision, float* grad_out, double* loss_out);
 /* Bilinear resize NHWC, half-pixel centres (align_corners = False), no antialiasing: the octave resize. */
 DCV_API int dcv_resize_bilinear(dcv_ctx* ctx, const float* x, int B, int H, int W, int C, int OH, int OW, float* out);
 /* numpy.roll over the two spatial axes by (oy, ox): the jitter. */
