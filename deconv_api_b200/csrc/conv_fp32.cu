@@ -15,11 +15,13 @@ namespace dcv {
 namespace {
 
 constexpr int TH = 8, TW = 16;        // output tile (pixels)
-constexpr int TC = 64;                // output channels per CTA
+// TC (output channels per CTA) is a template parameter: 64, or 32 for launches that would otherwise leave most
+// of the 148 SMs idle (the B=1 forward of the 28x28 / 14x14 layers).
 constexpr int KC = 8;                 // input channels per smem chunk
 constexpr int IN_W = TW + 2 + 2;      // 20: row pitch of the input patch (18 used)
 constexpr int IN_PLANE = (TH + 2) * IN_W;
 
+template <int TC>
 __global__ void __launch_bounds__(256, 2)
 conv3x3_fp32_kernel(const float* __restrict__ x, const float* __restrict__ w9, int H, int W, int cin, int cout,
                     int tiles_w, ConvEpilogue epi, float* __restrict__ out) {
@@ -27,19 +29,23 @@ conv3x3_fp32_kernel(const float* __restrict__ x, const float* __restrict__ w9, i
   __shared__ __align__(16) float w_s[9 * KC * TC];           // [tap][ci][co]
 
   const int tid = threadIdx.x;
-  const int tx = tid & 15;            // channel group: couts tx*4 .. tx*4+3
-  const int ty = tid >> 4;            // 0..15
-  const int row = ty >> 1;            // 0..7
-  const int col0 = (ty & 1) * 8;      // 0 or 8
+  constexpr int NTX = TC / 4;         // threads along the channel axis (4 couts each)
+  constexpr int NTY = 256 / NTX;      // pixel groups
+  constexpr int PXT = (TH * TW) / NTY;  // consecutive pixels of one row per thread: 8 (TC=64) or 4 (TC=32)
+  constexpr int GPR = TW / PXT;       // groups per tile row
+  const int tx = tid % NTX;           // channel group: couts tx*4 .. tx*4+3
+  const int ty = tid / NTX;
+  const int row = ty / GPR;           // 0..7
+  const int col0 = (ty % GPR) * PXT;
   const int tile_y = blockIdx.x / tiles_w, tile_x = blockIdx.x % tiles_w;
   const int y0 = tile_y * TH, x0 = tile_x * TW;
   const int co0 = blockIdx.y * TC;
   const size_t img_off = (size_t)blockIdx.z * H * W;
   const float* xin = x + img_off * cin;
 
-  float acc[8][4];
+  float acc[PXT][4];
 #pragma unroll
-  for (int p = 0; p < 8; ++p)
+  for (int p = 0; p < PXT; ++p)
 #pragma unroll
     for (int c = 0; c < 4; ++c) acc[p][c] = 0.f;
 
@@ -103,14 +109,14 @@ conv3x3_fp32_kernel(const float* __restrict__ x, const float* __restrict__ w9, i
 #pragma unroll
       for (int kh = 0; kh < 3; ++kh) {
         const float* ip = in_s + k * IN_PLANE + (row + kh) * IN_W + col0;
-        float iv[10];
+        float iv[PXT + 2];
 #pragma unroll
-        for (int j = 0; j < 10; ++j) iv[j] = ip[j];
+        for (int j = 0; j < PXT + 2; ++j) iv[j] = ip[j];
 #pragma unroll
         for (int kw = 0; kw < 3; ++kw) {
           const float4 wv = *reinterpret_cast<const float4*>(w_s + ((kh * 3 + kw) * KC + k) * TC + tx * 4);
 #pragma unroll
-          for (int p = 0; p < 8; ++p) {
+          for (int p = 0; p < PXT; ++p) {
             acc[p][0] = fmaf(iv[p + kw], wv.x, acc[p][0]);
             acc[p][1] = fmaf(iv[p + kw], wv.y, acc[p][1]);
             acc[p][2] = fmaf(iv[p + kw], wv.z, acc[p][2]);
@@ -134,7 +140,7 @@ conv3x3_fp32_kernel(const float* __restrict__ x, const float* __restrict__ w9, i
       if (co + c < cout) bv[c] = __ldg(epi.bias + co + c);
   }
 #pragma unroll
-  for (int p = 0; p < 8; ++p) {
+  for (int p = 0; p < PXT; ++p) {
     const int xx = x0 + col0 + p;
     if (xx >= W) break;
     const size_t o = (img_off + (size_t)y * W + xx) * cout + co;
@@ -174,12 +180,18 @@ void launch_conv3x3_fp32(const float* x, const float* w9, int B, int H, int W, i
   // gridDim.z is limited to 65535 items per launch
   for (int b0 = 0; b0 < B; b0 += 65535) {
     const int nb = (B - b0 < 65535) ? (B - b0) : 65535;
-    dim3 grid(tiles_w * tiles_h, (cout + TC - 1) / TC, nb);
     ConvEpilogue e = epi;
     const size_t ooff = (size_t)b0 * H * W * cout;
     if (e.sign_mask) e.sign_mask += ooff;
     if (e.add) e.add += ooff;
-    conv3x3_fp32_kernel<<<grid, 256, 0, s>>>(x + (size_t)b0 * H * W * cin, w9, H, W, cin, cout, tiles_w, e, out + ooff);
+    const size_t ctas64 = (size_t)tiles_w * tiles_h * ((cout + 63) / 64) * nb;
+    if (ctas64 < 2 * (size_t)kNumSMs && cout > 32) {
+      dim3 grid(tiles_w * tiles_h, (cout + 31) / 32, nb);
+      conv3x3_fp32_kernel<32><<<grid, 256, 0, s>>>(x + (size_t)b0 * H * W * cin, w9, H, W, cin, cout, tiles_w, e, out + ooff);
+    } else {
+      dim3 grid(tiles_w * tiles_h, (cout + 63) / 64, nb);
+      conv3x3_fp32_kernel<64><<<grid, 256, 0, s>>>(x + (size_t)b0 * H * W * cin, w9, H, W, cin, cout, tiles_w, e, out + ooff);
+    }
   }
 }
 

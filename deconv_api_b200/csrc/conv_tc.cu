@@ -21,6 +21,7 @@
 #include "internal.cuh"
 #include "tc_ptx.cuh"
 #include "tc_kernel.cuh"
+#include "tc_last.cuh"
 
 #include <algorithm>
 #include <cstdlib>
@@ -48,6 +49,20 @@ __global__ void pack_weights_tc_kernel(const float* __restrict__ wd, int kdim, i
     const int t = (int)(i / ((size_t)k_pad * n_pad));
     float v = 0.f;
     if (k < kdim && n < ndim) v = __ldg(wd + ((size_t)t * kdim + k) * ndim + n);
+    out[i] = __float2bfloat16_rn(v);
+  }
+}
+
+// All-tap weights of a narrow last layer for deconv_last_kernel: wd fp32 [9][K][N] -> bf16 [32][k_pad], row = tap*N + c.
+__global__ void pack_weights_alltap_kernel(const float* __restrict__ wd, int kdim, int ndim, int k_pad, __nv_bfloat16* __restrict__ out) {
+  const int total = 32 * k_pad;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int k = i % k_pad, row = i / k_pad;
+    float v = 0.f;
+    if (row < 9 * ndim && k < kdim) {
+      const int t = row / ndim, c = row % ndim;
+      v = __ldg(wd + ((size_t)t * kdim + k) * ndim + c);
+    }
     out[i] = __float2bfloat16_rn(v);
   }
 }
@@ -220,22 +235,20 @@ __global__ void __launch_bounds__(256) sumsq_bf16_kernel(const __nv_bfloat16* __
 }
 
 // Rank-1 first backward conv writing the padded-flat bf16 layout: out[r][ci] = relu(sum_tap map[p+tap] * wd[tap][f][ci]).
+// One block = RANK1_PX consecutive padded rows of one item.  A thread owns ONE channel pair for the whole block
+// (its 18 weights live in registers) and walks over the rows; the 9 map values of a row are shared-memory
+// broadcasts.  Stores are bf16x2, contiguous across the threads of a row: the kernel is bound by its HBM writes.
+constexpr int RANK1_PX = 128;
 __global__ void __launch_bounds__(256)
 rank1_pad_kernel(const float* __restrict__ maps, const float* __restrict__ wd, int cout, int cin, int c_pad,
                  const int* __restrict__ feat, int B, int h, int w, int relu, __nv_bfloat16* __restrict__ out) {
-  extern __shared__ float sm[];
-  float* wsl = sm;                 // [9][c_pad]
-  float* tap = sm + 9 * c_pad;     // [64][9]
+  __shared__ float tap[RANK1_PX * 9];
   const int item = blockIdx.y;
   const int f = feat[item / B];
   const int wp = w + 1, rp = (h + 1) * wp;
-  for (int i = threadIdx.x; i < 9 * c_pad; i += blockDim.x) {
-    const int t = i / c_pad, ci = i % c_pad;
-    wsl[i] = ci < cin ? __ldg(wd + ((size_t)t * cout + f) * cin + ci) : 0.f;
-  }
-  const int q0 = blockIdx.x * 64;
+  const int q0 = blockIdx.x * RANK1_PX;
   const float* m = maps + (size_t)item * h * w;
-  for (int i = threadIdx.x; i < 64 * 9; i += blockDim.x) {
+  for (int i = threadIdx.x; i < RANK1_PX * 9; i += blockDim.x) {
     const int pp = i / 9, t = i % 9;
     const int q = q0 + pp;
     float v = 0.f;
@@ -247,19 +260,30 @@ rank1_pad_kernel(const float* __restrict__ maps, const float* __restrict__ wd, i
     tap[i] = v;                     // all-zero taps at pad positions -> relu(0) = 0 is written there
   }
   __syncthreads();
-  const int cg = c_pad / 2;
-  for (int i = threadIdx.x; i < 64 * cg; i += blockDim.x) {
-    const int pp = i / cg, c2 = (i % cg) * 2;
-    if (q0 + pp >= rp) break;
-    float a = 0.f, b = 0.f;
+  const int cp = c_pad / 2;                         // channel pairs
+  const int lanes = blockDim.x / cp > 0 ? blockDim.x / cp : 1;     // row lanes when cp < blockDim.x
+  const int nrows = min(RANK1_PX, rp - q0);
+  for (int pair = threadIdx.x % cp; pair < cp; pair += (cp > (int)blockDim.x ? blockDim.x : cp)) {
+    const int c2 = pair * 2;
+    float wa[9], wb[9];
 #pragma unroll
     for (int t = 0; t < 9; ++t) {
-      const float tv = tap[pp * 9 + t];
-      a = fmaf(tv, wsl[t * c_pad + c2], a);
-      b = fmaf(tv, wsl[t * c_pad + c2 + 1], b);
+      const float* wr = wd + ((size_t)t * cout + f) * cin;
+      wa[t] = c2 < cin ? __ldg(wr + c2) : 0.f;
+      wb[t] = c2 + 1 < cin ? __ldg(wr + c2 + 1) : 0.f;
     }
-    if (relu) { a = fmaxf(a, 0.f); b = fmaxf(b, 0.f); }
-    *reinterpret_cast<__nv_bfloat162*>(out + ((size_t)item * rp + q0 + pp) * c_pad + c2) = __floats2bfloat162_rn(a, b);
+    for (int pp = (cp >= (int)blockDim.x ? 0 : threadIdx.x / cp); pp < nrows; pp += lanes) {
+      float a = 0.f, b = 0.f;
+#pragma unroll
+      for (int t = 0; t < 9; ++t) {
+        const float tv = tap[pp * 9 + t];
+        a = fmaf(tv, wa[t], a);
+        b = fmaf(tv, wb[t], b);
+      }
+      if (relu) { a = fmaxf(a, 0.f); b = fmaxf(b, 0.f); }
+      *reinterpret_cast<__nv_bfloat162*>(out + ((size_t)item * rp + q0 + pp) * c_pad + c2) = __floats2bfloat162_rn(a, b);
+    }
+    if (cp <= (int)blockDim.x) break;
   }
 }
 
@@ -300,6 +324,21 @@ int make_tmap(dcv_ctx* ctx, CUtensorMap* m, const void* base, uint64_t rows, uin
   return 0;
 }
 
+// Padded-flat activation viewed as (cols = C_pad, x = w+1, y = P*(h+1)); box = 64 channels x 16 x 16.
+int make_tmap_patch(dcv_ctx* ctx, CUtensorMap* m, const void* base, uint64_t c_pad, uint64_t wp, uint64_t ytot) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) return ctx->fail(DCV_ERR_CUDA, "cuTensorMapEncodeTiled is not available from the driver");
+  cuuint64_t dims[3] = {c_pad, wp, ytot};
+  cuuint64_t strides[2] = {c_pad * sizeof(__nv_bfloat16), wp * c_pad * sizeof(__nv_bfloat16)};
+  cuuint32_t box[3] = {64, (cuuint32_t)LAST_H, (cuuint32_t)LAST_H};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return ctx->fail(DCV_ERR_CUDA, "cuTensorMapEncodeTiled (3-D) failed with CUresult %d", (int)r);
+  return 0;
+}
+
 template <int BLOCK_N, int MODE>
 int launch_tc(dcv_ctx* ctx, const CUtensorMap& ta, const CUtensorMap& tb, TcParams p) {
   const int stage_bytes = tc_stage_bytes(MODE, BLOCK_N);
@@ -337,6 +376,12 @@ int tc_prepare_layer(dcv_ctx* ctx, Layer& l) {
   if (e != cudaSuccess) return ctx->fail(DCV_ERR_NOMEM, "cudaMalloc(bf16 weights): %s", cudaGetErrorString(e));
   pack_weights_tc_kernel<<<grid_for(n, 256), 256, 0, ctx->stream>>>(l.wd, l.cout, l.cin, l.tc.k_pad, l.tc.n_pad, l.tc.wd_bf16);
   ctx->launches++;
+  if (9 * l.cin <= LAST_N) {     // narrow last layer: all-tap weights for the GEMM + col2im kernel
+    e = cudaMalloc(&l.tc.wall_bf16, (size_t)LAST_N * l.tc.k_pad * sizeof(__nv_bfloat16));
+    if (e != cudaSuccess) return ctx->fail(DCV_ERR_NOMEM, "cudaMalloc(all-tap weights): %s", cudaGetErrorString(e));
+    pack_weights_alltap_kernel<<<grid_for((size_t)LAST_N * l.tc.k_pad, 256), 256, 0, ctx->stream>>>(l.wd, l.cout, l.cin, l.tc.k_pad, l.tc.wall_bf16);
+    ctx->launches++;
+  }
   e = cudaGetLastError();
   if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "pack_weights_tc_kernel: %s", cudaGetErrorString(e));
   return 0;
@@ -345,7 +390,8 @@ int tc_prepare_layer(dcv_ctx* ctx, Layer& l) {
 void tc_free_layer(Layer& l) {
   if (l.tc.wd_bf16) cudaFree(l.tc.wd_bf16);
   if (l.tc.wf_bf16) cudaFree(l.tc.wf_bf16);
-  l.tc.wd_bf16 = l.tc.wf_bf16 = nullptr;
+  if (l.tc.wall_bf16) cudaFree(l.tc.wall_bf16);
+  l.tc.wd_bf16 = l.tc.wf_bf16 = l.tc.wall_bf16 = nullptr;
 }
 
 int tc_pad_convert(dcv_ctx* ctx, const float* x, int P, int h, int w, int C, __nv_bfloat16* out) {
@@ -361,10 +407,9 @@ int tc_rank1(dcv_ctx* ctx, const float* maps, const Layer& l, const int* feat, i
              __nv_bfloat16* out) {
   const int c_pad = l.tc.n_pad;
   const int rp = (h + 1) * (w + 1);
-  dim3 grid((rp + 63) / 64, n * B);
-  const size_t smem = (size_t)(9 * c_pad + 64 * 9) * sizeof(float);
+  dim3 grid((rp + RANK1_PX - 1) / RANK1_PX, n * B);
   ProfScope ps(ctx, DCV_K_RANK1, 2.0 * 9 * n * B * h * w * (double)l.cin, (double)n * B * h * w * (4.0 + 2.0 * l.cin));
-  rank1_pad_kernel<<<grid, 256, smem, ctx->stream>>>(maps, l.wd, l.cout, l.cin, c_pad, feat, B, h, w, l.relu, out);
+  rank1_pad_kernel<<<grid, 256, 0, ctx->stream>>>(maps, l.wd, l.cout, l.cin, c_pad, feat, B, h, w, l.relu, out);
   ctx->launches++;
   return 0;
 }
@@ -431,6 +476,33 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& a, const __nv_bfloat16* i
 int tc_conv(dcv_ctx* ctx, const Layer& l, const __nv_bfloat16* in, int P, int h, int w, __nv_bfloat16* out_bf16,
             float* out_f32, int relu) {
   if (!l.tc.wd_bf16) return ctx->fail(DCV_ERR_STATE, "tensor-core weights were not prepared for this layer");
+  static const int use_last = getenv("DCV_TC_LAST") ? atoi(getenv("DCV_TC_LAST")) : 1;
+  if (out_f32 && l.tc.wall_bf16 && use_last) {
+    // narrow last layer: GEMM + col2im (tc_last.cuh)
+    LastParams p;
+    p.P = P; p.h = h; p.w = w; p.cout = l.cin; p.k_blocks = l.tc.k_pad / 64;
+    p.tiles_x = (w + LAST_T - 1) / LAST_T; p.tiles_y = (h + LAST_T - 1) / LAST_T;
+    const long long tt = (long long)P * p.tiles_x * p.tiles_y;
+    if (tt > 0x7FFFFFFFLL || (long long)P * (h + 1) > 0x7FFFFFFFLL) return ctx->fail(DCV_ERR_ARG, "tc_conv: too many tiles");
+    p.total_tiles = (int)tt;
+    p.relu = relu < 0 ? l.relu : relu;
+    p.out = out_f32;
+    CUtensorMap ta, tb;
+    int r = make_tmap_patch(ctx, &ta, in, (uint64_t)l.tc.k_pad, (uint64_t)(w + 1), (uint64_t)P * (h + 1));
+    if (r) return r;
+    r = make_tmap(ctx, &tb, l.tc.wall_bf16, LAST_N, (uint64_t)l.tc.k_pad, LAST_N);
+    if (r) return r;
+    const int smem = last_smem_bytes(p.k_blocks);
+    if (smem > 227 * 1024) return ctx->fail(DCV_ERR_UNSUPPORTED, "tc_conv: last-layer kernel needs %d bytes of shared memory", smem);
+    cudaError_t e = cudaFuncSetAttribute(deconv_last_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+    ProfScope ps(ctx, DCV_K_CONV_TC, 2.0 * 9 * P * h * w * (double)l.cin * l.cout, 2.0 * P * h * w * ((double)l.cout + 2.0 * l.cin));
+    deconv_last_kernel<<<std::min(p.total_tiles, ctx->num_sms), LAST_THREADS, smem, ctx->stream>>>(ta, tb, p);
+    ctx->launches++;
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "deconv_last_kernel launch: %s", cudaGetErrorString(e));
+    return 0;
+  }
   TcConvArgs a{l.tc.wd_bf16, l.tc.k_pad, l.tc.n_pad, l.cout, l.cin, relu < 0 ? l.relu : relu, nullptr};
   return tc_conv_run(ctx, a, in, P, h, w, out_bf16, out_f32);
 }

@@ -17,6 +17,7 @@ struct TcWeights {
   int n_pad = 0, k_pad = 0;           // N = cin, K = cout of the forward layer, rounded up to 64
   __nv_bfloat16* wf_bf16 = nullptr;   // forward weights [9][fn_pad][fk_pad] (N = cout, K = cin); built on first bf16 DeepDream
   int fn_pad = 0, fk_pad = 0;
+  __nv_bfloat16* wall_bf16 = nullptr; // narrow last layer (9*cin <= 32): all taps stacked along N, [32][k_pad]
 };
 
 struct Layer {
