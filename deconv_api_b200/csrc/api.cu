@@ -48,6 +48,7 @@ int DevBuf::ensure(dcv_ctx* ctx, size_t bytes) {
     return ctx->fail(DCV_ERR_NOMEM, "cudaMalloc(%zu bytes): %s", want, cudaGetErrorString(e));
   }
   cap = want;
+  ctx->alloc_epoch++;
   return 0;
 }
 
@@ -123,6 +124,7 @@ extern "C" void dcv_destroy(dcv_ctx* ctx) {
   if (!ctx) return;
   cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
+  dream_release_graphs(ctx);
   for (auto& l : ctx->net) free_layer(l);
   ctx->input.release();
   for (auto& b : ctx->ws) b.release();
@@ -130,6 +132,7 @@ extern "C" void dcv_destroy(dcv_ctx* ctx) {
   ctx->scratch.release();
   ctx->stage.release();
   for (auto& b : ctx->dream) b.release();
+  ctx->jit_dev.release();
   for (auto& b : ctx->out_stage) b.release();
   cudaStreamSynchronize(ctx->copy_stream);
   for (int i = 0; i < 2; ++i) { cudaEventDestroy(ctx->ev_ready[i]); cudaEventDestroy(ctx->ev_copied[i]); }

@@ -348,8 +348,14 @@ int launch_tc(dcv_ctx* ctx, const CUtensorMap& ta, const CUtensorMap& tb, TcPara
   if (stages < 2) return ctx->fail(DCV_ERR_UNSUPPORTED, "tc kernel: %d resident bytes leave no room for the pipeline", res_bytes);
   p.stages = stages;
   const int smem = res_bytes + stages * stage_bytes + 1024 /*align slack*/ + 256 /*barriers*/;
-  cudaError_t e = cudaFuncSetAttribute(deconv_tc_kernel<BLOCK_N, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-  if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "cudaFuncSetAttribute(smem %d): %s", smem, cudaGetErrorString(e));
+  // the attribute is per (kernel instantiation, device); remember the largest value already set
+  static int smem_set[64] = {};
+  cudaError_t e = cudaSuccess;
+  if (smem_set[ctx->device & 63] < smem) {
+    e = cudaFuncSetAttribute(deconv_tc_kernel<BLOCK_N, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "cudaFuncSetAttribute(smem %d): %s", smem, cudaGetErrorString(e));
+    smem_set[ctx->device & 63] = smem;
+  }
   const int tiles = p.m_tiles * p.n_tiles;
   const int grid = std::min(tiles, ctx->num_sms);
   deconv_tc_kernel<BLOCK_N, MODE><<<grid, NUM_THREADS, smem, ctx->stream>>>(ta, tb, p);
@@ -494,8 +500,13 @@ int tc_conv(dcv_ctx* ctx, const Layer& l, const __nv_bfloat16* in, int P, int h,
     if (r) return r;
     const int smem = last_smem_bytes(p.k_blocks);
     if (smem > 227 * 1024) return ctx->fail(DCV_ERR_UNSUPPORTED, "tc_conv: last-layer kernel needs %d bytes of shared memory", smem);
-    cudaError_t e = cudaFuncSetAttribute(deconv_last_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+    static int smem_set[64] = {};
+    cudaError_t e = cudaSuccess;
+    if (smem_set[ctx->device & 63] < smem) {
+      e = cudaFuncSetAttribute(deconv_last_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+      if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+      smem_set[ctx->device & 63] = smem;
+    }
     ProfScope ps(ctx, DCV_K_CONV_TC, 2.0 * 9 * P * h * w * (double)l.cin * l.cout, 2.0 * P * h * w * ((double)l.cout + 2.0 * l.cin));
     deconv_last_kernel<<<std::min(p.total_tiles, ctx->num_sms), LAST_THREADS, smem, ctx->stream>>>(ta, tb, p);
     ctx->launches++;
@@ -530,6 +541,9 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
   else if (l.n_pad % 256 == 0) bn = 256;
   else if (l.n_pad % 128 == 0) bn = 128;
   else bn = 64;
+  // few rows (single images at 14x14 .. 64x64): narrower N tiles give more CTAs and shorter MMAs, which matters
+  // more than operand re-use when the grid would not even fill the 148 SMs
+  while (bn > 64 && (long long)p.m_tiles * (l.n_pad / bn) < ctx->num_sms) bn >>= 1;
   p.n_tiles = bn == 16 ? 1 : l.n_pad / bn;
   // operand staging mode (tc_kernel.cuh): bands for narrow N, resident weights when they fit beside >= 4 stages
   static const int force_mode = getenv("DCV_TC_MODE") ? atoi(getenv("DCV_TC_MODE")) : -1;

@@ -12,6 +12,7 @@
 #include "internal.cuh"
 
 #include <algorithm>
+#include <cstdlib>
 #include <vector>
 
 using namespace dcv;
@@ -52,7 +53,11 @@ __global__ void resize_bilinear_kernel(const float* __restrict__ x, int B, int H
 }
 
 // out[b, y, x] = in[b, (y - oy) mod H, (x - ox) mod W]   (numpy.roll over the two spatial axes)
-__global__ void roll_kernel(const float* __restrict__ x, int B, int H, int W, int C, int oy, int ox, float* __restrict__ out) {
+// jit (optional): device array {counter, oy0, ox0, oy1, ox1, ...}; the offsets of iteration `counter` are used, so
+// that an iteration captured in a CUDA graph can be replayed with a different jitter every time
+__global__ void roll_kernel(const float* __restrict__ x, int B, int H, int W, int C, int oy, int ox, const int* __restrict__ jit,
+                            float* __restrict__ out) {
+  if (jit) { const int c = jit[0]; oy = jit[1 + 2 * c]; ox = jit[2 + 2 * c]; }
   const size_t total = (size_t)B * H * W * C;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
     const int c = (int)(i % C);
@@ -79,7 +84,8 @@ __global__ void dream_prep_kernel(float* __restrict__ g, const float* __restrict
 // img[b,y,x,c] += step / max(rms_b, 1e-7) * g[b,(y+oy) mod H,(x+ox) mod W,c]; rms from the fp64 block partials
 __global__ void __launch_bounds__(256)
 dream_update_kernel(float* __restrict__ img, const float* __restrict__ g, const double* __restrict__ partial, int np,
-                    int H, int W, int C, float step, int oy, int ox) {
+                    int H, int W, int C, float step, int oy, int ox, const int* __restrict__ jit) {
+  if (jit) { const int c = jit[0]; oy = jit[1 + 2 * c]; ox = jit[2 + 2 * c]; }
   __shared__ float s_scale;
   const size_t n = (size_t)H * W * C;
   if (threadIdx.x == 0) {
@@ -101,6 +107,8 @@ dream_update_kernel(float* __restrict__ img, const float* __restrict__ g, const 
   }
 }
 
+__global__ void bump_counter_kernel(int* counter) { *counter += 1; }
+
 __global__ void add_diff_kernel(float* __restrict__ img, const float* __restrict__ a, const float* __restrict__ b, size_t n) {
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
     img[i] += a[i] - b[i];
@@ -115,7 +123,7 @@ void launch_resize_bilinear(const float* x, int B, int H, int W, int C, int OH, 
 
 void launch_roll(const float* x, int B, int H, int W, int C, int oy, int ox, float* out, cudaStream_t s) {
   const size_t total = (size_t)B * H * W * C;
-  if (total) roll_kernel<<<grid_for(total, 256), 256, 0, s>>>(x, B, H, W, C, oy, ox, out);
+  if (total) roll_kernel<<<grid_for(total, 256), 256, 0, s>>>(x, B, H, W, C, oy, ox, nullptr, out);
 }
 
 // ---- host side ----------------------------------------------------------------------------------------
@@ -306,14 +314,14 @@ int dream_backward_bf16(dcv_ctx* ctx, const LossSpec& ls, float** grad, double* 
 }
 
 // one jittered ascent step on the device image img (B,H,W,C)
-int dream_iter(dcv_ctx* ctx, float* img, int B, int H, int W, int C, const LossSpec& ls, float step, int oy, int ox, double* loss_out,
-               int precision) {
+int dream_iter(dcv_ctx* ctx, float* img, int B, int H, int W, int C, const LossSpec& ls, float step, const int* jit_dev,
+               double* loss_out, int precision) {
   const size_t n = (size_t)B * H * W * C;
   TRYD(ctx->dream[3].ensure(ctx, n * sizeof(float)));
   float* x = (float*)ctx->dream[3].p;
   {
     ProfScope ps(ctx, DCV_K_OTHER, 0.0, 8.0 * n);
-    launch_roll(img, B, H, W, C, oy, ox, x, ctx->stream); ctx->launches++;
+    roll_kernel<<<grid_for(n, 256), 256, 0, ctx->stream>>>(img, B, H, W, C, 0, 0, jit_dev, x); ctx->launches++;
   }
   float* g = nullptr;
   if (precision == DCV_BF16) {
@@ -330,8 +338,77 @@ int dream_iter(dcv_ctx* ctx, float* img, int B, int H, int W, int C, const LossS
     ProfScope ps(ctx, DCV_K_OTHER, 0.0, 16.0 * per);
     launch_sum_stats(g + b * per, per, (double*)ctx->scratch.p, np, ctx->stream);
     dream_update_kernel<<<grid_for(per, 256, 8), 256, 0, ctx->stream>>>(img + b * per, g + b * per, (const double*)ctx->scratch.p, np,
-                                                                         H, W, C, step, oy, ox);
+                                                                         H, W, C, step, 0, 0, jit_dev);
     ctx->launches += 2;
+  }
+  bump_counter_kernel<<<1, 1, 0, ctx->stream>>>(const_cast<int*>(jit_dev)); ctx->launches++;
+  return 0;
+}
+
+// ---- CUDA graph of one iteration ------------------------------------------------------------------------
+// An iteration is ~80 small launches (plus two tensor-map encodes per conv); at 261x261 the host cannot issue them
+// as fast as the GPU retires them.  The first iteration of an octave runs eagerly (it sizes every buffer), the
+// second is captured, and the instantiated graph is replayed for the rest.  Graphs are cached per (shape, losses,
+// step, precision) and dropped when any workspace buffer has been re-allocated since (ctx->alloc_epoch).
+struct DreamGraphKey {
+  int B, H, W, precision, deepest;
+  float step;
+  std::vector<float> coeff;
+  bool operator==(const DreamGraphKey& o) const {
+    return B == o.B && H == o.H && W == o.W && precision == o.precision && deepest == o.deepest && step == o.step && coeff == o.coeff;
+  }
+};
+struct DreamGraph {
+  DreamGraphKey key;
+  cudaGraphExec_t exec = nullptr;
+  unsigned long long epoch = 0;
+  float* img = nullptr;
+};
+std::vector<DreamGraph>& graph_cache(dcv_ctx* ctx) {
+  if (!ctx->dream_graphs) ctx->dream_graphs = new std::vector<DreamGraph>();
+  return *static_cast<std::vector<DreamGraph>*>(ctx->dream_graphs);
+}
+
+int dream_iterations(dcv_ctx* ctx, float* img, int B, int H, int W, int C, const LossSpec& ls, float step, const int* jit_dev,
+                     double* losses, int precision, int iterations) {
+  static const int use_graph = getenv("DCV_DREAM_GRAPH") ? atoi(getenv("DCV_DREAM_GRAPH")) : 1;
+  const bool graphable = use_graph && !losses && !ctx->prof_on && iterations >= 3;
+  if (!graphable) {
+    for (int it = 0; it < iterations; ++it)
+      TRYD(dream_iter(ctx, img, B, H, W, C, ls, step, jit_dev, losses ? losses + it : nullptr, precision));
+    return 0;
+  }
+  DreamGraphKey key{B, H, W, precision, ls.deepest, step, ls.coeff};
+  auto& cache = graph_cache(ctx);
+  DreamGraph* hit = nullptr;
+  for (auto& g : cache)
+    if (g.key == key && g.img == img) { hit = &g; break; }
+  int done = 0;
+  if (hit && hit->epoch != ctx->alloc_epoch) {            // a buffer moved: the captured pointers are stale
+    cudaGraphExecDestroy(hit->exec);
+    hit->exec = nullptr;
+  }
+  if (!hit || !hit->exec) {
+    TRYD(dream_iter(ctx, img, B, H, W, C, ls, step, jit_dev, nullptr, precision));      // eager: sizes all buffers
+    done = 1;
+    const unsigned long long epoch = ctx->alloc_epoch;
+    CUD(ctx, cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeThreadLocal));
+    int r = dream_iter(ctx, img, B, H, W, C, ls, step, jit_dev, nullptr, precision);
+    cudaGraph_t graph = nullptr;
+    cudaError_t e = cudaStreamEndCapture(ctx->stream, &graph);
+    if (r) { if (graph) cudaGraphDestroy(graph); return r; }
+    if (e != cudaSuccess || !graph) return ctx->fail(DCV_ERR_CUDA, "dream: stream capture failed: %s", cudaGetErrorString(e));
+    if (ctx->alloc_epoch != epoch) { cudaGraphDestroy(graph); return ctx->fail(DCV_ERR_STATE, "dream: a buffer was re-allocated during capture"); }
+    cudaGraphExec_t exec = nullptr;
+    e = cudaGraphInstantiate(&exec, graph, 0);
+    cudaGraphDestroy(graph);
+    if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "dream: cudaGraphInstantiate: %s", cudaGetErrorString(e));
+    if (!hit) { cache.push_back(DreamGraph()); hit = &cache.back(); }
+    hit->key = key; hit->exec = exec; hit->epoch = epoch; hit->img = img;
+  }
+  for (int it = done; it < iterations; ++it) {
+    CUD(ctx, cudaGraphLaunch(hit->exec, ctx->stream));
+    ctx->launches += ctx->net.size() * 4;       // approximate: launches inside a replayed graph are not counted one by one
   }
   return 0;
 }
@@ -361,6 +438,11 @@ int dream_impl(dcv_ctx* ctx, const float* img_in, bool on_device, int B, int H, 
   float* shrunk = (float*)ctx->dream[2].p;
   float* tmp_a = (float*)ctx->stage.p;
   float* tmp_b = tmp_a + maxn;
+  // jitter offsets live on the device behind an iteration counter (see roll_kernel)
+  const size_t njit = (size_t)n_oct * iterations;
+  TRYD(ctx->jit_dev.ensure(ctx, (1 + 2 * njit + 2) * sizeof(int)));
+  CUD(ctx, cudaMemsetAsync(ctx->jit_dev.p, 0, sizeof(int), ctx->stream));
+  if (njit) CUD(ctx, cudaMemcpyAsync((int*)ctx->jit_dev.p + 1, jitter, 2 * njit * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
   CUD(ctx, cudaMemcpyAsync(orig, img_in, full * sizeof(float), on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, ctx->stream));
   CUD(ctx, cudaMemcpyAsync(img, orig, full * sizeof(float), cudaMemcpyDeviceToDevice, ctx->stream));
   int ch = H, cw = W;                       // current size of img
@@ -375,10 +457,8 @@ int dream_impl(dcv_ctx* ctx, const float* img_in, bool on_device, int B, int H, 
       CUD(ctx, cudaMemcpyAsync(img, tmp_a, n * sizeof(float), cudaMemcpyDeviceToDevice, ctx->stream));
       ch = oh; cw = ow;
     }
-    for (int it = 0; it < iterations; ++it) {
-      const int* j = jitter + 2 * ((size_t)k * iterations + it);
-      TRYD(dream_iter(ctx, img, B, oh, ow, C, ls, step, j[0], j[1], losses ? losses + (size_t)k * iterations + it : nullptr, precision));
-    }
+    TRYD(dream_iterations(ctx, img, B, oh, ow, C, ls, step, (const int*)ctx->jit_dev.p, losses ? losses + (size_t)k * iterations : nullptr,
+                          precision, iterations));
     // re-inject the detail lost by having worked at a lower resolution
     launch_resize_bilinear(shrunk, B, sh, sw, C, oh, ow, tmp_a, ctx->stream);          // upscaled shrunk original
     launch_resize_bilinear(orig, B, H, W, C, oh, ow, tmp_b, ctx->stream);              // original at this size
@@ -393,6 +473,15 @@ int dream_impl(dcv_ctx* ctx, const float* img_in, bool on_device, int B, int H, 
 }
 
 }  // namespace
+
+void dream_release_graphs(dcv_ctx* ctx) {
+  if (!ctx->dream_graphs) return;
+  auto* v = static_cast<std::vector<DreamGraph>*>(ctx->dream_graphs);
+  for (auto& g : *v)
+    if (g.exec) cudaGraphExecDestroy(g.exec);
+  delete v;
+  ctx->dream_graphs = nullptr;
+}
 
 #define ENTERD(ctx)                                                       \
   if (!(ctx)) return DCV_ERR_ARG;                                          \

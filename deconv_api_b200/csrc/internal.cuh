@@ -61,7 +61,10 @@ struct dcv_ctx {
   cudaStream_t copy_stream = nullptr;
   cudaEvent_t ev_ready[2] = {nullptr, nullptr}, ev_copied[2] = {nullptr, nullptr};
   DevBuf out_stage[2];
-  DevBuf dream[6];     // DeepDream: image, original, shrunk original, rolled input / resize temp, 2 gradient buffers
+  DevBuf dream[6];
+  void* dream_graphs = nullptr;   // cached CUDA graphs of DeepDream iterations (dream.cu)
+  DevBuf jit_dev;      // DeepDream: {iteration counter, (oy, ox) per iteration}
+  unsigned long long alloc_epoch = 0;   // bumped whenever a DevBuf is (re)allocated: invalidates captured graphs     // DeepDream: image, original, shrunk original, rolled input / resize temp, 2 gradient buffers
   // optional per-kernel-class timing (dcv_profile): CUDA events around every launch of a class
   bool prof_on = false;
   std::vector<ProfRec> prof;
@@ -79,6 +82,9 @@ struct ProfScope {
 
 // api.cu
 int forward_impl(dcv_ctx* ctx, const float* img, bool on_device, int B, int H, int W, int upto);
+
+// dream.cu
+void dream_release_graphs(dcv_ctx* ctx);
 
 // conv_tc.cu — bf16 tensor-core chain in the padded-flat layout (see the header comment there)
 int tc_prepare_layer(dcv_ctx* ctx, Layer& l);
