@@ -22,6 +22,7 @@
 #include "tc_ptx.cuh"
 #include "tc_kernel.cuh"
 #include "tc_last.cuh"
+#include "tc_kernel2.cuh"
 
 #include <algorithm>
 #include <cstdlib>
@@ -570,6 +571,28 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
     case MODE_BAND: return launch_tc<BN, MODE_BAND>(ctx, ta, tb, p);       \
     case MODE_BAND_RES: return launch_tc<BN, MODE_BAND_RES>(ctx, ta, tb, p); \
     default: return launch_tc<BN, MODE_TAP>(ctx, ta, tb, p);               \
+  }
+  static const int use_pair = getenv("DCV_TC_2CTA") ? atoi(getenv("DCV_TC_2CTA")) : 1;
+  if (bn == 256 && use_pair && ctx->num_sms >= 2) {
+    // CTA-pair kernel (tc_kernel2.cuh): tiles of 256 rows x 256 channels, one cluster of 2 per TPC
+    TcParams q = p;
+    q.m_tiles = (p.rows + 255) / 256;
+    CUtensorMap tb2;
+    r = make_tmap(ctx, &tb2, l.w, (uint64_t)9 * l.n_pad, (uint64_t)l.k_pad, 128);
+    if (r) return r;
+    static int attr_done[64] = {};
+    if (!attr_done[ctx->device & 63]) {
+      cudaError_t e = cudaFuncSetAttribute(deconv_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC2_SMEM_BYTES);
+      if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "cudaFuncSetAttribute(pair kernel): %s", cudaGetErrorString(e));
+      attr_done[ctx->device & 63] = 1;
+    }
+    const int tiles = q.m_tiles * q.n_tiles;
+    const int pairs = std::min(tiles, ctx->num_sms / 2);
+    deconv_tc2_kernel<<<2 * pairs, NUM_THREADS, TC2_SMEM_BYTES, ctx->stream>>>(ta, tb2, q);
+    ctx->launches++;
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "deconv_tc2_kernel launch: %s", cudaGetErrorString(e));
+    return 0;
   }
   switch (bn) {
     case 16: TC_DISPATCH(16)
