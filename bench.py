@@ -43,7 +43,7 @@ def parse():
     ap.add_argument("--precision", default=os.environ.get("DCV_BENCH_PRECISION", "bf16"), choices=["bf16", "fp32"])
     ap.add_argument("--layer", default=LAYER)
     ap.add_argument("--nfeat", type=int, default=NFEAT)
-    ap.add_argument("--cpu-sample", type=int, default=48, help="projections in the cpu_baseline sample")
+    ap.add_argument("--cpu-sample", type=int, default=512, help="projections in the cpu_baseline sample (~10 s of CPU work)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-dream", action="store_true", help="skip the secondary DeepDream measurement")
     ap.add_argument("--dream-size", type=int, default=512)
@@ -136,7 +136,7 @@ def cpu_projection_rate(layer, nproj, seed=0, batch=16, repeats=1):
 def run_reference(args, rank, world):
     if rank != 0:
         return
-    sample = max(8, min(args.cpu_sample, args.nfeat))
+    sample = max(8, min(args.cpu_sample, args.nfeat, 128))     # ~2-3 s of CPU work per step
     for _ in range(min(args.warmup, 1)):
         cpu_projection_rate(args.layer, 8)
     rates, secs = [], []
@@ -269,6 +269,14 @@ def run_ours(args, rank, world, local_rank):
                 "frac": achieved / pk["hbm"], "traffic": None, "peak_source": pk["source"],
                 "algorithmic_bytes_per_launch": d["bytes"] / max(d["launches"], 1),
                 "avg_launch_ms": d["ms"] / max(d["launches"], 1), "launches": d["launches"], "share_of_step": share}
+    # DRAM traffic per launch of the dominant class from the committed ncu capture of this same step
+    tpath = os.path.join(ROOT, "profiles", "r1_traffic.json")
+    if os.path.exists(tpath) and args.nfeat == NFEAT and args.layer == LAYER and prec == "bf16":
+        t = json.load(open(tpath)).get(dom)
+        if t:
+            roof["traffic"] = t["dram_bytes_per_launch"]
+            roof["traffic_source"] = t["source"]
+            roof["algorithmic_bytes_per_launch"] = d["bytes"] / max(d["launches"], 1)
     classes = {k: {"ms_per_step": v["ms"] / args.steps, "launches_per_step": v["launches"] / args.steps,
                    "tflops": (v["flops"] / (v["ms"] / 1e3) / 1e12) if v["ms"] > 0 and v["flops"] else None,
                    "gbs": (v["bytes"] / (v["ms"] / 1e3) / 1e9) if v["ms"] > 0 and v["bytes"] else None}
