@@ -573,25 +573,57 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
     default: return launch_tc<BN, MODE_TAP>(ctx, ta, tb, p);               \
   }
   static const int use_pair = getenv("DCV_TC_2CTA") ? atoi(getenv("DCV_TC_2CTA")) : 1;
-  if (bn == 256 && use_pair && ctx->num_sms >= 2) {
-    // CTA-pair kernel (tc_kernel2.cuh): tiles of 256 rows x 256 channels, one cluster of 2 per TPC
+  const int m_tiles2 = (p.rows + 255) / 256;
+  // Measured (profiles/r1_summary.md): the pair form gains 9-13 % at N tile 256 and nothing at N <= 128, where the
+  // A-operand read of each SM (unchanged by pairing) sets the pace; DCV_TC_2CTA=2 forces it everywhere for tests.
+  if (bn >= 64 && (use_pair == 2 || (use_pair == 1 && bn == 256)) && (long long)m_tiles2 * p.n_tiles >= ctx->num_sms / 2) {
+    // CTA-pair kernels (tc_kernel2.cuh): tiles of 256 rows x bn channels, each CTA stages half of the B tile
     TcParams q = p;
-    q.m_tiles = (p.rows + 255) / 256;
+    q.m_tiles = m_tiles2;
+    int mode2 = mode;
+    if (mode2 == MODE_BAND && q.n_tiles == 1 && tc2_resident_bytes(MODE_BAND_RES, bn, q.k_blocks) + 4 * A_BAND_BYTES <= SMEM_BUDGET)
+      mode2 = MODE_BAND_RES;       // half the weights per CTA: fits more layers than the single-CTA form
+    const int stage_bytes = tc2_stage_bytes(mode2, bn), res_bytes = tc2_resident_bytes(mode2, bn, q.k_blocks);
+    int stages = (SMEM_BUDGET - res_bytes) / stage_bytes;
+    if (stages > 8) stages = 8;
+    q.stages = stages;
+    const int smem = res_bytes + stages * stage_bytes + 1024 + 256;
     CUtensorMap tb2;
-    r = make_tmap(ctx, &tb2, l.w, (uint64_t)9 * l.n_pad, (uint64_t)l.k_pad, 128);
+    r = make_tmap(ctx, &tb2, l.w, (uint64_t)9 * l.n_pad, (uint64_t)l.k_pad, (uint32_t)(bn / 2));
     if (r) return r;
-    static int attr_done[64] = {};
-    if (!attr_done[ctx->device & 63]) {
-      cudaError_t e = cudaFuncSetAttribute(deconv_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC2_SMEM_BYTES);
-      if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "cudaFuncSetAttribute(pair kernel): %s", cudaGetErrorString(e));
-      attr_done[ctx->device & 63] = 1;
+    if (mode2 != mode) {           // A map box differs between tap (128 rows) and band (136 rows) modes
+      r = make_tmap(ctx, &ta, in, (uint64_t)p.rows, (uint64_t)l.k_pad, mode2 == MODE_TAP ? BLOCK_M : BAND_ROWS);
+      if (r) return r;
     }
     const int tiles = q.m_tiles * q.n_tiles;
     const int pairs = std::min(tiles, ctx->num_sms / 2);
-    deconv_tc2_kernel<<<2 * pairs, NUM_THREADS, TC2_SMEM_BYTES, ctx->stream>>>(ta, tb2, q);
+    cudaError_t e = cudaSuccess;
+#define TC2_LAUNCH(BN, MD)                                                                                           \
+    {                                                                                                                  \
+      static int smem_set[64] = {};                                                                                    \
+      if (smem_set[ctx->device & 63] < smem) {                                                                         \
+        e = cudaFuncSetAttribute(deconv_tc2_kernel<BN, MD>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);        \
+        if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "cudaFuncSetAttribute(pair kernel): %s", cudaGetErrorString(e)); \
+        smem_set[ctx->device & 63] = smem;                                                                             \
+      }                                                                                                                \
+      deconv_tc2_kernel<BN, MD><<<2 * pairs, NUM_THREADS, smem, ctx->stream>>>(ta, tb2, q);                            \
+    }
+#define TC2_MODES(BN)                                                     \
+    switch (mode2) {                                                      \
+      case MODE_BAND: TC2_LAUNCH(BN, MODE_BAND) break;                    \
+      case MODE_BAND_RES: TC2_LAUNCH(BN, MODE_BAND_RES) break;            \
+      default: TC2_LAUNCH(BN, MODE_TAP) break;                            \
+    }
+    switch (bn) {
+      case 64: TC2_MODES(64) break;
+      case 128: TC2_MODES(128) break;
+      default: TC2_LAUNCH(256, MODE_TAP) break;
+    }
+#undef TC2_MODES
+#undef TC2_LAUNCH
     ctx->launches++;
-    cudaError_t e = cudaGetLastError();
-    if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "deconv_tc2_kernel launch: %s", cudaGetErrorString(e));
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "deconv_tc2_kernel<%d,%d> launch: %s", bn, mode2, cudaGetErrorString(e));
     return 0;
   }
   switch (bn) {

@@ -17,9 +17,16 @@
 namespace dcv {
 namespace tc {
 
-constexpr int TC2_STAGE_BYTES = A_TILE_BYTES + 128 * 128;      // A (128 rows) + half of B (128 rows)
-constexpr int TC2_STAGES = 6;
-constexpr int TC2_SMEM_BYTES = TC2_STAGES * TC2_STAGE_BYTES + 1024 + 256;
+// per-CTA bytes of one pipeline stage / of the resident weights: as in tc_kernel.cuh, but each CTA of the pair
+// holds only HALF of the B tile (block_n / 2 weight rows)
+__host__ __device__ inline int tc2_stage_bytes(int mode, int block_n) {
+  if (mode == MODE_TAP) return A_TILE_BYTES + (block_n / 2) * 128;
+  if (mode == MODE_BAND) return A_BAND_BYTES + 3 * (block_n / 2) * 128;
+  return A_BAND_BYTES;
+}
+__host__ __device__ inline int tc2_resident_bytes(int mode, int block_n, int k_blocks) {
+  return mode == MODE_BAND_RES ? 9 * k_blocks * (block_n / 2) * 128 : 0;
+}
 
 __device__ __forceinline__ uint32_t cluster_ctarank() {
   uint32_t r;
@@ -75,17 +82,25 @@ __device__ __forceinline__ void umma_commit_pair(uint64_t* bar) {
                : "memory");
 }
 
+template <int BLOCK_N, int MODE>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
 deconv_tc2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, TcParams p) {
-  constexpr int BLOCK_N = 256;
-  constexpr int TMEM_COLS = 512;
+  constexpr int HALF_N = BLOCK_N / 2;
+  constexpr int B_HALF_BYTES = HALF_N * 128;
+  constexpr int TMEM_COLS = (2 * BLOCK_N) < 32 ? 32 : (2 * BLOCK_N);
+  constexpr int MAX_STAGES = 8;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + TC2_STAGES * TC2_STAGE_BYTES);
-  uint64_t* empty_bar = full_bar + TC2_STAGES;
-  uint64_t* tfull_bar = empty_bar + TC2_STAGES;
+  const int stage_bytes = tc2_stage_bytes(MODE, BLOCK_N);
+  const int res_bytes = tc2_resident_bytes(MODE, BLOCK_N, p.k_blocks);
+  uint8_t* wres = smem;
+  uint8_t* ring = smem + res_bytes;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(ring + p.stages * stage_bytes);
+  uint64_t* empty_bar = full_bar + MAX_STAGES;
+  uint64_t* tfull_bar = empty_bar + MAX_STAGES;
   uint64_t* tempty_bar = tfull_bar + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+  uint64_t* wres_bar = tempty_bar + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(wres_bar + 1);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -95,8 +110,9 @@ deconv_tc2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_a);
     tma_prefetch_desc(&tmap_b);
-    for (int s = 0; s < TC2_STAGES; ++s) { mbar_init(&full_bar[s], 2); mbar_init(&empty_bar[s], 1); }
+    for (int s = 0; s < p.stages; ++s) { mbar_init(&full_bar[s], 2); mbar_init(&empty_bar[s], 1); }
     for (int b = 0; b < 2; ++b) { mbar_init(&tfull_bar[b], 1); mbar_init(&tempty_bar[b], 8); }
+    mbar_init(wres_bar, 2);
     fence_barrier_init();
   }
   if (warp == 1) {
@@ -111,31 +127,57 @@ deconv_tc2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   const int total_tiles = p.m_tiles * p.n_tiles;          // m_tiles counts 256-row tiles here
   const int npairs = gridDim.x >> 1, pair = blockIdx.x >> 1;
   const int wp = p.w + 1;
-  const int total_kb = 9 * p.k_blocks;
+  const int groups = (MODE == MODE_TAP) ? 9 : 3;
+  const int total_st = groups * p.k_blocks;
 
   if (warp == 0) {
+    // ===== TMA producer (both CTAs; completion bytes go to the leader's barriers) =====
     if (lane == 0) {
+      if constexpr (MODE == MODE_BAND_RES) {
+        // this CTA's half of every weight tile, once; n_tiles == 1 in this mode
+        if (leader) mbar_arrive_expect_tx(wres_bar, 2u * (uint32_t)res_bytes);
+        for (int t = 0; t < 9; ++t)
+          for (int kc = 0; kc < p.k_blocks; ++kc)
+            tma_load_2d_pair(wres + (t * p.k_blocks + kc) * B_HALF_BYTES, &tmap_b, wres_bar, kc * BLOCK_K,
+                             t * p.n_pad + (int)rank * HALF_N);
+        if (!leader) mbar_arrive_remote(wres_bar, 0);
+      }
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = pair; tile < total_tiles; tile += npairs) {
         const int m0 = (tile / p.n_tiles) * 256 + (int)rank * 128;
-        const int n0 = (tile % p.n_tiles) * BLOCK_N + (int)rank * 128;
-        for (int kb = 0; kb < total_kb; ++kb) {
-          const int tap = kb / p.k_blocks, kc = kb % p.k_blocks;
-          const int shift = (tap / 3 - 1) * wp + (tap % 3 - 1);
+        const int n0 = (tile % p.n_tiles) * BLOCK_N + (int)rank * HALF_N;
+        for (int st = 0; st < total_st; ++st) {
+          const int g = st / p.k_blocks, kc = st % p.k_blocks;
           mbar_wait(&empty_bar[stage], phase ^ 1);
-          uint8_t* a_dst = smem + stage * TC2_STAGE_BYTES;
-          if (leader) mbar_arrive_expect_tx(&full_bar[stage], 2u * TC2_STAGE_BYTES);
-          tma_load_2d_pair(a_dst, &tmap_a, &full_bar[stage], kc * BLOCK_K, m0 + shift);
-          tma_load_2d_pair(a_dst + A_TILE_BYTES, &tmap_b, &full_bar[stage], kc * BLOCK_K, tap * p.n_pad + n0);
+          uint8_t* a_dst = ring + stage * stage_bytes;
+          if (leader) mbar_arrive_expect_tx(&full_bar[stage], 2u * (uint32_t)stage_bytes);
+          if constexpr (MODE == MODE_TAP) {
+            const int shift = (g / 3 - 1) * wp + (g % 3 - 1);
+            tma_load_2d_pair(a_dst, &tmap_a, &full_bar[stage], kc * BLOCK_K, m0 + shift);
+            tma_load_2d_pair(a_dst + A_TILE_BYTES, &tmap_b, &full_bar[stage], kc * BLOCK_K, g * p.n_pad + n0);
+          } else {
+            tma_load_2d_pair(a_dst, &tmap_a, &full_bar[stage], kc * BLOCK_K, m0 + (g - 1) * wp - 1);
+            if constexpr (MODE == MODE_BAND) {
+#pragma unroll
+              for (int dx = 0; dx < 3; ++dx)
+                tma_load_2d_pair(a_dst + A_BAND_BYTES + dx * B_HALF_BYTES, &tmap_b, &full_bar[stage], kc * BLOCK_K,
+                                 (g * 3 + dx) * p.n_pad + n0);
+            }
+          }
           if (!leader) mbar_arrive_remote(&full_bar[stage], 0);
-          if (++stage == TC2_STAGES) { stage = 0; phase ^= 1; }
+          if (++stage == p.stages) { stage = 0; phase ^= 1; }
         }
       }
     }
   } else if (warp == 1) {
+    // ===== MMA issuer: one thread of the LEADER issues 256 x BLOCK_N x 16 MMAs for the pair =====
     if (lane == 0 && leader) {
       constexpr uint32_t idesc = make_idesc_bf16(256, BLOCK_N);
+      if constexpr (MODE == MODE_BAND_RES) {
+        mbar_wait(wres_bar, 0);
+        tc_fence_after();
+      }
       int stage = 0;
       uint32_t phase = 0;
       int local = 0;
@@ -145,18 +187,33 @@ deconv_tc2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         mbar_wait(&tempty_bar[buf], (use & 1) ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + (uint32_t)(buf * BLOCK_N);
-        for (int kb = 0; kb < total_kb; ++kb) {
+        for (int st = 0; st < total_st; ++st) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
-          const uint32_t a_addr = smem_u32(smem + stage * TC2_STAGE_BYTES);
-          const uint64_t a_desc = make_sw128_kmajor_desc(a_addr, 0);
-          const uint64_t b_desc = make_sw128_kmajor_desc(a_addr + A_TILE_BYTES, 0);
+          const uint32_t a_addr = smem_u32(ring + stage * stage_bytes);
+          if constexpr (MODE == MODE_TAP) {
+            const uint64_t a_desc = make_sw128_kmajor_desc(a_addr, 0);
+            const uint64_t b_desc = make_sw128_kmajor_desc(a_addr + A_TILE_BYTES, 0);
 #pragma unroll
-          for (int k = 0; k < BLOCK_K / 16; ++k)
-            umma_bf16_pair(d_tmem, a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc, (kb | k) != 0);
+            for (int k = 0; k < BLOCK_K / 16; ++k)
+              umma_bf16_pair(d_tmem, a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc, (st | k) != 0);
+          } else {
+            const int g = st / p.k_blocks, kc = st % p.k_blocks;
+#pragma unroll
+            for (int dx = 0; dx < 3; ++dx) {
+              const uint64_t a_desc = make_sw128_kmajor_desc(a_addr + dx * 128, 0);
+              uint32_t b_addr;
+              if constexpr (MODE == MODE_BAND) b_addr = a_addr + A_BAND_BYTES + dx * B_HALF_BYTES;
+              else b_addr = smem_u32(wres + ((g * 3 + dx) * p.k_blocks + kc) * B_HALF_BYTES);
+              const uint64_t b_desc = make_sw128_kmajor_desc(b_addr, 0);
+#pragma unroll
+              for (int k = 0; k < BLOCK_K / 16; ++k)
+                umma_bf16_pair(d_tmem, a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc, (st | dx | k) != 0);
+            }
+          }
           umma_commit_pair(&empty_bar[stage]);
-          if (kb == total_kb - 1) umma_commit_pair(&tfull_bar[buf]);
-          if (++stage == TC2_STAGES) { stage = 0; phase ^= 1; }
+          if (st == total_st - 1) umma_commit_pair(&tfull_bar[buf]);
+          if (++stage == p.stages) { stage = 0; phase ^= 1; }
         }
       }
       // drain: the peer's epilogue arrives remotely on these barriers; do not leave before it has
@@ -166,6 +223,7 @@ deconv_tc2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       }
     }
   } else {
+    // ===== epilogue (both CTAs, own 128 TMEM lanes = own 128 rows of the 256-row tile) =====
     const int lg = warp & 3;
     const int rp = (p.h + 1) * wp;
     int local = 0;

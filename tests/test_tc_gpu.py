@@ -28,6 +28,11 @@ def bf16_round(a):
     (2, 9, 7, 5, 24, True),                # ragged channels and odd sizes: padded to 64
     (1, 224, 224, 3, 64, True),
     (300, 4, 4, 64, 64, True),             # many tiny items: tiles straddle many item boundaries
+    # large enough (>= 74 tiles of 256 rows) for the CTA-pair kernels (tc_kernel2.cuh), one per staging mode:
+    (40, 28, 28, 256, 512, True),          # pair, tap mode, N tile 256
+    (64, 28, 28, 128, 256, True),          # pair, band mode, N tile 128
+    (24, 56, 56, 64, 128, False),          # pair, band + resident half-weights, N tile 64, K = 128
+    (8, 112, 112, 64, 64, True),           # pair, band + resident, K = 64 (block1_conv2 shape)
 ])
 def test_deconv3x3_bf16_vs_oracle(engine, B, H, W, cin, cout, relu):
     rng = np.random.default_rng(B * 1000 + H + cin + cout + 7)
