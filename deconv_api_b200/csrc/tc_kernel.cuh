@@ -54,7 +54,11 @@ template <int BLOCK_N, int MODE>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, TcParams p) {
   constexpr int B_TILE_BYTES = BLOCK_N * 128;
-  constexpr int TMEM_COLS = (2 * BLOCK_N) < 32 ? 32 : (2 * BLOCK_N);
+  // K-split accumulators: consecutive MMAs into the SAME accumulator are a dependent chain (~90 cycles each for
+  // small N, measured), so the K steps of a tile rotate over KSPLIT accumulators that the epilogue adds up.
+  constexpr int KSPLIT = BLOCK_N <= 64 ? 4 : (BLOCK_N == 128 ? 2 : 1);
+  constexpr int ACC_COLS = BLOCK_N * KSPLIT;              // TMEM columns of one accumulator buffer
+  constexpr int TMEM_COLS = (2 * ACC_COLS) < 32 ? 32 : (2 * ACC_COLS);
   constexpr int MAX_STAGES = 8;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -132,8 +136,8 @@ deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer (single thread) =====
-    if (lane == 0) {
+    // ===== MMA issuer: the whole warp walks the pipeline (uniform control flow), one elected lane issues =====
+    {
       constexpr uint32_t idesc = make_idesc_bf16(BLOCK_M, BLOCK_N);
       if constexpr (MODE == MODE_BAND_RES) {
         mbar_wait(wres_bar, 0);
@@ -147,34 +151,39 @@ deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         const uint32_t use = (uint32_t)(local >> 1);          // how many times this buffer was used before
         mbar_wait(&tempty_bar[buf], (use & 1) ^ 1);           // epilogue has drained it
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + (uint32_t)(buf * BLOCK_N);
+        const uint32_t d_tmem = tmem_base + (uint32_t)(buf * ACC_COLS);
         for (int st = 0; st < total_st; ++st) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
           const uint32_t a_addr = smem_u32(ring + stage * stage_bytes);
-          if constexpr (MODE == MODE_TAP) {
-            const uint64_t a_desc = make_sw128_kmajor_desc(a_addr, 0);
-            const uint64_t b_desc = make_sw128_kmajor_desc(a_addr + A_TILE_BYTES, 0);
+          const int g = st / p.k_blocks, kc = st % p.k_blocks;
+          if (elect_one()) {
+            if constexpr (MODE == MODE_TAP) {
+              const uint64_t a_desc = make_sw128_kmajor_desc(a_addr, 0);
+              const uint64_t b_desc = make_sw128_kmajor_desc(a_addr + A_TILE_BYTES, 0);
 #pragma unroll
-            for (int k = 0; k < BLOCK_K / 16; ++k)   // +32 bytes along K inside the swizzle atom = +2 in addr>>4
-              umma_bf16(d_tmem, a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc, (st | k) != 0);
-          } else {
-            const int g = st / p.k_blocks, kc = st % p.k_blocks;
+              for (int k = 0; k < BLOCK_K / 16; ++k)   // +32 bytes along K inside the swizzle atom = +2 in addr>>4
+                umma_bf16(d_tmem + (uint32_t)((k % KSPLIT) * BLOCK_N), a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc,
+                          (st != 0) || (k >= KSPLIT));
+            } else {
 #pragma unroll
-            for (int dx = 0; dx < 3; ++dx) {
-              // tap (g-1, dx-1): the A operand starts dx rows (dx * 128 bytes) into the band
-              const uint64_t a_desc = make_sw128_kmajor_desc(a_addr + dx * 128, p.base_off ? (uint32_t)dx : 0u);
-              uint32_t b_addr;
-              if constexpr (MODE == MODE_BAND) b_addr = a_addr + A_BAND_BYTES + dx * B_TILE_BYTES;
-              else b_addr = smem_u32(wres + ((g * 3 + dx) * p.k_blocks + kc) * B_TILE_BYTES);
-              const uint64_t b_desc = make_sw128_kmajor_desc(b_addr, 0);
+              for (int dx = 0; dx < 3; ++dx) {
+                // tap (g-1, dx-1): the A operand starts dx rows (dx * 128 bytes) into the band
+                const uint64_t a_desc = make_sw128_kmajor_desc(a_addr + dx * 128, p.base_off ? (uint32_t)dx : 0u);
+                uint32_t b_addr;
+                if constexpr (MODE == MODE_BAND) b_addr = a_addr + A_BAND_BYTES + dx * B_TILE_BYTES;
+                else b_addr = smem_u32(wres + ((g * 3 + dx) * p.k_blocks + kc) * B_TILE_BYTES);
+                const uint64_t b_desc = make_sw128_kmajor_desc(b_addr, 0);
 #pragma unroll
-              for (int k = 0; k < BLOCK_K / 16; ++k)
-                umma_bf16(d_tmem, a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc, (st | dx | k) != 0);
+                for (int k = 0; k < BLOCK_K / 16; ++k)
+                  umma_bf16(d_tmem + (uint32_t)((k % KSPLIT) * BLOCK_N), a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc,
+                            ((st | dx) != 0) || (k >= KSPLIT));
+              }
             }
+            umma_commit(&empty_bar[stage]);                     // smem slot free once these MMAs retire
+            if (st == total_st - 1) umma_commit(&tfull_bar[buf]);
           }
-          umma_commit(&empty_bar[stage]);                     // smem slot free once these MMAs retire
-          if (st == total_st - 1) umma_commit(&tfull_bar[buf]);
+          __syncwarp();
           if (++stage == p.stages) { stage = 0; phase ^= 1; }
         }
       }
@@ -196,7 +205,7 @@ deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       const int y = q / wp, x = q % wp;
       const bool in_range = r < p.rows;
       const bool is_pixel = in_range && (x < p.w) && (y < p.h);
-      const uint32_t t_row = tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(buf * BLOCK_N);
+      const uint32_t t_row = tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(buf * ACC_COLS);
       constexpr int CHUNK = BLOCK_N >= 32 ? 32 : 16;
 #pragma unroll 1
       for (int c0 = 0; c0 < BLOCK_N; c0 += CHUNK) {
@@ -204,6 +213,17 @@ deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         if constexpr (CHUNK == 32) tmem_ld32(t_row + (uint32_t)c0, v);
         else tmem_ld16(t_row + (uint32_t)c0, v);
         tmem_ld_wait();
+        if constexpr (KSPLIT > 1) {              // add the other K-split accumulators
+#pragma unroll
+          for (int sp = 1; sp < KSPLIT; ++sp) {
+            uint32_t u[32];
+            if constexpr (CHUNK == 32) tmem_ld32(t_row + (uint32_t)(sp * BLOCK_N + c0), u);
+            else tmem_ld16(t_row + (uint32_t)(sp * BLOCK_N + c0), u);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < CHUNK; ++i) v[i] = __float_as_uint(__uint_as_float(v[i]) + __uint_as_float(u[i]));
+          }
+        }
         if (p.out_bf16) {
           if (in_range) {
             uint32_t packed[CHUNK / 2];
