@@ -104,3 +104,42 @@ def test_config2_slice_bf16_vs_fp32(vgg):
     # linearity in the seed does not hold (ReLU), but idempotence of the call does: same inputs, same bits
     a2 = eng.project(li, feats, precision="bf16")
     assert np.array_equal(a, a2)
+
+
+def test_mini_model_batch2_bf16(golden):
+    g = golden("mini_reference.npz")
+    mini = keras_shim.mini_model(seed=7)
+    res = dd.visualize_all_layers(mini, g["x2"].copy(), "block2_conv1", "all", precision="bf16")
+    for name, lst in res.items():
+        ref = g["all|b2|%s" % name]
+        assert np.stack(lst).shape == ref.shape
+        assert rel_l2(np.stack(lst), ref) < BF16_TOL, name
+
+
+def test_small_workspace_chunks_give_identical_bits(vgg, monkeypatch):
+    """A tiny workspace budget forces the projections through many chunks (and, for host output, through the
+    pipelined copy path); the bytes must be identical to the single-chunk result."""
+    from deconv_api_b200 import engine as E
+    model, img = vgg
+    eng = model.bound_engine(upto="block3_conv3")
+    li = eng.index["block3_conv3"]
+    eng.forward(img, li)
+    feats = np.arange(0, 96, dtype=np.int32)
+    want = {p: eng.project(li, feats, precision=p) for p in ("bf16", "fp32")}
+    monkeypatch.setenv("DCV_WORKSPACE_MB", "256")
+    small = E.Engine(0)
+    try:
+        for l in model.layers[1:]:
+            if l.kind == "conv":
+                W, b = l.get_weights()
+                small.add_conv(l.name, W, b, relu=True)
+            elif l.kind == "pool":
+                small.add_pool(l.name)
+            if l.name == "block3_conv3":
+                break
+        small.forward(img, small.index["block3_conv3"])
+        for p in ("bf16", "fp32"):
+            got = small.project(small.index["block3_conv3"], feats, precision=p)
+            assert np.array_equal(got, want[p]), p
+    finally:
+        small.close()
