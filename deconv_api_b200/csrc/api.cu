@@ -296,6 +296,14 @@ int forward_impl(dcv_ctx* ctx, const float* img, bool on_device, int B, int H, i
         if (flat) return ctx->fail(DCV_ERR_UNSUPPORTED, "conv after flatten");
         if (l.cin != cc) return ctx->fail(DCV_ERR_ARG, "layer %d: expects %d input channels, got %d", j, l.cin, cc);
         TRY(l.act.ensure(ctx, (size_t)cb * ch * cw * l.cout * sizeof(float)));
+        // fp32-accurate forward: tcgen05 with split operands (conv_tc.cu) for every layer but the first (K = 27),
+        // FFMA otherwise / when disabled (DCV_FWD_TC=0)
+        if (ctx->fwd_mode == 1 && l.cin >= 16) {
+          TRY(tc_prepare_forward_exact(ctx, l));
+          TRY(tc_conv_fwd_exact(ctx, l, cur, cb, ch, cw, (float*)l.act.p));
+          cc = l.cout;
+          break;
+        }
         ConvEpilogue e; e.bias = l.bias; e.relu = l.relu;
         {
           ProfScope ps(ctx, DCV_K_CONV_FP32, 2.0 * 9 * cb * ch * cw * (double)l.cin * l.cout,
@@ -348,6 +356,13 @@ int forward_impl(dcv_ctx* ctx, const float* img, bool on_device, int B, int H, i
   }
   CHECK_LAUNCH(ctx);
   ctx->tape_upto = upto;
+  return 0;
+}
+
+extern "C" int dcv_set_forward_mode(dcv_ctx* ctx, int mode) {
+  ENTER(ctx);
+  if (mode != 0 && mode != 1) return ctx->fail(DCV_ERR_ARG, "dcv_set_forward_mode: mode must be 0 (FFMA) or 1 (tensor cores)");
+  ctx->fwd_mode = mode;
   return 0;
 }
 
@@ -721,7 +736,10 @@ extern "C" int dcv_deprocess(dcv_ctx* ctx, float* x, size_t n, uint8_t* out, int
   CU(ctx, cudaMemcpyAsync(xd, x, n * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
   const int np = deprocess_partials(n);
   TRY(ctx->scratch.ensure(ctx, (size_t)np * 2 * sizeof(double)));
-  launch_deprocess(xd, n, (double*)ctx->scratch.p, np, od, nd, ctx->stream); ctx->launches += 2;
+  {
+    ProfScope ps(ctx, DCV_K_OTHER, 0.0, 9.0 * n);      // two reads of x + one byte written
+    launch_deprocess(xd, n, (double*)ctx->scratch.p, np, od, nd, ctx->stream); ctx->launches += 2;
+  }
   CHECK_LAUNCH(ctx);
   CU(ctx, cudaMemcpyAsync(out, od, n, cudaMemcpyDeviceToHost, ctx->stream));
   if (mutate) CU(ctx, cudaMemcpyAsync(x, nd, n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
@@ -741,7 +759,10 @@ extern "C" int dcv_maxpool_switch(dcv_ctx* ctx, const float* x, int B, int H, in
   TRY(ctx->stage.ensure(ctx, o2 + nout));
   char* base = (char*)ctx->stage.p;
   CU(ctx, cudaMemcpyAsync(base, x, nin * 4, cudaMemcpyHostToDevice, ctx->stream));
-  launch_maxpool_switch((const float*)base, B, H, W, C, (float*)(base + o1), (uint8_t*)(base + o2), ctx->stream); ctx->launches++;
+  {
+    ProfScope ps(ctx, DCV_K_POOL, 0.0, (double)B * H * W * C * (4.0 + 5.0 / 4.0));
+    launch_maxpool_switch((const float*)base, B, H, W, C, (float*)(base + o1), (uint8_t*)(base + o2), ctx->stream); ctx->launches++;
+  }
   CHECK_LAUNCH(ctx);
   CU(ctx, cudaMemcpyAsync(pooled, base + o1, nout * 4, cudaMemcpyDeviceToHost, ctx->stream));
   CU(ctx, cudaMemcpyAsync(sw, base + o2, nout, cudaMemcpyDeviceToHost, ctx->stream));
@@ -760,7 +781,10 @@ extern "C" int dcv_unpool_switch(dcv_ctx* ctx, const float* x, const uint8_t* sw
   char* base = (char*)ctx->stage.p;
   CU(ctx, cudaMemcpyAsync(base, x, nin * 4, cudaMemcpyHostToDevice, ctx->stream));
   CU(ctx, cudaMemcpyAsync(base + o1, sw, nin, cudaMemcpyHostToDevice, ctx->stream));
-  launch_unpool_switch((const float*)base, (const uint8_t*)(base + o1), B, H, W, C, 0, (float*)(base + o2), ctx->stream); ctx->launches++;
+  {
+    ProfScope ps(ctx, DCV_K_UNPOOL, 0.0, (double)B * H * W * C * (4.0 + 5.0 / 4.0));
+    launch_unpool_switch((const float*)base, (const uint8_t*)(base + o1), B, H, W, C, 0, (float*)(base + o2), ctx->stream); ctx->launches++;
+  }
   CHECK_LAUNCH(ctx);
   CU(ctx, cudaMemcpyAsync(out, base + o2, nout * 4, cudaMemcpyDeviceToHost, ctx->stream));
   CU(ctx, cudaStreamSynchronize(ctx->stream));

@@ -69,6 +69,67 @@ __global__ void pack_weights_alltap_kernel(const float* __restrict__ wd, int kdi
   }
 }
 
+// Exact-forward operands: x = hi + mid + lo with three bf16 planes (8 mantissa bits each, 24 together).
+__device__ __forceinline__ void split3(float x, __nv_bfloat16& h, __nv_bfloat16& m, __nv_bfloat16& l) {
+  h = __float2bfloat16_rn(x);
+  const float r1 = x - __bfloat162float(h);
+  m = __float2bfloat16_rn(r1);
+  l = __float2bfloat16_rn(r1 - __bfloat162float(m));
+}
+
+// fp32 compact (P,h,w,C) -> padded-flat bf16 with THREE planes per row: columns [hi | mid | lo], c_pad each.
+__global__ void split3_pad_kernel(const float* __restrict__ x, int P, int h, int w, int C, int c_pad,
+                                  __nv_bfloat16* __restrict__ out) {
+  const int wp = w + 1, rp = (h + 1) * wp, cg = c_pad / 8;
+  const size_t total = (size_t)P * rp * cg;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int g = (int)(i % cg);
+    const size_t r = i / cg;
+    const int q = (int)(r % rp);
+    const int item = (int)(r / rp);
+    const int y = q / wp, xx = q % wp;
+    float v[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) v[k] = 0.f;
+    if (y < h && xx < w) {
+      const float* src = x + (((size_t)item * h + y) * w + xx) * C + g * 8;
+      if ((C & 3) == 0 && g * 8 + 8 <= C) {
+        const float4 a = __ldg(reinterpret_cast<const float4*>(src)), b = __ldg(reinterpret_cast<const float4*>(src + 4));
+        v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+      } else {
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+          if (g * 8 + k < C) v[k] = __ldg(src + k);
+      }
+    }
+    __nv_bfloat16 hh[8], mm[8], ll[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) split3(v[k], hh[k], mm[k], ll[k]);
+    __nv_bfloat16* o = out + r * (3 * (size_t)c_pad) + g * 8;
+    *reinterpret_cast<uint4*>(o) = *reinterpret_cast<const uint4*>(hh);
+    *reinterpret_cast<uint4*>(o + c_pad) = *reinterpret_cast<const uint4*>(mm);
+    *reinterpret_cast<uint4*>(o + 2 * c_pad) = *reinterpret_cast<const uint4*>(ll);
+  }
+}
+
+// Forward weights for the exact path: w fp32 [9][K=cin][N=cout] -> bf16 [tap][plane (hi,mid,lo)][n_pad][k_pad].
+__global__ void pack_weights_fwd3_kernel(const float* __restrict__ w, int kdim, int ndim, int k_pad, int n_pad,
+                                         __nv_bfloat16* __restrict__ out) {
+  const size_t plane = (size_t)n_pad * k_pad;
+  const size_t total = (size_t)9 * plane;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int k = (int)(i % k_pad);
+    const int n = (int)((i / k_pad) % n_pad);
+    const int t = (int)(i / plane);
+    float v = 0.f;
+    if (k < kdim && n < ndim) v = __ldg(w + ((size_t)t * kdim + k) * ndim + n);
+    __nv_bfloat16 h, m, l;
+    split3(v, h, m, l);
+    const size_t o = ((size_t)t * 3) * plane + (size_t)n * k_pad + k;
+    out[o] = h; out[o + plane] = m; out[o + 2 * plane] = l;
+  }
+}
+
 // fp32 compact (P,h,w,C) -> bf16 padded-flat (P*(h+1)*(w+1), c_pad); one thread = 8 channels of one padded row.
 __global__ void pad_convert_kernel(const float* __restrict__ x, int P, int h, int w, int C, int c_pad,
                                    __nv_bfloat16* __restrict__ out) {
@@ -371,6 +432,18 @@ inline int round_up(int v, int m) { return (v + m - 1) / m * m; }
 
 }  // namespace
 
+struct TcConvArgs {
+  const __nv_bfloat16* w;   // [9][n_pad][k_pad]
+  int k_pad, n_pad;
+  int k_real, n_real;
+  int relu;
+  const float* bias;
+  int nprod = 1;            // 6: exact fp32 emulation (three operand planes, six products)
+};
+
+static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& a, const __nv_bfloat16* in, int P, int h, int w,
+                       __nv_bfloat16* out_bf16, float* out_f32);
+
 int tc_cpad(int c) { return round_up(c, 64); }
 
 size_t tc_padded_elems(int h, int w, int c) { return (size_t)(h + 1) * (w + 1) * tc_cpad(c); }
@@ -399,7 +472,8 @@ void tc_free_layer(Layer& l) {
   if (l.tc.wd_bf16) cudaFree(l.tc.wd_bf16);
   if (l.tc.wf_bf16) cudaFree(l.tc.wf_bf16);
   if (l.tc.wall_bf16) cudaFree(l.tc.wall_bf16);
-  l.tc.wd_bf16 = l.tc.wf_bf16 = l.tc.wall_bf16 = nullptr;
+  if (l.tc.wf3_bf16) cudaFree(l.tc.wf3_bf16);
+  l.tc.wd_bf16 = l.tc.wf_bf16 = l.tc.wall_bf16 = l.tc.wf3_bf16 = nullptr;
 }
 
 int tc_pad_convert(dcv_ctx* ctx, const float* x, int P, int h, int w, int C, __nv_bfloat16* out) {
@@ -457,6 +531,36 @@ int tc_sumsq(dcv_ctx* ctx, const __nv_bfloat16* x, size_t elems, double* partial
   return 0;
 }
 
+// Exact (fp32-accurate) forward conv on the tensor cores: both operands are split into three bf16 planes and the
+// six significant cross products are accumulated in fp32 (x*w = hh + hm + mh + hl + lh + mm, dropped terms ~2^-24).
+int tc_prepare_forward_exact(dcv_ctx* ctx, Layer& l) {
+  if (l.tc.wf3_bf16) return 0;
+  l.tc.fk_pad = tc_cpad(l.cin);
+  l.tc.fn_pad = tc_cpad(l.cout);
+  const size_t n = (size_t)9 * 3 * l.tc.fn_pad * l.tc.fk_pad;
+  cudaError_t e = cudaMalloc(&l.tc.wf3_bf16, n * sizeof(__nv_bfloat16));
+  if (e != cudaSuccess) return ctx->fail(DCV_ERR_NOMEM, "cudaMalloc(split forward weights): %s", cudaGetErrorString(e));
+  pack_weights_fwd3_kernel<<<grid_for(n / 3, 256), 256, 0, ctx->stream>>>(l.w, l.cin, l.cout, l.tc.fk_pad, l.tc.fn_pad, l.tc.wf3_bf16);
+  ctx->launches++;
+  return 0;
+}
+
+// in: fp32 compact (P,h,w,cin) -> out: fp32 compact (P,h,w,cout) = act(conv + bias); scratch: ctx->ws[4]
+int tc_conv_fwd_exact(dcv_ctx* ctx, const Layer& l, const float* in, int P, int h, int w, float* out) {
+  if (!l.tc.wf3_bf16) return ctx->fail(DCV_ERR_STATE, "split forward weights were not prepared for this layer");
+  const size_t elems = (size_t)P * (h + 1) * (w + 1) * 3 * l.tc.fk_pad;
+  int r = ctx->ws[4].ensure(ctx, elems * sizeof(__nv_bfloat16));
+  if (r) return r;
+  {
+    const size_t work = (size_t)P * (h + 1) * (w + 1) * (l.tc.fk_pad / 8);
+    ProfScope ps(ctx, DCV_K_OTHER, 0.0, 4.0 * P * h * w * l.cin + 6.0 * P * (h + 1) * (w + 1) * l.tc.fk_pad);
+    split3_pad_kernel<<<grid_for(work, 256), 256, 0, ctx->stream>>>(in, P, h, w, l.cin, l.tc.fk_pad, (__nv_bfloat16*)ctx->ws[4].p);
+    ctx->launches++;
+  }
+  TcConvArgs a{l.tc.wf3_bf16, l.tc.fk_pad, l.tc.fn_pad, l.cin, l.cout, l.relu, l.bias, 6};
+  return tc_conv_run(ctx, a, (const __nv_bfloat16*)ctx->ws[4].p, P, h, w, nullptr, out);
+}
+
 int tc_prepare_forward(dcv_ctx* ctx, Layer& l) {
   if (l.tc.wf_bf16) return 0;
   l.tc.fk_pad = tc_cpad(l.cin);
@@ -469,17 +573,6 @@ int tc_prepare_forward(dcv_ctx* ctx, Layer& l) {
   ctx->launches++;
   return 0;
 }
-
-struct TcConvArgs {
-  const __nv_bfloat16* w;   // [9][n_pad][k_pad]
-  int k_pad, n_pad;
-  int k_real, n_real;
-  int relu;
-  const float* bias;
-};
-
-static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& a, const __nv_bfloat16* in, int P, int h, int w,
-                       __nv_bfloat16* out_bf16, float* out_f32);
 
 int tc_conv(dcv_ctx* ctx, const Layer& l, const __nv_bfloat16* in, int P, int h, int w, __nv_bfloat16* out_bf16,
             float* out_f32, int relu) {
@@ -536,6 +629,8 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
   p.n_pad = l.n_pad; p.n_real = l.n_real;
   p.relu = l.relu;
   p.bias = l.bias;
+  p.nprod = l.nprod;
+  p.nprod_planes = l.nprod == 6 ? 3 : 1;
   p.out_bf16 = out_bf16; p.out_f32 = out_f32;
   p.m_tiles = (p.rows + BLOCK_M - 1) / BLOCK_M;
   int bn;
@@ -546,6 +641,7 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
   // few rows (single images at 14x14 .. 64x64): narrower N tiles give more CTAs and shorter MMAs, which matters
   // more than operand re-use when the grid would not even fill the 148 SMs
   while (bn > 64 && (long long)p.m_tiles * (l.n_pad / bn) < ctx->num_sms) bn >>= 1;
+  if (l.nprod == 6 && bn > 64) bn = 64;       // exact mode needs the four accumulators of the N-tile-64 kernels
   p.n_tiles = bn == 16 ? 1 : l.n_pad / bn;
   // operand staging mode (tc_kernel.cuh): bands for narrow N, resident weights when they fit beside >= 4 stages
   static const int force_mode = getenv("DCV_TC_MODE") ? atoi(getenv("DCV_TC_MODE")) : -1;
@@ -555,17 +651,19 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
   int mode = MODE_TAP;
   if (bn <= 128) {
     mode = MODE_BAND;
-    if (p.n_tiles == 1 && tc_resident_bytes(MODE_BAND_RES, bn, p.k_blocks) + 4 * A_BAND_BYTES <= SMEM_BUDGET) mode = MODE_BAND_RES;
+    if (l.nprod == 1 && p.n_tiles == 1 && tc_resident_bytes(MODE_BAND_RES, bn, p.k_blocks) + 4 * A_BAND_BYTES <= SMEM_BUDGET)
+      mode = MODE_BAND_RES;
   }
   if (force_mode >= 0 && bn <= 128) mode = force_mode;
-  if (mode == MODE_BAND_RES && p.n_tiles != 1) mode = MODE_BAND;
+  if (mode == MODE_BAND_RES && (p.n_tiles != 1 || l.nprod != 1)) mode = MODE_BAND;
   p.base_off = base_off;
   CUtensorMap ta, tb;
-  int r = make_tmap(ctx, &ta, in, (uint64_t)p.rows, (uint64_t)l.k_pad, mode == MODE_TAP ? BLOCK_M : BAND_ROWS);
+  const int planes = l.nprod == 6 ? 3 : 1;
+  int r = make_tmap(ctx, &ta, in, (uint64_t)p.rows, (uint64_t)planes * l.k_pad, mode == MODE_TAP ? BLOCK_M : BAND_ROWS);
   if (r) return r;
-  r = make_tmap(ctx, &tb, l.w, (uint64_t)9 * l.n_pad, (uint64_t)l.k_pad, (uint32_t)bn);
+  r = make_tmap(ctx, &tb, l.w, (uint64_t)9 * planes * l.n_pad, (uint64_t)l.k_pad, (uint32_t)bn);
   if (r) return r;
-  ProfScope ps(ctx, DCV_K_CONV_TC, 2.0 * 9 * P * h * w * (double)l.k_real * l.n_real,
+  ProfScope ps(ctx, l.nprod == 6 ? DCV_K_CONV_FWD : DCV_K_CONV_TC, 2.0 * 9 * P * h * w * (double)l.k_real * l.n_real,
                2.0 * P * h * w * ((double)l.k_real + (out_f32 ? 2.0 * l.n_real : (double)l.n_real)));
 #define TC_DISPATCH(BN)                                                    \
   switch (mode) {                                                          \
@@ -577,7 +675,7 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
   // shuffles per row pair, boundary exchange) is slower than the MMAs it saves: block1_conv2 4.4 ms vs 2.55 ms.
   // Kept opt-in (DCV_TC_DXG=1) as the starting point for a shared-memory col2im epilogue.
   static const int use_dxg = getenv("DCV_TC_DXG") ? atoi(getenv("DCV_TC_DXG")) : 0;
-  if (use_dxg && out_bf16 && l.n_pad == 64 && (p.rows + DXG_ROWS_OUT - 1) / DXG_ROWS_OUT >= ctx->num_sms) {
+  if (use_dxg && l.nprod == 1 && out_bf16 && l.n_pad == 64 && (p.rows + DXG_ROWS_OUT - 1) / DXG_ROWS_OUT >= ctx->num_sms) {
     // 64 output channels: dx-grouped GEMM (tc_dxg.cuh), tiles of 126 rows
     TcParams q = p;
     q.m_tiles = (p.rows + DXG_ROWS_OUT - 1) / DXG_ROWS_OUT;
@@ -616,7 +714,7 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
   const int m_tiles2 = (p.rows + 255) / 256;
   // Measured (profiles/r1_summary.md): the pair form gains 9-13 % at N tile 256 and nothing at N <= 128, where the
   // A-operand read of each SM (unchanged by pairing) sets the pace; DCV_TC_2CTA=2 forces it everywhere for tests.
-  if (bn >= 64 && (use_pair == 2 || (use_pair == 1 && bn == 256)) && (long long)m_tiles2 * p.n_tiles >= ctx->num_sms / 2) {
+  if (l.nprod == 1 && bn >= 64 && (use_pair == 2 || (use_pair == 1 && bn == 256)) && (long long)m_tiles2 * p.n_tiles >= ctx->num_sms / 2) {
     // CTA-pair kernels (tc_kernel2.cuh): tiles of 256 rows x bn channels, each CTA stages half of the B tile
     TcParams q = p;
     q.m_tiles = m_tiles2;

@@ -25,49 +25,92 @@ inline int grid_for(size_t work, int block, int waves = 16) {
   return (int)(b < 1 ? 1 : b);
 }
 
-// Bilinear resize, NHWC, align_corners = false: src = (dst + 0.5) * (in/out) - 0.5 clamped at 0,
-// neighbours x0 = floor(src), x1 = min(x0 + 1, in - 1).  One thread = one output element.
-__global__ void resize_bilinear_kernel(const float* __restrict__ x, int B, int H, int W, int C, int OH, int OW,
-                                       float* __restrict__ out) {
+// Bilinear resize, NHWC, align_corners = false: src = (dst + 0.5) * (in/out) - 0.5 clamped at 0, neighbours
+// x0 = floor(src), x1 = min(x0 + 1, in - 1).  One block row (blockIdx.y) = one output row of one image, so the
+// vertical weights are computed once per block and there is no 64-bit div/mod per element; one thread = one
+// output pixel (all C channels, C <= 4 in registers).
+template <int CMAX>
+__global__ void __launch_bounds__(256)
+resize_bilinear_kernel(const float* __restrict__ x, int H, int W, int C, int OH, int OW, float* __restrict__ out) {
+  const int oy = blockIdx.y % OH, b = blockIdx.y / OH;
   const float sh = (float)H / (float)OH, sw = (float)W / (float)OW;
-  const size_t total = (size_t)B * OH * OW * C;
-  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
-    const int c = (int)(i % C);
-    size_t p = i / C;
-    const int ox = (int)(p % OW); p /= OW;
-    const int oy = (int)(p % OH);
-    const int b = (int)(p / OH);
-    float fy = sh * ((float)oy + 0.5f) - 0.5f; if (fy < 0.f) fy = 0.f;
+  float fy = sh * ((float)oy + 0.5f) - 0.5f; if (fy < 0.f) fy = 0.f;
+  int y0 = (int)fy; if (y0 > H - 1) y0 = H - 1;
+  const int y1 = y0 + (y0 < H - 1 ? 1 : 0);
+  const float ly = fy - (float)y0, hy = 1.f - ly;
+  const float* r0 = x + ((size_t)b * H + y0) * W * C;
+  const float* r1 = x + ((size_t)b * H + y1) * W * C;
+  float* o = out + ((size_t)b * OH + oy) * OW * C;
+  for (int ox = blockIdx.x * blockDim.x + threadIdx.x; ox < OW; ox += gridDim.x * blockDim.x) {
     float fx = sw * ((float)ox + 0.5f) - 0.5f; if (fx < 0.f) fx = 0.f;
-    int y0 = (int)fy, x0 = (int)fx;
-    if (y0 > H - 1) y0 = H - 1;
-    if (x0 > W - 1) x0 = W - 1;
-    const int y1 = y0 + (y0 < H - 1 ? 1 : 0), x1 = x0 + (x0 < W - 1 ? 1 : 0);
-    const float ly = fy - (float)y0, lx = fx - (float)x0;
-    const float hy = 1.f - ly, hx = 1.f - lx;
-    const float* base = x + (size_t)b * H * W * C + c;
-    const float v00 = __ldg(base + ((size_t)y0 * W + x0) * C), v01 = __ldg(base + ((size_t)y0 * W + x1) * C);
-    const float v10 = __ldg(base + ((size_t)y1 * W + x0) * C), v11 = __ldg(base + ((size_t)y1 * W + x1) * C);
-    out[i] = hy * (hx * v00 + lx * v01) + ly * (hx * v10 + lx * v11);
+    int x0 = (int)fx; if (x0 > W - 1) x0 = W - 1;
+    const int x1 = x0 + (x0 < W - 1 ? 1 : 0);
+    const float lx = fx - (float)x0, hx = 1.f - lx;
+#pragma unroll
+    for (int c = 0; c < CMAX; ++c) {
+      if (c < C) {
+        const float v00 = __ldg(r0 + x0 * C + c), v01 = __ldg(r0 + x1 * C + c);
+        const float v10 = __ldg(r1 + x0 * C + c), v11 = __ldg(r1 + x1 * C + c);
+        o[ox * C + c] = hy * (hx * v00 + lx * v01) + ly * (hx * v10 + lx * v11);
+      }
+    }
   }
 }
 
-// out[b, y, x] = in[b, (y - oy) mod H, (x - ox) mod W]   (numpy.roll over the two spatial axes)
+// generic channel count: one thread per output element of the row
+__global__ void __launch_bounds__(256)
+resize_bilinear_rowc_kernel(const float* __restrict__ x, int H, int W, int C, int OH, int OW, float* __restrict__ out) {
+  const int oy = blockIdx.y % OH, b = blockIdx.y / OH;
+  const float sh = (float)H / (float)OH, sw = (float)W / (float)OW;
+  float fy = sh * ((float)oy + 0.5f) - 0.5f; if (fy < 0.f) fy = 0.f;
+  int y0 = (int)fy; if (y0 > H - 1) y0 = H - 1;
+  const int y1 = y0 + (y0 < H - 1 ? 1 : 0);
+  const float ly = fy - (float)y0, hy = 1.f - ly;
+  const float* r0 = x + ((size_t)b * H + y0) * W * C;
+  const float* r1 = x + ((size_t)b * H + y1) * W * C;
+  float* o = out + ((size_t)b * OH + oy) * OW * C;
+  for (int f = blockIdx.x * blockDim.x + threadIdx.x; f < OW * C; f += gridDim.x * blockDim.x) {
+    const int ox = f / C, c = f % C;
+    float fx = sw * ((float)ox + 0.5f) - 0.5f; if (fx < 0.f) fx = 0.f;
+    int x0 = (int)fx; if (x0 > W - 1) x0 = W - 1;
+    const int x1 = x0 + (x0 < W - 1 ? 1 : 0);
+    const float lx = fx - (float)x0, hx = 1.f - lx;
+    o[f] = hy * (hx * __ldg(r0 + x0 * C + c) + lx * __ldg(r0 + x1 * C + c)) + ly * (hx * __ldg(r1 + x0 * C + c) + lx * __ldg(r1 + x1 * C + c));
+  }
+}
+
+// numpy.roll over the two spatial axes: out[b, y, x] = in[b, (y - oy) mod H, (x - ox) mod W].  One block row =
+// one output row: a row is W*C contiguous floats rotated by ox*C, so the kernel is two contiguous segment copies
+// per row with no per-element div/mod.
 // jit (optional): device array {counter, oy0, ox0, oy1, ox1, ...}; the offsets of iteration `counter` are used, so
 // that an iteration captured in a CUDA graph can be replayed with a different jitter every time
-__global__ void roll_kernel(const float* __restrict__ x, int B, int H, int W, int C, int oy, int ox, const int* __restrict__ jit,
-                            float* __restrict__ out) {
+__global__ void __launch_bounds__(256)
+roll_kernel(const float* __restrict__ x, int B, int H, int W, int C, int oy, int ox, const int* __restrict__ jit,
+            float* __restrict__ out) {
   if (jit) { const int c = jit[0]; oy = jit[1 + 2 * c]; ox = jit[2 + 2 * c]; }
-  const size_t total = (size_t)B * H * W * C;
-  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
-    const int c = (int)(i % C);
-    size_t p = i / C;
-    const int xx = (int)(p % W); p /= W;
-    const int y = (int)(p % H);
-    const int b = (int)(p / H);
-    int sy = (y - oy) % H; if (sy < 0) sy += H;
-    int sx = (xx - ox) % W; if (sx < 0) sx += W;
-    out[i] = __ldg(x + (((size_t)b * H + sy) * W + sx) * C + c);
+  const int y = blockIdx.y % H, b = blockIdx.y / H;
+  int sy = (y - oy) % H; if (sy < 0) sy += H;
+  int sx = ox % W; if (sx < 0) sx += W;
+  const int wc = W * C, shift = sx * C;                  // out[f] = in[(f - shift) mod wc]
+  const float* src = x + ((size_t)b * H + sy) * wc;
+  float* dst = out + ((size_t)b * H + y) * wc;
+  if ((wc & 3) == 0) {
+    // 16-byte stores (rows start 16-byte aligned when W*C is a multiple of 4); the rotated source is read with four
+    // scalar loads that coalesce across the warp
+    for (int f = (blockIdx.x * blockDim.x + threadIdx.x) * 4; f < wc; f += gridDim.x * blockDim.x * 4) {
+      float v[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        int g = f + k - shift; if (g < 0) g += wc;
+        v[k] = __ldg(src + g);
+      }
+      *reinterpret_cast<float4*>(dst + f) = make_float4(v[0], v[1], v[2], v[3]);
+    }
+  } else {
+    for (int f = blockIdx.x * blockDim.x + threadIdx.x; f < wc; f += gridDim.x * blockDim.x) {
+      int g = f - shift; if (g < 0) g += wc;
+      dst[f] = __ldg(src + g);
+    }
   }
 }
 
@@ -117,13 +160,36 @@ __global__ void add_diff_kernel(float* __restrict__ img, const float* __restrict
 }  // namespace
 
 void launch_resize_bilinear(const float* x, int B, int H, int W, int C, int OH, int OW, float* out, cudaStream_t s) {
-  const size_t total = (size_t)B * OH * OW * C;
-  if (total) resize_bilinear_kernel<<<grid_for(total, 256), 256, 0, s>>>(x, B, H, W, C, OH, OW, out);
+  if ((size_t)B * OH * OW * C == 0) return;
+  int b0 = 0;
+  while (b0 < B) {                                   // gridDim.y <= 65535 output rows per launch
+    const int nb = std::min(B - b0, std::max(1, 65535 / OH));
+    const float* xi = x + (size_t)b0 * H * W * C;
+    float* oi = out + (size_t)b0 * OH * OW * C;
+    if (C <= 4) {
+      dim3 grid((OW + 255) / 256, nb * OH);
+      resize_bilinear_kernel<4><<<grid, 256, 0, s>>>(xi, H, W, C, OH, OW, oi);
+    } else {
+      dim3 grid(std::min((OW * C + 255) / 256, 64), nb * OH);
+      resize_bilinear_rowc_kernel<<<grid, 256, 0, s>>>(xi, H, W, C, OH, OW, oi);
+    }
+    b0 += nb;
+  }
+}
+
+static void launch_roll_impl(const float* x, int B, int H, int W, int C, int oy, int ox, const int* jit, float* out, cudaStream_t s) {
+  if ((size_t)B * H * W * C == 0) return;
+  int b0 = 0;
+  while (b0 < B) {
+    const int nb = std::min(B - b0, std::max(1, 65535 / H));
+    dim3 grid(std::min((W * C / 4 + 255) / 256 + 1, 64), nb * H);
+    roll_kernel<<<grid, 256, 0, s>>>(x + (size_t)b0 * H * W * C, nb, H, W, C, oy, ox, jit, out + (size_t)b0 * H * W * C);
+    b0 += nb;
+  }
 }
 
 void launch_roll(const float* x, int B, int H, int W, int C, int oy, int ox, float* out, cudaStream_t s) {
-  const size_t total = (size_t)B * H * W * C;
-  if (total) roll_kernel<<<grid_for(total, 256), 256, 0, s>>>(x, B, H, W, C, oy, ox, nullptr, out);
+  launch_roll_impl(x, B, H, W, C, oy, ox, nullptr, out, s);
 }
 
 // ---- host side ----------------------------------------------------------------------------------------
@@ -321,7 +387,7 @@ int dream_iter(dcv_ctx* ctx, float* img, int B, int H, int W, int C, const LossS
   float* x = (float*)ctx->dream[3].p;
   {
     ProfScope ps(ctx, DCV_K_OTHER, 0.0, 8.0 * n);
-    roll_kernel<<<grid_for(n, 256), 256, 0, ctx->stream>>>(img, B, H, W, C, 0, 0, jit_dev, x); ctx->launches++;
+    launch_roll_impl(img, B, H, W, C, 0, 0, jit_dev, x, ctx->stream); ctx->launches++;
   }
   float* g = nullptr;
   if (precision == DCV_BF16) {
@@ -535,7 +601,10 @@ extern "C" int dcv_resize_bilinear(dcv_ctx* ctx, const float* x, int B, int H, i
   TRYD(ctx->stage.ensure(ctx, o1 + nout * 4));
   char* base = (char*)ctx->stage.p;
   CUD(ctx, cudaMemcpyAsync(base, x, nin * 4, cudaMemcpyHostToDevice, ctx->stream));
-  launch_resize_bilinear((const float*)base, B, H, W, C, OH, OW, (float*)(base + o1), ctx->stream); ctx->launches++;
+  {
+    ProfScope ps(ctx, DCV_K_OTHER, 0.0, 4.0 * (nin + nout));
+    launch_resize_bilinear((const float*)base, B, H, W, C, OH, OW, (float*)(base + o1), ctx->stream); ctx->launches++;
+  }
   CUD(ctx, cudaGetLastError());
   CUD(ctx, cudaMemcpyAsync(out, base + o1, nout * 4, cudaMemcpyDeviceToHost, ctx->stream));
   CUD(ctx, cudaStreamSynchronize(ctx->stream));
@@ -550,7 +619,10 @@ extern "C" int dcv_roll(dcv_ctx* ctx, const float* x, int B, int H, int W, int C
   TRYD(ctx->stage.ensure(ctx, o1 + n * 4));
   char* base = (char*)ctx->stage.p;
   CUD(ctx, cudaMemcpyAsync(base, x, n * 4, cudaMemcpyHostToDevice, ctx->stream));
-  launch_roll((const float*)base, B, H, W, C, oy, ox, (float*)(base + o1), ctx->stream); ctx->launches++;
+  {
+    ProfScope ps(ctx, DCV_K_OTHER, 0.0, 8.0 * n);
+    launch_roll((const float*)base, B, H, W, C, oy, ox, (float*)(base + o1), ctx->stream); ctx->launches++;
+  }
   CUD(ctx, cudaGetLastError());
   CUD(ctx, cudaMemcpyAsync(out, base + o1, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
   CUD(ctx, cudaStreamSynchronize(ctx->stream));

@@ -17,6 +17,7 @@ struct TcWeights {
   int n_pad = 0, k_pad = 0;           // N = cin, K = cout of the forward layer, rounded up to 64
   __nv_bfloat16* wf_bf16 = nullptr;   // forward weights [9][fn_pad][fk_pad] (N = cout, K = cin); built on first bf16 DeepDream
   int fn_pad = 0, fk_pad = 0;
+  __nv_bfloat16* wf3_bf16 = nullptr;  // forward weights split into (hi, mid, lo) bf16 planes: [9][3][fn_pad][fk_pad] (exact forward)
   __nv_bfloat16* wall_bf16 = nullptr; // narrow last layer (9*cin <= 32): all taps stacked along N, [32][k_pad]
 };
 
@@ -51,6 +52,7 @@ struct dcv_ctx {
   size_t workspace_budget = 0;
   std::vector<Layer> net;
   int tape_upto = -1;
+  int fwd_mode = 1;    // dcv_set_forward_mode: 0 = FFMA fp32, 1 = tcgen05 with split operands (default)
   int in_B = 0, in_H = 0, in_W = 0, in_C = 0;
   DevBuf input;
   DevBuf ws[6];        // projection workspace: [0],[1] ping-pong tensors, [2],[3] maps, [4],[5] bf16 ping-pong
@@ -101,6 +103,9 @@ int tc_dream_prep(dcv_ctx* ctx, __nv_bfloat16* g, const __nv_bfloat16* act, size
 int tc_sumsq_partials(size_t elems);
 int tc_sumsq(dcv_ctx* ctx, const __nv_bfloat16* x, size_t elems, double* partial, int np);
 int tc_prepare_forward(dcv_ctx* ctx, Layer& l);
+// fp32-accurate forward conv on tcgen05 (bf16 x 3 operand split, six products); fp32 compact in and out
+int tc_prepare_forward_exact(dcv_ctx* ctx, Layer& l);
+int tc_conv_fwd_exact(dcv_ctx* ctx, const Layer& l, const float* in, int P, int h, int w, float* out);
 // backward conv; exactly one of out_bf16 (padded-flat, pitch l.tc.n_pad) / out_f32 (compact (P,h,w,l.cin)) is
 // non-null; relu < 0: the layer's own activation (deconvnet rule), 0/1: explicit (DeepDream uses 0)
 int tc_conv(dcv_ctx* ctx, const Layer& l, const __nv_bfloat16* in, int P, int h, int w, __nv_bfloat16* out_bf16, float* out_f32,

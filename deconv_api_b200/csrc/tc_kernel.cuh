@@ -36,6 +36,9 @@ struct TcParams {
   int relu;
   int stages;        // smem ring depth (host-computed from the budget)
   int base_off;      // 1: put (start_addr >> 7) & 7 into the descriptor's base-offset field
+  int nprod_planes;  // weight planes per tap in the packed weights: 1, or 3 with nprod == 6
+  int nprod;         // 1 = plain bf16 product; 6 = exact fp32 emulation: operands are split into three bf16 planes
+                     // (hi, mid, lo) and the six significant cross products are accumulated (tc forward conv)
   const float* bias;         // n_real entries added before the ReLU (forward conv), or null
   __nv_bfloat16* out_bf16;   // padded-flat (rows, n_pad), or null
   float* out_f32;            // compact (P,h,w,n_real), or null
@@ -96,7 +99,8 @@ deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   const int total_tiles = p.m_tiles * p.n_tiles;
   const int wp = p.w + 1;
   const int groups = (MODE == MODE_TAP) ? 9 : 3;      // stages per 64-channel block
-  const int total_st = groups * p.k_blocks;           // stages per tile
+  const int total_st = groups * p.nprod * p.k_blocks; // stages per tile
+  const int kcols = p.k_blocks * BLOCK_K;             // columns of one operand plane
 
   if (warp == 0) {
     // ===== TMA producer =====
@@ -114,21 +118,27 @@ deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         const int m0 = (tile / p.n_tiles) * BLOCK_M;
         const int n0 = (tile % p.n_tiles) * BLOCK_N;
         for (int st = 0; st < total_st; ++st) {
-          const int g = st / p.k_blocks, kc = st % p.k_blocks;
+          const int kc = st % p.k_blocks;
+          const int gp = st / p.k_blocks;
+          const int g = gp / p.nprod, prod = gp % p.nprod;
+          // operand planes of product `prod` (hi*hi, hi*mid, mid*hi, hi*lo, lo*hi, mid*mid); plane 0 when nprod == 1
+          const int pa = (0x120100 >> (4 * prod)) & 3;       // A plane: 0,0,1,0,2,1
+          const int pb = (0x102010 >> (4 * prod)) & 3;       // B plane: 0,1,0,2,0,1
+          const int a_col = pa * kcols + kc * BLOCK_K;
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* a_dst = ring + stage * stage_bytes;
           mbar_arrive_expect_tx(&full_bar[stage], (uint32_t)stage_bytes);
           if constexpr (MODE == MODE_TAP) {
             const int shift = (g / 3 - 1) * wp + (g % 3 - 1);
-            tma_load_2d(a_dst, &tmap_a, &full_bar[stage], kc * BLOCK_K, m0 + shift);
-            tma_load_2d(a_dst + A_TILE_BYTES, &tmap_b, &full_bar[stage], kc * BLOCK_K, g * p.n_pad + n0);
+            tma_load_2d(a_dst, &tmap_a, &full_bar[stage], a_col, m0 + shift);
+            tma_load_2d(a_dst + A_TILE_BYTES, &tmap_b, &full_bar[stage], kc * BLOCK_K, (g * p.nprod_planes + pb) * p.n_pad + n0);
           } else {
-            tma_load_2d(a_dst, &tmap_a, &full_bar[stage], kc * BLOCK_K, m0 + (g - 1) * wp - 1);
+            tma_load_2d(a_dst, &tmap_a, &full_bar[stage], a_col, m0 + (g - 1) * wp - 1);
             if constexpr (MODE == MODE_BAND) {
 #pragma unroll
               for (int dx = 0; dx < 3; ++dx)
                 tma_load_2d(a_dst + A_BAND_BYTES + dx * B_TILE_BYTES, &tmap_b, &full_bar[stage], kc * BLOCK_K,
-                            (g * 3 + dx) * p.n_pad + n0);
+                            ((g * 3 + dx) * p.nprod_planes + pb) * p.n_pad + n0);
             }
           }
           if (++stage == p.stages) { stage = 0; phase ^= 1; }
@@ -156,15 +166,29 @@ deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
           const uint32_t a_addr = smem_u32(ring + stage * stage_bytes);
-          const int g = st / p.k_blocks, kc = st % p.k_blocks;
+          const int kc = st % p.k_blocks;
+          const int gp = st / p.k_blocks;
+          const int g = gp / p.nprod, prod = gp % p.nprod;
+          // Split-operand (exact) mode, KSPLIT == 4: the tensor core TRUNCATES when it adds into an accumulator, so the
+          // error grows with the number of adds into a LARGE running sum.  The hi*hi products (which carry the
+          // magnitude) therefore rotate over accumulators 0..2 and the five small correction products share
+          // accumulator 3; the epilogue adds the four with fp32 round-to-nearest.
+          const bool exact = (p.nprod == 6) && (KSPLIT == 4);
           if (elect_one()) {
             if constexpr (MODE == MODE_TAP) {
               const uint64_t a_desc = make_sw128_kmajor_desc(a_addr, 0);
               const uint64_t b_desc = make_sw128_kmajor_desc(a_addr + A_TILE_BYTES, 0);
 #pragma unroll
-              for (int k = 0; k < BLOCK_K / 16; ++k)   // +32 bytes along K inside the swizzle atom = +2 in addr>>4
-                umma_bf16(d_tmem + (uint32_t)((k % KSPLIT) * BLOCK_N), a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc,
-                          (st != 0) || (k >= KSPLIT));
+              for (int k = 0; k < BLOCK_K / 16; ++k) {  // +32 bytes along K inside the swizzle atom = +2 in addr>>4
+                int acc = k % KSPLIT;
+                bool accumulate = (st != 0) || (k >= KSPLIT);
+                if (exact) {
+                  const int j = (g * p.k_blocks + kc) * 4 + k;             // running index of the hi*hi MMAs of this tile
+                  acc = prod == 0 ? j % 3 : 3;
+                  accumulate = prod == 0 ? j >= 3 : !(g == 0 && prod == 1 && kc == 0 && k == 0);
+                }
+                umma_bf16(d_tmem + (uint32_t)(acc * BLOCK_N), a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc, accumulate);
+              }
             } else {
 #pragma unroll
               for (int dx = 0; dx < 3; ++dx) {
@@ -175,9 +199,16 @@ deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                 else b_addr = smem_u32(wres + ((g * 3 + dx) * p.k_blocks + kc) * B_TILE_BYTES);
                 const uint64_t b_desc = make_sw128_kmajor_desc(b_addr, 0);
 #pragma unroll
-                for (int k = 0; k < BLOCK_K / 16; ++k)
-                  umma_bf16(d_tmem + (uint32_t)((k % KSPLIT) * BLOCK_N), a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc,
-                            ((st | dx) != 0) || (k >= KSPLIT));
+                for (int k = 0; k < BLOCK_K / 16; ++k) {
+                  int acc = k % KSPLIT;
+                  bool accumulate = ((st | dx) != 0) || (k >= KSPLIT);
+                  if (exact) {
+                    const int j = ((g * 3 + dx) * p.k_blocks + kc) * 4 + k;
+                    acc = prod == 0 ? j % 3 : 3;
+                    accumulate = prod == 0 ? j >= 3 : !(g == 0 && dx == 0 && prod == 1 && kc == 0 && k == 0);
+                  }
+                  umma_bf16(d_tmem + (uint32_t)(acc * BLOCK_N), a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc, accumulate);
+                }
               }
             }
             umma_commit(&empty_bar[stage]);                     // smem slot free once these MMAs retire
@@ -248,14 +279,28 @@ deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         } else if (is_pixel) {
           const int item = r / rp;
           float* dst = p.out_f32 + (((size_t)item * p.h + y) * p.w + x) * p.n_real;
+          if ((p.n_real & 3) == 0 && n0 + c0 + CHUNK <= p.n_real) {      // 16-byte stores for whole chunks
 #pragma unroll
-          for (int i = 0; i < CHUNK; ++i) {
-            const int c = n0 + c0 + i;
-            if (c < p.n_real) {
-              float a = __uint_as_float(v[i]);
-              if (p.bias) a += __ldg(p.bias + c);
-              if (p.relu) a = fmaxf(a, 0.f);
-              dst[c] = a;
+            for (int i = 0; i < CHUNK; i += 4) {
+              float a[4];
+#pragma unroll
+              for (int k = 0; k < 4; ++k) {
+                a[k] = __uint_as_float(v[i + k]);
+                if (p.bias) a[k] += __ldg(p.bias + n0 + c0 + i + k);
+                if (p.relu) a[k] = fmaxf(a[k], 0.f);
+              }
+              *reinterpret_cast<float4*>(dst + n0 + c0 + i) = make_float4(a[0], a[1], a[2], a[3]);
+            }
+          } else {
+#pragma unroll
+            for (int i = 0; i < CHUNK; ++i) {
+              const int c = n0 + c0 + i;
+              if (c < p.n_real) {
+                float a = __uint_as_float(v[i]);
+                if (p.bias) a += __ldg(p.bias + c);
+                if (p.relu) a = fmaxf(a, 0.f);
+                dst[c] = a;
+              }
             }
           }
         }

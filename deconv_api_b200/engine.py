@@ -76,7 +76,7 @@ class Engine(object):
         return self.lib.dcv_stream(self.ctx)
 
     # -- per-kernel-class timing
-    KERNEL_CLASSES = ("conv_fp32", "conv_tc", "pool", "unpool", "rank1", "other")
+    KERNEL_CLASSES = ("conv_fp32", "conv_tc", "pool", "unpool", "rank1", "other", "conv_fwd")
 
     def profile(self, enable=True):
         self._ck(self.lib.dcv_profile(self.ctx, 1 if enable else 0))
@@ -141,6 +141,10 @@ class Engine(object):
         self.index[name] = idx
 
     # -- forward tape
+    def set_forward_mode(self, tensor_cores):
+        """False: FFMA fp32 forward (parity mode, default); True: tcgen05 split-operand forward (~2e-6 per layer)."""
+        self._ck(self.lib.dcv_set_forward_mode(self.ctx, 1 if tensor_cores else 0))
+
     def forward(self, data, upto):
         data = _f32(data)
         assert data.ndim == 4, "data must be (B,H,W,C)"

@@ -75,7 +75,8 @@ enum dcv_kernel_class {
   DCV_K_UNPOOL = 3,     /* switch-driven unpool (tensor and single-map forms) */
   DCV_K_RANK1 = 4,      /* rank-1 first backward conv */
   DCV_K_OTHER = 5,      /* seed gather, layout/precision conversion, sums, de-process, dense */
-  DCV_K_NUM = 6
+  DCV_K_CONV_FWD = 6,   /* tcgen05 forward conv with split operands (6 MMA products per algorithmic flop) */
+  DCV_K_NUM = 7
 };
 /* enable != 0: record a CUDA event pair on the context's stream around every kernel launch (cleared on
  * every call).  dcv_profile_read synchronises and returns, for one class, the summed device time in
@@ -108,6 +109,12 @@ DCV_API int dcv_net_num_layers(const dcv_ctx* ctx);
  * Runs layers 0..upto_layer on a batch of B images (B,H,W,C0) and keeps every layer's output (and
  * every pool's switches) on the device until the next dcv_forward. ---------------------------- */
 DCV_API int dcv_forward(dcv_ctx* ctx, const float* img_nhwc, int B, int H, int W, int upto_layer);
+/* Arithmetic of the forward convs (no counterpart in the reference).  1 (default): tcgen05 with both operands
+ * split into three bf16 planes and the six significant cross products accumulated in fp32 (x*w = hh + hm + mh + hl
+ * + lh + mm; the hi*hi products rotate over three accumulators, the corrections use a fourth, because the tensor
+ * core truncates when it adds into an accumulator): measured rel-L2 1e-7 .. 1e-6 per layer against float64, the same
+ * as the FFMA kernel, at 3-10x its speed for batch 1; the first conv (K = 27) stays FFMA.  0: FFMA fp32 everywhere. */
+DCV_API int dcv_set_forward_mode(dcv_ctx* ctx, int mode);
 DCV_API int dcv_forward_dev(dcv_ctx* ctx, const float* img_nhwc_dev, int B, int H, int W, int upto_layer);
 /* Shape of layer `layer`'s output in the current tape: dims[0..3] = B,H,W,C (H=W=1 after flatten). */
 DCV_API int dcv_layer_shape(const dcv_ctx* ctx, int layer, int dims[4]);
