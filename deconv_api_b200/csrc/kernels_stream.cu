@@ -218,7 +218,19 @@ __global__ void __launch_bounds__(256) deprocess_stats_kernel(const float* __res
   double s = 0.0, q = 0.0;
   const size_t n4 = n / 4;
   const float4* x4 = reinterpret_cast<const float4*>(x);
-  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  // four independent 16-byte loads in flight per thread; per-load fp32 partials are folded into fp64 at once
+  for (; i + 3 * stride < n4; i += 4 * stride) {
+    const float4 a = __ldg(x4 + i), b = __ldg(x4 + i + stride), c = __ldg(x4 + i + 2 * stride), d = __ldg(x4 + i + 3 * stride);
+    s += ((double)a.x + (double)a.y + (double)a.z + (double)a.w) + ((double)b.x + (double)b.y + (double)b.z + (double)b.w) +
+         ((double)c.x + (double)c.y + (double)c.z + (double)c.w) + ((double)d.x + (double)d.y + (double)d.z + (double)d.w);
+    q += ((double)a.x * a.x + (double)a.y * a.y + (double)a.z * a.z + (double)a.w * a.w) +
+         ((double)b.x * b.x + (double)b.y * b.y + (double)b.z * b.z + (double)b.w * b.w) +
+         ((double)c.x * c.x + (double)c.y * c.y + (double)c.z * c.z + (double)c.w * c.w) +
+         ((double)d.x * d.x + (double)d.y * d.y + (double)d.z * d.z + (double)d.w * d.w);
+  }
+  for (; i < n4; i += stride) {
     const float4 a = __ldg(x4 + i);
     s += (double)a.x + (double)a.y + (double)a.z + (double)a.w;
     q += (double)a.x * a.x + (double)a.y * a.y + (double)a.z * a.z + (double)a.w * a.w;
@@ -278,6 +290,7 @@ __global__ void __launch_bounds__(256) deprocess_map_kernel(const float* __restr
   const float mean = sh[0], denom = sh[1];
   const size_t n4 = n / 4;
   const float4* x4 = reinterpret_cast<const float4*>(x);
+#pragma unroll 4
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
     const float4 a = __ldg(x4 + i);
     uchar4 r;
