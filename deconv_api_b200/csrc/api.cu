@@ -582,6 +582,24 @@ static int project_chunk(dcv_ctx* ctx, int layer, int foff, int n, int vis_mode,
             rep_bf16 = true;
           }
           if (more_convs) {
+            // a pool layer directly below: its switch-driven unpool is fused into this conv's epilogue
+            static const int fuse_unpool = getenv("DCV_TC_FUSE_UNPOOL") ? atoi(getenv("DCV_TC_FUSE_UNPOOL")) : 1;
+            // Measured: the 4x wider stores make the epilogue the bottleneck for N tiles <= 128 (block3_conv1 +0.14 ms,
+            // block2_conv1 +0.48 ms net), so only layers that run with the N-tile-256 kernels fuse (DCV_TC_FUSE_UNPOOL=2: all)
+            const bool wide = l.tc.n_pad % 256 == 0 && (long long)P * (h + 1) * (w + 1) >= 256LL * ctx->num_sms / 2;
+            const Layer* pl = (fuse_unpool && (wide || fuse_unpool == 2) && j > 0 && ctx->net[j - 1].kind == LK_POOL) ? &ctx->net[j - 1] : nullptr;
+            if (pl) {
+              if ((pl->in_H & 1) || (pl->in_W & 1))
+                return ctx->fail(DCV_ERR_ARG, "unpool of layer %d: odd input size %dx%d (the reference raises here too)", j - 1, pl->in_H, pl->in_W);
+              TcUnpool up{(const uint8_t*)pl->sw.p, B, l.cin, pl->in_H, pl->in_W};
+              TRY(tc_conv(ctx, l, hb[hcur], P, h, w, hb[hcur ^ 1], nullptr, -1, &up));
+              h = pl->in_H; w = pl->in_W;
+              nonneg = l.relu != 0;
+              C = l.cin;
+              hcur ^= 1;
+              --j;                      // the pool layer is done
+              continue;
+            }
             TRY(tc_conv(ctx, l, hb[hcur], P, h, w, hb[hcur ^ 1], nullptr, -1));
             hcur ^= 1;
             cur ^= 1;                   // keeps the fp32 ping-pong bookkeeping below uniform

@@ -439,6 +439,7 @@ struct TcConvArgs {
   int relu;
   const float* bias;
   int nprod = 1;            // 6: exact fp32 emulation (three operand planes, six products)
+  const TcUnpool* up = nullptr;
 };
 
 static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& a, const __nv_bfloat16* in, int P, int h, int w,
@@ -575,7 +576,8 @@ int tc_prepare_forward(dcv_ctx* ctx, Layer& l) {
 }
 
 int tc_conv(dcv_ctx* ctx, const Layer& l, const __nv_bfloat16* in, int P, int h, int w, __nv_bfloat16* out_bf16,
-            float* out_f32, int relu) {
+            float* out_f32, int relu, const TcUnpool* up) {
+  if (up && !out_bf16) return ctx->fail(DCV_ERR_ARG, "tc_conv: fused unpool needs the bf16 output form");
   if (!l.tc.wd_bf16) return ctx->fail(DCV_ERR_STATE, "tensor-core weights were not prepared for this layer");
   static const int use_last = getenv("DCV_TC_LAST") ? atoi(getenv("DCV_TC_LAST")) : 1;
   if (out_f32 && l.tc.wall_bf16 && use_last) {
@@ -610,6 +612,7 @@ int tc_conv(dcv_ctx* ctx, const Layer& l, const __nv_bfloat16* in, int P, int h,
     return 0;
   }
   TcConvArgs a{l.tc.wd_bf16, l.tc.k_pad, l.tc.n_pad, l.cout, l.cin, relu < 0 ? l.relu : relu, nullptr};
+  a.up = up;
   return tc_conv_run(ctx, a, in, P, h, w, out_bf16, out_f32);
 }
 
@@ -631,6 +634,8 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
   p.bias = l.bias;
   p.nprod = l.nprod;
   p.nprod_planes = l.nprod == 6 ? 3 : 1;
+  p.up_sw = l.up ? l.up->sw : nullptr;
+  p.up_B = l.up ? l.up->B : 0; p.up_C = l.up ? l.up->C : 0; p.up_h = l.up ? l.up->h : 0; p.up_w = l.up ? l.up->w : 0;
   p.out_bf16 = out_bf16; p.out_f32 = out_f32;
   p.m_tiles = (p.rows + BLOCK_M - 1) / BLOCK_M;
   int bn;
@@ -675,7 +680,7 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
   // shuffles per row pair, boundary exchange) is slower than the MMAs it saves: block1_conv2 4.4 ms vs 2.55 ms.
   // Kept opt-in (DCV_TC_DXG=1) as the starting point for a shared-memory col2im epilogue.
   static const int use_dxg = getenv("DCV_TC_DXG") ? atoi(getenv("DCV_TC_DXG")) : 0;
-  if (use_dxg && l.nprod == 1 && out_bf16 && l.n_pad == 64 && (p.rows + DXG_ROWS_OUT - 1) / DXG_ROWS_OUT >= ctx->num_sms) {
+  if (use_dxg && l.nprod == 1 && !l.up && out_bf16 && l.n_pad == 64 && (p.rows + DXG_ROWS_OUT - 1) / DXG_ROWS_OUT >= ctx->num_sms) {
     // 64 output channels: dx-grouped GEMM (tc_dxg.cuh), tiles of 126 rows
     TcParams q = p;
     q.m_tiles = (p.rows + DXG_ROWS_OUT - 1) / DXG_ROWS_OUT;

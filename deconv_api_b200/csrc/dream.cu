@@ -357,10 +357,20 @@ int dream_backward_bf16(dcv_ctx* ctx, const LossSpec& ls, float** grad, double* 
     }
     const float scale = coeff != 0.f ? 2.f * coeff / (float)n : 0.f;
     if (!has_g && scale == 0.f) continue;
-    TRYD(tc_dream_prep(ctx, hb[cur], (const __nv_bfloat16*)l.act_h.p, elems, scale, has_g ? 1 : 0, l.kind == LK_CONV ? l.relu : 0));
+    const int prep_relu = l.kind == LK_CONV ? l.relu : 0;
+    if (scale != 0.f || prep_relu)     // a pool that is not a loss layer passes the gradient through unchanged
+      TRYD(tc_dream_prep(ctx, hb[cur], (const __nv_bfloat16*)l.act_h.p, elems, scale, has_g ? 1 : 0, prep_relu));
     if (l.kind == LK_CONV) {
       if (j == 0) {
         TRYD(tc_conv(ctx, l, hb[cur], l.B, l.H, l.W, nullptr, (float*)ctx->ws[0].p, 0));
+      } else if (ctx->net[j - 1].kind == LK_POOL && ls.coeff[j - 1] == 0.f && l.tc.n_pad % 256 == 0 &&
+                 (long long)l.B * (l.H + 1) * (l.W + 1) >= 256LL * ctx->num_sms / 2) {
+        // max-pool backward of the layer below fused into this conv's epilogue (no seed to add at that pool)
+        const Layer& pl = ctx->net[j - 1];
+        TcUnpool up{(const uint8_t*)pl.sw.p, pl.B, pl.C, pl.in_H, pl.in_W};
+        TRYD(tc_conv(ctx, l, hb[cur], l.B, l.H, l.W, hb[cur ^ 1], nullptr, 0, &up));
+        cur ^= 1;
+        --j;
       } else {
         TRYD(tc_conv(ctx, l, hb[cur], l.B, l.H, l.W, hb[cur ^ 1], nullptr, 0));
         cur ^= 1;

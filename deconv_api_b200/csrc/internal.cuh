@@ -108,8 +108,11 @@ int tc_prepare_forward_exact(dcv_ctx* ctx, Layer& l);
 int tc_conv_fwd_exact(dcv_ctx* ctx, const Layer& l, const float* in, int P, int h, int w, float* out);
 // backward conv; exactly one of out_bf16 (padded-flat, pitch l.tc.n_pad) / out_f32 (compact (P,h,w,l.cin)) is
 // non-null; relu < 0: the layer's own activation (deconvnet rule), 0/1: explicit (DeepDream uses 0)
+// up (optional, bf16 output only): fuse the switch-driven unpool of the pool layer below into the epilogue; out_bf16 is
+// then the padded-flat tensor at the unpooled size (up->h, up->w) and the pooled tensor is never written
+struct TcUnpool { const uint8_t* sw; int B, C, h, w; };
 int tc_conv(dcv_ctx* ctx, const Layer& l, const __nv_bfloat16* in, int P, int h, int w, __nv_bfloat16* out_bf16, float* out_f32,
-            int relu);
+            int relu, const TcUnpool* up = nullptr);
 // forward conv + bias + activation, bf16 padded-flat in and out
 int tc_conv_fwd(dcv_ctx* ctx, const Layer& l, const __nv_bfloat16* in, int P, int h, int w, __nv_bfloat16* out_bf16);
 int tc_deconv(dcv_ctx* ctx, const Layer& l, const float* in, int P, int h, int w, float* out);

@@ -40,6 +40,10 @@ struct TcParams {
   int nprod;         // 1 = plain bf16 product; 6 = exact fp32 emulation: operands are split into three bf16 planes
                      // (hi, mid, lo) and the six significant cross products are accumulated (tc forward conv)
   const float* bias;         // n_real entries added before the ReLU (forward conv), or null
+  // fused switch-driven unpool of the result (the conv's output feeds a pool layer's .down): out_bf16 is then the
+  // padded-flat tensor at the UNPOOLED size (up_h, up_w) and every output row is expanded into its 2x2 quad
+  const uint8_t* up_sw;      // switches (up_B, h, w, up_C) bytes, or null = plain store
+  int up_B, up_C, up_h, up_w;
   __nv_bfloat16* out_bf16;   // padded-flat (rows, n_pad), or null
   float* out_f32;            // compact (P,h,w,n_real), or null
 };
@@ -51,6 +55,63 @@ __host__ __device__ inline int tc_stage_bytes(int mode, int block_n) {
 }
 __host__ __device__ inline int tc_resident_bytes(int mode, int block_n, int k_blocks) {
   return mode == MODE_BAND_RES ? 9 * k_blocks * block_n * 128 : 0;
+}
+
+// Stores CHUNK bf16 values (packed pairs) of output row r, columns [col, col + CHUNK).  Plain: one row of the
+// padded-flat output.  With p.up_sw: the row is a POOLED pixel (item, y, x) whose values go to the position its
+// switch names inside the 2x2 quad of the unpooled output, zeros to the other three (DPooling.down fused into the
+// producing conv's epilogue: the pooled tensor is never written).  Pad rows of the pooled grid write the zero pad
+// row / column of the unpooled tensor.
+template <int CHUNK>
+__device__ __forceinline__ void store_bf16_chunk(const TcParams& p, const uint32_t (&packed)[CHUNK / 2], int r, bool is_pixel,
+                                                 int item, int y, int x, int col) {
+  if (!p.up_sw) {
+    uint4* dst = reinterpret_cast<uint4*>(p.out_bf16 + (size_t)r * p.n_pad + col);
+#pragma unroll
+    for (int i = 0; i < CHUNK / 8; ++i) dst[i] = make_uint4(packed[4 * i], packed[4 * i + 1], packed[4 * i + 2], packed[4 * i + 3]);
+    return;
+  }
+  uint32_t sidx[CHUNK / 4];                      // 4 switch bytes per word
+  if (is_pixel) {
+    const uint8_t* sp = p.up_sw + (((size_t)(item % p.up_B) * p.h + y) * p.w + x) * p.up_C + col;
+    if ((p.up_C & 15) == 0 && col + CHUNK <= p.up_C) {
+#pragma unroll
+      for (int i = 0; i < CHUNK / 16; ++i) {
+        const uint4 q = __ldg(reinterpret_cast<const uint4*>(sp) + i);
+        sidx[4 * i] = q.x; sidx[4 * i + 1] = q.y; sidx[4 * i + 2] = q.z; sidx[4 * i + 3] = q.w;
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < CHUNK / 4; ++i) {
+        uint32_t wd = 0xFFFFFFFFu;
+#pragma unroll
+        for (int b = 0; b < 4; ++b)
+          if (col + 4 * i + b < p.up_C) wd = (wd & ~(0xFFu << (8 * b))) | ((uint32_t)__ldg(sp + 4 * i + b) << (8 * b));
+        sidx[i] = wd;
+      }
+    }
+  }
+  const int owp = p.up_w + 1;
+  const size_t obase = (size_t)item * (p.up_h + 1) * owp;
+#pragma unroll
+  for (int qd = 0; qd < 4; ++qd) {
+    const int oy = 2 * y + (qd >> 1), ox = 2 * x + (qd & 1);
+    if (oy > p.up_h || ox > p.up_w) continue;
+    uint32_t o[CHUNK / 2];
+#pragma unroll
+    for (int i = 0; i < CHUNK / 2; ++i) {
+      uint32_t v = 0u;
+      if (is_pixel) {
+        const uint32_t s2 = sidx[i >> 1] >> (16 * (i & 1));          // switches of elements 2i, 2i+1
+        v = (((s2 & 0xFFu) == (uint32_t)qd) ? (packed[i] & 0xFFFFu) : 0u) |
+            ((((s2 >> 8) & 0xFFu) == (uint32_t)qd) ? (packed[i] & 0xFFFF0000u) : 0u);
+      }
+      o[i] = v;
+    }
+    uint4* dst = reinterpret_cast<uint4*>(p.out_bf16 + (obase + (size_t)oy * owp + ox) * p.n_pad + col);
+#pragma unroll
+    for (int i = 0; i < CHUNK / 8; ++i) dst[i] = make_uint4(o[4 * i], o[4 * i + 1], o[4 * i + 2], o[4 * i + 3]);
+  }
 }
 
 template <int BLOCK_N, int MODE>
@@ -271,10 +332,7 @@ deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
               __nv_bfloat162 h2 = __floats2bfloat162_rn(a, b);
               packed[i] = *reinterpret_cast<uint32_t*>(&h2);
             }
-            uint4* dst = reinterpret_cast<uint4*>(p.out_bf16 + (size_t)r * p.n_pad + n0 + c0);
-#pragma unroll
-            for (int i = 0; i < CHUNK / 8; ++i)
-              dst[i] = make_uint4(packed[4 * i], packed[4 * i + 1], packed[4 * i + 2], packed[4 * i + 3]);
+            store_bf16_chunk<CHUNK>(p, packed, r, is_pixel, r / rp, y, x, n0 + c0);
           }
         } else if (is_pixel) {
           const int item = r / rp;

@@ -261,10 +261,7 @@ deconv_tc2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
               __nv_bfloat162 h2 = __floats2bfloat162_rn(a, b);
               packed[i] = *reinterpret_cast<uint32_t*>(&h2);
             }
-            uint4* dst = reinterpret_cast<uint4*>(p.out_bf16 + (size_t)r * p.n_pad + n0 + c0);
-#pragma unroll
-            for (int i = 0; i < 4; ++i)
-              dst[i] = make_uint4(packed[4 * i], packed[4 * i + 1], packed[4 * i + 2], packed[4 * i + 3]);
+            store_bf16_chunk<32>(p, packed, r, is_pixel, r / rp, y, x, n0 + c0);
           }
         } else if (is_pixel) {
           const int item = r / rp;
