@@ -1,22 +1,20 @@
-// Tensor-core backward conv (a3 in SURVEY.md §8a): relu(conv3x3_same(x, flipT(W))) as an implicit GEMM
-// on tcgen05 with TMEM accumulators, operands staged by TMA — hand-written for sm_100a.
+// Tensor-core side of the library: padded-flat bf16 layout, weight packing, streaming helpers and the host
+// dispatch of the tcgen05 kernels (tc_kernel.cuh single CTA, tc_kernel2.cuh CTA pair, tc_last.cuh GEMM+col2im for the
+// 3-channel last layer, tc_dxg.cuh opt-in experiment) — hand-written for sm_100a.
 //
 // Layout ("padded-flat"): an activation of P items x (h,w) x C is stored as a 2-D bf16 matrix
 //   rows = P*(h+1)*(w+1), cols = C_pad (multiple of 64); pixel (p,y,x) is row p*(h+1)*(w+1)+y*(w+1)+x,
 // with one zero column (x == w) per image row and one zero row (y == h) per image.  In that layout the
 // input a 3x3 tap (dy,dx) needs for output row r is simply row r + dy*(w+1) + dx: the halo of a 'same'
 // convolution is the shared zero row/column, or an out-of-range row that TMA zero-fills.  So the A tile
-// of every (tap, 64-channel block) is ONE plain 2-D TMA box of 128 consecutive rows at a shifted row
+// of every (tap, 64-channel block) is ONE plain 2-D TMA box of consecutive rows at a shifted row
 // coordinate, landing in shared memory already in the 128-byte-swizzled K-major form UMMA reads.
 //   GEMM view:  M = padded rows, N = output channels, K = 9 taps x C_pad;
 //   A tile 128 x 64 (16 KB), B tile BLOCK_N x 64 from weights packed [tap][N_pad][K_pad] bf16.
 // Output rows at pad positions are garbage by construction and are written as zeros (bf16 output, so
-// the next layer's halo stays zero) or skipped (fp32 compact output of the last layer).
-//
-// One persistent CTA per SM, 6 warps: warp 0 = TMA producer, warp 1 = MMA issuer (one thread) and TMEM
-// owner, warps 2-5 = epilogue (TMEM -> registers -> ReLU/mask -> global).  Pipelines: smem ring
-// (full/empty mbarriers, 4-8 stages) and a 2-deep TMEM accumulator ring so the epilogue of tile i
-// overlaps the MMAs of tile i+1.
+// the next layer's halo stays zero) or skipped (fp32 compact output).
+// Used for: the backward projection chain (DCV_BF16), the fp32-accurate forward tape (three bf16 operand planes,
+// six products) and the DeepDream forward/backward (bf16 tape).
 #include "common.cuh"
 #include "internal.cuh"
 #include "tc_ptx.cuh"

@@ -118,8 +118,9 @@ template <int BLOCK_N, int MODE>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, TcParams p) {
   constexpr int B_TILE_BYTES = BLOCK_N * 128;
-  // K-split accumulators: consecutive MMAs into the SAME accumulator are a dependent chain (~90 cycles each for
-  // small N, measured), so the K steps of a tile rotate over KSPLIT accumulators that the epilogue adds up.
+  // K-split accumulators: the K steps of a tile rotate over KSPLIT TMEM accumulators that the epilogue adds up.
+  // Measured: no speed-up by itself (the ~85 cycles per small-N MMA are the shared-memory operand fetch, not a
+  // dependency chain), but the four accumulators are what keeps the split-operand forward conv fp32-accurate.
   constexpr int KSPLIT = BLOCK_N <= 64 ? 4 : (BLOCK_N == 128 ? 2 : 1);
   constexpr int ACC_COLS = BLOCK_N * KSPLIT;              // TMEM columns of one accumulator buffer
   constexpr int TMEM_COLS = (2 * ACC_COLS) < 32 ? 32 : (2 * ACC_COLS);

@@ -168,3 +168,33 @@ def test_wrapper_classes_mirror_reference(engine, golden):
     assert np.array_equal(a.up(x), np.maximum(x, 0)) and np.array_equal(a.down(-x), np.maximum(-x, 0))
     i = dd.DInput(layers.InputLayer((10, 10, 4)))
     assert i.up(x) is x and i.down(x) is x
+
+
+def test_error_paths(engine):
+    """Call-order and argument errors come back as negative status codes with a message, never as a crash."""
+    import ctypes
+    from deconv_api_b200 import engine as E, _native
+    e = E.Engine(0)
+    try:
+        lib = e.lib
+        feats = np.zeros(1, np.int32)
+        out = np.zeros((1, 1, 8, 8, 3), np.float32)
+        # project before any network / forward
+        assert lib.dcv_project(e.ctx, 0, feats.ctypes.data, 1, 0, 0, out.ctypes.data) < 0
+        W = np.zeros((3, 3, 3, 4), np.float32)
+        e.add_conv("c", W, None)
+        assert lib.dcv_project(e.ctx, 0, feats.ctypes.data, 1, 0, 0, out.ctypes.data) == -3      # DCV_ERR_STATE: no tape
+        assert b"dcv_forward" in lib.dcv_last_error(e.ctx)
+        e.forward(np.zeros((1, 8, 8, 3), np.float32), 0)
+        bad = np.array([7], np.int32)
+        assert lib.dcv_project(e.ctx, 0, bad.ctypes.data, 1, 0, 0, out.ctypes.data) == -1         # feature out of range
+        assert lib.dcv_project(e.ctx, 0, feats.ctypes.data, 1, 5, 0, out.ctypes.data) == -1       # illegal visualize mode
+        assert lib.dcv_project(e.ctx, 0, feats.ctypes.data, 1, 0, 9, out.ctypes.data) == -1       # unknown precision
+        assert lib.dcv_forward(e.ctx, None, 1, 8, 8, 0) == -1
+        assert lib.dcv_forward(e.ctx, out.ctypes.data, 1, 8, 8, 3) == -1                          # layer out of range
+        with pytest.raises(_native.DcvError):
+            e.forward(np.zeros((1, 8, 8, 5), np.float32), 0)                                      # wrong channel count
+        assert lib.dcv_set_forward_mode(e.ctx, 7) == -1
+        assert e.project(0, [0, 1]).shape == (2, 1, 8, 8, 3)
+    finally:
+        e.close()
