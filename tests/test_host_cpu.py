@@ -118,3 +118,25 @@ def test_gloo_world2_broadcast_and_sharding(tmp_path):
                          capture_output=True, text=True, timeout=300, env=env)
     assert out.returncode == 0, out.stdout + out.stderr
     assert "OK 58" in out.stdout
+
+
+def test_npz_weight_ingestion(tmp_path):
+    """weights exported from Keras as <layer>/kernel (HWIO) and <layer>/bias load into the model."""
+    src = vgg16.VGG16(weights=None, include_top=False, input_shape=(32, 32, 3), seed=5, bias=True)
+    arrays = {}
+    for l in src.layers:
+        if l.kind == "conv":
+            W, b = l.get_weights()
+            arrays[l.name + "/kernel"], arrays[l.name + "/bias"] = W, b
+    path = str(tmp_path / "vgg16_keras.npz")
+    np.savez(path, **arrays)
+    m = vgg16.VGG16(weights=path, include_top=False, input_shape=(32, 32, 3))
+    for a, b in zip(src.layers, m.layers):
+        for wa, wb in zip(a.get_weights(), b.get_weights()):
+            assert np.array_equal(wa, wb)
+    bad = dict(arrays)
+    bad["block1_conv1/kernel"] = np.zeros((64, 3, 3, 3), np.float32)      # OIHW (torch layout) must be refused
+    np.savez(path, **bad)
+    import pytest
+    with pytest.raises(ValueError):
+        vgg16.VGG16(weights=path, include_top=False, input_shape=(32, 32, 3))
