@@ -674,16 +674,15 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
     case MODE_BAND_RES: return launch_tc<BN, MODE_BAND_RES>(ctx, ta, tb, p); \
     default: return launch_tc<BN, MODE_TAP>(ctx, ta, tb, p);               \
   }
-  // Measured (round 1): the dx-grouped form needs a third of the A reads but its epilogue (3x the TMEM reads, 128
-  // shuffles per row pair, boundary exchange) is slower than the MMAs it saves: block1_conv2 4.4 ms vs 2.55 ms.
-  // Kept opt-in (DCV_TC_DXG=1) as the starting point for a shared-memory col2im epilogue.
-  static const int use_dxg = getenv("DCV_TC_DXG") ? atoi(getenv("DCV_TC_DXG")) : 0;
+  // Measured (round 1): block1_conv2 2.40 ms vs 2.55-2.9 ms, block2_conv1 0.90 vs 1.07 ms against the band + resident
+  // kernels — once the epilogue got 16 warps and per-warp overlapping A segments (no cross-warp exchange).
+  static const int use_dxg = getenv("DCV_TC_DXG") ? atoi(getenv("DCV_TC_DXG")) : 1;
   if (use_dxg && l.nprod == 1 && !l.up && out_bf16 && l.n_pad == 64 && (p.rows + DXG_ROWS_OUT - 1) / DXG_ROWS_OUT >= ctx->num_sms) {
     // 64 output channels: dx-grouped GEMM (tc_dxg.cuh), tiles of 126 rows
     TcParams q = p;
     q.m_tiles = (p.rows + DXG_ROWS_OUT - 1) / DXG_ROWS_OUT;
     q.n_tiles = 1;
-    const int xs_bytes = 2 * 2 * 4 * 3 * 32 * 4;
+    const int xs_bytes = 0;
     const int resident = dxg_resident_bytes(1, q.k_blocks) + 4 * A_TILE_BYTES + xs_bytes <= SMEM_BUDGET ? 1 : 0;
     const int res_bytes = dxg_resident_bytes(resident, q.k_blocks), stage_bytes = dxg_stage_bytes(resident);
     int stages = (SMEM_BUDGET - res_bytes - xs_bytes) / stage_bytes;
@@ -692,7 +691,7 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
       q.stages = stages;
       const int smem = res_bytes + stages * stage_bytes + xs_bytes + 1024 + 256;
       CUtensorMap ta2, tb2;
-      r = make_tmap(ctx, &ta2, in, (uint64_t)p.rows, (uint64_t)l.k_pad, BLOCK_M);
+      r = make_tmap(ctx, &ta2, in, (uint64_t)p.rows, (uint64_t)l.k_pad, 32);
       if (r) return r;
       r = make_tmap(ctx, &tb2, l.w, (uint64_t)9 * l.n_pad, (uint64_t)l.k_pad, DXG_N);
       if (r) return r;
@@ -705,8 +704,8 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
         smem_set[resident][ctx->device & 63] = smem;
       }
       const int grid = std::min(q.m_tiles, ctx->num_sms);
-      if (resident) deconv_dxg_kernel<1><<<grid, NUM_THREADS, smem, ctx->stream>>>(ta2, tb2, q);
-      else deconv_dxg_kernel<0><<<grid, NUM_THREADS, smem, ctx->stream>>>(ta2, tb2, q);
+      if (resident) deconv_dxg_kernel<1><<<grid, DXG_THREADS, smem, ctx->stream>>>(ta2, tb2, q);
+      else deconv_dxg_kernel<0><<<grid, DXG_THREADS, smem, ctx->stream>>>(ta2, tb2, q);
       ctx->launches++;
       e = cudaGetLastError();
       if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "deconv_dxg_kernel launch: %s", cudaGetErrorString(e));

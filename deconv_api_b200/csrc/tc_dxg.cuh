@@ -3,12 +3,14 @@
 // With N = 64 the kernels of tc_kernel.cuh are bound by fetching the UMMA operands from shared memory (~64 B/clk):
 // each of the 9 taps re-reads its own 128x64 A tile for only 64 output columns (32 % tensor-pipe utilisation,
 // profiles/r1_summary.md).  Here the three dx taps of one dy share ONE un-shifted A tile by being stacked along N:
-//   D[i][dx*64 + c] = sum_dy sum_k X[m0 - 1 + i + (dy-1)*(w+1)][k] * wd[dy*3+dx][k][c]        (N = 192, 3 x fewer A reads)
+//   D[i][dx*64 + c] = sum_dy sum_k X[row(i) + (dy-1)*(w+1)][k] * wd[dy*3+dx][k][c]            (N = 192, 3 x fewer A reads)
 // and the dx shift is applied to the RESULT instead of the operand:
-//   out[m0 + j][c] = D[j][c] + D[j+1][64 + c] + D[j+2][128 + c],     j = 0..125,
-// i.e. one and two TMEM lanes further down: warp shuffles, plus a 3-row exchange through shared memory at the warp
-// boundaries.  Tiles therefore advance by 126 rows.  The packed weights [tap][64][K_pad] already have the three dx
-// blocks of a dy contiguous (192 rows), so B is one TMA box per (dy, 64-channel block).
+//   out[row(j) + 1][c] = D[j][c] + D[j+1][64 + c] + D[j+2][128 + c]
+// i.e. one and two TMEM lanes further down = warp shuffles.  To keep every shuffle inside one warp (a warp can only
+// read its own 32 TMEM lanes) the 128-row A tile is built from FOUR 32-row TMA boxes that start 30 rows apart: warp k
+// owns input rows m0-1+30k .. m0+30k+30 and produces the 30 output rows m0+30k .. m0+30k+29.  No shared-memory
+// exchange, no barrier in the epilogue; a tile yields 120 output rows (94 % of the MMA rows).  The packed weights
+// [tap][64][K_pad] already have the three dx blocks of a dy contiguous (192 rows): B is one TMA box per (dy, k block).
 #pragma once
 #include "tc_kernel.cuh"
 
@@ -16,14 +18,17 @@ namespace dcv {
 namespace tc {
 
 constexpr int DXG_N = 192;
-constexpr int DXG_ROWS_OUT = 126;
+constexpr int DXG_ROWS_OUT = 120;             // 4 warps x 30 rows
+constexpr int DXG_SEG = 30;
+constexpr int DXG_EPI_WARPS = 16;              // 4 lane quarters x 4 column chunks of 16: one warp per SMSP would be latency-bound
+constexpr int DXG_THREADS = 64 + 32 * DXG_EPI_WARPS;
 constexpr int DXG_B_BYTES = DXG_N * 128;              // 24 KB per (dy, k block)
 
 __host__ __device__ inline int dxg_resident_bytes(int resident, int k_blocks) { return resident ? 3 * k_blocks * DXG_B_BYTES : 0; }
 __host__ __device__ inline int dxg_stage_bytes(int resident) { return A_TILE_BYTES + (resident ? 0 : DXG_B_BYTES); }
 
 template <int RESIDENT>
-__global__ void __launch_bounds__(NUM_THREADS, 1)
+__global__ void __launch_bounds__(DXG_THREADS, 1)
 deconv_dxg_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, TcParams p) {
   constexpr int TMEM_COLS = 512;                      // 2 accumulators x 192 columns
   constexpr int ACC_STRIDE = 256;
@@ -34,8 +39,7 @@ deconv_dxg_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   const int res_bytes = dxg_resident_bytes(RESIDENT, p.k_blocks);
   uint8_t* wres = smem;
   uint8_t* ring = smem + res_bytes;
-  float* xs = reinterpret_cast<float*>(ring + p.stages * stage_bytes);      // [2 tiles][2 chunks][4 warps][3][32]
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(xs + 2 * 2 * 4 * 3 * 32);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(ring + p.stages * stage_bytes);
   uint64_t* empty_bar = full_bar + MAX_STAGES;
   uint64_t* tfull_bar = empty_bar + MAX_STAGES;
   uint64_t* tempty_bar = tfull_bar + 2;
@@ -49,7 +53,7 @@ deconv_dxg_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     tma_prefetch_desc(&tmap_a);
     tma_prefetch_desc(&tmap_b);
     for (int s = 0; s < p.stages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-    for (int b = 0; b < 2; ++b) { mbar_init(&tfull_bar[b], 1); mbar_init(&tempty_bar[b], 4); }
+    for (int b = 0; b < 2; ++b) { mbar_init(&tfull_bar[b], 1); mbar_init(&tempty_bar[b], DXG_EPI_WARPS); }
     mbar_init(wres_bar, 1);
     fence_barrier_init();
   }
@@ -83,7 +87,9 @@ deconv_dxg_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* a_dst = ring + stage * stage_bytes;
           mbar_arrive_expect_tx(&full_bar[stage], (uint32_t)stage_bytes);
-          tma_load_2d(a_dst, &tmap_a, &full_bar[stage], kc * BLOCK_K, m0 - 1 + (dy - 1) * wp);
+#pragma unroll
+          for (int k = 0; k < 4; ++k)      // four 32-row segments, 30 rows apart (2 rows of overlap per warp boundary)
+            tma_load_2d(a_dst + k * 32 * 128, &tmap_a, &full_bar[stage], kc * BLOCK_K, m0 - 1 + DXG_SEG * k + (dy - 1) * wp);
           if constexpr (!RESIDENT) tma_load_2d(a_dst + A_TILE_BYTES, &tmap_b, &full_bar[stage], kc * BLOCK_K, dy * DXG_N);
           if (++stage == p.stages) { stage = 0; phase ^= 1; }
         }
@@ -123,7 +129,8 @@ deconv_dxg_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       }
     }
   } else {
-    const int lg = warp & 3;
+    const int lg = warp & 3;                                  // TMEM lane quarter this warp may read
+    const int c0 = ((warp - 2) >> 2) * 16;                    // its 16 output columns
     const int rp = (p.h + 1) * wp;
     int local = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++local) {
@@ -132,64 +139,38 @@ deconv_dxg_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       const uint32_t use = (uint32_t)(local >> 1);
       mbar_wait(&tfull_bar[buf], use & 1);
       tc_fence_after();
-      const int i = lg * 32 + lane;                           // D row of this thread = output row j
-      const int r = m0 + i;
+      const int r = m0 + DXG_SEG * lg + lane;                 // output row of this thread (lanes 30, 31: helpers only)
       const int q = r % rp;
       const int y = q / wp, x = q % wp;
-      const bool in_range = (i < DXG_ROWS_OUT) && (r < p.rows);
+      const bool in_range = (lane < DXG_SEG) && (r < p.rows);
       const bool is_pixel = in_range && (x < p.w) && (y < p.h);
       const uint32_t t_row = tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(buf * ACC_STRIDE);
-#pragma unroll 1
-      for (int ch = 0; ch < 2; ++ch) {
-        const int c0 = ch * 32;
-        uint32_t v0[32], v1[32], v2[32];
-        tmem_ld32(t_row + (uint32_t)c0, v0);
-        tmem_ld32(t_row + (uint32_t)(64 + c0), v1);
-        tmem_ld32(t_row + (uint32_t)(128 + c0), v2);
+      {
+        uint32_t v0[32], v1[32], v2[32];                      // 16 used
+        tmem_ld16(t_row + (uint32_t)c0, v0);
+        tmem_ld16(t_row + (uint32_t)(64 + c0), v1);
+        tmem_ld16(t_row + (uint32_t)(128 + c0), v2);
         tmem_ld_wait();
-        // rows this warp cannot reach by shuffle come from the next warp's lanes 0 and 1, through shared memory:
-        // slot layout [0..31] = v1 of lane 0, [32..63] = v2 of lane 0, [64..95] = v2 of lane 1
-        float* xw = xs + (((buf * 2 + ch) * 4 + lg) * 3) * 32;
-        if (lane < 2) {
+        uint32_t packed[8];
 #pragma unroll
-          for (int c = 0; c < 32; ++c) {
-            if (lane == 0) xw[c] = __uint_as_float(v1[c]);
-            xw[32 + lane * 32 + c] = __uint_as_float(v2[c]);
+        for (int c = 0; c < 16; c += 2) {
+          float s[2];
+#pragma unroll
+          for (int e = 0; e < 2; ++e) {
+            float t = __uint_as_float(v0[c + e]) + __shfl_down_sync(0xffffffffu, __uint_as_float(v1[c + e]), 1) +
+                      __shfl_down_sync(0xffffffffu, __uint_as_float(v2[c + e]), 2);
+            if (p.bias && c0 + c + e < p.n_real) t += __ldg(p.bias + c0 + c + e);
+            if (p.relu) t = fmaxf(t, 0.f);
+            if (!is_pixel) t = 0.f;
+            s[e] = t;
           }
-        }
-        asm volatile("bar.sync 1, 128;" ::: "memory");
-        float t[32];
-#pragma unroll
-        for (int c = 0; c < 32; ++c)       // branch-free for lanes 0..29 (lanes 30, 31 are redone below)
-          t[c] = __uint_as_float(v0[c]) + __shfl_down_sync(0xffffffffu, __uint_as_float(v1[c]), 1) +
-                 __shfl_down_sync(0xffffffffu, __uint_as_float(v2[c]), 2);
-        if (lane >= 30) {
-          const float* xn = xs + (((buf * 2 + ch) * 4 + ((lg + 1) & 3)) * 3) * 32;
-          const float* x2 = xn + (lane == 30 ? 32 : 64);
-#pragma unroll
-          for (int c = 0; c < 32; ++c) {
-            float a1 = __shfl_down_sync(0xC0000000u, __uint_as_float(v1[c]), 1);      // lane 30 <- lane 31
-            if (lane == 31) a1 = xn[c];
-            t[c] = __uint_as_float(v0[c]) + a1 + x2[c];
-          }
-        }
-        uint32_t packed[16];
-#pragma unroll
-        for (int c = 0; c < 32; c += 2) {
-          float s0 = t[c], s1 = t[c + 1];
-          if (p.bias) {
-            if (c0 + c < p.n_real) s0 += __ldg(p.bias + c0 + c);
-            if (c0 + c + 1 < p.n_real) s1 += __ldg(p.bias + c0 + c + 1);
-          }
-          if (p.relu) { s0 = fmaxf(s0, 0.f); s1 = fmaxf(s1, 0.f); }
-          if (!is_pixel) { s0 = 0.f; s1 = 0.f; }
-          __nv_bfloat162 h2 = __floats2bfloat162_rn(s0, s1);
+          __nv_bfloat162 h2 = __floats2bfloat162_rn(s[0], s[1]);
           packed[c / 2] = *reinterpret_cast<uint32_t*>(&h2);
         }
         if (in_range) {
           uint4* dst = reinterpret_cast<uint4*>(p.out_bf16 + (size_t)r * p.n_pad + c0);
-#pragma unroll
-          for (int k = 0; k < 4; ++k) dst[k] = make_uint4(packed[4 * k], packed[4 * k + 1], packed[4 * k + 2], packed[4 * k + 3]);
+          dst[0] = make_uint4(packed[0], packed[1], packed[2], packed[3]);
+          dst[1] = make_uint4(packed[4], packed[5], packed[6], packed[7]);
         }
       }
       tc_fence_before();

@@ -107,6 +107,7 @@ class Engine(object):
         self._ck(self.lib.dcv_net_clear(self.ctx))
         self.layer_names, self.index, self.kinds = [], {}, []
         self._net_owner = None
+        self._in_channels = None
 
     def add_conv(self, name, W, b, relu=True):
         W = _f32(W)
@@ -114,6 +115,8 @@ class Engine(object):
         cin, cout = W.shape[2], W.shape[3]
         b = _f32(b) if b is not None else np.zeros((cout,), np.float32)
         idx = self._ck(self.lib.dcv_net_add_conv(self.ctx, _ptr(W), _ptr(b), cin, cout, 1 if relu else 0))
+        if not any(k == "conv" for k in self.kinds):
+            self._in_channels = cin          # the C-ABI takes the input channel count from the first conv
         self._register(name, idx, "conv")
         return idx
 
@@ -148,6 +151,9 @@ class Engine(object):
     def forward(self, data, upto):
         data = _f32(data)
         assert data.ndim == 4, "data must be (B,H,W,C)"
+        want = getattr(self, "_in_channels", None)
+        if want is not None and data.shape[3] != want:
+            raise _native.DcvError(-1, "forward: the network expects %d input channels, data has %d" % (want, data.shape[3]))
         B, H, W, _ = data.shape
         self._ck(self.lib.dcv_forward(self.ctx, _ptr(data), B, H, W, int(upto)))
         self.input_shape = data.shape
