@@ -164,7 +164,8 @@ __global__ void pad_convert_kernel(const float* __restrict__ x, int P, int h, in
 // One thread = 8 channels of one 2x2 output quad; quads beyond the pooled grid are zero rows / columns.
 __global__ void __launch_bounds__(256)
 unpool_pad_kernel(const __nv_bfloat16* __restrict__ x, const uint8_t* __restrict__ sw, int P, int Bsw, int ph, int pw,
-                  int h, int w, int C, int c_pad, __nv_bfloat16* __restrict__ out) {
+                  int h, int w, int C, int c_pad, __nv_bfloat16* __restrict__ out,
+                  const __nv_bfloat16* __restrict__ prep_act, float prep_scale, int prep_relu) {
   const int iwp = pw + 1, irp = (ph + 1) * iwp;
   const int owp = w + 1, orp = (h + 1) * owp;
   const int qh = (h + 2) / 2, qw = (w + 2) / 2;          // quads covering y in [0,h], x in [0,w]
@@ -205,7 +206,24 @@ unpool_pad_kernel(const __nv_bfloat16* __restrict__ x, const uint8_t* __restrict
         const uint32_t hi = (sidx[2 * k + 1] == (uint32_t)qd) ? (vv[k] & 0xFFFF0000u) : 0u;
         o[k] = lo | hi;
       }
-      *reinterpret_cast<uint4*>(out + ((size_t)item * orp + y * owp + xx) * c_pad + g * 8) = make_uint4(o[0], o[1], o[2], o[3]);
+      const size_t oo = ((size_t)item * orp + y * owp + xx) * c_pad + g * 8;
+      if (prep_act && y < h && xx < w) {                  // gradient prep of the layer below (pad rows / columns stay zero)
+        const uint4 a4 = __ldg(reinterpret_cast<const uint4*>(prep_act + oo));
+        const uint32_t aw[4] = {a4.x, a4.y, a4.z, a4.w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const float a0 = __uint_as_float(aw[k] << 16), a1 = __uint_as_float(aw[k] & 0xFFFF0000u);
+          float v0 = fmaf(prep_scale, a0, __uint_as_float(o[k] << 16));
+          float v1 = fmaf(prep_scale, a1, __uint_as_float(o[k] & 0xFFFF0000u));
+          if (prep_relu) {
+            if (!(a0 > 0.f)) v0 = 0.f;
+            if (!(a1 > 0.f)) v1 = 0.f;
+          }
+          __nv_bfloat162 h2 = __floats2bfloat162_rn(v0, v1);
+          o[k] = *reinterpret_cast<uint32_t*>(&h2);
+        }
+      }
+      *reinterpret_cast<uint4*>(out + oo) = make_uint4(o[0], o[1], o[2], o[3]);
     }
   }
 }
@@ -438,6 +456,7 @@ struct TcConvArgs {
   const float* bias;
   int nprod = 1;            // 6: exact fp32 emulation (three operand planes, six products)
   const TcUnpool* up = nullptr;
+  const TcPrep* prep = nullptr;
 };
 
 static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& a, const __nv_bfloat16* in, int P, int h, int w,
@@ -496,12 +515,14 @@ int tc_rank1(dcv_ctx* ctx, const float* maps, const Layer& l, const int* feat, i
 }
 
 int tc_unpool(dcv_ctx* ctx, const __nv_bfloat16* x, const uint8_t* sw, int P, int Bsw, int ph, int pw, int h, int w,
-              int C, __nv_bfloat16* out) {
+              int C, __nv_bfloat16* out, const TcPrep* prep) {
   const int c_pad = tc_cpad(C);
   const size_t work = (size_t)P * ((h + 2) / 2) * ((w + 2) / 2) * (c_pad / 8);
   // algorithmic bytes in this layout: 2 B/elem read at pooled size + 1 B switch, 2 B/elem written at full size
   ProfScope ps(ctx, DCV_K_UNPOOL, 0.0, (double)P * ph * pw * C * (2.0 + 1.0 + 8.0));
-  unpool_pad_kernel<<<grid_for(work, 256), 256, 0, ctx->stream>>>(x, sw, P, Bsw, ph, pw, h, w, C, c_pad, out);
+  unpool_pad_kernel<<<grid_for(work, 256), 256, 0, ctx->stream>>>(x, sw, P, Bsw, ph, pw, h, w, C, c_pad, out,
+                                                                  prep ? prep->act : nullptr, prep ? prep->scale : 0.f,
+                                                                  prep ? prep->relu : 0);
   ctx->launches++;
   return 0;
 }
@@ -574,8 +595,9 @@ int tc_prepare_forward(dcv_ctx* ctx, Layer& l) {
 }
 
 int tc_conv(dcv_ctx* ctx, const Layer& l, const __nv_bfloat16* in, int P, int h, int w, __nv_bfloat16* out_bf16,
-            float* out_f32, int relu, const TcUnpool* up) {
+            float* out_f32, int relu, const TcUnpool* up, const TcPrep* prep) {
   if (up && !out_bf16) return ctx->fail(DCV_ERR_ARG, "tc_conv: fused unpool needs the bf16 output form");
+  if (prep && (!out_bf16 || up)) return ctx->fail(DCV_ERR_ARG, "tc_conv: fused gradient prep needs the plain bf16 output form");
   if (!l.tc.wd_bf16) return ctx->fail(DCV_ERR_STATE, "tensor-core weights were not prepared for this layer");
   static const int use_last = getenv("DCV_TC_LAST") ? atoi(getenv("DCV_TC_LAST")) : 1;
   if (out_f32 && l.tc.wall_bf16 && use_last) {
@@ -611,6 +633,7 @@ int tc_conv(dcv_ctx* ctx, const Layer& l, const __nv_bfloat16* in, int P, int h,
   }
   TcConvArgs a{l.tc.wd_bf16, l.tc.k_pad, l.tc.n_pad, l.cout, l.cin, relu < 0 ? l.relu : relu, nullptr};
   a.up = up;
+  a.prep = prep;
   return tc_conv_run(ctx, a, in, P, h, w, out_bf16, out_f32);
 }
 
@@ -632,6 +655,9 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
   p.bias = l.bias;
   p.nprod = l.nprod;
   p.nprod_planes = l.nprod == 6 ? 3 : 1;
+  p.prep_act = l.prep ? l.prep->act : nullptr;
+  p.prep_scale = l.prep ? l.prep->scale : 0.f;
+  p.prep_relu = l.prep ? l.prep->relu : 0;
   p.up_sw = l.up ? l.up->sw : nullptr;
   p.up_B = l.up ? l.up->B : 0; p.up_C = l.up ? l.up->C : 0; p.up_h = l.up ? l.up->h : 0; p.up_w = l.up ? l.up->w : 0;
   p.out_bf16 = out_bf16; p.out_f32 = out_f32;

@@ -336,8 +336,10 @@ int dream_backward_bf16(dcv_ctx* ctx, const LossSpec& ls, float** grad, double* 
   TRYD(ctx->dream[5].ensure(ctx, max_pad * sizeof(__nv_bfloat16)));
   TRYD(ctx->ws[0].ensure(ctx, (size_t)B * ctx->in_H * ctx->in_W * ctx->in_C * sizeof(float)));
   __nv_bfloat16* hb[2] = {(__nv_bfloat16*)ctx->dream[4].p, (__nv_bfloat16*)ctx->dream[5].p};
+  static const int fuse_prep = getenv("DCV_DREAM_FUSE_PREP") ? atoi(getenv("DCV_DREAM_FUSE_PREP")) : 1;
   int cur = 0;
   bool has_g = false;
+  bool prepped = false;              // hb[cur] already carries this layer's mask and loss seed (folded into its producer)
   double loss = 0.0;
   for (int j = ls.deepest; j >= 0; --j) {
     const Layer& l = ctx->net[j];
@@ -358,8 +360,20 @@ int dream_backward_bf16(dcv_ctx* ctx, const LossSpec& ls, float** grad, double* 
     const float scale = coeff != 0.f ? 2.f * coeff / (float)n : 0.f;
     if (!has_g && scale == 0.f) continue;
     const int prep_relu = l.kind == LK_CONV ? l.relu : 0;
-    if (scale != 0.f || prep_relu)     // a pool that is not a loss layer passes the gradient through unchanged
+    if (!prepped && (scale != 0.f || prep_relu))     // a pool that is not a loss layer passes the gradient through unchanged
       TRYD(tc_dream_prep(ctx, hb[cur], (const __nv_bfloat16*)l.act_h.p, elems, scale, has_g ? 1 : 0, prep_relu));
+    prepped = false;
+    // the same step for the layer below, folded into the kernel that produces its gradient
+    TcPrep below{nullptr, 0.f, 0};
+    const TcPrep* fold = nullptr;
+    if (fuse_prep && j > 0) {
+      const Layer& lo = ctx->net[j - 1];
+      const size_t n_lo = (size_t)lo.B * lo.H * lo.W * lo.C;
+      below.act = (const __nv_bfloat16*)lo.act_h.p;
+      below.scale = ls.coeff[j - 1] != 0.f ? 2.f * ls.coeff[j - 1] / (float)n_lo : 0.f;
+      below.relu = lo.kind == LK_CONV ? lo.relu : 0;
+      if (below.scale != 0.f || below.relu) fold = &below;
+    }
     if (l.kind == LK_CONV) {
       if (j == 0) {
         TRYD(tc_conv(ctx, l, hb[cur], l.B, l.H, l.W, nullptr, (float*)ctx->ws[0].p, 0));
@@ -372,12 +386,14 @@ int dream_backward_bf16(dcv_ctx* ctx, const LossSpec& ls, float** grad, double* 
         cur ^= 1;
         --j;
       } else {
-        TRYD(tc_conv(ctx, l, hb[cur], l.B, l.H, l.W, hb[cur ^ 1], nullptr, 0));
+        TRYD(tc_conv(ctx, l, hb[cur], l.B, l.H, l.W, hb[cur ^ 1], nullptr, 0, nullptr, fold));
         cur ^= 1;
+        prepped = fold != nullptr;
       }
     } else {
-      TRYD(tc_unpool(ctx, hb[cur], (const uint8_t*)l.sw.p, l.B, l.B, l.H, l.W, l.in_H, l.in_W, l.C, hb[cur ^ 1]));
+      TRYD(tc_unpool(ctx, hb[cur], (const uint8_t*)l.sw.p, l.B, l.B, l.H, l.W, l.in_H, l.in_W, l.C, hb[cur ^ 1], fold));
       cur ^= 1;
+      prepped = fold != nullptr;
     }
     has_g = true;
   }

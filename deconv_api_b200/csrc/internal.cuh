@@ -96,8 +96,11 @@ size_t tc_padded_elems(int h, int w, int c);         // bf16 elements of one pad
 int tc_pad_convert(dcv_ctx* ctx, const float* x, int P, int h, int w, int C, __nv_bfloat16* out);
 int tc_rank1(dcv_ctx* ctx, const float* maps, const Layer& l, const int* feat, int n, int B, int h, int w, __nv_bfloat16* out);
 // (ph,pw) pooled size, (h,w) unpooled size with h in {2ph, 2ph+1}
+// DeepDream gradient prep of the layer the result flows into, folded into the producing kernel:
+//   out = mask(act > 0 if relu) * (value + scale * act), act in the output's padded-flat layout
+struct TcPrep { const __nv_bfloat16* act; float scale; int relu; };
 int tc_unpool(dcv_ctx* ctx, const __nv_bfloat16* x, const uint8_t* sw, int P, int Bsw, int ph, int pw, int h, int w, int C,
-              __nv_bfloat16* out);
+              __nv_bfloat16* out, const TcPrep* prep = nullptr);
 int tc_pool(dcv_ctx* ctx, const __nv_bfloat16* x, int P, int h, int w, int C, __nv_bfloat16* out, uint8_t* sw);
 int tc_dream_prep(dcv_ctx* ctx, __nv_bfloat16* g, const __nv_bfloat16* act, size_t elems, float scale, int has_g, int relu);
 int tc_sumsq_partials(size_t elems);
@@ -112,7 +115,7 @@ int tc_conv_fwd_exact(dcv_ctx* ctx, const Layer& l, const float* in, int P, int 
 // then the padded-flat tensor at the unpooled size (up->h, up->w) and the pooled tensor is never written
 struct TcUnpool { const uint8_t* sw; int B, C, h, w; };
 int tc_conv(dcv_ctx* ctx, const Layer& l, const __nv_bfloat16* in, int P, int h, int w, __nv_bfloat16* out_bf16, float* out_f32,
-            int relu, const TcUnpool* up = nullptr);
+            int relu, const TcUnpool* up = nullptr, const TcPrep* prep = nullptr);
 // forward conv + bias + activation, bf16 padded-flat in and out
 int tc_conv_fwd(dcv_ctx* ctx, const Layer& l, const __nv_bfloat16* in, int P, int h, int w, __nv_bfloat16* out_bf16);
 int tc_deconv(dcv_ctx* ctx, const Layer& l, const float* in, int P, int h, int w, float* out);

@@ -152,6 +152,12 @@ deconv_dxg_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         tmem_ld16(t_row + (uint32_t)(128 + c0), v2);
         tmem_ld_wait();
         uint32_t packed[8];
+        uint32_t actw[8];
+        if (p.prep_act && in_range) {
+          const uint4* ap = reinterpret_cast<const uint4*>(p.prep_act + (size_t)r * p.n_pad + c0);
+          const uint4 t0 = __ldg(ap), t1 = __ldg(ap + 1);
+          actw[0] = t0.x; actw[1] = t0.y; actw[2] = t0.z; actw[3] = t0.w; actw[4] = t1.x; actw[5] = t1.y; actw[6] = t1.z; actw[7] = t1.w;
+        }
 #pragma unroll
         for (int c = 0; c < 16; c += 2) {
           float s[2];
@@ -161,9 +167,10 @@ deconv_dxg_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                       __shfl_down_sync(0xffffffffu, __uint_as_float(v2[c + e]), 2);
             if (p.bias && c0 + c + e < p.n_real) t += __ldg(p.bias + c0 + c + e);
             if (p.relu) t = fmaxf(t, 0.f);
-            if (!is_pixel) t = 0.f;
             s[e] = t;
           }
+          if (p.prep_act && in_range) prep_pair(p, actw[c / 2], s[0], s[1]);
+          if (!is_pixel) { s[0] = 0.f; s[1] = 0.f; }
           __nv_bfloat162 h2 = __floats2bfloat162_rn(s[0], s[1]);
           packed[c / 2] = *reinterpret_cast<uint32_t*>(&h2);
         }

@@ -42,6 +42,11 @@ struct TcParams {
   const float* bias;         // n_real entries added before the ReLU (forward conv), or null
   // fused switch-driven unpool of the result (the conv's output feeds a pool layer's .down): out_bf16 is then the
   // padded-flat tensor at the UNPOOLED size (up_h, up_w) and every output row is expanded into its 2x2 quad
+  // DeepDream backward: fold the NEXT layer's gradient prep into this epilogue (bf16 plain store only):
+  //   out = mask(act > 0) * (acc + prep_scale * act), act = that layer's bf16 tape in the output's layout
+  const __nv_bfloat16* prep_act;
+  float prep_scale;
+  int prep_relu;
   const uint8_t* up_sw;      // switches (up_B, h, w, up_C) bytes, or null = plain store
   int up_B, up_C, up_h, up_w;
   __nv_bfloat16* out_bf16;   // padded-flat (rows, n_pad), or null
@@ -62,6 +67,17 @@ __host__ __device__ inline int tc_resident_bytes(int mode, int block_n, int k_bl
 // switch names inside the 2x2 quad of the unpooled output, zeros to the other three (DPooling.down fused into the
 // producing conv's epilogue: the pooled tensor is never written).  Pad rows of the pooled grid write the zero pad
 // row / column of the unpooled tensor.
+// gradient prep on a pair of values; actbits = two bf16 activations of the layer the gradient is flowing into
+__device__ __forceinline__ void prep_pair(const TcParams& p, uint32_t actbits, float& a, float& b) {
+  const float a0 = __uint_as_float(actbits << 16), a1 = __uint_as_float(actbits & 0xFFFF0000u);
+  a = fmaf(p.prep_scale, a0, a);
+  b = fmaf(p.prep_scale, a1, b);
+  if (p.prep_relu) {
+    if (!(a0 > 0.f)) a = 0.f;
+    if (!(a1 > 0.f)) b = 0.f;
+  }
+}
+
 template <int CHUNK>
 __device__ __forceinline__ void store_bf16_chunk(const TcParams& p, const uint32_t (&packed)[CHUNK / 2], int r, bool is_pixel,
                                                  int item, int y, int x, int col) {
@@ -320,6 +336,15 @@ deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         if (p.out_bf16) {
           if (in_range) {
             uint32_t packed[CHUNK / 2];
+            uint32_t actw[CHUNK / 2];
+            if (p.prep_act) {
+              const uint4* ap = reinterpret_cast<const uint4*>(p.prep_act + (size_t)r * p.n_pad + n0 + c0);
+#pragma unroll
+              for (int i = 0; i < CHUNK / 8; ++i) {
+                const uint4 t = __ldg(ap + i);
+                actw[4 * i] = t.x; actw[4 * i + 1] = t.y; actw[4 * i + 2] = t.z; actw[4 * i + 3] = t.w;
+              }
+            }
 #pragma unroll
             for (int i = 0; i < CHUNK / 2; ++i) {
               float a = __uint_as_float(v[2 * i]), b = __uint_as_float(v[2 * i + 1]);
@@ -329,6 +354,7 @@ deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                 if (c + 1 < p.n_real) b += __ldg(p.bias + c + 1);
               }
               if (p.relu) { a = fmaxf(a, 0.f); b = fmaxf(b, 0.f); }
+              if (p.prep_act) prep_pair(p, actw[i], a, b);
               if (!is_pixel) { a = 0.f; b = 0.f; }
               __nv_bfloat162 h2 = __floats2bfloat162_rn(a, b);
               packed[i] = *reinterpret_cast<uint32_t*>(&h2);

@@ -248,6 +248,15 @@ deconv_tc2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         if (p.out_bf16) {
           if (in_range) {
             uint32_t packed[16];
+            uint32_t actw[16];
+            if (p.prep_act) {
+              const uint4* ap = reinterpret_cast<const uint4*>(p.prep_act + (size_t)r * p.n_pad + n0 + c0);
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                const uint4 t = __ldg(ap + i);
+                actw[4 * i] = t.x; actw[4 * i + 1] = t.y; actw[4 * i + 2] = t.z; actw[4 * i + 3] = t.w;
+              }
+            }
 #pragma unroll
             for (int i = 0; i < 16; ++i) {
               float a = __uint_as_float(v[2 * i]), b = __uint_as_float(v[2 * i + 1]);
@@ -257,6 +266,7 @@ deconv_tc2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                 if (c + 1 < p.n_real) b += __ldg(p.bias + c + 1);
               }
               if (p.relu) { a = fmaxf(a, 0.f); b = fmaxf(b, 0.f); }
+              if (p.prep_act) prep_pair(p, actw[i], a, b);
               if (!is_pixel) { a = 0.f; b = 0.f; }
               __nv_bfloat162 h2 = __floats2bfloat162_rn(a, b);
               packed[i] = *reinterpret_cast<uint32_t*>(&h2);
