@@ -15,7 +15,7 @@ LIBDIR = os.path.join(HERE, "_lib")
 LIB = os.path.join(LIBDIR, "libdcv.so")
 INCLUDE = os.path.join(os.path.dirname(HERE), "include")
 
-SOURCES = ["api.cu", "kernels_stream.cu", "conv_fp32.cu", "conv_tc.cu", "noalloc.cu", "dream.cu"]
+SOURCES = ["api.cu", "kernels_stream.cu", "conv_fp32.cu", "conv_tc.cu", "noalloc.cu", "dream.cu", "dev_ops.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden"]
 

@@ -736,7 +736,10 @@ extern "C" int dcv_deprocess_dev(dcv_ctx* ctx, const float* x_dev, size_t n, uin
   if (((uintptr_t)x_dev & 15) || ((uintptr_t)out_dev & 3)) return ctx->fail(DCV_ERR_ARG, "dcv_deprocess_dev: x must be 16-byte and out 4-byte aligned");
   const int np = deprocess_partials(n);
   TRY(ctx->scratch.ensure(ctx, (size_t)np * 2 * sizeof(double)));
-  launch_deprocess(x_dev, n, (double*)ctx->scratch.p, np, out_dev, nullptr, ctx->stream); ctx->launches += 2;
+  {
+    ProfScope ps(ctx, DCV_K_OTHER, 0.0, 9.0 * n);      // two reads of x + one byte written
+    launch_deprocess(x_dev, n, (double*)ctx->scratch.p, np, out_dev, nullptr, ctx->stream); ctx->launches += 2;
+  }
   CHECK_LAUNCH(ctx);
   return 0;
 }

@@ -13,6 +13,27 @@ namespace dcv {
 
 constexpr int kNumSMs = 148;   // B200: 2 dies x 74 SMs; grids are sized in multiples of this
 
+#ifdef __CUDACC__
+// Sum of the fp64 (sum, sum of squares) block partials written by deprocess_stats_kernel, by all 256 threads of the
+// calling block in a fixed order (strided per-thread sums, then a shuffle / shared-memory tree): every block and
+// every run gets the same bits.  Result valid in all threads after the call.
+__device__ __forceinline__ void block_sum_partials(const double* __restrict__ partial, int np, double& ts, double& tq) {
+  __shared__ double ps_s[8], ps_q[8];
+  double s = 0.0, q = 0.0;
+  for (int k = threadIdx.x; k < np; k += blockDim.x) { s += partial[2 * k]; q += partial[2 * k + 1]; }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    s += __shfl_xor_sync(0xffffffffu, s, o);
+    q += __shfl_xor_sync(0xffffffffu, q, o);
+  }
+  if ((threadIdx.x & 31) == 0) { ps_s[threadIdx.x >> 5] = s; ps_q[threadIdx.x >> 5] = q; }
+  __syncthreads();
+  ts = 0.0; tq = 0.0;
+  const int nw = (blockDim.x + 31) >> 5;
+  for (int k = 0; k < nw; ++k) { ts += ps_s[k]; tq += ps_q[k]; }
+}
+#endif
+
 // ---- epilogue of the conv kernels -------------------------------------------------------------
 struct ConvEpilogue {
   const float* bias = nullptr;      // per output channel, may be null (backward pass: zero bias)

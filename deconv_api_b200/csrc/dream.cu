@@ -57,25 +57,91 @@ resize_bilinear_kernel(const float* __restrict__ x, int H, int W, int C, int OH,
   }
 }
 
-// generic channel count: one thread per output element of the row
+// Strip form used for every shape (profiles/ub_stream.cu compares the candidates).  A block of 256 threads owns
+// RESIZE_U * 256 consecutive elements f = ox*C + c of the flat output row and walks RESIZE_STRIP output rows:
+//  * the x coordinates / weights of a thread's elements are computed once, the y coordinates of the strip once per
+//    block (shared memory) - the per-element coordinate arithmetic, not memory, bounded the one-thread-per-pixel form;
+//  * the horizontally interpolated values of the two source rows stay in registers and are re-used while the
+//    source rows do not change (an enlargement by 1.4 touches 0.71 new source rows per output row; the branches are
+//    warp-uniform), so ~1.4 loads + 1 store per output element instead of 4 + 1, all warp-coalesced.
+// The arithmetic is the same expression in the same order as the per-pixel form above.
+constexpr int RESIZE_STRIP = 16;
+constexpr int RESIZE_U = 3;
 __global__ void __launch_bounds__(256)
-resize_bilinear_rowc_kernel(const float* __restrict__ x, int H, int W, int C, int OH, int OW, float* __restrict__ out) {
-  const int oy = blockIdx.y % OH, b = blockIdx.y / OH;
-  const float sh = (float)H / (float)OH, sw = (float)W / (float)OW;
-  float fy = sh * ((float)oy + 0.5f) - 0.5f; if (fy < 0.f) fy = 0.f;
-  int y0 = (int)fy; if (y0 > H - 1) y0 = H - 1;
-  const int y1 = y0 + (y0 < H - 1 ? 1 : 0);
-  const float ly = fy - (float)y0, hy = 1.f - ly;
-  const float* r0 = x + ((size_t)b * H + y0) * W * C;
-  const float* r1 = x + ((size_t)b * H + y1) * W * C;
-  float* o = out + ((size_t)b * OH + oy) * OW * C;
-  for (int f = blockIdx.x * blockDim.x + threadIdx.x; f < OW * C; f += gridDim.x * blockDim.x) {
-    const int ox = f / C, c = f % C;
+resize_bilinear_strip_kernel(const float* __restrict__ x, int H, int W, int C, int OH, int OW, float* __restrict__ out) {
+  __shared__ int sy0[RESIZE_STRIP], sy1[RESIZE_STRIP];
+  __shared__ float sly[RESIZE_STRIP];
+  const int strips = (OH + RESIZE_STRIP - 1) / RESIZE_STRIP;
+  const int b = blockIdx.y / strips, oy_begin = (blockIdx.y % strips) * RESIZE_STRIP;
+  const int rows = min(RESIZE_STRIP, OH - oy_begin);
+  if (threadIdx.x < RESIZE_STRIP) {
+    const int oy = min(oy_begin + (int)threadIdx.x, OH - 1);
+    const float sh = (float)H / (float)OH;
+    float fy = sh * ((float)oy + 0.5f) - 0.5f; if (fy < 0.f) fy = 0.f;
+    int y0 = (int)fy; if (y0 > H - 1) y0 = H - 1;
+    sy0[threadIdx.x] = y0;
+    sy1[threadIdx.x] = y0 + (y0 < H - 1 ? 1 : 0);
+    sly[threadIdx.x] = fy - (float)y0;
+  }
+  const int n = OW * C;
+  const int f0 = blockIdx.x * 256 * RESIZE_U + threadIdx.x;
+  const float sw = (float)W / (float)OW;
+  int i0[RESIZE_U], i1[RESIZE_U];
+  float lx[RESIZE_U];
+#pragma unroll
+  for (int k = 0; k < RESIZE_U; ++k) {
+    const int f = min(f0 + k * 256, n - 1);
+    const int ox = f / C, c = f - ox * C;
     float fx = sw * ((float)ox + 0.5f) - 0.5f; if (fx < 0.f) fx = 0.f;
     int x0 = (int)fx; if (x0 > W - 1) x0 = W - 1;
     const int x1 = x0 + (x0 < W - 1 ? 1 : 0);
-    const float lx = fx - (float)x0, hx = 1.f - lx;
-    o[f] = hy * (hx * __ldg(r0 + x0 * C + c) + lx * __ldg(r0 + x1 * C + c)) + ly * (hx * __ldg(r1 + x0 * C + c) + lx * __ldg(r1 + x1 * C + c));
+    lx[k] = fx - (float)x0;
+    i0[k] = x0 * C + c; i1[k] = x1 * C + c;
+  }
+  __syncthreads();
+  const float* img = x + (size_t)b * H * W * C;
+  const size_t wc = (size_t)W * C;
+  float* o = out + ((size_t)b * OH + oy_begin) * n;
+  int cy0 = -1, cy1 = -1;                       // source rows whose horizontal interpolation is held in h0 / h1
+  float h0[RESIZE_U], h1[RESIZE_U];
+  for (int r = 0; r < rows; ++r, o += n) {
+    const int y0 = sy0[r], y1 = sy1[r];
+    const float ly = sly[r], hy = 1.f - ly;
+    float n0[RESIZE_U], n1[RESIZE_U];
+    if (y0 == cy0) {
+#pragma unroll
+      for (int k = 0; k < RESIZE_U; ++k) n0[k] = h0[k];
+    } else if (y0 == cy1) {
+#pragma unroll
+      for (int k = 0; k < RESIZE_U; ++k) n0[k] = h1[k];
+    } else {
+      const float* rp = img + (size_t)y0 * wc;
+      float a[RESIZE_U], bb[RESIZE_U];
+#pragma unroll
+      for (int k = 0; k < RESIZE_U; ++k) { a[k] = __ldg(rp + i0[k]); bb[k] = __ldg(rp + i1[k]); }
+#pragma unroll
+      for (int k = 0; k < RESIZE_U; ++k) n0[k] = (1.f - lx[k]) * a[k] + lx[k] * bb[k];
+    }
+    if (y1 == y0) {
+#pragma unroll
+      for (int k = 0; k < RESIZE_U; ++k) n1[k] = n0[k];
+    } else if (y1 == cy1) {
+#pragma unroll
+      for (int k = 0; k < RESIZE_U; ++k) n1[k] = h1[k];
+    } else {
+      const float* rp = img + (size_t)y1 * wc;
+      float a[RESIZE_U], bb[RESIZE_U];
+#pragma unroll
+      for (int k = 0; k < RESIZE_U; ++k) { a[k] = __ldg(rp + i0[k]); bb[k] = __ldg(rp + i1[k]); }
+#pragma unroll
+      for (int k = 0; k < RESIZE_U; ++k) n1[k] = (1.f - lx[k]) * a[k] + lx[k] * bb[k];
+    }
+#pragma unroll
+    for (int k = 0; k < RESIZE_U; ++k) { h0[k] = n0[k]; h1[k] = n1[k]; }
+    cy0 = y0; cy1 = y1;
+#pragma unroll
+    for (int k = 0; k < RESIZE_U; ++k)
+      if (f0 + k * 256 < n) o[f0 + k * 256] = hy * h0[k] + ly * h1[k];
   }
 }
 
@@ -94,23 +160,24 @@ roll_kernel(const float* __restrict__ x, int B, int H, int W, int C, int oy, int
   const int wc = W * C, shift = sx * C;                  // out[f] = in[(f - shift) mod wc]
   const float* src = x + ((size_t)b * H + sy) * wc;
   float* dst = out + ((size_t)b * H + y) * wc;
-  if ((wc & 3) == 0) {
-    // 16-byte stores (rows start 16-byte aligned when W*C is a multiple of 4); the rotated source is read with four
-    // scalar loads that coalesce across the warp
-    for (int f = (blockIdx.x * blockDim.x + threadIdx.x) * 4; f < wc; f += gridDim.x * blockDim.x * 4) {
-      float v[4];
+  // 4-byte accesses that coalesce to full 128-byte lines on both sides (the rotation breaks 16-byte alignment of one
+  // side for most shifts); eight independent elements per thread keep enough loads in flight.  Measured against the
+  // 16-byte-store, shared-memory and shuffle forms in profiles/ub_stream.cu: this one matches a device-to-device copy.
+  const int tstride = gridDim.x * blockDim.x;
+  int f = blockIdx.x * blockDim.x + threadIdx.x;
+  for (; f + 7 * tstride < wc; f += 8 * tstride) {
+    float v[8];
 #pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        int g = f + k - shift; if (g < 0) g += wc;
-        v[k] = __ldg(src + g);
-      }
-      *reinterpret_cast<float4*>(dst + f) = make_float4(v[0], v[1], v[2], v[3]);
+    for (int k = 0; k < 8; ++k) {
+      int g = f + k * tstride - shift; if (g < 0) g += wc;
+      v[k] = __ldg(src + g);
     }
-  } else {
-    for (int f = blockIdx.x * blockDim.x + threadIdx.x; f < wc; f += gridDim.x * blockDim.x) {
-      int g = f - shift; if (g < 0) g += wc;
-      dst[f] = __ldg(src + g);
-    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) dst[f + k * tstride] = v[k];
+  }
+  for (; f < wc; f += tstride) {
+    int g = f - shift; if (g < 0) g += wc;
+    dst[f] = __ldg(src + g);
   }
 }
 
@@ -129,16 +196,11 @@ __global__ void __launch_bounds__(256)
 dream_update_kernel(float* __restrict__ img, const float* __restrict__ g, const double* __restrict__ partial, int np,
                     int H, int W, int C, float step, int oy, int ox, const int* __restrict__ jit) {
   if (jit) { const int c = jit[0]; oy = jit[1 + 2 * c]; ox = jit[2 + 2 * c]; }
-  __shared__ float s_scale;
   const size_t n = (size_t)H * W * C;
-  if (threadIdx.x == 0) {
-    double q = 0.0;
-    for (int k = 0; k < np; ++k) q += partial[2 * k + 1];
-    const float rms = (float)sqrt(q / (double)n);
-    s_scale = step / fmaxf(rms, 1e-7f);
-  }
-  __syncthreads();
-  const float sc = s_scale;
+  double ts, tq;
+  block_sum_partials(partial, np, ts, tq);
+  const float rms = (float)sqrt(tq / (double)n);
+  const float sc = step / fmaxf(rms, 1e-7f);
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
     const int c = (int)(i % C);
     size_t p = i / C;
@@ -161,17 +223,19 @@ __global__ void add_diff_kernel(float* __restrict__ img, const float* __restrict
 
 void launch_resize_bilinear(const float* x, int B, int H, int W, int C, int OH, int OW, float* out, cudaStream_t s) {
   if ((size_t)B * OH * OW * C == 0) return;
+  static const int per_pixel = getenv("DCV_RESIZE_PIXEL") ? atoi(getenv("DCV_RESIZE_PIXEL")) : 0;
+  const int strips = (OH + RESIZE_STRIP - 1) / RESIZE_STRIP;
   int b0 = 0;
-  while (b0 < B) {                                   // gridDim.y <= 65535 output rows per launch
-    const int nb = std::min(B - b0, std::max(1, 65535 / OH));
+  while (b0 < B) {                                   // gridDim.y <= 65535 per launch
+    const int nb = std::min(B - b0, std::max(1, 65535 / (per_pixel ? OH : strips)));
     const float* xi = x + (size_t)b0 * H * W * C;
     float* oi = out + (size_t)b0 * OH * OW * C;
-    if (C <= 4) {
+    if (per_pixel && C <= 4) {
       dim3 grid((OW + 255) / 256, nb * OH);
       resize_bilinear_kernel<4><<<grid, 256, 0, s>>>(xi, H, W, C, OH, OW, oi);
     } else {
-      dim3 grid(std::min((OW * C + 255) / 256, 64), nb * OH);
-      resize_bilinear_rowc_kernel<<<grid, 256, 0, s>>>(xi, H, W, C, OH, OW, oi);
+      dim3 grid((OW * C + 256 * RESIZE_U - 1) / (256 * RESIZE_U), nb * strips);
+      resize_bilinear_strip_kernel<<<grid, 256, 0, s>>>(xi, H, W, C, OH, OW, oi);
     }
     b0 += nb;
   }
@@ -182,7 +246,7 @@ static void launch_roll_impl(const float* x, int B, int H, int W, int C, int oy,
   int b0 = 0;
   while (b0 < B) {
     const int nb = std::min(B - b0, std::max(1, 65535 / H));
-    dim3 grid(std::min((W * C / 4 + 255) / 256 + 1, 64), nb * H);
+    dim3 grid(std::max(1, std::min(W * C / 2048, 16)), nb * H);
     roll_kernel<<<grid, 256, 0, s>>>(x + (size_t)b0 * H * W * C, nb, H, W, C, oy, ox, jit, out + (size_t)b0 * H * W * C);
     b0 += nb;
   }

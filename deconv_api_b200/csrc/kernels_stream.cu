@@ -275,19 +275,13 @@ __device__ __forceinline__ uint8_t deprocess_one(float v, float mean, float deno
 __global__ void __launch_bounds__(256) deprocess_map_kernel(const float* __restrict__ x, size_t n,
                                                             const double* __restrict__ partial, int npartial,
                                                             uint8_t* __restrict__ out, float* __restrict__ norm) {
-  __shared__ float sh[2];
-  if (threadIdx.x == 0) {
-    double ts = 0.0, tq = 0.0;
-    for (int k = 0; k < npartial; ++k) { ts += partial[2 * k]; tq += partial[2 * k + 1]; }
-    const double mean = ts / (double)n;
-    double var = tq / (double)n - mean * mean;      // population variance (ddof = 0)
-    if (var < 0.0) var = 0.0;
-    // std of the CENTRED data equals std of x; the reference adds K.epsilon() = 1e-7 to it
-    sh[0] = (float)mean;
-    sh[1] = (float)(sqrt(var) + 1e-7);
-  }
-  __syncthreads();
-  const float mean = sh[0], denom = sh[1];
+  double ts, tq;
+  block_sum_partials(partial, npartial, ts, tq);
+  const double dmean = ts / (double)n;
+  double var = tq / (double)n - dmean * dmean;      // population variance (ddof = 0)
+  if (var < 0.0) var = 0.0;
+  // std of the CENTRED data equals std of x; the reference adds K.epsilon() = 1e-7 to it
+  const float mean = (float)dmean, denom = (float)(sqrt(var) + 1e-7);
   const size_t n4 = n / 4;
   const float4* x4 = reinterpret_cast<const float4*>(x);
 #pragma unroll 4

@@ -306,6 +306,26 @@ class Engine(object):
         self._ck(self.lib.dcv_roll(self.ctx, _ptr(x), B, H, W, C, int(oy), int(ox), _ptr(out)))
         return out
 
+    # -- device-resident forms (raw device pointers, e.g. torch.Tensor.data_ptr(); asynchronous on the context stream)
+    def maxpool_switch_dev(self, x_ptr, shape, pooled_ptr, sw_ptr):
+        B, H, W, C = (int(v) for v in shape)
+        self._ck(self.lib.dcv_maxpool_switch_dev(self.ctx, ctypes.c_void_p(x_ptr), B, H, W, C, ctypes.c_void_p(pooled_ptr),
+                                                 ctypes.c_void_p(sw_ptr)))
+
+    def unpool_switch_dev(self, x_ptr, sw_ptr, out_shape, out_ptr):
+        B, H, W, C = (int(v) for v in out_shape)
+        self._ck(self.lib.dcv_unpool_switch_dev(self.ctx, ctypes.c_void_p(x_ptr), ctypes.c_void_p(sw_ptr), B, H, W, C,
+                                                ctypes.c_void_p(out_ptr)))
+
+    def resize_bilinear_dev(self, x_ptr, shape, out_hw, out_ptr):
+        B, H, W, C = (int(v) for v in shape)
+        self._ck(self.lib.dcv_resize_bilinear_dev(self.ctx, ctypes.c_void_p(x_ptr), B, H, W, C, int(out_hw[0]), int(out_hw[1]),
+                                                  ctypes.c_void_p(out_ptr)))
+
+    def roll_dev(self, x_ptr, shape, oy, ox, out_ptr):
+        B, H, W, C = (int(v) for v in shape)
+        self._ck(self.lib.dcv_roll_dev(self.ctx, ctypes.c_void_p(x_ptr), B, H, W, C, int(oy), int(ox), ctypes.c_void_p(out_ptr)))
+
     def dream_gradient(self, img, loss_layers, coeffs, precision="fp32"):
         """-> (dloss/dimg (B,H,W,C) float32, loss float)"""
         img = _f32(img)

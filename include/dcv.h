@@ -216,6 +216,15 @@ DCV_API int dcv_resize_bilinear(dcv_ctx* ctx, const float* x, int B, int H, int 
 /* numpy.roll over the two spatial axes by (oy, ox): the jitter. */
 DCV_API int dcv_roll(dcv_ctx* ctx, const float* x, int B, int H, int W, int C, int oy, int ox, float* out);
 
+/* ---- device-resident forms of the streaming operators above: x_dev / out_dev / sw_dev are device pointers owned
+ * by the caller (16-byte aligned for pool / unpool), nothing is copied or allocated, and the call is asynchronous
+ * on the context's stream (dcv_sync to wait).  Same arithmetic as the host-buffer forms; for pipelines that keep
+ * their images on the GPU between DPooling.up / DPooling.down (deepdream.py:129-150) or DeepDream steps. --- */
+DCV_API int dcv_maxpool_switch_dev(dcv_ctx* ctx, const float* x_dev, int B, int H, int W, int C, float* pooled_dev, uint8_t* sw_dev);
+DCV_API int dcv_unpool_switch_dev(dcv_ctx* ctx, const float* x_dev, const uint8_t* sw_dev, int B, int H, int W, int C, float* out_dev);
+DCV_API int dcv_resize_bilinear_dev(dcv_ctx* ctx, const float* x_dev, int B, int H, int W, int C, int OH, int OW, float* out_dev);
+DCV_API int dcv_roll_dev(dcv_ctx* ctx, const float* x_dev, int B, int H, int W, int C, int oy, int ox, float* out_dev);
+
 #ifdef __cplusplus
 }
 #endif

@@ -198,3 +198,52 @@ def test_error_paths(engine):
         assert e.project(0, [0, 1]).shape == (2, 1, 8, 8, 3)
     finally:
         e.close()
+
+
+@pytest.mark.gpu
+def test_device_resident_ops_match_host_forms(engine):
+    """dcv_*_dev entry points (caller-owned device buffers) give the same bits as the host-buffer forms, which
+    are the ones checked against the oracle above; resize also at shapes that exercise every branch of the strip
+    kernel (enlarging, shrinking, identity, ragged last strip / last block)."""
+    import torch
+    from oracle import dream_oracle as do
+    rng = np.random.default_rng(5)
+    dev = torch.device("cuda:0")
+    x = np.maximum(rng.normal(0, 1, (3, 10, 12, 24)), 0).astype(np.float32)
+    x[0, :2, :2, :] = 0.0                                   # all-equal patches: switch (0,0)
+    pooled, sw = engine.maxpool_switch(x)
+    xd = torch.from_numpy(x).to(dev)
+    pd = torch.empty((3, 5, 6, 24), device=dev)
+    sd = torch.empty((3, 5, 6, 24), device=dev, dtype=torch.uint8)
+    torch.cuda.synchronize()
+    engine.maxpool_switch_dev(xd.data_ptr(), x.shape, pd.data_ptr(), sd.data_ptr())
+    engine.sync()
+    assert np.array_equal(pd.cpu().numpy(), pooled) and np.array_equal(sd.cpu().numpy(), sw)
+    ud = torch.empty_like(xd)
+    engine.unpool_switch_dev(pd.data_ptr(), sd.data_ptr(), x.shape, ud.data_ptr())
+    engine.sync()
+    assert np.array_equal(ud.cpu().numpy(), engine.unpool_switch(pooled, sw))
+    with pytest.raises(Exception):
+        engine.unpool_switch_dev(pd.data_ptr(), sd.data_ptr(), (3, 9, 12, 24), ud.data_ptr())     # odd output size
+
+    for (h, w, c), (oh, ow) in (((37, 53, 3), (61, 44)), ((64, 64, 3), (45, 45)), ((100, 90, 3), (140, 126)),
+                                ((20, 30, 5), (20, 30)), ((9, 7, 1), (33, 300)), ((300, 260, 3), (17, 19))):
+        img = rng.normal(0, 50, (2, h, w, c)).astype(np.float32)
+        idv = torch.from_numpy(img).to(dev)
+        od = torch.empty((2, oh, ow, c), device=dev)
+        torch.cuda.synchronize()
+        engine.resize_bilinear_dev(idv.data_ptr(), img.shape, (oh, ow), od.data_ptr())
+        engine.sync()
+        got = od.cpu().numpy()
+        assert np.array_equal(got, engine.resize_bilinear(img, (oh, ow)))
+        assert rel_l2(got, do.resize(img, (oh, ow))) < 1e-6
+    img = rng.normal(0, 1, (2, 33, 700, 3)).astype(np.float32)       # 2100 floats per row: unrolled body + tail
+    idv = torch.from_numpy(img).to(dev)
+    od = torch.empty_like(idv)
+    torch.cuda.synchronize()
+    for oy, ox in ((0, 0), (5, -7), (-32, 32), (33, 700), (40, -1401)):
+        engine.roll_dev(idv.data_ptr(), img.shape, oy, ox, od.data_ptr())
+        engine.sync()
+        assert np.array_equal(od.cpu().numpy(), np.roll(img, (oy, ox), axis=(1, 2)))
+    with pytest.raises(Exception):
+        engine.roll_dev(idv.data_ptr(), img.shape, 1, 1, idv.data_ptr())                          # in place
