@@ -22,6 +22,7 @@
 #include "tc_last.cuh"
 #include "tc_kernel2.cuh"
 #include "tc_dxg.cuh"
+#include "tc_exact.cuh"
 
 #include <algorithm>
 #include <cstdlib>
@@ -457,6 +458,7 @@ struct TcConvArgs {
   int nprod = 1;            // 6: exact fp32 emulation (three operand planes, six products)
   const TcUnpool* up = nullptr;
   const TcPrep* prep = nullptr;
+  int prof_class = -1;      // profiling class override (default: conv_fwd for nprod 6, conv_tc otherwise)
 };
 
 static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& a, const __nv_bfloat16* in, int P, int h, int w,
@@ -491,7 +493,8 @@ void tc_free_layer(Layer& l) {
   if (l.tc.wf_bf16) cudaFree(l.tc.wf_bf16);
   if (l.tc.wall_bf16) cudaFree(l.tc.wall_bf16);
   if (l.tc.wf3_bf16) cudaFree(l.tc.wf3_bf16);
-  l.tc.wd_bf16 = l.tc.wf_bf16 = l.tc.wall_bf16 = l.tc.wf3_bf16 = nullptr;
+  if (l.tc.wd3_bf16) cudaFree(l.tc.wd3_bf16);
+  l.tc.wd_bf16 = l.tc.wf_bf16 = l.tc.wall_bf16 = l.tc.wf3_bf16 = l.tc.wd3_bf16 = nullptr;
 }
 
 int tc_pad_convert(dcv_ctx* ctx, const float* x, int P, int h, int w, int C, __nv_bfloat16* out) {
@@ -581,6 +584,39 @@ int tc_conv_fwd_exact(dcv_ctx* ctx, const Layer& l, const float* in, int P, int 
   return tc_conv_run(ctx, a, (const __nv_bfloat16*)ctx->ws[4].p, P, h, w, nullptr, out);
 }
 
+size_t tc_split_elems(int h, int w, int c) { return (size_t)(h + 1) * (w + 1) * 3 * tc_cpad(c); }
+
+// Backward conv of the fp32 projection mode on the tensor cores, same six-product scheme.  l.wd is the flipped,
+// transposed fp32 kernel [9][cout][cin] = [tap][K][N], i.e. the layout pack_weights_fwd3_kernel expects.
+int tc_prepare_backward_exact(dcv_ctx* ctx, Layer& l) {
+  if (l.tc.wd3_bf16) return 0;
+  if (!l.wd) return ctx->fail(DCV_ERR_STATE, "backward weights were not prepared for this layer");
+  const int k_pad = tc_cpad(l.cout), n_pad = tc_cpad(l.cin);
+  const size_t n = (size_t)9 * 3 * n_pad * k_pad;
+  cudaError_t e = cudaMalloc(&l.tc.wd3_bf16, n * sizeof(__nv_bfloat16));
+  if (e != cudaSuccess) return ctx->fail(DCV_ERR_NOMEM, "cudaMalloc(split backward weights): %s", cudaGetErrorString(e));
+  pack_weights_fwd3_kernel<<<grid_for(n / 3, 256), 256, 0, ctx->stream>>>(l.wd, l.cout, l.cin, k_pad, n_pad, l.tc.wd3_bf16);
+  ctx->launches++;
+  return 0;
+}
+
+int tc_conv_bwd_exact(dcv_ctx* ctx, const Layer& l, const float* in, int P, int h, int w, float* out, int relu) {
+  if (!l.tc.wd3_bf16) return ctx->fail(DCV_ERR_STATE, "split backward weights were not prepared for this layer");
+  const int k_pad = tc_cpad(l.cout), n_pad = tc_cpad(l.cin);
+  const size_t elems = (size_t)P * tc_split_elems(h, w, l.cout);
+  int r = ctx->ws[4].ensure(ctx, elems * sizeof(__nv_bfloat16));
+  if (r) return r;
+  {
+    const size_t work = (size_t)P * (h + 1) * (w + 1) * (k_pad / 8);
+    ProfScope ps(ctx, DCV_K_OTHER, 0.0, 4.0 * P * h * w * l.cout + 6.0 * P * (h + 1) * (w + 1) * k_pad);
+    split3_pad_kernel<<<grid_for(work, 256), 256, 0, ctx->stream>>>(in, P, h, w, l.cout, k_pad, (__nv_bfloat16*)ctx->ws[4].p);
+    ctx->launches++;
+  }
+  TcConvArgs a{l.tc.wd3_bf16, k_pad, n_pad, l.cout, l.cin, relu, nullptr, 6};
+  a.prof_class = DCV_K_CONV_TC;
+  return tc_conv_run(ctx, a, (const __nv_bfloat16*)ctx->ws[4].p, P, h, w, nullptr, out);
+}
+
 int tc_prepare_forward(dcv_ctx* ctx, Layer& l) {
   if (l.tc.wf_bf16) return 0;
   l.tc.fk_pad = tc_cpad(l.cin);
@@ -662,6 +698,48 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
   p.up_B = l.up ? l.up->B : 0; p.up_C = l.up ? l.up->C : 0; p.up_h = l.up ? l.up->h : 0; p.up_w = l.up ? l.up->w : 0;
   p.out_bf16 = out_bf16; p.out_f32 = out_f32;
   p.m_tiles = (p.rows + BLOCK_M - 1) / BLOCK_M;
+  // fp32-accurate mode: accumulation in registers (tc_exact.cuh); DCV_TC_EXACT=0 keeps the in-TMEM form below
+  static const int exact_regs = getenv("DCV_TC_EXACT") ? atoi(getenv("DCV_TC_EXACT")) : 1;
+  if (l.nprod == 6 && out_f32 && exact_regs) {
+    int bn = l.n_real <= 16 ? 16 : (l.n_pad % 128 == 0 ? 128 : 64);
+    if (bn == 128 && (long long)p.m_tiles * (l.n_pad / 128) < ctx->num_sms) bn = 64;      // few rows: more, smaller tiles
+    if (exact_regs == 2 && bn == 128) bn = 64;
+    p.n_tiles = bn == 16 ? 1 : l.n_pad / bn;
+    int stages = SMEM_BUDGET / exact_stage_bytes(bn);
+    if (stages > 8) stages = 8;
+    p.stages = stages;
+    p.base_off = 0;
+    const int smem = stages * exact_stage_bytes(bn) + 1024 + 256;
+    CUtensorMap ta, tb;
+    int r = make_tmap(ctx, &ta, in, (uint64_t)p.rows, (uint64_t)3 * l.k_pad, BAND_ROWS);
+    if (r) return r;
+    r = make_tmap(ctx, &tb, l.w, (uint64_t)9 * 3 * l.n_pad, (uint64_t)l.k_pad, (uint32_t)bn);
+    if (r) return r;
+    ProfScope ps(ctx, l.prof_class >= 0 ? l.prof_class : DCV_K_CONV_FWD, 2.0 * 9 * P * h * w * (double)l.k_real * l.n_real,
+                 2.0 * P * h * w * ((double)l.k_real + 2.0 * l.n_real));
+    const int grid = std::min(p.m_tiles * p.n_tiles, ctx->num_sms);
+    cudaError_t e = cudaSuccess;
+#define EXACT_LAUNCH(BN)                                                                                         \
+    {                                                                                                              \
+      static int smem_set[64] = {};                                                                                \
+      if (smem_set[ctx->device & 63] < smem) {                                                                     \
+        e = cudaFuncSetAttribute(conv_exact_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);        \
+        if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "cudaFuncSetAttribute(exact kernel): %s", cudaGetErrorString(e)); \
+        smem_set[ctx->device & 63] = smem;                                                                         \
+      }                                                                                                            \
+      conv_exact_kernel<BN><<<grid, NUM_THREADS, smem, ctx->stream>>>(ta, tb, p);                                  \
+    }
+    switch (bn) {
+      case 16: EXACT_LAUNCH(16) break;
+      case 64: EXACT_LAUNCH(64) break;
+      default: EXACT_LAUNCH(128) break;
+    }
+#undef EXACT_LAUNCH
+    ctx->launches++;
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "conv_exact_kernel<%d> launch: %s", bn, cudaGetErrorString(e));
+    return 0;
+  }
   int bn;
   if (out_f32 && l.n_real <= 16) bn = 16;
   else if (l.n_pad % 256 == 0) bn = 256;
@@ -692,7 +770,8 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
   if (r) return r;
   r = make_tmap(ctx, &tb, l.w, (uint64_t)9 * planes * l.n_pad, (uint64_t)l.k_pad, (uint32_t)bn);
   if (r) return r;
-  ProfScope ps(ctx, l.nprod == 6 ? DCV_K_CONV_FWD : DCV_K_CONV_TC, 2.0 * 9 * P * h * w * (double)l.k_real * l.n_real,
+  ProfScope ps(ctx, l.prof_class >= 0 ? l.prof_class : (l.nprod == 6 ? DCV_K_CONV_FWD : DCV_K_CONV_TC),
+               2.0 * 9 * P * h * w * (double)l.k_real * l.n_real,
                2.0 * P * h * w * ((double)l.k_real + (out_f32 ? 2.0 * l.n_real : (double)l.n_real)));
 #define TC_DISPATCH(BN)                                                    \
   switch (mode) {                                                          \

@@ -17,6 +17,7 @@ struct TcWeights {
   int n_pad = 0, k_pad = 0;           // N = cin, K = cout of the forward layer, rounded up to 64
   __nv_bfloat16* wf_bf16 = nullptr;   // forward weights [9][fn_pad][fk_pad] (N = cout, K = cin); built on first bf16 DeepDream
   int fn_pad = 0, fk_pad = 0;
+  __nv_bfloat16* wd3_bf16 = nullptr;  // backward (flipped, transposed) weights split the same way: [9][3][n_pad][k_pad] (exact projection)
   __nv_bfloat16* wf3_bf16 = nullptr;  // forward weights split into (hi, mid, lo) bf16 planes: [9][3][fn_pad][fk_pad] (exact forward)
   __nv_bfloat16* wall_bf16 = nullptr; // narrow last layer (9*cin <= 32): all taps stacked along N, [32][k_pad]
 };
@@ -109,6 +110,11 @@ int tc_prepare_forward(dcv_ctx* ctx, Layer& l);
 // fp32-accurate forward conv on tcgen05 (bf16 x 3 operand split, six products); fp32 compact in and out
 int tc_prepare_forward_exact(dcv_ctx* ctx, Layer& l);
 int tc_conv_fwd_exact(dcv_ctx* ctx, const Layer& l, const float* in, int P, int h, int w, float* out);
+// the same for the backward (deconvnet) conv of the fp32 projection mode: in fp32 compact (P,h,w,cout) ->
+// out fp32 compact (P,h,w,cin) = relu?(conv(in, flipT(W))); scratch ctx->ws[4] sized by tc_split_elems()
+int tc_prepare_backward_exact(dcv_ctx* ctx, Layer& l);
+int tc_conv_bwd_exact(dcv_ctx* ctx, const Layer& l, const float* in, int P, int h, int w, float* out, int relu);
+size_t tc_split_elems(int h, int w, int c);          // bf16 elements of one item split into three planes
 // backward conv; exactly one of out_bf16 (padded-flat, pitch l.tc.n_pad) / out_f32 (compact (P,h,w,l.cin)) is
 // non-null; relu < 0: the layer's own activation (deconvnet rule), 0/1: explicit (DeepDream uses 0)
 // up (optional, bf16 output only): fuse the switch-driven unpool of the pool layer below into the epilogue; out_bf16 is

@@ -1,0 +1,198 @@
+// fp32-accurate 3x3 conv on tcgen05 (included by conv_tc.cu only): the kernel behind the forward pass and the
+// DCV_FP32 projection mode.
+//
+// Arithmetic.  Both operands are split into three bf16 planes (x = hi + mid + lo, 8 mantissa bits each) and the six
+// significant cross products hi*hi, hi*mid, mid*hi, hi*lo, lo*hi, mid*mid are formed on the tensor cores; every bf16
+// product is exact in fp32, the dropped terms are ~2^-24 relative.  What is NOT exact is the tensor core's own
+// accumulation: it truncates when it adds into a TMEM accumulator, so a long K chain inside TMEM drifts towards zero
+// (measured: 1e-5 relative after 13 chained layers with three rotating accumulators).  This kernel therefore never
+// chains more than one pipeline stage (12 MMAs of K = 16) inside TMEM: each stage starts a fresh accumulator slot,
+// and the four epilogue warps - idle during the main loop of the bf16 kernels - drain finished slots into fp32
+// REGISTER accumulators with round-to-nearest adds while the next stages run.  Result: error below the FFMA
+// kernel's (sequential fp32 sums), at several times its speed.
+//
+// Pipeline.  warp 0: TMA producer (one A band of 136 rows serving the three dx taps + three weight tiles per
+// stage, as MODE_BAND of tc_kernel.cuh); warp 1: MMA issuer; warps 2-5: accumulate + epilogue.  Barriers:
+// full/empty per smem stage, slot_full/slot_empty per TMEM slot.
+#pragma once
+#include "tc_kernel.cuh"
+
+namespace dcv {
+namespace tc {
+
+constexpr int EXACT_SLOTS = 4;
+
+__host__ __device__ inline int exact_stage_bytes(int block_n) { return A_BAND_BYTES + 3 * block_n * 128; }
+
+template <int BLOCK_N>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+conv_exact_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, TcParams p) {
+  constexpr int B_TILE_BYTES = BLOCK_N * 128;
+  constexpr int TMEM_COLS = EXACT_SLOTS * BLOCK_N < 32 ? 32 : EXACT_SLOTS * BLOCK_N;
+  constexpr int MAX_STAGES = 8;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* ring = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  const int stage_bytes = exact_stage_bytes(BLOCK_N);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(ring + p.stages * stage_bytes);
+  uint64_t* empty_bar = full_bar + MAX_STAGES;
+  uint64_t* sfull_bar = empty_bar + MAX_STAGES;         // [EXACT_SLOTS] slot holds a finished stage
+  uint64_t* sempty_bar = sfull_bar + EXACT_SLOTS;       // [EXACT_SLOTS] slot drained by the four epilogue warps
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sempty_bar + EXACT_SLOTS);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap_a);
+    tma_prefetch_desc(&tmap_b);
+    for (int s = 0; s < p.stages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    for (int s = 0; s < EXACT_SLOTS; ++s) { mbar_init(&sfull_bar[s], 1); mbar_init(&sempty_bar[s], 4); }
+    fence_barrier_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, TMEM_COLS);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int total_tiles = p.m_tiles * p.n_tiles;
+  const int wp = p.w + 1;
+  const int total_st = 3 * 6 * p.k_blocks;            // (dy, product, 64-channel block) stages per tile
+  const int kcols = p.k_blocks * BLOCK_K;             // columns of one operand plane
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int m0 = (tile / p.n_tiles) * BLOCK_M;
+        const int n0 = (tile % p.n_tiles) * BLOCK_N;
+        for (int st = 0; st < total_st; ++st) {
+          const int kc = st % p.k_blocks;
+          const int gp = st / p.k_blocks;
+          const int g = gp / 6, prod = gp % 6;
+          const int pa = (0x120100 >> (4 * prod)) & 3;       // A plane: 0,0,1,0,2,1
+          const int pb = (0x102010 >> (4 * prod)) & 3;       // B plane: 0,1,0,2,0,1
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* a_dst = ring + stage * stage_bytes;
+          mbar_arrive_expect_tx(&full_bar[stage], (uint32_t)stage_bytes);
+          tma_load_2d(a_dst, &tmap_a, &full_bar[stage], pa * kcols + kc * BLOCK_K, m0 + (g - 1) * wp - 1);
+#pragma unroll
+          for (int dx = 0; dx < 3; ++dx)
+            tma_load_2d(a_dst + A_BAND_BYTES + dx * B_TILE_BYTES, &tmap_b, &full_bar[stage], kc * BLOCK_K,
+                        ((g * 3 + dx) * 3 + pb) * p.n_pad + n0);
+          if (++stage == p.stages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer =====
+    constexpr uint32_t idesc = make_idesc_bf16(BLOCK_M, BLOCK_N);
+    int stage = 0;
+    uint32_t phase = 0;
+    uint32_t chunk = 0;                                 // running stage count of this CTA: slot = chunk % EXACT_SLOTS
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      for (int st = 0; st < total_st; ++st, ++chunk) {
+        const uint32_t slot = chunk % EXACT_SLOTS, suse = chunk / EXACT_SLOTS;
+        mbar_wait(&sempty_bar[slot], (suse & 1) ^ 1);   // the accumulate warps have read this slot's previous stage
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        const uint32_t a_addr = smem_u32(ring + stage * stage_bytes);
+        const uint32_t d_tmem = tmem_base + slot * BLOCK_N;
+        if (elect_one()) {
+#pragma unroll
+          for (int dx = 0; dx < 3; ++dx) {
+            const uint64_t a_desc = make_sw128_kmajor_desc(a_addr + dx * 128, 0u);
+            const uint64_t b_desc = make_sw128_kmajor_desc(a_addr + A_BAND_BYTES + dx * B_TILE_BYTES, 0u);
+#pragma unroll
+            for (int k = 0; k < BLOCK_K / 16; ++k)
+              umma_bf16(d_tmem, a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc, (dx | k) != 0);
+          }
+          umma_commit(&empty_bar[stage]);
+          umma_commit(&sfull_bar[slot]);
+        }
+        __syncwarp();
+        if (++stage == p.stages) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else {
+    // ===== accumulate + epilogue warps 2..5: TMEM lane group = warp % 4, one output row per thread =====
+    const int lg = warp & 3;
+    const int rp = (p.h + 1) * wp;
+    uint32_t chunk = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      const int m0 = (tile / p.n_tiles) * BLOCK_M;
+      const int n0 = (tile % p.n_tiles) * BLOCK_N;
+      float acc[BLOCK_N];
+#pragma unroll
+      for (int i = 0; i < BLOCK_N; ++i) acc[i] = 0.f;
+      for (int st = 0; st < total_st; ++st, ++chunk) {
+        const uint32_t slot = chunk % EXACT_SLOTS, suse = chunk / EXACT_SLOTS;
+        mbar_wait(&sfull_bar[slot], suse & 1);
+        tc_fence_after();
+        const uint32_t t_row = tmem_base + ((uint32_t)(lg * 32) << 16) + slot * BLOCK_N;
+        if constexpr (BLOCK_N >= 32) {
+#pragma unroll
+          for (int c0 = 0; c0 < BLOCK_N; c0 += 32) {
+            uint32_t v[32];
+            tmem_ld32(t_row + (uint32_t)c0, v);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) acc[c0 + i] += __uint_as_float(v[i]);
+          }
+        } else {
+          uint32_t v[32];
+          tmem_ld16(t_row, v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 16; ++i) acc[i] += __uint_as_float(v[i]);
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&sempty_bar[slot]);
+      }
+      // epilogue: bias, ReLU, fp32 compact store (P,h,w,n_real)
+      const int r = m0 + lg * 32 + lane;
+      const int q = r % rp;
+      const int y = q / wp, x = q % wp;
+      if (r < p.rows && x < p.w && y < p.h) {
+        const int item = r / rp;
+        float* dst = p.out_f32 + (((size_t)item * p.h + y) * p.w + x) * p.n_real + n0;
+        if ((p.n_real & 3) == 0 && n0 + BLOCK_N <= p.n_real) {
+#pragma unroll
+          for (int i = 0; i < BLOCK_N; i += 4) {
+            float a[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              a[k] = acc[i + k];
+              if (p.bias) a[k] += __ldg(p.bias + n0 + i + k);
+              if (p.relu) a[k] = fmaxf(a[k], 0.f);
+            }
+            *reinterpret_cast<float4*>(dst + i) = make_float4(a[0], a[1], a[2], a[3]);
+          }
+        } else {
+#pragma unroll
+          for (int i = 0; i < BLOCK_N; ++i) {
+            if (n0 + i < p.n_real) {
+              float a = acc[i];
+              if (p.bias) a += __ldg(p.bias + n0 + i);
+              if (p.relu) a = fmaxf(a, 0.f);
+              dst[i] = a;
+            }
+          }
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, TMEM_COLS);
+}
+
+}  // namespace tc
+}  // namespace dcv
