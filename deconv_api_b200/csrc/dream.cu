@@ -319,9 +319,16 @@ int dream_backward(dcv_ctx* ctx, const LossSpec& ls, float** grad, double* loss_
         dream_prep_kernel<<<grid_for(n, 256), 256, 0, ctx->stream>>>(bufs[cur], (const float*)l.act.p, n, scale, has_g ? 1 : 0, l.relu);
         ctx->launches++;
       }
-      ConvEpilogue e;                                  // conv backward-data: no bias, no ReLU
-      ProfScope ps(ctx, DCV_K_CONV_FP32, 2.0 * 9 * l.B * l.H * l.W * (double)l.cin * l.cout, 4.0 * l.B * l.H * l.W * ((double)l.cin + l.cout));
-      launch_conv3x3_fp32(bufs[cur], l.wd, l.B, l.H, l.W, l.cout, l.cin, e, bufs[cur ^ 1], ctx->stream); ctx->launches++;
+      static const int fp32_tc = getenv("DCV_FP32_TC") ? atoi(getenv("DCV_FP32_TC")) : 1;
+      if (fp32_tc && l.wd) {
+        // conv backward-data on the tensor cores, fp32-accurate (split operands, register accumulation)
+        TRYD(tc_prepare_backward_exact(ctx, ctx->net[j]));
+        TRYD(tc_conv_bwd_exact(ctx, l, bufs[cur], l.B, l.H, l.W, bufs[cur ^ 1], 0));
+      } else {
+        ConvEpilogue e;                                  // conv backward-data: no bias, no ReLU
+        ProfScope ps(ctx, DCV_K_CONV_FP32, 2.0 * 9 * l.B * l.H * l.W * (double)l.cin * l.cout, 4.0 * l.B * l.H * l.W * ((double)l.cin + l.cout));
+        launch_conv3x3_fp32(bufs[cur], l.wd, l.B, l.H, l.W, l.cout, l.cin, e, bufs[cur ^ 1], ctx->stream); ctx->launches++;
+      }
       cur ^= 1;
       has_g = true;
     } else if (l.kind == LK_POOL) {
