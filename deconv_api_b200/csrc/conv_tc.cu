@@ -745,9 +745,26 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
   else if (l.n_pad % 256 == 0) bn = 256;
   else if (l.n_pad % 128 == 0) bn = 128;
   else bn = 64;
-  // few rows (single images at 14x14 .. 64x64): narrower N tiles give more CTAs and shorter MMAs, which matters
-  // more than operand re-use when the grid would not even fill the 148 SMs
-  while (bn > 64 && (long long)p.m_tiles * (l.n_pad / bn) < ctx->num_sms) bn >>= 1;
+  // Few rows (single images at 14x14 .. 129x129; DeepDream sets ctx->latency_tiles, the projection path keeps the
+  // fixed rule below so that its bits do not depend on how the feature maps are chunked): pick the N tile that
+  // minimises waves x cycles per K step.
+  // Measured cycles per 128-row MMA step: ~85 at N=64, ~92 at N=128 (A-operand fetch bound), ~140 at N=256 (single
+  // CTA).  A narrower tile gives more CTAs, but pays only if it does not add a wave: 65x65x512 runs one wave of 136
+  // N=128 tiles instead of two waves of N=64 tiles, 129x129x256 one wave of 133 N=256 tiles instead of two of N=128.
+  static const int bn_model = getenv("DCV_TC_BN_MODEL") ? atoi(getenv("DCV_TC_BN_MODEL")) : 1;
+  if (bn_model && ctx->latency_tiles) {
+    auto cost = [&](int b) {
+      const long long tiles = (long long)p.m_tiles * (l.n_pad / b);
+      const long long waves = (tiles + ctx->num_sms - 1) / ctx->num_sms;
+      return waves * (b == 256 ? 200 : (b == 128 ? 92 : 85));      // N=256 single-CTA: measured slower than two N=128 waves at 129x129
+    };
+    int best = bn;
+    for (int b = bn >> 1; b >= 64 && bn > 64; b >>= 1)
+      if (cost(b) < cost(best)) best = b;
+    bn = best;
+  } else {
+    while (bn > 64 && (long long)p.m_tiles * (l.n_pad / bn) < ctx->num_sms) bn >>= 1;
+  }
   if (l.nprod == 6 && bn > 64) bn = 64;       // exact mode needs the four accumulators of the N-tile-64 kernels
   p.n_tiles = bn == 16 ? 1 : l.n_pad / bn;
   // operand staging mode (tc_kernel.cuh): bands for narrow N, resident weights when they fit beside >= 4 stages

@@ -488,6 +488,7 @@ int dream_iter(dcv_ctx* ctx, float* img, int B, int H, int W, int C, const LossS
   }
   float* g = nullptr;
   if (precision == DCV_BF16) {
+    struct Latency { dcv_ctx* c; Latency(dcv_ctx* c_) : c(c_) { c->latency_tiles = 1; } ~Latency() { c->latency_tiles = 0; } } lat(ctx);
     TRYD(dream_forward_bf16(ctx, x, B, H, W, ls.deepest));
     TRYD(dream_backward_bf16(ctx, ls, &g, loss_out));
   } else {

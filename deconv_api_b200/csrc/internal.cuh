@@ -53,6 +53,7 @@ struct dcv_ctx {
   size_t workspace_budget = 0;
   std::vector<Layer> net;
   int tape_upto = -1;
+  int latency_tiles = 0;   // 1 while DeepDream runs: N tiles chosen by the wave/cycle model (conv_tc.cu)
   int fwd_mode = 1;    // dcv_set_forward_mode: 0 = FFMA fp32, 1 = tcgen05 with split operands (default)
   int in_B = 0, in_H = 0, in_W = 0, in_C = 0;
   DevBuf input;
