@@ -129,6 +129,56 @@ __global__ void pack_weights_fwd3_kernel(const float* __restrict__ w, int kdim, 
   }
 }
 
+// First-layer im2col: fp32 image (P,h,w,C), C <= 4 -> rows of 64 bf16 in the padded-flat row order:
+// columns [0, 9C) = bf16(x) of the 3x3 neighbourhood (tap-major, channel-minor), [9C, 18C) = bf16(x - hi), rest zero.
+// With weights [n][64] holding bf16(w) under both halves, one K=64 GEMM gives sum (x_hi + x_lo) * w: the image keeps
+// 16 mantissa bits, the weights are bf16 like everywhere else in the bf16 chain.  One thread per padded row.
+template <int C>
+__global__ void __launch_bounds__(128)
+im2col_first_kernel(const float* __restrict__ x, int P, int h, int w, __nv_bfloat16* __restrict__ out) {
+  const int wp = w + 1, rp = (h + 1) * wp;
+  const size_t total = (size_t)P * rp;
+  for (size_t r = (size_t)blockIdx.x * blockDim.x + threadIdx.x; r < total; r += (size_t)gridDim.x * blockDim.x) {
+    const int q = (int)(r % rp);
+    const int item = (int)(r / rp);
+    const int y = q / wp, xx = q % wp;
+    __nv_bfloat16 row[64];
+#pragma unroll
+    for (int k = 0; k < 64; ++k) row[k] = __float2bfloat16(0.f);
+    if (y < h && xx < w) {
+      const float* img = x + (size_t)item * h * w * C;
+#pragma unroll
+      for (int t = 0; t < 9; ++t) {
+        const int yy = y + t / 3 - 1, xs = xx + t % 3 - 1;
+        if (yy >= 0 && yy < h && xs >= 0 && xs < w) {
+#pragma unroll
+          for (int c = 0; c < C; ++c) {
+            const float v = __ldg(img + ((size_t)yy * w + xs) * C + c);
+            const __nv_bfloat16 hi = __float2bfloat16(v);
+            row[t * C + c] = hi;
+            row[9 * C + t * C + c] = __float2bfloat16(v - __bfloat162float(hi));
+          }
+        }
+      }
+    }
+    uint4* o = reinterpret_cast<uint4*>(out + r * 64);
+    const uint4* src = reinterpret_cast<const uint4*>(row);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) o[k] = src[k];
+  }
+}
+
+// first-layer weights for the GEMM above: w fp32 [9][C][cout] -> bf16 [n_pad][64]
+__global__ void pack_first_kernel(const float* __restrict__ w, int C, int cout, int n_pad, __nv_bfloat16* __restrict__ out) {
+  const int total = n_pad * 64;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int k = i % 64, n = i / 64;
+    float v = 0.f;
+    if (n < cout && k < 18 * C) v = __ldg(w + (size_t)(k % (9 * C)) * cout + n);     // [t][c][n] flattened = (t*C + c)*cout + n
+    out[i] = __float2bfloat16(v);
+  }
+}
+
 // fp32 compact (P,h,w,C) -> bf16 padded-flat (P*(h+1)*(w+1), c_pad); one thread = 8 channels of one padded row.
 __global__ void pad_convert_kernel(const float* __restrict__ x, int P, int h, int w, int C, int c_pad,
                                    __nv_bfloat16* __restrict__ out) {
@@ -458,6 +508,7 @@ struct TcConvArgs {
   int nprod = 1;            // 6: exact fp32 emulation (three operand planes, six products)
   const TcUnpool* up = nullptr;
   const TcPrep* prep = nullptr;
+  int ntaps = 9;            // 1: un-shifted GEMM (first layer over im2col rows)
   int prof_class = -1;      // profiling class override (default: conv_fwd for nprod 6, conv_tc otherwise)
 };
 
@@ -494,6 +545,8 @@ void tc_free_layer(Layer& l) {
   if (l.tc.wall_bf16) cudaFree(l.tc.wall_bf16);
   if (l.tc.wf3_bf16) cudaFree(l.tc.wf3_bf16);
   if (l.tc.wd3_bf16) cudaFree(l.tc.wd3_bf16);
+  if (l.tc.wf0_bf16) cudaFree(l.tc.wf0_bf16);
+  l.tc.wf0_bf16 = nullptr;
   l.tc.wd_bf16 = l.tc.wf_bf16 = l.tc.wall_bf16 = l.tc.wf3_bf16 = l.tc.wd3_bf16 = nullptr;
 }
 
@@ -617,6 +670,36 @@ int tc_conv_bwd_exact(dcv_ctx* ctx, const Layer& l, const float* in, int P, int 
   return tc_conv_run(ctx, a, (const __nv_bfloat16*)ctx->ws[4].p, P, h, w, nullptr, out);
 }
 
+bool tc_first_layer_ok(const Layer& l) { return l.kind == LK_CONV && l.cin >= 1 && l.cin <= 3; }
+
+int tc_conv_first(dcv_ctx* ctx, Layer& l, const float* x, int P, int h, int w, __nv_bfloat16* out_bf16) {
+  if (!tc_first_layer_ok(l)) return ctx->fail(DCV_ERR_UNSUPPORTED, "tc_conv_first: %d input channels", l.cin);
+  const int n_pad = tc_cpad(l.cout);
+  if (!l.tc.wf0_bf16) {
+    cudaError_t e = cudaMalloc(&l.tc.wf0_bf16, (size_t)n_pad * 64 * sizeof(__nv_bfloat16));
+    if (e != cudaSuccess) return ctx->fail(DCV_ERR_NOMEM, "cudaMalloc(first-layer weights): %s", cudaGetErrorString(e));
+    pack_first_kernel<<<grid_for((size_t)n_pad * 64, 256), 256, 0, ctx->stream>>>(l.w, l.cin, l.cout, n_pad, l.tc.wf0_bf16);
+    ctx->launches++;
+  }
+  const size_t rows = (size_t)P * (h + 1) * (w + 1);
+  int r = ctx->ws[4].ensure(ctx, rows * 64 * sizeof(__nv_bfloat16));
+  if (r) return r;
+  __nv_bfloat16* cols = (__nv_bfloat16*)ctx->ws[4].p;
+  {
+    ProfScope ps(ctx, DCV_K_OTHER, 0.0, 4.0 * P * h * w * l.cin + 128.0 * rows);
+    const int grid = grid_for(rows, 128);
+    switch (l.cin) {
+      case 1: im2col_first_kernel<1><<<grid, 128, 0, ctx->stream>>>(x, P, h, w, cols); break;
+      case 2: im2col_first_kernel<2><<<grid, 128, 0, ctx->stream>>>(x, P, h, w, cols); break;
+      default: im2col_first_kernel<3><<<grid, 128, 0, ctx->stream>>>(x, P, h, w, cols); break;
+    }
+    ctx->launches++;
+  }
+  TcConvArgs a{l.tc.wf0_bf16, 64, n_pad, l.cin, l.cout, l.relu, l.bias};
+  a.ntaps = 1;
+  return tc_conv_run(ctx, a, cols, P, h, w, out_bf16, nullptr);
+}
+
 int tc_prepare_forward(dcv_ctx* ctx, Layer& l) {
   if (l.tc.wf_bf16) return 0;
   l.tc.fk_pad = tc_cpad(l.cin);
@@ -690,6 +773,7 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
   p.relu = l.relu;
   p.bias = l.bias;
   p.nprod = l.nprod;
+  p.ntaps = l.ntaps;
   p.nprod_planes = l.nprod == 6 ? 3 : 1;
   p.prep_act = l.prep ? l.prep->act : nullptr;
   p.prep_scale = l.prep ? l.prep->scale : 0.f;
@@ -698,9 +782,10 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
   p.up_B = l.up ? l.up->B : 0; p.up_C = l.up ? l.up->C : 0; p.up_h = l.up ? l.up->h : 0; p.up_w = l.up ? l.up->w : 0;
   p.out_bf16 = out_bf16; p.out_f32 = out_f32;
   p.m_tiles = (p.rows + BLOCK_M - 1) / BLOCK_M;
-  // fp32-accurate mode: accumulation in registers (tc_exact.cuh); DCV_TC_EXACT=0 keeps the in-TMEM form below
+  // fp32-accurate mode: accumulation in registers (tc_exact.cuh); DCV_TC_EXACT=2 forces N tile 64
   static const int exact_regs = getenv("DCV_TC_EXACT") ? atoi(getenv("DCV_TC_EXACT")) : 1;
-  if (l.nprod == 6 && out_f32 && exact_regs) {
+  if (l.nprod == 6) {
+    if (!out_f32) return ctx->fail(DCV_ERR_UNSUPPORTED, "tc_conv: the split-operand mode writes fp32 only");
     int bn = l.n_real <= 16 ? 16 : (l.n_pad % 128 == 0 ? 128 : 64);
     if (bn == 128 && (long long)p.m_tiles * (l.n_pad / 128) < ctx->num_sms) bn = 64;      // few rows: more, smaller tiles
     if (exact_regs == 2 && bn == 128) bn = 64;
@@ -765,7 +850,6 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
   } else {
     while (bn > 64 && (long long)p.m_tiles * (l.n_pad / bn) < ctx->num_sms) bn >>= 1;
   }
-  if (l.nprod == 6 && bn > 64) bn = 64;       // exact mode needs the four accumulators of the N-tile-64 kernels
   p.n_tiles = bn == 16 ? 1 : l.n_pad / bn;
   // operand staging mode (tc_kernel.cuh): bands for narrow N, resident weights when they fit beside >= 4 stages
   static const int force_mode = getenv("DCV_TC_MODE") ? atoi(getenv("DCV_TC_MODE")) : -1;
@@ -773,19 +857,19 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
   // that starts 1-2 rows into a TMA box needs base offset 0 (1 gives wrong results; tests/test_tc_gpu.py).
   static const int base_off = getenv("DCV_TC_BASEOFF") ? atoi(getenv("DCV_TC_BASEOFF")) : 0;
   int mode = MODE_TAP;
-  if (bn <= 128) {
+  if (bn <= 128 && l.ntaps == 9) {
     mode = MODE_BAND;
     if (l.nprod == 1 && p.n_tiles == 1 && tc_resident_bytes(MODE_BAND_RES, bn, p.k_blocks) + 4 * A_BAND_BYTES <= SMEM_BUDGET)
       mode = MODE_BAND_RES;
   }
-  if (force_mode >= 0 && bn <= 128) mode = force_mode;
+  if (force_mode >= 0 && bn <= 128 && l.ntaps == 9) mode = force_mode;
   if (mode == MODE_BAND_RES && (p.n_tiles != 1 || l.nprod != 1)) mode = MODE_BAND;
   p.base_off = base_off;
   CUtensorMap ta, tb;
   const int planes = l.nprod == 6 ? 3 : 1;
   int r = make_tmap(ctx, &ta, in, (uint64_t)p.rows, (uint64_t)planes * l.k_pad, mode == MODE_TAP ? BLOCK_M : BAND_ROWS);
   if (r) return r;
-  r = make_tmap(ctx, &tb, l.w, (uint64_t)9 * planes * l.n_pad, (uint64_t)l.k_pad, (uint32_t)bn);
+  r = make_tmap(ctx, &tb, l.w, (uint64_t)l.ntaps * planes * l.n_pad, (uint64_t)l.k_pad, (uint32_t)bn);
   if (r) return r;
   ProfScope ps(ctx, l.prof_class >= 0 ? l.prof_class : (l.nprod == 6 ? DCV_K_CONV_FWD : DCV_K_CONV_TC),
                2.0 * 9 * P * h * w * (double)l.k_real * l.n_real,
@@ -799,7 +883,7 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
   // Measured (round 1): block1_conv2 2.40 ms vs 2.55-2.9 ms, block2_conv1 0.90 vs 1.07 ms against the band + resident
   // kernels — once the epilogue got 16 warps and per-warp overlapping A segments (no cross-warp exchange).
   static const int use_dxg = getenv("DCV_TC_DXG") ? atoi(getenv("DCV_TC_DXG")) : 1;
-  if (use_dxg && l.nprod == 1 && !l.up && out_bf16 && l.n_pad == 64 && (p.rows + DXG_ROWS_OUT - 1) / DXG_ROWS_OUT >= ctx->num_sms) {
+  if (use_dxg && l.ntaps == 9 && l.nprod == 1 && !l.up && out_bf16 && l.n_pad == 64 && (p.rows + DXG_ROWS_OUT - 1) / DXG_ROWS_OUT >= ctx->num_sms) {
     // 64 output channels: dx-grouped GEMM (tc_dxg.cuh), tiles of 126 rows
     TcParams q = p;
     q.m_tiles = (p.rows + DXG_ROWS_OUT - 1) / DXG_ROWS_OUT;
@@ -838,7 +922,7 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
   const int m_tiles2 = (p.rows + 255) / 256;
   // Measured (profiles/r1_summary.md): the pair form gains 9-13 % at N tile 256 and nothing at N <= 128, where the
   // A-operand read of each SM (unchanged by pairing) sets the pace; DCV_TC_2CTA=2 forces it everywhere for tests.
-  if (l.nprod == 1 && bn >= 64 && (use_pair == 2 || (use_pair == 1 && bn == 256)) && (long long)m_tiles2 * p.n_tiles >= ctx->num_sms / 2) {
+  if (l.ntaps == 9 && l.nprod == 1 && bn >= 64 && (use_pair == 2 || (use_pair == 1 && bn == 256)) && (long long)m_tiles2 * p.n_tiles >= ctx->num_sms / 2) {
     // CTA-pair kernels (tc_kernel2.cuh): tiles of 256 rows x bn channels, each CTA stages half of the B tile
     TcParams q = p;
     q.m_tiles = m_tiles2;

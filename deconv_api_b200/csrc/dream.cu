@@ -364,14 +364,20 @@ int dream_forward_bf16(dcv_ctx* ctx, const float* x, int B, int H, int W, int up
   ctx->tape_upto = -1;                      // the fp32 projection tape is not valid after this
   Layer& l0 = ctx->net[0];
   ctx->in_B = B; ctx->in_H = H; ctx->in_W = W; ctx->in_C = l0.cin;
-  TRYD(l0.act.ensure(ctx, (size_t)B * H * W * l0.cout * sizeof(float)));
   TRYD(l0.act_h.ensure(ctx, (size_t)B * tc_padded_elems(H, W, l0.cout) * sizeof(__nv_bfloat16)));
-  {
-    ConvEpilogue e; e.bias = l0.bias; e.relu = l0.relu;
-    ProfScope ps(ctx, DCV_K_CONV_FP32, 2.0 * 9 * B * H * W * (double)l0.cin * l0.cout, 4.0 * B * H * W * ((double)l0.cin + l0.cout));
-    launch_conv3x3_fp32(x, l0.w, B, H, W, l0.cin, l0.cout, e, (float*)l0.act.p, ctx->stream); ctx->launches++;
+  static const int first_tc = getenv("DCV_DREAM_FIRST_TC") ? atoi(getenv("DCV_DREAM_FIRST_TC")) : 1;
+  if (first_tc && tc_first_layer_ok(l0)) {
+    // K = 27: im2col rows + one un-shifted tcgen05 GEMM writing the bf16 tape directly
+    TRYD(tc_conv_first(ctx, l0, x, B, H, W, (__nv_bfloat16*)l0.act_h.p));
+  } else {
+    TRYD(l0.act.ensure(ctx, (size_t)B * H * W * l0.cout * sizeof(float)));
+    {
+      ConvEpilogue e; e.bias = l0.bias; e.relu = l0.relu;
+      ProfScope ps(ctx, DCV_K_CONV_FP32, 2.0 * 9 * B * H * W * (double)l0.cin * l0.cout, 4.0 * B * H * W * ((double)l0.cin + l0.cout));
+      launch_conv3x3_fp32(x, l0.w, B, H, W, l0.cin, l0.cout, e, (float*)l0.act.p, ctx->stream); ctx->launches++;
+    }
+    TRYD(tc_pad_convert(ctx, (const float*)l0.act.p, B, H, W, l0.cout, (__nv_bfloat16*)l0.act_h.p));
   }
-  TRYD(tc_pad_convert(ctx, (const float*)l0.act.p, B, H, W, l0.cout, (__nv_bfloat16*)l0.act_h.p));
   l0.B = B; l0.H = H; l0.W = W; l0.C = l0.cout;
   int ch = H, cw = W, cc = l0.cout;
   for (int j = 1; j <= upto; ++j) {

@@ -17,6 +17,7 @@ struct TcWeights {
   int n_pad = 0, k_pad = 0;           // N = cin, K = cout of the forward layer, rounded up to 64
   __nv_bfloat16* wf_bf16 = nullptr;   // forward weights [9][fn_pad][fk_pad] (N = cout, K = cin); built on first bf16 DeepDream
   int fn_pad = 0, fk_pad = 0;
+  __nv_bfloat16* wf0_bf16 = nullptr;  // first layer (cin <= 4) as a GEMM over im2col rows: [n_pad][64], taps x channels along K, twice (for the hi / lo planes of the input)
   __nv_bfloat16* wd3_bf16 = nullptr;  // backward (flipped, transposed) weights split the same way: [9][3][n_pad][k_pad] (exact projection)
   __nv_bfloat16* wf3_bf16 = nullptr;  // forward weights split into (hi, mid, lo) bf16 planes: [9][3][fn_pad][fk_pad] (exact forward)
   __nv_bfloat16* wall_bf16 = nullptr; // narrow last layer (9*cin <= 32): all taps stacked along N, [32][k_pad]
@@ -108,6 +109,10 @@ int tc_dream_prep(dcv_ctx* ctx, __nv_bfloat16* g, const __nv_bfloat16* act, size
 int tc_sumsq_partials(size_t elems);
 int tc_sumsq(dcv_ctx* ctx, const __nv_bfloat16* x, size_t elems, double* partial, int np);
 int tc_prepare_forward(dcv_ctx* ctx, Layer& l);
+// first conv layer (cin <= 4) of the bf16 DeepDream forward: fp32 image (P,h,w,cin) -> bf16 padded-flat activations;
+// im2col rows (9*cin values as bf16 hi + lo planes, K = 64) + one un-shifted GEMM with bias / ReLU epilogue
+bool tc_first_layer_ok(const Layer& l);
+int tc_conv_first(dcv_ctx* ctx, Layer& l, const float* x, int P, int h, int w, __nv_bfloat16* out_bf16);
 // fp32-accurate forward conv on tcgen05 (bf16 x 3 operand split, six products); fp32 compact in and out
 int tc_prepare_forward_exact(dcv_ctx* ctx, Layer& l);
 int tc_conv_fwd_exact(dcv_ctx* ctx, const Layer& l, const float* in, int P, int h, int w, float* out);

@@ -36,6 +36,7 @@ struct TcParams {
   int relu;
   int stages;        // smem ring depth (host-computed from the budget)
   int base_off;      // 1: put (start_addr >> 7) & 7 into the descriptor's base-offset field
+  int ntaps;         // 9 = 3x3 conv; 1 = plain GEMM over un-shifted rows (first layer through im2col), MODE_TAP only
   int nprod_planes;  // weight planes per tap in the packed weights: 1, or 3 with nprod == 6
   int nprod;         // 1 = plain bf16 product; 6 = exact fp32 emulation: operands are split into three bf16 planes
                      // (hi, mid, lo) and the six significant cross products are accumulated (tc forward conv)
@@ -134,10 +135,10 @@ template <int BLOCK_N, int MODE>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, TcParams p) {
   constexpr int B_TILE_BYTES = BLOCK_N * 128;
-  // K-split accumulators: the K steps of a tile rotate over KSPLIT TMEM accumulators that the epilogue adds up.
-  // Measured: no speed-up by itself (the ~85 cycles per small-N MMA are the shared-memory operand fetch, not a
-  // dependency chain), but the four accumulators are what keeps the split-operand forward conv fp32-accurate.
-  constexpr int KSPLIT = BLOCK_N <= 64 ? 4 : (BLOCK_N == 128 ? 2 : 1);
+  // One TMEM accumulator per tile buffer.  (Rotating the K steps over several accumulators was measured to give no
+  // speed-up - the ~85 cycles per small-N MMA are the shared-memory operand fetch, not a dependency chain - and only
+  // cost epilogue time; the fp32-accurate mode that needed them now accumulates in registers, tc_exact.cuh.)
+  constexpr int KSPLIT = 1;
   constexpr int ACC_COLS = BLOCK_N * KSPLIT;              // TMEM columns of one accumulator buffer
   constexpr int TMEM_COLS = (2 * ACC_COLS) < 32 ? 32 : (2 * ACC_COLS);
   constexpr int MAX_STAGES = 8;
@@ -176,7 +177,7 @@ deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 
   const int total_tiles = p.m_tiles * p.n_tiles;
   const int wp = p.w + 1;
-  const int groups = (MODE == MODE_TAP) ? 9 : 3;      // stages per 64-channel block
+  const int groups = (MODE == MODE_TAP) ? p.ntaps : 3; // stages per 64-channel block
   const int total_st = groups * p.nprod * p.k_blocks; // stages per tile
   const int kcols = p.k_blocks * BLOCK_K;             // columns of one operand plane
 
@@ -207,7 +208,7 @@ deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
           uint8_t* a_dst = ring + stage * stage_bytes;
           mbar_arrive_expect_tx(&full_bar[stage], (uint32_t)stage_bytes);
           if constexpr (MODE == MODE_TAP) {
-            const int shift = (g / 3 - 1) * wp + (g % 3 - 1);
+            const int shift = p.ntaps == 1 ? 0 : (g / 3 - 1) * wp + (g % 3 - 1);
             tma_load_2d(a_dst, &tmap_a, &full_bar[stage], a_col, m0 + shift);
             tma_load_2d(a_dst + A_TILE_BYTES, &tmap_b, &full_bar[stage], kc * BLOCK_K, (g * p.nprod_planes + pb) * p.n_pad + n0);
           } else {
@@ -246,26 +247,15 @@ deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
           const uint32_t a_addr = smem_u32(ring + stage * stage_bytes);
           const int kc = st % p.k_blocks;
           const int gp = st / p.k_blocks;
-          const int g = gp / p.nprod, prod = gp % p.nprod;
-          // Split-operand (exact) mode, KSPLIT == 4: the tensor core TRUNCATES when it adds into an accumulator, so the
-          // error grows with the number of adds into a LARGE running sum.  The hi*hi products (which carry the
-          // magnitude) therefore rotate over accumulators 0..2 and the five small correction products share
-          // accumulator 3; the epilogue adds the four with fp32 round-to-nearest.
-          const bool exact = (p.nprod == 6) && (KSPLIT == 4);
+          const int g = gp / p.nprod;
           if (elect_one()) {
             if constexpr (MODE == MODE_TAP) {
               const uint64_t a_desc = make_sw128_kmajor_desc(a_addr, 0);
               const uint64_t b_desc = make_sw128_kmajor_desc(a_addr + A_TILE_BYTES, 0);
 #pragma unroll
               for (int k = 0; k < BLOCK_K / 16; ++k) {  // +32 bytes along K inside the swizzle atom = +2 in addr>>4
-                int acc = k % KSPLIT;
-                bool accumulate = (st != 0) || (k >= KSPLIT);
-                if (exact) {
-                  const int j = (g * p.k_blocks + kc) * 4 + k;             // running index of the hi*hi MMAs of this tile
-                  acc = prod == 0 ? j % 3 : 3;
-                  accumulate = prod == 0 ? j >= 3 : !(g == 0 && prod == 1 && kc == 0 && k == 0);
-                }
-                umma_bf16(d_tmem + (uint32_t)(acc * BLOCK_N), a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc, accumulate);
+                const bool accumulate = (st != 0) || (k != 0);
+                umma_bf16(d_tmem, a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc, accumulate);
               }
             } else {
 #pragma unroll
@@ -278,14 +268,8 @@ deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                 const uint64_t b_desc = make_sw128_kmajor_desc(b_addr, 0);
 #pragma unroll
                 for (int k = 0; k < BLOCK_K / 16; ++k) {
-                  int acc = k % KSPLIT;
-                  bool accumulate = ((st | dx) != 0) || (k >= KSPLIT);
-                  if (exact) {
-                    const int j = ((g * 3 + dx) * p.k_blocks + kc) * 4 + k;
-                    acc = prod == 0 ? j % 3 : 3;
-                    accumulate = prod == 0 ? j >= 3 : !(g == 0 && dx == 0 && prod == 1 && kc == 0 && k == 0);
-                  }
-                  umma_bf16(d_tmem + (uint32_t)(acc * BLOCK_N), a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc, accumulate);
+                  const bool accumulate = ((st | dx) != 0) || (k != 0);
+                  umma_bf16(d_tmem, a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc, accumulate);
                 }
               }
             }
