@@ -902,16 +902,28 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
       r = make_tmap(ctx, &tb2, l.w, (uint64_t)9 * l.n_pad, (uint64_t)l.k_pad, DXG_N);
       if (r) return r;
       cudaError_t e = cudaSuccess;
-      static int smem_set[2][64] = {};
-      if (smem_set[resident][ctx->device & 63] < smem) {
-        e = resident ? cudaFuncSetAttribute(deconv_dxg_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)
-                     : cudaFuncSetAttribute(deconv_dxg_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-        if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "cudaFuncSetAttribute(dxg kernel): %s", cudaGetErrorString(e));
-        smem_set[resident][ctx->device & 63] = smem;
-      }
+      const int epi = (q.bias ? 1 : 0) | (q.prep_act ? 2 : 0);
       const int grid = std::min(q.m_tiles, ctx->num_sms);
-      if (resident) deconv_dxg_kernel<1><<<grid, DXG_THREADS, smem, ctx->stream>>>(ta2, tb2, q);
-      else deconv_dxg_kernel<0><<<grid, DXG_THREADS, smem, ctx->stream>>>(ta2, tb2, q);
+#define DXG_LAUNCH(RES, EPI)                                                                                          \
+      {                                                                                                                \
+        static int smem_set[64] = {};                                                                                  \
+        if (smem_set[ctx->device & 63] < smem) {                                                                       \
+          e = cudaFuncSetAttribute(deconv_dxg_kernel<RES, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);    \
+          if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "cudaFuncSetAttribute(dxg kernel): %s", cudaGetErrorString(e)); \
+          smem_set[ctx->device & 63] = smem;                                                                           \
+        }                                                                                                              \
+        deconv_dxg_kernel<RES, EPI><<<grid, DXG_THREADS, smem, ctx->stream>>>(ta2, tb2, q);                            \
+      }
+#define DXG_EPIS(RES)                                \
+      switch (epi) {                                 \
+        case 0: DXG_LAUNCH(RES, 0) break;            \
+        case 1: DXG_LAUNCH(RES, 1) break;            \
+        case 2: DXG_LAUNCH(RES, 2) break;            \
+        default: DXG_LAUNCH(RES, 3) break;           \
+      }
+      if (resident) { DXG_EPIS(1) } else { DXG_EPIS(0) }
+#undef DXG_EPIS
+#undef DXG_LAUNCH
       ctx->launches++;
       e = cudaGetLastError();
       if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "deconv_dxg_kernel launch: %s", cudaGetErrorString(e));

@@ -27,7 +27,8 @@ constexpr int DXG_B_BYTES = DXG_N * 128;              // 24 KB per (dy, k block)
 __host__ __device__ inline int dxg_resident_bytes(int resident, int k_blocks) { return resident ? 3 * k_blocks * DXG_B_BYTES : 0; }
 __host__ __device__ inline int dxg_stage_bytes(int resident) { return A_TILE_BYTES + (resident ? 0 : DXG_B_BYTES); }
 
-template <int RESIDENT>
+// EPI bits: 1 = add the bias (forward conv), 2 = fold the DeepDream gradient prep of the next layer in
+template <int RESIDENT, int EPI>
 __global__ void __launch_bounds__(DXG_THREADS, 1)
 deconv_dxg_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, TcParams p) {
   constexpr int TMEM_COLS = 512;                      // 2 accumulators x 192 columns
@@ -132,6 +133,12 @@ deconv_dxg_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     const int lg = warp & 3;                                  // TMEM lane quarter this warp may read
     const int c0 = ((warp - 2) >> 2) * 16;                    // its 16 output columns
     const int rp = (p.h + 1) * wp;
+    const float relu_lo = p.relu ? 0.f : -INFINITY;
+    float bias_r[16];
+    if constexpr (EPI & 1) {
+#pragma unroll
+      for (int i = 0; i < 16; ++i) bias_r[i] = (c0 + i < p.n_real) ? __ldg(p.bias + c0 + i) : 0.f;
+    }
     int local = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++local) {
       const int m0 = tile * DXG_ROWS_OUT;
@@ -145,44 +152,46 @@ deconv_dxg_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       const bool in_range = (lane < DXG_SEG) && (r < p.rows);
       const bool is_pixel = in_range && (x < p.w) && (y < p.h);
       const uint32_t t_row = tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(buf * ACC_STRIDE);
-      {
-        uint32_t v0[32], v1[32], v2[32];                      // 16 used
-        tmem_ld16(t_row + (uint32_t)c0, v0);
-        tmem_ld16(t_row + (uint32_t)(64 + c0), v1);
-        tmem_ld16(t_row + (uint32_t)(128 + c0), v2);
-        tmem_ld_wait();
-        uint32_t packed[8];
-        uint32_t actw[8];
-        if (p.prep_act && in_range) {
+      uint32_t v0[32], v1[32], v2[32];                        // 16 used
+      tmem_ld16(t_row + (uint32_t)c0, v0);
+      tmem_ld16(t_row + (uint32_t)(64 + c0), v1);
+      tmem_ld16(t_row + (uint32_t)(128 + c0), v2);
+      tmem_ld_wait();
+      // the accumulator is in registers: hand the TMEM buffer back before the arithmetic and the stores
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty_bar[buf]);
+      // Measured: this epilogue, not the tensor pipe, paces the kernel (12 MMAs per tile; skipping the body took
+      // block1_conv2 from 2.4 to 1.35 ms), and it is instruction-bound - so the optional steps are compiled out
+      // (EPI) and the ReLU / pad masking are branch-free.
+      uint32_t actw[8];
+      if constexpr (EPI & 2) {
+        if (in_range) {
           const uint4* ap = reinterpret_cast<const uint4*>(p.prep_act + (size_t)r * p.n_pad + c0);
           const uint4 t0 = __ldg(ap), t1 = __ldg(ap + 1);
           actw[0] = t0.x; actw[1] = t0.y; actw[2] = t0.z; actw[3] = t0.w; actw[4] = t1.x; actw[5] = t1.y; actw[6] = t1.z; actw[7] = t1.w;
         }
-#pragma unroll
-        for (int c = 0; c < 16; c += 2) {
-          float s[2];
-#pragma unroll
-          for (int e = 0; e < 2; ++e) {
-            float t = __uint_as_float(v0[c + e]) + __shfl_down_sync(0xffffffffu, __uint_as_float(v1[c + e]), 1) +
-                      __shfl_down_sync(0xffffffffu, __uint_as_float(v2[c + e]), 2);
-            if (p.bias && c0 + c + e < p.n_real) t += __ldg(p.bias + c0 + c + e);
-            if (p.relu) t = fmaxf(t, 0.f);
-            s[e] = t;
-          }
-          if (p.prep_act && in_range) prep_pair(p, actw[c / 2], s[0], s[1]);
-          if (!is_pixel) { s[0] = 0.f; s[1] = 0.f; }
-          __nv_bfloat162 h2 = __floats2bfloat162_rn(s[0], s[1]);
-          packed[c / 2] = *reinterpret_cast<uint32_t*>(&h2);
-        }
-        if (in_range) {
-          uint4* dst = reinterpret_cast<uint4*>(p.out_bf16 + (size_t)r * p.n_pad + c0);
-          dst[0] = make_uint4(packed[0], packed[1], packed[2], packed[3]);
-          dst[1] = make_uint4(packed[4], packed[5], packed[6], packed[7]);
-        }
       }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&tempty_bar[buf]);
+      uint32_t packed[8];
+#pragma unroll
+      for (int c = 0; c < 16; c += 2) {
+        float s[2];
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          float t = __uint_as_float(v0[c + e]) + __shfl_down_sync(0xffffffffu, __uint_as_float(v1[c + e]), 1) +
+                    __shfl_down_sync(0xffffffffu, __uint_as_float(v2[c + e]), 2);
+          if constexpr (EPI & 1) t += bias_r[c + e];
+          s[e] = fmaxf(t, relu_lo);
+        }
+        if constexpr (EPI & 2) { if (in_range) prep_pair(p, actw[c / 2], s[0], s[1]); }
+        __nv_bfloat162 h2 = __floats2bfloat162_rn(s[0], s[1]);
+        packed[c / 2] = is_pixel ? *reinterpret_cast<uint32_t*>(&h2) : 0u;
+      }
+      if (in_range) {
+        uint4* dst = reinterpret_cast<uint4*>(p.out_bf16 + (size_t)r * p.n_pad + c0);
+        dst[0] = make_uint4(packed[0], packed[1], packed[2], packed[3]);
+        dst[1] = make_uint4(packed[4], packed[5], packed[6], packed[7]);
+      }
     }
   }
 
