@@ -888,7 +888,7 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
     TcParams q = p;
     q.m_tiles = (p.rows + DXG_ROWS_OUT - 1) / DXG_ROWS_OUT;
     q.n_tiles = 1;
-    const int xs_bytes = 0;
+    const int xs_bytes = DXG_OUT_BYTES;
     const int resident = dxg_resident_bytes(1, q.k_blocks) + 4 * A_TILE_BYTES + xs_bytes <= SMEM_BUDGET ? 1 : 0;
     const int res_bytes = dxg_resident_bytes(resident, q.k_blocks), stage_bytes = dxg_stage_bytes(resident);
     int stages = (SMEM_BUDGET - res_bytes - xs_bytes) / stage_bytes;
@@ -901,6 +901,9 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
       if (r) return r;
       r = make_tmap(ctx, &tb2, l.w, (uint64_t)9 * l.n_pad, (uint64_t)l.k_pad, DXG_N);
       if (r) return r;
+      CUtensorMap to2;
+      r = make_tmap(ctx, &to2, out_bf16, (uint64_t)p.rows, (uint64_t)l.n_pad, DXG_ROWS_OUT);
+      if (r) return r;
       cudaError_t e = cudaSuccess;
       const int epi = (q.bias ? 1 : 0) | (q.prep_act ? 2 : 0);
       const int grid = std::min(q.m_tiles, ctx->num_sms);
@@ -912,7 +915,7 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
           if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "cudaFuncSetAttribute(dxg kernel): %s", cudaGetErrorString(e)); \
           smem_set[ctx->device & 63] = smem;                                                                           \
         }                                                                                                              \
-        deconv_dxg_kernel<RES, EPI><<<grid, DXG_THREADS, smem, ctx->stream>>>(ta2, tb2, q);                            \
+        deconv_dxg_kernel<RES, EPI><<<grid, DXG_THREADS, smem, ctx->stream>>>(ta2, tb2, to2, q);                            \
       }
 #define DXG_EPIS(RES)                                \
       switch (epi) {                                 \
