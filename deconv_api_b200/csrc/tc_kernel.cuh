@@ -285,6 +285,7 @@ deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     // ===== epilogue warps 2..5: TMEM lane group = warp % 4 =====
     const int lg = warp & 3;
     const int rp = (p.h + 1) * wp;
+    const float relu_lo = p.relu ? 0.f : -INFINITY;
     int local = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++local) {
       const int m0 = (tile / p.n_tiles) * BLOCK_M;
@@ -319,29 +320,37 @@ deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         }
         if (p.out_bf16) {
           if (in_range) {
-            uint32_t packed[CHUNK / 2];
-            uint32_t actw[CHUNK / 2];
+            // optional steps as separate, warp-uniform passes over the chunk (nothing per element when they are off);
+            // ReLU and pad masking branch-free.  One epilogue warp per sub-partition is latency-bound, so its
+            // instruction count is the epilogue's duration.
+            if (p.bias) {
+#pragma unroll
+              for (int i = 0; i < CHUNK; ++i) {
+                const int c = n0 + c0 + i;
+                if (c < p.n_real) v[i] = __float_as_uint(__uint_as_float(v[i]) + __ldg(p.bias + c));
+              }
+            }
+#pragma unroll
+            for (int i = 0; i < CHUNK; ++i) v[i] = __float_as_uint(fmaxf(__uint_as_float(v[i]), relu_lo));
             if (p.prep_act) {
               const uint4* ap = reinterpret_cast<const uint4*>(p.prep_act + (size_t)r * p.n_pad + n0 + c0);
 #pragma unroll
               for (int i = 0; i < CHUNK / 8; ++i) {
                 const uint4 t = __ldg(ap + i);
-                actw[4 * i] = t.x; actw[4 * i + 1] = t.y; actw[4 * i + 2] = t.z; actw[4 * i + 3] = t.w;
+                const uint32_t aw[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                  float a = __uint_as_float(v[8 * i + 2 * k]), b = __uint_as_float(v[8 * i + 2 * k + 1]);
+                  prep_pair(p, aw[k], a, b);
+                  v[8 * i + 2 * k] = __float_as_uint(a); v[8 * i + 2 * k + 1] = __float_as_uint(b);
+                }
               }
             }
+            uint32_t packed[CHUNK / 2];
 #pragma unroll
             for (int i = 0; i < CHUNK / 2; ++i) {
-              float a = __uint_as_float(v[2 * i]), b = __uint_as_float(v[2 * i + 1]);
-              if (p.bias) {
-                const int c = n0 + c0 + 2 * i;
-                if (c < p.n_real) a += __ldg(p.bias + c);
-                if (c + 1 < p.n_real) b += __ldg(p.bias + c + 1);
-              }
-              if (p.relu) { a = fmaxf(a, 0.f); b = fmaxf(b, 0.f); }
-              if (p.prep_act) prep_pair(p, actw[i], a, b);
-              if (!is_pixel) { a = 0.f; b = 0.f; }
-              __nv_bfloat162 h2 = __floats2bfloat162_rn(a, b);
-              packed[i] = *reinterpret_cast<uint32_t*>(&h2);
+              __nv_bfloat162 h2 = __floats2bfloat162_rn(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1]));
+              packed[i] = is_pixel ? *reinterpret_cast<uint32_t*>(&h2) : 0u;
             }
             store_bf16_chunk<CHUNK>(p, packed, r, is_pixel, r / rp, y, x, n0 + c0);
           }
