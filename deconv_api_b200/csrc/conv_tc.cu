@@ -889,9 +889,14 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
     q.m_tiles = (p.rows + DXG_ROWS_OUT - 1) / DXG_ROWS_OUT;
     q.n_tiles = 1;
     const int xs_bytes = DXG_OUT_BYTES;
-    const int resident = dxg_resident_bytes(1, q.k_blocks) + 4 * A_TILE_BYTES + xs_bytes <= SMEM_BUDGET ? 1 : 0;
+    // Resident weights whenever they fit the full 227 KB of shared memory next to >= 4 A stages: for K = 128
+    // (block2_conv1, 144 KB of weights) re-loading the 24 KB weight tile with every stage made the L2 -> SM stream the
+    // bottleneck (7.8 GB per launch).  DCV_TC_DXG_RES=0 restores the 200 KB rule.
+    static const int big_res = getenv("DCV_TC_DXG_RES") ? atoi(getenv("DCV_TC_DXG_RES")) : 1;
+    const int budget = big_res ? 232448 - 1024 - 256 : SMEM_BUDGET;
+    const int resident = dxg_resident_bytes(1, q.k_blocks) + 4 * A_TILE_BYTES + xs_bytes <= budget ? 1 : 0;
     const int res_bytes = dxg_resident_bytes(resident, q.k_blocks), stage_bytes = dxg_stage_bytes(resident);
-    int stages = (SMEM_BUDGET - res_bytes - xs_bytes) / stage_bytes;
+    int stages = ((resident ? budget : SMEM_BUDGET) - res_bytes - xs_bytes) / stage_bytes;
     if (stages > 8) stages = 8;
     if (stages >= 2) {
       q.stages = stages;
