@@ -82,3 +82,24 @@ def test_dream_loop_bf16_vs_oracle():
     out_ref, _ = do.dream(ref, img, layers, dm.octave_shapes(96, 80, 3, 1.4), 4, 1.0, dm.jitter_offsets(12, 8, 3))
     assert rel_l2(out, out_ref) < 2e-2                      # north_star: dream images within 2e-2 in bf16
     assert rel_l2(out - img, out_ref - img) < 0.2           # and the applied change itself agrees to 20 %
+
+
+def test_gradient_bf16_large_image_kernel_variants():
+    """At >= 134x134 pixels the 64-channel layers switch to the dx-grouped kernel (bias epilogue in the forward,
+    prep epilogue in the backward, output through a shared-memory tile + TMA store) and block2+ use multi-wave grids;
+    the first layer runs as im2col + GEMM.  Odd size on purpose (ragged last tile, pools floor)."""
+    model = vgg16.VGG16(weights=None, include_top=False, input_shape=(None, None, 3), seed=9, bias=True)
+    ref = keras_shim.VGG16(include_top=False, input_shape=(None, None, 3), seed=9, bias=True)
+    layers = {"block1_conv2": 0.3, "block2_conv2": 0.7, "block3_conv2": 1.5}
+    hw = (171, 150)
+    img = synth.caffe_preprocess(synth.smooth_image_u8(7, *hw))
+    eng = model.bound_engine(upto="block3_conv2")
+    g, loss = eng.dream_gradient(img, [eng.index[n] for n in layers], list(layers.values()), precision="bf16")
+    loss_ref, g_ref = do.loss_and_grad(do._convs(ref, "block3_conv2"), img, layers)
+    assert abs(loss - loss_ref) <= 2e-2 * abs(loss_ref)
+    cos = float((g * g_ref).sum() / (np.linalg.norm(g) * np.linalg.norm(g_ref)))
+    assert cos > 0.99 and rel_l2(g, g_ref) < 0.15, (cos, rel_l2(g, g_ref))
+    # and the fp32 mode (tensor cores, split operands) at the same size against the same oracle
+    g32, loss32 = eng.dream_gradient(img, [eng.index[n] for n in layers], list(layers.values()), precision="fp32")
+    assert abs(loss32 - loss_ref) <= 1e-5 * abs(loss_ref)
+    assert rel_l2(g32, g_ref) < 1e-5
