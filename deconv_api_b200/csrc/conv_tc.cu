@@ -136,6 +136,8 @@ __global__ void pack_weights_fwd3_kernel(const float* __restrict__ w, int kdim, 
 template <int C>
 __global__ void __launch_bounds__(128)
 im2col_first_kernel(const float* __restrict__ x, int P, int h, int w, __nv_bfloat16* __restrict__ out) {
+  // one thread per padded row (measured: a 16-byte-chunk-per-thread form with coalesced stores is 3x slower,
+  // the index arithmetic dominates)
   const int wp = w + 1, rp = (h + 1) * wp;
   const size_t total = (size_t)P * rp;
   for (size_t r = (size_t)blockIdx.x * blockDim.x + threadIdx.x; r < total; r += (size_t)gridDim.x * blockDim.x) {
@@ -883,6 +885,44 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
   // Measured (round 1): block1_conv2 2.40 ms vs 2.55-2.9 ms, block2_conv1 0.90 vs 1.07 ms against the band + resident
   // kernels — once the epilogue got 16 warps and per-warp overlapping A segments (no cross-warp exchange).
   static const int use_dxg = getenv("DCV_TC_DXG") ? atoi(getenv("DCV_TC_DXG")) : 1;
+  if (use_dxg && l.ntaps == 1 && l.nprod == 1 && !l.up && !l.prep && out_bf16 && l.n_pad == 64) {
+    // plain GEMM over un-shifted rows (first layer through im2col): the 16-warp epilogue + TMA store of tc_dxg.cuh
+    TcParams q = p;
+    q.m_tiles = (p.rows + 127) / 128;
+    q.n_tiles = 1;
+    const int res_bytes = q.k_blocks * 64 * 128, out_bytes = 128 * 128;
+    int stages = (SMEM_BUDGET - res_bytes - out_bytes) / A_TILE_BYTES;
+    if (stages > 8) stages = 8;
+    if (stages >= 2) {
+      q.stages = stages;
+      const int smem = res_bytes + stages * A_TILE_BYTES + out_bytes + 1024 + 256;
+      CUtensorMap ta2, tb2, to2;
+      r = make_tmap(ctx, &ta2, in, (uint64_t)p.rows, (uint64_t)l.k_pad, 32);
+      if (r) return r;
+      r = make_tmap(ctx, &tb2, l.w, (uint64_t)l.n_pad, (uint64_t)l.k_pad, 64);
+      if (r) return r;
+      r = make_tmap(ctx, &to2, out_bf16, (uint64_t)p.rows, (uint64_t)l.n_pad, 128);
+      if (r) return r;
+      const int grid = std::min(q.m_tiles, ctx->num_sms);
+      cudaError_t e = cudaSuccess;
+#define GEMM64_LAUNCH(EPI)                                                                                             \
+      {                                                                                                                \
+        static int smem_set[64] = {};                                                                                  \
+        if (smem_set[ctx->device & 63] < smem) {                                                                       \
+          e = cudaFuncSetAttribute(deconv_dxg_kernel<1, EPI, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);   \
+          if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "cudaFuncSetAttribute(gemm64 kernel): %s", cudaGetErrorString(e)); \
+          smem_set[ctx->device & 63] = smem;                                                                           \
+        }                                                                                                              \
+        deconv_dxg_kernel<1, EPI, 0><<<grid, DXG_THREADS, smem, ctx->stream>>>(ta2, tb2, to2, q);                      \
+      }
+      if (q.bias) GEMM64_LAUNCH(1) else GEMM64_LAUNCH(0)
+#undef GEMM64_LAUNCH
+      ctx->launches++;
+      e = cudaGetLastError();
+      if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "gemm64 kernel launch: %s", cudaGetErrorString(e));
+      return 0;
+    }
+  }
   if (use_dxg && l.ntaps == 9 && l.nprod == 1 && !l.up && out_bf16 && l.n_pad == 64 && (p.rows + DXG_ROWS_OUT - 1) / DXG_ROWS_OUT >= ctx->num_sms) {
     // 64 output channels: dx-grouped GEMM (tc_dxg.cuh), tiles of 126 rows
     TcParams q = p;

@@ -28,22 +28,30 @@ constexpr int DXG_OUT_BYTES = DXG_ROWS_OUT * 128;     // output tile staged in s
 __host__ __device__ inline int dxg_resident_bytes(int resident, int k_blocks) { return resident ? 3 * k_blocks * DXG_B_BYTES : 0; }
 __host__ __device__ inline int dxg_stage_bytes(int resident) { return A_TILE_BYTES + (resident ? 0 : DXG_B_BYTES); }
 
-// EPI bits: 1 = add the bias (forward conv), 2 = fold the DeepDream gradient prep of the next layer in
-template <int RESIDENT, int EPI>
+// EPI bits: 1 = add the bias (forward conv), 2 = fold the DeepDream gradient prep of the next layer in.
+// GROUPED = 0 turns the kernel into a plain [rows x K] x [K x 64] GEMM (one un-shifted tap, N = 64, four contiguous
+// 32-row segments = 128 output rows per tile, no shuffles): the first conv layer over im2col rows, which with 4 MMAs
+// per tile is all epilogue - in tc_kernel.cuh's 4-warp epilogue it ran at 3 us per tile (11 cycles per instruction).
+template <int RESIDENT, int EPI, int GROUPED = 1>
 __global__ void __launch_bounds__(DXG_THREADS, 1)
 deconv_dxg_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                   const __grid_constant__ CUtensorMap tmap_out, TcParams p) {
   constexpr int TMEM_COLS = 512;                      // 2 accumulators x 192 columns
   constexpr int ACC_STRIDE = 256;
   constexpr int MAX_STAGES = 8;
+  constexpr int N_TILE = GROUPED ? DXG_N : 64;
+  constexpr int SEG = GROUPED ? DXG_SEG : 32;         // output rows per lane quarter
+  constexpr int ROWS_OUT = 4 * SEG;
+  constexpr int B_BYTES = N_TILE * 128;
+  constexpr int NDY = GROUPED ? 3 : 1;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  const int stage_bytes = dxg_stage_bytes(RESIDENT);
-  const int res_bytes = dxg_resident_bytes(RESIDENT, p.k_blocks);
+  const int stage_bytes = A_TILE_BYTES + (RESIDENT ? 0 : B_BYTES);
+  const int res_bytes = RESIDENT ? NDY * p.k_blocks * B_BYTES : 0;
   uint8_t* wres = smem;
   uint8_t* ring = smem + res_bytes;
-  uint8_t* out_tile = ring + p.stages * stage_bytes;          // [120 rows][128 B], 128-byte swizzle, source of the TMA store
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(out_tile + DXG_OUT_BYTES);
+  uint8_t* out_tile = ring + p.stages * stage_bytes;          // [ROWS_OUT][128 B], 128-byte swizzle, source of the TMA store
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(out_tile + ROWS_OUT * 128);
   uint64_t* empty_bar = full_bar + MAX_STAGES;
   uint64_t* tfull_bar = empty_bar + MAX_STAGES;
   uint64_t* tempty_bar = tfull_bar + 2;
@@ -73,35 +81,37 @@ deconv_dxg_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
 
   const int total_tiles = p.m_tiles;                  // tiles of 126 output rows; n_tiles == 1
   const int wp = p.w + 1;
-  const int total_st = 3 * p.k_blocks;
+  const int total_st = NDY * p.k_blocks;
 
   if (warp == 0) {
     if (lane == 0) {
       if constexpr (RESIDENT) {
         mbar_arrive_expect_tx(wres_bar, (uint32_t)res_bytes);
-        for (int dy = 0; dy < 3; ++dy)
+        for (int dy = 0; dy < NDY; ++dy)
           for (int kc = 0; kc < p.k_blocks; ++kc)
-            tma_load_2d(wres + (dy * p.k_blocks + kc) * DXG_B_BYTES, &tmap_b, wres_bar, kc * BLOCK_K, dy * DXG_N);
+            tma_load_2d(wres + (dy * p.k_blocks + kc) * B_BYTES, &tmap_b, wres_bar, kc * BLOCK_K, dy * N_TILE);
       }
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        const int m0 = tile * DXG_ROWS_OUT;
+        const int m0 = tile * ROWS_OUT;
         for (int st = 0; st < total_st; ++st) {
           const int dy = st / p.k_blocks, kc = st % p.k_blocks;
+          // grouped: input rows m0-1 .. of image row dy-1; plain GEMM: the tile's own rows
+          const int row0 = GROUPED ? m0 - 1 + (dy - 1) * wp : m0;
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* a_dst = ring + stage * stage_bytes;
           mbar_arrive_expect_tx(&full_bar[stage], (uint32_t)stage_bytes);
 #pragma unroll
-          for (int k = 0; k < 4; ++k)      // four 32-row segments, 30 rows apart (2 rows of overlap per warp boundary)
-            tma_load_2d(a_dst + k * 32 * 128, &tmap_a, &full_bar[stage], kc * BLOCK_K, m0 - 1 + DXG_SEG * k + (dy - 1) * wp);
-          if constexpr (!RESIDENT) tma_load_2d(a_dst + A_TILE_BYTES, &tmap_b, &full_bar[stage], kc * BLOCK_K, dy * DXG_N);
+          for (int k = 0; k < 4; ++k)      // four 32-row segments, SEG rows apart (grouped: 2 rows of overlap per warp boundary)
+            tma_load_2d(a_dst + k * 32 * 128, &tmap_a, &full_bar[stage], kc * BLOCK_K, row0 + SEG * k);
+          if constexpr (!RESIDENT) tma_load_2d(a_dst + A_TILE_BYTES, &tmap_b, &full_bar[stage], kc * BLOCK_K, dy * N_TILE);
           if (++stage == p.stages) { stage = 0; phase ^= 1; }
         }
       }
     }
   } else if (warp == 1) {
-    constexpr uint32_t idesc = make_idesc_bf16(BLOCK_M, DXG_N);
+    constexpr uint32_t idesc = make_idesc_bf16(BLOCK_M, N_TILE);
     if constexpr (RESIDENT) {
       mbar_wait(wres_bar, 0);
       tc_fence_after();
@@ -119,7 +129,7 @@ deconv_dxg_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         mbar_wait(&full_bar[stage], phase);
         tc_fence_after();
         const uint32_t a_addr = smem_u32(ring + stage * stage_bytes);
-        const uint32_t b_addr = RESIDENT ? smem_u32(wres + st * DXG_B_BYTES) : a_addr + A_TILE_BYTES;
+        const uint32_t b_addr = RESIDENT ? smem_u32(wres + st * B_BYTES) : a_addr + A_TILE_BYTES;
         if (elect_one()) {
           const uint64_t a_desc = make_sw128_kmajor_desc(a_addr, 0);
           const uint64_t b_desc = make_sw128_kmajor_desc(b_addr, 0);
@@ -145,21 +155,23 @@ deconv_dxg_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     }
     int local = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++local) {
-      const int m0 = tile * DXG_ROWS_OUT;
+      const int m0 = tile * ROWS_OUT;
       const int buf = local & 1;
       const uint32_t use = (uint32_t)(local >> 1);
       mbar_wait(&tfull_bar[buf], use & 1);
       tc_fence_after();
-      const int r = m0 + DXG_SEG * lg + lane;                 // output row of this thread (lanes 30, 31: helpers only)
+      const int r = m0 + SEG * lg + lane;                     // output row of this thread (grouped: lanes 30, 31 are helpers only)
       const int q = r % rp;
       const int y = q / wp, x = q % wp;
-      const bool in_range = (lane < DXG_SEG) && (r < p.rows);
+      const bool in_range = (lane < SEG) && (r < p.rows);
       const bool is_pixel = in_range && (x < p.w) && (y < p.h);
       const uint32_t t_row = tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(buf * ACC_STRIDE);
       uint32_t v0[32], v1[32], v2[32];                        // 16 used
       tmem_ld16(t_row + (uint32_t)c0, v0);
-      tmem_ld16(t_row + (uint32_t)(64 + c0), v1);
-      tmem_ld16(t_row + (uint32_t)(128 + c0), v2);
+      if constexpr (GROUPED) {
+        tmem_ld16(t_row + (uint32_t)(64 + c0), v1);
+        tmem_ld16(t_row + (uint32_t)(128 + c0), v2);
+      }
       tmem_ld_wait();
       // the accumulator is in registers: hand the TMEM buffer back before the arithmetic and the stores
       tc_fence_before();
@@ -182,8 +194,9 @@ deconv_dxg_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         float s[2];
 #pragma unroll
         for (int e = 0; e < 2; ++e) {
-          float t = __uint_as_float(v0[c + e]) + __shfl_down_sync(0xffffffffu, __uint_as_float(v1[c + e]), 1) +
-                    __shfl_down_sync(0xffffffffu, __uint_as_float(v2[c + e]), 2);
+          float t = __uint_as_float(v0[c + e]);
+          if constexpr (GROUPED)
+            t += __shfl_down_sync(0xffffffffu, __uint_as_float(v1[c + e]), 1) + __shfl_down_sync(0xffffffffu, __uint_as_float(v2[c + e]), 2);
           if constexpr (EPI & 1) t += bias_r[c + e];
           s[e] = fmaxf(t, relu_lo);
         }
@@ -196,8 +209,8 @@ deconv_dxg_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       const bool issuer = (warp == 2) && (lane == 0);
       if (issuer) tma_store_wait_read();                      // the previous tile's store has read the staging tile
       named_barrier_sync(1, 32 * DXG_EPI_WARPS);
-      if (lane < DXG_SEG) {
-        const int row_local = DXG_SEG * lg + lane;
+      if (lane < SEG) {
+        const int row_local = SEG * lg + lane;
         const int j = c0 >> 3;                                // 16-byte chunk index of this thread's first 8 channels
         uint8_t* rowp = out_tile + row_local * 128;
         *reinterpret_cast<uint4*>(rowp + (((j) ^ (row_local & 7)) << 4)) = make_uint4(packed[0], packed[1], packed[2], packed[3]);
