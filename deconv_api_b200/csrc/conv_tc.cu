@@ -490,7 +490,7 @@ int launch_tc(dcv_ctx* ctx, const CUtensorMap& ta, const CUtensorMap& tb, TcPara
   }
   const int tiles = p.m_tiles * p.n_tiles;
   const int grid = std::min(tiles, ctx->num_sms);
-  deconv_tc_kernel<BLOCK_N, MODE><<<grid, NUM_THREADS, smem, ctx->stream>>>(ta, tb, p);
+  deconv_tc_kernel<BLOCK_N, MODE><<<grid, TC1_THREADS, smem, ctx->stream>>>(ta, tb, p);
   ctx->launches++;
   e = cudaGetLastError();
   if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "deconv_tc_kernel<%d,%d> launch: %s", BLOCK_N, MODE, cudaGetErrorString(e));

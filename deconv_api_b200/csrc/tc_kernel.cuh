@@ -21,7 +21,8 @@ constexpr int BLOCK_K = 64;                 // bf16 elements = 128 bytes = one s
 constexpr int A_TILE_BYTES = BLOCK_M * 128;
 constexpr int BAND_ROWS = 136;              // 128 + 2 halo rows, rounded up to the 8-row swizzle atom
 constexpr int A_BAND_BYTES = BAND_ROWS * 128;
-constexpr int NUM_THREADS = 192;
+constexpr int NUM_THREADS = 192;            // pair / exact kernels: TMA warp, MMA warp, 4 epilogue warps
+constexpr int TC1_THREADS = 320;            // deconv_tc_kernel: 8 epilogue warps (two per TMEM lane quarter, alternating column chunks)
 constexpr int SMEM_BUDGET = 200 * 1024;
 
 enum { MODE_TAP = 0, MODE_BAND = 1, MODE_BAND_RES = 2 };
@@ -132,7 +133,7 @@ __device__ __forceinline__ void store_bf16_chunk(const TcParams& p, const uint32
 }
 
 template <int BLOCK_N, int MODE>
-__global__ void __launch_bounds__(NUM_THREADS, 1)
+__global__ void __launch_bounds__(TC1_THREADS, 1)
 deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, TcParams p) {
   constexpr int B_TILE_BYTES = BLOCK_N * 128;
   // One TMEM accumulator per tile buffer.  (Rotating the K steps over several accumulators was measured to give no
@@ -162,7 +163,7 @@ deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     tma_prefetch_desc(&tmap_a);
     tma_prefetch_desc(&tmap_b);
     for (int s = 0; s < p.stages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-    for (int b = 0; b < 2; ++b) { mbar_init(&tfull_bar[b], 1); mbar_init(&tempty_bar[b], 4); }
+    for (int b = 0; b < 2; ++b) { mbar_init(&tfull_bar[b], 1); mbar_init(&tempty_bar[b], 8); }
     mbar_init(wres_bar, 1);
     fence_barrier_init();
   }
@@ -282,8 +283,11 @@ deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       }
     }
   } else {
-    // ===== epilogue warps 2..5: TMEM lane group = warp % 4 =====
+    // ===== epilogue warps 2..9: TMEM lane group = warp % 4; warps 2-5 take the even column chunks, 6-9 the odd ones.
+    // One warp per sub-partition runs at ~11 cycles per instruction (latency-bound), which made the epilogue - not the
+    // MMAs - the pace of every layer with few K steps per tile (forward convs with bias, K = 64 layers) =====
     const int lg = warp & 3;
+    const int half = (warp - 2) >> 2;
     const int rp = (p.h + 1) * wp;
     const float relu_lo = p.relu ? 0.f : -INFINITY;
     int local = 0;
@@ -302,7 +306,7 @@ deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       const uint32_t t_row = tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(buf * ACC_COLS);
       constexpr int CHUNK = BLOCK_N >= 32 ? 32 : 16;
 #pragma unroll 1
-      for (int c0 = 0; c0 < BLOCK_N; c0 += CHUNK) {
+      for (int c0 = half * CHUNK; c0 < BLOCK_N; c0 += 2 * CHUNK) {
         uint32_t v[32];
         if constexpr (CHUNK == 32) tmem_ld32(t_row + (uint32_t)c0, v);
         else tmem_ld16(t_row + (uint32_t)c0, v);
@@ -324,10 +328,22 @@ deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             // ReLU and pad masking branch-free.  One epilogue warp per sub-partition is latency-bound, so its
             // instruction count is the epilogue's duration.
             if (p.bias) {
+              if ((p.n_real & 3) == 0 && n0 + c0 + CHUNK <= p.n_real) {
+                const float4* bp = reinterpret_cast<const float4*>(p.bias + n0 + c0);
 #pragma unroll
-              for (int i = 0; i < CHUNK; ++i) {
-                const int c = n0 + c0 + i;
-                if (c < p.n_real) v[i] = __float_as_uint(__uint_as_float(v[i]) + __ldg(p.bias + c));
+                for (int i = 0; i < CHUNK / 4; ++i) {
+                  const float4 b4 = __ldg(bp + i);
+                  v[4 * i] = __float_as_uint(__uint_as_float(v[4 * i]) + b4.x);
+                  v[4 * i + 1] = __float_as_uint(__uint_as_float(v[4 * i + 1]) + b4.y);
+                  v[4 * i + 2] = __float_as_uint(__uint_as_float(v[4 * i + 2]) + b4.z);
+                  v[4 * i + 3] = __float_as_uint(__uint_as_float(v[4 * i + 3]) + b4.w);
+                }
+              } else {
+#pragma unroll
+                for (int i = 0; i < CHUNK; ++i) {
+                  const int c = n0 + c0 + i;
+                  if (c < p.n_real) v[i] = __float_as_uint(__uint_as_float(v[i]) + __ldg(p.bias + c));
+                }
               }
             }
 #pragma unroll
