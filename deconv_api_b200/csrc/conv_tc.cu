@@ -814,7 +814,7 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
         if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "cudaFuncSetAttribute(exact kernel): %s", cudaGetErrorString(e)); \
         smem_set[ctx->device & 63] = smem;                                                                         \
       }                                                                                                            \
-      conv_exact_kernel<BN><<<grid, NUM_THREADS, smem, ctx->stream>>>(ta, tb, p);                                  \
+      conv_exact_kernel<BN><<<grid, EXACT_THREADS, smem, ctx->stream>>>(ta, tb, p);                                  \
     }
     switch (bn) {
       case 16: EXACT_LAUNCH(16) break;

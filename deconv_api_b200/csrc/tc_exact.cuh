@@ -24,8 +24,10 @@ constexpr int EXACT_SLOTS = 4;
 
 __host__ __device__ inline int exact_stage_bytes(int block_n) { return A_BAND_BYTES + 3 * block_n * 128; }
 
+constexpr int EXACT_THREADS = 320;   // TMA warp, MMA warp, 8 accumulate warps (two per TMEM lane quarter, half of the columns each)
+
 template <int BLOCK_N>
-__global__ void __launch_bounds__(NUM_THREADS, 1)
+__global__ void __launch_bounds__(EXACT_THREADS, 1)
 conv_exact_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, TcParams p) {
   constexpr int B_TILE_BYTES = BLOCK_N * 128;
   constexpr int TMEM_COLS = EXACT_SLOTS * BLOCK_N < 32 ? 32 : EXACT_SLOTS * BLOCK_N;
@@ -46,7 +48,7 @@ conv_exact_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     tma_prefetch_desc(&tmap_a);
     tma_prefetch_desc(&tmap_b);
     for (int s = 0; s < p.stages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-    for (int s = 0; s < EXACT_SLOTS; ++s) { mbar_init(&sfull_bar[s], 1); mbar_init(&sempty_bar[s], 4); }
+    for (int s = 0; s < EXACT_SLOTS; ++s) { mbar_init(&sfull_bar[s], 1); mbar_init(&sempty_bar[s], 8); }
     fence_barrier_init();
   }
   if (warp == 1) {
@@ -121,30 +123,35 @@ conv_exact_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     }
   } else {
     // ===== accumulate + epilogue warps 2..5: TMEM lane group = warp % 4, one output row per thread =====
+    // (one warp per sub-partition runs at ~11 cycles per instruction; with four warps the adds of an N = 128 stage
+    // took longer than its MMAs)
     const int lg = warp & 3;
+    constexpr int COLS = BLOCK_N >= 32 ? BLOCK_N / 2 : BLOCK_N;      // columns owned by this warp
+    const int cbase = BLOCK_N >= 32 ? ((warp - 2) >> 2) * COLS : 0;
+    const bool owner = BLOCK_N >= 32 || warp < 6;                    // N = 16: warps 6-9 only keep the barriers balanced
     const int rp = (p.h + 1) * wp;
     uint32_t chunk = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
       const int m0 = (tile / p.n_tiles) * BLOCK_M;
-      const int n0 = (tile % p.n_tiles) * BLOCK_N;
-      float acc[BLOCK_N];
+      const int n0 = (tile % p.n_tiles) * BLOCK_N + cbase;
+      float acc[COLS];
 #pragma unroll
-      for (int i = 0; i < BLOCK_N; ++i) acc[i] = 0.f;
+      for (int i = 0; i < COLS; ++i) acc[i] = 0.f;
       for (int st = 0; st < total_st; ++st, ++chunk) {
         const uint32_t slot = chunk % EXACT_SLOTS, suse = chunk / EXACT_SLOTS;
         mbar_wait(&sfull_bar[slot], suse & 1);
         tc_fence_after();
-        const uint32_t t_row = tmem_base + ((uint32_t)(lg * 32) << 16) + slot * BLOCK_N;
-        if constexpr (BLOCK_N >= 32) {
+        const uint32_t t_row = tmem_base + ((uint32_t)(lg * 32) << 16) + slot * BLOCK_N + (uint32_t)cbase;
+        if constexpr (BLOCK_N >= 64) {
 #pragma unroll
-          for (int c0 = 0; c0 < BLOCK_N; c0 += 32) {
+          for (int c0 = 0; c0 < COLS; c0 += 32) {
             uint32_t v[32];
             tmem_ld32(t_row + (uint32_t)c0, v);
             tmem_ld_wait();
 #pragma unroll
             for (int i = 0; i < 32; ++i) acc[c0 + i] += __uint_as_float(v[i]);
           }
-        } else {
+        } else if (owner) {
           uint32_t v[32];
           tmem_ld16(t_row, v);
           tmem_ld_wait();
@@ -159,12 +166,12 @@ conv_exact_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       const int r = m0 + lg * 32 + lane;
       const int q = r % rp;
       const int y = q / wp, x = q % wp;
-      if (r < p.rows && x < p.w && y < p.h) {
+      if (owner && r < p.rows && x < p.w && y < p.h) {
         const int item = r / rp;
         float* dst = p.out_f32 + (((size_t)item * p.h + y) * p.w + x) * p.n_real + n0;
-        if ((p.n_real & 3) == 0 && n0 + BLOCK_N <= p.n_real) {
+        if ((p.n_real & 3) == 0 && n0 + COLS <= p.n_real) {
 #pragma unroll
-          for (int i = 0; i < BLOCK_N; i += 4) {
+          for (int i = 0; i < COLS; i += 4) {
             float a[4];
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
@@ -176,7 +183,7 @@ conv_exact_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           }
         } else {
 #pragma unroll
-          for (int i = 0; i < BLOCK_N; ++i) {
+          for (int i = 0; i < COLS; ++i) {
             if (n0 + i < p.n_real) {
               float a = acc[i];
               if (p.bias) a += __ldg(p.bias + n0 + i);
