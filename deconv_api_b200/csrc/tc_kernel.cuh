@@ -22,7 +22,8 @@ constexpr int A_TILE_BYTES = BLOCK_M * 128;
 constexpr int BAND_ROWS = 136;              // 128 + 2 halo rows, rounded up to the 8-row swizzle atom
 constexpr int A_BAND_BYTES = BAND_ROWS * 128;
 constexpr int NUM_THREADS = 192;            // pair / exact kernels: TMA warp, MMA warp, 4 epilogue warps
-constexpr int TC1_THREADS = 320;            // deconv_tc_kernel: 8 epilogue warps (two per TMEM lane quarter, alternating column chunks)
+constexpr int TC1_EPI_WARPS = 8;            // deconv_tc_kernel: two epilogue warps per TMEM lane quarter, interleaved column chunks (16 measured equal)
+constexpr int TC1_THREADS = 64 + 32 * TC1_EPI_WARPS;
 constexpr int SMEM_BUDGET = 200 * 1024;
 
 enum { MODE_TAP = 0, MODE_BAND = 1, MODE_BAND_RES = 2 };
@@ -163,7 +164,7 @@ deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     tma_prefetch_desc(&tmap_a);
     tma_prefetch_desc(&tmap_b);
     for (int s = 0; s < p.stages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-    for (int b = 0; b < 2; ++b) { mbar_init(&tfull_bar[b], 1); mbar_init(&tempty_bar[b], 8); }
+    for (int b = 0; b < 2; ++b) { mbar_init(&tfull_bar[b], 1); mbar_init(&tempty_bar[b], TC1_EPI_WARPS); }
     mbar_init(wres_bar, 1);
     fence_barrier_init();
   }
@@ -287,7 +288,8 @@ deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     // One warp per sub-partition runs at ~11 cycles per instruction (latency-bound), which made the epilogue - not the
     // MMAs - the pace of every layer with few K steps per tile (forward convs with bias, K = 64 layers) =====
     const int lg = warp & 3;
-    const int half = (warp - 2) >> 2;
+    const int sub = (warp - 2) >> 2;
+    constexpr int NSUB = TC1_EPI_WARPS / 4;
     const int rp = (p.h + 1) * wp;
     const float relu_lo = p.relu ? 0.f : -INFINITY;
     int local = 0;
@@ -304,9 +306,9 @@ deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       const bool in_range = r < p.rows;
       const bool is_pixel = in_range && (x < p.w) && (y < p.h);
       const uint32_t t_row = tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(buf * ACC_COLS);
-      constexpr int CHUNK = BLOCK_N >= 32 ? 32 : 16;
+      constexpr int CHUNK = BLOCK_N >= 32 * NSUB ? 32 : 16;
 #pragma unroll 1
-      for (int c0 = half * CHUNK; c0 < BLOCK_N; c0 += 2 * CHUNK) {
+      for (int c0 = sub * CHUNK; c0 < BLOCK_N; c0 += NSUB * CHUNK) {
         uint32_t v[32];
         if constexpr (CHUNK == 32) tmem_ld32(t_row + (uint32_t)c0, v);
         else tmem_ld16(t_row + (uint32_t)c0, v);
