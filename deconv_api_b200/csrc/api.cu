@@ -693,7 +693,8 @@ static int project_impl(dcv_ctx* ctx, int layer, const int* feat, int n, int vis
   // Host output: split into >= 4 chunks so that the device-to-host copy of chunk i (second stream) overlaps
   // the kernels of chunk i+1; each chunk still carries >= 32 feature maps, far more rows than the GPU needs.
   const bool pipelined = !out_on_device && n >= 64;
-  if (pipelined) chunk = std::min(chunk, std::max(32, (n + 3) / 4));
+  static const int pipe_chunks = getenv("DCV_PIPE_CHUNKS") ? std::max(1, atoi(getenv("DCV_PIPE_CHUNKS"))) : 4;
+  if (pipelined) chunk = std::min(chunk, std::max(32, (n + pipe_chunks - 1) / pipe_chunks));
   TRY(ctx->ws[0].ensure(ctx, (size_t)chunk * B * max_elems * sizeof(float)));
   TRY(ctx->ws[1].ensure(ctx, (size_t)chunk * B * max_elems * sizeof(float)));
   if (max_split) TRY(ctx->ws[4].ensure(ctx, (size_t)chunk * B * max_split * sizeof(__nv_bfloat16)));
