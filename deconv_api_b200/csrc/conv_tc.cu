@@ -135,9 +135,13 @@ __global__ void pack_weights_fwd3_kernel(const float* __restrict__ w, int kdim, 
 // 16 mantissa bits, the weights are bf16 like everywhere else in the bf16 chain.  One thread per padded row.
 template <int C>
 __global__ void __launch_bounds__(128)
-im2col_first_kernel(const float* __restrict__ x, int P, int h, int w, __nv_bfloat16* __restrict__ out) {
+im2col_first_kernel(const float* __restrict__ x, int P, int h, int w, const int* __restrict__ jit,
+                    __nv_bfloat16* __restrict__ out) {
   // one thread per padded row (measured: a 16-byte-chunk-per-thread form with coalesced stores is 3x slower,
-  // the index arithmetic dominates)
+  // the index arithmetic dominates).  jit (optional): {counter, oy0, ox0, ...} - the rows are taken from the image
+  // rolled by (oy, ox) of iteration `counter` (numpy.roll), i.e. DeepDream's jitter is folded into this gather.
+  int roll_y = 0, roll_x = 0;
+  if (jit) { const int c = jit[0]; roll_y = jit[1 + 2 * c] % h; roll_x = jit[2 + 2 * c] % w; if (roll_y < 0) roll_y += h; if (roll_x < 0) roll_x += w; }
   const int wp = w + 1, rp = (h + 1) * wp;
   const size_t total = (size_t)P * rp;
   for (size_t r = (size_t)blockIdx.x * blockDim.x + threadIdx.x; r < total; r += (size_t)gridDim.x * blockDim.x) {
@@ -153,9 +157,11 @@ im2col_first_kernel(const float* __restrict__ x, int P, int h, int w, __nv_bfloa
       for (int t = 0; t < 9; ++t) {
         const int yy = y + t / 3 - 1, xs = xx + t % 3 - 1;
         if (yy >= 0 && yy < h && xs >= 0 && xs < w) {
+          int sy = yy - roll_y; if (sy < 0) sy += h;          // rolled[yy][xs] = img[(yy - oy) mod h][(xs - ox) mod w]
+          int sx = xs - roll_x; if (sx < 0) sx += w;
 #pragma unroll
           for (int c = 0; c < C; ++c) {
-            const float v = __ldg(img + ((size_t)yy * w + xs) * C + c);
+            const float v = __ldg(img + ((size_t)sy * w + sx) * C + c);
             const __nv_bfloat16 hi = __float2bfloat16(v);
             row[t * C + c] = hi;
             row[9 * C + t * C + c] = __float2bfloat16(v - __bfloat162float(hi));
@@ -674,7 +680,7 @@ int tc_conv_bwd_exact(dcv_ctx* ctx, const Layer& l, const float* in, int P, int 
 
 bool tc_first_layer_ok(const Layer& l) { return l.kind == LK_CONV && l.cin >= 1 && l.cin <= 3; }
 
-int tc_conv_first(dcv_ctx* ctx, Layer& l, const float* x, int P, int h, int w, __nv_bfloat16* out_bf16) {
+int tc_conv_first(dcv_ctx* ctx, Layer& l, const float* x, int P, int h, int w, __nv_bfloat16* out_bf16, const int* jit) {
   if (!tc_first_layer_ok(l)) return ctx->fail(DCV_ERR_UNSUPPORTED, "tc_conv_first: %d input channels", l.cin);
   const int n_pad = tc_cpad(l.cout);
   if (!l.tc.wf0_bf16) {
@@ -691,9 +697,9 @@ int tc_conv_first(dcv_ctx* ctx, Layer& l, const float* x, int P, int h, int w, _
     ProfScope ps(ctx, DCV_K_OTHER, 0.0, 4.0 * P * h * w * l.cin + 128.0 * rows);
     const int grid = grid_for(rows, 128);
     switch (l.cin) {
-      case 1: im2col_first_kernel<1><<<grid, 128, 0, ctx->stream>>>(x, P, h, w, cols); break;
-      case 2: im2col_first_kernel<2><<<grid, 128, 0, ctx->stream>>>(x, P, h, w, cols); break;
-      default: im2col_first_kernel<3><<<grid, 128, 0, ctx->stream>>>(x, P, h, w, cols); break;
+      case 1: im2col_first_kernel<1><<<grid, 128, 0, ctx->stream>>>(x, P, h, w, jit, cols); break;
+      case 2: im2col_first_kernel<2><<<grid, 128, 0, ctx->stream>>>(x, P, h, w, jit, cols); break;
+      default: im2col_first_kernel<3><<<grid, 128, 0, ctx->stream>>>(x, P, h, w, jit, cols); break;
     }
     ctx->launches++;
   }

@@ -359,17 +359,24 @@ int dream_backward(dcv_ctx* ctx, const LossSpec& ls, float** grad, double* loss_
 // ---- bf16 / tensor-core variant: the tape lives in the padded-flat bf16 layout of conv_tc.cu -------------
 // Forward: layer 0 (3 input channels, K = 27) stays on the FFMA kernel and is converted; every other conv is
 // tc_conv_fwd (tcgen05, bias + ReLU epilogue), pools are tc_pool.  x is a device pointer (B,H,W,C0) fp32.
-int dream_forward_bf16(dcv_ctx* ctx, const float* x, int B, int H, int W, int upto) {
+bool dream_first_on_tc(const dcv_ctx* ctx) {
+  static const int first_tc = getenv("DCV_DREAM_FIRST_TC") ? atoi(getenv("DCV_DREAM_FIRST_TC")) : 1;
+  return first_tc && !ctx->net.empty() && tc_first_layer_ok(ctx->net[0]);
+}
+
+// x: the image the forward pass sees; with jit != null (and the first layer on the tensor cores) x is the UN-rolled
+// image and the jitter roll is applied by the first layer's gather
+int dream_forward_bf16(dcv_ctx* ctx, const float* x, int B, int H, int W, int upto, const int* jit = nullptr) {
   if (ctx->net.empty() || ctx->net[0].kind != LK_CONV) return ctx->fail(DCV_ERR_STATE, "dream: network must start with a conv layer");
   ctx->tape_upto = -1;                      // the fp32 projection tape is not valid after this
   Layer& l0 = ctx->net[0];
   ctx->in_B = B; ctx->in_H = H; ctx->in_W = W; ctx->in_C = l0.cin;
   TRYD(l0.act_h.ensure(ctx, (size_t)B * tc_padded_elems(H, W, l0.cout) * sizeof(__nv_bfloat16)));
-  static const int first_tc = getenv("DCV_DREAM_FIRST_TC") ? atoi(getenv("DCV_DREAM_FIRST_TC")) : 1;
-  if (first_tc && tc_first_layer_ok(l0)) {
+  if (dream_first_on_tc(ctx)) {
     // K = 27: im2col rows + one un-shifted tcgen05 GEMM writing the bf16 tape directly
-    TRYD(tc_conv_first(ctx, l0, x, B, H, W, (__nv_bfloat16*)l0.act_h.p));
+    TRYD(tc_conv_first(ctx, l0, x, B, H, W, (__nv_bfloat16*)l0.act_h.p, jit));
   } else {
+    if (jit) return ctx->fail(DCV_ERR_STATE, "dream: fused jitter needs the tensor-core first layer");
     TRYD(l0.act.ensure(ctx, (size_t)B * H * W * l0.cout * sizeof(float)));
     {
       ConvEpilogue e; e.bias = l0.bias; e.relu = l0.relu;
@@ -486,16 +493,18 @@ int dream_backward_bf16(dcv_ctx* ctx, const LossSpec& ls, float** grad, double* 
 int dream_iter(dcv_ctx* ctx, float* img, int B, int H, int W, int C, const LossSpec& ls, float step, const int* jit_dev,
                double* loss_out, int precision) {
   const size_t n = (size_t)B * H * W * C;
-  TRYD(ctx->dream[3].ensure(ctx, n * sizeof(float)));
-  float* x = (float*)ctx->dream[3].p;
-  {
+  const bool fused_roll = precision == DCV_BF16 && dream_first_on_tc(ctx);   // the first layer's gather applies the jitter
+  float* x = img;
+  if (!fused_roll) {
+    TRYD(ctx->dream[3].ensure(ctx, n * sizeof(float)));
+    x = (float*)ctx->dream[3].p;
     ProfScope ps(ctx, DCV_K_OTHER, 0.0, 8.0 * n);
     launch_roll_impl(img, B, H, W, C, 0, 0, jit_dev, x, ctx->stream); ctx->launches++;
   }
   float* g = nullptr;
   if (precision == DCV_BF16) {
     struct Latency { dcv_ctx* c; Latency(dcv_ctx* c_) : c(c_) { c->latency_tiles = 1; } ~Latency() { c->latency_tiles = 0; } } lat(ctx);
-    TRYD(dream_forward_bf16(ctx, x, B, H, W, ls.deepest));
+    TRYD(dream_forward_bf16(ctx, x, B, H, W, ls.deepest, fused_roll ? jit_dev : nullptr));
     TRYD(dream_backward_bf16(ctx, ls, &g, loss_out));
   } else {
     TRYD(forward_impl(ctx, x, true, B, H, W, ls.deepest));
@@ -507,7 +516,8 @@ int dream_iter(dcv_ctx* ctx, float* img, int B, int H, int W, int C, const LossS
   for (int b = 0; b < B; ++b) {          // the RMS normalisation is per image
     ProfScope ps(ctx, DCV_K_OTHER, 0.0, 16.0 * per);
     launch_sum_stats(g + b * per, per, (double*)ctx->scratch.p, np, ctx->stream);
-    dream_update_kernel<<<grid_for(per, 256, 8), 256, 0, ctx->stream>>>(img + b * per, g + b * per, (const double*)ctx->scratch.p, np,
+    // few, fat blocks: every block first reduces the block partials of the RMS
+    dream_update_kernel<<<(int)std::min<size_t>(std::max<size_t>((per + 4095) / 4096, 1), 4 * kNumSMs), 256, 0, ctx->stream>>>(img + b * per, g + b * per, (const double*)ctx->scratch.p, np,
                                                                          H, W, C, step, 0, 0, jit_dev);
     ctx->launches += 2;
   }

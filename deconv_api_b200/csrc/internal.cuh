@@ -112,7 +112,8 @@ int tc_prepare_forward(dcv_ctx* ctx, Layer& l);
 // first conv layer (cin <= 4) of the bf16 DeepDream forward: fp32 image (P,h,w,cin) -> bf16 padded-flat activations;
 // im2col rows (9*cin values as bf16 hi + lo planes, K = 64) + one un-shifted GEMM with bias / ReLU epilogue
 bool tc_first_layer_ok(const Layer& l);
-int tc_conv_first(dcv_ctx* ctx, Layer& l, const float* x, int P, int h, int w, __nv_bfloat16* out_bf16);
+int tc_conv_first(dcv_ctx* ctx, Layer& l, const float* x, int P, int h, int w, __nv_bfloat16* out_bf16,
+                  const int* jit = nullptr);      // jit: device jitter table, the image is read rolled (DeepDream)
 // fp32-accurate forward conv on tcgen05 (bf16 x 3 operand split, six products); fp32 compact in and out
 int tc_prepare_forward_exact(dcv_ctx* ctx, Layer& l);
 int tc_conv_fwd_exact(dcv_ctx* ctx, const Layer& l, const float* in, int P, int h, int w, float* out);
