@@ -690,10 +690,11 @@ static int project_impl(dcv_ctx* ctx, int layer, const int* feat, int n, int vis
                     (size_t)B * max_split * sizeof(__nv_bfloat16);
   int chunk = (int)std::max<size_t>(1, ctx->workspace_budget / per_feat);
   chunk = std::min(chunk, n);
-  // Host output: split into >= 4 chunks so that the device-to-host copy of chunk i (second stream) overlaps
-  // the kernels of chunk i+1; each chunk still carries >= 32 feature maps, far more rows than the GPU needs.
+  // Host output: split into chunks so that the device-to-host copy of chunk i (second stream) overlaps the kernels
+  // of chunk i+1; each chunk still carries >= 32 feature maps, far more rows than the GPU needs.  Measured with the
+  // tapered tail below (512 maps): 2 base chunks (256,128,64,32,32) 40.2 k proj/s end to end, 3: 38.7, 4: 39.6, 5: 38.7.
   const bool pipelined = !out_on_device && n >= 64;
-  static const int pipe_chunks = getenv("DCV_PIPE_CHUNKS") ? std::max(1, atoi(getenv("DCV_PIPE_CHUNKS"))) : 4;
+  static const int pipe_chunks = getenv("DCV_PIPE_CHUNKS") ? std::max(1, atoi(getenv("DCV_PIPE_CHUNKS"))) : 2;
   if (pipelined) chunk = std::min(chunk, std::max(32, (n + pipe_chunks - 1) / pipe_chunks));
   TRY(ctx->ws[0].ensure(ctx, (size_t)chunk * B * max_elems * sizeof(float)));
   TRY(ctx->ws[1].ensure(ctx, (size_t)chunk * B * max_elems * sizeof(float)));
@@ -712,9 +713,21 @@ static int project_impl(dcv_ctx* ctx, int layer, const int* feat, int n, int vis
   if (pipelined) {
     for (int i = 0; i < 2; ++i) TRY(ctx->out_stage[i].ensure(ctx, (size_t)chunk * out_elems * sizeof(float)));
   }
-  int ci = 0;
-  for (int f0 = 0; f0 < n; f0 += chunk, ++ci) {
-    const int nf = std::min(chunk, n - f0);
+  // Chunk schedule.  Host output: the copy of the LAST chunk is the only one nothing overlaps, so the last chunk is
+  // halved repeatedly (128 -> 64, 32, 32): 0.34 ms of exposed copy instead of 1.4 ms for 512 maps of 224x224x3.
+  std::vector<int> sizes;
+  for (int f0 = 0; f0 < n; f0 += chunk) sizes.push_back(std::min(chunk, n - f0));
+  static const int taper = getenv("DCV_PIPE_TAPER") ? atoi(getenv("DCV_PIPE_TAPER")) : 32;
+  if (pipelined && taper > 0 && !sizes.empty()) {
+    int last = sizes.back();
+    sizes.pop_back();
+    while (last > 2 * taper) { const int half = (last / 2 + 7) / 8 * 8; sizes.push_back(half); last -= half; }
+    if (last > taper) { sizes.push_back(last - taper); last = taper; }
+    sizes.push_back(last);
+  }
+  int ci = 0, f0 = 0;
+  for (size_t k = 0; k < sizes.size(); f0 += sizes[k], ++k, ++ci) {
+    const int nf = sizes[k];
     float* res = nullptr;
     float* dst = out + (size_t)f0 * out_elems;
     if (pipelined) {
