@@ -76,6 +76,22 @@ __device__ __forceinline__ void split3(float x, __nv_bfloat16& h, __nv_bfloat16&
   l = __float2bfloat16_rn(r1 - __bfloat162float(m));
 }
 
+// the all-tap weights of pack_weights_alltap_kernel as three planes: out [3][32][k_pad]
+__global__ void pack_weights_alltap3_kernel(const float* __restrict__ wd, int kdim, int ndim, int k_pad, __nv_bfloat16* __restrict__ out) {
+  const int total = 32 * k_pad;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int k = i % k_pad, row = i / k_pad;
+    float v = 0.f;
+    if (row < 9 * ndim && k < kdim) {
+      const int t = row / ndim, c = row % ndim;
+      v = __ldg(wd + ((size_t)t * kdim + k) * ndim + c);
+    }
+    __nv_bfloat16 h, m, l;
+    split3(v, h, m, l);
+    out[i] = h; out[total + i] = m; out[2 * total + i] = l;
+  }
+}
+
 // fp32 compact (P,h,w,C) -> padded-flat bf16 with THREE planes per row: columns [hi | mid | lo], c_pad each.
 __global__ void split3_pad_kernel(const float* __restrict__ x, int P, int h, int w, int C, int c_pad,
                                   __nv_bfloat16* __restrict__ out) {
@@ -553,6 +569,8 @@ void tc_free_layer(Layer& l) {
   if (l.tc.wall_bf16) cudaFree(l.tc.wall_bf16);
   if (l.tc.wf3_bf16) cudaFree(l.tc.wf3_bf16);
   if (l.tc.wd3_bf16) cudaFree(l.tc.wd3_bf16);
+  if (l.tc.wall3_bf16) cudaFree(l.tc.wall3_bf16);
+  l.tc.wall3_bf16 = nullptr;
   if (l.tc.wf0_bf16) cudaFree(l.tc.wf0_bf16);
   l.tc.wf0_bf16 = nullptr;
   l.tc.wd_bf16 = l.tc.wf_bf16 = l.tc.wall_bf16 = l.tc.wf3_bf16 = l.tc.wd3_bf16 = nullptr;
@@ -658,6 +676,12 @@ int tc_prepare_backward_exact(dcv_ctx* ctx, Layer& l) {
   if (e != cudaSuccess) return ctx->fail(DCV_ERR_NOMEM, "cudaMalloc(split backward weights): %s", cudaGetErrorString(e));
   pack_weights_fwd3_kernel<<<grid_for(n / 3, 256), 256, 0, ctx->stream>>>(l.wd, l.cout, l.cin, k_pad, n_pad, l.tc.wd3_bf16);
   ctx->launches++;
+  if (9 * l.cin <= LAST_N) {          // narrow last layer: all-tap weights for the exact GEMM + col2im kernel
+    e = cudaMalloc(&l.tc.wall3_bf16, (size_t)3 * LAST_N * k_pad * sizeof(__nv_bfloat16));
+    if (e != cudaSuccess) return ctx->fail(DCV_ERR_NOMEM, "cudaMalloc(split all-tap weights): %s", cudaGetErrorString(e));
+    pack_weights_alltap3_kernel<<<grid_for((size_t)LAST_N * k_pad, 256), 256, 0, ctx->stream>>>(l.wd, l.cout, l.cin, k_pad, l.tc.wall3_bf16);
+    ctx->launches++;
+  }
   return 0;
 }
 
@@ -672,6 +696,39 @@ int tc_conv_bwd_exact(dcv_ctx* ctx, const Layer& l, const float* in, int P, int 
     ProfScope ps(ctx, DCV_K_OTHER, 0.0, 4.0 * P * h * w * l.cout + 6.0 * P * (h + 1) * (w + 1) * k_pad);
     split3_pad_kernel<<<grid_for(work, 256), 256, 0, ctx->stream>>>(in, P, h, w, l.cout, k_pad, (__nv_bfloat16*)ctx->ws[4].p);
     ctx->launches++;
+  }
+  static const int use_last = getenv("DCV_TC_LAST") ? atoi(getenv("DCV_TC_LAST")) : 1;
+  if (l.tc.wall3_bf16 && use_last) {
+    // narrow last layer: GEMM + col2im with split operands (tc_last.cuh, EXACT)
+    LastParams p;
+    p.P = P; p.h = h; p.w = w; p.cout = l.cin; p.k_blocks = k_pad / 64;
+    p.tiles_x = (w + LAST_T - 1) / LAST_T; p.tiles_y = (h + LAST_T - 1) / LAST_T;
+    const long long tt = (long long)P * p.tiles_x * p.tiles_y;
+    if (tt > 0x7FFFFFFFLL || (long long)P * (h + 1) > 0x7FFFFFFFLL) return ctx->fail(DCV_ERR_ARG, "tc_conv: too many tiles");
+    p.total_tiles = (int)tt;
+    p.relu = relu;
+    p.out = out;
+    CUtensorMap ta, tb;
+    r = make_tmap_patch(ctx, &ta, ctx->ws[4].p, (uint64_t)3 * k_pad, (uint64_t)(w + 1), (uint64_t)P * (h + 1));
+    if (r) return r;
+    r = make_tmap(ctx, &tb, l.tc.wall3_bf16, (uint64_t)3 * LAST_N, (uint64_t)k_pad, LAST_N);
+    if (r) return r;
+    const int smem = last_smem_bytes(p.k_blocks, 1);
+    if (smem <= 227 * 1024) {
+      static int smem_set[64] = {};
+      cudaError_t e = cudaSuccess;
+      if (smem_set[ctx->device & 63] < smem) {
+        e = cudaFuncSetAttribute(deconv_last_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+        smem_set[ctx->device & 63] = smem;
+      }
+      ProfScope ps(ctx, DCV_K_CONV_TC, 2.0 * 9 * P * h * w * (double)l.cin * l.cout, 2.0 * P * h * w * (3.0 * l.cout + 2.0 * l.cin));
+      deconv_last_kernel<1><<<std::min(p.total_tiles, ctx->num_sms), LAST_THREADS, smem, ctx->stream>>>(ta, tb, p);
+      ctx->launches++;
+      e = cudaGetLastError();
+      if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "deconv_last_kernel<exact> launch: %s", cudaGetErrorString(e));
+      return 0;
+    }
   }
   TcConvArgs a{l.tc.wd3_bf16, k_pad, n_pad, l.cout, l.cin, relu, nullptr, 6};
   a.prof_class = DCV_K_CONV_TC;
@@ -747,12 +804,12 @@ int tc_conv(dcv_ctx* ctx, const Layer& l, const __nv_bfloat16* in, int P, int h,
     static int smem_set[64] = {};
     cudaError_t e = cudaSuccess;
     if (smem_set[ctx->device & 63] < smem) {
-      e = cudaFuncSetAttribute(deconv_last_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+      e = cudaFuncSetAttribute(deconv_last_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
       if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
       smem_set[ctx->device & 63] = smem;
     }
     ProfScope ps(ctx, DCV_K_CONV_TC, 2.0 * 9 * P * h * w * (double)l.cin * l.cout, 2.0 * P * h * w * ((double)l.cout + 2.0 * l.cin));
-    deconv_last_kernel<<<std::min(p.total_tiles, ctx->num_sms), LAST_THREADS, smem, ctx->stream>>>(ta, tb, p);
+    deconv_last_kernel<0><<<std::min(p.total_tiles, ctx->num_sms), LAST_THREADS, smem, ctx->stream>>>(ta, tb, p);
     ctx->launches++;
     e = cudaGetLastError();
     if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "deconv_last_kernel launch: %s", cudaGetErrorString(e));

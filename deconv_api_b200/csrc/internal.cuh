@@ -18,6 +18,7 @@ struct TcWeights {
   __nv_bfloat16* wf_bf16 = nullptr;   // forward weights [9][fn_pad][fk_pad] (N = cout, K = cin); built on first bf16 DeepDream
   int fn_pad = 0, fk_pad = 0;
   __nv_bfloat16* wf0_bf16 = nullptr;  // first layer (cin <= 4) as a GEMM over im2col rows: [n_pad][64], taps x channels along K, twice (for the hi / lo planes of the input)
+  __nv_bfloat16* wall3_bf16 = nullptr; // all-tap weights of a narrow last layer split into three planes: [3][32][k_pad] (exact GEMM + col2im)
   __nv_bfloat16* wd3_bf16 = nullptr;  // backward (flipped, transposed) weights split the same way: [9][3][n_pad][k_pad] (exact projection)
   __nv_bfloat16* wf3_bf16 = nullptr;  // forward weights split into (hi, mid, lo) bf16 planes: [9][3][fn_pad][fk_pad] (exact forward)
   __nv_bfloat16* wall_bf16 = nullptr; // narrow last layer (9*cin <= 32): all taps stacked along N, [32][k_pad]

@@ -8,6 +8,12 @@
 // Tiles are 2-D patches so that the shifted rows stay inside the tile: 14x14 output pixels need the 16x16 halo
 // patch = 256 rows = two M=128 MMAs per 64-channel block; the patch is ONE 3-D TMA box (64 ch, 16 x, 16 y) over
 // the padded-flat tensor viewed as (C_pad, w+1, P*(h+1)).  4*k_blocks*2 MMAs per 196 pixels instead of 36 per 128.
+//
+// EXACT = 1 (fp32 projection mode): the operands are the three-plane bf16 splits of conv_tc.cu (activations: columns
+// [hi | mid | lo] of the padded-flat tensor; weights: three 32-row blocks).  One ring stage holds ONE plane's patch; the
+// planes arrive lo, mid, hi and the MMA warp issues the products each plane takes part in (lo*hi | mid*mid, mid*hi |
+// hi*lo, hi*mid, hi*hi), so the small correction products enter the TMEM accumulator first and only the four hi*hi
+// MMAs of a 64-channel block are added while it is large (the tensor core truncates on accumulate).
 #pragma once
 #include "common.cuh"
 #include "tc_ptx.cuh"
@@ -33,8 +39,8 @@ struct LastParams {
   float* out;                 // compact (P,h,w,cout) fp32
 };
 
-__host__ __device__ inline int last_smem_bytes(int k_blocks) {
-  return k_blocks * LAST_N * 128 + LAST_STAGES * LAST_A_BYTES + 2 * LAST_ROWS * LAST_PS * 4 + 1024 + 256;
+__host__ __device__ inline int last_smem_bytes(int k_blocks, int exact = 0) {
+  return (exact ? 3 : 1) * k_blocks * LAST_N * 128 + LAST_STAGES * LAST_A_BYTES + 2 * LAST_ROWS * LAST_PS * 4 + 1024 + 256;
 }
 
 __device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1, int c2) {
@@ -45,11 +51,13 @@ __device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* m, uin
       : "memory");
 }
 
+template <int EXACT>
 __global__ void __launch_bounds__(LAST_THREADS, 1)
 deconv_last_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, LastParams p) {
+  constexpr int NPLANES = EXACT ? 3 : 1;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  const int w_bytes = p.k_blocks * LAST_N * 128;
+  const int w_bytes = NPLANES * p.k_blocks * LAST_N * 128;   // resident weights [plane][k_block][32 rows][128 B]
   uint8_t* wres = smem;                                       // resident all-tap weights [k_block][32 rows][128 B]
   uint8_t* ring = smem + w_bytes;                             // A patches
   float* ps_base = reinterpret_cast<float*>(ring + LAST_STAGES * LAST_A_BYTES);  // two P tiles [256][LAST_PS]
@@ -85,17 +93,23 @@ deconv_last_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
   if (warp == 0) {
     if (lane == 0) {
       mbar_arrive_expect_tx(wres_bar, (uint32_t)w_bytes);
-      for (int kc = 0; kc < p.k_blocks; ++kc) tma_load_2d(wres + kc * LAST_N * 128, &tmap_b, wres_bar, kc * 64, 0);
+      for (int pl = 0; pl < NPLANES; ++pl)
+        for (int kc = 0; kc < p.k_blocks; ++kc)
+          tma_load_2d(wres + (pl * p.k_blocks + kc) * LAST_N * 128, &tmap_b, wres_bar, kc * 64, pl * LAST_N);
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
         const int item = tile / tiles_per_item, t2 = tile % tiles_per_item;
         const int y0 = (t2 / p.tiles_x) * LAST_T, x0 = (t2 % p.tiles_x) * LAST_T;
         for (int kc = 0; kc < p.k_blocks; ++kc) {
-          mbar_wait(&empty_bar[stage], phase ^ 1);
-          mbar_arrive_expect_tx(&full_bar[stage], (uint32_t)LAST_A_BYTES);
-          tma_load_3d(ring + stage * LAST_A_BYTES, &tmap_a, &full_bar[stage], kc * 64, x0 - 1, item * (p.h + 1) + y0 - 1);
-          if (++stage == LAST_STAGES) { stage = 0; phase ^= 1; }
+          for (int pi = 0; pi < NPLANES; ++pi) {
+            const int pl = NPLANES - 1 - pi;                 // exact: lo, mid, hi
+            mbar_wait(&empty_bar[stage], phase ^ 1);
+            mbar_arrive_expect_tx(&full_bar[stage], (uint32_t)LAST_A_BYTES);
+            tma_load_3d(ring + stage * LAST_A_BYTES, &tmap_a, &full_bar[stage], (pl * p.k_blocks + kc) * 64, x0 - 1,
+                        item * (p.h + 1) + y0 - 1);
+            if (++stage == LAST_STAGES) { stage = 0; phase ^= 1; }
+          }
         }
       }
     }
@@ -113,21 +127,30 @@ deconv_last_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
         mbar_wait(&tempty_bar[buf], (use & 1) ^ 1);
         tc_fence_after();
         for (int kc = 0; kc < p.k_blocks; ++kc) {
-          mbar_wait(&full_bar[stage], phase);
-          tc_fence_after();
-          const uint32_t a_addr = smem_u32(ring + stage * LAST_A_BYTES);
-          const uint64_t b_desc = make_sw128_kmajor_desc(smem_u32(wres + kc * LAST_N * 128), 0);
+          for (int pi = 0; pi < NPLANES; ++pi) {
+            const int pa = NPLANES - 1 - pi;                 // activation plane in this stage (exact: lo, mid, hi)
+            mbar_wait(&full_bar[stage], phase);
+            tc_fence_after();
+            const uint32_t a_addr = smem_u32(ring + stage * LAST_A_BYTES);
+            // weight planes this activation plane is multiplied with, smallest product first:
+            // lo -> {hi}; mid -> {mid, hi}; hi -> {lo, mid, hi}   (plain mode: the one plane)
+            const int nb = EXACT ? 3 - pa : 1;
+            for (int q = 0; q < nb; ++q) {
+              const int pb = EXACT ? nb - 1 - q : 0;
+              const uint64_t b_desc = make_sw128_kmajor_desc(smem_u32(wres + (pb * p.k_blocks + kc) * LAST_N * 128), 0);
 #pragma unroll
-          for (int half = 0; half < 2; ++half) {
-            const uint64_t a_desc = make_sw128_kmajor_desc(a_addr + half * 128 * 128, 0);
-            const uint32_t d_tmem = tmem_base + (uint32_t)(buf * 64 + half * 32);
+              for (int half = 0; half < 2; ++half) {
+                const uint64_t a_desc = make_sw128_kmajor_desc(a_addr + half * 128 * 128, 0);
+                const uint32_t d_tmem = tmem_base + (uint32_t)(buf * 64 + half * 32);
 #pragma unroll
-            for (int k = 0; k < 4; ++k)
-              umma_bf16(d_tmem, a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc, (kc | k) != 0);
+                for (int k = 0; k < 4; ++k)
+                  umma_bf16(d_tmem, a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc, (kc | pi | q | k) != 0);
+              }
+            }
+            umma_commit(&empty_bar[stage]);
+            if (kc == p.k_blocks - 1 && pi == NPLANES - 1) umma_commit(&tfull_bar[buf]);
+            if (++stage == LAST_STAGES) { stage = 0; phase ^= 1; }
           }
-          umma_commit(&empty_bar[stage]);
-          if (kc == p.k_blocks - 1) umma_commit(&tfull_bar[buf]);
-          if (++stage == LAST_STAGES) { stage = 0; phase ^= 1; }
         }
       }
     }
