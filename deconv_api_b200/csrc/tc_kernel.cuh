@@ -176,6 +176,10 @@ deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  // Programmatic dependent launch (DeepDream chains of small convs): the next kernel may run ITS prologue (barrier
+  // init, TMEM allocation, descriptor prefetch) on an SM as soon as this CTA has left it; it blocks in griddep_wait()
+  // below, before its first activation load, until this whole grid has finished.
+  griddep_launch_dependents();
 
   const int total_tiles = p.m_tiles * p.n_tiles;
   const int wp = p.w + 1;
@@ -193,6 +197,7 @@ deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
           for (int kc = 0; kc < p.k_blocks; ++kc)
             tma_load_2d(wres + (t * p.k_blocks + kc) * B_TILE_BYTES, &tmap_b, wres_bar, kc * BLOCK_K, t * p.n_pad);
       }
+      griddep_wait();                 // the activations were written by the previous kernel of the stream
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
