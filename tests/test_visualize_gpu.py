@@ -131,3 +131,23 @@ def test_vgg16_only_layers_and_vs_oracle_bias():
     ref = rs.visualize_all_layers(ref_model, img, "block3_conv1", "max", top=2, only_layers=["block3_conv1"])
     for a, b in zip(got["block3_conv1"], ref["block3_conv1"]):
         assert rel_l2(a, b) < FP32_TOL
+
+
+def test_vgg16_dense_targets_vs_oracle():
+    """Full-size dense head (fc1 is 25088 x 4096): projections of `predictions` (softmax both ways), `fc2` and `fc1`
+    through DDense.down, DFlatten.down and the whole conv chain, against the CPU restatement.  1e-4 for chains that
+    start above the Flatten (un-rectified x W^T terms cancel), bf16 chain 2e-2."""
+    model = vgg16.VGG16(weights="imagenet", include_top=True)
+    ref_model = keras_shim.VGG16(include_top=True)
+    img = synth.image_batch(1)
+    layers = ["predictions", "fc2", "fc1"]
+    ref = rs.visualize_all_layers(ref_model, img, "predictions", "all", top=2, only_layers=layers)
+    got = dd.visualize_all_layers(model, img, "predictions", "all", only_layers=layers, top=2, precision="fp32")
+    got16 = dd.visualize_all_layers(model, img, "predictions", "all", only_layers=layers, top=2, precision="bf16")
+    assert list(got.keys()) == list(ref.keys()) == layers
+    for name in layers:
+        assert len(got[name]) == len(ref[name]) == len(got16[name]) == 2
+        for a, a16, b in zip(got[name], got16[name], ref[name]):
+            assert a.shape == b.shape == (224, 224, 3)
+            assert rel_l2(a, b) < 1e-4, name
+            assert rel_l2(a16, b) < 2e-2, name
