@@ -442,6 +442,13 @@ __global__ void __launch_bounds__(256) rs_p(const float* __restrict__ x, RS p, f
   }
 }
 
+__global__ void fill_random(float* x, size_t n) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    unsigned h = (unsigned)i * 2654435761u; h ^= h >> 15; h *= 2246822519u; h ^= h >> 13;
+    x[i] = (float)(int)(h & 0xFFFF) * (1.f / 65536.f) - 0.5f;
+  }
+}
+
 template <class F> float time_ms(F f, int reps = 10) {
   cudaEvent_t a, b; cudaEventCreate(&a); cudaEventCreate(&b);
   f(); f();
@@ -461,6 +468,10 @@ int main() {
   float *x, *y;
   CK(cudaMalloc(&x, n * 4)); CK(cudaMalloc(&y, n * 4));
   CK(cudaMemset(x, 1, n * 4)); CK(cudaMemset(y, 0, n * 4));
+#ifdef RANDOM_DATA
+  fill_random<<<148 * 8, 256>>>(x, n);          // data-dependent effects (DRAM / datapath toggling) show up with this
+  CK(cudaDeviceSynchronize());
+#endif
   const int oy = 17, shift = ((-29 % W) + W) % W * C;
   const double gb = 2.0 * n * 4 / 1e9;
   auto rep = [&](const char* name, float ms, double g) { printf("%-44s %7.3f ms  %7.1f GB/s\n", name, ms, g / ms * 1e3); };
