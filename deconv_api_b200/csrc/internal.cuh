@@ -67,10 +67,10 @@ struct dcv_ctx {
   cudaStream_t copy_stream = nullptr;
   cudaEvent_t ev_ready[2] = {nullptr, nullptr}, ev_copied[2] = {nullptr, nullptr};
   DevBuf out_stage[2];
-  DevBuf dream[6];
+  DevBuf dream[6];     // DeepDream: image, original, shrunk original, rolled input / resize temp, 2 gradient buffers
   void* dream_graphs = nullptr;   // cached CUDA graphs of DeepDream iterations (dream.cu)
   DevBuf jit_dev;      // DeepDream: {iteration counter, (oy, ox) per iteration}
-  unsigned long long alloc_epoch = 0;   // bumped whenever a DevBuf is (re)allocated: invalidates captured graphs     // DeepDream: image, original, shrunk original, rolled input / resize temp, 2 gradient buffers
+  unsigned long long alloc_epoch = 0;   // bumped whenever a DevBuf is (re)allocated: invalidates captured graphs
   // optional per-kernel-class timing (dcv_profile): CUDA events around every launch of a class
   bool prof_on = false;
   std::vector<ProfRec> prof;
