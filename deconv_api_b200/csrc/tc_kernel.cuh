@@ -39,17 +39,17 @@ struct TcParams {
   int stages;        // smem ring depth (host-computed from the budget)
   int base_off;      // 1: put (start_addr >> 7) & 7 into the descriptor's base-offset field
   int ntaps;         // 9 = 3x3 conv; 1 = plain GEMM over un-shifted rows (first layer through im2col), MODE_TAP only
-  int nprod_planes;  // weight planes per tap in the packed weights: 1, or 3 with nprod == 6
-  int nprod;         // 1 = plain bf16 product; 6 = exact fp32 emulation: operands are split into three bf16 planes
-                     // (hi, mid, lo) and the six significant cross products are accumulated (tc forward conv)
+  int nprod_planes;  // weight planes per tap in the packed weights: 1, or 3 for the split-operand kernels (tc_exact.cuh)
+  int nprod;         // 1 = plain bf16 product (the kernels of this file); 6 = fp32-accurate mode: operands split into
+                     // three bf16 planes (hi, mid, lo), six cross products - conv_exact_kernel only
   const float* bias;         // n_real entries added before the ReLU (forward conv), or null
-  // fused switch-driven unpool of the result (the conv's output feeds a pool layer's .down): out_bf16 is then the
-  // padded-flat tensor at the UNPOOLED size (up_h, up_w) and every output row is expanded into its 2x2 quad
   // DeepDream backward: fold the NEXT layer's gradient prep into this epilogue (bf16 plain store only):
   //   out = mask(act > 0) * (acc + prep_scale * act), act = that layer's bf16 tape in the output's layout
   const __nv_bfloat16* prep_act;
   float prep_scale;
   int prep_relu;
+  // fused switch-driven unpool of the result (the conv's output feeds a pool layer's .down): out_bf16 is then the
+  // padded-flat tensor at the UNPOOLED size (up_h, up_w) and every output row is expanded into its 2x2 quad
   const uint8_t* up_sw;      // switches (up_B, h, w, up_C) bytes, or null = plain store
   int up_B, up_C, up_h, up_w;
   __nv_bfloat16* out_bf16;   // padded-flat (rows, n_pad), or null
