@@ -7,12 +7,12 @@
 // accumulation: it truncates when it adds into a TMEM accumulator, so a long K chain inside TMEM drifts towards zero
 // (measured: 1e-5 relative after 13 chained layers with three rotating accumulators).  This kernel therefore never
 // chains more than one pipeline stage (12 MMAs of K = 16) inside TMEM: each stage starts a fresh accumulator slot,
-// and the four epilogue warps - idle during the main loop of the bf16 kernels - drain finished slots into fp32
+// and the eight accumulate warps - idle during the main loop of the bf16 kernels - drain finished slots into fp32
 // REGISTER accumulators with round-to-nearest adds while the next stages run.  Result: error below the FFMA
 // kernel's (sequential fp32 sums), at several times its speed.
 //
 // Pipeline.  warp 0: TMA producer (one A band of 136 rows serving the three dx taps + three weight tiles per
-// stage, as MODE_BAND of tc_kernel.cuh); warp 1: MMA issuer; warps 2-5: accumulate + epilogue.  Barriers:
+// stage, as MODE_BAND of tc_kernel.cuh); warp 1: MMA issuer; warps 2-9: accumulate + epilogue.  Barriers:
 // full/empty per smem stage, slot_full/slot_empty per TMEM slot.
 #pragma once
 #include "tc_kernel.cuh"
@@ -38,7 +38,7 @@ conv_exact_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(ring + p.stages * stage_bytes);
   uint64_t* empty_bar = full_bar + MAX_STAGES;
   uint64_t* sfull_bar = empty_bar + MAX_STAGES;         // [EXACT_SLOTS] slot holds a finished stage
-  uint64_t* sempty_bar = sfull_bar + EXACT_SLOTS;       // [EXACT_SLOTS] slot drained by the four epilogue warps
+  uint64_t* sempty_bar = sfull_bar + EXACT_SLOTS;       // [EXACT_SLOTS] slot drained by the eight accumulate warps
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sempty_bar + EXACT_SLOTS);
 
   const int warp = threadIdx.x >> 5;
@@ -122,7 +122,7 @@ conv_exact_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       }
     }
   } else {
-    // ===== accumulate + epilogue warps 2..5: TMEM lane group = warp % 4, one output row per thread =====
+    // ===== accumulate + epilogue warps 2..9: TMEM lane group = warp % 4, one output row per thread =====
     // (one warp per sub-partition runs at ~11 cycles per instruction; with four warps the adds of an N = 128 stage
     // took longer than its MMAs)
     const int lg = warp & 3;
