@@ -8,9 +8,12 @@
 //   out[row(j) + 1][c] = D[j][c] + D[j+1][64 + c] + D[j+2][128 + c]
 // i.e. one and two TMEM lanes further down = warp shuffles.  To keep every shuffle inside one warp (a warp can only
 // read its own 32 TMEM lanes) the 128-row A tile is built from FOUR 32-row TMA boxes that start 30 rows apart: warp k
-// owns input rows m0-1+30k .. m0+30k+30 and produces the 30 output rows m0+30k .. m0+30k+29.  No shared-memory
-// exchange, no barrier in the epilogue; a tile yields 120 output rows (94 % of the MMA rows).  The packed weights
+// owns input rows m0-1+30k .. m0+30k+30 and produces the 30 output rows m0+30k .. m0+30k+29.  No cross-warp
+// exchange of accumulator data; a tile yields 120 output rows (94 % of the MMA rows).  The packed weights
 // [tap][64][K_pad] already have the three dx blocks of a dy contiguous (192 rows): B is one TMA box per (dy, k block).
+// With only 12 MMAs per tile the epilogue sets the pace: 16 epilogue warps (lane quarter x 16-column group), the TMEM
+// buffer is released as soon as the accumulator is in registers, optional steps are compiled out (EPI), and the
+// 120 x 64 bf16 result goes through a swizzled shared-memory tile and ONE TMA store per tile.
 #pragma once
 #include "tc_kernel.cuh"
 
@@ -79,7 +82,7 @@ deconv_dxg_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  const int total_tiles = p.m_tiles;                  // tiles of 126 output rows; n_tiles == 1
+  const int total_tiles = p.m_tiles;                  // tiles of ROWS_OUT output rows; n_tiles == 1
   const int wp = p.w + 1;
   const int total_st = NDY * p.k_blocks;
 
