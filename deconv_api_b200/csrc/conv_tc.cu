@@ -156,6 +156,8 @@ im2col_first_kernel(const float* __restrict__ x, int P, int h, int w, const int*
   // one thread per padded row (measured: a 16-byte-chunk-per-thread form with coalesced stores is 3x slower,
   // the index arithmetic dominates).  jit (optional): {counter, oy0, ox0, ...} - the rows are taken from the image
   // rolled by (oy, ox) of iteration `counter` (numpy.roll), i.e. DeepDream's jitter is folded into this gather.
+  griddep_wait();
+  griddep_launch_dependents();
   int roll_y = 0, roll_x = 0;
   if (jit) { const int c = jit[0]; roll_y = jit[1 + 2 * c] % h; roll_x = jit[2 + 2 * c] % w; if (roll_y < 0) roll_y += h; if (roll_x < 0) roll_x += w; }
   const int wp = w + 1, rp = (h + 1) * wp;
@@ -241,6 +243,8 @@ __global__ void __launch_bounds__(256)
 unpool_pad_kernel(const __nv_bfloat16* __restrict__ x, const uint8_t* __restrict__ sw, int P, int Bsw, int ph, int pw,
                   int h, int w, int C, int c_pad, __nv_bfloat16* __restrict__ out,
                   const __nv_bfloat16* __restrict__ prep_act, float prep_scale, int prep_relu) {
+  griddep_wait();                    // no-ops unless launched as a programmatic dependent (launch_k below)
+  griddep_launch_dependents();
   const int iwp = pw + 1, irp = (ph + 1) * iwp;
   const int owp = w + 1, orp = (h + 1) * owp;
   const int qh = (h + 2) / 2, qw = (w + 2) / 2;          // quads covering y in [0,h], x in [0,w]
@@ -309,6 +313,8 @@ unpool_pad_kernel(const __nv_bfloat16* __restrict__ x, const uint8_t* __restrict
 __global__ void __launch_bounds__(256)
 pool_pad_kernel(const __nv_bfloat16* __restrict__ x, int P, int h, int w, int C, int c_pad,
                 __nv_bfloat16* __restrict__ out, uint8_t* __restrict__ sw) {
+  griddep_wait();
+  griddep_launch_dependents();
   const int ph = h / 2, pw = w / 2;
   const int iwp = w + 1, irp = (h + 1) * iwp;
   const int owp = pw + 1, orp = (ph + 1) * owp;
@@ -355,6 +361,8 @@ pool_pad_kernel(const __nv_bfloat16* __restrict__ x, int P, int h, int w, int C,
 // DeepDream backward, padded-flat bf16: g = mask(act > 0) * (g_above + scale * act); g_above may be absent.
 __global__ void dream_prep_pad_kernel(__nv_bfloat16* __restrict__ g, const __nv_bfloat16* __restrict__ act, size_t n2,
                                       float scale, int has_g, int relu) {
+  griddep_wait();
+  griddep_launch_dependents();
   __nv_bfloat162* g2 = reinterpret_cast<__nv_bfloat162*>(g);
   const __nv_bfloat162* a2 = reinterpret_cast<const __nv_bfloat162*>(act);
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n2; i += (size_t)gridDim.x * blockDim.x) {
@@ -493,6 +501,22 @@ int make_tmap_patch(dcv_ctx* ctx, CUtensorMap* m, const void* base, uint64_t c_p
   return 0;
 }
 
+// Launch on the context's stream; while DeepDream runs (ctx->latency_tiles) as a programmatic dependent of the
+// previous kernel: its CTAs may start (prologue, constant loads) while the predecessor drains, and every kernel
+// launched through here calls griddep_wait() before it touches anything the predecessor wrote.  DCV_PDL=0: plain.
+template <typename... KArgs, typename... Args>
+cudaError_t launch_k(dcv_ctx* ctx, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, Args... args) {
+  static const int use_pdl = getenv("DCV_PDL") ? atoi(getenv("DCV_PDL")) : 1;     // measured: +2-4 % on DeepDream 512x512
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = ctx->stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = (use_pdl && ctx->latency_tiles) ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
 template <int BLOCK_N, int MODE>
 int launch_tc(dcv_ctx* ctx, const CUtensorMap& ta, const CUtensorMap& tb, TcParams p) {
   const int stage_bytes = tc_stage_bytes(MODE, BLOCK_N);
@@ -512,19 +536,8 @@ int launch_tc(dcv_ctx* ctx, const CUtensorMap& ta, const CUtensorMap& tb, TcPara
   }
   const int tiles = p.m_tiles * p.n_tiles;
   const int grid = std::min(tiles, ctx->num_sms);
-  static const int use_pdl = getenv("DCV_PDL") ? atoi(getenv("DCV_PDL")) : 1;     // measured: +2 % on DeepDream 512x512
-  if (use_pdl && ctx->latency_tiles) {
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(TC1_THREADS); cfg.dynamicSmemBytes = smem; cfg.stream = ctx->stream;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs = attr; cfg.numAttrs = 1;
-    e = cudaLaunchKernelEx(&cfg, deconv_tc_kernel<BLOCK_N, MODE>, ta, tb, p);
-    if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "cudaLaunchKernelEx(deconv_tc_kernel<%d,%d>): %s", BLOCK_N, MODE, cudaGetErrorString(e));
-  } else {
-    deconv_tc_kernel<BLOCK_N, MODE><<<grid, TC1_THREADS, smem, ctx->stream>>>(ta, tb, p);
-  }
+  e = launch_k(ctx, deconv_tc_kernel<BLOCK_N, MODE>, dim3(grid), dim3(TC1_THREADS), (size_t)smem, ta, tb, p);
+  if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "launch(deconv_tc_kernel<%d,%d>): %s", BLOCK_N, MODE, cudaGetErrorString(e));
   ctx->launches++;
   e = cudaGetLastError();
   if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "deconv_tc_kernel<%d,%d> launch: %s", BLOCK_N, MODE, cudaGetErrorString(e));
@@ -614,9 +627,8 @@ int tc_unpool(dcv_ctx* ctx, const __nv_bfloat16* x, const uint8_t* sw, int P, in
   const size_t work = (size_t)P * ((h + 2) / 2) * ((w + 2) / 2) * (c_pad / 8);
   // algorithmic bytes in this layout: 2 B/elem read at pooled size + 1 B switch, 2 B/elem written at full size
   ProfScope ps(ctx, DCV_K_UNPOOL, 0.0, (double)P * ph * pw * C * (2.0 + 1.0 + 8.0));
-  unpool_pad_kernel<<<grid_for(work, 256), 256, 0, ctx->stream>>>(x, sw, P, Bsw, ph, pw, h, w, C, c_pad, out,
-                                                                  prep ? prep->act : nullptr, prep ? prep->scale : 0.f,
-                                                                  prep ? prep->relu : 0);
+  launch_k(ctx, unpool_pad_kernel, dim3(grid_for(work, 256)), dim3(256), (size_t)0, x, sw, P, Bsw, ph, pw, h, w, C, c_pad, out,
+           prep ? prep->act : (const __nv_bfloat16*)nullptr, prep ? prep->scale : 0.f, prep ? prep->relu : 0);
   ctx->launches++;
   return 0;
 }
@@ -625,14 +637,14 @@ int tc_pool(dcv_ctx* ctx, const __nv_bfloat16* x, int P, int h, int w, int C, __
   const int c_pad = tc_cpad(C);
   const size_t work = (size_t)P * (h / 2 + 1) * (w / 2 + 1) * (c_pad / 8);
   ProfScope ps(ctx, DCV_K_POOL, 0.0, (double)P * h * w * C * (2.0 + 3.0 / 4.0));
-  pool_pad_kernel<<<grid_for(work, 256), 256, 0, ctx->stream>>>(x, P, h, w, C, c_pad, out, sw);
+  launch_k(ctx, pool_pad_kernel, dim3(grid_for(work, 256)), dim3(256), (size_t)0, x, P, h, w, C, c_pad, out, sw);
   ctx->launches++;
   return 0;
 }
 
 int tc_dream_prep(dcv_ctx* ctx, __nv_bfloat16* g, const __nv_bfloat16* act, size_t elems, float scale, int has_g, int relu) {
   ProfScope ps(ctx, DCV_K_OTHER, 0.0, 6.0 * elems);
-  dream_prep_pad_kernel<<<grid_for(elems / 2, 256), 256, 0, ctx->stream>>>(g, act, elems / 2, scale, has_g, relu);
+  launch_k(ctx, dream_prep_pad_kernel, dim3(grid_for(elems / 2, 256)), dim3(256), (size_t)0, g, act, elems / 2, scale, has_g, relu);
   ctx->launches++;
   return 0;
 }
@@ -766,9 +778,9 @@ int tc_conv_first(dcv_ctx* ctx, Layer& l, const float* x, int P, int h, int w, _
     ProfScope ps(ctx, DCV_K_OTHER, 0.0, 4.0 * P * h * w * l.cin + 128.0 * rows);
     const int grid = grid_for(rows, 128);
     switch (l.cin) {
-      case 1: im2col_first_kernel<1><<<grid, 128, 0, ctx->stream>>>(x, P, h, w, jit, cols); break;
-      case 2: im2col_first_kernel<2><<<grid, 128, 0, ctx->stream>>>(x, P, h, w, jit, cols); break;
-      default: im2col_first_kernel<3><<<grid, 128, 0, ctx->stream>>>(x, P, h, w, jit, cols); break;
+      case 1: launch_k(ctx, im2col_first_kernel<1>, dim3(grid), dim3(128), (size_t)0, x, P, h, w, jit, cols); break;
+      case 2: launch_k(ctx, im2col_first_kernel<2>, dim3(grid), dim3(128), (size_t)0, x, P, h, w, jit, cols); break;
+      default: launch_k(ctx, im2col_first_kernel<3>, dim3(grid), dim3(128), (size_t)0, x, P, h, w, jit, cols); break;
     }
     ctx->launches++;
   }
@@ -821,7 +833,7 @@ int tc_conv(dcv_ctx* ctx, const Layer& l, const __nv_bfloat16* in, int P, int h,
       smem_set[ctx->device & 63] = smem;
     }
     ProfScope ps(ctx, DCV_K_CONV_TC, 2.0 * 9 * P * h * w * (double)l.cin * l.cout, 2.0 * P * h * w * ((double)l.cout + 2.0 * l.cin));
-    deconv_last_kernel<0><<<std::min(p.total_tiles, ctx->num_sms), LAST_THREADS, smem, ctx->stream>>>(ta, tb, p);
+    launch_k(ctx, deconv_last_kernel<0>, dim3(std::min(p.total_tiles, ctx->num_sms)), dim3(LAST_THREADS), (size_t)smem, ta, tb, p);
     ctx->launches++;
     e = cudaGetLastError();
     if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "deconv_last_kernel launch: %s", cudaGetErrorString(e));
@@ -988,7 +1000,7 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
           if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "cudaFuncSetAttribute(gemm64 kernel): %s", cudaGetErrorString(e)); \
           smem_set[ctx->device & 63] = smem;                                                                           \
         }                                                                                                              \
-        deconv_dxg_kernel<1, EPI, 0><<<grid, DXG_THREADS, smem, ctx->stream>>>(ta2, tb2, to2, q);                      \
+        launch_k(ctx, deconv_dxg_kernel<1, EPI, 0>, dim3(grid), dim3(DXG_THREADS), (size_t)smem, ta2, tb2, to2, q);   \
       }
       if (q.bias) GEMM64_LAUNCH(1) else GEMM64_LAUNCH(0)
 #undef GEMM64_LAUNCH
@@ -1035,7 +1047,7 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
           if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "cudaFuncSetAttribute(dxg kernel): %s", cudaGetErrorString(e)); \
           smem_set[ctx->device & 63] = smem;                                                                           \
         }                                                                                                              \
-        deconv_dxg_kernel<RES, EPI><<<grid, DXG_THREADS, smem, ctx->stream>>>(ta2, tb2, to2, q);                            \
+        launch_k(ctx, deconv_dxg_kernel<RES, EPI, 1>, dim3(grid), dim3(DXG_THREADS), (size_t)smem, ta2, tb2, to2, q);      \
       }
 #define DXG_EPIS(RES)                                \
       switch (epi) {                                 \

@@ -81,6 +81,7 @@ deconv_dxg_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  griddep_launch_dependents();                        // programmatic dependent launch, see tc_kernel.cuh
 
   const int total_tiles = p.m_tiles;                  // tiles of ROWS_OUT output rows; n_tiles == 1
   const int wp = p.w + 1;
@@ -94,6 +95,7 @@ deconv_dxg_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           for (int kc = 0; kc < p.k_blocks; ++kc)
             tma_load_2d(wres + (dy * p.k_blocks + kc) * B_BYTES, &tmap_b, wres_bar, kc * BLOCK_K, dy * N_TILE);
       }
+      griddep_wait();                                 // the activations come from the previous kernel of the stream
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {

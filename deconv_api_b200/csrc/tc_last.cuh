@@ -88,6 +88,7 @@ deconv_last_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  griddep_launch_dependents();                        // programmatic dependent launch, see tc_kernel.cuh
   const int tiles_per_item = p.tiles_x * p.tiles_y;
 
   if (warp == 0) {
@@ -96,6 +97,7 @@ deconv_last_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
       for (int pl = 0; pl < NPLANES; ++pl)
         for (int kc = 0; kc < p.k_blocks; ++kc)
           tma_load_2d(wres + (pl * p.k_blocks + kc) * LAST_N * 128, &tmap_b, wres_bar, kc * 64, pl * LAST_N);
+      griddep_wait();                                 // the activations come from the previous kernel of the stream
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
