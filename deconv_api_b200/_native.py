@@ -91,9 +91,13 @@ def load():
     global _LIB
     if _LIB is not None:
         return _LIB
-    path = _build.LIB
-    if not os.path.exists(path) or os.environ.get("DCV_REBUILD"):
+    # build() returns at once when the stored source hash matches, so a library left behind by an older
+    # checkout of csrc/ is never loaded silently; without nvcc a stale or missing library is an error
+    try:
         path = _build.build(force=bool(os.environ.get("DCV_REBUILD")))
+    except Exception as e:
+        raise ImportError("deconv_api_b200: %s is missing or older than csrc/ and cannot be rebuilt (%s); "
+                          "there is no fallback" % (_build.LIB, e))
     try:
         lib = ctypes.CDLL(path)
     except OSError as e:

@@ -212,6 +212,9 @@ extern "C" int dcv_profile_launch(dcv_ctx* ctx, int index, int* cat, double* ms,
 extern "C" int dcv_net_clear(dcv_ctx* ctx) {
   ENTER(ctx);
   CU(ctx, cudaStreamSynchronize(ctx->stream));
+  // captured DeepDream graphs hold raw pointers into the tape and weight buffers freed below
+  dream_release_graphs(ctx);
+  ctx->alloc_epoch++;
   for (auto& l : ctx->net) free_layer(l);
   ctx->net.clear();
   ctx->tape_upto = -1;

@@ -15,6 +15,8 @@
 #include "common.cuh"
 #include "internal.cuh"
 
+#include <atomic>
+
 using namespace dcv;
 
 namespace {
@@ -23,18 +25,23 @@ constexpr int kMaxPartials = DCV_DEPROCESS_NOALLOC_MAX_PARTIALS;          // (su
 static __device__ __align__(256) double g_deprocess_partials[2 * kMaxPartials];
 
 constexpr int kMaxDevices = 64;
-double* g_scratch_on_device[kMaxDevices] = {};
+// One slot per device; atomics because contexts on different host threads may make their first call at the
+// same time (both would store the same address).  The address stays valid until cudaDeviceReset, which this
+// cache does not observe: do not reset a device while the library is in use.
+std::atomic<double*> g_scratch_on_device[kMaxDevices] = {};
 
-// Device address of the array on `device` (which must be current).  Looked up once per device.
+// Device address of the array on `device` (which must be current).  Looked up once per device.  This first
+// lookup may make the runtime load the library's device code onto that GPU (lazy module loading), which is the
+// only allocation-like event the entry point can cause; later calls touch no allocator at all.
 int resolve_scratch(dcv_ctx* ctx, double** out) {
   if (ctx->device < 0 || ctx->device >= kMaxDevices)
     return ctx->fail(DCV_ERR_UNSUPPORTED, "dcv_deprocess_dev_noalloc: device index %d beyond %d", ctx->device, kMaxDevices);
-  double* p = g_scratch_on_device[ctx->device];
+  double* p = g_scratch_on_device[ctx->device].load(std::memory_order_acquire);
   if (!p) {
     cudaError_t e = cudaGetSymbolAddress((void**)&p, g_deprocess_partials);
     if (e != cudaSuccess || !p)
       return ctx->fail(DCV_ERR_CUDA, "dcv_deprocess_dev_noalloc: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
-    g_scratch_on_device[ctx->device] = p;
+    g_scratch_on_device[ctx->device].store(p, std::memory_order_release);
   }
   *out = p;
   return 0;

@@ -3,14 +3,32 @@
 ``preprocess_input``).
 
 There is no network on the build/GPU boxes, so ``weights='imagenet'`` cannot download the Keras
-``.h5``; it and ``weights=None`` give the seeded Glorot-uniform init of ``synth`` (Keras' own default
-initialiser), and ``weights='<file>.npz'`` loads arrays saved under the Keras names
-``<layer>/kernel`` (HWIO / (in,out)) and ``<layer>/bias``.
+``.h5``.  It resolves an ``.npz`` export of those weights instead (``DCV_IMAGENET_NPZ``, or
+``~/.keras/models/vgg16_weights_tf_dim_ordering_tf_kernels.npz`` next to where Keras caches the
+``.h5``) and RAISES when none exists: a drop-in user must never get a random network silently.
+``DCV_ALLOW_SYNTH=1`` downgrades that error to a warning and falls back to the seeded init.
+``weights=None`` gives the seeded Glorot-uniform init of ``synth`` (Keras' own default initialiser),
+and ``weights='<file>.npz'`` loads arrays saved under the Keras names ``<layer>/kernel`` (HWIO /
+(in,out)) and ``<layer>/bias``.
 """
+import os
+import warnings
+
 import numpy as np
 
 from . import synth
 from .layers import (Convolution2D, Dense, Flatten, InputLayer, MaxPooling2D, Model)
+
+
+IMAGENET_NPZ_DEFAULT = os.path.join("~", ".keras", "models", "vgg16_weights_tf_dim_ordering_tf_kernels.npz")
+
+
+def imagenet_npz_path():
+    """Path of an .npz export of the Keras ImageNet VGG16 weights, or None."""
+    for cand in (os.environ.get("DCV_IMAGENET_NPZ"), os.path.expanduser(IMAGENET_NPZ_DEFAULT)):
+        if cand and os.path.isfile(cand):
+            return cand
+    return None
 
 
 def VGG16(include_top=True, weights="imagenet", input_shape=None, seed=1234, bias=False):
@@ -19,7 +37,21 @@ def VGG16(include_top=True, weights="imagenet", input_shape=None, seed=1234, bia
     npz = None
     if isinstance(weights, str) and weights.endswith(".npz"):
         npz = np.load(weights)
-    elif weights not in (None, "imagenet"):
+    elif weights == "imagenet":
+        path = imagenet_npz_path()
+        if path is not None:
+            npz = np.load(path)
+        elif os.environ.get("DCV_ALLOW_SYNTH", "0") == "1":
+            warnings.warn("VGG16(weights='imagenet'): no ImageNet weight file found (DCV_IMAGENET_NPZ, %s); "
+                          "DCV_ALLOW_SYNTH=1 -> using seeded RANDOM weights, the visualisations are of an untrained network"
+                          % IMAGENET_NPZ_DEFAULT, RuntimeWarning, stacklevel=2)
+        else:
+            raise FileNotFoundError(
+                "VGG16(weights='imagenet'): the Keras ImageNet weights cannot be downloaded here (no network) and no "
+                ".npz export was found; set DCV_IMAGENET_NPZ (or DCV_WEIGHTS for the service) to a file with the arrays "
+                "'<layer>/kernel' and '<layer>/bias', put it at %s, pass weights=None for the seeded random init, "
+                "or set DCV_ALLOW_SYNTH=1 to accept random weights with a warning" % IMAGENET_NPZ_DEFAULT)
+    elif weights is not None:
         raise ValueError("weights must be None, 'imagenet' or a path to an .npz file")
     conv_w = dict(zip([n for n, _, _ in synth.VGG16_CONVS], synth.conv_weights(seed, bias)))
     layers = []

@@ -157,8 +157,10 @@ DCV_API int dcv_deprocess_dev(dcv_ctx* ctx, const float* x_dev, size_t n, uint8_
  * process exits) instead of the context's growable scratch buffer.
  *   - x_dev (16-byte aligned) and out_dev (4-byte aligned) are device pointers supplied by the caller;
  *     n <= DCV_DEPROCESS_NOALLOC_MAX_ELEMS, larger inputs are refused with DCV_ERR_ARG;
- *   - the first call on each device looks up the array's device address; make that call before any
- *     stream capture begins;
+ *   - the first call on each device looks up the array's device address (and may make the CUDA runtime load
+ *     the library's device code onto that GPU); make that call before any stream capture begins.  From the
+ *     second call on nothing is allocated.  The address is cached for the life of the process: do not call
+ *     cudaDeviceReset while the library is in use;
  *   - all calls (from every context on that device) share the one array: two calls whose kernels can
  *     overlap on the GPU race on it — issue them on one stream or order them with events;
  *   - the call is asynchronous on the context's stream, like dcv_deprocess_dev. */

@@ -6,7 +6,7 @@ import numpy as np
 
 if len(sys.argv) > 1:
     from deconv_api_b200 import deepdream as dd, synth, vgg16
-    model = vgg16.VGG16(weights="imagenet", include_top=True)
+    model = vgg16.VGG16(weights=None, include_top=True)
     res = dd.visualize_all_layers(model, synth.image_batch(1), "block5_conv3", "all", precision="fp32")
     np.savez(sys.argv[1], **{"%s|%d" % (k, i): a for k, v in res.items() for i, a in enumerate(v)})
     sys.exit(0)

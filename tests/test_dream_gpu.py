@@ -103,3 +103,22 @@ def test_gradient_bf16_large_image_kernel_variants():
     g32, loss32 = eng.dream_gradient(img, [eng.index[n] for n in layers], list(layers.values()), precision="fp32")
     assert abs(loss32 - loss_ref) <= 1e-5 * abs(loss_ref)
     assert rel_l2(g32, g_ref) < 1e-5
+
+
+def test_dream_after_set_weights_does_not_replay_a_stale_graph():
+    """A cached CUDA graph of the bf16 dream holds raw pointers into the tape and the packed weights.  Changing the
+    weights makes the model rebuild its engine network (dcv_net_clear frees those buffers): the next dream with the
+    SAME key (shape, losses, step) must re-capture, and equal a fresh model that was given the new weights up front."""
+    layers = {"block2_conv2": 0.5, "block3_conv3": 2.0}
+    img = synth.caffe_preprocess(synth.smooth_image_u8(4, 96, 80))
+    kw = dict(layers=layers, num_octave=2, iterations=4, step=1.0, jitter=8, seed=3, precision="bf16")
+    model = vgg16.VGG16(weights=None, include_top=False, input_shape=(None, None, 3), seed=9)
+    first = dm.dream(model, img, **kw)
+    other = vgg16.VGG16(weights=None, include_top=False, input_shape=(None, None, 3), seed=21)
+    for dst, src in zip(model.layers, other.layers):
+        if dst.kind == "conv":
+            dst.set_weights(src.get_weights())
+    second = dm.dream(model, img, **kw)                  # same engine, network cleared and re-added
+    fresh = dm.dream(vgg16.VGG16(weights=None, include_top=False, input_shape=(None, None, 3), seed=21), img, **kw)
+    assert rel_l2(second, fresh) < 1e-6
+    assert rel_l2(second - img, first - img) > 0.1       # the new weights really changed the result

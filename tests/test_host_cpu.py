@@ -6,6 +6,7 @@ import subprocess
 import sys
 
 import numpy as np
+import pytest
 
 from deconv_api_b200 import deepdream as dd, layers, parallel, synth, vgg16
 from oracle import keras_shim, restatement as rs
@@ -36,7 +37,7 @@ def test_shard_work_by_image_then_feature():
 
 
 def test_model_description_matches_keras_shapes():
-    m = vgg16.VGG16(weights="imagenet", include_top=True)
+    m = vgg16.VGG16(weights=None, include_top=True)
     assert [l.name for l in m.layers] == [n for _, n in synth.VGG16_TOPOLOGY]
     assert m.get_layer("block5_conv3").output_shape == (None, 14, 14, 512)
     assert m.get_layer("flatten").output_shape == (None, 25088)
@@ -140,3 +141,28 @@ def test_npz_weight_ingestion(tmp_path):
     import pytest
     with pytest.raises(ValueError):
         vgg16.VGG16(weights=path, include_top=False, input_shape=(32, 32, 3))
+
+
+def test_imagenet_weights_never_fall_back_silently(tmp_path, monkeypatch):
+    """weights='imagenet' without a weight file raises (ADVICE r1); DCV_ALLOW_SYNTH=1 turns that into a warning;
+    an .npz export found through DCV_IMAGENET_NPZ is loaded."""
+    monkeypatch.delenv("DCV_IMAGENET_NPZ", raising=False)
+    monkeypatch.setenv("HOME", str(tmp_path))
+    monkeypatch.setenv("DCV_ALLOW_SYNTH", "0")
+    with pytest.raises(FileNotFoundError):
+        vgg16.VGG16(weights="imagenet", include_top=False)
+    monkeypatch.setenv("DCV_ALLOW_SYNTH", "1")
+    with pytest.warns(RuntimeWarning, match="RANDOM"):
+        m = vgg16.VGG16(weights="imagenet", include_top=False)
+    arrays = {}
+    for l in m.layers:
+        if l.kind == "conv":
+            W, b = l.get_weights()
+            arrays[l.name + "/kernel"], arrays[l.name + "/bias"] = W * 0 + 0.25, b + 1.0
+    path = tmp_path / "vgg.npz"
+    np.savez(path, **arrays)
+    monkeypatch.setenv("DCV_ALLOW_SYNTH", "0")
+    monkeypatch.setenv("DCV_IMAGENET_NPZ", str(path))
+    m2 = vgg16.VGG16(weights="imagenet", include_top=False)
+    W, b = m2.get_layer("block2_conv1").get_weights()
+    assert float(W.min()) == 0.25 and float(b.max()) == 1.0

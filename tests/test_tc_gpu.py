@@ -62,7 +62,7 @@ def test_mini_model_bf16(golden):
 
 @pytest.fixture(scope="module")
 def vgg():
-    return vgg16.VGG16(weights="imagenet", include_top=True), synth.image_batch(1)
+    return vgg16.VGG16(weights=None, include_top=True), synth.image_batch(1)
 
 
 def test_vgg16_block5_conv3_bf16_vs_reference_golden(vgg, golden):

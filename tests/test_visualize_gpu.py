@@ -54,7 +54,7 @@ def test_illegal_mode_and_unknown_layer():
 
 @pytest.fixture(scope="module")
 def vgg_run():
-    model = vgg16.VGG16(weights="imagenet", include_top=True)
+    model = vgg16.VGG16(weights=None, include_top=True)
     img = synth.image_batch(1)
     res = dd.visualize_all_layers(model, img, "block5_conv3", "all")
     return model, img, res
@@ -137,7 +137,7 @@ def test_vgg16_dense_targets_vs_oracle():
     """Full-size dense head (fc1 is 25088 x 4096): projections of `predictions` (softmax both ways), `fc2` and `fc1`
     through DDense.down, DFlatten.down and the whole conv chain, against the CPU restatement.  1e-4 for chains that
     start above the Flatten (un-rectified x W^T terms cancel), bf16 chain 2e-2."""
-    model = vgg16.VGG16(weights="imagenet", include_top=True)
+    model = vgg16.VGG16(weights=None, include_top=True)
     ref_model = keras_shim.VGG16(include_top=True)
     img = synth.image_batch(1)
     layers = ["predictions", "fc2", "fc1"]

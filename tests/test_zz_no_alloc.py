@@ -39,6 +39,42 @@ def test_noalloc_deprocess_matches_regular_entry_point_twice(engine):
         assert torch.equal(x_dev.cpu(), torch.from_numpy(x))            # the input is not modified
 
 
+def test_noalloc_call_leaves_free_memory_unchanged(engine):
+    """The point of the entry point: once the first call on the device has resolved the array's address (and the
+    runtime has loaded the kernels), a call must not change the amount of free device memory."""
+    import torch
+    lib = engine.lib
+    n = 224 * 224 * 3 * 8
+    x_dev = torch.randn(n, dtype=torch.float32, device="cuda")
+    out_dev = torch.zeros(n, dtype=torch.uint8, device="cuda")
+    _run(engine, lib.dcv_deprocess_dev_noalloc, x_dev, n, out_dev)          # warm-up: address lookup, module load
+    torch.cuda.synchronize()
+    free0, _ = torch.cuda.mem_get_info()
+    for _ in range(3):
+        _run(engine, lib.dcv_deprocess_dev_noalloc, x_dev, n, out_dev)
+    torch.cuda.synchronize()
+    free1, _ = torch.cuda.mem_get_info()
+    assert free1 == free0
+
+
+def test_noalloc_two_contexts_share_the_array_in_stream_order():
+    """Two contexts on one device use the same fixed array; called one after the other (each synchronised) both
+    give the regular entry point's bytes."""
+    import torch
+    from deconv_api_b200 import engine as E
+    a, b = E.Engine(0), E.Engine(0)
+    try:
+        rng = np.random.default_rng(5)
+        for eng, n in ((a, 50001), (b, 1234), (a, 77)):
+            x_dev = torch.from_numpy(rng.normal(1.0, 3.0, (n,)).astype(np.float32)).cuda()
+            want = _run(eng, eng.lib.dcv_deprocess_dev, x_dev, n, torch.zeros(n, dtype=torch.uint8, device="cuda"))
+            got = _run(eng, eng.lib.dcv_deprocess_dev_noalloc, x_dev, n, torch.zeros(n, dtype=torch.uint8, device="cuda"))
+            assert np.array_equal(want, got)
+    finally:
+        a.close()
+        b.close()
+
+
 def test_noalloc_rejects_oversize_and_bad_pointers(engine):
     import torch
     lib = engine.lib
