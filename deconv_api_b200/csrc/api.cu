@@ -58,6 +58,8 @@ void DevBuf::release() {
   cap = 0;
 }
 
+static size_t align256(size_t b) { return (b + 255) & ~(size_t)255; }
+
 static int set_device(dcv_ctx* ctx) {
   CU(ctx, cudaSetDevice(ctx->device));
   return 0;
@@ -646,16 +648,34 @@ static int project_chunk(dcv_ctx* ctx, int layer, int foff, int n, int vis_mode,
   return 0;
 }
 
-static int project_impl(dcv_ctx* ctx, int layer, const int* feat, int n, int vis_mode, int precision, float* out,
-                        bool out_on_device) {
-  if (!feat || !out || n < 0) return ctx->fail(DCV_ERR_ARG, "dcv_project: bad arguments");
+// Converts `items` fp32 projections of `len` floats at `src` into the requested result format at `dst` (device).
+static int convert_result(dcv_ctx* ctx, const float* src, int items, size_t len, int fmt, void* dst) {
+  if (fmt == DCV_OUT_U8) {
+    TRY(ctx->scratch.ensure(ctx, (size_t)items * kItemPartials * 2 * sizeof(double)));
+    ProfScope ps(ctx, DCV_K_OTHER, 0.0, 9.0 * items * len);      // two reads of the projection + one byte written
+    launch_deprocess_items(src, items, len, (double*)ctx->scratch.p, (uint8_t*)dst, ctx->stream); ctx->launches += 2;
+  } else {
+    ProfScope ps(ctx, DCV_K_OTHER, 0.0, 6.0 * items * len);
+    launch_convert_bf16(src, (size_t)items * len, (__nv_bfloat16*)dst, ctx->stream); ctx->launches++;
+  }
+  CHECK_LAUNCH(ctx);
+  return 0;
+}
+
+// feat == nullptr: the n feature indices are already in ctx->feat_dev (written by a kernel, dcv_request_mosaic)
+static int project_impl(dcv_ctx* ctx, int layer, const int* feat, int n, int vis_mode, int precision, void* out_v,
+                        bool out_on_device, int fmt = DCV_OUT_F32) {
+  if (!out_v || n < 0) return ctx->fail(DCV_ERR_ARG, "dcv_project: bad arguments");
   if (vis_mode != DCV_VIS_ALL && vis_mode != DCV_VIS_MAX) return ctx->fail(DCV_ERR_ARG, "Illegal visualize mode");
   if (precision != DCV_FP32 && precision != DCV_BF16) return ctx->fail(DCV_ERR_ARG, "dcv_project: unknown precision");
+  if (fmt != DCV_OUT_F32 && fmt != DCV_OUT_BF16 && fmt != DCV_OUT_U8) return ctx->fail(DCV_ERR_ARG, "dcv_project: unknown output format %d", fmt);
   TRY(check_tape(ctx, ctx, layer, "dcv_project"));
   const Layer& top = ctx->net[layer];
-  for (int k = 0; k < n; ++k)
+  for (int k = 0; feat && k < n; ++k)
     if (feat[k] < 0 || feat[k] >= top.C) return ctx->fail(DCV_ERR_ARG, "dcv_project: feature %d out of range [0,%d)", feat[k], top.C);
   if (n == 0) return 0;
+  const size_t esz = fmt == DCV_OUT_F32 ? sizeof(float) : (fmt == DCV_OUT_BF16 ? 2 : 1);
+  char* out = (char*)out_v;
   const int B = ctx->in_B;
   const size_t out_elems = (size_t)B * ctx->in_H * ctx->in_W * ctx->in_C;   // per feature
   size_t max_elems = chain_max_elems(ctx, layer);                           // fp32 elements per item
@@ -711,10 +731,14 @@ static int project_impl(dcv_ctx* ctx, int layer, const int* feat, int n, int vis
   map_elems = std::max(map_elems, (size_t)ctx->in_H * ctx->in_W);
   TRY(ctx->ws[2].ensure(ctx, (size_t)chunk * B * map_elems * sizeof(float)));
   TRY(ctx->ws[3].ensure(ctx, (size_t)chunk * B * map_elems * sizeof(float)));
-  TRY(ctx->feat_dev.ensure(ctx, (size_t)n * sizeof(int)));
-  CU(ctx, cudaMemcpyAsync(ctx->feat_dev.p, feat, (size_t)n * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+  if (feat) {
+    TRY(ctx->feat_dev.ensure(ctx, (size_t)n * sizeof(int)));
+    CU(ctx, cudaMemcpyAsync(ctx->feat_dev.p, feat, (size_t)n * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+  }
   if (pipelined) {
-    for (int i = 0; i < 2; ++i) TRY(ctx->out_stage[i].ensure(ctx, (size_t)chunk * out_elems * sizeof(float)));
+    for (int i = 0; i < 2; ++i) TRY(ctx->out_stage[i].ensure(ctx, (size_t)chunk * out_elems * esz));
+  } else if (!out_on_device && fmt != DCV_OUT_F32) {
+    TRY(ctx->out_stage[0].ensure(ctx, (size_t)chunk * out_elems * esz));
   }
   // Chunk schedule.  Host output: the copy of the LAST chunk is the only one nothing overlaps, so the last chunk is
   // halved repeatedly (128 -> 64, 32, 32): 0.34 ms of exposed copy instead of 1.4 ms for 512 maps of 224x224x3.
@@ -732,22 +756,37 @@ static int project_impl(dcv_ctx* ctx, int layer, const int* feat, int n, int vis
   for (size_t k = 0; k < sizes.size(); f0 += sizes[k], ++k, ++ci) {
     const int nf = sizes[k];
     float* res = nullptr;
-    float* dst = out + (size_t)f0 * out_elems;
+    char* dst = out + (size_t)f0 * out_elems * esz;
+    // out_elems covers the B images of one feature map; every (feature, image) projection is its own item
+    const size_t item_len = out_elems / B;
     if (pipelined) {
       const int s = ci & 1;
-      float* stage = (float*)ctx->out_stage[s].p;
+      void* stage = ctx->out_stage[s].p;
       if (ci >= 2) CU(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_copied[s], 0));    // stage buffer is free again
-      TRY(project_chunk(ctx, layer, f0, nf, vis_mode, precision, stage, &res));
-      if (res != stage)
-        CU(ctx, cudaMemcpyAsync(stage, res, (size_t)nf * out_elems * sizeof(float), cudaMemcpyDeviceToDevice, ctx->stream));
+      if (fmt == DCV_OUT_F32) {
+        TRY(project_chunk(ctx, layer, f0, nf, vis_mode, precision, (float*)stage, &res));
+        if (res != stage)
+          CU(ctx, cudaMemcpyAsync(stage, res, (size_t)nf * out_elems * sizeof(float), cudaMemcpyDeviceToDevice, ctx->stream));
+      } else {
+        TRY(project_chunk(ctx, layer, f0, nf, vis_mode, precision, nullptr, &res));
+        TRY(convert_result(ctx, res, nf * B, item_len, fmt, stage));
+      }
       CU(ctx, cudaEventRecord(ctx->ev_ready[s], ctx->stream));
       CU(ctx, cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_ready[s], 0));
-      CU(ctx, cudaMemcpyAsync(dst, stage, (size_t)nf * out_elems * sizeof(float), cudaMemcpyDeviceToHost, ctx->copy_stream));
+      CU(ctx, cudaMemcpyAsync(dst, stage, (size_t)nf * out_elems * esz, cudaMemcpyDeviceToHost, ctx->copy_stream));
       CU(ctx, cudaEventRecord(ctx->ev_copied[s], ctx->copy_stream));
       continue;
     }
-    TRY(project_chunk(ctx, layer, f0, nf, vis_mode, precision, out_on_device ? dst : nullptr, &res));
-    if (res != dst)
+    if (fmt != DCV_OUT_F32) {
+      TRY(project_chunk(ctx, layer, f0, nf, vis_mode, precision, nullptr, &res));
+      void* conv_dst = out_on_device ? (void*)dst : ctx->out_stage[0].p;
+      TRY(convert_result(ctx, res, nf * B, item_len, fmt, conv_dst));
+      if (!out_on_device)
+        CU(ctx, cudaMemcpyAsync(dst, conv_dst, (size_t)nf * out_elems * esz, cudaMemcpyDeviceToHost, ctx->stream));
+      continue;
+    }
+    TRY(project_chunk(ctx, layer, f0, nf, vis_mode, precision, out_on_device ? (float*)dst : nullptr, &res));
+    if ((char*)res != dst)
       CU(ctx, cudaMemcpyAsync(dst, res, (size_t)nf * out_elems * sizeof(float),
                               out_on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, ctx->stream));
   }
@@ -759,6 +798,7 @@ static int project_impl(dcv_ctx* ctx, int layer, const int* feat, int n, int vis
 
 extern "C" int dcv_project(dcv_ctx* ctx, int layer, const int* feat, int n, int vis_mode, int precision, float* out) {
   ENTER(ctx);
+  if (!feat) return ctx->fail(DCV_ERR_ARG, "dcv_project: bad arguments");
   TRY(project_impl(ctx, layer, feat, n, vis_mode, precision, out, false));
   CU(ctx, cudaStreamSynchronize(ctx->stream));
   return 0;
@@ -766,7 +806,73 @@ extern "C" int dcv_project(dcv_ctx* ctx, int layer, const int* feat, int n, int 
 
 extern "C" int dcv_project_dev(dcv_ctx* ctx, int layer, const int* feat, int n, int vis_mode, int precision, float* out_dev) {
   ENTER(ctx);
+  if (!feat) return ctx->fail(DCV_ERR_ARG, "dcv_project: bad arguments");
   return project_impl(ctx, layer, feat, n, vis_mode, precision, out_dev, true);
+}
+
+extern "C" int dcv_project_fmt(dcv_ctx* ctx, int layer, const int* feat, int n, int vis_mode, int precision, int out_format,
+                               void* out) {
+  ENTER(ctx);
+  if (!feat) return ctx->fail(DCV_ERR_ARG, "dcv_project: bad arguments");
+  TRY(project_impl(ctx, layer, feat, n, vis_mode, precision, out, false, out_format));
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+extern "C" int dcv_project_fmt_dev(dcv_ctx* ctx, int layer, const int* feat, int n, int vis_mode, int precision, int out_format,
+                                   void* out_dev) {
+  ENTER(ctx);
+  if (!feat) return ctx->fail(DCV_ERR_ARG, "dcv_project: bad arguments");
+  return project_impl(ctx, layer, feat, n, vis_mode, precision, out_dev, true, out_format);
+}
+
+// ---- request tail (main.py:60-72) ---------------------------------------------------------------------
+// uint8 BGR image -> caffe preprocess -> forward tape -> per-channel sums -> top-4 maps -> four projections ->
+// 2x2 mosaic -> de-process, all on the device: 3*H*W bytes go up, 12*H*W bytes (+ 5 ints) come back.
+extern "C" int dcv_request_mosaic(dcv_ctx* ctx, const uint8_t* img_bgr, int H, int W, int layer, int vis_mode, int precision,
+                                  uint8_t* out_mosaic, int* feats_out) {
+  ENTER(ctx);
+  if (!img_bgr || !out_mosaic || H <= 0 || W <= 0) return ctx->fail(DCV_ERR_ARG, "dcv_request_mosaic: bad arguments");
+  if (layer < 0 || layer >= (int)ctx->net.size()) return ctx->fail(DCV_ERR_ARG, "dcv_request_mosaic: layer %d out of range", layer);
+  const size_t npix = (size_t)H * W;
+  const size_t o_img = 0, o_pre = align256(npix * 3), o_mos = o_pre + align256(npix * 3 * sizeof(float));
+  const size_t o_proj = o_mos + align256(npix * 12);
+  TRY(ctx->stage.ensure(ctx, o_proj + align256(4 * npix * 3 * sizeof(float))));
+  char* base = (char*)ctx->stage.p;
+  CU(ctx, cudaMemcpyAsync(base + o_img, img_bgr, npix * 3, cudaMemcpyHostToDevice, ctx->stream));
+  launch_preprocess_caffe((const uint8_t*)(base + o_img), npix, (float*)(base + o_pre), ctx->stream); ctx->launches++;
+  TRY(forward_impl(ctx, (const float*)(base + o_pre), true, 1, H, W, layer));
+  if (ctx->in_C != 3) return ctx->fail(DCV_ERR_UNSUPPORTED, "dcv_request_mosaic: the network takes %d input channels, the request image has 3", ctx->in_C);
+  const Layer& l = ctx->net[layer];
+  // find_top_filters (deepdream.py:369-380) on the device; the reference sums a float64 array at pool layers
+  const size_t rows = (size_t)l.B * l.H * l.W;
+  const int np = channel_sums_partials(rows, l.C);
+  TRY(ctx->scratch.ensure(ctx, ((size_t)np + 1) * l.C * sizeof(double)));
+  double* partial = (double*)ctx->scratch.p;
+  double* sums = partial + (size_t)np * l.C;
+  launch_channel_sums((const float*)l.act.p, rows, l.C, partial, np, sums, ctx->stream); ctx->launches += 2;
+  TRY(ctx->feat_dev.ensure(ctx, 8 * sizeof(int)));
+  launch_top_filters(sums, l.C, l.kind == LK_POOL ? 0 : 1, 4, (int*)ctx->feat_dev.p, ctx->stream); ctx->launches++;
+  CHECK_LAUNCH(ctx);
+  // main.py:67-68 indexes [0..3] of the top-8 list: with fewer than four positive maps the reference raises
+  // IndexError.  The count is needed on the host before the projections are queued (indices of -1 must not run).
+  int top4[5];
+  CU(ctx, cudaMemcpyAsync(top4, ctx->feat_dev.p, sizeof top4, cudaMemcpyDeviceToHost, ctx->stream));
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  if (feats_out) memcpy(feats_out, top4, 4 * sizeof(int));
+  if (top4[4] < 4) return ctx->fail(DCV_ERR_STATE, "list index out of range: layer %d has only %d feature maps with a positive sum", layer, top4[4]);
+  float* proj = (float*)(base + o_proj);
+  TRY(project_impl(ctx, layer, nullptr, 4, vis_mode, precision, proj, true));
+  const int npd = deprocess_partials(4 * npix * 3);
+  TRY(ctx->scratch.ensure(ctx, (size_t)npd * 2 * sizeof(double)));
+  {
+    ProfScope ps(ctx, DCV_K_OTHER, 0.0, 9.0 * 4 * npix * 3);
+    launch_deprocess_mosaic(proj, H, W, 3, (double*)ctx->scratch.p, npd, (uint8_t*)(base + o_mos), ctx->stream); ctx->launches += 2;
+  }
+  CHECK_LAUNCH(ctx);
+  CU(ctx, cudaMemcpyAsync(out_mosaic, base + o_mos, npix * 12, cudaMemcpyDeviceToHost, ctx->stream));
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  return 0;
 }
 
 // ---- de-process -------------------------------------------------------------------------------------
@@ -810,7 +916,6 @@ extern "C" int dcv_deprocess(dcv_ctx* ctx, float* x, size_t n, uint8_t* out, int
 }
 
 // ---- standalone operators on host buffers -----------------------------------------------------------
-static size_t align256(size_t b) { return (b + 255) & ~(size_t)255; }
 
 extern "C" int dcv_maxpool_switch(dcv_ctx* ctx, const float* x, int B, int H, int W, int C, float* pooled, uint8_t* sw) {
   ENTER(ctx);

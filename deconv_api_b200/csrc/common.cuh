@@ -57,6 +57,14 @@ int channel_sums_partials(size_t rows, int C);
 void launch_deprocess(const float* x, size_t n, double* partial, int npartial, uint8_t* out, float* norm, cudaStream_t s);
 int deprocess_partials(size_t n);
 void launch_sum_stats(const float* x, size_t n, double* partial, int npartial, cudaStream_t s);
+// batched de-process: `items` arrays of `len` floats, each with its own mean / std; partial: items*kItemPartials*2 doubles
+constexpr int kItemPartials = 8;
+void launch_deprocess_items(const float* x, int items, size_t len, double* partial, uint8_t* out, cudaStream_t s);
+void launch_convert_bf16(const float* x, size_t n, __nv_bfloat16* out, cudaStream_t s);
+// request tail (main.py:60-72): caffe preprocess of a uint8 image, top-k feature selection, 2x2 mosaic + de-process
+void launch_preprocess_caffe(const uint8_t* img, size_t npix, float* out, cudaStream_t s);
+void launch_top_filters(const double* sums, int C, int as_f32, int top, int* feat_out, cudaStream_t s);
+void launch_deprocess_mosaic(const float* x, int H, int W, int C, double* partial, int npartial, uint8_t* out, cudaStream_t s);
 // seed maps: maps[(k*B+b), y, x] = act[b, y, x, feat[k]]
 void launch_gather_map(const float* act, int B, int H, int W, int C, const int* feat_dev, int n, float* maps, cudaStream_t s);
 // DCV_VIS_MAX: maps (n, len) -> keep only the entries equal to the map maximum

@@ -314,6 +314,207 @@ void launch_deprocess(const float* x, size_t n, double* partial, int npartial, u
   deprocess_map_kernel<<<grid_for((n + 3) / 4, 256, 8), 256, 0, s>>>(x, n, partial, npartial, out, norm);
 }
 
+// ------------------------------------------------------------------------------------------------
+// Batched de-process: `items` projections of `len` floats each, every one normalised by ITS OWN mean / std
+// (deprocess_image applied per projection, deepdream.py:483-498), uint8 out.  Same arithmetic as the kernels above;
+// kItemPartials blocks per item in the statistics pass, their partials summed in a fixed order by every map block.
+// VEC: len % 4 == 0 (every item starts 16-byte aligned) -> float4 / uchar4 accesses; otherwise scalar.
+template <bool VEC>
+__global__ void __launch_bounds__(256) deprocess_items_stats_kernel(const float* __restrict__ x, size_t len,
+                                                                    double* __restrict__ partial) {
+  const float* xi = x + (size_t)blockIdx.y * len;
+  double s = 0.0, q = 0.0;
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  const size_t i0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (VEC) {
+    const float4* x4 = reinterpret_cast<const float4*>(xi);
+    const size_t n4 = len / 4;
+    size_t i = i0;
+    for (; i + stride < n4; i += 2 * stride) {
+      const float4 a = __ldg(x4 + i), b = __ldg(x4 + i + stride);
+      s += ((double)a.x + (double)a.y + (double)a.z + (double)a.w) + ((double)b.x + (double)b.y + (double)b.z + (double)b.w);
+      q += ((double)a.x * a.x + (double)a.y * a.y + (double)a.z * a.z + (double)a.w * a.w) +
+           ((double)b.x * b.x + (double)b.y * b.y + (double)b.z * b.z + (double)b.w * b.w);
+    }
+    for (; i < n4; i += stride) {
+      const float4 a = __ldg(x4 + i);
+      s += (double)a.x + (double)a.y + (double)a.z + (double)a.w;
+      q += (double)a.x * a.x + (double)a.y * a.y + (double)a.z * a.z + (double)a.w * a.w;
+    }
+  } else {
+    for (size_t i = i0; i < len; i += stride) { const float a = __ldg(xi + i); s += a; q += (double)a * a; }
+  }
+  __shared__ double rs[8], rq[8];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    s += __shfl_xor_sync(0xffffffffu, s, o);
+    q += __shfl_xor_sync(0xffffffffu, q, o);
+  }
+  if ((threadIdx.x & 31) == 0) { rs[threadIdx.x >> 5] = s; rq[threadIdx.x >> 5] = q; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double ts = 0.0, tq = 0.0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) { ts += rs[k]; tq += rq[k]; }
+    double* p = partial + ((size_t)blockIdx.y * gridDim.x + blockIdx.x) * 2;
+    p[0] = ts; p[1] = tq;
+  }
+}
+
+template <bool VEC>
+__global__ void __launch_bounds__(256) deprocess_items_map_kernel(const float* __restrict__ x, size_t len,
+                                                                  const double* __restrict__ partial, int npartial,
+                                                                  uint8_t* __restrict__ out) {
+  const float* xi = x + (size_t)blockIdx.y * len;
+  uint8_t* oi = out + (size_t)blockIdx.y * len;
+  double ts, tq;
+  block_sum_partials(partial + (size_t)blockIdx.y * npartial * 2, npartial, ts, tq);
+  const double dmean = ts / (double)len;
+  double var = tq / (double)len - dmean * dmean;
+  if (var < 0.0) var = 0.0;
+  const float mean = (float)dmean, denom = (float)(sqrt(var) + 1e-7);
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  const size_t i0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (VEC) {
+    const float4* x4 = reinterpret_cast<const float4*>(xi);
+    const size_t n4 = len / 4;
+#pragma unroll 4
+    for (size_t i = i0; i < n4; i += stride) {
+      const float4 a = __ldg(x4 + i);
+      uchar4 r;
+      r.x = deprocess_one(a.x, mean, denom);
+      r.y = deprocess_one(a.y, mean, denom);
+      r.z = deprocess_one(a.z, mean, denom);
+      r.w = deprocess_one(a.w, mean, denom);
+      reinterpret_cast<uchar4*>(oi)[i] = r;
+    }
+  } else {
+    for (size_t i = i0; i < len; i += stride) oi[i] = deprocess_one(__ldg(xi + i), mean, denom);
+  }
+}
+
+void launch_deprocess_items(const float* x, int items, size_t len, double* partial, uint8_t* out, cudaStream_t s) {
+  if (items <= 0 || len == 0) return;
+  const dim3 grid(kItemPartials, items);
+  if ((len & 3) == 0) {
+    deprocess_items_stats_kernel<true><<<grid, 256, 0, s>>>(x, len, partial);
+    deprocess_items_map_kernel<true><<<grid, 256, 0, s>>>(x, len, partial, kItemPartials, out);
+  } else {
+    deprocess_items_stats_kernel<false><<<grid, 256, 0, s>>>(x, len, partial);
+    deprocess_items_map_kernel<false><<<grid, 256, 0, s>>>(x, len, partial, kItemPartials, out);
+  }
+}
+
+// fp32 -> bf16 (round to nearest even), the compact result format of the projection entry points
+__global__ void __launch_bounds__(256) convert_bf16_kernel(const float* __restrict__ x, size_t n, __nv_bfloat16* __restrict__ out) {
+  const size_t n4 = n / 4, stride = (size_t)gridDim.x * blockDim.x;
+  const float4* x4 = reinterpret_cast<const float4*>(x);
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
+    const float4 a = __ldg(x4 + i);
+    __nv_bfloat162 lo = __floats2bfloat162_rn(a.x, a.y), hi = __floats2bfloat162_rn(a.z, a.w);
+    uint2 pk;
+    pk.x = *reinterpret_cast<uint32_t*>(&lo);
+    pk.y = *reinterpret_cast<uint32_t*>(&hi);
+    reinterpret_cast<uint2*>(out)[i] = pk;
+  }
+  if (blockIdx.x == 0 && threadIdx.x < (n & 3)) out[n4 * 4 + threadIdx.x] = __float2bfloat16_rn(x[n4 * 4 + threadIdx.x]);
+}
+
+void launch_convert_bf16(const float* x, size_t n, __nv_bfloat16* out, cudaStream_t s) {
+  if (!n) return;
+  convert_bf16_kernel<<<grid_for((n + 3) / 4, 256, 8), 256, 0, s>>>(x, n, out);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Request tail of the API (reference main.py:60-72) on the device.
+// 'caffe' preprocess of Keras-Applications 1.0.8 as main.py:60-61 applies it: float32(pixel), channel axis
+// reversed, minus [103.939, 116.779, 123.68] in the reversed order.  img: npix x 3 bytes.
+__global__ void preprocess_caffe_kernel(const uint8_t* __restrict__ img, size_t npix, float* __restrict__ out) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < npix; i += (size_t)gridDim.x * blockDim.x) {
+    const uint8_t* p = img + 3 * i;
+    out[3 * i + 0] = (float)p[2] - 103.939f;
+    out[3 * i + 1] = (float)p[1] - 116.779f;
+    out[3 * i + 2] = (float)p[0] - 123.68f;
+  }
+}
+
+void launch_preprocess_caffe(const uint8_t* img, size_t npix, float* out, cudaStream_t s) {
+  if (!npix) return;
+  preprocess_caffe_kernel<<<grid_for(npix, 256), 256, 0, s>>>(img, npix, out);
+}
+
+// find_top_filters (deepdream.py:369-380) on the per-channel fp64 sums, on the device: keep sums > 0, order by the
+// sum (as float32 where the reference sums a float32 array) descending, ties in index order (Python's sort is
+// stable), first `top`.  One block; feat_out[0..top) = indices (-1 where fewer exist), feat_out[top] = how many.
+__global__ void __launch_bounds__(256) top_filters_kernel(const double* __restrict__ sums, int C, int as_f32, int top,
+                                                          int* __restrict__ feat_out) {
+  __shared__ int chosen[16];
+  __shared__ double bv[256];
+  __shared__ int bi[256];
+  int count = 0;
+  for (int t = 0; t < top; ++t) {
+    double best = 0.0;
+    int besti = -1;
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+      double v = sums[c];
+      if (as_f32) v = (double)(float)v;
+      if (!(v > 0.0)) continue;
+      bool taken = false;
+      for (int k = 0; k < t; ++k) taken |= (chosen[k] == c);
+      if (taken) continue;
+      if (besti < 0 || v > best) { best = v; besti = c; }          // c ascends: the first of equal sums is kept
+    }
+    bv[threadIdx.x] = best; bi[threadIdx.x] = besti;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+      if ((int)threadIdx.x < o) {
+        const double v2 = bv[threadIdx.x + o];
+        const int i2 = bi[threadIdx.x + o];
+        const int i1 = bi[threadIdx.x];
+        if (i2 >= 0 && (i1 < 0 || v2 > bv[threadIdx.x] || (v2 == bv[threadIdx.x] && i2 < i1))) { bv[threadIdx.x] = v2; bi[threadIdx.x] = i2; }
+      }
+      __syncthreads();
+    }
+    if (threadIdx.x == 0) { chosen[t] = bi[0]; feat_out[t] = bi[0]; }
+    if (bi[0] >= 0) ++count;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) feat_out[top] = count;
+}
+
+void launch_top_filters(const double* sums, int C, int as_f32, int top, int* feat_out, cudaStream_t s) {
+  top_filters_kernel<<<1, 256, 0, s>>>(sums, C, as_f32, top, feat_out);
+}
+
+// 2x2 mosaic + de-process (main.py:67-72): x = four projections (4,H,W,C) fp32, out = (2H,2W,C) uint8 with
+// projection 0 | 1 on top of 2 | 3; mean / std over the whole mosaic = over the four projections together
+// (partials from deprocess_stats_kernel over the 4*H*W*C floats).
+__global__ void __launch_bounds__(256) deprocess_mosaic_kernel(const float* __restrict__ x, int H, int W, int C,
+                                                               const double* __restrict__ partial, int npartial,
+                                                               uint8_t* __restrict__ out) {
+  double ts, tq;
+  block_sum_partials(partial, npartial, ts, tq);
+  const size_t per = (size_t)H * W * C, n = 4 * per;
+  const double dmean = ts / (double)n;
+  double var = tq / (double)n - dmean * dmean;
+  if (var < 0.0) var = 0.0;
+  const float mean = (float)dmean, denom = (float)(sqrt(var) + 1e-7);
+  const size_t rowlen = (size_t)W * C;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const int item = (int)(i / per);
+    const size_t r = i % per;
+    const size_t y = r / rowlen, xc = r % rowlen;
+    const size_t oy = y + (size_t)(item >> 1) * H, ox = xc + (size_t)(item & 1) * rowlen;
+    out[oy * 2 * rowlen + ox] = deprocess_one(__ldg(x + i), mean, denom);
+  }
+}
+
+void launch_deprocess_mosaic(const float* x, int H, int W, int C, double* partial, int npartial, uint8_t* out, cudaStream_t s) {
+  const size_t n = (size_t)4 * H * W * C;
+  deprocess_stats_kernel<<<npartial, 256, 0, s>>>(x, n, partial);
+  deprocess_mosaic_kernel<<<grid_for(n, 256, 8), 256, 0, s>>>(x, H, W, C, partial, npartial, out);
+}
+
 // fp64 (sum, sum of squares) block partials of x[0..n): partial[2*b], partial[2*b+1]; x 16-byte aligned
 void launch_sum_stats(const float* x, size_t n, double* partial, int npartial, cudaStream_t s) {
   deprocess_stats_kernel<<<npartial, 256, 0, s>>>(x, n, partial);

@@ -14,6 +14,13 @@ FP32, BF16 = 0, 1
 VIS = {"all": 0, "max": 1}
 _PREC = {"fp32": FP32, "bf16": BF16, FP32: FP32, BF16: BF16}
 ACT = {"linear": 0, None: 0, "relu": 1, "softmax": 2}
+# result formats of project(): name -> (dcv_out_format id, numpy dtype of the returned array)
+OUT_FORMATS = {"f32": (0, np.float32), "bf16": (1, np.uint16), "u8": (2, np.uint8)}
+
+
+def bf16_bits_to_f32(a):
+    """uint16 bf16 bit patterns (project(..., out_format='bf16')) -> float32 values."""
+    return (np.asarray(a, np.uint16).astype(np.uint32) << 16).view(np.float32)
 
 _default_lock = threading.Lock()
 _default_engines = {}
@@ -192,21 +199,52 @@ class Engine(object):
         return out
 
     # -- projection
-    def project(self, idx, feats, mode="all", precision="fp32", out=None):
-        """-> (n, B, H0, W0, C0) float32.  `out` may be a preallocated (e.g. pinned) array."""
+    def project(self, idx, feats, mode="all", precision="fp32", out=None, out_format="f32"):
+        """-> (n, B, H0, W0, C0) projections.  out_format 'f32' (what the reference returns), 'bf16' (uint16 bit
+        patterns, see bf16_bits_to_f32) or 'u8' (every projection passed through deprocess_image on the GPU).
+        `out` may be a preallocated (e.g. pinned) array of the matching dtype."""
         feats = np.ascontiguousarray(feats, dtype=np.int32)
         n = int(feats.size)
+        fmt, dtype = OUT_FORMATS[out_format]
         shape = (n,) + tuple(self.input_shape)
         if out is None:
-            out = np.empty(shape, np.float32)
-        assert out.dtype == np.float32 and out.size == int(np.prod(shape)) and out.flags.c_contiguous
-        self._ck(self.lib.dcv_project(self.ctx, int(idx), _ptr(feats), n, VIS[mode], precision_id(precision), _ptr(out)))
+            out = np.empty(shape, dtype)
+        assert out.dtype == dtype and out.size == int(np.prod(shape)) and out.flags.c_contiguous
+        if fmt == 0:
+            self._ck(self.lib.dcv_project(self.ctx, int(idx), _ptr(feats), n, VIS[mode], precision_id(precision), _ptr(out)))
+        else:
+            self._ck(self.lib.dcv_project_fmt(self.ctx, int(idx), _ptr(feats), n, VIS[mode], precision_id(precision), fmt,
+                                              _ptr(out)))
         return out.reshape(shape)
 
-    def project_dev(self, idx, feats, out_dev_ptr, mode="all", precision="fp32"):
+    def project_dev(self, idx, feats, out_dev_ptr, mode="all", precision="fp32", out_format="f32"):
         feats = np.ascontiguousarray(feats, dtype=np.int32)
-        self._ck(self.lib.dcv_project_dev(self.ctx, int(idx), _ptr(feats), int(feats.size), VIS[mode],
-                                          precision_id(precision), ctypes.c_void_p(out_dev_ptr)))
+        fmt = OUT_FORMATS[out_format][0]
+        if fmt == 0:
+            self._ck(self.lib.dcv_project_dev(self.ctx, int(idx), _ptr(feats), int(feats.size), VIS[mode],
+                                              precision_id(precision), ctypes.c_void_p(out_dev_ptr)))
+        else:
+            self._ck(self.lib.dcv_project_fmt_dev(self.ctx, int(idx), _ptr(feats), int(feats.size), VIS[mode],
+                                                  precision_id(precision), fmt, ctypes.c_void_p(out_dev_ptr)))
+
+    def request_mosaic(self, img_bgr_u8, idx, mode="all", precision="fp32"):
+        """The request tail of reference main.py:60-72 in one call: (H,W,3) uint8 image as cv2 decoded it ->
+        ((2H,2W,3) uint8 mosaic of the four strongest maps of layer `idx`, their feature indices).  Raises IndexError
+        like main.py:67-68 when fewer than four maps have a positive sum."""
+        img = np.ascontiguousarray(img_bgr_u8, dtype=np.uint8)
+        assert img.ndim == 3 and img.shape[2] == 3, "image must be (H,W,3) uint8"
+        H, W, _ = img.shape
+        out = np.empty((2 * H, 2 * W, 3), np.uint8)
+        feats = np.empty((4,), np.int32)
+        rc = self.lib.dcv_request_mosaic(self.ctx, _ptr(img), H, W, int(idx), VIS[mode], precision_id(precision), _ptr(out),
+                                         _ptr(feats))
+        if rc == -3:
+            msg = (self.lib.dcv_last_error(self.ctx) or b"").decode("utf-8", "replace")
+            if msg.startswith("list index out of range"):
+                raise IndexError(msg)
+        self._ck(rc)
+        self.input_shape = (1, H, W, 3)
+        return out, feats
 
     # -- image tail
     def deprocess(self, x, mutate=True):

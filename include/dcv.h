@@ -43,10 +43,16 @@ enum dcv_status {
 /* visualize_mode of visualize_all_layers (deepdream.py:383,454-460) */
 enum dcv_vis_mode { DCV_VIS_ALL = 0, DCV_VIS_MAX = 1 };
 
-/* arithmetic of the backward projection chain.  FP32: CUDA-core FFMA, fp32 tape and chain (parity
- * mode, rel-L2 <= 1e-5).  BF16: tcgen05 tensor-core chain on bf16 operands with fp32 accumulation
- * (throughput mode, rel-L2 <= 2e-2); the forward tape and the switches stay fp32 in both. */
+/* arithmetic of the backward projection chain.  FP32 (parity mode, rel-L2 <= 1e-5): fp32 data between the layers;
+ * the convs run on the tcgen05 tensor cores with both operands split into three bf16 planes and the six
+ * significant cross products accumulated in fp32 registers (DCV_FP32_TC=0 in the environment selects the
+ * CUDA-core FFMA kernels instead).  BF16 (throughput mode, rel-L2 <= 2e-2): tcgen05 chain on bf16 operands
+ * with fp32 accumulation in TMEM.  The forward tape and the switches are fp32-accurate in both. */
 enum dcv_precision { DCV_FP32 = 0, DCV_BF16 = 1 };
+
+/* element type of the projections returned by dcv_project_fmt.  U8 = deprocess_image (deepdream.py:483-498)
+ * applied to every projection separately, which is what the reference's only consumer does next (main.py:72). */
+enum dcv_out_format { DCV_OUT_F32 = 0, DCV_OUT_BF16 = 1, DCV_OUT_U8 = 2 };
 
 /* activation ids for dcv_net_add_dense */
 enum dcv_act { DCV_ACT_LINEAR = 0, DCV_ACT_RELU = 1, DCV_ACT_SOFTMAX = 2 };
@@ -142,6 +148,25 @@ DCV_API int dcv_project(dcv_ctx* ctx, int layer, const int* feat, int n, int vis
 /* Same with the result left in device memory (n*B*H0*W0*C0 floats at out_dev). */
 DCV_API int dcv_project_dev(dcv_ctx* ctx, int layer, const int* feat, int n, int vis_mode, int precision, float* out_dev);
 
+/* The same projections in a compact result format (dcv_out_format): BF16 halves and U8 quarters the bytes that leave
+ * the GPU.  U8: every (feature, image) projection is de-processed with its own mean / std, exactly deprocess_image
+ * (deepdream.py:483-498) called on that projection, as main.py:72 does with the reference's result.  out: n*B*H0*W0*C0
+ * elements of the chosen type (bf16 = the upper 16 bits of the float, round to nearest even). */
+DCV_API int dcv_project_fmt(dcv_ctx* ctx, int layer, const int* feat, int n, int vis_mode, int precision, int out_format,
+                            void* out);
+DCV_API int dcv_project_fmt_dev(dcv_ctx* ctx, int layer, const int* feat, int n, int vis_mode, int precision, int out_format,
+                                void* out_dev);
+
+/* ---- request tail: replaces what return_deconv does between cv2.resize and cv2.imencode (main.py:60-72) in ONE call:
+ * img_to_array + preprocess_input 'caffe' (channel flip, mean subtraction; main.py:60-61) of the uint8 (H,W,3) image
+ * that cv2 decoded, forward tape up to `layer`, find_top_filters (deepdream.py:369-380), projection of the four
+ * strongest maps (main.py:64,67-68 use [0..3] of the top-8 list), 2x2 mosaic (main.py:67-69: maps 0|1 over 2|3) and
+ * deprocess_image over the whole mosaic (main.py:72).  out_mosaic: (2H,2W,3) uint8; feats_out (optional): the four
+ * feature indices.  DCV_ERR_STATE when fewer than four maps have a positive sum (the reference raises IndexError).
+ * Only 3*H*W bytes go to the GPU and 12*H*W come back; the tape stays valid for later dcv_project calls. */
+DCV_API int dcv_request_mosaic(dcv_ctx* ctx, const uint8_t* img_bgr, int H, int W, int layer, int vis_mode, int precision,
+                               uint8_t* out_mosaic, int* feats_out);
+
 /* ---- image tail: replaces deprocess_image (deepdream.py:483-498): (x-mean)/(std+1e-7)*0.1+0.5,
  * clip to [0,1], *255, clip, truncate to uint8; population std.  n elements in, n bytes out.
  * The reference mutates its argument in place up to the "+= 0.5" step (:485-490); with mutate != 0
@@ -201,8 +226,9 @@ DCV_API int dcv_dense_transpose(dcv_ctx* ctx, const float* x, const float* w, in
  * shapes: n_oct (h,w) pairs, smallest first, the last one equal to (H,W); jitter: n_oct*iterations (oy,ox)
  * pairs drawn by the caller (so that an oracle can use the same stream); losses (optional, host):
  * n_oct*iterations loss values BEFORE each update (costs a device sync per iteration).
- * precision: DCV_FP32 = FFMA forward and backward; DCV_BF16 = forward AND backward on tcgen05 with a bf16
- * tape in the padded-flat layout (layer 0, K = 27, stays FFMA); the image and its update stay fp32. ---- */
+ * precision: DCV_FP32 = fp32-accurate forward and backward (split-operand tcgen05 kernels; FFMA with DCV_FP32_TC=0);
+ * DCV_BF16 = forward AND backward on tcgen05 with a bf16 tape in the padded-flat layout (layer 0, K = 27, runs as
+ * im2col rows + one K = 64 GEMM); the image and its update stay fp32. ---- */
 DCV_API int dcv_dream(dcv_ctx* ctx, const float* img, int B, int H, int W, const int* loss_layers, const float* coeffs, int nl,
                       const int* shapes, int n_oct, int iterations, float step, const int* jitter, int precision, float* out,
                       double* losses);

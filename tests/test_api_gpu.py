@@ -16,8 +16,12 @@ def _post(client, png, layer):
     return client.post("/", data={"file": uri, "layer": layer})
 
 
-def test_post_matches_reference_response(golden):
+@pytest.mark.parametrize("fast_tail", [False, True])
+def test_post_matches_reference_response(golden, monkeypatch, fast_tail):
+    """fast_tail False: the reference's own sequence (full sweep, host mosaic, deprocess_image); True: the fused
+    request tail (DCV_API_FAST=1, one dcv_request_mosaic call).  Both must give the reference's response."""
     from deconv_api_b200 import main as api
+    monkeypatch.setattr(api, "FAST_TAIL", fast_tail)
     g = golden("api_reference.npz")
     client = TestClient(api.app)
     for layer in ("block3_conv3", "block1_conv2"):
@@ -38,8 +42,10 @@ def test_post_matches_reference_response(golden):
         assert d.mean() < 0.25 and np.percentile(d, 99.9) <= 6, (layer, d.mean(), d.max())
 
 
-def test_unknown_layer_is_500_like_reference(golden):
+@pytest.mark.parametrize("fast_tail", [False, True])
+def test_unknown_layer_is_500_like_reference(golden, monkeypatch, fast_tail):
     from deconv_api_b200 import main as api
+    monkeypatch.setattr(api, "FAST_TAIL", fast_tail)
     g = golden("api_reference.npz")
     client = TestClient(api.app, raise_server_exceptions=False)
     assert _post(client, g["request_png"].tobytes(), "nope").status_code == 500
