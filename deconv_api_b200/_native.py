@@ -37,6 +37,7 @@ SIGNATURES = {
     "dcv_net_add_dense": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_void_p, _c.c_int, _c.c_int, _c.c_int]),
     "dcv_net_num_layers": (_c.c_int, [_c.c_void_p]),
     "dcv_set_forward_mode": (_c.c_int, [_c.c_void_p, _c.c_int]),
+    "dcv_set_fp32_mode": (_c.c_int, [_c.c_void_p, _c.c_int]),
     "dcv_forward": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_int, _c.c_int, _c.c_int, _c.c_int]),
     "dcv_forward_dev": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_int, _c.c_int, _c.c_int, _c.c_int]),
     "dcv_layer_shape": (_c.c_int, [_c.c_void_p, _c.c_int, P_I32]),

@@ -106,6 +106,7 @@ extern "C" int dcv_create(int device, dcv_ctx** out) {
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ctx->ev_copied[i], cudaEventDisableTiming);
   }
   if (e != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete ctx; return DCV_ERR_CUDA; }
+  if (const char* t = getenv("DCV_FP32_TC")) ctx->fp32_tc = atoi(t) != 0;
   const char* ws = getenv("DCV_WORKSPACE_MB");
   ctx->workspace_budget = (ws ? (size_t)atoll(ws) : (size_t)12288) << 20;
   *out = ctx;
@@ -371,6 +372,17 @@ extern "C" int dcv_set_forward_mode(dcv_ctx* ctx, int mode) {
   return 0;
 }
 
+extern "C" int dcv_set_fp32_mode(dcv_ctx* ctx, int mode) {
+  ENTER(ctx);
+  if (mode != 0 && mode != 1) return ctx->fail(DCV_ERR_ARG, "dcv_set_fp32_mode: mode must be 0 (FFMA) or 1 (tensor cores)");
+  if (ctx->fp32_tc != mode) {
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    dream_release_graphs(ctx);          // captured fp32 iterations hold the other kernels
+    ctx->fp32_tc = mode;
+  }
+  return 0;
+}
+
 extern "C" int dcv_forward(dcv_ctx* ctx, const float* img, int B, int H, int W, int upto) {
   ENTER(ctx);
   TRY(forward_impl(ctx, img, false, B, H, W, upto));
@@ -487,11 +499,7 @@ static int ensure_nonneg(dcv_ctx* ctx, bool& nonneg, float* data, size_t n) {
 // DCV_FP32 projections run their backward convs on the tensor cores too (operands split into three bf16 planes,
 // fp32 accumulation in registers: tc_exact.cuh) unless DCV_FP32_TC=0 asks for the FFMA kernels.  Measured on the
 // block5_conv3 sweep against the reference's golden projections: rel-L2 1.8e-6 (FFMA 6.3e-6), 3.6x the throughput.
-static bool fp32_on_tc(const dcv_ctx* ctx, const Layer& l) {
-  static const int fp32_tc = getenv("DCV_FP32_TC") ? atoi(getenv("DCV_FP32_TC")) : 1;
-  (void)ctx;
-  return fp32_tc != 0 && l.wd != nullptr;
-}
+static bool fp32_on_tc(const dcv_ctx* ctx, const Layer& l) { return ctx->fp32_tc != 0 && l.wd != nullptr; }
 
 static int project_chunk(dcv_ctx* ctx, int layer, int foff, int n, int vis_mode, int precision, float* final_dst,
                          float** result) {
@@ -969,9 +977,22 @@ extern "C" int dcv_conv3x3(dcv_ctx* ctx, const float* x, const float* w_hwio, co
   CU(ctx, cudaMemcpyAsync(base, x, nin * 4, cudaMemcpyHostToDevice, ctx->stream));
   CU(ctx, cudaMemcpyAsync(base + o1, w_hwio, nw * 4, cudaMemcpyHostToDevice, ctx->stream));
   if (bias) CU(ctx, cudaMemcpyAsync(base + o2, bias, (size_t)cout * 4, cudaMemcpyHostToDevice, ctx->stream));
-  ConvEpilogue e; e.bias = bias ? (const float*)(base + o2) : nullptr; e.relu = relu;
-  launch_conv3x3_fp32((const float*)base, (const float*)(base + o1), B, H, W, cin, cout, e, (float*)(base + o3), ctx->stream);
-  ctx->launches++;
+  if (ctx->fwd_mode == 1 && cin >= 16) {
+    // the kernel the forward tape uses for this layer shape (forward_impl): split-operand tcgen05
+    Layer tmp;
+    tmp.kind = LK_CONV; tmp.cin = cin; tmp.cout = cout; tmp.relu = relu ? 1 : 0;
+    tmp.w = (float*)(base + o1);
+    tmp.bias = bias ? (float*)(base + o2) : nullptr;
+    int r = tc_prepare_forward_exact(ctx, tmp);
+    if (!r) r = tc_conv_fwd_exact(ctx, tmp, (const float*)base, B, H, W, (float*)(base + o3));
+    if (!r && cudaStreamSynchronize(ctx->stream) != cudaSuccess) r = ctx->fail(DCV_ERR_CUDA, "dcv_conv3x3: kernel failed");
+    tc_free_layer(tmp);
+    if (r) return r;
+  } else {
+    ConvEpilogue e; e.bias = bias ? (const float*)(base + o2) : nullptr; e.relu = relu;
+    launch_conv3x3_fp32((const float*)base, (const float*)(base + o1), B, H, W, cin, cout, e, (float*)(base + o3), ctx->stream);
+    ctx->launches++;
+  }
   CHECK_LAUNCH(ctx);
   CU(ctx, cudaMemcpyAsync(out, base + o3, nout * 4, cudaMemcpyDeviceToHost, ctx->stream));
   CU(ctx, cudaStreamSynchronize(ctx->stream));
@@ -996,6 +1017,16 @@ extern "C" int dcv_deconv3x3(dcv_ctx* ctx, const float* x, const float* w_hwio, 
     tmp.wd = (float*)(base + o2);
     int r = tc_prepare_layer(ctx, tmp);
     if (!r) r = tc_deconv(ctx, tmp, (const float*)base, B, H, W, (float*)(base + o3));
+    if (!r && cudaStreamSynchronize(ctx->stream) != cudaSuccess) r = ctx->fail(DCV_ERR_CUDA, "dcv_deconv3x3: kernel failed");
+    tc_free_layer(tmp);
+    if (r) return r;
+  } else if (ctx->fp32_tc) {
+    // the kernels the DCV_FP32 projection chain uses: split-operand tcgen05 (GEMM + col2im form for <= 3 channels)
+    Layer tmp;
+    tmp.kind = LK_CONV; tmp.cin = cin; tmp.cout = cout; tmp.relu = relu ? 1 : 0;
+    tmp.wd = (float*)(base + o2);
+    int r = tc_prepare_backward_exact(ctx, tmp);
+    if (!r) r = tc_conv_bwd_exact(ctx, tmp, (const float*)base, B, H, W, (float*)(base + o3), tmp.relu);
     if (!r && cudaStreamSynchronize(ctx->stream) != cudaSuccess) r = ctx->fail(DCV_ERR_CUDA, "dcv_deconv3x3: kernel failed");
     tc_free_layer(tmp);
     if (r) return r;

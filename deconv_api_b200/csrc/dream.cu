@@ -319,8 +319,7 @@ int dream_backward(dcv_ctx* ctx, const LossSpec& ls, float** grad, double* loss_
         dream_prep_kernel<<<grid_for(n, 256), 256, 0, ctx->stream>>>(bufs[cur], (const float*)l.act.p, n, scale, has_g ? 1 : 0, l.relu);
         ctx->launches++;
       }
-      static const int fp32_tc = getenv("DCV_FP32_TC") ? atoi(getenv("DCV_FP32_TC")) : 1;
-      if (fp32_tc && l.wd) {
+      if (ctx->fp32_tc && l.wd) {
         // conv backward-data on the tensor cores, fp32-accurate (split operands, register accumulation)
         TRYD(tc_prepare_backward_exact(ctx, ctx->net[j]));
         TRYD(tc_conv_bwd_exact(ctx, l, bufs[cur], l.B, l.H, l.W, bufs[cur ^ 1], 0));

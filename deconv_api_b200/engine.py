@@ -152,8 +152,12 @@ class Engine(object):
 
     # -- forward tape
     def set_forward_mode(self, tensor_cores):
-        """False: FFMA fp32 forward (parity mode, default); True: tcgen05 split-operand forward (~2e-6 per layer)."""
+        """True (default): tcgen05 split-operand forward, fp32-accurate (~1e-6 per layer); False: FFMA fp32 forward."""
         self._ck(self.lib.dcv_set_forward_mode(self.ctx, 1 if tensor_cores else 0))
+
+    def set_fp32_mode(self, tensor_cores):
+        """Backward convs of the fp32 chain: True (default) split-operand tcgen05, False CUDA-core FFMA."""
+        self._ck(self.lib.dcv_set_fp32_mode(self.ctx, 1 if tensor_cores else 0))
 
     def forward(self, data, upto):
         data = _f32(data)

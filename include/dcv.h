@@ -121,6 +121,10 @@ DCV_API int dcv_forward(dcv_ctx* ctx, const float* img_nhwc, int B, int H, int W
  * core truncates when it adds into an accumulator): measured rel-L2 1e-7 .. 1e-6 per layer against float64, the same
  * as the FFMA kernel, at 3-10x its speed for batch 1; the first conv (K = 27) stays FFMA.  0: FFMA fp32 everywhere. */
 DCV_API int dcv_set_forward_mode(dcv_ctx* ctx, int mode);
+/* Arithmetic of the backward convs of the DCV_FP32 chain (projection, DeepDream, dcv_deconv3x3); no counterpart in
+ * the reference.  1 (default, or DCV_FP32_TC in the environment): the same split-operand tcgen05 kernels with fp32
+ * register accumulation; 0: CUDA-core FFMA.  Both meet rel-L2 <= 1e-5; the switch exists for A/B parity tests. */
+DCV_API int dcv_set_fp32_mode(dcv_ctx* ctx, int mode);
 DCV_API int dcv_forward_dev(dcv_ctx* ctx, const float* img_nhwc_dev, int B, int H, int W, int upto_layer);
 /* Shape of layer `layer`'s output in the current tape: dims[0..3] = B,H,W,C (H=W=1 after flatten). */
 DCV_API int dcv_layer_shape(const dcv_ctx* ctx, int layer, int dims[4]);
@@ -200,11 +204,13 @@ DCV_API int dcv_maxpool_switch(dcv_ctx* ctx, const float* x, int B, int H, int W
 /* DPooling.down (deepdream.py:141-150,191-209).  x (B,H/2,W/2,C), sw same shape -> out (B,H,W,C).
  * H and W must be even (the reference raises on odd sizes). */
 DCV_API int dcv_unpool_switch(dcv_ctx* ctx, const float* x, const uint8_t* sw, int B, int H, int W, int C, float* out);
-/* DConvolution2D.up (deepdream.py:91-100): out = act(conv3x3_same(x, W) + b). */
+/* DConvolution2D.up (deepdream.py:91-100): out = act(conv3x3_same(x, W) + b).  Runs the kernel the forward tape
+ * would use for this shape (dcv_set_forward_mode; tensor cores from 16 input channels up). */
 DCV_API int dcv_conv3x3(dcv_ctx* ctx, const float* x, const float* w_hwio, const float* bias,
                 int B, int H, int W, int cin, int cout, int relu, float* out);
 /* DConvolution2D.down (deepdream.py:102-111): out = act(conv3x3_same(x, flipT(W))), zero bias;
- * x has `cout` channels, out has `cin`.  precision selects the FFMA or the tensor-core kernel. */
+ * x has `cout` channels, out has `cin`.  precision: DCV_BF16 = the bf16 tcgen05 kernels, DCV_FP32 = the kernels of
+ * the fp32 chain (dcv_set_fp32_mode: split-operand tcgen05 by default, FFMA otherwise). */
 DCV_API int dcv_deconv3x3(dcv_ctx* ctx, const float* x, const float* w_hwio,
                   int B, int H, int W, int cin, int cout, int relu, int precision, float* out);
 

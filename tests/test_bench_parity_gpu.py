@@ -1,0 +1,77 @@
+"""Parity of the configurations that bench.py actually times (BASELINE.json configs[1] and the shape of configs[3]),
+through the C-ABI, against the oracle — every projection, both precisions.
+
+  * configs[1]: one 224x224 image, forward to block4_conv3, ALL 512 feature maps projected;
+  * configs[3] shape: a batch of VGG-size images sharing one tape, block5_conv3 on top, 64 maps: every (feature, image)
+    item reads the switches of ITS image (item % B in the kernels).
+
+Tolerances (north_star): rel-L2 <= 1e-5 per projection in the fp32 mode, <= 2e-2 in the bf16 mode.  Pool switches
+that differ from the oracle's must be near-ties of the fp32 conv below (conftest.following_tape)."""
+import numpy as np
+import pytest
+
+from oracle import keras_shim
+from deconv_api_b200 import synth, vgg16
+from conftest import following_tape, rel_l2
+
+pytestmark = pytest.mark.gpu
+
+FP32_TOL, BF16_TOL = 1e-5, 2e-2
+
+
+def _project_ref(tape, feats, batch=32):
+    out = []
+    for i in range(0, len(feats), batch):
+        out.append(tape.project([int(f) for f in feats[i:i + batch]]))
+    return np.concatenate(out, axis=0)
+
+
+def test_all_512_block4_conv3_maps_vs_oracle():
+    """The benchmarked step itself: bench.py's image (seed 0), every one of the 512 maps, fp32 and bf16."""
+    model = vgg16.VGG16(weights=None, include_top=False, input_shape=(224, 224, 3))
+    ref_model = keras_shim.VGG16(include_top=False, input_shape=(224, 224, 3))
+    img = synth.image_batch(1, 224, 224, seed0=0)
+    eng = model.bound_engine(upto="block4_conv3")
+    li = eng.index["block4_conv3"]
+    eng.forward(img, li)
+    tape, _ = following_tape(eng, ref_model, "block4_conv3", img)
+    feats = np.arange(512, dtype=np.int32)
+    want = _project_ref(tape, feats)
+    live = [k for k in range(512) if np.abs(want[k]).max() > 0]
+    assert len(live) > 400                                   # random-init VGG16: most maps are alive
+    for prec, tol in (("fp32", FP32_TOL), ("bf16", BF16_TOL)):
+        got = eng.project(li, feats, precision=prec)[:, 0]
+        assert got.shape == want.shape == (512, 224, 224, 3)
+        worst = max(rel_l2(got[k], want[k]) for k in live)
+        assert worst < tol, (prec, worst)
+        dead = [k for k in range(512) if k not in live]
+        assert all(np.abs(got[k]).max() == 0 for k in dead)   # a dead map projects to exactly zero
+        assert got.min() >= 0                                 # every projection ends in block1_conv1's own ReLU
+
+
+def test_config4_shape_batch_of_images_block5_conv3():
+    """Two VGG-size images in ONE tape, block5_conv3 on top, 64 maps, both precisions, per image against the oracle.
+    Image seed 4 has a 1-ulp near-tie in block2_pool (profiles/diag_b2.py): the flip handling is exercised too."""
+    model = vgg16.VGG16(weights=None, include_top=False, input_shape=(224, 224, 3))
+    ref_model = keras_shim.VGG16(include_top=False, input_shape=(224, 224, 3))
+    img = synth.image_batch(2, 224, 224, seed0=3)
+    eng = model.bound_engine(upto="block5_conv3")
+    li = eng.index["block5_conv3"]
+    eng.forward(img, li)
+    sums = eng.channel_sums(li)
+    feats = np.argsort(-sums, kind="stable")[:48].astype(np.int32)
+    feats = np.concatenate([feats, np.arange(0, 512, 32, dtype=np.int32)])          # + 16 fixed ones (some weak / dead)
+    assert feats.size == 64
+    tapes = [following_tape(eng, ref_model, "block5_conv3", img[b:b + 1], b=b)[0] for b in range(2)]
+    want = np.stack([_project_ref(t, feats) for t in tapes], axis=1)              # (64, 2, 224, 224, 3)
+    for prec, tol in (("fp32", FP32_TOL), ("bf16", BF16_TOL)):
+        got = eng.project(li, feats, precision=prec)
+        assert got.shape == want.shape
+        for k in range(64):
+            for b in range(2):
+                if np.abs(want[k, b]).max() > 0:
+                    assert rel_l2(got[k, b], want[k, b]) < tol, (prec, k, b)
+                else:
+                    assert np.abs(got[k, b]).max() == 0
+    # the two images really are different units: image 1's projections are not image 0's
+    assert rel_l2(want[0, 1], want[0, 0]) > 0.1

@@ -55,15 +55,33 @@ def test_pool_empty_and_odd(engine):
     assert rc == -1 and b"even" in engine.lib.dcv_last_error(engine.ctx)
 
 
+@pytest.fixture(params=["tensor_cores", "ffma"])
+def fp32_kernels(request, engine):
+    """Both kernel families behind the fp32 operators: the split-operand tcgen05 kernels (conv_exact_kernel, the
+    default of the forward tape and of the DCV_FP32 chain; GEMM + col2im form for <= 3 output channels) and the
+    CUDA-core FFMA kernel.  Both are held to the same 1e-5."""
+    tc = request.param == "tensor_cores"
+    engine.set_forward_mode(tc)
+    engine.set_fp32_mode(tc)
+    yield request.param
+    engine.set_forward_mode(True)
+    engine.set_fp32_mode(True)
+
+
 @pytest.mark.parametrize("B,H,W,cin,cout,bias,relu", [
-    (1, 16, 16, 3, 64, True, True),        # first layer: K = 27
-    (2, 20, 12, 64, 64, True, True),
-    (1, 14, 14, 512, 512, False, True),    # block5 shape
-    (1, 9, 11, 8, 5, True, False),         # odd sizes, ragged channels, linear
-    (1, 33, 17, 16, 24, False, True),
+    (1, 16, 16, 3, 64, True, True),        # first layer: K = 27 (FFMA in both modes, like the tape)
+    (2, 20, 12, 64, 64, True, True),       # N tile 64
+    (1, 14, 14, 512, 512, False, True),    # block5 shape: few rows -> N tile 64, 8 k-blocks
+    (1, 9, 11, 8, 5, True, False),         # odd sizes, ragged channels, linear (cin < 16: FFMA)
+    (1, 33, 17, 16, 24, False, True),      # smallest tensor-core K (padded to 64), ragged N
     (1, 224, 224, 3, 64, True, True),
+    (4, 56, 56, 64, 256, True, True),      # enough rows for the N tile 128 form (204 tiles)
+    (1, 33, 17, 16, 8, True, True),        # <= 16 output channels: N tile 16
+    (2, 9, 7, 40, 72, True, False),        # ragged K and N with bias, odd sizes, linear
+    (300, 4, 4, 64, 64, True, True),       # many tiny items: tiles straddle many item boundaries
+    (3, 28, 28, 256, 512, False, True),    # block4 shape, batch 3
 ])
-def test_conv3x3_vs_oracle(engine, B, H, W, cin, cout, bias, relu):
+def test_conv3x3_vs_oracle(engine, fp32_kernels, B, H, W, cin, cout, bias, relu):
     rng = np.random.default_rng(B * 1000 + H + cin + cout)
     x = rng.normal(0, 1, (B, H, W, cin)).astype(np.float32)
     lim = np.sqrt(6.0 / (9 * cin + 9 * cout))
@@ -76,12 +94,18 @@ def test_conv3x3_vs_oracle(engine, B, H, W, cin, cout, bias, relu):
 
 
 @pytest.mark.parametrize("B,H,W,cin,cout,relu", [
-    (1, 16, 16, 3, 64, True),              # last backward layer: 64 -> 3 channels
+    (1, 16, 16, 3, 64, True),              # last backward layer: 64 -> 3 channels (exact GEMM + col2im)
     (2, 12, 20, 64, 128, True),
     (1, 14, 14, 512, 512, True),
     (1, 7, 9, 5, 8, False),
+    (2, 31, 45, 3, 64, True),              # last-layer kernel: ragged 14x14 patches, two items
+    (4, 56, 56, 128, 64, True),            # N tile 64 with K = 64... the block2_conv1 shape
+    (6, 56, 56, 256, 128, True),           # N tile 128 (228 tiles)
+    (2, 9, 7, 72, 40, False),              # ragged channels, odd sizes, linear
+    (300, 4, 4, 64, 64, True),
+    (1, 33, 17, 8, 16, True),              # N tile 16 through the generic kernel (9 * 8 > 32)
 ])
-def test_deconv3x3_fp32_vs_oracle(engine, B, H, W, cin, cout, relu):
+def test_deconv3x3_fp32_vs_oracle(engine, fp32_kernels, B, H, W, cin, cout, relu):
     rng = np.random.default_rng(B * 1000 + H + cin + cout + 1)
     x = np.maximum(rng.normal(0, 1, (B, H, W, cout)), 0).astype(np.float32)
     lim = np.sqrt(6.0 / (9 * cin + 9 * cout))
@@ -92,6 +116,26 @@ def test_deconv3x3_fp32_vs_oracle(engine, B, H, W, cin, cout, relu):
     assert rel_l2(out, ref) < FP32_TOL
     if relu:
         assert out.min() >= 0
+
+
+def test_exact_kernels_against_float64(engine):
+    """The split-operand tensor-core conv against a float64 convolution of the same fp32 operands: the error of the
+    kernel itself (six of nine cross products, fp32 register accumulation), without the oracle's own fp32 rounding."""
+    import torch
+    import torch.nn.functional as F
+    rng = np.random.default_rng(123)
+    x = rng.normal(0, 1, (2, 28, 28, 256)).astype(np.float32)
+    lim = np.sqrt(6.0 / (9 * 256 + 9 * 256))
+    Wt = rng.uniform(-lim, lim, (3, 3, 256, 256)).astype(np.float32)
+    ref64 = F.conv2d(torch.from_numpy(x).double().permute(0, 3, 1, 2), torch.from_numpy(Wt).double().permute(3, 2, 0, 1),
+                     padding=1).permute(0, 2, 3, 1).numpy()
+    engine.set_forward_mode(True)
+    out = engine.conv3x3(x, Wt, None, relu=False)
+    assert rel_l2(out, ref64) < 2e-6
+    engine.set_forward_mode(False)
+    ffma = engine.conv3x3(x, Wt, None, relu=False)
+    engine.set_forward_mode(True)
+    assert rel_l2(ffma, ref64) < 2e-6
 
 
 def test_channel_sums_and_top_filters(engine):
