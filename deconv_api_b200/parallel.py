@@ -74,10 +74,141 @@ def broadcast_model_weights(model, dist, src=0, device=None, include_dense=False
     return flat.size * 4
 
 
-def gather_outputs(local, dist, dst=0):
-    """Optional per-request gather of each rank's projections (numpy, first axis = units) to `dst`."""
-    objs = [None] * dist.get_world_size() if dist.get_rank() == dst else None
-    dist.gather_object(local, objs, dst=dst)
-    if dist.get_rank() != dst:
+def gather_outputs(local, dist, dst=0, device=None):
+    """Per-request gather of each rank's results (numpy array, first axis = units, any length per rank) to `dst`:
+    two tensor collectives (the lengths, then the zero-padded payload) — no pickling, so it works for gigabytes and
+    for NCCL (`device` = the rank's CUDA device) as well as gloo.  Returns the concatenation on `dst`, None elsewhere."""
+    import torch
+    local = np.ascontiguousarray(local)
+    world, rank = dist.get_world_size(), dist.get_rank()
+    tail = tuple(local.shape[1:])
+    row = int(np.prod(tail)) if tail else 1
+    nbytes = local.dtype.itemsize * row
+    n = torch.tensor([local.shape[0]], dtype=torch.int64)
+    if device is not None:
+        n = n.to(device)
+    counts = [torch.zeros_like(n) for _ in range(world)]
+    dist.all_gather(counts, n)
+    counts = [int(c.item()) for c in counts]
+    cap = max(max(counts), 1)
+    pad = torch.zeros((cap * nbytes,), dtype=torch.uint8)
+    pad[:local.shape[0] * nbytes] = torch.from_numpy(local.reshape(-1).view(np.uint8))
+    if device is not None:
+        pad = pad.to(device)
+    bufs = [torch.empty_like(pad) for _ in range(world)] if rank == dst else None
+    dist.gather(pad, bufs, dst=dst)
+    if rank != dst:
         return None
-    return np.concatenate([o for o in objs if o is not None and len(o)], axis=0)
+    parts = [b.cpu().numpy()[:c * nbytes].view(local.dtype).reshape((c,) + tail) for b, c in zip(bufs, counts) if c]
+    return np.concatenate(parts, axis=0) if parts else np.zeros((0,) + tail, local.dtype)
+
+
+# ------------------------------------------------------------------------------------------------------------
+# Sharded drivers (BASELINE.json configs[3] and [4]).  The unit of work is one (image, layer, feature map) backward
+# pass of visualize_all_layers (reference app/deepdream.py:441-474), resp. one image of a DeepDream batch.
+class _NoDist(object):
+    """Stand-in for torch.distributed in a single process."""
+
+    @staticmethod
+    def get_rank():
+        return 0
+
+    @staticmethod
+    def get_world_size():
+        return 1
+
+
+def _engine_runner(model, layer_name, precision, out_format, visualize_mode, device):
+    """runner(images (B,H,W,3) f32, feats) -> (n_feat, B, H, W, 3): one forward tape, one batched projection."""
+    eng = model.bound_engine(device, upto=layer_name)
+    li = eng.index[layer_name]
+
+    def run(images, feats, out=None):
+        eng.forward(images, li)
+        return eng.project(li, feats, mode=visualize_mode, precision=precision, out=out, out_format=out_format)
+    return run
+
+
+def visualize_batch(model, images, layer_name, features=None, dist=None, precision="bf16", out_format="u8",
+                    visualize_mode="all", images_per_tape=8, gather=False, device=None, runner=None, sink=None,
+                    torch_device=None):
+    """Project feature maps `features` (default: every map) of `layer_name` for every image of `images`
+    ((N,H,W,3) float32, preprocessed; every rank passes the same array), sharded over the ranks of `dist`
+    (torch.distributed, or None for one process) by `shard_work`: by image when N >= world, otherwise every rank
+    replicates the cheap forward and takes a contiguous slice of `features`.  No collective touches the data path.
+
+    Returns a list of blocks ``(image_indices, feature_indices, array)`` with array of shape
+    (len(feature_indices), len(image_indices), H, W, 3) in `out_format` ('u8' = every projection de-processed on the
+    GPU, 'bf16' bit patterns, or 'f32') — this rank's share, left where it is.  `gather=True` additionally collects
+    every rank's blocks on rank 0 (tensor collectives) and returns there ONE array (N, n_features, H, W, 3), None on
+    the other ranks.  `sink(image_indices, feature_indices, array)`, when given, consumes each block as soon as it is
+    complete and the block list is not kept (the array may be reused for the next block)."""
+    from . import deepdream as _dd
+    m = _dd.adopt(model)
+    d = dist if dist is not None else _NoDist
+    world, rank = d.get_world_size(), d.get_rank()
+    images = np.asarray(images, np.float32)
+    assert images.ndim == 4, "images must be (N,H,W,3)"
+    N = images.shape[0]
+    if features is None:
+        features = np.arange(m.get_layer(layer_name).output_shape[-1], dtype=np.int32)
+    features = np.ascontiguousarray(features, np.int32)
+    units = shard_work(N, int(features.size), world, rank)
+    run = runner if runner is not None else _engine_runner(m, layer_name, precision, out_format, visualize_mode, device)
+    blocks = []
+    if units:
+        flo, fhi = units[0][1], units[0][2]
+        feats = features[flo:fhi]
+        mine = [i for i, _, _ in units]
+        reuse = None
+        for k in range(0, len(mine), images_per_tape):
+            idx = mine[k:k + images_per_tape]
+            batch = np.ascontiguousarray(images[idx])
+            if sink is not None and reuse is not None and reuse.shape[1] == len(idx):
+                arr = run(batch, feats, reuse)
+            else:
+                arr = run(batch, feats)
+            if sink is not None:
+                sink(idx, feats, arr)
+                reuse = arr
+            else:
+                blocks.append((idx, feats, arr))
+    if not gather:
+        return blocks
+    # rows = (image, feature) pairs in this rank's order, plus their coordinates
+    rows, coords = [], []
+    for idx, feats, arr in blocks:
+        a = np.moveaxis(arr, 0, 1)                       # (images, features, H, W, 3)
+        rows.append(a.reshape((-1,) + a.shape[2:]))
+        coords += [(i, int(f)) for i in idx for f in feats]
+    tail = images.shape[1:]
+    dtype = {"u8": np.uint8, "bf16": np.uint16, "f32": np.float32}[out_format]
+    local = np.concatenate(rows, axis=0) if rows else np.zeros((0,) + tail, dtype)
+    cl = np.asarray(coords, np.int64).reshape(-1, 2)
+    data = gather_outputs(local, d, 0, torch_device) if world > 1 else local
+    coord = gather_outputs(cl, d, 0, torch_device) if world > 1 else cl
+    if rank != 0:
+        return None
+    out = np.zeros((N, int(features.size)) + tail, dtype)
+    pos = {int(f): j for j, f in enumerate(features)}
+    for r, (i, f) in enumerate(coord):
+        out[int(i), pos[int(f)]] = data[r]
+    return out
+
+
+def dream_batch(model, images, dist=None, gather=False, device=None, runner=None, torch_device=None, **dream_kwargs):
+    """DeepDream on a batch of images ((N,H,W,3) float32), the batch sharded over the ranks (config 5: one or more
+    2048x2048 images per GPU).  A single image is never split across GPUs (it would need halo exchange): replicas
+    only.  Returns [(image_index, dreamed image)] for this rank, or with gather=True the (N,H,W,3) array on rank 0."""
+    from . import dream as _dm
+    d = dist if dist is not None else _NoDist
+    world, rank = d.get_world_size(), d.get_rank()
+    images = np.asarray(images, np.float32)
+    lo, hi = partition(images.shape[0], world, rank)
+    run = runner if runner is not None else (lambda img: _dm.dream(model, img, device=device, **dream_kwargs))
+    local = [(i, np.asarray(run(images[i]), np.float32)) for i in range(lo, hi)]
+    if not gather:
+        return local
+    arr = np.stack([a for _, a in local]) if local else np.zeros((0,) + images.shape[1:], np.float32)
+    data = gather_outputs(arr, d, 0, torch_device) if world > 1 else arr      # partition() is contiguous and ordered by rank
+    return data if rank == 0 else None

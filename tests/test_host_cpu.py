@@ -104,6 +104,36 @@ local = np.array([[i, lo, hi] for i, lo, hi in units], np.int64)
 allu = parallel.gather_outputs(local, dist, dst=0)
 if rank == 0:
     assert sorted(allu[:, 0].tolist()) == list(range(6))
+# the sharded driver with a stub in place of the GPU engine: result[feature, image] encodes (image id, feature id).
+# 5 images on 2 ranks -> image split (3 + 2, tapes of 2 images); 1 image on 2 ranks -> feature split, forward replicated
+def runner(images, feats, out=None):
+    n, B = len(feats), images.shape[0]
+    r = np.zeros((n, B) + images.shape[1:], np.float32)
+    for k, f in enumerate(feats):
+        for b in range(B):
+            r[k, b] = images[b] * 1000 + f
+    return r
+for N in (5, 1):
+    imgs = np.arange(N, dtype=np.float32).reshape(N, 1, 1, 1) * np.ones((N, 2, 2, 3), np.float32)
+    feats = [7, 3, 11, 2, 5]
+    blocks = parallel.visualize_batch(m, imgs, "block1_conv1", features=feats, dist=dist, out_format="f32", images_per_tape=2, runner=runner)
+    mine = sorted(i for idx, _, _ in blocks for i in idx)
+    want_units = parallel.shard_work(N, len(feats), world, rank)
+    assert mine == sorted(i for i, _, _ in want_units)
+    for idx, fs, arr in blocks:
+        assert arr.shape == (len(fs), len(idx), 2, 2, 3)
+        assert list(fs) == feats[want_units[0][1]:want_units[0][2]]
+    full = parallel.visualize_batch(m, imgs, "block1_conv1", features=feats, dist=dist, out_format="f32", images_per_tape=2, runner=runner, gather=True)
+    if rank == 0:
+        assert full.shape == (N, len(feats), 2, 2, 3)
+        for i in range(N):
+            for j, f in enumerate(feats):
+                assert np.all(full[i, j] == i * 1000 + f), (N, i, f)
+    else:
+        assert full is None
+dreams = parallel.dream_batch(m, np.arange(3, dtype=np.float32).reshape(3, 1, 1, 1) * np.ones((3, 2, 2, 3), np.float32), dist=dist, gather=True, runner=lambda img: img + 0.5)
+if rank == 0:
+    assert dreams.shape == (3, 2, 2, 3) and np.all(dreams[2] == 2.5)
     print("OK", nbytes)
 dist.barrier()
 dist.destroy_process_group()
