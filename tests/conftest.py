@@ -47,13 +47,20 @@ def engine():
     return E.default_engine(0)
 
 
-def following_tape(eng, ref_model, layer, img, b=0, max_flips=4, gap=1e-5):
+def following_tape(eng, ref_model, layer, img, b=0, max_flips=4, gap=1e-5, follow_top=False):
     """oracle.restatement.FastTape of image `img` (1,H,W,3) whose pooling indices FOLLOW the switches of image `b` in
     the engine's current tape.  Two correct fp32 convolutions with different summation orders (ours, torch's, the
-    reference's Eigen kernels) may rank the two largest values of a pooling window differently when they differ by a
-    few ulp; every switch that differs from the oracle's own is therefore required to be such a near-tie (relative gap
-    <= `gap`, at most `max_flips` of them), and the oracle then takes the library's choice, so that the projection
-    chain itself can be held to the 1e-5 / 2e-2 tolerances.  Returns (tape, number of near-tie flips)."""
+    reference's Eigen kernels) agree to ~1e-6 of the LAYER's scale, not of each element, so they may rank the two
+    largest values of a pooling window differently when those are that close.  Every switch that differs from the
+    oracle's own is therefore required to be such a near-tie (|difference| <= `gap` x the largest activation of the
+    conv layer below, at most `max_flips` of them), and the oracle then takes the library's choice, so that the
+    projection chain itself can be held to the 1e-5 / 2e-2 tolerances.
+    follow_top: also seed the oracle's projections with the LIBRARY's activations of `layer` (after checking that
+    they agree with the oracle's to rel-L2 <= 1e-5): a feature map that is almost dead inherits the forward pass's
+    absolute error as a large RELATIVE error of its one or two seed values (measured: map 312 of block4_conv3 has a
+    single non-zero activation of 6.8e-3 in a layer whose maximum is 2.2; ours and torch's differ by 2e-4 there, and
+    the whole projection is proportional to it), which says nothing about the backward chain under test.
+    Returns (tape, number of near-tie flips)."""
     import torch
     from oracle import restatement as rs
     tape = rs.FastTape(ref_model, layer, img)
@@ -69,13 +76,19 @@ def following_tape(eng, ref_model, layer, img, b=0, max_flips=4, gap=1e-5):
         bad = np.argwhere(sw != sw_ref)
         if len(bad):
             act = eng.activation(eng.index[name] - 1)[b]
+            scale = float(np.abs(act).max())
             for (y, x, c) in bad:
                 win = act[2 * y:2 * y + 2, 2 * x:2 * x + 2, c].ravel()
-                assert abs(win[sw[y, x, c]] - win[sw_ref[y, x, c]]) <= gap * np.abs(win).max(), (name, y, x, c, win)
+                assert abs(win[sw[y, x, c]] - win[sw_ref[y, x, c]]) <= gap * scale, (name, y, x, c, win, scale)
                 flips += 1
             h, w, C = sw.shape
             yy, xx = np.meshgrid(np.arange(h), np.arange(w), indexing="ij")
             follow = ((2 * yy[..., None] + sw // 2) * W + 2 * xx[..., None] + sw % 2).transpose(2, 0, 1)[None]
             tape.ops[op_i] = ("pool", torch.from_numpy(np.ascontiguousarray(follow)), (H, W))
     assert flips <= max_flips, "%d switch flips" % flips
+    if follow_top:
+        ours = eng.activation(eng.index[layer])[b:b + 1]
+        theirs = tape.top.permute(0, 2, 3, 1).numpy()
+        assert rel_l2(ours, theirs) < 1e-5
+        tape.top = torch.from_numpy(np.ascontiguousarray(ours)).permute(0, 3, 1, 2).contiguous()
     return tape, flips
