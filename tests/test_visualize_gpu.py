@@ -23,10 +23,11 @@ def test_mini_model_all_targets_vs_reference_golden(golden):
             for name, lst in res.items():
                 ref = g["%s|%s|%s" % (mode, tgt, name)]
                 assert len(lst) == len(ref), (mode, tgt, name)
-                # chains that start above the Flatten run through un-rectified x W^T products whose terms
-                # cancel: two fp32 implementations legitimately differ by a few 1e-5 there (the golden is
-                # itself torch-CPU fp32 arithmetic); conv/pool targets keep north_star's 1e-5
-                tol = 1e-4 if name in ("predictions", "fc1", "flatten") else FP32_TOL
+                # `predictions` projects ALL ten softmax outputs (top-8 of 10): the weakest classes have
+                # probabilities ~1e-6 whose expf differs by 8e-6 relative between two fp32 implementations, and
+                # a projection is proportional to its seed (measured 2.7e-5, profiles/diag_mini.py; fc1 / flatten
+                # and every conv / pool target: < 1e-6).  Everything else keeps north_star's 1e-5.
+                tol = 1e-4 if name == "predictions" else FP32_TOL
                 for a, b in zip(lst, ref):
                     assert a.shape == b.shape and a.dtype == np.float32
                     assert rel_l2(a, b) < tol, (mode, tgt, name)
