@@ -27,6 +27,8 @@ SIGNATURES = {
     "dcv_sync": (_c.c_int, [_c.c_void_p]),
     "dcv_launch_count": (_c.c_longlong, [_c.c_void_p]),
     "dcv_stream": (_c.c_void_p, [_c.c_void_p]),
+    "dcv_host_alloc": (_c.c_int, [_c.c_void_p, _c.c_size_t, _c.POINTER(_c.c_void_p)]),
+    "dcv_host_free": (_c.c_int, [_c.c_void_p, _c.c_void_p]),
     "dcv_profile": (_c.c_int, [_c.c_void_p, _c.c_int]),
     "dcv_profile_read": (_c.c_int, [_c.c_void_p, _c.c_int, P_F64, _c.POINTER(_c.c_longlong), P_F64, P_F64]),
     "dcv_profile_launch": (_c.c_int, [_c.c_void_p, _c.c_int, P_I32, P_F64, P_F64, P_F64]),

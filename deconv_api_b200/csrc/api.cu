@@ -155,6 +155,23 @@ extern "C" int dcv_sync(dcv_ctx* ctx) {
   return 0;
 }
 
+// ---- page-locked host memory for result buffers (device-to-host copies into pageable memory are staged by the driver
+// at a fraction of the PCIe rate) ---------------------------------------------------------------------
+extern "C" int dcv_host_alloc(dcv_ctx* ctx, size_t bytes, void** out) {
+  ENTER(ctx);
+  if (!out) return ctx->fail(DCV_ERR_ARG, "dcv_host_alloc: null output");
+  *out = nullptr;
+  cudaError_t e = cudaHostAlloc(out, bytes ? bytes : 1, cudaHostAllocDefault);
+  if (e != cudaSuccess) { *out = nullptr; return ctx->fail(DCV_ERR_NOMEM, "cudaHostAlloc(%zu bytes): %s", bytes, cudaGetErrorString(e)); }
+  return 0;
+}
+
+extern "C" int dcv_host_free(dcv_ctx* ctx, void* p) {
+  ENTER(ctx);
+  if (p) CU(ctx, cudaFreeHost(p));
+  return 0;
+}
+
 // ---- per-class kernel timing -------------------------------------------------------------------------
 void dcv_ctx::prof_begin(int cat, double flops, double bytes) {
   ProfRec r;

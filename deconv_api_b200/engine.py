@@ -59,6 +59,9 @@ class Engine(object):
     # -- life cycle
     def close(self):
         if getattr(self, "ctx", None):
+            for addr in list(getattr(self, "_pinned", ())):
+                self._pinned.discard(addr)
+                self.lib.dcv_host_free(self.ctx, ctypes.c_void_p(addr))
             self.lib.dcv_destroy(self.ctx)
             self.ctx = None
 
@@ -81,6 +84,28 @@ class Engine(object):
     @property
     def stream(self):
         return self.lib.dcv_stream(self.ctx)
+
+    # -- page-locked host buffers
+    def pinned_empty(self, shape, dtype):
+        """numpy array in page-locked host memory (full-rate, overlappable device-to-host copies).  The memory is
+        released when the array (and every view of it) has been garbage-collected, or at close()."""
+        import weakref
+        dtype = np.dtype(dtype)
+        nbytes = int(np.prod(shape)) * dtype.itemsize
+        p = ctypes.c_void_p()
+        self._ck(self.lib.dcv_host_alloc(self.ctx, nbytes, ctypes.byref(p)))
+        buf = (ctypes.c_uint8 * max(nbytes, 1)).from_address(p.value)
+        arr = np.frombuffer(buf, dtype=np.uint8, count=nbytes).view(dtype).reshape(shape)
+        lib, ctx, addr = self.lib, self.ctx, p.value
+        live = self._pinned = getattr(self, "_pinned", set())
+        live.add(addr)
+
+        def release(_lib=lib, _ctx=ctx, _addr=addr, _live=live):
+            if _addr in _live:
+                _live.discard(_addr)
+                _lib.dcv_host_free(_ctx, ctypes.c_void_p(_addr))
+        weakref.finalize(buf, release)
+        return arr
 
     # -- per-kernel-class timing
     KERNEL_CLASSES = ("conv_fp32", "conv_tc", "pool", "unpool", "rank1", "other", "conv_fwd")

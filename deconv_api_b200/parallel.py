@@ -120,12 +120,17 @@ class _NoDist(object):
 
 def _engine_runner(model, layer_name, precision, out_format, visualize_mode, device):
     """runner(images (B,H,W,3) f32, feats) -> (n_feat, B, H, W, 3): one forward tape, one batched projection."""
+    from . import engine as _engine
     eng = model.bound_engine(device, upto=layer_name)
     li = eng.index[layer_name]
+    dtype = _engine.OUT_FORMATS[out_format][1]
 
-    def run(images, feats, out=None):
+    def run(images, feats, out=None, pinned=False):
         eng.forward(images, li)
+        if out is None and pinned:          # a buffer the caller will reuse: page-locked, so the copies run at PCIe rate
+            out = eng.pinned_empty((len(feats),) + tuple(images.shape), dtype)
         return eng.project(li, feats, mode=visualize_mode, precision=precision, out=out, out_format=out_format)
+    run.supports_pinned = True
     return run
 
 
@@ -142,7 +147,8 @@ def visualize_batch(model, images, layer_name, features=None, dist=None, precisi
     GPU, 'bf16' bit patterns, or 'f32') — this rank's share, left where it is.  `gather=True` additionally collects
     every rank's blocks on rank 0 (tensor collectives) and returns there ONE array (N, n_features, H, W, 3), None on
     the other ranks.  `sink(image_indices, feature_indices, array)`, when given, consumes each block as soon as it is
-    complete and the block list is not kept (the array may be reused for the next block)."""
+    complete and the block list is not kept: the array is ONE page-locked buffer reused for every block (full-rate
+    device-to-host copies), valid only inside the call."""
     from . import deepdream as _dd
     m = _dd.adopt(model)
     d = dist if dist is not None else _NoDist
@@ -166,6 +172,8 @@ def visualize_batch(model, images, layer_name, features=None, dist=None, precisi
             batch = np.ascontiguousarray(images[idx])
             if sink is not None and reuse is not None and reuse.shape[1] == len(idx):
                 arr = run(batch, feats, reuse)
+            elif sink is not None and getattr(run, "supports_pinned", False):
+                arr = run(batch, feats, None, True)
             else:
                 arr = run(batch, feats)
             if sink is not None:

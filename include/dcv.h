@@ -73,6 +73,12 @@ DCV_API long long dcv_launch_count(const dcv_ctx* ctx);
 /* The context's cudaStream_t, as an opaque pointer (for event timing by the caller). */
 DCV_API void* dcv_stream(const dcv_ctx* ctx);
 
+/* Page-locked host memory for result buffers (no counterpart in the reference): a device-to-host copy into ordinary
+ * pageable memory is staged by the driver at a fraction of the PCIe rate, into these buffers it runs at full rate and
+ * overlaps the kernels.  Free with dcv_host_free before dcv_destroy. */
+DCV_API int dcv_host_alloc(dcv_ctx* ctx, size_t bytes, void** out);
+DCV_API int dcv_host_free(dcv_ctx* ctx, void* p);
+
 /* Kernel classes for dcv_profile_read. */
 enum dcv_kernel_class {
   DCV_K_CONV_FP32 = 0,  /* FFMA 3x3 conv / backward conv */
