@@ -62,6 +62,8 @@ SIGNATURES = {
                                _c.c_int, _c.c_int, _c.c_int, _c.c_void_p]),
     "dcv_deconv3x3": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_void_p, _c.c_int, _c.c_int, _c.c_int, _c.c_int,
                                  _c.c_int, _c.c_int, _c.c_int, _c.c_void_p]),
+    "dcv_deconv_tail": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_void_p, _c.c_int, _c.c_int, _c.c_int, _c.c_void_p, _c.c_int, _c.c_int,
+                                   _c.c_int, _c.c_void_p, _c.c_int, _c.c_int, _c.c_void_p]),
     "dcv_activation": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_int, _c.c_int, _c.c_int, _c.c_void_p]),
     "dcv_dense": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_void_p, _c.c_void_p, _c.c_int, _c.c_int, _c.c_int,
                              _c.c_int, _c.c_void_p]),

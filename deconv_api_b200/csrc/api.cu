@@ -583,6 +583,34 @@ static int project_chunk(dcv_ctx* ctx, int layer, int foff, int n, int vis_mode,
         launch_unpool_map(maps, (const uint8_t*)l.sw.p, B, h, w, C, feat, n, maps2, ctx->stream); ctx->launches++;
         std::swap(maps, maps2);
       } else if (rep_bf16) {
+        // 64-channel tail (block1 of VGG16): unpool -> 64 -> 64 conv [-> last conv] as ONE kernel (tc_strip.cuh); the
+        // unpooled tensor and the conv's 64-channel output never touch HBM.  DCV_TC_TAIL: bit 0 = fuse the unpool, bit 1 =
+        // fuse the last conv (default 3).
+        static const int tail = getenv("DCV_TC_TAIL") ? atoi(getenv("DCV_TC_TAIL")) : 3;
+        const bool big = (long long)P * (l.in_H + 1) * (l.in_W + 1) / 120 >= ctx->num_sms;
+        if ((tail & 1) && big && j >= 1 && tc_strip_conv_ok(ctx->net[j - 1]) && ctx->net[j - 1].cout == 64 && C == 64 &&
+            (nonneg || !ctx->net[j - 1].relu)) {
+          const Layer& c2 = ctx->net[j - 1];
+          const Layer* c1 = ((tail & 2) && j >= 2 && j - 2 == lowest_conv && tc_strip_last_ok(c2, ctx->net[j - 2])) ? &ctx->net[j - 2] : nullptr;
+          if (c1) {
+            if (j - 2 == 0 && final_dst) bufs[cur ^ 1] = final_dst;
+            TRY(tc_strip(ctx, c2, c1, hb[hcur], (const uint8_t*)l.sw.p, B, P, l.in_H, l.in_W, nullptr, bufs[cur ^ 1], -1));
+            cur ^= 1;
+            rep_bf16 = false;
+            nonneg = c1->relu != 0;
+            C = c1->cin;
+            j -= 2;
+          } else {
+            TRY(tc_strip(ctx, c2, nullptr, hb[hcur], (const uint8_t*)l.sw.p, B, P, l.in_H, l.in_W, hb[hcur ^ 1], nullptr, -1));
+            hcur ^= 1;
+            nonneg = c2.relu != 0;
+            C = c2.cin;
+            j -= 1;
+          }
+          h = l.in_H; w = l.in_W;
+          mode = M_TENSOR;
+          continue;
+        }
         TRY(tc_unpool(ctx, hb[hcur], (const uint8_t*)l.sw.p, P, B, h, w, l.in_H, l.in_W, C, hb[hcur ^ 1]));
         hcur ^= 1;
       } else {
@@ -637,6 +665,20 @@ static int project_chunk(dcv_ctx* ctx, int layer, int foff, int n, int vis_mode,
               C = l.cin;
               hcur ^= 1;
               --j;                      // the pool layer is done
+              continue;
+            }
+            static const int tail2 = getenv("DCV_TC_TAIL") ? atoi(getenv("DCV_TC_TAIL")) : 3;
+            if ((tail2 & 2) && j - 1 == lowest_conv && tc_strip_conv_ok(l) && tc_strip_last_ok(l, ctx->net[j - 1]) &&
+                (long long)P * (h + 1) * (w + 1) / 120 >= ctx->num_sms) {
+              // 64 -> 64 conv with the last conv fused behind it (no pool in between, or unpool fusion switched off)
+              const Layer& c1 = ctx->net[j - 1];
+              if (j - 1 == 0 && final_dst) bufs[cur ^ 1] = final_dst;
+              TRY(tc_strip(ctx, l, &c1, hb[hcur], nullptr, B, P, h, w, nullptr, bufs[cur ^ 1], -1));
+              cur ^= 1;
+              rep_bf16 = false;
+              nonneg = c1.relu != 0;
+              C = c1.cin;
+              --j;
               continue;
             }
             TRY(tc_conv(ctx, l, hb[hcur], P, h, w, hb[hcur ^ 1], nullptr, -1));
@@ -1055,6 +1097,72 @@ extern "C" int dcv_deconv3x3(dcv_ctx* ctx, const float* x, const float* w_hwio, 
   CHECK_LAUNCH(ctx);
   CU(ctx, cudaMemcpyAsync(out, base + o3, nout * 4, cudaMemcpyDeviceToHost, ctx->stream));
   CU(ctx, cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+// Fused tail of the bf16 projection chain as one operator (unit parity of tc_strip.cuh): [DPooling.down] ->
+// DConvolution2D.down of a 64 -> 64 conv -> [DConvolution2D.down of the conv below it].
+extern "C" int dcv_deconv_tail(dcv_ctx* ctx, const float* x, const uint8_t* sw, int B, int H, int W, const float* w2_hwio, int cmid,
+                               int c2, int relu2, const float* w1_hwio, int c0, int relu1, float* out) {
+  ENTER(ctx);
+  if (!x || !w2_hwio || !out || B <= 0 || H <= 0 || W <= 0 || cmid <= 0 || c2 <= 0 || (w1_hwio && c0 <= 0))
+    return ctx->fail(DCV_ERR_ARG, "dcv_deconv_tail: bad arguments");
+  if (sw && ((H & 1) || (W & 1))) return ctx->fail(DCV_ERR_ARG, "dcv_deconv_tail: unpool needs an even output size, got %dx%d", H, W);
+  const int ih = sw ? H / 2 : H, iw = sw ? W / 2 : W;
+  const size_t nin = (size_t)B * ih * iw * c2, nsw = sw ? nin : 0;
+  const size_t nw2 = (size_t)9 * cmid * c2, nw1 = w1_hwio ? (size_t)9 * c0 * cmid : 0;
+  const int cl = w1_hwio ? c0 : cmid;
+  const size_t nout = (size_t)B * H * W * cl;
+  const size_t o_sw = align256(nin * 4), o_w2 = o_sw + align256(nsw), o_w2d = o_w2 + align256(nw2 * 4), o_w1 = o_w2d + align256(nw2 * 4);
+  const size_t o_w1d = o_w1 + align256(nw1 * 4), o_out = o_w1d + align256(nw1 * 4);
+  const size_t o_mid = o_out + align256(nout * 4);
+  const size_t pad_in = (size_t)B * tc_padded_elems(ih, iw, c2) * 2, pad_out = (size_t)B * tc_padded_elems(H, W, cmid) * 2;
+  TRY(ctx->stage.ensure(ctx, o_mid + align256(pad_in) + align256(pad_out)));
+  char* base = (char*)ctx->stage.p;
+  CU(ctx, cudaMemcpyAsync(base, x, nin * 4, cudaMemcpyHostToDevice, ctx->stream));
+  if (sw) CU(ctx, cudaMemcpyAsync(base + o_sw, sw, nsw, cudaMemcpyHostToDevice, ctx->stream));
+  CU(ctx, cudaMemcpyAsync(base + o_w2, w2_hwio, nw2 * 4, cudaMemcpyHostToDevice, ctx->stream));
+  if (w1_hwio) CU(ctx, cudaMemcpyAsync(base + o_w1, w1_hwio, nw1 * 4, cudaMemcpyHostToDevice, ctx->stream));
+  Layer l2, l1;
+  l2.kind = LK_CONV; l2.cin = cmid; l2.cout = c2; l2.relu = relu2 ? 1 : 0; l2.wd = (float*)(base + o_w2d);
+  launch_flip_transpose((const float*)(base + o_w2), cmid, c2, l2.wd, ctx->stream); ctx->launches++;
+  int r = tc_prepare_layer(ctx, l2);
+  if (!r && w1_hwio) {
+    l1.kind = LK_CONV; l1.cin = c0; l1.cout = cmid; l1.relu = relu1 ? 1 : 0; l1.wd = (float*)(base + o_w1d);
+    launch_flip_transpose((const float*)(base + o_w1), c0, cmid, l1.wd, ctx->stream); ctx->launches++;
+    r = tc_prepare_layer(ctx, l1);
+  }
+  __nv_bfloat16* pin = (__nv_bfloat16*)(base + o_mid);
+  __nv_bfloat16* pmid = (__nv_bfloat16*)(base + o_mid + align256(pad_in));
+  if (!r) r = tc_pad_convert(ctx, (const float*)base, B, ih, iw, c2, pin);
+  if (!r && !(tc_strip_conv_ok(l2) && (!w1_hwio || tc_strip_last_ok(l2, l1))))
+    r = ctx->fail(DCV_ERR_UNSUPPORTED, "dcv_deconv_tail: the fused tail needs a 64 -> 64 conv (and <= 3 channels below it)");
+  if (!r) r = tc_strip(ctx, l2, w1_hwio ? &l1 : nullptr, pin, sw ? (const uint8_t*)(base + o_sw) : nullptr, B, B, H, W,
+                       w1_hwio ? nullptr : pmid, w1_hwio ? (float*)(base + o_out) : nullptr, -1);
+  if (!r && !w1_hwio) {
+    // padded-flat bf16 -> compact fp32 on the host side of the test operator: copy the padded tensor back as it is
+    r = 0;
+  }
+  if (!r && cudaStreamSynchronize(ctx->stream) != cudaSuccess) r = ctx->fail(DCV_ERR_CUDA, "dcv_deconv_tail: kernel failed: %s", cudaGetErrorString(cudaGetLastError()));
+  tc_free_layer(l2);
+  if (w1_hwio) tc_free_layer(l1);
+  if (r) return r;
+  if (w1_hwio) {
+    CU(ctx, cudaMemcpyAsync(out, base + o_out, nout * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+  } else {
+    // un-pad on the host: rows (b, y, x) of the padded-flat bf16 tensor, 64 channels each
+    std::vector<uint16_t> tmp((size_t)B * (H + 1) * (W + 1) * 64);
+    CU(ctx, cudaMemcpyAsync(tmp.data(), pmid, tmp.size() * 2, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    for (int b = 0; b < B; ++b)
+      for (int y = 0; y < H; ++y)
+        for (int xx = 0; xx < W; ++xx) {
+          const uint16_t* src = tmp.data() + (((size_t)b * (H + 1) + y) * (W + 1) + xx) * 64;
+          float* dst = out + (((size_t)b * H + y) * W + xx) * cmid;
+          for (int c = 0; c < cmid; ++c) { uint32_t u = (uint32_t)src[c] << 16; memcpy(dst + c, &u, 4); }
+        }
+  }
   return 0;
 }
 

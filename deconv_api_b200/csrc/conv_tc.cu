@@ -22,6 +22,7 @@
 #include "tc_last.cuh"
 #include "tc_kernel2.cuh"
 #include "tc_dxg.cuh"
+#include "tc_strip.cuh"
 #include "tc_exact.cuh"
 
 #include <algorithm>
@@ -1011,6 +1012,14 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
     }
   }
   if (use_dxg && l.ntaps == 9 && l.nprod == 1 && !l.up && out_bf16 && l.n_pad == 64 && (p.rows + DXG_ROWS_OUT - 1) / DXG_ROWS_OUT >= ctx->num_sms) {
+    // K = 64 without epilogue extras: the strip form of the same GEMM (one A tile per tile instead of three)
+    static const int use_strip = getenv("DCV_TC_STRIP") ? atoi(getenv("DCV_TC_STRIP")) : 1;
+    if (use_strip && l.k_pad == 64 && !l.bias && !l.prep) {
+      Layer tmp;
+      tmp.kind = LK_CONV; tmp.cin = l.n_real; tmp.cout = l.k_real; tmp.relu = l.relu;
+      tmp.tc.wd_bf16 = const_cast<__nv_bfloat16*>(l.w); tmp.tc.k_pad = 64; tmp.tc.n_pad = 64;
+      return tc_strip(ctx, tmp, nullptr, in, nullptr, 0, P, h, w, out_bf16, nullptr, l.relu);
+    }
     // 64 output channels: dx-grouped GEMM (tc_dxg.cuh), tiles of 126 rows
     TcParams q = p;
     q.m_tiles = (p.rows + DXG_ROWS_OUT - 1) / DXG_ROWS_OUT;
@@ -1126,6 +1135,75 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
     default: return launch_tc<256, MODE_TAP>(ctx, ta, tb, p);
   }
 #undef TC_DISPATCH
+}
+
+// ---- strip kernel (tc_strip.cuh): 64 -> 64 backward conv, optionally with the unpool in front of it and the last
+// (64 -> <= 3) conv behind it fused in -----------------------------------------------------------------------------
+bool tc_strip_conv_ok(const Layer& l) {
+  return l.kind == LK_CONV && l.tc.wd_bf16 && l.tc.k_pad == 64 && l.tc.n_pad == 64;
+}
+bool tc_strip_last_ok(const Layer& conv, const Layer& last) {
+  return last.kind == LK_CONV && last.tc.wall_bf16 && last.tc.k_pad == 64 && last.cout == conv.cin && 9 * last.cin <= 27;
+}
+
+template <bool UNPOOL, bool LAST>
+static int launch_strip(dcv_ctx* ctx, const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tbl, const CUtensorMap& to,
+                        const StripParams& p) {
+  const int smem = strip_smem_bytes(LAST);
+  static int smem_set[64] = {};
+  cudaError_t e = cudaSuccess;
+  if (smem_set[ctx->device & 63] < smem) {
+    e = cudaFuncSetAttribute(deconv_strip_kernel<UNPOOL, LAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "cudaFuncSetAttribute(strip kernel, %d bytes): %s", smem, cudaGetErrorString(e));
+    smem_set[ctx->device & 63] = smem;
+  }
+  const int grid = std::min(p.total_strips, ctx->num_sms);
+  e = launch_k(ctx, deconv_strip_kernel<UNPOOL, LAST>, dim3(grid), dim3(strip_threads(UNPOOL)), (size_t)smem, ta, tb, tbl, to, p);
+  if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "launch(deconv_strip_kernel<%d,%d>): %s", (int)UNPOOL, (int)LAST, cudaGetErrorString(e));
+  ctx->launches++;
+  e = cudaGetLastError();
+  if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "deconv_strip_kernel<%d,%d> launch: %s", (int)UNPOOL, (int)LAST, cudaGetErrorString(e));
+  return 0;
+}
+
+// in: padded-flat bf16 at (h, w) — or, with sw != null, at the POOLED size (h/2, w/2), unpooled on the fly with the
+// switches (Bsw, h/2, w/2, conv.cout).  last == null: out_bf16 = relu?(conv) padded-flat (P,(h+1),(w+1),64);
+// last != null: out_f32 = act(last(act(conv))) compact (P, h, w, last->cin).
+int tc_strip(dcv_ctx* ctx, const Layer& conv, const Layer* last, const __nv_bfloat16* in, const uint8_t* sw, int Bsw, int P, int h,
+             int w, __nv_bfloat16* out_bf16, float* out_f32, int relu) {
+  if (!tc_strip_conv_ok(conv)) return ctx->fail(DCV_ERR_UNSUPPORTED, "tc_strip: the layer is not a 64 -> 64 channel conv");
+  if (last && !tc_strip_last_ok(conv, *last)) return ctx->fail(DCV_ERR_UNSUPPORTED, "tc_strip: the last layer cannot be fused");
+  if (sw && ((h & 1) || (w & 1) || conv.cout != 64)) return ctx->fail(DCV_ERR_UNSUPPORTED, "tc_strip: fused unpool needs even sizes and 64 channels");
+  if (last ? !out_f32 : !out_bf16) return ctx->fail(DCV_ERR_ARG, "tc_strip: missing output");
+  const long long rows_ll = (long long)P * (h + 1) * (w + 1);
+  if (rows_ll > 0x7FFFFF00LL) return ctx->fail(DCV_ERR_ARG, "tc_strip: %lld padded rows exceed the TMA coordinate range", rows_ll);
+  StripParams p = {};
+  p.rows = (int)rows_ll; p.h = h; p.w = w; p.T = P * (h + 1);
+  p.n_cb = w + 1 <= STRIP_POS ? 1 : (w - (STRIP_POS - 1) + STRIP_CB - 1) / STRIP_CB + 1;
+  // strip height: tall enough that the two halo rows (four with the fused last layer) cost a few percent, short enough
+  // for several strips per SM
+  int R = 64;
+  while (R > 8 && (long long)p.n_cb * ((p.T + R - 1) / R) < 6LL * ctx->num_sms) R >>= 1;
+  static const int force_r = getenv("DCV_TC_STRIP_ROWS") ? atoi(getenv("DCV_TC_STRIP_ROWS")) : 0;
+  if (force_r > 0) R = force_r;
+  p.R = R;
+  p.total_strips = p.n_cb * ((p.T + R - 1) / R);
+  p.relu = relu < 0 ? conv.relu : relu;
+  p.pooled = sw ? in : nullptr; p.sw = sw; p.Bsw = Bsw; p.C = conv.cout; p.ph = h / 2; p.pw = w / 2;
+  p.cout3 = last ? last->cin : 0; p.relu_last = last ? last->relu : 0; p.out = out_f32;
+  CUtensorMap ta, tb, tbl, to;
+  int r = make_tmap(ctx, &tb, conv.tc.wd_bf16, (uint64_t)9 * 64, 64, STRIP_N);
+  if (r) return r;
+  ta = tb; tbl = tb; to = tb;
+  if (!sw) { r = make_tmap(ctx, &ta, in, (uint64_t)p.rows, 64, 32); if (r) return r; }
+  if (last) { r = make_tmap(ctx, &tbl, last->tc.wall_bf16, LAST_N, 64, LAST_N); if (r) return r; }
+  else { r = make_tmap(ctx, &to, out_bf16, (uint64_t)p.rows, 64, (uint32_t)std::min(STRIP_POS, w + 1)); if (r) return r; }
+  const double px = (double)P * h * w;
+  double flops = 2.0 * 9 * px * conv.cin * conv.cout, bytes = 2.0 * px * conv.cout * (sw ? 0.25 + 0.125 : 1.0);
+  if (last) { flops += 2.0 * 9 * px * last->cin * last->cout; bytes += 4.0 * px * last->cin; } else bytes += 2.0 * px * conv.cin;
+  ProfScope ps(ctx, DCV_K_CONV_TC, flops, bytes);
+  if (sw) return last ? launch_strip<true, true>(ctx, ta, tb, tbl, to, p) : launch_strip<true, false>(ctx, ta, tb, tbl, to, p);
+  return last ? launch_strip<false, true>(ctx, ta, tb, tbl, to, p) : launch_strip<false, false>(ctx, ta, tb, tbl, to, p);
 }
 
 // Stand-alone operator (dcv_deconv3x3 with DCV_BF16): fp32 compact in -> fp32 compact out.

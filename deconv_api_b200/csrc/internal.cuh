@@ -134,3 +134,9 @@ int tc_conv(dcv_ctx* ctx, const Layer& l, const __nv_bfloat16* in, int P, int h,
 // forward conv + bias + activation, bf16 padded-flat in and out
 int tc_conv_fwd(dcv_ctx* ctx, const Layer& l, const __nv_bfloat16* in, int P, int h, int w, __nv_bfloat16* out_bf16);
 int tc_deconv(dcv_ctx* ctx, const Layer& l, const float* in, int P, int h, int w, float* out);
+// strip kernel (tc_strip.cuh): 64 -> 64 backward conv with optional fused unpool (sw != null: `in` is the pooled tensor)
+// and optional fused last conv (last != null: fp32 compact result of the whole tail)
+bool tc_strip_conv_ok(const Layer& l);
+bool tc_strip_last_ok(const Layer& conv, const Layer& last);
+int tc_strip(dcv_ctx* ctx, const Layer& conv, const Layer* last, const __nv_bfloat16* in, const uint8_t* sw, int Bsw, int P, int h,
+             int w, __nv_bfloat16* out_bf16, float* out_f32, int relu);

@@ -1,0 +1,415 @@
+// "Strip" kernel for the 64-channel tail of a projection (included by conv_tc.cu only): the dx-grouped GEMM of
+// tc_dxg.cuh walked DOWN the image instead of along it, so that everything a tile shares with the tile below it stays
+// in shared memory — and with that the two neighbours of the 64 -> 64 conv can be fused into it:
+//
+//   UNPOOL  the conv's input is the switch-driven unpool of a pooled tensor (DPooling.down, deepdream.py:191-209):
+//           four producer warps expand pooled rows + switch bytes straight into the swizzled A tiles, the 4x larger
+//           unpooled tensor is never written to or read from HBM;
+//   LAST    the conv's output feeds the last backward conv (64 -> <= 3 channels, deepdream.py:102-111 of block1_conv1):
+//           the bf16 output tile stays in shared memory as the A operand of a second GEMM (all 9 taps stacked along N,
+//           the "GEMM + col2im" of tc_last.cuh), three consecutive P tiles give one finished row of the projection;
+//           the conv's 64-channel output never leaves the SM.
+//
+// Geometry.  The padded-flat tensor of P items x (h+1) x (w+1) rows is one tall image of T = P*(h+1) "tall rows" of
+// width wp = w+1 (pad rows / columns are zero, so a 3x3 'same' conv needs no other halo).  A tile is 120 consecutive
+// positions of ONE tall row (4 lane quarters x 30, as in tc_dxg.cuh); a strip is a column block (118 apart) times R
+// consecutive tall rows, processed top to bottom by one CTA.  The input rows live in a ring of IN_SLOTS shared-memory
+// A tiles: tile t multiplies rows t-1, t, t+1 (dy = -1, 0, +1) and only row t+1 is new - one 16 KB A tile per tile
+// instead of three.  Strips cost two extra input rows (and, with LAST, two extra tiles) at their top and bottom.
+//
+// Roles: warp 0 TMA (weights; input rows unless UNPOOL), warp 1 MMA issue, warps 2-17 epilogue (TMEM lane quarter x
+// 16-column group), warps 18-21 unpool producers (UNPOOL only).
+#pragma once
+#include "tc_kernel.cuh"
+
+namespace dcv {
+namespace tc {
+
+constexpr int STRIP_N = 192;                 // three dx taps x 64 output channels
+constexpr int STRIP_SEG = 30;                // output positions per lane quarter
+constexpr int STRIP_POS = 120;               // positions per tile
+constexpr int STRIP_CB = 118;                // column-block pitch (LAST loses one position at each end of a tile)
+constexpr int STRIP_IN_SLOTS = 4;
+constexpr int STRIP_EPI_WARPS = 16;
+constexpr int STRIP_PROD_WARPS = 4;
+constexpr int STRIP_W_BYTES = 3 * STRIP_N * 128;        // resident conv weights: [dy][192][64] bf16
+constexpr int STRIP_WL_BYTES = 32 * 128;                // resident all-tap weights of the last layer: [32][64] bf16
+constexpr int STRIP_PS = 29;                            // P row pitch in floats (27 used, odd: conflict-free)
+constexpr int STRIP_P_BYTES = 128 * STRIP_PS * 4;
+constexpr int STRIP_P_SLOTS = 3;
+
+__host__ __device__ constexpr int strip_threads(bool unpool) { return 64 + 32 * STRIP_EPI_WARPS + (unpool ? 32 * STRIP_PROD_WARPS : 0); }
+__host__ __device__ constexpr int strip_smem_bytes(bool last) {
+  return STRIP_W_BYTES + STRIP_IN_SLOTS * A_TILE_BYTES +
+         (last ? STRIP_WL_BYTES + 2 * A_TILE_BYTES + STRIP_P_SLOTS * STRIP_P_BYTES : A_TILE_BYTES) + 1024 + 256;
+}
+
+struct StripParams {
+  int rows;                  // P * (h+1) * (w+1)
+  int h, w;                  // image size at the conv (unpooled size with UNPOOL)
+  int T;                     // tall rows: P * (h+1)
+  int n_cb;                  // column blocks per tall row
+  int R;                     // tall rows per strip
+  int total_strips;
+  int relu;                  // activation of the 64 -> 64 conv
+  // UNPOOL: pooled padded-flat input (P, ph+1, pw+1, 64) bf16 and the pool layer's switches (Bsw, ph, pw, C) bytes
+  const __nv_bfloat16* pooled;
+  const uint8_t* sw;
+  int Bsw, C, ph, pw;
+  // LAST: the 64 -> cout3 conv; fp32 compact output (P, h, w, cout3)
+  int cout3, relu_last;
+  float* out;
+};
+
+// TMEM -> registers: this warp's 32 lanes x 8 consecutive fp32 columns
+__device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t (&v)[8]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7])
+               : "r"(taddr)
+               : "memory");
+}
+
+// what every role needs to know about a strip; all roles walk the same sequence
+struct StripWalk {
+  int c0;        // first position of the column block
+  int tfirst;    // tall row of the strip's first tile
+  int nt;        // tiles in the strip
+};
+template <bool LAST>
+__device__ __forceinline__ StripWalk strip_walk(const StripParams& p, int s) {
+  StripWalk k;
+  const int rc = s / p.n_cb, cb = s % p.n_cb;
+  const int t0 = rc * p.R;
+  const int rr = min(p.R, p.T - t0);
+  // without LAST the tile is stored as it is: the last block is pulled back so that it ends with the row (the store's
+  // box is min(120, wp) positions); with LAST positions beyond the row are never used
+  k.c0 = LAST ? cb * STRIP_CB : min(cb * STRIP_CB, max(0, p.w + 1 - STRIP_POS));
+  k.tfirst = t0 - (LAST ? 1 : 0);
+  k.nt = rr + (LAST ? 2 : 0);
+  return k;
+}
+
+template <bool UNPOOL, bool LAST>
+__global__ void __launch_bounds__(strip_threads(UNPOOL), 1)
+deconv_strip_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                    const __grid_constant__ CUtensorMap tmap_bl, const __grid_constant__ CUtensorMap tmap_out, StripParams p) {
+  constexpr int TMEM_COLS = 512;                      // conv accumulators at columns 0 / 256 (192 wide), P accumulators at 192 / 448 (32 wide)
+  constexpr int ACC_STRIDE = 256;
+  constexpr int PACC_OFF = 192;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* wres = smem;                                             // [dy][192 rows][128 B]
+  uint8_t* in_ring = wres + STRIP_W_BYTES;                          // IN_SLOTS A tiles (one input row of the strip each)
+  uint8_t* xs_base = in_ring + STRIP_IN_SLOTS * A_TILE_BYTES;       // !LAST: staging tile of the TMA store; LAST: two X tiles
+  uint8_t* wlast = xs_base + (LAST ? 2 : 1) * A_TILE_BYTES;         // LAST: [32 rows][128 B]
+  float* ps_base = reinterpret_cast<float*>(wlast + (LAST ? STRIP_WL_BYTES : 0));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(ps_base) + (LAST ? STRIP_P_SLOTS * STRIP_P_BYTES : 0));
+  uint64_t* in_full = bars;                           // [IN_SLOTS]
+  uint64_t* in_empty = in_full + STRIP_IN_SLOTS;      // [IN_SLOTS]
+  uint64_t* tfull_bar = in_empty + STRIP_IN_SLOTS;    // [2] conv accumulator ready
+  uint64_t* tempty_bar = tfull_bar + 2;               // [2] conv accumulator drained
+  uint64_t* xfull_bar = tempty_bar + 2;               // [2] X tile written by the epilogue
+  uint64_t* xempty_bar = xfull_bar + 2;               // [2] X tile consumed by the second GEMM
+  uint64_t* pfull_bar = xempty_bar + 2;               // [2] P accumulator ready
+  uint64_t* pempty_bar = pfull_bar + 2;               // [2] P accumulator drained
+  uint64_t* wres_bar = pempty_bar + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(wres_bar + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap_b);
+    if (!UNPOOL) tma_prefetch_desc(&tmap_a);
+    if (LAST) tma_prefetch_desc(&tmap_bl); else tma_prefetch_desc(&tmap_out);
+    for (int s = 0; s < STRIP_IN_SLOTS; ++s) { mbar_init(&in_full[s], UNPOOL ? STRIP_PROD_WARPS : 1); mbar_init(&in_empty[s], 1); }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&tfull_bar[b], 1); mbar_init(&tempty_bar[b], STRIP_EPI_WARPS);
+      mbar_init(&xfull_bar[b], STRIP_EPI_WARPS); mbar_init(&xempty_bar[b], 1);
+      mbar_init(&pfull_bar[b], 1); mbar_init(&pempty_bar[b], STRIP_EPI_WARPS);
+    }
+    mbar_init(wres_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, TMEM_COLS);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  griddep_launch_dependents();
+
+  const int wp = p.w + 1;
+
+  if (warp == 0) {
+    // ===== TMA: resident weights once; without UNPOOL also one input row (four 32-row boxes, 30 apart) per tile =====
+    if (lane == 0) {
+      mbar_arrive_expect_tx(wres_bar, (uint32_t)(STRIP_W_BYTES + (LAST ? STRIP_WL_BYTES : 0)));
+      for (int dy = 0; dy < 3; ++dy) tma_load_2d(wres + dy * STRIP_N * 128, &tmap_b, wres_bar, 0, dy * STRIP_N);
+      if (LAST) tma_load_2d(wlast, &tmap_bl, wres_bar, 0, 0);
+      if (!UNPOOL) {
+        griddep_wait();
+        uint32_t gi = 0;                              // input rows loaded by this CTA so far
+        for (int s = blockIdx.x; s < p.total_strips; s += gridDim.x) {
+          const StripWalk k = strip_walk<LAST>(p, s);
+          for (int i = 0; i < k.nt + 2; ++i, ++gi) {
+            const uint32_t slot = gi % STRIP_IN_SLOTS, use = gi / STRIP_IN_SLOTS;
+            mbar_wait(&in_empty[slot], (use & 1) ^ 1);
+            uint8_t* dst = in_ring + slot * A_TILE_BYTES;
+            mbar_arrive_expect_tx(&in_full[slot], (uint32_t)A_TILE_BYTES);
+            const int row0 = (k.tfirst - 1 + i) * wp + k.c0 - 1;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) tma_load_2d(dst + q * 32 * 128, &tmap_a, &in_full[slot], 0, row0 + STRIP_SEG * q);
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issue: conv tile g (12 MMAs, N = 192) then, with LAST, the second GEMM of tile g-1 (4 MMAs, N = 32) =====
+    constexpr uint32_t idesc = make_idesc_bf16(BLOCK_M, STRIP_N);
+    constexpr uint32_t idesc_l = make_idesc_bf16(BLOCK_M, 32);
+    mbar_wait(wres_bar, 0);
+    tc_fence_after();
+    const uint64_t bl_desc = make_sw128_kmajor_desc(smem_u32(wlast), 0);
+    auto second_gemm = [&](uint32_t g) {              // P(g) = X(g) * Wall
+      const uint32_t b = g & 1, use = g >> 1;
+      mbar_wait(&xfull_bar[b], use & 1);
+      mbar_wait(&pempty_bar[b], (use & 1) ^ 1);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint64_t a_desc = make_sw128_kmajor_desc(smem_u32(xs_base + b * A_TILE_BYTES), 0);
+        const uint32_t d = tmem_base + (uint32_t)(b * ACC_STRIDE + PACC_OFF);
+#pragma unroll
+        for (int kk = 0; kk < BLOCK_K / 16; ++kk) umma_bf16(d, a_desc + (uint64_t)(2 * kk), bl_desc + (uint64_t)(2 * kk), idesc_l, kk != 0);
+        umma_commit(&xempty_bar[b]);
+        umma_commit(&pfull_bar[b]);
+      }
+      __syncwarp();
+    };
+    uint32_t gi0 = 0;                                 // global index of the strip's first input row
+    uint32_t g = 0;                                   // tiles issued by this CTA so far
+    for (int s = blockIdx.x; s < p.total_strips; s += gridDim.x) {
+      const StripWalk k = strip_walk<LAST>(p, s);
+      for (int j = 0; j < k.nt; ++j, ++g) {
+        const uint32_t buf = g & 1, use = g >> 1;
+        mbar_wait(&tempty_bar[buf], (use & 1) ^ 1);
+        for (int dy = (j == 0 ? 0 : 2); dy < 3; ++dy) {   // rows j, j+1 arrived with the previous tiles
+          const uint32_t gi = gi0 + j + dy;
+          mbar_wait(&in_full[gi % STRIP_IN_SLOTS], (gi / STRIP_IN_SLOTS) & 1);
+        }
+        tc_fence_after();
+        if (elect_one()) {
+          const uint32_t d_tmem = tmem_base + buf * ACC_STRIDE;
+#pragma unroll
+          for (int dy = 0; dy < 3; ++dy) {
+            const uint32_t gi = gi0 + j + dy;
+            const uint64_t a_desc = make_sw128_kmajor_desc(smem_u32(in_ring + (gi % STRIP_IN_SLOTS) * A_TILE_BYTES), 0);
+            const uint64_t b_desc = make_sw128_kmajor_desc(smem_u32(wres + dy * STRIP_N * 128), 0);
+#pragma unroll
+            for (int kk = 0; kk < BLOCK_K / 16; ++kk)
+              umma_bf16(d_tmem, a_desc + (uint64_t)(2 * kk), b_desc + (uint64_t)(2 * kk), idesc, (dy | kk) != 0);
+          }
+          umma_commit(&tfull_bar[buf]);
+          umma_commit(&in_empty[(gi0 + j) % STRIP_IN_SLOTS]);          // row j is not needed below this tile
+          if (j == k.nt - 1) {                                          // bottom of the strip: its last two rows too
+            umma_commit(&in_empty[(gi0 + j + 1) % STRIP_IN_SLOTS]);
+            umma_commit(&in_empty[(gi0 + j + 2) % STRIP_IN_SLOTS]);
+          }
+        }
+        __syncwarp();
+        if (LAST && g > 0) second_gemm(g - 1);
+      }
+      gi0 += (uint32_t)k.nt + 2;
+    }
+    if (LAST && g > 0) second_gemm(g - 1);
+  } else if (warp < 2 + STRIP_EPI_WARPS) {
+    // ===== epilogue warps =====
+    const int lg = warp & 3;                                  // TMEM lane quarter this warp may read
+    const int cg = (warp - 2) >> 2;                           // column group
+    const int cc = cg * 16;                                   // its 16 output channels of the 64 -> 64 conv
+    const int et = threadIdx.x - 64;                          // 0 .. 511 among the epilogue threads
+    const int rp = (p.h + 1) * wp;
+    const float relu_lo = p.relu ? 0.f : -INFINITY;
+    const bool issuer = (warp == 2) && (lane == 0);
+    // LAST: the last three tiles (oldest first) for the col2im of the middle one
+    int hj[3] = {-1, -1, -1}, hnt[3] = {0, 0, 0}, ht[3] = {0, 0, 0}, hc0[3] = {0, 0, 0};
+
+    // finishes the projection row of the tile in history slot 1 from the P tiles of g-3, g-2, g-1 (g = tiles drained + 1)
+    auto col2im = [&](uint32_t g) {
+      const int jc = hj[1];
+      if (jc >= 1 && jc <= hnt[1] - 2) {                      // top and bottom tiles of a strip are halo only
+        const int tc = ht[1], c0 = hc0[1];
+        const int y = tc % (p.h + 1), item = tc / (p.h + 1);
+        const int xs = c0 == 0 ? 0 : c0 + 1;
+        const int xe = min(c0 + STRIP_POS - 1, p.w);
+        const int m = et;                                     // one output value per thread: (x - xs) * cout3 + c
+        if (y < p.h && m < (xe - xs) * p.cout3) {
+          const int xl = m / p.cout3, c = m - xl * p.cout3;
+          const int i = xs + xl - c0;                         // position inside the tile
+          float acc = 0.f;
+#pragma unroll
+          for (int dy = 0; dy < 3; ++dy) {
+            const float* ps = ps_base + ((g - 3 + dy) % STRIP_P_SLOTS) * (128 * STRIP_PS);
+#pragma unroll
+            for (int dx = 0; dx < 3; ++dx) {
+              const int ii = i + dx - 1;
+              if (ii >= 0) acc += ps[ii * STRIP_PS + (dy * 3 + dx) * p.cout3 + c];
+            }
+          }
+          if (p.relu_last) acc = fmaxf(acc, 0.f);
+          p.out[(((size_t)item * p.h + y) * p.w + xs + xl) * p.cout3 + c] = acc;
+        }
+      }
+    };
+    // moves P(g) from its TMEM accumulator into shared memory slot g % 3
+    auto drain_p = [&](uint32_t g) {
+      const uint32_t b = g & 1, use = g >> 1;
+      mbar_wait(&pfull_bar[b], use & 1);
+      tc_fence_after();
+      uint32_t v[8];
+      tmem_ld8(tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(b * ACC_STRIDE + PACC_OFF + cg * 8), v);
+      tmem_ld_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&pempty_bar[b]);
+      float* dst = ps_base + (g % STRIP_P_SLOTS) * (128 * STRIP_PS) + (lg * 32 + lane) * STRIP_PS + cg * 8;
+#pragma unroll
+      for (int q = 0; q < 8; ++q)
+        if (cg * 8 + q < 27) dst[q] = __uint_as_float(v[q]);
+    };
+
+    uint32_t g = 0;
+    for (int s = blockIdx.x; s < p.total_strips; s += gridDim.x) {
+      const StripWalk k = strip_walk<LAST>(p, s);
+      for (int j = 0; j < k.nt; ++j, ++g) {
+        const uint32_t buf = g & 1, use = g >> 1;
+        const int tall = k.tfirst + j;
+        const long long r = (long long)tall * wp + k.c0 + STRIP_SEG * lg + lane;      // flat output row of this thread
+        const bool in_range = (lane < STRIP_SEG) && r >= 0 && r < (long long)p.rows;
+        const int q = in_range ? (int)(r % rp) : 0;
+        const bool is_pixel = in_range && (q % wp < p.w) && (q / wp < p.h);
+        mbar_wait(&tfull_bar[buf], use & 1);
+        tc_fence_after();
+        const uint32_t t_row = tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(buf * ACC_STRIDE);
+        uint32_t v0[32], v1[32], v2[32];                      // 16 used
+        tmem_ld16(t_row + (uint32_t)cc, v0);
+        tmem_ld16(t_row + (uint32_t)(64 + cc), v1);
+        tmem_ld16(t_row + (uint32_t)(128 + cc), v2);
+        tmem_ld_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tempty_bar[buf]);
+        uint32_t packed[8];
+#pragma unroll
+        for (int c = 0; c < 16; c += 2) {
+          float sv[2];
+#pragma unroll
+          for (int e = 0; e < 2; ++e) {
+            float t = __uint_as_float(v0[c + e]);
+            t += __shfl_down_sync(0xffffffffu, __uint_as_float(v1[c + e]), 1) + __shfl_down_sync(0xffffffffu, __uint_as_float(v2[c + e]), 2);
+            sv[e] = fmaxf(t, relu_lo);
+          }
+          __nv_bfloat162 h2 = __floats2bfloat162_rn(sv[0], sv[1]);
+          packed[c / 2] = is_pixel ? *reinterpret_cast<uint32_t*>(&h2) : 0u;
+        }
+        const int row_local = STRIP_SEG * lg + lane;
+        const int jch = cc >> 3;                              // 16-byte chunk of this thread's first 8 channels
+        if constexpr (!LAST) {
+          if (issuer) tma_store_wait_read();                  // the previous tile's store has read the staging tile
+          named_barrier_sync(1, 32 * STRIP_EPI_WARPS);
+          if (lane < STRIP_SEG) {
+            uint8_t* rowp = xs_base + row_local * 128;
+            *reinterpret_cast<uint4*>(rowp + (((jch) ^ (row_local & 7)) << 4)) = make_uint4(packed[0], packed[1], packed[2], packed[3]);
+            *reinterpret_cast<uint4*>(rowp + (((jch + 1) ^ (row_local & 7)) << 4)) = make_uint4(packed[4], packed[5], packed[6], packed[7]);
+          }
+          fence_proxy_async_smem();
+          named_barrier_sync(1, 32 * STRIP_EPI_WARPS);
+          if (issuer && tall >= 0) {
+            tma_store_2d(&tmap_out, xs_base, 0, tall * wp + k.c0);
+            tma_store_commit();
+          }
+        } else {
+          // X tile = A operand of the second GEMM (rows = positions, 128 B = 64 channels, 128-byte swizzle)
+          mbar_wait(&xempty_bar[buf], (use & 1) ^ 1);
+          if (lane < STRIP_SEG) {
+            uint8_t* rowp = xs_base + buf * A_TILE_BYTES + row_local * 128;
+            *reinterpret_cast<uint4*>(rowp + (((jch) ^ (row_local & 7)) << 4)) = make_uint4(packed[0], packed[1], packed[2], packed[3]);
+            *reinterpret_cast<uint4*>(rowp + (((jch + 1) ^ (row_local & 7)) << 4)) = make_uint4(packed[4], packed[5], packed[6], packed[7]);
+          }
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&xfull_bar[buf]);
+          // software pipeline: P of the previous tile, then the finished row two tiles back
+          // (history: [2] = tile g-1, [1] = tile g-2, the middle of the col2im; a middle with 1 <= j <= nt-2 has both
+          // neighbours in its own strip)
+          if (g > 0) drain_p(g - 1);
+          named_barrier_sync(1, 32 * STRIP_EPI_WARPS);
+          if (g > 1) col2im(g);
+          named_barrier_sync(1, 32 * STRIP_EPI_WARPS);
+          hj[0] = hj[1]; hnt[0] = hnt[1]; ht[0] = ht[1]; hc0[0] = hc0[1];
+          hj[1] = hj[2]; hnt[1] = hnt[2]; ht[1] = ht[2]; hc0[1] = hc0[2];
+          hj[2] = j; hnt[2] = k.nt; ht[2] = tall; hc0[2] = k.c0;
+        }
+      }
+    }
+    if constexpr (!LAST) {
+      if (issuer) tma_store_wait_read();
+    } else if (g > 0) {
+      drain_p(g - 1);
+      named_barrier_sync(1, 32 * STRIP_EPI_WARPS);
+      if (g > 1) col2im(g);
+    }
+  } else if (UNPOOL) {
+    // ===== unpool producers (warps 18-21): one input row of the strip = 128 A rows x 8 chunks of 8 channels.
+    // A row holds position x = c0 - 1 + 30*seg + l of tall row tin; its value is the pooled pixel (y/2, x/2) where the
+    // switch names this corner of the 2x2 quad, zero elsewhere (DPooling.down) =====
+    const int pt = threadIdx.x - 32 * (2 + STRIP_EPI_WARPS);  // 0 .. 127
+    const int chunk = pt & 7;
+    const int pwp = p.pw + 1, prp = (p.ph + 1) * pwp;
+    griddep_wait();
+    uint32_t gi = 0;
+    for (int s = blockIdx.x; s < p.total_strips; s += gridDim.x) {
+      const StripWalk k = strip_walk<LAST>(p, s);
+      for (int i = 0; i < k.nt + 2; ++i, ++gi) {
+        const uint32_t slot = gi % STRIP_IN_SLOTS, use = gi / STRIP_IN_SLOTS;
+        const int tin = k.tfirst - 1 + i;
+        const bool row_ok = tin >= 0 && tin < p.T && (tin % (p.h + 1)) < p.h;
+        const int y = row_ok ? tin % (p.h + 1) : 0, item = row_ok ? tin / (p.h + 1) : 0;
+        const __nv_bfloat16* prow = p.pooled + ((size_t)item * prp + (size_t)(y >> 1) * pwp) * 64 + chunk * 8;
+        const uint8_t* srow = p.sw + ((size_t)(item % p.Bsw) * p.ph + (y >> 1)) * p.pw * p.C + chunk * 8;
+        const uint32_t qy = (uint32_t)(y & 1) * 2u;
+        mbar_wait(&in_empty[slot], (use & 1) ^ 1);
+        uint8_t* dst = in_ring + slot * A_TILE_BYTES;
+#pragma unroll 4
+        for (int jj = 0; jj < 8; ++jj) {
+          const int rr = (pt >> 3) + 16 * jj;                 // A row 0 .. 127
+          const int x = k.c0 - 1 + STRIP_SEG * (rr >> 5) + (rr & 31);
+          uint4 val = make_uint4(0u, 0u, 0u, 0u);
+          if (row_ok && x >= 0 && x < p.w) {
+            const uint4 pv = __ldg(reinterpret_cast<const uint4*>(prow + (size_t)(x >> 1) * 64));
+            const uint2 sv = __ldg(reinterpret_cast<const uint2*>(srow + (size_t)(x >> 1) * p.C));
+            const uint32_t want = (qy + (uint32_t)(x & 1)) * 0x01010101u;
+            const uint32_t m0 = __vcmpeq4(sv.x, want), m1 = __vcmpeq4(sv.y, want);   // 0xFF per matching switch byte
+            val.x = pv.x & __byte_perm(m0, 0, 0x1100);
+            val.y = pv.y & __byte_perm(m0, 0, 0x3322);
+            val.z = pv.z & __byte_perm(m1, 0, 0x1100);
+            val.w = pv.w & __byte_perm(m1, 0, 0x3322);
+          }
+          *reinterpret_cast<uint4*>(dst + rr * 128 + ((chunk ^ (rr & 7)) << 4)) = val;
+        }
+        fence_proxy_async_smem();                             // the MMA reads the tile through the async proxy
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&in_full[slot]);
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, TMEM_COLS);
+}
+
+}  // namespace tc
+}  // namespace dcv

@@ -324,6 +324,27 @@ class Engine(object):
         return out
 
 
+    def deconv_tail(self, x, W2, W1=None, sw=None, relu2=True, relu1=True):
+        """[unpool by `sw`] -> backward conv of forward kernel W2 (3,3,cmid,c2) -> [backward conv of W1 (3,3,c0,cmid)],
+        the fused bf16 tail kernel.  x: (B,H,W,c2), or the pooled (B,H/2,W/2,c2) when sw is given."""
+        x, W2 = _f32(x), _f32(W2)
+        B, ih, iw, c2 = x.shape
+        H, W = (2 * ih, 2 * iw) if sw is not None else (ih, iw)
+        cmid = W2.shape[2]
+        assert W2.shape == (3, 3, cmid, c2)
+        c0 = 0
+        if W1 is not None:
+            W1 = _f32(W1)
+            c0 = W1.shape[2]
+            assert W1.shape == (3, 3, c0, cmid)
+        if sw is not None:
+            sw = np.ascontiguousarray(sw, np.uint8)
+            assert sw.shape == x.shape
+        out = np.empty((B, H, W, c0 if W1 is not None else cmid), np.float32)
+        self._ck(self.lib.dcv_deconv_tail(self.ctx, _ptr(x), _ptr(sw) if sw is not None else None, B, H, W, _ptr(W2), cmid, c2,
+                                          1 if relu2 else 0, _ptr(W1) if W1 is not None else None, c0, 1 if relu1 else 0, _ptr(out)))
+        return out
+
     def _activation(self, x, act):
         x = _f32(x)
         n = x.shape[-1]

@@ -220,6 +220,15 @@ DCV_API int dcv_conv3x3(dcv_ctx* ctx, const float* x, const float* w_hwio, const
 DCV_API int dcv_deconv3x3(dcv_ctx* ctx, const float* x, const float* w_hwio,
                   int B, int H, int W, int cin, int cout, int relu, int precision, float* out);
 
+/* The 64-channel tail of a DCV_BF16 projection as ONE kernel (unit-parity hook of csrc/tc_strip.cuh): optional
+ * DPooling.down (deepdream.py:141-150,191-209; sw != NULL: x is the pooled tensor (B,H/2,W/2,c2) and sw its switches),
+ * DConvolution2D.down (deepdream.py:102-111) of a conv with forward kernel w2 (3,3,cmid,c2), and optionally the same of
+ * the conv below it, w1 (3,3,c0,cmid) (w1 == NULL: out = (B,H,W,cmid), else (B,H,W,c0)).  bf16 operands, fp32
+ * accumulation; the intermediate between the two convs is rounded to bf16 as in the unfused chain.  Needs
+ * cmid == c2 == 64 and c0 <= 3 (VGG16 block1), DCV_ERR_UNSUPPORTED otherwise. */
+DCV_API int dcv_deconv_tail(dcv_ctx* ctx, const float* x, const uint8_t* sw, int B, int H, int W, const float* w2_hwio, int cmid,
+                            int c2, int relu2, const float* w1_hwio, int c0, int relu1, float* out);
+
 /* DActivation.up/.down (deepdream.py:212-261): the layer's activation (dcv_act id) applied to `rows`
  * rows of `n` values; softmax runs along each row. */
 DCV_API int dcv_activation(dcv_ctx* ctx, const float* x, int rows, int n, int act, float* out);
