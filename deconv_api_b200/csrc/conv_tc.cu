@@ -564,6 +564,9 @@ struct TcConvArgs {
 
 static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& a, const __nv_bfloat16* in, int P, int h, int w,
                        __nv_bfloat16* out_bf16, float* out_f32);
+static int tc_strip_impl(dcv_ctx* ctx, const Layer& conv, const Layer* last, const __nv_bfloat16* in, const uint8_t* sw, int Bsw, int P,
+                         int h, int w, __nv_bfloat16* out_bf16, float* out_f32, int relu, bool prof);
+
 
 int tc_cpad(int c) { return round_up(c, 64); }
 
@@ -1018,7 +1021,7 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
       Layer tmp;
       tmp.kind = LK_CONV; tmp.cin = l.n_real; tmp.cout = l.k_real; tmp.relu = l.relu;
       tmp.tc.wd_bf16 = const_cast<__nv_bfloat16*>(l.w); tmp.tc.k_pad = 64; tmp.tc.n_pad = 64;
-      return tc_strip(ctx, tmp, nullptr, in, nullptr, 0, P, h, w, out_bf16, nullptr, l.relu);
+      return tc_strip_impl(ctx, tmp, nullptr, in, nullptr, 0, P, h, w, out_bf16, nullptr, l.relu, false);
     }
     // 64 output channels: dx-grouped GEMM (tc_dxg.cuh), tiles of 126 rows
     TcParams q = p;
@@ -1149,7 +1152,7 @@ bool tc_strip_last_ok(const Layer& conv, const Layer& last) {
 template <bool UNPOOL, bool LAST>
 static int launch_strip(dcv_ctx* ctx, const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tbl, const CUtensorMap& to,
                         const StripParams& p) {
-  const int smem = strip_smem_bytes(LAST);
+  const int smem = strip_smem_bytes(UNPOOL, LAST);
   static int smem_set[64] = {};
   cudaError_t e = cudaSuccess;
   if (smem_set[ctx->device & 63] < smem) {
@@ -1158,7 +1161,7 @@ static int launch_strip(dcv_ctx* ctx, const CUtensorMap& ta, const CUtensorMap& 
     smem_set[ctx->device & 63] = smem;
   }
   const int grid = std::min(p.total_strips, ctx->num_sms);
-  e = launch_k(ctx, deconv_strip_kernel<UNPOOL, LAST>, dim3(grid), dim3(strip_threads(UNPOOL)), (size_t)smem, ta, tb, tbl, to, p);
+  e = launch_k(ctx, deconv_strip_kernel<UNPOOL, LAST>, dim3(grid), dim3(strip_threads(UNPOOL, LAST)), (size_t)smem, ta, tb, tbl, to, p);
   if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "launch(deconv_strip_kernel<%d,%d>): %s", (int)UNPOOL, (int)LAST, cudaGetErrorString(e));
   ctx->launches++;
   e = cudaGetLastError();
@@ -1171,6 +1174,11 @@ static int launch_strip(dcv_ctx* ctx, const CUtensorMap& ta, const CUtensorMap& 
 // last != null: out_f32 = act(last(act(conv))) compact (P, h, w, last->cin).
 int tc_strip(dcv_ctx* ctx, const Layer& conv, const Layer* last, const __nv_bfloat16* in, const uint8_t* sw, int Bsw, int P, int h,
              int w, __nv_bfloat16* out_bf16, float* out_f32, int relu) {
+  return tc_strip_impl(ctx, conv, last, in, sw, Bsw, P, h, w, out_bf16, out_f32, relu, true);
+}
+
+static int tc_strip_impl(dcv_ctx* ctx, const Layer& conv, const Layer* last, const __nv_bfloat16* in, const uint8_t* sw, int Bsw, int P,
+                         int h, int w, __nv_bfloat16* out_bf16, float* out_f32, int relu, bool prof) {
   if (!tc_strip_conv_ok(conv)) return ctx->fail(DCV_ERR_UNSUPPORTED, "tc_strip: the layer is not a 64 -> 64 channel conv");
   if (last && !tc_strip_last_ok(conv, *last)) return ctx->fail(DCV_ERR_UNSUPPORTED, "tc_strip: the last layer cannot be fused");
   if (sw && ((h & 1) || (w & 1) || conv.cout != 64)) return ctx->fail(DCV_ERR_UNSUPPORTED, "tc_strip: fused unpool needs even sizes and 64 channels");
@@ -1201,7 +1209,8 @@ int tc_strip(dcv_ctx* ctx, const Layer& conv, const Layer* last, const __nv_bflo
   const double px = (double)P * h * w;
   double flops = 2.0 * 9 * px * conv.cin * conv.cout, bytes = 2.0 * px * conv.cout * (sw ? 0.25 + 0.125 : 1.0);
   if (last) { flops += 2.0 * 9 * px * last->cin * last->cout; bytes += 4.0 * px * last->cin; } else bytes += 2.0 * px * conv.cin;
-  ProfScope ps(ctx, DCV_K_CONV_TC, flops, bytes);
+  dcv_ctx silent;                              // the caller's ProfScope is already open: record nothing here
+  ProfScope ps(prof ? ctx : &silent, DCV_K_CONV_TC, flops, bytes);
   if (sw) return last ? launch_strip<true, true>(ctx, ta, tb, tbl, to, p) : launch_strip<true, false>(ctx, ta, tb, tbl, to, p);
   return last ? launch_strip<false, true>(ctx, ta, tb, tbl, to, p) : launch_strip<false, false>(ctx, ta, tb, tbl, to, p);
 }

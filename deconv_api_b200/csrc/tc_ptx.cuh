@@ -28,6 +28,18 @@ __device__ __forceinline__ bool elect_one() {
   return pred != 0;
 }
 
+// Shared-memory accesses by 32-bit shared-window address: generic-pointer arithmetic on the dynamic shared array makes
+// the compiler emit LD.E / ST.E with 64-bit address math (measured in tc_strip.cuh's producer: 26 instructions per 16-byte
+// store instead of ~12).
+__device__ __forceinline__ void sts128(uint32_t addr, const uint4& v) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ uint2 lds64(uint32_t addr) {
+  uint2 v;
+  asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr));
+  return v;
+}
+
 // ---- mbarrier ---------------------------------------------------------------------------------------
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
@@ -52,6 +64,23 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
       "DONE:\n"
       "}\n" ::"r"(smem_u32(bar)),
       "r"(parity)
+      : "memory");
+}
+
+// The same wait with a suspend-time hint: the hardware may park the thread until the phase completes (or the hint, in
+// ns, runs out) instead of re-issuing the test in a tight loop - for warps that wait long next to warps that must get
+// issue slots (tc_strip.cuh: 16 + 4 waiting warps share their schedulers with the unpool producers).
+__device__ __forceinline__ void mbar_wait_parked(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred P1;\n"
+      "LAB_WAIT:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1, %2;\n"
+      "@P1 bra DONE;\n"
+      "bra LAB_WAIT;\n"
+      "DONE:\n"
+      "}\n" ::"r"(smem_u32(bar)),
+      "r"(parity), "r"(20000u)
       : "memory");
 }
 

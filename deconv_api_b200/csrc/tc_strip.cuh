@@ -17,8 +17,10 @@
 // A tiles: tile t multiplies rows t-1, t, t+1 (dy = -1, 0, +1) and only row t+1 is new - one 16 KB A tile per tile
 // instead of three.  Strips cost two extra input rows (and, with LAST, two extra tiles) at their top and bottom.
 //
-// Roles: warp 0 TMA (weights; input rows unless UNPOOL), warp 1 MMA issue, warps 2-17 epilogue (TMEM lane quarter x
-// 16-column group), warps 18-21 unpool producers (UNPOOL only).
+// Roles: warp 0 TMA (weights; input rows unless UNPOOL), warp 1 MMA issue, warps 2-17 conv epilogue (TMEM lane quarter x
+// 16-column group), then four "tail" warps (LAST: P tiles out of TMEM, col2im, fp32 stores) and four unpool producer warps
+// (UNPOOL).  Every stage hands over through mbarriers only; measured with the col2im inside the conv epilogue's
+// lock-step (two 512-thread barriers per tile) the fused kernel was no faster than the two kernels it replaces.
 #pragma once
 #include "tc_kernel.cuh"
 
@@ -38,9 +40,13 @@ constexpr int STRIP_PS = 29;                            // P row pitch in floats
 constexpr int STRIP_P_BYTES = 128 * STRIP_PS * 4;
 constexpr int STRIP_P_SLOTS = 3;
 
-__host__ __device__ constexpr int strip_threads(bool unpool) { return 64 + 32 * STRIP_EPI_WARPS + (unpool ? 32 * STRIP_PROD_WARPS : 0); }
-__host__ __device__ constexpr int strip_smem_bytes(bool last) {
-  return STRIP_W_BYTES + STRIP_IN_SLOTS * A_TILE_BYTES +
+constexpr int STRIP_TAIL_WARPS = 4;
+__host__ __device__ constexpr int strip_threads(bool unpool, bool last) {
+  return 64 + 32 * STRIP_EPI_WARPS + (last ? 32 * STRIP_TAIL_WARPS : 0) + (unpool ? 32 * STRIP_PROD_WARPS : 0);
+}
+constexpr int STRIP_LUT_BYTES = 4 * 256 * 8;            // UNPOOL: switch bytes -> lane masks, per quad corner
+__host__ __device__ constexpr int strip_smem_bytes(bool unpool, bool last) {
+  return STRIP_W_BYTES + STRIP_IN_SLOTS * A_TILE_BYTES + (unpool ? STRIP_LUT_BYTES : 0) +
          (last ? STRIP_WL_BYTES + 2 * A_TILE_BYTES + STRIP_P_SLOTS * STRIP_P_BYTES : A_TILE_BYTES) + 1024 + 256;
 }
 
@@ -90,7 +96,7 @@ __device__ __forceinline__ StripWalk strip_walk(const StripParams& p, int s) {
 }
 
 template <bool UNPOOL, bool LAST>
-__global__ void __launch_bounds__(strip_threads(UNPOOL), 1)
+__global__ void __launch_bounds__(strip_threads(UNPOOL, LAST), 1)
 deconv_strip_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                     const __grid_constant__ CUtensorMap tmap_bl, const __grid_constant__ CUtensorMap tmap_out, StripParams p) {
   constexpr int TMEM_COLS = 512;                      // conv accumulators at columns 0 / 256 (192 wide), P accumulators at 192 / 448 (32 wide)
@@ -103,7 +109,8 @@ deconv_strip_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
   uint8_t* xs_base = in_ring + STRIP_IN_SLOTS * A_TILE_BYTES;       // !LAST: staging tile of the TMA store; LAST: two X tiles
   uint8_t* wlast = xs_base + (LAST ? 2 : 1) * A_TILE_BYTES;         // LAST: [32 rows][128 B]
   float* ps_base = reinterpret_cast<float*>(wlast + (LAST ? STRIP_WL_BYTES : 0));
-  uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(ps_base) + (LAST ? STRIP_P_SLOTS * STRIP_P_BYTES : 0));
+  uint2* lut = reinterpret_cast<uint2*>(reinterpret_cast<uint8_t*>(ps_base) + (LAST ? STRIP_P_SLOTS * STRIP_P_BYTES : 0));   // UNPOOL: [corner][256]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(lut) + (UNPOOL ? STRIP_LUT_BYTES : 0));
   uint64_t* in_full = bars;                           // [IN_SLOTS]
   uint64_t* in_empty = in_full + STRIP_IN_SLOTS;      // [IN_SLOTS]
   uint64_t* tfull_bar = in_empty + STRIP_IN_SLOTS;    // [2] conv accumulator ready
@@ -126,7 +133,7 @@ deconv_strip_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     for (int b = 0; b < 2; ++b) {
       mbar_init(&tfull_bar[b], 1); mbar_init(&tempty_bar[b], STRIP_EPI_WARPS);
       mbar_init(&xfull_bar[b], STRIP_EPI_WARPS); mbar_init(&xempty_bar[b], 1);
-      mbar_init(&pfull_bar[b], 1); mbar_init(&pempty_bar[b], STRIP_EPI_WARPS);
+      mbar_init(&pfull_bar[b], 1); mbar_init(&pempty_bar[b], STRIP_TAIL_WARPS);
     }
     mbar_init(wres_bar, 1);
     fence_barrier_init();
@@ -225,72 +232,28 @@ deconv_strip_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     }
     if (LAST && g > 0) second_gemm(g - 1);
   } else if (warp < 2 + STRIP_EPI_WARPS) {
-    // ===== epilogue warps =====
+    // ===== conv epilogue warps: accumulator -> dx combination (lane shuffles) -> ReLU -> bf16 tile in shared memory;
+    // !LAST: one TMA store per tile; LAST: the tile is the A operand of the second GEMM =====
     const int lg = warp & 3;                                  // TMEM lane quarter this warp may read
-    const int cg = (warp - 2) >> 2;                           // column group
-    const int cc = cg * 16;                                   // its 16 output channels of the 64 -> 64 conv
-    const int et = threadIdx.x - 64;                          // 0 .. 511 among the epilogue threads
-    const int rp = (p.h + 1) * wp;
+    const int cc = ((warp - 2) >> 2) * 16;                    // its 16 output channels
     const float relu_lo = p.relu ? 0.f : -INFINITY;
     const bool issuer = (warp == 2) && (lane == 0);
-    // LAST: the last three tiles (oldest first) for the col2im of the middle one
-    int hj[3] = {-1, -1, -1}, hnt[3] = {0, 0, 0}, ht[3] = {0, 0, 0}, hc0[3] = {0, 0, 0};
-
-    // finishes the projection row of the tile in history slot 1 from the P tiles of g-3, g-2, g-1 (g = tiles drained + 1)
-    auto col2im = [&](uint32_t g) {
-      const int jc = hj[1];
-      if (jc >= 1 && jc <= hnt[1] - 2) {                      // top and bottom tiles of a strip are halo only
-        const int tc = ht[1], c0 = hc0[1];
-        const int y = tc % (p.h + 1), item = tc / (p.h + 1);
-        const int xs = c0 == 0 ? 0 : c0 + 1;
-        const int xe = min(c0 + STRIP_POS - 1, p.w);
-        const int m = et;                                     // one output value per thread: (x - xs) * cout3 + c
-        if (y < p.h && m < (xe - xs) * p.cout3) {
-          const int xl = m / p.cout3, c = m - xl * p.cout3;
-          const int i = xs + xl - c0;                         // position inside the tile
-          float acc = 0.f;
-#pragma unroll
-          for (int dy = 0; dy < 3; ++dy) {
-            const float* ps = ps_base + ((g - 3 + dy) % STRIP_P_SLOTS) * (128 * STRIP_PS);
-#pragma unroll
-            for (int dx = 0; dx < 3; ++dx) {
-              const int ii = i + dx - 1;
-              if (ii >= 0) acc += ps[ii * STRIP_PS + (dy * 3 + dx) * p.cout3 + c];
-            }
-          }
-          if (p.relu_last) acc = fmaxf(acc, 0.f);
-          p.out[(((size_t)item * p.h + y) * p.w + xs + xl) * p.cout3 + c] = acc;
-        }
-      }
-    };
-    // moves P(g) from its TMEM accumulator into shared memory slot g % 3
-    auto drain_p = [&](uint32_t g) {
-      const uint32_t b = g & 1, use = g >> 1;
-      mbar_wait(&pfull_bar[b], use & 1);
-      tc_fence_after();
-      uint32_t v[8];
-      tmem_ld8(tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(b * ACC_STRIDE + PACC_OFF + cg * 8), v);
-      tmem_ld_wait();
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&pempty_bar[b]);
-      float* dst = ps_base + (g % STRIP_P_SLOTS) * (128 * STRIP_PS) + (lg * 32 + lane) * STRIP_PS + cg * 8;
-#pragma unroll
-      for (int q = 0; q < 8; ++q)
-        if (cg * 8 + q < 27) dst[q] = __uint_as_float(v[q]);
-    };
-
+    const int row_local = STRIP_SEG * lg + lane;
+    const int jch = cc >> 3;                                  // 16-byte chunk of this thread's first 8 channels
+    const uint32_t xs_u32 = smem_u32(xs_base);
     uint32_t g = 0;
     for (int s = blockIdx.x; s < p.total_strips; s += gridDim.x) {
       const StripWalk k = strip_walk<LAST>(p, s);
-      for (int j = 0; j < k.nt; ++j, ++g) {
+      // a position is a pixel when its column is one (positions past the row's end belong to the next tall row and are
+      // never used) and its tall row is not a pad row; the row's y is kept incrementally (no division per tile)
+      const bool col_ok = (lane < STRIP_SEG) && (k.c0 + row_local < p.w);
+      int tall = k.tfirst;
+      int y = tall >= 0 ? tall % (p.h + 1) : p.h;
+      for (int j = 0; j < k.nt; ++j, ++g, ++tall) {
         const uint32_t buf = g & 1, use = g >> 1;
-        const int tall = k.tfirst + j;
-        const long long r = (long long)tall * wp + k.c0 + STRIP_SEG * lg + lane;      // flat output row of this thread
-        const bool in_range = (lane < STRIP_SEG) && r >= 0 && r < (long long)p.rows;
-        const int q = in_range ? (int)(r % rp) : 0;
-        const bool is_pixel = in_range && (q % wp < p.w) && (q / wp < p.h);
-        mbar_wait(&tfull_bar[buf], use & 1);
+        const bool is_pixel = col_ok && tall >= 0 && tall < p.T && y < p.h;
+        if (tall < 0) y = 0; else if (++y > p.h) y = 0;       // y of the next tile
+        mbar_wait_parked(&tfull_bar[buf], use & 1);
         tc_fence_after();
         const uint32_t t_row = tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(buf * ACC_STRIDE);
         uint32_t v0[32], v1[32], v2[32];                      // 16 used
@@ -314,15 +277,13 @@ deconv_strip_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
           __nv_bfloat162 h2 = __floats2bfloat162_rn(sv[0], sv[1]);
           packed[c / 2] = is_pixel ? *reinterpret_cast<uint32_t*>(&h2) : 0u;
         }
-        const int row_local = STRIP_SEG * lg + lane;
-        const int jch = cc >> 3;                              // 16-byte chunk of this thread's first 8 channels
         if constexpr (!LAST) {
           if (issuer) tma_store_wait_read();                  // the previous tile's store has read the staging tile
           named_barrier_sync(1, 32 * STRIP_EPI_WARPS);
           if (lane < STRIP_SEG) {
-            uint8_t* rowp = xs_base + row_local * 128;
-            *reinterpret_cast<uint4*>(rowp + (((jch) ^ (row_local & 7)) << 4)) = make_uint4(packed[0], packed[1], packed[2], packed[3]);
-            *reinterpret_cast<uint4*>(rowp + (((jch + 1) ^ (row_local & 7)) << 4)) = make_uint4(packed[4], packed[5], packed[6], packed[7]);
+            const uint32_t rowp = xs_u32 + row_local * 128;
+            sts128(rowp + (((jch) ^ (row_local & 7)) << 4), make_uint4(packed[0], packed[1], packed[2], packed[3]));
+            sts128(rowp + (((jch + 1) ^ (row_local & 7)) << 4), make_uint4(packed[4], packed[5], packed[6], packed[7]));
           }
           fence_proxy_async_smem();
           named_barrier_sync(1, 32 * STRIP_EPI_WARPS);
@@ -331,77 +292,203 @@ deconv_strip_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
             tma_store_commit();
           }
         } else {
-          // X tile = A operand of the second GEMM (rows = positions, 128 B = 64 channels, 128-byte swizzle)
-          mbar_wait(&xempty_bar[buf], (use & 1) ^ 1);
+          // X tile (rows = positions, 128 B = 64 channels, 128-byte swizzle); no barrier among the warps: each one
+          // credits the tile's mbarrier when its part is visible to the async proxy
+          mbar_wait_parked(&xempty_bar[buf], (use & 1) ^ 1);
           if (lane < STRIP_SEG) {
-            uint8_t* rowp = xs_base + buf * A_TILE_BYTES + row_local * 128;
-            *reinterpret_cast<uint4*>(rowp + (((jch) ^ (row_local & 7)) << 4)) = make_uint4(packed[0], packed[1], packed[2], packed[3]);
-            *reinterpret_cast<uint4*>(rowp + (((jch + 1) ^ (row_local & 7)) << 4)) = make_uint4(packed[4], packed[5], packed[6], packed[7]);
+            const uint32_t rowp = xs_u32 + buf * A_TILE_BYTES + row_local * 128;
+            sts128(rowp + (((jch) ^ (row_local & 7)) << 4), make_uint4(packed[0], packed[1], packed[2], packed[3]));
+            sts128(rowp + (((jch + 1) ^ (row_local & 7)) << 4), make_uint4(packed[4], packed[5], packed[6], packed[7]));
           }
           fence_proxy_async_smem();
           __syncwarp();
           if (lane == 0) mbar_arrive(&xfull_bar[buf]);
-          // software pipeline: P of the previous tile, then the finished row two tiles back
-          // (history: [2] = tile g-1, [1] = tile g-2, the middle of the col2im; a middle with 1 <= j <= nt-2 has both
-          // neighbours in its own strip)
-          if (g > 0) drain_p(g - 1);
-          named_barrier_sync(1, 32 * STRIP_EPI_WARPS);
-          if (g > 1) col2im(g);
-          named_barrier_sync(1, 32 * STRIP_EPI_WARPS);
-          hj[0] = hj[1]; hnt[0] = hnt[1]; ht[0] = ht[1]; hc0[0] = hc0[1];
-          hj[1] = hj[2]; hnt[1] = hnt[2]; ht[1] = ht[2]; hc0[1] = hc0[2];
-          hj[2] = j; hnt[2] = k.nt; ht[2] = tall; hc0[2] = k.c0;
         }
       }
     }
     if constexpr (!LAST) {
       if (issuer) tma_store_wait_read();
-    } else if (g > 0) {
-      drain_p(g - 1);
-      named_barrier_sync(1, 32 * STRIP_EPI_WARPS);
-      if (g > 1) col2im(g);
+    }
+  } else if (LAST && warp < 2 + STRIP_EPI_WARPS + STRIP_TAIL_WARPS) {
+    // ===== tail warps: P(g) = X(g) * Wall out of TMEM into a ring of three shared-memory tiles, then the finished
+    // projection row of tile g-1:  out[x][c] = act( sum_{dy,dx} P(g-2+dy)[x+dx-1][(dy*3+dx)*cout3 + c] ) =====
+    const int lg = warp & 3;
+    const int tt = threadIdx.x - 32 * (2 + STRIP_EPI_WARPS);  // 0 .. 127
+    int hj = -1, hnt = 0, ht = 0, hc0 = 0;                    // the previous tile (the middle of the col2im)
+    uint32_t g = 0;
+    for (int s = blockIdx.x; s < p.total_strips; s += gridDim.x) {
+      const StripWalk k = strip_walk<LAST>(p, s);
+      for (int j = 0; j < k.nt; ++j, ++g) {
+        const uint32_t b = g & 1, use = g >> 1;
+        mbar_wait_parked(&pfull_bar[b], use & 1);
+        tc_fence_after();
+        uint32_t v[32];
+        tmem_ld32(tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(b * ACC_STRIDE + PACC_OFF), v);
+        tmem_ld_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&pempty_bar[b]);
+        float* dst = ps_base + (g % STRIP_P_SLOTS) * (128 * STRIP_PS) + (lg * 32 + lane) * STRIP_PS;
+#pragma unroll
+        for (int q = 0; q < 27; ++q) dst[q] = __uint_as_float(v[q]);
+        named_barrier_sync(2, 32 * STRIP_TAIL_WARPS);         // P(g) complete in shared memory
+        if (hj >= 1 && hj <= hnt - 2) {                       // top and bottom tiles of a strip are halo only
+          const int y = ht % (p.h + 1), item = ht / (p.h + 1);
+          const int xs = hc0 == 0 ? 0 : hc0 + 1;
+          const int xe = min(hc0 + STRIP_POS - 1, p.w);
+          if (y < p.h) {
+            const float* p0 = ps_base + ((g + 1) % STRIP_P_SLOTS) * (128 * STRIP_PS);   // P(g-2): (g-2) % 3 == (g+1) % 3
+            const float* p1 = ps_base + ((g + 2) % STRIP_P_SLOTS) * (128 * STRIP_PS);   // P(g-1)
+            const float* p2 = ps_base + (g % STRIP_P_SLOTS) * (128 * STRIP_PS);         // P(g)
+            float* orow = p.out + (((size_t)item * p.h + y) * p.w) * p.cout3;
+            for (int x = xs + tt; x < xe; x += 32 * STRIP_TAIL_WARPS) {
+              const int i = x - hc0;                          // position inside the tile; i-1 = -1 only at x = 0 (zero pad)
+              float acc[3] = {0.f, 0.f, 0.f};
+#pragma unroll
+              for (int dy = 0; dy < 3; ++dy) {
+                const float* ps = dy == 0 ? p0 : (dy == 1 ? p1 : p2);
+#pragma unroll
+                for (int dx = 0; dx < 3; ++dx) {
+                  const int ii = i + dx - 1;
+                  if (ii >= 0) {
+#pragma unroll
+                    for (int c = 0; c < 3; ++c)
+                      if (c < p.cout3) acc[c] += ps[ii * STRIP_PS + (dy * 3 + dx) * p.cout3 + c];
+                  }
+                }
+              }
+#pragma unroll
+              for (int c = 0; c < 3; ++c)
+                if (c < p.cout3) orow[(size_t)x * p.cout3 + c] = p.relu_last ? fmaxf(acc[c], 0.f) : acc[c];
+            }
+          }
+        }
+        named_barrier_sync(2, 32 * STRIP_TAIL_WARPS);         // the slot of P(g-2) may be overwritten by P(g+1)
+        hj = j; hnt = k.nt; ht = k.tfirst + j; hc0 = k.c0;
+      }
     }
   } else if (UNPOOL) {
-    // ===== unpool producers (warps 18-21): one input row of the strip = 128 A rows x 8 chunks of 8 channels.
-    // A row holds position x = c0 - 1 + 30*seg + l of tall row tin; its value is the pooled pixel (y/2, x/2) where the
-    // switch names this corner of the 2x2 quad, zero elsewhere (DPooling.down) =====
-    const int pt = threadIdx.x - 32 * (2 + STRIP_EPI_WARPS);  // 0 .. 127
-    const int chunk = pt & 7;
+    // ===== unpool producers: one input row of the strip = positions x = c0-1 .. c0+120 of tall row tin, as 128 A rows
+    // (four 32-row segments 30 positions apart).  A position holds the pooled pixel (y/2, x/2) where the switch names
+    // this corner of the 2x2 quad and zero elsewhere (DPooling.down).  A thread owns one 8-channel chunk of four pooled
+    // pixels; the pooled row serves two input rows (y even / odd) and the next one is prefetched into registers while
+    // the current one is expanded.  The expansion is a table lookup: four switch bytes (two bits each) index a
+    // 256-entry table per corner that holds the four 16-bit lane masks (measured: with the masks computed by byte
+    // compares the four producer warps needed 570 instructions per row and paced the whole kernel) =====
+    const int pt = threadIdx.x - 32 * (2 + STRIP_EPI_WARPS + (LAST ? STRIP_TAIL_WARPS : 0));  // 0 .. 127
+    const int chunk = pt & 7, pp = pt >> 3;
     const int pwp = p.pw + 1, prp = (p.ph + 1) * pwp;
+    for (int e = pt; e < 4 * 256; e += 32 * STRIP_PROD_WARPS) {
+      const uint32_t qc = (uint32_t)e >> 8, idx = (uint32_t)e & 255u;
+      uint32_t m[4];
+#pragma unroll
+      for (int b4 = 0; b4 < 4; ++b4) m[b4] = (((idx >> (2 * b4)) & 3u) == qc) ? 0xFFFFu : 0u;
+      lut[e] = make_uint2(m[0] | (m[1] << 16), m[2] | (m[3] << 16));
+    }
+    named_barrier_sync(3, 32 * STRIP_PROD_WARPS);
+    const uint32_t lut_u32 = smem_u32(lut), in_ring_u32 = smem_u32(in_ring);
     griddep_wait();
+    uint4 pv[4], npv[4];
+    uint32_t si[4], nsi[4];                                   // per pooled pixel: table index of channels 0-3 | 4-7 << 8
+    int curid = -1, nid = -1;                                 // pooled row (item * ph + py) the registers hold / will hold
+    auto load_row = [&](int item, int py, int px0, uint4 (&dv)[4], uint32_t (&ds)[4]) {
+      const __nv_bfloat16* prow = p.pooled + ((size_t)item * prp + (size_t)py * pwp) * 64 + chunk * 8;
+      const uint8_t* srow = p.sw + ((size_t)(item % p.Bsw) * p.ph + py) * p.pw * p.C + chunk * 8;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int px = px0 + pp + 16 * q;
+        if (px >= 0 && px < p.pw) {
+          dv[q] = __ldg(reinterpret_cast<const uint4*>(prow + (size_t)px * 64));
+          const uint2 s2 = __ldg(reinterpret_cast<const uint2*>(srow + (size_t)px * p.C));
+          // bytes b0..b3 in 0..3 -> b0 | b1 << 2 | b2 << 4 | b3 << 6 (the products of the other byte pairs fall below bit 24 or overflow)
+          ds[q] = ((s2.x * 0x01041040u) >> 24) | (((s2.y * 0x01041040u) >> 24) << 8);
+        } else {
+          dv[q] = make_uint4(0u, 0u, 0u, 0u);
+          ds[q] = 0u;
+        }
+      }
+    };
     uint32_t gi = 0;
     for (int s = blockIdx.x; s < p.total_strips; s += gridDim.x) {
       const StripWalk k = strip_walk<LAST>(p, s);
-      for (int i = 0; i < k.nt + 2; ++i, ++gi) {
-        const uint32_t slot = gi % STRIP_IN_SLOTS, use = gi / STRIP_IN_SLOTS;
-        const int tin = k.tfirst - 1 + i;
-        const bool row_ok = tin >= 0 && tin < p.T && (tin % (p.h + 1)) < p.h;
-        const int y = row_ok ? tin % (p.h + 1) : 0, item = row_ok ? tin / (p.h + 1) : 0;
-        const __nv_bfloat16* prow = p.pooled + ((size_t)item * prp + (size_t)(y >> 1) * pwp) * 64 + chunk * 8;
-        const uint8_t* srow = p.sw + ((size_t)(item % p.Bsw) * p.ph + (y >> 1)) * p.pw * p.C + chunk * 8;
-        const uint32_t qy = (uint32_t)(y & 1) * 2u;
-        mbar_wait(&in_empty[slot], (use & 1) ^ 1);
-        uint8_t* dst = in_ring + slot * A_TILE_BYTES;
-#pragma unroll 4
-        for (int jj = 0; jj < 8; ++jj) {
-          const int rr = (pt >> 3) + 16 * jj;                 // A row 0 .. 127
-          const int x = k.c0 - 1 + STRIP_SEG * (rr >> 5) + (rr & 31);
-          uint4 val = make_uint4(0u, 0u, 0u, 0u);
-          if (row_ok && x >= 0 && x < p.w) {
-            const uint4 pv = __ldg(reinterpret_cast<const uint4*>(prow + (size_t)(x >> 1) * 64));
-            const uint2 sv = __ldg(reinterpret_cast<const uint2*>(srow + (size_t)(x >> 1) * p.C));
-            const uint32_t want = (qy + (uint32_t)(x & 1)) * 0x01010101u;
-            const uint32_t m0 = __vcmpeq4(sv.x, want), m1 = __vcmpeq4(sv.y, want);   // 0xFF per matching switch byte
-            val.x = pv.x & __byte_perm(m0, 0, 0x1100);
-            val.y = pv.y & __byte_perm(m0, 0, 0x3322);
-            val.z = pv.z & __byte_perm(m1, 0, 0x1100);
-            val.w = pv.w & __byte_perm(m1, 0, 0x3322);
+      const int px0 = (k.c0 - 1) >> 1;
+      // byte offsets inside the A tile of this thread's eight positions (pooled pixel q, corner column xb): the row of
+      // its segment, and for the two positions that two segments share also the row in the segment before; 0xFFFF = none
+      uint32_t offs[8];
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        const int xr = 2 * (px0 + pp + 16 * (e >> 1)) + (e & 1) - (k.c0 - 1);      // 0 .. 121 are positions of the tile
+        uint32_t o1 = 0xFFFFu, o2 = 0xFFFFu;
+        if (xr >= 0 && xr <= 121) {
+          const int seg = min(3, xr / STRIP_SEG), l = xr - STRIP_SEG * seg;
+          int rr = 32 * seg + l;
+          o1 = (uint32_t)(rr * 128 + ((chunk ^ (rr & 7)) << 4));
+          if (seg > 0 && l < 2) {
+            rr = 32 * (seg - 1) + l + STRIP_SEG;
+            o2 = (uint32_t)(rr * 128 + ((chunk ^ (rr & 7)) << 4));
           }
-          *reinterpret_cast<uint4*>(dst + rr * 128 + ((chunk ^ (rr & 7)) << 4)) = val;
+        }
+        offs[e] = o1 | (o2 << 16);
+      }
+      curid = nid = -1;                                       // the cached pixels belong to the previous strip's column block
+      // (item, y) of the input row, kept incrementally: no division per row.  Rows above the tensor count as pad rows.
+      int tin = k.tfirst - 1;
+      int item = tin >= 0 ? tin / (p.h + 1) : 0, y = tin >= 0 ? tin % (p.h + 1) : p.h;
+      for (int i = 0; i < k.nt + 2; ++i, ++gi, ++tin) {
+        const uint32_t slot = gi % STRIP_IN_SLOTS, use = gi / STRIP_IN_SLOTS;
+        const bool live = tin >= 0 && tin < p.T && y < p.h;   // otherwise a zero row (pad row, or outside the tensor)
+        const int key = live ? 0 : -1;
+        if (live) {
+          const int id = item * p.ph + (y >> 1);
+          if (id != curid) {
+            if (id == nid) {
+#pragma unroll
+              for (int q = 0; q < 4; ++q) { pv[q] = npv[q]; si[q] = nsi[q]; }
+            } else {
+              load_row(item, y >> 1, px0, pv, si);
+            }
+            curid = id;
+          }
+        }
+        // the next pooled row of this item, wanted two input rows from now at the latest; issued AFTER this row's
+        // proxy fence (below): the fence is a MEMBAR that would wait for loads in flight
+        const int py2 = (y >> 1) + 1;
+        const bool want_next = live && py2 < p.ph && curid + 1 != nid && tin + 2 - (y & 1) < p.T && i + 2 - (y & 1) < k.nt + 2;
+        const int item_now = item;
+        const uint32_t yodd = (uint32_t)(y & 1);
+        if (tin < 0) y = (tin == -1) ? 0 : p.h;              // state of the NEXT row; rows above the tensor are pad rows
+        else if (++y > p.h) { y = 0; ++item; }
+        mbar_wait_parked(&in_empty[slot], (use & 1) ^ 1);
+        const uint32_t dst = in_ring_u32 + slot * A_TILE_BYTES;
+        if (key >= 0) {
+          const uint32_t lq = lut_u32 + yodd * 4096u;                                  // corners (y & 1) * 2 + {0, 1}
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            const uint32_t o1 = offs[e] & 0xFFFFu, o2 = offs[e] >> 16;
+            if (o1 != 0xFFFFu) {
+              const uint32_t le = lq + (e & 1) * 2048u;
+              const uint2 ma = lds64(le + (si[e >> 1] & 255u) * 8u), mb = lds64(le + (si[e >> 1] >> 8) * 8u);
+              const uint4 val = make_uint4(pv[e >> 1].x & ma.x, pv[e >> 1].y & ma.y, pv[e >> 1].z & mb.x, pv[e >> 1].w & mb.y);
+              sts128(dst + o1, val);
+              if (o2 != 0xFFFFu) sts128(dst + o2, val);
+            }
+          }
+        } else {
+          const uint4 zero = make_uint4(0u, 0u, 0u, 0u);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            const uint32_t o1 = offs[e] & 0xFFFFu, o2 = offs[e] >> 16;
+            if (o1 != 0xFFFFu) sts128(dst + o1, zero);
+            if (o2 != 0xFFFFu) sts128(dst + o2, zero);
+          }
         }
         fence_proxy_async_smem();                             // the MMA reads the tile through the async proxy
         __syncwarp();
         if (lane == 0) mbar_arrive(&in_full[slot]);
+        if (want_next) {
+          load_row(item_now, py2, px0, npv, nsi);
+          nid = curid + 1;
+        }
       }
     }
   }
