@@ -308,6 +308,7 @@ int forward_impl(dcv_ctx* ctx, const float* img, bool on_device, int B, int H, i
   TRY(ctx->input.ensure(ctx, n_in * sizeof(float)));
   CU(ctx, cudaMemcpyAsync(ctx->input.p, img, n_in * sizeof(float),
                           on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, ctx->stream));
+  if (!on_device) CU(ctx, cudaEventRecord(ctx->ev_ready[0], ctx->stream));    // the host image may be released after this point
   ctx->in_B = B; ctx->in_H = H; ctx->in_W = W; ctx->in_C = C;
   const float* cur = (const float*)ctx->input.p;
   int cb = B, ch = H, cw = W, cc = C;
@@ -403,7 +404,10 @@ extern "C" int dcv_set_fp32_mode(dcv_ctx* ctx, int mode) {
 extern "C" int dcv_forward(dcv_ctx* ctx, const float* img, int B, int H, int W, int upto) {
   ENTER(ctx);
   TRY(forward_impl(ctx, img, false, B, H, W, upto));
-  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  // The borrowed host image is only needed until its copy has finished; the tape's kernels stay queued on the context's
+  // stream, where every later call (dcv_project, dcv_read_activation, ...) is ordered behind them.  Draining the stream
+  // here cost the end-to-end step ~0.5 ms of idle GPU per request.
+  CU(ctx, cudaEventSynchronize(ctx->ev_ready[0]));
   return 0;
 }
 

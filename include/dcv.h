@@ -119,7 +119,9 @@ DCV_API int dcv_net_num_layers(const dcv_ctx* ctx);
 /* ---- forward tape: replaces the forward pass of visualize_all_layers (deepdream.py:426-428), i.e.
  * DConvolution2D.up (:91-100), DActivation.up (:238-248) and DPooling.up (:129-139,152-188).
  * Runs layers 0..upto_layer on a batch of B images (B,H,W,C0) and keeps every layer's output (and
- * every pool's switches) on the device until the next dcv_forward. ---------------------------- */
+ * every pool's switches) on the device until the next dcv_forward.
+ * dcv_forward returns as soon as the host image has been copied (it may then be reused); the tape's kernels are queued on
+ * the context's stream and every later call on the context is ordered behind them (a kernel error surfaces there). */
 DCV_API int dcv_forward(dcv_ctx* ctx, const float* img_nhwc, int B, int H, int W, int upto_layer);
 /* Arithmetic of the forward convs (no counterpart in the reference).  1 (default): tcgen05 with both operands
  * split into three bf16 planes and the six significant cross products accumulated in fp32 (x*w = hh + hm + mh + hl
