@@ -100,6 +100,15 @@ def load():
     global _LIB
     if _LIB is not None:
         return _LIB
+    override = os.environ.get("DCV_LIB_PATH")           # A/B measurements of differently compiled builds (profiles/)
+    if override:
+        lib = ctypes.CDLL(override)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(lib, name)
+            fn.restype = res
+            fn.argtypes = args
+        _LIB = lib
+        return lib
     # build() returns at once when the stored source hash matches, so a library left behind by an older
     # checkout of csrc/ is never loaded silently; without nvcc a stale or missing library is an error
     try:

@@ -17,10 +17,12 @@
 // A tiles: tile t multiplies rows t-1, t, t+1 (dy = -1, 0, +1) and only row t+1 is new - one 16 KB A tile per tile
 // instead of three.  Strips cost two extra input rows (and, with LAST, two extra tiles) at their top and bottom.
 //
-// Roles: warp 0 TMA (weights; input rows unless UNPOOL), warp 1 MMA issue, warps 2-17 conv epilogue (TMEM lane quarter x
-// 16-column group), then four "tail" warps (LAST: P tiles out of TMEM, col2im, fp32 stores) and four unpool producer warps
-// (UNPOOL).  Every stage hands over through mbarriers only; measured with the col2im inside the conv epilogue's
-// lock-step (two 512-thread barriers per tile) the fused kernel was no faster than the two kernels it replaces.
+// Roles: warp 0 TMA (weights; input rows unless UNPOOL), warp 1 MMA issue, then 8 conv epilogue warps (TMEM lane quarter
+// x 32 output channels, two 16-channel passes), four "tail" warps (LAST: P tiles out of TMEM, col2im, fp32 stores) and
+// eight unpool producer warps (UNPOOL).  Every stage hands over through mbarriers only; measured with the col2im inside
+// the conv epilogue's lock-step (two 512-thread barriers per tile) the fused kernel was no faster than the two kernels it
+// replaces.  Warp split measured on the 512-projection step (epilogue / producer warps): 16/4 12.1 ms, 16/8 12.0, 8/4
+// 11.9, 8/16 11.9, 4/16 11.7, 8/8 and 4/8 11.3 (profiles/build_variants.sh): the producers need the issue slots.
 #pragma once
 #include "tc_kernel.cuh"
 
@@ -32,8 +34,17 @@ constexpr int STRIP_SEG = 30;                // output positions per lane quarte
 constexpr int STRIP_POS = 120;               // positions per tile
 constexpr int STRIP_CB = 118;                // column-block pitch (LAST loses one position at each end of a tile)
 constexpr int STRIP_IN_SLOTS = 4;
-constexpr int STRIP_EPI_WARPS = 16;
-constexpr int STRIP_PROD_WARPS = 4;
+#ifndef STRIP_EPI_WARPS_CFG
+#define STRIP_EPI_WARPS_CFG 8
+#endif
+#ifndef STRIP_PROD_WARPS_CFG
+#define STRIP_PROD_WARPS_CFG 8
+#endif
+constexpr int STRIP_EPI_WARPS = STRIP_EPI_WARPS_CFG;    // 16: one 16-channel group per warp; 8: two groups per warp, one after the other
+constexpr int STRIP_EPI_PASSES = 16 / STRIP_EPI_WARPS;  // 16-channel groups per epilogue warp
+constexpr int STRIP_PROD_WARPS = STRIP_PROD_WARPS_CFG;  // 4: four pooled pixels per thread; 8: two
+constexpr int STRIP_NPX = 16 / STRIP_PROD_WARPS;        // pooled pixels per producer thread
+constexpr int STRIP_PXSTEP = 4 * STRIP_PROD_WARPS;      // distance between a thread's pooled pixels
 constexpr int STRIP_W_BYTES = 3 * STRIP_N * 128;        // resident conv weights: [dy][192][64] bf16
 constexpr int STRIP_WL_BYTES = 32 * 128;                // resident all-tap weights of the last layer: [32][64] bf16
 constexpr int STRIP_PS = 29;                            // P row pitch in floats (27 used, odd: conflict-free)
@@ -235,7 +246,7 @@ deconv_strip_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     // ===== conv epilogue warps: accumulator -> dx combination (lane shuffles) -> ReLU -> bf16 tile in shared memory;
     // !LAST: one TMA store per tile; LAST: the tile is the A operand of the second GEMM =====
     const int lg = warp & 3;                                  // TMEM lane quarter this warp may read
-    const int cc = ((warp - 2) >> 2) * 16;                    // its 16 output channels
+    const int cc = ((warp - 2) >> 2) * 16 * STRIP_EPI_PASSES; // its first output channel (16 per pass)
     const float relu_lo = p.relu ? 0.f : -INFINITY;
     const bool issuer = (warp == 2) && (lane == 0);
     const int row_local = STRIP_SEG * lg + lane;
@@ -256,34 +267,43 @@ deconv_strip_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         mbar_wait_parked(&tfull_bar[buf], use & 1);
         tc_fence_after();
         const uint32_t t_row = tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(buf * ACC_STRIDE);
-        uint32_t v0[32], v1[32], v2[32];                      // 16 used
-        tmem_ld16(t_row + (uint32_t)cc, v0);
-        tmem_ld16(t_row + (uint32_t)(64 + cc), v1);
-        tmem_ld16(t_row + (uint32_t)(128 + cc), v2);
-        tmem_ld_wait();
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&tempty_bar[buf]);
-        uint32_t packed[8];
+        uint32_t packed[STRIP_EPI_PASSES][8];
 #pragma unroll
-        for (int c = 0; c < 16; c += 2) {
-          float sv[2];
-#pragma unroll
-          for (int e = 0; e < 2; ++e) {
-            float t = __uint_as_float(v0[c + e]);
-            t += __shfl_down_sync(0xffffffffu, __uint_as_float(v1[c + e]), 1) + __shfl_down_sync(0xffffffffu, __uint_as_float(v2[c + e]), 2);
-            sv[e] = fmaxf(t, relu_lo);
+        for (int ps = 0; ps < STRIP_EPI_PASSES; ++ps) {
+          const int cp = cc + 16 * ps;
+          uint32_t v0[32], v1[32], v2[32];                    // 16 used
+          tmem_ld16(t_row + (uint32_t)cp, v0);
+          tmem_ld16(t_row + (uint32_t)(64 + cp), v1);
+          tmem_ld16(t_row + (uint32_t)(128 + cp), v2);
+          tmem_ld_wait();
+          if (ps == STRIP_EPI_PASSES - 1) {                   // the accumulator is in registers: hand the TMEM buffer back
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tempty_bar[buf]);
           }
-          __nv_bfloat162 h2 = __floats2bfloat162_rn(sv[0], sv[1]);
-          packed[c / 2] = is_pixel ? *reinterpret_cast<uint32_t*>(&h2) : 0u;
+#pragma unroll
+          for (int c = 0; c < 16; c += 2) {
+            float sv[2];
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+              float t = __uint_as_float(v0[c + e]);
+              t += __shfl_down_sync(0xffffffffu, __uint_as_float(v1[c + e]), 1) + __shfl_down_sync(0xffffffffu, __uint_as_float(v2[c + e]), 2);
+              sv[e] = fmaxf(t, relu_lo);
+            }
+            __nv_bfloat162 h2 = __floats2bfloat162_rn(sv[0], sv[1]);
+            packed[ps][c / 2] = is_pixel ? *reinterpret_cast<uint32_t*>(&h2) : 0u;
+          }
         }
         if constexpr (!LAST) {
           if (issuer) tma_store_wait_read();                  // the previous tile's store has read the staging tile
           named_barrier_sync(1, 32 * STRIP_EPI_WARPS);
           if (lane < STRIP_SEG) {
             const uint32_t rowp = xs_u32 + row_local * 128;
-            sts128(rowp + (((jch) ^ (row_local & 7)) << 4), make_uint4(packed[0], packed[1], packed[2], packed[3]));
-            sts128(rowp + (((jch + 1) ^ (row_local & 7)) << 4), make_uint4(packed[4], packed[5], packed[6], packed[7]));
+#pragma unroll
+            for (int ps = 0; ps < STRIP_EPI_PASSES; ++ps) {
+              sts128(rowp + (((jch + 2 * ps) ^ (row_local & 7)) << 4), make_uint4(packed[ps][0], packed[ps][1], packed[ps][2], packed[ps][3]));
+              sts128(rowp + (((jch + 2 * ps + 1) ^ (row_local & 7)) << 4), make_uint4(packed[ps][4], packed[ps][5], packed[ps][6], packed[ps][7]));
+            }
           }
           fence_proxy_async_smem();
           named_barrier_sync(1, 32 * STRIP_EPI_WARPS);
@@ -297,8 +317,11 @@ deconv_strip_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
           mbar_wait_parked(&xempty_bar[buf], (use & 1) ^ 1);
           if (lane < STRIP_SEG) {
             const uint32_t rowp = xs_u32 + buf * A_TILE_BYTES + row_local * 128;
-            sts128(rowp + (((jch) ^ (row_local & 7)) << 4), make_uint4(packed[0], packed[1], packed[2], packed[3]));
-            sts128(rowp + (((jch + 1) ^ (row_local & 7)) << 4), make_uint4(packed[4], packed[5], packed[6], packed[7]));
+#pragma unroll
+            for (int ps = 0; ps < STRIP_EPI_PASSES; ++ps) {
+              sts128(rowp + (((jch + 2 * ps) ^ (row_local & 7)) << 4), make_uint4(packed[ps][0], packed[ps][1], packed[ps][2], packed[ps][3]));
+              sts128(rowp + (((jch + 2 * ps + 1) ^ (row_local & 7)) << 4), make_uint4(packed[ps][4], packed[ps][5], packed[ps][6], packed[ps][7]));
+            }
           }
           fence_proxy_async_smem();
           __syncwarp();
@@ -388,15 +411,15 @@ deconv_strip_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     named_barrier_sync(3, 32 * STRIP_PROD_WARPS);
     const uint32_t lut_u32 = smem_u32(lut), in_ring_u32 = smem_u32(in_ring);
     griddep_wait();
-    uint4 pv[4], npv[4];
-    uint32_t si[4], nsi[4];                                   // per pooled pixel: table index of channels 0-3 | 4-7 << 8
+    uint4 pv[STRIP_NPX], npv[STRIP_NPX];
+    uint32_t si[STRIP_NPX], nsi[STRIP_NPX];                                   // per pooled pixel: table index of channels 0-3 | 4-7 << 8
     int curid = -1, nid = -1;                                 // pooled row (item * ph + py) the registers hold / will hold
-    auto load_row = [&](int item, int py, int px0, uint4 (&dv)[4], uint32_t (&ds)[4]) {
+    auto load_row = [&](int item, int py, int px0, uint4 (&dv)[STRIP_NPX], uint32_t (&ds)[STRIP_NPX]) {
       const __nv_bfloat16* prow = p.pooled + ((size_t)item * prp + (size_t)py * pwp) * 64 + chunk * 8;
       const uint8_t* srow = p.sw + ((size_t)(item % p.Bsw) * p.ph + py) * p.pw * p.C + chunk * 8;
 #pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        const int px = px0 + pp + 16 * q;
+      for (int q = 0; q < STRIP_NPX; ++q) {
+        const int px = px0 + pp + STRIP_PXSTEP * q;
         if (px >= 0 && px < p.pw) {
           dv[q] = __ldg(reinterpret_cast<const uint4*>(prow + (size_t)px * 64));
           const uint2 s2 = __ldg(reinterpret_cast<const uint2*>(srow + (size_t)px * p.C));
@@ -414,10 +437,10 @@ deconv_strip_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
       const int px0 = (k.c0 - 1) >> 1;
       // byte offsets inside the A tile of this thread's eight positions (pooled pixel q, corner column xb): the row of
       // its segment, and for the two positions that two segments share also the row in the segment before; 0xFFFF = none
-      uint32_t offs[8];
+      uint32_t offs[2 * STRIP_NPX];
 #pragma unroll
-      for (int e = 0; e < 8; ++e) {
-        const int xr = 2 * (px0 + pp + 16 * (e >> 1)) + (e & 1) - (k.c0 - 1);      // 0 .. 121 are positions of the tile
+      for (int e = 0; e < 2 * STRIP_NPX; ++e) {
+        const int xr = 2 * (px0 + pp + STRIP_PXSTEP * (e >> 1)) + (e & 1) - (k.c0 - 1);      // 0 .. 121 are positions of the tile
         uint32_t o1 = 0xFFFFu, o2 = 0xFFFFu;
         if (xr >= 0 && xr <= 121) {
           const int seg = min(3, xr / STRIP_SEG), l = xr - STRIP_SEG * seg;
@@ -443,7 +466,7 @@ deconv_strip_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
           if (id != curid) {
             if (id == nid) {
 #pragma unroll
-              for (int q = 0; q < 4; ++q) { pv[q] = npv[q]; si[q] = nsi[q]; }
+              for (int q = 0; q < STRIP_NPX; ++q) { pv[q] = npv[q]; si[q] = nsi[q]; }
             } else {
               load_row(item, y >> 1, px0, pv, si);
             }
@@ -463,7 +486,7 @@ deconv_strip_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         if (key >= 0) {
           const uint32_t lq = lut_u32 + yodd * 4096u;                                  // corners (y & 1) * 2 + {0, 1}
 #pragma unroll
-          for (int e = 0; e < 8; ++e) {
+          for (int e = 0; e < 2 * STRIP_NPX; ++e) {
             const uint32_t o1 = offs[e] & 0xFFFFu, o2 = offs[e] >> 16;
             if (o1 != 0xFFFFu) {
               const uint32_t le = lq + (e & 1) * 2048u;
@@ -476,7 +499,7 @@ deconv_strip_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         } else {
           const uint4 zero = make_uint4(0u, 0u, 0u, 0u);
 #pragma unroll
-          for (int e = 0; e < 8; ++e) {
+          for (int e = 0; e < 2 * STRIP_NPX; ++e) {
             const uint32_t o1 = offs[e] & 0xFFFFu, o2 = offs[e] >> 16;
             if (o1 != 0xFFFFu) sts128(dst + o1, zero);
             if (o2 != 0xFFFFu) sts128(dst + o2, zero);
