@@ -133,6 +133,7 @@ extern "C" void dcv_destroy(dcv_ctx* ctx) {
   for (auto& b : ctx->ws) b.release();
   ctx->feat_dev.release();
   ctx->scratch.release();
+  ctx->amax.release();
   ctx->stage.release();
   for (auto& b : ctx->dream) b.release();
   ctx->jit_dev.release();

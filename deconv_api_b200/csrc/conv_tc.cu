@@ -25,6 +25,8 @@
 #include "tc_strip.cuh"
 #include "tc_exact.cuh"
 
+#include <cuda_fp16.h>
+
 #include <algorithm>
 #include <cstdlib>
 
@@ -125,6 +127,145 @@ __global__ void split3_pad_kernel(const float* __restrict__ x, int P, int h, int
     *reinterpret_cast<uint4*>(o) = *reinterpret_cast<const uint4*>(hh);
     *reinterpret_cast<uint4*>(o + c_pad) = *reinterpret_cast<const uint4*>(mm);
     *reinterpret_cast<uint4*>(o + 2 * c_pad) = *reinterpret_cast<const uint4*>(ll);
+  }
+}
+
+// ---- fp16 two-plane scheme (tc_exact.cuh, SCHEME 1) ------------------------------------------------------------------
+// Largest |x| of a tensor as a float bit pattern (non-negative floats order like unsigned integers): one atomicMax
+// per block; *out must be zero before the launch.
+__global__ void __launch_bounds__(256) absmax_kernel(const float* __restrict__ x, size_t n, uint32_t* __restrict__ out) {
+  uint32_t m = 0;
+  const size_t n4 = n / 4, stride = (size_t)gridDim.x * blockDim.x;
+  const uint4* x4 = reinterpret_cast<const uint4*>(x);
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
+    const uint4 a = __ldg(x4 + i);
+    m = max(max(m, a.x & 0x7FFFFFFFu), max(max(a.y & 0x7FFFFFFFu, a.z & 0x7FFFFFFFu), a.w & 0x7FFFFFFFu));
+  }
+  if (blockIdx.x == 0 && threadIdx.x < (n & 3)) m = max(m, __float_as_uint(x[n4 * 4 + threadIdx.x]) & 0x7FFFFFFFu);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
+  __shared__ uint32_t red[8];
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = m;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int k = 1; k < 8; ++k) m = max(m, red[k]);
+    if (m) atomicMax(out, m);
+  }
+}
+
+// The same per item: `items` consecutive arrays of `len` floats, out[item]; grid (blocks per item, items).  Every
+// projection is scaled by ITS OWN maximum: the items of a batch are independent and can differ by many orders of
+// magnitude (the ten softmax outputs of a `predictions` target span 1e-1 .. 1e-6), and a result that depends only on
+// the item does not change with how the batch is chunked.
+__global__ void __launch_bounds__(256) absmax_items_kernel(const float* __restrict__ x, size_t len, uint32_t* __restrict__ out) {
+  const float* xi = x + (size_t)blockIdx.y * len;
+  uint32_t m = 0;
+  const size_t stride = (size_t)gridDim.x * blockDim.x, i0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if ((len & 3) == 0) {                               // every item starts 16-byte aligned
+    const uint4* x4 = reinterpret_cast<const uint4*>(xi);
+    const size_t n4 = len / 4;
+    size_t i = i0;
+    for (; i + stride < n4; i += 2 * stride) {
+      const uint4 a = __ldg(x4 + i), b = __ldg(x4 + i + stride);
+      m = max(m, max(max(a.x & 0x7FFFFFFFu, a.y & 0x7FFFFFFFu), max(a.z & 0x7FFFFFFFu, a.w & 0x7FFFFFFFu)));
+      m = max(m, max(max(b.x & 0x7FFFFFFFu, b.y & 0x7FFFFFFFu), max(b.z & 0x7FFFFFFFu, b.w & 0x7FFFFFFFu)));
+    }
+    for (; i < n4; i += stride) {
+      const uint4 a = __ldg(x4 + i);
+      m = max(m, max(max(a.x & 0x7FFFFFFFu, a.y & 0x7FFFFFFFu), max(a.z & 0x7FFFFFFFu, a.w & 0x7FFFFFFFu)));
+    }
+  } else {
+    for (size_t i = i0; i < len; i += stride) m = max(m, __float_as_uint(__ldg(xi + i)) & 0x7FFFFFFFu);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
+  __shared__ uint32_t red[8];
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = m;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int k = 1; k < 8; ++k) m = max(m, red[k]);
+    if (m) atomicMax(out + blockIdx.y, m);
+  }
+}
+
+// x*s = hi + lo with two fp16 planes (11 significand bits each; s = power of two that puts the tensor's maximum into
+// [2^13, 2^14)): exact to ~2^-22 relative, or 2^-39 of the maximum for the smallest values (fp16 subnormals).
+__device__ __forceinline__ void split2h(float xs, __half& h, __half& l) {
+  h = __float2half_rn(xs);
+  l = __float2half_rn(xs - __half2float(h));
+}
+
+// fp32 compact (P,h,w,C) -> padded-flat fp16 with TWO planes per row: columns [hi | lo], c_pad each.
+__global__ void split2_pad_kernel(const float* __restrict__ x, int P, int h, int w, int C, int c_pad,
+                                  const uint32_t* __restrict__ amax, __half* __restrict__ out) {
+  const int wp = w + 1, rp = (h + 1) * wp, cg = c_pad / 8;
+  const size_t total = (size_t)P * rp * cg;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int g = (int)(i % cg);
+    const size_t r = i / cg;
+    const int q = (int)(r % rp);
+    const int item = (int)(r / rp);
+    const int y = q / wp, xx = q % wp;
+    float v[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) v[k] = 0.f;
+    if (y < h && xx < w) {
+      const float* src = x + (((size_t)item * h + y) * w + xx) * C + g * 8;
+      if ((C & 3) == 0 && g * 8 + 8 <= C) {
+        const float4 a = __ldg(reinterpret_cast<const float4*>(src)), b = __ldg(reinterpret_cast<const float4*>(src + 4));
+        v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+      } else {
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+          if (g * 8 + k < C) v[k] = __ldg(src + k);
+      }
+    }
+    const float s = pow2_scale_from_amax(__ldg(amax + item));        // this item's own scale
+    __half hh[8], ll[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) split2h(v[k] * s, hh[k], ll[k]);
+    __half* o = out + r * (2 * (size_t)c_pad) + g * 8;
+    *reinterpret_cast<uint4*>(o) = *reinterpret_cast<const uint4*>(hh);
+    *reinterpret_cast<uint4*>(o + c_pad) = *reinterpret_cast<const uint4*>(ll);
+  }
+}
+
+// Weights for the two-plane scheme: w fp32 [9][K][N] -> fp16 [tap][plane (hi,lo)][n_pad][k_pad], scaled like the activations.
+__global__ void pack_weights_2h_kernel(const float* __restrict__ w, int kdim, int ndim, int k_pad, int n_pad,
+                                       const uint32_t* __restrict__ amax, __half* __restrict__ out) {
+  const float s = pow2_scale_from_amax(__ldg(amax));
+  const size_t plane = (size_t)n_pad * k_pad;
+  const size_t total = (size_t)9 * plane;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int k = (int)(i % k_pad);
+    const int n = (int)((i / k_pad) % n_pad);
+    const int t = (int)(i / plane);
+    float v = 0.f;
+    if (k < kdim && n < ndim) v = __ldg(w + ((size_t)t * kdim + k) * ndim + n);
+    __half h, l;
+    split2h(v * s, h, l);
+    const size_t o = ((size_t)t * 2) * plane + (size_t)n * k_pad + k;
+    out[o] = h; out[o + plane] = l;
+  }
+}
+
+// the all-tap weights of a narrow last layer in the same form: out [2][32][k_pad], row = tap*N + c
+__global__ void pack_weights_alltap2h_kernel(const float* __restrict__ wd, int kdim, int ndim, int k_pad,
+                                             const uint32_t* __restrict__ amax, __half* __restrict__ out) {
+  const float s = pow2_scale_from_amax(__ldg(amax));
+  const int total = 32 * k_pad;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int k = i % k_pad, row = i / k_pad;
+    float v = 0.f;
+    if (row < 9 * ndim && k < kdim) {
+      const int t = row / ndim, c = row % ndim;
+      v = __ldg(wd + ((size_t)t * kdim + k) * ndim + c);
+    }
+    __half h, l;
+    split2h(v * s, h, l);
+    out[i] = h; out[total + i] = l;
   }
 }
 
@@ -560,6 +701,9 @@ struct TcConvArgs {
   const TcPrep* prep = nullptr;
   int ntaps = 9;            // 1: un-shifted GEMM (first layer over im2col rows)
   int prof_class = -1;      // profiling class override (default: conv_fwd for nprod 6, conv_tc otherwise)
+  int scheme = 0;           // split-operand mode (nprod 6): 0 = three bf16 planes / six products, 1 = two fp16 planes / three
+  const uint32_t* amax_a = nullptr;
+  const uint32_t* amax_b = nullptr;
 };
 
 static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& a, const __nv_bfloat16* in, int P, int h, int w,
@@ -602,6 +746,11 @@ void tc_free_layer(Layer& l) {
   l.tc.wall3_bf16 = nullptr;
   if (l.tc.wf0_bf16) cudaFree(l.tc.wf0_bf16);
   l.tc.wf0_bf16 = nullptr;
+  if (l.tc.wd2_f16) cudaFree(l.tc.wd2_f16);
+  if (l.tc.wall2_f16) cudaFree(l.tc.wall2_f16);
+  if (l.tc.wd_amax) cudaFree(l.tc.wd_amax);
+  l.tc.wd2_f16 = l.tc.wall2_f16 = nullptr;
+  l.tc.wd_amax = nullptr;
   l.tc.wd_bf16 = l.tc.wf_bf16 = l.tc.wall_bf16 = l.tc.wf3_bf16 = l.tc.wd3_bf16 = nullptr;
 }
 
@@ -695,7 +844,40 @@ size_t tc_split_elems(int h, int w, int c) { return (size_t)(h + 1) * (w + 1) * 
 
 // Backward conv of the fp32 projection mode on the tensor cores, same six-product scheme.  l.wd is the flipped,
 // transposed fp32 kernel [9][cout][cin] = [tap][K][N], i.e. the layout pack_weights_fwd3_kernel expects.
+// DCV_FP32_SCHEME: 1 (default) = two fp16 planes, three products; 0 = three bf16 planes, six products (the forward's scheme)
+static int fp32_scheme() {
+  static const int s = getenv("DCV_FP32_SCHEME") ? atoi(getenv("DCV_FP32_SCHEME")) : 1;
+  return s;
+}
+
+static int tc_prepare_backward_2h(dcv_ctx* ctx, Layer& l) {
+  if (l.tc.wd2_f16) return 0;
+  if (!l.wd) return ctx->fail(DCV_ERR_STATE, "backward weights were not prepared for this layer");
+  const int k_pad = tc_cpad(l.cout), n_pad = tc_cpad(l.cin);
+  const size_t nw = (size_t)9 * l.cin * l.cout;
+  cudaError_t e = cudaMalloc(&l.tc.wd_amax, 256);
+  if (e != cudaSuccess) return ctx->fail(DCV_ERR_NOMEM, "cudaMalloc(weight maximum): %s", cudaGetErrorString(e));
+  cudaMemsetAsync(l.tc.wd_amax, 0, 256, ctx->stream);
+  absmax_kernel<<<grid_for(nw / 4 + 1, 256, 4), 256, 0, ctx->stream>>>(l.wd, nw, l.tc.wd_amax);
+  ctx->launches++;
+  const size_t n = (size_t)9 * 2 * n_pad * k_pad;
+  e = cudaMalloc(&l.tc.wd2_f16, n * sizeof(__half));
+  if (e != cudaSuccess) return ctx->fail(DCV_ERR_NOMEM, "cudaMalloc(two-plane backward weights): %s", cudaGetErrorString(e));
+  pack_weights_2h_kernel<<<grid_for(n / 2, 256), 256, 0, ctx->stream>>>(l.wd, l.cout, l.cin, k_pad, n_pad, l.tc.wd_amax, (__half*)l.tc.wd2_f16);
+  ctx->launches++;
+  if (9 * l.cin <= LAST_N) {
+    e = cudaMalloc(&l.tc.wall2_f16, (size_t)2 * LAST_N * k_pad * sizeof(__half));
+    if (e != cudaSuccess) return ctx->fail(DCV_ERR_NOMEM, "cudaMalloc(two-plane all-tap weights): %s", cudaGetErrorString(e));
+    pack_weights_alltap2h_kernel<<<grid_for((size_t)LAST_N * k_pad, 256), 256, 0, ctx->stream>>>(l.wd, l.cout, l.cin, k_pad, l.tc.wd_amax, (__half*)l.tc.wall2_f16);
+    ctx->launches++;
+  }
+  e = cudaGetLastError();
+  if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "two-plane weight packing: %s", cudaGetErrorString(e));
+  return 0;
+}
+
 int tc_prepare_backward_exact(dcv_ctx* ctx, Layer& l) {
+  if (fp32_scheme() == 1) return tc_prepare_backward_2h(ctx, l);
   if (l.tc.wd3_bf16) return 0;
   if (!l.wd) return ctx->fail(DCV_ERR_STATE, "backward weights were not prepared for this layer");
   const int k_pad = tc_cpad(l.cout), n_pad = tc_cpad(l.cin);
@@ -713,7 +895,68 @@ int tc_prepare_backward_exact(dcv_ctx* ctx, Layer& l) {
   return 0;
 }
 
+// fp16 two-plane form of the backward conv: absmax -> scaled split -> conv_exact_kernel<.., 1> (or the GEMM + col2im last layer)
+static int tc_conv_bwd_2h(dcv_ctx* ctx, const Layer& l, const float* in, int P, int h, int w, float* out, int relu) {
+  if (!l.tc.wd2_f16) return ctx->fail(DCV_ERR_STATE, "two-plane backward weights were not prepared for this layer");
+  const int k_pad = tc_cpad(l.cout), n_pad = tc_cpad(l.cin);
+  const size_t elems = (size_t)P * (h + 1) * (w + 1) * 2 * k_pad;
+  int r = ctx->ws[4].ensure(ctx, elems * sizeof(__half));
+  if (r) return r;
+  r = ctx->amax.ensure(ctx, (size_t)P * sizeof(uint32_t) + 256);
+  if (r) return r;
+  uint32_t* amax = (uint32_t*)ctx->amax.p;
+  const size_t len = (size_t)h * w * l.cout, n_in = (size_t)P * len;
+  {
+    ProfScope ps(ctx, DCV_K_OTHER, 0.0, 8.0 * n_in + 4.0 * P * (h + 1) * (w + 1) * k_pad);
+    cudaMemsetAsync(amax, 0, (size_t)P * sizeof(uint32_t), ctx->stream);
+    const int bpi = (int)std::max<size_t>(1, std::min<size_t>((len + 8191) / 8192, std::max<size_t>(1, (size_t)16 * kNumSMs / P)));
+    absmax_items_kernel<<<dim3(bpi, P), 256, 0, ctx->stream>>>(in, len, amax);
+    const size_t work = (size_t)P * (h + 1) * (w + 1) * (k_pad / 8);
+    split2_pad_kernel<<<grid_for(work, 256), 256, 0, ctx->stream>>>(in, P, h, w, l.cout, k_pad, amax, (__half*)ctx->ws[4].p);
+    ctx->launches += 2;
+  }
+  static const int use_last = getenv("DCV_TC_LAST") ? atoi(getenv("DCV_TC_LAST")) : 1;
+  if (l.tc.wall2_f16 && use_last) {
+    LastParams p = {};
+    p.P = P; p.h = h; p.w = w; p.cout = l.cin; p.k_blocks = k_pad / 64;
+    p.tiles_x = (w + LAST_T - 1) / LAST_T; p.tiles_y = (h + LAST_T - 1) / LAST_T;
+    const long long tt = (long long)P * p.tiles_x * p.tiles_y;
+    if (tt > 0x7FFFFFFFLL || (long long)P * (h + 1) > 0x7FFFFFFFLL) return ctx->fail(DCV_ERR_ARG, "tc_conv: too many tiles");
+    p.total_tiles = (int)tt;
+    p.relu = relu;
+    p.out = out;
+    p.amax_a = amax; p.amax_b = l.tc.wd_amax;
+    CUtensorMap ta, tb;
+    r = make_tmap_patch(ctx, &ta, ctx->ws[4].p, (uint64_t)2 * k_pad, (uint64_t)(w + 1), (uint64_t)P * (h + 1));
+    if (r) return r;
+    r = make_tmap(ctx, &tb, l.tc.wall2_f16, (uint64_t)2 * LAST_N, (uint64_t)k_pad, LAST_N);
+    if (r) return r;
+    const int smem = last_smem_bytes(p.k_blocks, 2);
+    if (smem <= 227 * 1024) {
+      static int smem_set[64] = {};
+      cudaError_t e = cudaSuccess;
+      if (smem_set[ctx->device & 63] < smem) {
+        e = cudaFuncSetAttribute(deconv_last_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+        smem_set[ctx->device & 63] = smem;
+      }
+      ProfScope ps(ctx, DCV_K_CONV_TC, 2.0 * 9 * P * h * w * (double)l.cin * l.cout, 2.0 * P * h * w * (2.0 * l.cout + 2.0 * l.cin));
+      deconv_last_kernel<2><<<std::min(p.total_tiles, ctx->num_sms), LAST_THREADS, smem, ctx->stream>>>(ta, tb, p);
+      ctx->launches++;
+      e = cudaGetLastError();
+      if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "deconv_last_kernel<fp16> launch: %s", cudaGetErrorString(e));
+      return 0;
+    }
+  }
+  TcConvArgs a{l.tc.wd2_f16, k_pad, n_pad, l.cout, l.cin, relu, nullptr, 6};
+  a.prof_class = DCV_K_CONV_TC;
+  a.scheme = 1;
+  a.amax_a = amax; a.amax_b = l.tc.wd_amax;
+  return tc_conv_run(ctx, a, (const __nv_bfloat16*)ctx->ws[4].p, P, h, w, nullptr, out);
+}
+
 int tc_conv_bwd_exact(dcv_ctx* ctx, const Layer& l, const float* in, int P, int h, int w, float* out, int relu) {
+  if (fp32_scheme() == 1) return tc_conv_bwd_2h(ctx, l, in, P, h, w, out, relu);
   if (!l.tc.wd3_bf16) return ctx->fail(DCV_ERR_STATE, "split backward weights were not prepared for this layer");
   const int k_pad = tc_cpad(l.cout), n_pad = tc_cpad(l.cin);
   const size_t elems = (size_t)P * tc_split_elems(h, w, l.cout);
@@ -859,7 +1102,7 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
                        __nv_bfloat16* out_bf16, float* out_f32) {
   const long long rows_ll = (long long)P * (h + 1) * (w + 1);
   if (rows_ll > 0x7FFFFF00LL) return ctx->fail(DCV_ERR_ARG, "tc_conv: %lld padded rows exceed the TMA coordinate range", rows_ll);
-  TcParams p;
+  TcParams p = {};
   p.rows = (int)rows_ll; p.h = h; p.w = w;
   p.k_blocks = l.k_pad / 64;
   p.n_pad = l.n_pad; p.n_real = l.n_real;
@@ -888,10 +1131,12 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
     p.stages = stages;
     p.base_off = 0;
     const int smem = stages * exact_stage_bytes(bn) + 1024 + 256;
+    const int npl = l.scheme == 1 ? 2 : 3;
+    p.amax_a = l.amax_a; p.amax_b = l.amax_b;
     CUtensorMap ta, tb;
-    int r = make_tmap(ctx, &ta, in, (uint64_t)p.rows, (uint64_t)3 * l.k_pad, BAND_ROWS);
+    int r = make_tmap(ctx, &ta, in, (uint64_t)p.rows, (uint64_t)npl * l.k_pad, BAND_ROWS);
     if (r) return r;
-    r = make_tmap(ctx, &tb, l.w, (uint64_t)9 * 3 * l.n_pad, (uint64_t)l.k_pad, (uint32_t)bn);
+    r = make_tmap(ctx, &tb, l.w, (uint64_t)9 * npl * l.n_pad, (uint64_t)l.k_pad, (uint32_t)bn);
     if (r) return r;
     ProfScope ps(ctx, l.prof_class >= 0 ? l.prof_class : DCV_K_CONV_FWD, 2.0 * 9 * P * h * w * (double)l.k_real * l.n_real,
                  2.0 * P * h * w * ((double)l.k_real + 2.0 * l.n_real));
@@ -905,7 +1150,14 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
         if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "cudaFuncSetAttribute(exact kernel): %s", cudaGetErrorString(e)); \
         smem_set[ctx->device & 63] = smem;                                                                         \
       }                                                                                                            \
-      conv_exact_kernel<BN><<<grid, EXACT_THREADS, smem, ctx->stream>>>(ta, tb, p);                                  \
+      static int smem_set1[64] = {};                                                                               \
+      if (l.scheme == 1 && smem_set1[ctx->device & 63] < smem) {                                                   \
+        e = cudaFuncSetAttribute(conv_exact_kernel<BN, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);     \
+        if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "cudaFuncSetAttribute(exact kernel): %s", cudaGetErrorString(e)); \
+        smem_set1[ctx->device & 63] = smem;                                                                        \
+      }                                                                                                            \
+      if (l.scheme == 1) conv_exact_kernel<BN, 1><<<grid, EXACT_THREADS, smem, ctx->stream>>>(ta, tb, p);           \
+      else conv_exact_kernel<BN, 0><<<grid, EXACT_THREADS, smem, ctx->stream>>>(ta, tb, p);                         \
     }
     switch (bn) {
       case 16: EXACT_LAUNCH(16) break;

@@ -22,6 +22,10 @@ struct TcWeights {
   __nv_bfloat16* wd3_bf16 = nullptr;  // backward (flipped, transposed) weights split the same way: [9][3][n_pad][k_pad] (exact projection)
   __nv_bfloat16* wf3_bf16 = nullptr;  // forward weights split into (hi, mid, lo) bf16 planes: [9][3][fn_pad][fk_pad] (exact forward)
   __nv_bfloat16* wall_bf16 = nullptr; // narrow last layer (9*cin <= 32): all taps stacked along N, [32][k_pad]
+  // fp16 two-plane scheme of the DCV_FP32 backward convs (tc_exact.cuh, SCHEME 1); 16-bit storage, fp16 contents
+  __nv_bfloat16* wd2_f16 = nullptr;   // backward weights scaled by a power of two and split into (hi, lo): [9][2][n_pad][k_pad]
+  __nv_bfloat16* wall2_f16 = nullptr; // the same for the all-tap weights of a narrow last layer: [2][32][k_pad]
+  uint32_t* wd_amax = nullptr;        // float bit pattern of the largest |weight| (device scalar)
 };
 
 struct Layer {
@@ -63,6 +67,7 @@ struct dcv_ctx {
   DevBuf ws[6];        // projection workspace: [0],[1] ping-pong tensors, [2],[3] maps, [4],[5] bf16 ping-pong
   DevBuf feat_dev;
   DevBuf scratch;      // reduction partials
+  DevBuf amax;         // fp16 scheme: float bit pattern of the largest |activation| of the tensor being split
   DevBuf stage;        // staging for host-buffer entry points
   // host-output projections: chunks are copied back on a second stream while the next chunk computes
   cudaStream_t copy_stream = nullptr;

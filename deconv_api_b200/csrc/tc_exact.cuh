@@ -26,7 +26,12 @@ __host__ __device__ inline int exact_stage_bytes(int block_n) { return A_BAND_BY
 
 constexpr int EXACT_THREADS = 320;   // TMA warp, MMA warp, 8 accumulate warps (two per TMEM lane quarter, half of the columns each)
 
-template <int BLOCK_N>
+// SCHEME 0: three bf16 planes, six products (hh, hm, mh, hl, lh, mm), ~2^-24: the forward tape.
+// SCHEME 1: two fp16 planes of the operands scaled into fp16's range by a power of two taken from the tensor's largest
+// magnitude (x*s = hi + lo, 11 significand bits each), three products (hh, hl, lh): ~2^-21 per product at HALF the MMA
+// work - the backward convs of the DCV_FP32 chain (measured on the 512-map step against the oracle: see DESIGN.md §4).
+// Everything else is shared: one fresh TMEM slot per stage, fp32 register accumulation, the result rescaled once.
+template <int BLOCK_N, int SCHEME = 0>
 __global__ void __launch_bounds__(EXACT_THREADS, 1)
 conv_exact_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, TcParams p) {
   constexpr int B_TILE_BYTES = BLOCK_N * 128;
@@ -62,7 +67,9 @@ conv_exact_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
 
   const int total_tiles = p.m_tiles * p.n_tiles;
   const int wp = p.w + 1;
-  const int total_st = 3 * 6 * p.k_blocks;            // (dy, product, 64-channel block) stages per tile
+  constexpr int NPROD = SCHEME == 0 ? 6 : 3;
+  constexpr int NPLANE = SCHEME == 0 ? 3 : 2;
+  const int total_st = 3 * NPROD * p.k_blocks;        // (dy, product, 64-channel block) stages per tile
   const int kcols = p.k_blocks * BLOCK_K;             // columns of one operand plane
 
   if (warp == 0) {
@@ -76,9 +83,9 @@ conv_exact_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         for (int st = 0; st < total_st; ++st) {
           const int kc = st % p.k_blocks;
           const int gp = st / p.k_blocks;
-          const int g = gp / 6, prod = gp % 6;
-          const int pa = (0x120100 >> (4 * prod)) & 3;       // A plane: 0,0,1,0,2,1
-          const int pb = (0x102010 >> (4 * prod)) & 3;       // B plane: 0,1,0,2,0,1
+          const int g = gp / NPROD, prod = gp % NPROD;
+          const int pa = SCHEME == 0 ? (0x120100 >> (4 * prod)) & 3 : (0x100 >> (4 * prod)) & 3;   // A plane: 0,0,1,0,2,1 | 0,0,1
+          const int pb = SCHEME == 0 ? (0x102010 >> (4 * prod)) & 3 : (0x010 >> (4 * prod)) & 3;   // B plane: 0,1,0,2,0,1 | 0,1,0
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* a_dst = ring + stage * stage_bytes;
           mbar_arrive_expect_tx(&full_bar[stage], (uint32_t)stage_bytes);
@@ -86,14 +93,14 @@ conv_exact_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
 #pragma unroll
           for (int dx = 0; dx < 3; ++dx)
             tma_load_2d(a_dst + A_BAND_BYTES + dx * B_TILE_BYTES, &tmap_b, &full_bar[stage], kc * BLOCK_K,
-                        ((g * 3 + dx) * 3 + pb) * p.n_pad + n0);
+                        ((g * 3 + dx) * NPLANE + pb) * p.n_pad + n0);
           if (++stage == p.stages) { stage = 0; phase ^= 1; }
         }
       }
     }
   } else if (warp == 1) {
     // ===== MMA issuer =====
-    constexpr uint32_t idesc = make_idesc_bf16(BLOCK_M, BLOCK_N);
+    constexpr uint32_t idesc = SCHEME == 0 ? make_idesc_bf16(BLOCK_M, BLOCK_N) : make_idesc_f16(BLOCK_M, BLOCK_N);
     int stage = 0;
     uint32_t phase = 0;
     uint32_t chunk = 0;                                 // running stage count of this CTA: slot = chunk % EXACT_SLOTS
@@ -130,6 +137,8 @@ conv_exact_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     const int cbase = BLOCK_N >= 32 ? ((warp - 2) >> 2) * COLS : 0;
     const bool owner = BLOCK_N >= 32 || warp < 6;                    // N = 16: warps 6-9 only keep the barriers balanced
     const int rp = (p.h + 1) * wp;
+    // SCHEME 1: both operands carry a power-of-two scale; undo it once, on the fp32 sum (exact)
+    const float wscale_inv = SCHEME == 0 ? 1.f : 1.f / pow2_scale_from_amax(__ldg(p.amax_b));
     uint32_t chunk = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
       const int m0 = (tile / p.n_tiles) * BLOCK_M;
@@ -168,6 +177,7 @@ conv_exact_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       const int y = q / wp, x = q % wp;
       if (owner && r < p.rows && x < p.w && y < p.h) {
         const int item = r / rp;
+        const float oscale = SCHEME == 0 ? 1.f : wscale_inv / pow2_scale_from_amax(__ldg(p.amax_a + item));   // per-item activation scale
         float* dst = p.out_f32 + (((size_t)item * p.h + y) * p.w + x) * p.n_real + n0;
         if ((p.n_real & 3) == 0 && n0 + COLS <= p.n_real) {
 #pragma unroll
@@ -175,7 +185,7 @@ conv_exact_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             float a[4];
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
-              a[k] = acc[i + k];
+              a[k] = SCHEME == 0 ? acc[i + k] : acc[i + k] * oscale;
               if (p.bias) a[k] += __ldg(p.bias + n0 + i + k);
               if (p.relu) a[k] = fmaxf(a[k], 0.f);
             }
@@ -185,7 +195,7 @@ conv_exact_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
 #pragma unroll
           for (int i = 0; i < COLS; ++i) {
             if (n0 + i < p.n_real) {
-              float a = acc[i];
+              float a = SCHEME == 0 ? acc[i] : acc[i] * oscale;
               if (p.bias) a += __ldg(p.bias + n0 + i);
               if (p.relu) a = fmaxf(a, 0.f);
               dst[i] = a;

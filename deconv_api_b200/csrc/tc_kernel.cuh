@@ -42,6 +42,10 @@ struct TcParams {
   int nprod_planes;  // weight planes per tap in the packed weights: 1, or 3 for the split-operand kernels (tc_exact.cuh)
   int nprod;         // 1 = plain bf16 product (the kernels of this file); 6 = fp32-accurate mode: operands split into
                      // three bf16 planes (hi, mid, lo), six cross products - conv_exact_kernel only
+  // fp16 two-plane scheme of the exact kernels (tc_exact.cuh, SCHEME 1): bit patterns of the largest |activation| and
+  // |weight| (device scalars); both operands were scaled by pow2_scale_from_amax() before they were split
+  const uint32_t* amax_a;
+  const uint32_t* amax_b;
   const float* bias;         // n_real entries added before the ReLU (forward conv), or null
   // DeepDream backward: fold the NEXT layer's gradient prep into this epilogue (bf16 plain store only):
   //   out = mask(act > 0) * (acc + prep_scale * act), act = that layer's bf16 tape in the output's layout

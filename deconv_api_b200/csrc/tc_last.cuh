@@ -37,10 +37,14 @@ struct LastParams {
   int tiles_x, tiles_y, total_tiles;
   int relu;
   float* out;                 // compact (P,h,w,cout) fp32
+  // EXACT = 2: fp16 two-plane operands scaled by powers of two (tc_exact.cuh, SCHEME 1): the largest |activation| and
+  // |weight| as float bit patterns (device scalars)
+  const uint32_t* amax_a;
+  const uint32_t* amax_b;
 };
 
 __host__ __device__ inline int last_smem_bytes(int k_blocks, int exact = 0) {
-  return (exact ? 3 : 1) * k_blocks * LAST_N * 128 + LAST_STAGES * LAST_A_BYTES + 2 * LAST_ROWS * LAST_PS * 4 + 1024 + 256;
+  return (exact == 1 ? 3 : (exact == 2 ? 2 : 1)) * k_blocks * LAST_N * 128 + LAST_STAGES * LAST_A_BYTES + 2 * LAST_ROWS * LAST_PS * 4 + 1024 + 256;
 }
 
 __device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1, int c2) {
@@ -54,7 +58,7 @@ __device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* m, uin
 template <int EXACT>
 __global__ void __launch_bounds__(LAST_THREADS, 1)
 deconv_last_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, LastParams p) {
-  constexpr int NPLANES = EXACT ? 3 : 1;
+  constexpr int NPLANES = EXACT == 1 ? 3 : (EXACT == 2 ? 2 : 1);
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   const int w_bytes = NPLANES * p.k_blocks * LAST_N * 128;   // resident weights [plane][k_block][32 rows][128 B]
@@ -117,7 +121,7 @@ deconv_last_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
     }
   } else if (warp == 1) {
     if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_bf16(128, LAST_N);
+      constexpr uint32_t idesc = EXACT == 2 ? make_idesc_f16(128, LAST_N) : make_idesc_bf16(128, LAST_N);
       mbar_wait(wres_bar, 0);
       tc_fence_after();
       int stage = 0;
@@ -136,7 +140,7 @@ deconv_last_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
             const uint32_t a_addr = smem_u32(ring + stage * LAST_A_BYTES);
             // weight planes this activation plane is multiplied with, smallest product first:
             // lo -> {hi}; mid -> {mid, hi}; hi -> {lo, mid, hi}   (plain mode: the one plane)
-            const int nb = EXACT ? 3 - pa : 1;
+            const int nb = EXACT ? NPLANES - pa : 1;
             for (int q = 0; q < nb; ++q) {
               const int pb = EXACT ? nb - 1 - q : 0;
               const uint64_t b_desc = make_sw128_kmajor_desc(smem_u32(wres + (pb * p.k_blocks + kc) * LAST_N * 128), 0);
@@ -165,6 +169,7 @@ deconv_last_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
     const int ncol = 9 * p.cout;
     const int ly = et / LAST_T, lx = et % LAST_T;             // this thread's output pixel inside the patch
     const bool has_px = et < LAST_T * LAST_T;
+    const float wscale_inv = EXACT == 2 ? 1.f / pow2_scale_from_amax(__ldg(p.amax_b)) : 1.f;
     int local = 0;
     for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++local) {
       const int item = tile / tiles_per_item, t2 = tile % tiles_per_item;
@@ -195,6 +200,7 @@ deconv_last_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
           float acc = 0.f;
 #pragma unroll
           for (int t = 0; t < 9; ++t) acc += pp[((t / 3) * LAST_H + (t % 3)) * LAST_PS + t * p.cout + c];
+          if (EXACT == 2) acc *= wscale_inv / pow2_scale_from_amax(__ldg(p.amax_a + item));      // per-item activation scale
           if (p.relu) acc = fmaxf(acc, 0.f);
           dst[c] = acc;
         }

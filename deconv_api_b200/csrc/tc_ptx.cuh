@@ -194,5 +194,22 @@ __host__ __device__ constexpr uint32_t make_idesc_bf16(uint32_t m, uint32_t n) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((n >> 3) << 17) | ((m >> 4) << 24);
 }
 
+// The same for fp16 operands (format code 0): 11 significand bits per plane instead of 8, same MMA rate.
+__host__ __device__ constexpr uint32_t make_idesc_f16(uint32_t m, uint32_t n) {
+  return (1u << 4) | ((n >> 3) << 17) | ((m >> 4) << 24);
+}
+
+// Power-of-two scale that brings a tensor whose largest magnitude has the float bit pattern `amax_bits` into
+// [2^13, 2^14): fp16 planes then neither overflow nor lose their top bits.  Zero / denormal maxima scale by 1.
+__host__ __device__ inline float pow2_scale_from_amax(uint32_t amax_bits) {
+  const int e = (int)((amax_bits >> 23) & 0xFFu);        // biased exponent of the maximum
+  if (e == 0 || e == 255) return 1.f;
+  int se = 127 + 13 - (e - 127);                         // biased exponent of the scale
+  se = se < 1 ? 1 : (se > 254 ? 254 : se);
+  union { uint32_t u; float f; } c;
+  c.u = (uint32_t)se << 23;
+  return c.f;
+}
+
 }  // namespace tc
 }  // namespace dcv
