@@ -364,10 +364,10 @@ def run_ours(args, rank, world, local_rank):
             c = p32["conv_tc"]
             extras["fp32_mode"] = {
                 "what": "the same step in the reference-precision mode (DCV_FP32: rel-L2 <= 1e-5): backward convs on tcgen05 with "
-                        "operands split into three bf16 planes, six products, fp32 register accumulation",
+                        "operands scaled per projection and split into two fp16 planes, three products, fp32 register accumulation",
                 "value": tot / (ms / 1e3), "e2e": tot / (ms_h / 1e3), "unit": UNIT, "ms_per_step": ms / n_x,
                 "roofline": {"bound": "tensor", "kernel": "conv_tc (split-operand)", "achieved": c["flops"] / (c["ms"] / 1e3) / 1e12,
-                             "peak": peaks()["tf_sus"], "unit": "TFLOP/s (algorithmic; the kernel issues 6 MMA flops per algorithmic flop)",
+                             "peak": peaks()["tf_sus"], "unit": "TFLOP/s (algorithmic; the kernel issues 3 MMA flops per algorithmic flop)",
                              "frac": c["flops"] / (c["ms"] / 1e3) / 1e12 / peaks()["tf_sus"]} if c["ms"] > 0 else None}
 
     if rank == 0 and not args.no_extras:

@@ -44,10 +44,11 @@ enum dcv_status {
 enum dcv_vis_mode { DCV_VIS_ALL = 0, DCV_VIS_MAX = 1 };
 
 /* arithmetic of the backward projection chain.  FP32 (parity mode, rel-L2 <= 1e-5): fp32 data between the layers;
- * the convs run on the tcgen05 tensor cores with both operands split into three bf16 planes and the six
- * significant cross products accumulated in fp32 registers (DCV_FP32_TC=0 in the environment selects the
- * CUDA-core FFMA kernels instead).  BF16 (throughput mode, rel-L2 <= 2e-2): tcgen05 chain on bf16 operands
- * with fp32 accumulation in TMEM.  The forward tape and the switches are fp32-accurate in both. */
+ * the convs run on the tcgen05 tensor cores with every projection scaled by a power of two into fp16's range and both
+ * operands split into two fp16 planes (22 significand bits), the three significant cross products accumulated in
+ * fp32 registers (DCV_FP32_SCHEME=0: three bf16 planes / six products as in the forward pass; DCV_FP32_TC=0 or
+ * dcv_set_fp32_mode(ctx, 0): the CUDA-core FFMA kernels).  BF16 (throughput mode, rel-L2 <= 2e-2): tcgen05 chain on
+ * bf16 operands with fp32 accumulation in TMEM.  The forward tape and the switches are fp32-accurate in both. */
 enum dcv_precision { DCV_FP32 = 0, DCV_BF16 = 1 };
 
 /* element type of the projections returned by dcv_project_fmt.  U8 = deprocess_image (deepdream.py:483-498)
