@@ -3,7 +3,7 @@
 // in shared memory — and with that the two neighbours of the 64 -> 64 conv can be fused into it:
 //
 //   UNPOOL  the conv's input is the switch-driven unpool of a pooled tensor (DPooling.down, deepdream.py:191-209):
-//           four producer warps expand pooled rows + switch bytes straight into the swizzled A tiles, the 4x larger
+//           producer warps expand pooled rows + switch bytes straight into the swizzled A tiles, the 4x larger
 //           unpooled tensor is never written to or read from HBM;
 //   LAST    the conv's output feeds the last backward conv (64 -> <= 3 channels, deepdream.py:102-111 of block1_conv1):
 //           the bf16 output tile stays in shared memory as the A operand of a second GEMM (all 9 taps stacked along N,
