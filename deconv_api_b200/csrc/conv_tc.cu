@@ -704,6 +704,7 @@ struct TcConvArgs {
   int scheme = 0;           // split-operand mode (nprod 6): 0 = three bf16 planes / six products, 1 = two fp16 planes / three
   const uint32_t* amax_a = nullptr;
   const uint32_t* amax_b = nullptr;
+  uint32_t* amax_out = nullptr;
 };
 
 static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& a, const __nv_bfloat16* in, int P, int h, int w,
@@ -896,25 +897,37 @@ int tc_prepare_backward_exact(dcv_ctx* ctx, Layer& l) {
 }
 
 // fp16 two-plane form of the backward conv: absmax -> scaled split -> conv_exact_kernel<.., 1> (or the GEMM + col2im last layer)
-static int tc_conv_bwd_2h(dcv_ctx* ctx, const Layer& l, const float* in, int P, int h, int w, float* out, int relu) {
+// chain: the per-item maxima of `in` were left by the conv that produced it (TcParams::amax_out; an unpool or a ReLU in
+// between does not raise them) - the extra pass over the input is skipped
+static int tc_conv_bwd_2h(dcv_ctx* ctx, const Layer& l, const float* in, int P, int h, int w, float* out, int relu, bool chain) {
   if (!l.tc.wd2_f16) return ctx->fail(DCV_ERR_STATE, "two-plane backward weights were not prepared for this layer");
   const int k_pad = tc_cpad(l.cout), n_pad = tc_cpad(l.cin);
   const size_t elems = (size_t)P * (h + 1) * (w + 1) * 2 * k_pad;
   int r = ctx->ws[4].ensure(ctx, elems * sizeof(__half));
   if (r) return r;
-  r = ctx->amax.ensure(ctx, (size_t)P * sizeof(uint32_t) + 256);
+  // two arrays of per-item maxima: the one this conv reads and the one it fills for the next conv of the chain
+  const size_t half = ((size_t)P * sizeof(uint32_t) + 255) & ~(size_t)255;
+  const bool grew = ctx->amax.cap < 2 * half;
+  r = ctx->amax.ensure(ctx, 2 * half);
   if (r) return r;
-  uint32_t* amax = (uint32_t*)ctx->amax.p;
+  if (grew || !chain || ctx->amax_cur < 0) { chain = false; ctx->amax_cur = 0; }
+  uint32_t* amax = (uint32_t*)((char*)ctx->amax.p + ctx->amax_cur * half);
+  uint32_t* amax_next = (uint32_t*)((char*)ctx->amax.p + (ctx->amax_cur ^ 1) * half);
   const size_t len = (size_t)h * w * l.cout, n_in = (size_t)P * len;
   {
-    ProfScope ps(ctx, DCV_K_OTHER, 0.0, 8.0 * n_in + 4.0 * P * (h + 1) * (w + 1) * k_pad);
-    cudaMemsetAsync(amax, 0, (size_t)P * sizeof(uint32_t), ctx->stream);
-    const int bpi = (int)std::max<size_t>(1, std::min<size_t>((len + 8191) / 8192, std::max<size_t>(1, (size_t)16 * kNumSMs / P)));
-    absmax_items_kernel<<<dim3(bpi, P), 256, 0, ctx->stream>>>(in, len, amax);
+    ProfScope ps(ctx, DCV_K_OTHER, 0.0, (chain ? 4.0 : 8.0) * n_in + 4.0 * P * (h + 1) * (w + 1) * k_pad);
+    if (!chain) {
+      cudaMemsetAsync(amax, 0, (size_t)P * sizeof(uint32_t), ctx->stream);
+      const int bpi = (int)std::max<size_t>(1, std::min<size_t>((len + 8191) / 8192, std::max<size_t>(1, (size_t)16 * kNumSMs / P)));
+      absmax_items_kernel<<<dim3(bpi, P), 256, 0, ctx->stream>>>(in, len, amax);
+      ctx->launches++;
+    }
+    cudaMemsetAsync(amax_next, 0, (size_t)P * sizeof(uint32_t), ctx->stream);
     const size_t work = (size_t)P * (h + 1) * (w + 1) * (k_pad / 8);
     split2_pad_kernel<<<grid_for(work, 256), 256, 0, ctx->stream>>>(in, P, h, w, l.cout, k_pad, amax, (__half*)ctx->ws[4].p);
-    ctx->launches += 2;
+    ctx->launches++;
   }
+  ctx->amax_cur = -1;          // set again below once a kernel that fills amax_next has been queued
   static const int use_last = getenv("DCV_TC_LAST") ? atoi(getenv("DCV_TC_LAST")) : 1;
   if (l.tc.wall2_f16 && use_last) {
     LastParams p = {};
@@ -952,11 +965,14 @@ static int tc_conv_bwd_2h(dcv_ctx* ctx, const Layer& l, const float* in, int P, 
   a.prof_class = DCV_K_CONV_TC;
   a.scheme = 1;
   a.amax_a = amax; a.amax_b = l.tc.wd_amax;
-  return tc_conv_run(ctx, a, (const __nv_bfloat16*)ctx->ws[4].p, P, h, w, nullptr, out);
+  a.amax_out = amax_next;
+  r = tc_conv_run(ctx, a, (const __nv_bfloat16*)ctx->ws[4].p, P, h, w, nullptr, out);
+  if (!r) ctx->amax_cur = (int)(amax_next != (uint32_t*)ctx->amax.p);
+  return r;
 }
 
-int tc_conv_bwd_exact(dcv_ctx* ctx, const Layer& l, const float* in, int P, int h, int w, float* out, int relu) {
-  if (fp32_scheme() == 1) return tc_conv_bwd_2h(ctx, l, in, P, h, w, out, relu);
+int tc_conv_bwd_exact(dcv_ctx* ctx, const Layer& l, const float* in, int P, int h, int w, float* out, int relu, bool chain) {
+  if (fp32_scheme() == 1) return tc_conv_bwd_2h(ctx, l, in, P, h, w, out, relu, chain);
   if (!l.tc.wd3_bf16) return ctx->fail(DCV_ERR_STATE, "split backward weights were not prepared for this layer");
   const int k_pad = tc_cpad(l.cout), n_pad = tc_cpad(l.cin);
   const size_t elems = (size_t)P * tc_split_elems(h, w, l.cout);
@@ -1132,7 +1148,7 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
     p.base_off = 0;
     const int smem = stages * exact_stage_bytes(bn) + 1024 + 256;
     const int npl = l.scheme == 1 ? 2 : 3;
-    p.amax_a = l.amax_a; p.amax_b = l.amax_b;
+    p.amax_a = l.amax_a; p.amax_b = l.amax_b; p.amax_out = l.amax_out;
     CUtensorMap ta, tb;
     int r = make_tmap(ctx, &ta, in, (uint64_t)p.rows, (uint64_t)npl * l.k_pad, BAND_ROWS);
     if (r) return r;

@@ -67,7 +67,8 @@ struct dcv_ctx {
   DevBuf ws[6];        // projection workspace: [0],[1] ping-pong tensors, [2],[3] maps, [4],[5] bf16 ping-pong
   DevBuf feat_dev;
   DevBuf scratch;      // reduction partials
-  DevBuf amax;         // fp16 scheme: float bit pattern of the largest |activation| of the tensor being split
+  DevBuf amax;         // fp16 scheme: per-item float bit patterns of the largest |activation|, two arrays (read / filled)
+  int amax_cur = -1;   // which of the two holds the maxima of the last exact conv's output (-1: none)
   DevBuf stage;        // staging for host-buffer entry points
   // host-output projections: chunks are copied back on a second stream while the next chunk computes
   cudaStream_t copy_stream = nullptr;
@@ -127,7 +128,9 @@ int tc_conv_fwd_exact(dcv_ctx* ctx, const Layer& l, const float* in, int P, int 
 // the same for the backward (deconvnet) conv of the fp32 projection mode: in fp32 compact (P,h,w,cout) ->
 // out fp32 compact (P,h,w,cin) = relu?(conv(in, flipT(W))); scratch ctx->ws[4] sized by tc_split_elems()
 int tc_prepare_backward_exact(dcv_ctx* ctx, Layer& l);
-int tc_conv_bwd_exact(dcv_ctx* ctx, const Layer& l, const float* in, int P, int h, int w, float* out, int relu);
+// chain: `in` is the output of the previous tc_conv_bwd_exact call on this context (possibly unpooled / rectified since):
+// its per-item maxima are already known
+int tc_conv_bwd_exact(dcv_ctx* ctx, const Layer& l, const float* in, int P, int h, int w, float* out, int relu, bool chain = false);
 size_t tc_split_elems(int h, int w, int c);          // bf16 elements of one item split into three planes
 // backward conv; exactly one of out_bf16 (padded-flat, pitch l.tc.n_pad) / out_f32 (compact (P,h,w,l.cin)) is
 // non-null; relu < 0: the layer's own activation (deconvnet rule), 0/1: explicit (DeepDream uses 0)

@@ -175,8 +175,10 @@ conv_exact_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       const int r = m0 + lg * 32 + lane;
       const int q = r % rp;
       const int y = q / wp, x = q % wp;
+      float vmax = 0.f;                                 // largest |output| of this thread's row part (amax_out)
+      const int item_of_row = r / rp;
       if (owner && r < p.rows && x < p.w && y < p.h) {
-        const int item = r / rp;
+        const int item = item_of_row;
         const float oscale = SCHEME == 0 ? 1.f : wscale_inv / pow2_scale_from_amax(__ldg(p.amax_a + item));   // per-item activation scale
         float* dst = p.out_f32 + (((size_t)item * p.h + y) * p.w + x) * p.n_real + n0;
         if ((p.n_real & 3) == 0 && n0 + COLS <= p.n_real) {
@@ -188,6 +190,7 @@ conv_exact_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
               a[k] = SCHEME == 0 ? acc[i + k] : acc[i + k] * oscale;
               if (p.bias) a[k] += __ldg(p.bias + n0 + i + k);
               if (p.relu) a[k] = fmaxf(a[k], 0.f);
+              vmax = fmaxf(vmax, fabsf(a[k]));
             }
             *reinterpret_cast<float4*>(dst + i) = make_float4(a[0], a[1], a[2], a[3]);
           }
@@ -198,9 +201,21 @@ conv_exact_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
               float a = SCHEME == 0 ? acc[i] : acc[i] * oscale;
               if (p.bias) a += __ldg(p.bias + n0 + i);
               if (p.relu) a = fmaxf(a, 0.f);
+              vmax = fmaxf(vmax, fabsf(a));
               dst[i] = a;
             }
           }
+        }
+      }
+      if (p.amax_out) {
+        // one atomic per warp when the whole warp sits in one item (the rule; tiles straddle items only at their ends)
+        const int item0 = __shfl_sync(0xffffffffu, item_of_row, 0);
+        if (__all_sync(0xffffffffu, item_of_row == item0)) {
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) vmax = fmaxf(vmax, __shfl_xor_sync(0xffffffffu, vmax, o));
+          if (lane == 0 && vmax > 0.f) atomicMax(p.amax_out + item0, __float_as_uint(vmax));
+        } else if (vmax > 0.f) {
+          atomicMax(p.amax_out + item_of_row, __float_as_uint(vmax));
         }
       }
     }

@@ -46,6 +46,7 @@ struct TcParams {
   // |weight| (device scalars); both operands were scaled by pow2_scale_from_amax() before they were split
   const uint32_t* amax_a;
   const uint32_t* amax_b;
+  uint32_t* amax_out;        // optional: per-item maximum of |output| (float bits, atomicMax; zeroed by the host): the scale of the NEXT conv
   const float* bias;         // n_real entries added before the ReLU (forward conv), or null
   // DeepDream backward: fold the NEXT layer's gradient prep into this epilogue (bf16 plain store only):
   //   out = mask(act > 0) * (acc + prep_scale * act), act = that layer's bf16 tape in the output's layout
