@@ -1477,8 +1477,7 @@ static int tc_strip_impl(dcv_ctx* ctx, const Layer& conv, const Layer* last, con
   const double px = (double)P * h * w;
   double flops = 2.0 * 9 * px * conv.cin * conv.cout, bytes = 2.0 * px * conv.cout * (sw ? 0.25 + 0.125 : 1.0);
   if (last) { flops += 2.0 * 9 * px * last->cin * last->cout; bytes += 4.0 * px * last->cin; } else bytes += 2.0 * px * conv.cin;
-  dcv_ctx silent;                              // the caller's ProfScope is already open: record nothing here
-  ProfScope ps(prof ? ctx : &silent, DCV_K_CONV_TC, flops, bytes);
+  ProfScope ps(ctx, DCV_K_CONV_TC, flops, bytes, prof);      // prof = false: the caller's scope is already open
   if (sw) return last ? launch_strip<true, true>(ctx, ta, tb, tbl, to, p) : launch_strip<true, false>(ctx, ta, tb, tbl, to, p);
   return last ? launch_strip<false, true>(ctx, ta, tb, tbl, to, p) : launch_strip<false, false>(ctx, ta, tb, tbl, to, p);
 }

@@ -89,8 +89,12 @@ struct dcv_ctx {
 
 struct ProfScope {
   dcv_ctx* c;
-  ProfScope(dcv_ctx* ctx, int cat, double flops, double bytes) : c(ctx) { if (c->prof_on) c->prof_begin(cat, flops, bytes); }
-  ~ProfScope() { if (c->prof_on) c->prof_end(); }
+  bool on;
+  // enabled = false: a caller up the stack already has a scope open around this launch
+  ProfScope(dcv_ctx* ctx, int cat, double flops, double bytes, bool enabled = true) : c(ctx), on(enabled && ctx->prof_on) {
+    if (on) c->prof_begin(cat, flops, bytes);
+  }
+  ~ProfScope() { if (on) c->prof_end(); }
 };
 
 // api.cu

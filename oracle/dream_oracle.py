@@ -23,12 +23,28 @@ def _convs(model, upto):
     return ops
 
 
-def loss_and_grad(ops, x_nhwc, layers):
-    """loss = sum_l coeff_l * mean(act_l^2); returns (loss, dloss/dx NHWC)."""
+def _pool_with_idx(t, idx_nhwc):
+    """2x2/2 max pool that takes, for every window, the element a given switch index (N,h,w,C; r*2+c) names — the
+    same value as F.max_pool2d wherever the index is the window's arg-max, and differentiable the same way."""
+    n, c, h, w = t.shape
+    ph, pw = h // 2, w // 2
+    win = t[:, :, :2 * ph, :2 * pw].reshape(n, c, ph, 2, pw, 2).permute(0, 1, 2, 4, 3, 5).reshape(n, c, ph, pw, 4)
+    idx = torch.from_numpy(np.ascontiguousarray(idx_nhwc)).permute(0, 3, 1, 2).long()
+    return win.gather(-1, idx[..., None])[..., 0]
+
+
+def loss_and_grad(ops, x_nhwc, layers, pool_idx=None):
+    """loss = sum_l coeff_l * mean(act_l^2); returns (loss, dloss/dx NHWC).  pool_idx (optional): {pool layer name:
+    switch indices (N,h,w,C)} to route a pool by (tests that follow an implementation's choice at near-ties)."""
     x = torch.from_numpy(np.ascontiguousarray(x_nhwc, np.float32)).permute(0, 3, 1, 2).clone().requires_grad_(True)
     t, loss = x, 0.0
     for kind, name, W, b in ops:
-        t = F.relu(F.conv2d(t, W, b, padding=1)) if kind == "conv" else F.max_pool2d(t, 2, 2)
+        if kind == "conv":
+            t = F.relu(F.conv2d(t, W, b, padding=1))
+        elif pool_idx is not None and name in pool_idx:
+            t = _pool_with_idx(t, pool_idx[name])
+        else:
+            t = F.max_pool2d(t, 2, 2)
         if name in layers:
             loss = loss + layers[name] * (t * t).mean()
     loss.backward()

@@ -127,3 +127,38 @@ def test_request_mosaic_with_fewer_than_four_positive_maps_raises_index_error():
     eng = model.bound_engine(upto="block1_conv1")
     with pytest.raises(IndexError):
         eng.request_mosaic(synth.smooth_image_u8(1, 32, 32), eng.index["block1_conv1"])
+
+
+def test_result_format_and_request_tail_error_paths(engine):
+    """Argument checking of the new entry points: every refusal is a negative status with a message, nothing crashes."""
+    import ctypes
+    lib = engine.lib
+    model = vgg16.VGG16(weights=None, include_top=False, input_shape=(32, 32, 3), seed=2)
+    eng = model.bound_engine(upto="block1_conv2")
+    li = eng.index["block1_conv2"]
+    eng.forward(synth.caffe_preprocess(synth.smooth_image_u8(1, 32, 32)), li)
+    feats = np.array([0, 1], np.int32)
+    out = np.zeros((2, 1, 32, 32, 3), np.uint8)
+    P = lambda a: a.ctypes.data_as(ctypes.c_void_p)
+    assert lib.dcv_project_fmt(eng.ctx, li, P(feats), 2, 0, 0, 7, P(out)) == -1          # unknown format
+    assert b"format" in lib.dcv_last_error(eng.ctx)
+    assert lib.dcv_project_fmt(eng.ctx, li, None, 2, 0, 0, 2, P(out)) == -1              # no feature list
+    assert lib.dcv_project_fmt(eng.ctx, li, P(feats), 2, 0, 0, 2, None) == -1            # no output
+    assert lib.dcv_project_fmt(eng.ctx, li, P(np.array([0, 64], np.int32)), 2, 0, 0, 2, P(out)) == -1   # feature out of range
+    assert lib.dcv_project_fmt(eng.ctx, li, P(feats), 0, 0, 0, 2, P(out)) == 0           # nothing to do
+    assert lib.dcv_project_fmt(eng.ctx, li + 5, P(feats), 2, 0, 0, 2, P(out)) == -1      # layer outside the network
+    img = np.zeros((32, 32, 3), np.uint8)
+    mosaic = np.zeros((64, 64, 3), np.uint8)
+    assert lib.dcv_request_mosaic(eng.ctx, None, 32, 32, li, 0, 0, P(mosaic), None) == -1
+    assert lib.dcv_request_mosaic(eng.ctx, P(img), 0, 32, li, 0, 0, P(mosaic), None) == -1
+    assert lib.dcv_request_mosaic(eng.ctx, P(img), 32, 32, 99, 0, 0, P(mosaic), None) == -1
+    assert lib.dcv_request_mosaic(eng.ctx, P(img), 32, 32, li, 5, 0, P(mosaic), None) == -1   # illegal visualize mode
+    # page-locked buffers: round trip through a projection, then release
+    buf = eng.pinned_empty((2, 1, 32, 32, 3), np.uint8)
+    got = eng.project(li, feats, out=buf, out_format="u8")
+    assert np.array_equal(got, eng.project(li, feats, out_format="u8"))
+    p = ctypes.c_void_p()
+    assert lib.dcv_host_alloc(eng.ctx, 1 << 20, None) == -1
+    assert lib.dcv_host_alloc(eng.ctx, 1 << 20, ctypes.byref(p)) == 0 and p.value
+    assert lib.dcv_host_free(eng.ctx, p) == 0
+    assert lib.dcv_host_free(eng.ctx, None) == 0
