@@ -619,6 +619,20 @@ static int project_chunk(dcv_ctx* ctx, int layer, int foff, int n, int vis_mode,
         }
         TRY(tc_unpool(ctx, hb[hcur], (const uint8_t*)l.sw.p, P, B, h, w, l.in_H, l.in_W, C, hb[hcur ^ 1]));
         hcur ^= 1;
+      } else if (precision == DCV_FP32 && mode == M_TENSOR && j >= 1 && ctx->net[j - 1].kind == LK_CONV && ctx->net[j - 1].cout == C &&
+                 fp32_on_tc(ctx, ctx->net[j - 1]) && tc_bwd_exact_fuses_unpool() && (nonneg || !ctx->net[j - 1].relu)) {
+        // fp32 mode: the unpool is done by the operand split of the conv below (the unpooled fp32 tensor is never written)
+        Layer& cl = ctx->net[j - 1];
+        if (j - 1 == 0 && final_dst) bufs[cur ^ 1] = final_dst;
+        TRY(tc_prepare_backward_exact(ctx, cl));
+        TRY(tc_conv_bwd_exact_unpool(ctx, cl, bufs[cur], (const uint8_t*)l.sw.p, B, P, l.in_H, l.in_W, bufs[cur ^ 1], cl.relu, exact_chain));
+        exact_chain = true;
+        cur ^= 1;
+        h = l.in_H; w = l.in_W;
+        nonneg = cl.relu != 0;
+        C = cl.cin;
+        --j;                          // the conv layer is done
+        continue;
       } else {
         // algorithmic bytes: 5*HWC/4 read + 4*HWC written, (H,W) = unpooled size
         ProfScope ps(ctx, DCV_K_UNPOOL, 0.0, (double)P * l.in_H * l.in_W * C * (4.0 + 5.0 / 4.0));

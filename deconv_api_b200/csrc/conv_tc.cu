@@ -232,6 +232,52 @@ __global__ void split2_pad_kernel(const float* __restrict__ x, int P, int h, int
   }
 }
 
+// The same with the switch-driven unpool (DPooling.down) in front: x is the POOLED fp32 tensor (P,h/2,w/2,C), sw its
+// switches (Bsw,h/2,w/2,C); the unpooled fp32 tensor (4x the elements, written once and read once before) never exists.
+__global__ void split2_unpool_pad_kernel(const float* __restrict__ x, const uint8_t* __restrict__ sw, int Bsw, int P, int h, int w,
+                                         int C, int c_pad, const uint32_t* __restrict__ amax, __half* __restrict__ out) {
+  const int wp = w + 1, rp = (h + 1) * wp, cg = c_pad / 8;
+  const int ph = h / 2, pw = w / 2;
+  const size_t total = (size_t)P * rp * cg;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int g = (int)(i % cg);
+    const size_t r = i / cg;
+    const int q = (int)(r % rp);
+    const int item = (int)(r / rp);
+    const int y = q / wp, xx = q % wp;
+    float v[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) v[k] = 0.f;
+    if (y < h && xx < w) {
+      const size_t pix = ((size_t)(y >> 1) * pw + (xx >> 1)) * C + g * 8;
+      const float* src = x + (size_t)item * ph * pw * C + pix;
+      const uint8_t* sp = sw + (size_t)(item % Bsw) * ph * pw * C + pix;
+      const uint32_t corner = (uint32_t)((y & 1) * 2 + (xx & 1));
+      if ((C & 7) == 0 && g * 8 + 8 <= C) {
+        const float4 a = __ldg(reinterpret_cast<const float4*>(src)), b = __ldg(reinterpret_cast<const float4*>(src + 4));
+        const uint2 s2 = __ldg(reinterpret_cast<const uint2*>(sp));
+        const float t[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const uint32_t sb = ((k < 4 ? s2.x : s2.y) >> (8 * (k & 3))) & 0xFFu;
+          v[k] = sb == corner ? t[k] : 0.f;
+        }
+      } else {
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+          if (g * 8 + k < C && __ldg(sp + k) == corner) v[k] = __ldg(src + k);
+      }
+    }
+    const float s = pow2_scale_from_amax(__ldg(amax + item));
+    __half hh[8], ll[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) split2h(v[k] * s, hh[k], ll[k]);
+    __half* o = out + r * (2 * (size_t)c_pad) + g * 8;
+    *reinterpret_cast<uint4*>(o) = *reinterpret_cast<const uint4*>(hh);
+    *reinterpret_cast<uint4*>(o + c_pad) = *reinterpret_cast<const uint4*>(ll);
+  }
+}
+
 // Weights for the two-plane scheme: w fp32 [9][K][N] -> fp16 [tap][plane (hi,lo)][n_pad][k_pad], scaled like the activations.
 __global__ void pack_weights_2h_kernel(const float* __restrict__ w, int kdim, int ndim, int k_pad, int n_pad,
                                        const uint32_t* __restrict__ amax, __half* __restrict__ out) {
@@ -899,7 +945,9 @@ int tc_prepare_backward_exact(dcv_ctx* ctx, Layer& l) {
 // fp16 two-plane form of the backward conv: absmax -> scaled split -> conv_exact_kernel<.., 1> (or the GEMM + col2im last layer)
 // chain: the per-item maxima of `in` were left by the conv that produced it (TcParams::amax_out; an unpool or a ReLU in
 // between does not raise them) - the extra pass over the input is skipped
-static int tc_conv_bwd_2h(dcv_ctx* ctx, const Layer& l, const float* in, int P, int h, int w, float* out, int relu, bool chain) {
+// up_sw != null: `in` is the pooled tensor (P,h/2,w/2,cout) and the unpool by these switches is done by the split pass
+static int tc_conv_bwd_2h(dcv_ctx* ctx, const Layer& l, const float* in, int P, int h, int w, float* out, int relu, bool chain,
+                          const uint8_t* up_sw = nullptr, int up_Bsw = 1) {
   if (!l.tc.wd2_f16) return ctx->fail(DCV_ERR_STATE, "two-plane backward weights were not prepared for this layer");
   const int k_pad = tc_cpad(l.cout), n_pad = tc_cpad(l.cin);
   const size_t elems = (size_t)P * (h + 1) * (w + 1) * 2 * k_pad;
@@ -913,9 +961,9 @@ static int tc_conv_bwd_2h(dcv_ctx* ctx, const Layer& l, const float* in, int P, 
   if (grew || !chain || ctx->amax_cur < 0) { chain = false; ctx->amax_cur = 0; }
   uint32_t* amax = (uint32_t*)((char*)ctx->amax.p + ctx->amax_cur * half);
   uint32_t* amax_next = (uint32_t*)((char*)ctx->amax.p + (ctx->amax_cur ^ 1) * half);
-  const size_t len = (size_t)h * w * l.cout, n_in = (size_t)P * len;
+  const size_t len = (size_t)(up_sw ? (h / 2) * (w / 2) : h * w) * l.cout, n_in = (size_t)P * len;   // elements actually read
   {
-    ProfScope ps(ctx, DCV_K_OTHER, 0.0, (chain ? 4.0 : 8.0) * n_in + 4.0 * P * (h + 1) * (w + 1) * k_pad);
+    ProfScope ps(ctx, DCV_K_OTHER, 0.0, (chain ? 4.0 : 8.0) * n_in + (up_sw ? 1.0 * n_in : 0.0) + 4.0 * P * (h + 1) * (w + 1) * k_pad);
     if (!chain) {
       cudaMemsetAsync(amax, 0, (size_t)P * sizeof(uint32_t), ctx->stream);
       const int bpi = (int)std::max<size_t>(1, std::min<size_t>((len + 8191) / 8192, std::max<size_t>(1, (size_t)16 * kNumSMs / P)));
@@ -924,7 +972,10 @@ static int tc_conv_bwd_2h(dcv_ctx* ctx, const Layer& l, const float* in, int P, 
     }
     cudaMemsetAsync(amax_next, 0, (size_t)P * sizeof(uint32_t), ctx->stream);
     const size_t work = (size_t)P * (h + 1) * (w + 1) * (k_pad / 8);
-    split2_pad_kernel<<<grid_for(work, 256), 256, 0, ctx->stream>>>(in, P, h, w, l.cout, k_pad, amax, (__half*)ctx->ws[4].p);
+    if (up_sw)
+      split2_unpool_pad_kernel<<<grid_for(work, 256), 256, 0, ctx->stream>>>(in, up_sw, up_Bsw, P, h, w, l.cout, k_pad, amax, (__half*)ctx->ws[4].p);
+    else
+      split2_pad_kernel<<<grid_for(work, 256), 256, 0, ctx->stream>>>(in, P, h, w, l.cout, k_pad, amax, (__half*)ctx->ws[4].p);
     ctx->launches++;
   }
   ctx->amax_cur = -1;          // set again below once a kernel that fills amax_next has been queued
@@ -969,6 +1020,15 @@ static int tc_conv_bwd_2h(dcv_ctx* ctx, const Layer& l, const float* in, int P, 
   r = tc_conv_run(ctx, a, (const __nv_bfloat16*)ctx->ws[4].p, P, h, w, nullptr, out);
   if (!r) ctx->amax_cur = (int)(amax_next != (uint32_t*)ctx->amax.p);
   return r;
+}
+
+bool tc_bwd_exact_fuses_unpool() { return fp32_scheme() == 1; }
+
+int tc_conv_bwd_exact_unpool(dcv_ctx* ctx, const Layer& l, const float* pooled, const uint8_t* sw, int Bsw, int P, int h, int w,
+                             float* out, int relu, bool chain) {
+  if (fp32_scheme() != 1) return ctx->fail(DCV_ERR_UNSUPPORTED, "fused unpool needs the two-plane scheme");
+  if ((h & 1) || (w & 1)) return ctx->fail(DCV_ERR_ARG, "fused unpool needs an even size");
+  return tc_conv_bwd_2h(ctx, l, pooled, P, h, w, out, relu, chain, sw, Bsw);
 }
 
 int tc_conv_bwd_exact(dcv_ctx* ctx, const Layer& l, const float* in, int P, int h, int w, float* out, int relu, bool chain) {

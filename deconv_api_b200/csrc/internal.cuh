@@ -135,6 +135,10 @@ int tc_prepare_backward_exact(dcv_ctx* ctx, Layer& l);
 // chain: `in` is the output of the previous tc_conv_bwd_exact call on this context (possibly unpooled / rectified since):
 // its per-item maxima are already known
 int tc_conv_bwd_exact(dcv_ctx* ctx, const Layer& l, const float* in, int P, int h, int w, float* out, int relu, bool chain = false);
+// the same with DPooling.down in front: `pooled` is (P,h/2,w/2,cout), unpooled by the switches inside the split pass
+bool tc_bwd_exact_fuses_unpool();
+int tc_conv_bwd_exact_unpool(dcv_ctx* ctx, const Layer& l, const float* pooled, const uint8_t* sw, int Bsw, int P, int h, int w,
+                             float* out, int relu, bool chain);
 size_t tc_split_elems(int h, int w, int c);          // bf16 elements of one item split into three planes
 // backward conv; exactly one of out_bf16 (padded-flat, pitch l.tc.n_pad) / out_f32 (compact (P,h,w,l.cin)) is
 // non-null; relu < 0: the layer's own activation (deconvnet rule), 0/1: explicit (DeepDream uses 0)
