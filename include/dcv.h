@@ -125,14 +125,14 @@ DCV_API int dcv_net_num_layers(const dcv_ctx* ctx);
  * the context's stream and every later call on the context is ordered behind them (a kernel error surfaces there). */
 DCV_API int dcv_forward(dcv_ctx* ctx, const float* img_nhwc, int B, int H, int W, int upto_layer);
 /* Arithmetic of the forward convs (no counterpart in the reference).  1 (default): tcgen05 with both operands
- * split into three bf16 planes and the six significant cross products accumulated in fp32 (x*w = hh + hm + mh + hl
- * + lh + mm; the hi*hi products rotate over three accumulators, the corrections use a fourth, because the tensor
- * core truncates when it adds into an accumulator): measured rel-L2 1e-7 .. 1e-6 per layer against float64, the same
- * as the FFMA kernel, at 3-10x its speed for batch 1; the first conv (K = 27) stays FFMA.  0: FFMA fp32 everywhere. */
+ * split into three bf16 planes and the six significant cross products (x*w = hh + hm + mh + hl + lh + mm) summed in
+ * fp32 REGISTERS - every pipeline stage starts a fresh TMEM accumulator, because the tensor core truncates when it
+ * adds into one: measured rel-L2 1e-7 .. 1e-6 per layer against float64, the same as the FFMA kernel, at 3-10x its
+ * speed for batch 1; the first conv (K = 27) stays FFMA.  0: FFMA fp32 everywhere. */
 DCV_API int dcv_set_forward_mode(dcv_ctx* ctx, int mode);
 /* Arithmetic of the backward convs of the DCV_FP32 chain (projection, DeepDream, dcv_deconv3x3); no counterpart in
- * the reference.  1 (default, or DCV_FP32_TC in the environment): the same split-operand tcgen05 kernels with fp32
- * register accumulation; 0: CUDA-core FFMA.  Both meet rel-L2 <= 1e-5; the switch exists for A/B parity tests. */
+ * the reference.  1 (default, or DCV_FP32_TC in the environment): split-operand tcgen05 kernels with fp32 register
+ * accumulation (two fp16 planes per operand and a per-projection power-of-two scale, see dcv_precision); 0: CUDA-core FFMA.  Both meet rel-L2 <= 1e-5; the switch exists for A/B parity tests. */
 DCV_API int dcv_set_fp32_mode(dcv_ctx* ctx, int mode);
 DCV_API int dcv_forward_dev(dcv_ctx* ctx, const float* img_nhwc_dev, int B, int H, int W, int upto_layer);
 /* Shape of layer `layer`'s output in the current tape: dims[0..3] = B,H,W,C (H=W=1 after flatten). */
