@@ -95,3 +95,26 @@ def test_config4_shape_batch_of_images_block5_conv3():
                     assert np.abs(got[k, b]).max() == 0
     # the two images really are different units: image 1's projections are not image 0's
     assert rel_l2(want[0, 1], want[0, 0]) > 0.1
+
+
+def test_batched_tape_equals_single_image_tapes_at_full_size():
+    """Size-independent property for the configs[3] path at its real size: 8 images in one tape (what
+    parallel.visualize_batch runs per block) must give, image by image, what 8 single-image tapes give — every item
+    reads its own image's switches and activations.  bf16 chain, uint8 and float32 results."""
+    model = vgg16.VGG16(weights=None, include_top=False, input_shape=(224, 224, 3))
+    imgs = synth.image_batch(8, 224, 224, seed0=10)
+    eng = model.bound_engine(upto="block5_conv3")
+    li = eng.index["block5_conv3"]
+    feats = np.arange(0, 512, 16, dtype=np.int32)                  # 32 maps x 8 images = 256 items
+    eng.forward(imgs, li)
+    both = eng.project(li, feats, precision="bf16")
+    both8 = eng.project(li, feats, precision="bf16", out_format="u8")
+    assert both.shape == (32, 8, 224, 224, 3)
+    for b in (0, 3, 7):
+        eng.forward(imgs[b:b + 1], li)
+        one = eng.project(li, feats, precision="bf16")[:, 0]
+        one8 = eng.project(li, feats, precision="bf16", out_format="u8")[:, 0]
+        # the batch decides tile shapes (more rows: other kernel variants), so bits may differ at bf16 level
+        assert rel_l2(both[:, b], one) < 5e-3, b
+        d = np.abs(both8[:, b].astype(np.int16) - one8.astype(np.int16))
+        assert np.percentile(d, 99.9) <= 2, (b, d.max())

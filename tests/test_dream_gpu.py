@@ -177,3 +177,17 @@ def test_gradient_at_config3_size_512():
     # bounds (the dream image is, at 2e-2: test_dream_loop_bf16_vs_oracle); this pins the direction of ascent.
     cos = float((g16 * g_ref).sum() / (np.linalg.norm(g16) * np.linalg.norm(g_ref)))
     assert cos > 0.97 and rel_l2(g16, g_ref) < 0.25, (cos, rel_l2(g16, g_ref))
+
+
+def test_dream_at_config5_size_runs_and_is_deterministic():
+    """configs[4] size (2048 x 2048, four octaves): no oracle at this size (minutes of CPU autograd), so the properties
+    that do not depend on one — the loop changes the image, stays finite, keeps the shape, and two runs give the same bits
+    (fixed jitter stream, deterministic reductions, CUDA-graph replay included)."""
+    model = vgg16.VGG16(weights=None, include_top=False, input_shape=(None, None, 3))
+    img = synth.caffe_preprocess(synth.smooth_image_u8(0, 2048, 2048))
+    kw = dict(num_octave=4, iterations=3, precision="bf16", seed=1)
+    a = dm.dream(model, img, **kw)
+    b = dm.dream(model, img, **kw)
+    assert a.shape == img.shape and np.isfinite(a).all()
+    assert np.array_equal(a, b)
+    assert rel_l2(a, img) > 1e-3

@@ -70,3 +70,27 @@ def test_tail_linear_and_unsupported(engine):
     from deconv_api_b200 import _native
     with pytest.raises(_native.DcvError):
         engine.deconv_tail(rng.normal(0, 1, (1, 8, 8, 128)).astype(np.float32), glorot(rng, 64, 128))
+
+
+def test_fused_tail_equals_the_three_operators_it_replaces_at_full_size(engine):
+    """Size-independent property at the benchmark's own size (224 x 224, 64 channels): the fused kernel against the
+    chain of stand-alone operators it replaces — DPooling.down, then DConvolution2D.down of block1_conv2 and of
+    block1_conv1 in the bf16 mode (each of those is pinned against the oracle on its own in test_tc_gpu.py /
+    test_ops_gpu.py).  Same bf16 roundings at the same places, so only the fp32 summation order differs."""
+    rng = np.random.default_rng(77)
+    B = 4
+    x = np.maximum(rng.normal(0, 1, (B, 112, 112, 64)), 0).astype(np.float32)
+    x[rng.random(x.shape) < 0.5] = 0
+    sw = rng.integers(0, 4, x.shape).astype(np.uint8)
+    W2, W1 = glorot(rng, 64, 64), glorot(rng, 3, 64)
+    fused = engine.deconv_tail(x, W2, W1, sw)
+    step1 = engine.unpool_switch(bf16_round(x), sw)
+    step2 = engine.deconv3x3(step1, W2, relu=True, precision="bf16")
+    step3 = engine.deconv3x3(bf16_round(step2), W1, relu=True, precision="bf16")
+    assert fused.shape == step3.shape == (B, 224, 224, 3)
+    assert rel_l2(fused, step3) < 1e-3, rel_l2(fused, step3)
+    # and the half-fused forms agree with it too
+    only_unpool = engine.deconv_tail(x, W2, None, sw)
+    assert rel_l2(only_unpool, bf16_round(step2)) < 1e-3
+    only_last = engine.deconv_tail(step1, W2, W1, None)
+    assert rel_l2(only_last, step3) < 1e-3
