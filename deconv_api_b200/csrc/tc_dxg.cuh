@@ -163,13 +163,24 @@ deconv_dxg_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       const int m0 = tile * ROWS_OUT;
       const int buf = local & 1;
       const uint32_t use = (uint32_t)(local >> 1);
-      mbar_wait(&tfull_bar[buf], use & 1);
-      tc_fence_after();
       const int r = m0 + SEG * lg + lane;                     // output row of this thread (grouped: lanes 30, 31 are helpers only)
       const int q = r % rp;
       const int y = q / wp, x = q % wp;
       const bool in_range = (lane < SEG) && (r < p.rows);
       const bool is_pixel = in_range && (x < p.w) && (y < p.h);
+      // gradient prep: the activations this tile will be masked / seeded with do not depend on the accumulator - fetch
+      // them BEFORE waiting for the MMAs (behind the wait the load latency sat on the epilogue's critical path:
+      // block1_conv2's backward ran at 493 TFLOP/s against 862 for the same conv without the prep)
+      uint32_t actw[8];
+      if constexpr (EPI & 2) {
+        if (in_range) {
+          const uint4* ap = reinterpret_cast<const uint4*>(p.prep_act + (size_t)r * p.n_pad + c0);
+          const uint4 t0 = __ldg(ap), t1 = __ldg(ap + 1);
+          actw[0] = t0.x; actw[1] = t0.y; actw[2] = t0.z; actw[3] = t0.w; actw[4] = t1.x; actw[5] = t1.y; actw[6] = t1.z; actw[7] = t1.w;
+        }
+      }
+      mbar_wait(&tfull_bar[buf], use & 1);
+      tc_fence_after();
       const uint32_t t_row = tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(buf * ACC_STRIDE);
       uint32_t v0[32], v1[32], v2[32];                        // 16 used
       tmem_ld16(t_row + (uint32_t)c0, v0);
@@ -185,14 +196,6 @@ deconv_dxg_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       // Measured: this epilogue, not the tensor pipe, paces the kernel (12 MMAs per tile; skipping the body took
       // block1_conv2 from 2.4 to 1.35 ms), and it is instruction-bound - so the optional steps are compiled out
       // (EPI) and the ReLU / pad masking are branch-free.
-      uint32_t actw[8];
-      if constexpr (EPI & 2) {
-        if (in_range) {
-          const uint4* ap = reinterpret_cast<const uint4*>(p.prep_act + (size_t)r * p.n_pad + c0);
-          const uint4 t0 = __ldg(ap), t1 = __ldg(ap + 1);
-          actw[0] = t0.x; actw[1] = t0.y; actw[2] = t0.z; actw[3] = t0.w; actw[4] = t1.x; actw[5] = t1.y; actw[6] = t1.z; actw[7] = t1.w;
-        }
-      }
       uint32_t packed[8];
 #pragma unroll
       for (int c = 0; c < 16; c += 2) {
