@@ -692,39 +692,54 @@ int make_tmap_patch(dcv_ctx* ctx, CUtensorMap* m, const void* base, uint64_t c_p
 // Launch on the context's stream; while DeepDream runs (ctx->latency_tiles) as a programmatic dependent of the
 // previous kernel: its CTAs may start (prologue, constant loads) while the predecessor drains, and every kernel
 // launched through here calls griddep_wait() before it touches anything the predecessor wrote.  DCV_PDL=0: plain.
+// `cluster` > 1: the grid is launched as thread-block clusters of that many CTAs (along x).
 template <typename... KArgs, typename... Args>
-cudaError_t launch_k(dcv_ctx* ctx, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, Args... args) {
+cudaError_t launch_kc(dcv_ctx* ctx, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, int cluster, Args... args) {
   static const int use_pdl = getenv("DCV_PDL") ? atoi(getenv("DCV_PDL")) : 1;     // measured: +2-4 % on DeepDream 512x512
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = ctx->stream;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cudaLaunchAttribute attr[2];
+  int n = 0;
+  if (use_pdl && ctx->latency_tiles) {
+    attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[n].val.programmaticStreamSerializationAllowed = 1;
+    ++n;
+  }
+  if (cluster > 1) {
+    attr[n].id = cudaLaunchAttributeClusterDimension;
+    attr[n].val.clusterDim.x = (unsigned)cluster; attr[n].val.clusterDim.y = 1; attr[n].val.clusterDim.z = 1;
+    ++n;
+  }
   cfg.attrs = attr;
-  cfg.numAttrs = (use_pdl && ctx->latency_tiles) ? 1 : 0;
+  cfg.numAttrs = n;
   return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
 }
+template <typename... KArgs, typename... Args>
+cudaError_t launch_k(dcv_ctx* ctx, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, Args... args) {
+  return launch_kc(ctx, kernel, grid, block, smem, 1, args...);
+}
 
-template <int BLOCK_N, int MODE>
+template <int BLOCK_N, int MODE, int SPLIT = 1>
 int launch_tc(dcv_ctx* ctx, const CUtensorMap& ta, const CUtensorMap& tb, TcParams p) {
   const int stage_bytes = tc_stage_bytes(MODE, BLOCK_N);
   const int res_bytes = tc_resident_bytes(MODE, BLOCK_N, p.k_blocks);
-  int stages = (SMEM_BUDGET - res_bytes) / stage_bytes;
+  const int red_bytes = (SPLIT - 1) * BLOCK_M * BLOCK_N * 4;        // the peers' partial sums (K split over a cluster)
+  int stages = (SMEM_BUDGET - res_bytes - red_bytes) / stage_bytes;
   if (stages > 8) stages = 8;
   if (stages < 2) return ctx->fail(DCV_ERR_UNSUPPORTED, "tc kernel: %d resident bytes leave no room for the pipeline", res_bytes);
   p.stages = stages;
-  const int smem = res_bytes + stages * stage_bytes + 1024 /*align slack*/ + 256 /*barriers*/;
+  const int smem = res_bytes + stages * stage_bytes + 1024 /*align slack*/ + 256 /*barriers*/ + red_bytes;
   // the attribute is per (kernel instantiation, device); remember the largest value already set
   static int smem_set[64] = {};
   cudaError_t e = cudaSuccess;
   if (smem_set[ctx->device & 63] < smem) {
-    e = cudaFuncSetAttribute(deconv_tc_kernel<BLOCK_N, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    e = cudaFuncSetAttribute(deconv_tc_kernel<BLOCK_N, MODE, SPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "cudaFuncSetAttribute(smem %d): %s", smem, cudaGetErrorString(e));
     smem_set[ctx->device & 63] = smem;
   }
   const int tiles = p.m_tiles * p.n_tiles;
-  const int grid = std::min(tiles, ctx->num_sms);
-  e = launch_k(ctx, deconv_tc_kernel<BLOCK_N, MODE>, dim3(grid), dim3(TC1_THREADS), (size_t)smem, ta, tb, p);
+  const int grid = SPLIT * std::min(tiles, ctx->num_sms / SPLIT);
+  e = launch_kc(ctx, deconv_tc_kernel<BLOCK_N, MODE, SPLIT>, dim3(grid), dim3(TC1_THREADS), (size_t)smem, SPLIT, ta, tb, p);
   if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "launch(deconv_tc_kernel<%d,%d>): %s", BLOCK_N, MODE, cudaGetErrorString(e));
   ctx->launches++;
   e = cudaGetLastError();
@@ -1295,6 +1310,18 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
   ProfScope ps(ctx, l.prof_class >= 0 ? l.prof_class : (l.nprod == 6 ? DCV_K_CONV_FWD : DCV_K_CONV_TC),
                2.0 * 9 * P * h * w * (double)l.k_real * l.n_real,
                2.0 * P * h * w * ((double)l.k_real + (out_f32 ? 2.0 * l.n_real : (double)l.n_real)));
+  // DeepDream's small layers: too few tiles to fill the GPU -> split K over a cluster of 2 or 4 CTAs per tile
+  static const int use_split = getenv("DCV_TC_SPLITK") ? atoi(getenv("DCV_TC_SPLITK")) : 1;
+  if (use_split && ctx->latency_tiles && mode == MODE_BAND && l.nprod == 1 && (bn == 64 || bn == 128)) {
+    const int tiles = p.m_tiles * p.n_tiles;
+    int split = 1;
+    if (tiles * 4 <= ctx->num_sms && p.k_blocks % 4 == 0 && p.k_blocks >= 8) split = 4;
+    else if (tiles * 2 <= ctx->num_sms && p.k_blocks % 2 == 0 && p.k_blocks >= 4) split = 2;
+    if (use_split > 1 && p.k_blocks % use_split == 0 && (use_split == 2 || use_split == 4)) split = use_split;   // forced (tests)
+    if (split == 4 && bn == 128) split = 2;      // three 64 KB partial accumulators would leave no room for the pipeline
+    if (split == 4) return launch_tc<64, MODE_BAND, 4>(ctx, ta, tb, p);
+    if (split == 2) return bn == 64 ? launch_tc<64, MODE_BAND, 2>(ctx, ta, tb, p) : launch_tc<128, MODE_BAND, 2>(ctx, ta, tb, p);
+  }
 #define TC_DISPATCH(BN)                                                    \
   switch (mode) {                                                          \
     case MODE_BAND: return launch_tc<BN, MODE_BAND>(ctx, ta, tb, p);       \

@@ -138,7 +138,11 @@ __device__ __forceinline__ void store_bf16_chunk(const TcParams& p, const uint32
   }
 }
 
-template <int BLOCK_N, int MODE>
+// SPLIT > 1 (DeepDream's small layers, MODE_BAND): the kernel runs as clusters of SPLIT CTAs that share one output tile
+// and each take 1/SPLIT of the 64-channel blocks of K.  CTAs 1.. of the cluster write their fp32 accumulators into the
+// shared memory of CTA 0 (st.shared::cluster), which adds them to its own in the epilogue - a 16 x 16 x 512 -> 512 conv
+// is 24 tiles of 24 K steps, i.e. 24 busy SMs out of 148 for 13 us; split four ways it is 96 SMs for 6 steps each.
+template <int BLOCK_N, int MODE, int SPLIT = 1>
 __global__ void __launch_bounds__(TC1_THREADS, 1)
 deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, TcParams p) {
   constexpr int B_TILE_BYTES = BLOCK_N * 128;
@@ -160,7 +164,14 @@ deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   uint64_t* tfull_bar = empty_bar + MAX_STAGES;       // [2] accumulator ready
   uint64_t* tempty_bar = tfull_bar + 2;               // [2] accumulator drained
   uint64_t* wres_bar = tempty_bar + 2;                // resident weights landed
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(wres_bar + 1);
+  uint64_t* red_full = wres_bar + 1;                  // SPLIT: the peers' partial sums of a tile have landed (CTA 0)
+  uint64_t* red_free = red_full + 1;                  // SPLIT: CTA 0 has read this CTA's partial sums (peers)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(red_free + 1);
+  // SPLIT: (SPLIT - 1) partial accumulators of 128 x BLOCK_N floats behind the barriers, as [peer][column / 4][row][4]
+  // (one 16-byte vector per row and column quad: rows - the lanes - are consecutive, so the writes and reads are
+  // free of bank conflicts)
+  float4* red = reinterpret_cast<float4*>(reinterpret_cast<uint8_t*>(full_bar) + 256);
+  const uint32_t crank = SPLIT > 1 ? cluster_ctarank() : 0u;
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -171,6 +182,8 @@ deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     for (int s = 0; s < p.stages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
     for (int b = 0; b < 2; ++b) { mbar_init(&tfull_bar[b], 1); mbar_init(&tempty_bar[b], TC1_EPI_WARPS); }
     mbar_init(wres_bar, 1);
+    mbar_init(red_full, (SPLIT - 1) * TC1_EPI_WARPS);
+    mbar_init(red_free, TC1_EPI_WARPS);
     fence_barrier_init();
   }
   if (warp == 1) {
@@ -178,7 +191,8 @@ deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     tmem_relinquish();
   }
   tc_fence_before();
-  __syncthreads();
+  if constexpr (SPLIT > 1) cluster_sync_all();          // the peers' barriers exist before anyone arrives on them
+  else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   // Programmatic dependent launch (DeepDream chains of small convs): the next kernel may run ITS prologue (barrier
@@ -189,7 +203,10 @@ deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   const int total_tiles = p.m_tiles * p.n_tiles;
   const int wp = p.w + 1;
   const int groups = (MODE == MODE_TAP) ? p.ntaps : 3; // stages per 64-channel block
-  const int total_st = groups * p.nprod * p.k_blocks; // stages per tile
+  const int kcl = p.k_blocks / SPLIT;                 // 64-channel blocks this CTA multiplies
+  const int kc0 = (int)crank * kcl;
+  const int total_st = groups * p.nprod * kcl;        // stages per tile
+  const int tile0 = blockIdx.x / SPLIT, tile_step = gridDim.x / SPLIT;
   const int kcols = p.k_blocks * BLOCK_K;             // columns of one operand plane
 
   if (warp == 0) {
@@ -205,12 +222,12 @@ deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       griddep_wait();                 // the activations were written by the previous kernel of the stream
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      for (int tile = tile0; tile < total_tiles; tile += tile_step) {
         const int m0 = (tile / p.n_tiles) * BLOCK_M;
         const int n0 = (tile % p.n_tiles) * BLOCK_N;
         for (int st = 0; st < total_st; ++st) {
-          const int kc = st % p.k_blocks;
-          const int gp = st / p.k_blocks;
+          const int kc = kc0 + st % kcl;
+          const int gp = st / kcl;
           const int g = gp / p.nprod, prod = gp % p.nprod;
           // operand planes of product `prod` (hi*hi, hi*mid, mid*hi, hi*lo, lo*hi, mid*mid); plane 0 when nprod == 1
           const int pa = (0x120100 >> (4 * prod)) & 3;       // A plane: 0,0,1,0,2,1
@@ -247,7 +264,7 @@ deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       int stage = 0;
       uint32_t phase = 0;
       int local = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++local) {
+      for (int tile = tile0; tile < total_tiles; tile += tile_step, ++local) {
         const int buf = local & 1;
         const uint32_t use = (uint32_t)(local >> 1);          // how many times this buffer was used before
         mbar_wait(&tempty_bar[buf], (use & 1) ^ 1);           // epilogue has drained it
@@ -257,8 +274,8 @@ deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
           const uint32_t a_addr = smem_u32(ring + stage * stage_bytes);
-          const int kc = st % p.k_blocks;
-          const int gp = st / p.k_blocks;
+          const int kc = kc0 + st % kcl;
+          const int gp = st / kcl;
           const int g = gp / p.nprod;
           if (elect_one()) {
             if constexpr (MODE == MODE_TAP) {
@@ -303,13 +320,42 @@ deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     const int rp = (p.h + 1) * wp;
     const float relu_lo = p.relu ? 0.f : -INFINITY;
     int local = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++local) {
+    for (int tile = tile0; tile < total_tiles; tile += tile_step, ++local) {
       const int m0 = (tile / p.n_tiles) * BLOCK_M;
       const int n0 = (tile % p.n_tiles) * BLOCK_N;
       const int buf = local & 1;
       const uint32_t use = (uint32_t)(local >> 1);
       mbar_wait(&tfull_bar[buf], use & 1);
       tc_fence_after();
+      if constexpr (SPLIT > 1) {
+        constexpr int CH = BLOCK_N >= 32 * NSUB ? 32 : 16;
+        const uint32_t t_acc = tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(buf * ACC_COLS);
+        if (crank != 0) {
+          // a peer: hand the partial sums to CTA 0 and go on to the next tile
+          mbar_wait_cluster(red_free, (uint32_t)(local & 1) ^ 1u);      // CTA 0 has read the previous tile's
+          const uint32_t dst0 = mapa_u32(smem_u32(red), 0) +
+                                (uint32_t)((((int)crank - 1) * (BLOCK_N / 4) * BLOCK_M + lg * 32 + lane) * 16);
+#pragma unroll 1
+          for (int c0 = sub * CH; c0 < BLOCK_N; c0 += NSUB * CH) {
+            uint32_t v[32];
+            if constexpr (CH == 32) tmem_ld32(t_acc + (uint32_t)c0, v);
+            else tmem_ld16(t_acc + (uint32_t)c0, v);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < CH / 4; ++i)
+              st_cluster_v4(dst0 + (uint32_t)((c0 / 4 + i) * BLOCK_M * 16), v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+          }
+          fence_acq_rel_cluster();
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) {
+            mbar_arrive_remote_release(red_full, 0);
+            mbar_arrive(&tempty_bar[buf]);
+          }
+          continue;
+        }
+        mbar_wait_cluster(red_full, (uint32_t)(local & 1));
+      }
       const int r = m0 + lg * 32 + lane;                      // this thread's output row
       const int q = r % rp;
       const int y = q / wp, x = q % wp;
@@ -323,6 +369,20 @@ deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         if constexpr (CHUNK == 32) tmem_ld32(t_row + (uint32_t)c0, v);
         else tmem_ld16(t_row + (uint32_t)c0, v);
         tmem_ld_wait();
+        if constexpr (SPLIT > 1) {               // add the peers' partial sums, in CTA order
+          const float4* rp4 = red + (size_t)(c0 / 4) * BLOCK_M + lg * 32 + lane;
+#pragma unroll
+          for (int sp = 0; sp < SPLIT - 1; ++sp) {
+#pragma unroll
+            for (int i = 0; i < CHUNK / 4; ++i) {
+              const float4 u = rp4[(size_t)(sp * (BLOCK_N / 4) + i) * BLOCK_M];
+              v[4 * i] = __float_as_uint(__uint_as_float(v[4 * i]) + u.x);
+              v[4 * i + 1] = __float_as_uint(__uint_as_float(v[4 * i + 1]) + u.y);
+              v[4 * i + 2] = __float_as_uint(__uint_as_float(v[4 * i + 2]) + u.z);
+              v[4 * i + 3] = __float_as_uint(__uint_as_float(v[4 * i + 3]) + u.w);
+            }
+          }
+        }
         if constexpr (KSPLIT > 1) {              // add the other K-split accumulators
 #pragma unroll
           for (int sp = 1; sp < KSPLIT; ++sp) {
@@ -413,12 +473,18 @@ deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&tempty_bar[buf]);
+      if (lane == 0) {
+        mbar_arrive(&tempty_bar[buf]);
+        if constexpr (SPLIT > 1) {               // the peers may overwrite their part of `red`
+          for (uint32_t c = 1; c < (uint32_t)SPLIT; ++c) mbar_arrive_remote_release(red_free, c);
+        }
+      }
     }
   }
 
   tc_fence_before();
-  __syncthreads();
+  if constexpr (SPLIT > 1) cluster_sync_all();          // no CTA leaves while a peer may still write to it or arrive on it
+  else __syncthreads();
   if (warp == 1) tmem_dealloc(tmem_base, TMEM_COLS);
 }
 

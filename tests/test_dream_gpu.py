@@ -191,3 +191,41 @@ def test_dream_at_config5_size_runs_and_is_deterministic():
     assert a.shape == img.shape and np.isfinite(a).all()
     assert np.array_equal(a, b)
     assert rel_l2(a, img) > 1e-3
+
+
+_SPLITK_SCRIPT = r"""
+import sys, numpy as np
+from deconv_api_b200 import synth, vgg16
+model = vgg16.VGG16(weights=None, include_top=False, input_shape=(None, None, 3), seed=9, bias=True)
+layers = {"block3_conv3": 1.0, "block4_conv3": 1.5, "block5_conv3": 2.0}
+out = {}
+for hw in ((64, 64), (200, 184)):
+    img = synth.caffe_preprocess(synth.smooth_image_u8(5, *hw))
+    eng = model.bound_engine(upto="block5_conv3")
+    g, loss = eng.dream_gradient(img, [eng.index[n] for n in layers], list(layers.values()), precision="bf16")
+    g2, loss2 = eng.dream_gradient(img, [eng.index[n] for n in layers], list(layers.values()), precision="bf16")
+    assert np.array_equal(g, g2) and loss == loss2          # the cluster reduction adds in a fixed order
+    out["g%d" % hw[0]] = g
+    out["l%d" % hw[0]] = np.float64(loss)
+np.savez(sys.argv[1], **out)
+"""
+
+
+def test_cluster_split_k_variants_agree(tmp_path):
+    """DeepDream's deep layers have fewer tiles than SMs; the band kernel then runs as clusters of 2 or 4 CTAs per tile
+    that split K and reduce through CTA 0's shared memory (tc_kernel.cuh, SPLIT).  The rule picks the split per layer;
+    DCV_TC_SPLITK = 2 / 4 forces it on every layer it divides (clusters then walk several tiles: the hand-back of the
+    reduction buffer is exercised), 0 turns it off.  All variants must give the same gradient up to the fp32 summation
+    order (outputs are bf16: a last-place flip here and there)."""
+    import os, subprocess, sys
+    res = {}
+    for mode in ("0", "1", "2", "4"):
+        path = str(tmp_path / ("g%s.npz" % mode))
+        env = dict(os.environ, DCV_TC_SPLITK=mode, PYTHONPATH=os.pathsep.join(sys.path))
+        subprocess.run([sys.executable, "-c", _SPLITK_SCRIPT, path], check=True, env=env, timeout=300)
+        res[mode] = np.load(path)
+    for mode in ("1", "2", "4"):
+        for k in ("g64", "g200"):
+            assert rel_l2(res[mode][k], res["0"][k]) < 1e-2, (mode, k, rel_l2(res[mode][k], res["0"][k]))
+        for k in ("l64", "l200"):
+            assert abs(res[mode][k] - res["0"][k]) <= 1e-3 * abs(res["0"][k])
