@@ -10,6 +10,7 @@
 // roll, gradient prep (seed + ReLU mask), RMS partials, fused normalise + un-roll + update.
 #include "common.cuh"
 #include "internal.cuh"
+#include "tc_ptx.cuh"
 
 #include <algorithm>
 #include <cstdlib>
@@ -145,6 +146,248 @@ resize_bilinear_strip_kernel(const float* __restrict__ x, int H, int W, int C, i
   }
 }
 
+// Parity-slot form (default).  The strip kernel above spends its time on instruction issue, not on memory (ncu: 81 %
+// of the issue slots, DRAM at 52 %): every gathered load carried four instructions of 64-bit address arithmetic and
+// every output row a round of register copies between the "held" and the "needed" rows.  Here
+//  * a gathered load's address is the thread's pointer into source row 0 plus row * row bytes: one IMAD.WIDE.U32,
+//  * the horizontally interpolated source row y lives in the register slot of y's parity (y0 and y1 = y0 + 1 never
+//    share a slot), tagged with its row number: a row is loaded and interpolated once, nothing is copied, the blend
+//    picks its two operands with a block-uniform select.
+// A variant that staged the source rows through shared memory (coalesced loads, gathers from shared) was slower
+// (0.215 against 0.152 ms at 8 x 1462^2 -> 2048^2): one barrier per source row serialises the block on the load latency.
+// Same expression, same operation order as the two kernels above.
+constexpr int RZ_THREADS = 256;
+constexpr int RZ_U = 3;
+constexpr int RZ_SEG = RZ_THREADS * RZ_U;
+constexpr int RZ_STRIP = 32;
+
+// *(const float*)(p + row * row_bytes), read-only path; the address is one mad.wide.u32
+__device__ __forceinline__ float ldg_row(const char* p, unsigned row, unsigned row_bytes) {
+  float v;
+  asm("{\n"
+      ".reg .u64 a;\n"
+      "mad.wide.u32 a, %1, %2, %3;\n"
+      "ld.global.nc.f32 %0, [a];\n"
+      "}\n" : "=f"(v) : "r"(row), "r"(row_bytes), "l"(p));
+  return v;
+}
+
+__global__ void __launch_bounds__(RZ_THREADS)
+resize_bilinear_slots_kernel(const float* __restrict__ x, int H, int W, int C, int OH, int OW, float* __restrict__ out) {
+  __shared__ int sy0[RZ_STRIP], sy1[RZ_STRIP];
+  __shared__ float sly[RZ_STRIP];
+  const int tid = threadIdx.x;
+  const int strips = (OH + RZ_STRIP - 1) / RZ_STRIP;
+  const int b = blockIdx.y / strips, oy_begin = (blockIdx.y % strips) * RZ_STRIP;
+  const int rows = min(RZ_STRIP, OH - oy_begin);
+  if (tid < RZ_STRIP) {
+    const int oy = min(oy_begin + tid, OH - 1);
+    const float sh = (float)H / (float)OH;
+    float fy = sh * ((float)oy + 0.5f) - 0.5f; if (fy < 0.f) fy = 0.f;
+    int y0 = (int)fy; if (y0 > H - 1) y0 = H - 1;
+    sy0[tid] = y0;
+    sy1[tid] = y0 + (y0 < H - 1 ? 1 : 0);
+    sly[tid] = fy - (float)y0;
+  }
+  const int n = OW * C;
+  const int f_begin = blockIdx.x * RZ_SEG;
+  const float sw = (float)W / (float)OW;
+  // per-thread byte pointers to the two neighbours in source row 0 of this image; row y is one 32 x 32 -> 64 bit
+  // multiply-add away (IMAD.WIDE.U32)
+  const unsigned row_bytes = (unsigned)W * (unsigned)C * 4u;
+  const char* img = reinterpret_cast<const char*>(x + (size_t)b * H * W * C);
+  const char *q0[RZ_U], *q1[RZ_U];
+  float lx[RZ_U];
+#pragma unroll
+  for (int k = 0; k < RZ_U; ++k) {
+    const int f = min(f_begin + tid + k * RZ_THREADS, n - 1);
+    const int ox = f / C, c = f - ox * C;
+    float fx = sw * ((float)ox + 0.5f) - 0.5f; if (fx < 0.f) fx = 0.f;
+    int x0 = (int)fx; if (x0 > W - 1) x0 = W - 1;
+    const int x1 = x0 + (x0 < W - 1 ? 1 : 0);
+    lx[k] = fx - (float)x0;
+    q0[k] = img + (size_t)(x0 * C + c) * 4; q1[k] = img + (size_t)(x1 * C + c) * 4;
+  }
+  __syncthreads();
+  float* o = out + ((size_t)b * OH + oy_begin) * n + f_begin + tid;
+  int tag_e = -1, tag_o = -1;                  // source rows held in the even / odd slot
+  float he[RZ_U], ho[RZ_U];
+#define RZ_LOAD_ROW(y, dst)                                                                  \
+  {                                                                                          \
+    float a[RZ_U], bb[RZ_U];                                                                 \
+    _Pragma("unroll") for (int k = 0; k < RZ_U; ++k) {                                       \
+      a[k] = ldg_row(q0[k], (unsigned)(y), row_bytes);                                       \
+      bb[k] = ldg_row(q1[k], (unsigned)(y), row_bytes);                                      \
+    }                                                                                        \
+    _Pragma("unroll") for (int k = 0; k < RZ_U; ++k) dst[k] = (1.f - lx[k]) * a[k] + lx[k] * bb[k];           \
+  }
+  for (int r = 0; r < rows; ++r, o += n) {
+    const int y0 = sy0[r], y1 = sy1[r];
+    const float ly = sly[r], hy = 1.f - ly;
+    if (y0 & 1) { if (tag_o != y0) { RZ_LOAD_ROW(y0, ho) tag_o = y0; } }
+    else        { if (tag_e != y0) { RZ_LOAD_ROW(y0, he) tag_e = y0; } }
+    if (y1 & 1) { if (tag_o != y1) { RZ_LOAD_ROW(y1, ho) tag_o = y1; } }
+    else        { if (tag_e != y1) { RZ_LOAD_ROW(y1, he) tag_e = y1; } }
+    const bool top_odd = y0 & 1, bot_odd = y1 & 1;
+#pragma unroll
+    for (int k = 0; k < RZ_U; ++k) {
+      const float top = top_odd ? ho[k] : he[k], bot = bot_odd ? ho[k] : he[k];
+      if (f_begin + tid + k * RZ_THREADS < n) o[k * RZ_THREADS] = hy * top + ly * bot;
+    }
+  }
+#undef RZ_LOAD_ROW
+}
+
+// Pipelined form (default): the source rows arrive through a ring of shared-memory stages filled by bulk async copies
+// (cp.async.bulk global -> shared, completion on an mbarrier), issued by a producer warp several rows ahead of the eight
+// consumer warps.  The parity-slot kernel above still waits for its own gathered loads (ncu: 13-20 warps stalled on the
+// long scoreboard per issued instruction, issue slots 41-58 % busy, DRAM 4.2-4.5 TB/s); here a consumer's loads are
+// shared-memory gathers by 32-bit addresses and the only wait is for data that HBM has not delivered yet.
+//  * A block owns RT_SEG consecutive elements of the flat output row over RT_STRIP output rows.  Every source row it
+//    needs is ONE contiguous run of floats (block-uniform start / length); the copy starts at the 16-byte boundary at or
+//    below the run and ends at the one at or above it (bulk copies move whole 16-byte units; both boundaries lie inside
+//    the allocation because allocations are 16-byte granular).
+//  * The rows are consumed in increasing order, each once: y0 / y1 of consecutive output rows never decrease, so "row
+//    not seen yet" is y > last, for the producer and the consumers alike.  The interpolated row goes to the register
+//    slot of its parity as in the kernel above.
+// Same expression, same operation order as the other forms.
+constexpr int RT_CONS_WARPS = 8;
+constexpr int RT_THREADS = 32 * (RT_CONS_WARPS + 1);
+constexpr int RT_U = 3;
+constexpr int RT_SEG = 32 * RT_CONS_WARPS * RT_U;
+constexpr int RT_STRIP = 32;
+constexpr int RT_MAX_STAGES = 8;
+
+__device__ __forceinline__ void bulk_load_1d(void* dst_smem, unsigned long long src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   tc::smem_u32(dst_smem)),
+               "l"(src), "r"(bytes), "r"(tc::smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ float lds_f32(uint32_t addr) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
+  return v;
+}
+
+__global__ void __launch_bounds__(RT_THREADS)
+resize_bilinear_pipe_kernel(const float* __restrict__ x, int H, int W, int C, int OH, int OW, float* __restrict__ out,
+                            int stage_bytes, int nstage) {
+  extern __shared__ __align__(128) uint8_t rt_stage[];
+  __shared__ int sy0[RT_STRIP], sy1[RT_STRIP];
+  __shared__ float sly[RT_STRIP];
+  __shared__ uint64_t full_bar[RT_MAX_STAGES], empty_bar[RT_MAX_STAGES];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int strips = (OH + RT_STRIP - 1) / RT_STRIP;
+  const int b = blockIdx.y / strips, oy_begin = (blockIdx.y % strips) * RT_STRIP;
+  const int rows = min(RT_STRIP, OH - oy_begin);
+  if (tid < RT_STRIP) {
+    const int oy = min(oy_begin + tid, OH - 1);
+    const float sh = (float)H / (float)OH;
+    float fy = sh * ((float)oy + 0.5f) - 0.5f; if (fy < 0.f) fy = 0.f;
+    int y0 = (int)fy; if (y0 > H - 1) y0 = H - 1;
+    sy0[tid] = y0;
+    sy1[tid] = y0 + (y0 < H - 1 ? 1 : 0);
+    sly[tid] = fy - (float)y0;
+  }
+  if (tid == 0) {
+    for (int s = 0; s < nstage; ++s) { tc::mbar_init(&full_bar[s], 1); tc::mbar_init(&empty_bar[s], RT_CONS_WARPS); }
+    tc::fence_barrier_init();
+  }
+  const int n = OW * C;
+  const int f_begin = blockIdx.x * RT_SEG;
+  const float sw = (float)W / (float)OW;
+  // the run of source floats of this segment: [s_lo, s_lo + len) of every source row
+  int s_lo, len;
+  {
+    float fa = sw * ((float)(f_begin / C) + 0.5f) - 0.5f; if (fa < 0.f) fa = 0.f;
+    int xa = (int)fa; if (xa > W - 1) xa = W - 1;
+    float fb = sw * ((float)(min(f_begin + RT_SEG - 1, n - 1) / C) + 0.5f) - 0.5f; if (fb < 0.f) fb = 0.f;
+    int xb = (int)fb; if (xb > W - 1) xb = W - 1;
+    xb += (xb < W - 1 ? 1 : 0);
+    s_lo = xa * C;
+    len = (xb + 1) * C - s_lo;
+  }
+  const unsigned long long row_bytes = (unsigned long long)W * C * 4ull;
+  const unsigned long long run0 = reinterpret_cast<unsigned long long>(x) + (unsigned long long)b * H * row_bytes + (unsigned long long)s_lo * 4ull;
+  __syncthreads();
+  if (warp == RT_CONS_WARPS) {
+    // ===== producer: one lane walks the strip's source rows =====
+    if (lane == 0) {
+      int last = -1, s = 0;
+      uint32_t ph = 0;
+      for (int r = 0; r < rows; ++r) {
+#pragma unroll
+        for (int t = 0; t < 2; ++t) {
+          const int y = t ? sy1[r] : sy0[r];
+          if (y > last) {
+            last = y;
+            const unsigned long long a = run0 + (unsigned long long)y * row_bytes;
+            const unsigned long long a0 = a & ~15ull;
+            const uint32_t bytes = (uint32_t)(((a + (unsigned long long)len * 4ull + 15ull) & ~15ull) - a0);
+            tc::mbar_wait(&empty_bar[s], ph ^ 1u);
+            tc::mbar_arrive_expect_tx(&full_bar[s], bytes);
+            bulk_load_1d(rt_stage + (size_t)s * stage_bytes, a0, bytes, &full_bar[s]);
+            if (++s == nstage) { s = 0; ph ^= 1u; }
+          }
+        }
+      }
+    }
+    return;
+  }
+  // ===== consumers =====
+  uint32_t g0[RT_U], g1[RT_U];                 // byte offsets of the two horizontal neighbours inside the run
+  float lx[RT_U];
+#pragma unroll
+  for (int k = 0; k < RT_U; ++k) {
+    const int f = min(f_begin + tid + k * 32 * RT_CONS_WARPS, n - 1);
+    const int ox = f / C, c = f - ox * C;
+    float fx = sw * ((float)ox + 0.5f) - 0.5f; if (fx < 0.f) fx = 0.f;
+    int x0 = (int)fx; if (x0 > W - 1) x0 = W - 1;
+    const int x1 = x0 + (x0 < W - 1 ? 1 : 0);
+    lx[k] = fx - (float)x0;
+    g0[k] = (uint32_t)(x0 * C + c - s_lo) * 4u; g1[k] = (uint32_t)(x1 * C + c - s_lo) * 4u;
+  }
+  float* o = out + ((size_t)b * OH + oy_begin) * n + f_begin + tid;
+  const uint32_t stage0 = tc::smem_u32(rt_stage);
+  float he[RT_U], ho[RT_U];
+  int last = -1, s = 0;
+  uint32_t ph = 0;
+  for (int r = 0; r < rows; ++r, o += n) {
+    const int y0 = sy0[r], y1 = sy1[r];
+    const float ly = sly[r], hy = 1.f - ly;
+#pragma unroll
+    for (int t = 0; t < 2; ++t) {
+      const int y = t ? y1 : y0;
+      if (y > last) {
+        last = y;
+        const uint32_t mis = (uint32_t)((run0 + (unsigned long long)y * row_bytes) & 15ull);
+        const uint32_t base = stage0 + (uint32_t)s * (uint32_t)stage_bytes + mis;
+        tc::mbar_wait(&full_bar[s], ph);
+        float v[RT_U];
+#pragma unroll
+        for (int k = 0; k < RT_U; ++k) v[k] = (1.f - lx[k]) * lds_f32(base + g0[k]) + lx[k] * lds_f32(base + g1[k]);
+        if (y & 1) {
+#pragma unroll
+          for (int k = 0; k < RT_U; ++k) ho[k] = v[k];
+        } else {
+#pragma unroll
+          for (int k = 0; k < RT_U; ++k) he[k] = v[k];
+        }
+        __syncwarp();
+        if (lane == 0) tc::mbar_arrive(&empty_bar[s]);
+        if (++s == nstage) { s = 0; ph ^= 1u; }
+      }
+    }
+    const bool top_odd = y0 & 1, bot_odd = y1 & 1;
+#pragma unroll
+    for (int k = 0; k < RT_U; ++k) {
+      const float top = top_odd ? ho[k] : he[k], bot = bot_odd ? ho[k] : he[k];
+      if (f_begin + tid + k * 32 * RT_CONS_WARPS < n) o[k * 32 * RT_CONS_WARPS] = hy * top + ly * bot;
+    }
+  }
+}
+
 // numpy.roll over the two spatial axes: out[b, y, x] = in[b, (y - oy) mod H, (x - ox) mod W].  One block row =
 // one output row: a row is W*C contiguous floats rotated by ox*C, so the kernel is two contiguous segment copies
 // per row with no per-element div/mod.
@@ -223,16 +466,30 @@ __global__ void add_diff_kernel(float* __restrict__ img, const float* __restrict
 
 void launch_resize_bilinear(const float* x, int B, int H, int W, int C, int OH, int OW, float* out, cudaStream_t s) {
   if ((size_t)B * OH * OW * C == 0) return;
+  // DCV_RESIZE_PIXEL: 0 = the pipelined kernel (default), 1 = one thread per pixel, 2 = the strip kernel, 3 = the parity-slot kernel
   static const int per_pixel = getenv("DCV_RESIZE_PIXEL") ? atoi(getenv("DCV_RESIZE_PIXEL")) : 0;
-  const int strips = (OH + RESIZE_STRIP - 1) / RESIZE_STRIP;
+  const int strips = (OH + RESIZE_STRIP - 1) / RESIZE_STRIP, zstrips = (OH + RZ_STRIP - 1) / RZ_STRIP;
+  // pipelined kernel: one stage holds the source run of an output segment (+ 16-byte alignment slack on both sides)
+  const double ratio = (double)W / (double)OW;
+  const long long run_floats = ((long long)((RT_SEG / C + 2) * ratio) + 4) * C;
+  const int stage_bytes = (int)((run_floats * 4 + 32 + 127) / 128 * 128);
+  const int nstage = std::min(RT_MAX_STAGES, 36 * 1024 / std::max(stage_bytes, 1));
+  const bool piped = per_pixel == 0 && run_floats < (1 << 20) && nstage >= 3 && zstrips == (OH + RT_STRIP - 1) / RT_STRIP;
+  const bool staged = (per_pixel == 0 || per_pixel == 3) && (long long)H * W * C < (1ll << 30);     // row * row bytes is a 32 x 32 bit product
   int b0 = 0;
   while (b0 < B) {                                   // gridDim.y <= 65535 per launch
-    const int nb = std::min(B - b0, std::max(1, 65535 / (per_pixel ? OH : strips)));
+    const int nb = std::min(B - b0, std::max(1, 65535 / (per_pixel == 1 ? OH : strips)));
     const float* xi = x + (size_t)b0 * H * W * C;
     float* oi = out + (size_t)b0 * OH * OW * C;
-    if (per_pixel && C <= 4) {
+    if (per_pixel == 1 && C <= 4) {
       dim3 grid((OW + 255) / 256, nb * OH);
       resize_bilinear_kernel<4><<<grid, 256, 0, s>>>(xi, H, W, C, OH, OW, oi);
+    } else if (piped) {
+      dim3 grid((OW * C + RT_SEG - 1) / RT_SEG, nb * zstrips);
+      resize_bilinear_pipe_kernel<<<grid, RT_THREADS, (size_t)nstage * stage_bytes, s>>>(xi, H, W, C, OH, OW, oi, stage_bytes, nstage);
+    } else if (staged) {
+      dim3 grid((OW * C + RZ_SEG - 1) / RZ_SEG, nb * zstrips);
+      resize_bilinear_slots_kernel<<<grid, RZ_THREADS, 0, s>>>(xi, H, W, C, OH, OW, oi);
     } else {
       dim3 grid((OW * C + 256 * RESIZE_U - 1) / (256 * RESIZE_U), nb * strips);
       resize_bilinear_strip_kernel<<<grid, 256, 0, s>>>(xi, H, W, C, OH, OW, oi);

@@ -229,3 +229,14 @@ def test_cluster_split_k_variants_agree(tmp_path):
             assert rel_l2(res[mode][k], res["0"][k]) < 1e-2, (mode, k, rel_l2(res[mode][k], res["0"][k]))
         for k in ("l64", "l200"):
             assert abs(res[mode][k] - res["0"][k]) <= 1e-3 * abs(res["0"][k])
+
+
+def test_resize_kernel_variants_are_bit_equal():
+    """The pipelined resize (bulk async copies into a shared-memory ring), the parity-slot, the strip and the
+    one-thread-per-pixel kernels compute the same expression in the same order: equal bits on ten shapes (odd sizes,
+    1 / 3 / 4 / 5 channels, enlargements and reductions up to 2.7x, 1 x 1 inputs, 2048 x 2048)."""
+    import os, subprocess, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "profiles", "resize_variants.py")], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    assert "variants equal" in r.stdout, r.stdout[-2000:]
