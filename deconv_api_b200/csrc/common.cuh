@@ -18,7 +18,7 @@ constexpr int kNumSMs = 148;   // B200: 2 dies x 74 SMs; grids are sized in mult
 // calling block in a fixed order (strided per-thread sums, then a shuffle / shared-memory tree): every block and
 // every run gets the same bits.  Result valid in all threads after the call.
 __device__ __forceinline__ void block_sum_partials(const double* __restrict__ partial, int np, double& ts, double& tq) {
-  __shared__ double ps_s[8], ps_q[8];
+  __shared__ double ps_s[16], ps_q[16];   // up to 16 warps per block
   double s = 0.0, q = 0.0;
   for (int k = threadIdx.x; k < np; k += blockDim.x) { s += partial[2 * k]; q += partial[2 * k + 1]; }
 #pragma unroll

@@ -3,6 +3,7 @@
 // All of them are bandwidth-bound: 128-bit accesses along the NHWC channel axis, grids sized in
 // multiples of the SM count, no shared-memory staging (no reuse to exploit).
 #include "common.cuh"
+#include "tc_ptx.cuh"
 
 namespace dcv {
 
@@ -259,8 +260,8 @@ __global__ void __launch_bounds__(256) deprocess_stats_kernel(const float* __res
 __device__ __forceinline__ float deprocess_norm(float v, float mean, float denom) {
   v = v - mean;            // x -= x.mean()
   v = v / denom;           // x /= (x.std() + epsilon)
-  v = v * 0.1f;            // x *= 0.1
-  v = v + 0.5f;            // x += 0.5
+  v = __fmul_rn(v, 0.1f);  // x *= 0.1   (separate roundings like numpy: no contraction into one FMA)
+  v = __fadd_rn(v, 0.5f);  // x += 0.5
   return v;
 }
 
@@ -307,6 +308,122 @@ __global__ void __launch_bounds__(256) deprocess_map_kernel(const float* __restr
   }
 }
 
+// Four quotients x / d by one divisor, correctly rounded (the bits of IEEE division) without a division per element:
+// with r = RN(1 / d): q = RN(x * r), remainder e = x - q * d (exact in one FMA), q' = RN(q + e * r) - the correction step
+// of the compiler's own division sequence, which spends a reciprocal, a Newton step and a range check on every
+// element.  The step is exact only while nothing under- or overflows: quotients outside [1e-20, 1e30] (zero, infinities
+// and NaNs included - the sum carries them) send all four through the division instruction; the caller passes r = NaN
+// when d itself is out of range (1 / d subnormal).  tests/test_ops_gpu.py compares with the dividing form bit for bit.
+__device__ __forceinline__ void quot4(const float (&x)[4], float d, float r, float (&q)[4]) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float q0 = x[i] * r;
+    q[i] = fmaf(fmaf(-q0, d, x[i]), r, q0);
+  }
+  const float sum = (fabsf(q[0]) + fabsf(q[1])) + (fabsf(q[2]) + fabsf(q[3]));
+  const float lo = fminf(fminf(fabsf(q[0]), fabsf(q[1])), fminf(fabsf(q[2]), fabsf(q[3])));
+  if (!(sum < 1e30f && lo > 1e-20f)) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) q[i] = x[i] / d;
+  }
+}
+
+// The map pass as a pipeline: a producer warp streams x through a ring of shared-memory stages with bulk async copies
+// (cp.async.bulk, completion on an mbarrier), eight consumer warps read 16 bytes per lane from the stage, apply the map
+// and store 4 bytes per lane.  The grid-stride form above waits for its own loads (ncu: 61 registers -> 4 blocks per
+// SM, 9 warps stalled on the long scoreboard per issued instruction, 3.3 TB/s); here the loads of the next DP_STAGES
+// chunks are always in flight.  Same arithmetic (deprocess_one / deprocess_norm).
+constexpr int DP_CONS_WARPS = 8;
+constexpr int DP_THREADS = 32 * (DP_CONS_WARPS + 1);
+constexpr int DP_CHUNK = 2048;                  // floats per stage (8 KB)
+constexpr int DP_STAGES = 5;
+
+__global__ void __launch_bounds__(DP_THREADS) deprocess_map_pipe_kernel(const float* __restrict__ x, size_t n,
+                                                                        const double* __restrict__ partial, int npartial,
+                                                                        uint8_t* __restrict__ out, float* __restrict__ norm) {
+  __shared__ __align__(128) float stage[DP_STAGES][DP_CHUNK];
+  __shared__ uint64_t full_bar[DP_STAGES], empty_bar[DP_STAGES];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const size_t n4 = n / 4;                                        // whole 16-byte units; the last n % 4 floats: block 0 below
+  const size_t chunks = (n4 * 4 + DP_CHUNK - 1) / DP_CHUNK;
+  if (tid == 0) {
+    for (int s = 0; s < DP_STAGES; ++s) { tc::mbar_init(&full_bar[s], 1); tc::mbar_init(&empty_bar[s], DP_CONS_WARPS); }
+    tc::fence_barrier_init();
+  }
+  __syncthreads();
+  auto issue = [&](size_t c, int s) {
+    const size_t first = c * DP_CHUNK;
+    const uint32_t bytes = (uint32_t)(min((size_t)DP_CHUNK, n4 * 4 - first) * 4);
+    tc::mbar_arrive_expect_tx(&full_bar[s], bytes);
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     tc::smem_u32(&stage[s][0])),
+                 "l"(reinterpret_cast<unsigned long long>(x + first)), "r"(bytes), "r"(tc::smem_u32(&full_bar[s]))
+                 : "memory");
+  };
+  // the first ring of copies goes out before the statistics are reduced
+  if (warp == DP_CONS_WARPS && lane == 0) {
+    size_t c = blockIdx.x;
+    for (int s = 0; s < DP_STAGES && c < chunks; ++s, c += gridDim.x) issue(c, s);
+  }
+  double ts, tq;
+  block_sum_partials(partial, npartial, ts, tq);
+  const double dmean = ts / (double)n;
+  double var = tq / (double)n - dmean * dmean;      // population variance (ddof = 0)
+  if (var < 0.0) var = 0.0;
+  const float mean = (float)dmean, denom = (float)(sqrt(var) + 1e-7);
+  const float rd = denom < 1e30f ? 1.f / denom : __int_as_float(0x7fc00000);     // denom >= 1e-7 by construction
+  if (warp == DP_CONS_WARPS) {
+    if (lane == 0) {
+      int s = 0;
+      uint32_t ph = 0;
+      size_t k = 0;
+      for (size_t c = blockIdx.x; c < chunks; c += gridDim.x, ++k) {
+        if (k >= DP_STAGES) {                        // re-use of a stage: wait until the consumers have drained it
+          tc::mbar_wait(&empty_bar[s], ph ^ 1u);
+          issue(c, s);
+        }
+        if (++s == DP_STAGES) { s = 0; ph ^= 1u; }
+      }
+    }
+  } else {
+    int s = 0;
+    uint32_t ph = 0;
+    for (size_t c = blockIdx.x; c < chunks; c += gridDim.x) {
+      const size_t first4 = c * (DP_CHUNK / 4);
+      const int cnt4 = (int)min((size_t)(DP_CHUNK / 4), n4 - first4);
+      tc::mbar_wait(&full_bar[s], ph);
+      const float4* st = reinterpret_cast<const float4*>(&stage[s][0]);
+#pragma unroll
+      for (int j = 0; j < DP_CHUNK / 4 / (32 * DP_CONS_WARPS); ++j) {
+        const int i = tid + j * 32 * DP_CONS_WARPS;
+        if (i < cnt4) {
+          const float4 a = st[i];
+          const float c[4] = {a.x - mean, a.y - mean, a.z - mean, a.w - mean};      // x -= x.mean()
+          float q[4];
+          quot4(c, denom, rd, q);                                                   // x /= (x.std() + epsilon)
+          uint32_t r = 0;
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            q[e] = __fadd_rn(__fmul_rn(q[e], 0.1f), 0.5f);                          // x *= 0.1; x += 0.5 (two roundings)
+            // clip to [0, 1] (NaN -> 0), * 255, truncate; the reference's second clip cannot change a value in [0, 255]
+            r |= (uint32_t)(__saturatef(q[e]) * 255.f) << (8 * e);
+          }
+          reinterpret_cast<uint32_t*>(out)[first4 + i] = r;
+          if (norm) reinterpret_cast<float4*>(norm)[first4 + i] = make_float4(q[0], q[1], q[2], q[3]);
+        }
+      }
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(&empty_bar[s]);
+      if (++s == DP_STAGES) { s = 0; ph ^= 1u; }
+    }
+  }
+  if (blockIdx.x == 0 && tid < (int)(n & 3)) {
+    const size_t j = n4 * 4 + tid;
+    out[j] = deprocess_one(x[j], mean, denom);
+    if (norm) norm[j] = deprocess_norm(x[j], mean, denom);
+  }
+}
+
 int deprocess_partials(size_t n) {
   return grid_for((n + 3) / 4, 256, 4);
 }
@@ -314,7 +431,12 @@ int deprocess_partials(size_t n) {
 void launch_deprocess(const float* x, size_t n, double* partial, int npartial, uint8_t* out, float* norm,
                       cudaStream_t s) {
   deprocess_stats_kernel<<<npartial, 256, 0, s>>>(x, n, partial);
-  deprocess_map_kernel<<<grid_for((n + 3) / 4, 256, 8), 256, 0, s>>>(x, n, partial, npartial, out, norm);
+  static const int pipe = getenv("DCV_DEPROCESS_PIPE") ? atoi(getenv("DCV_DEPROCESS_PIPE")) : 1;
+  // bulk copies need 16-byte aligned sources (the grid-stride form reads float4, so x is aligned that far anyway)
+  if (pipe && n >= 4 * DP_CHUNK && (reinterpret_cast<uintptr_t>(x) & 15) == 0)
+    deprocess_map_pipe_kernel<<<grid_for((n + DP_CHUNK - 1) / DP_CHUNK, 1, 5), DP_THREADS, 0, s>>>(x, n, partial, npartial, out, norm);
+  else
+    deprocess_map_kernel<<<grid_for((n + 3) / 4, 256, 8), 256, 0, s>>>(x, n, partial, npartial, out, norm);
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -291,3 +291,43 @@ def test_device_resident_ops_match_host_forms(engine):
         assert np.array_equal(od.cpu().numpy(), np.roll(img, (oy, ox), axis=(1, 2)))
     with pytest.raises(Exception):
         engine.roll_dev(idv.data_ptr(), img.shape, 1, 1, idv.data_ptr())                          # in place
+
+
+_DEPROCESS_SCRIPT = r"""
+import sys, numpy as np
+from deconv_api_b200 import engine as E
+eng = E.Engine(0)
+rng = np.random.default_rng(11)
+out = {}
+n = 3 * 2048 * 37 + 3                       # ragged: a partial last chunk and n % 4 != 0
+cases = {
+    "normal": rng.normal(2.0, 3.0, n),
+    "wide": rng.normal(0, 1, n) * 10.0 ** rng.uniform(-30, 30, n),          # 60 decades of magnitude
+    "tiny_std": 1.0 + rng.normal(0, 1e-6, n),
+    "huge": rng.normal(0, 1e37, n),
+    "subnormal": rng.normal(0, 1e-41, n),
+    "ones_mantissa": np.ldexp(2.0 - 2.0 ** -23, rng.integers(-20, 20, n)),  # divisor-like worst cases as dividends
+}
+for k, v in cases.items():
+    x = v.astype(np.float32)
+    out[k + "_u8"] = eng.deprocess(x, mutate=True)
+    out[k + "_norm"] = x
+np.savez(sys.argv[1], **out)
+"""
+
+
+def test_deprocess_pipelined_map_equals_division_form(tmp_path):
+    """The pipelined map pass (bulk async copies, quotient by reciprocal + two FMA corrections) against the grid-stride
+    form that divides (DCV_DEPROCESS_PIPE=0): uint8 output AND the normalised floats left in the argument are equal
+    bit for bit, on ordinary data and on data built to stress the quotient (60 decades of magnitude, std -> 0,
+    values next to overflow, subnormals, all-ones mantissas)."""
+    import os, subprocess, sys
+    res = {}
+    for mode in ("0", "1"):
+        path = str(tmp_path / ("d%s.npz" % mode))
+        env = dict(os.environ, DCV_DEPROCESS_PIPE=mode, PYTHONPATH=os.pathsep.join(sys.path))
+        subprocess.run([sys.executable, "-W", "ignore", "-c", _DEPROCESS_SCRIPT, path], check=True, env=env, timeout=300)
+        res[mode] = np.load(path)
+    for k in res["0"].files:
+        a, b = res["0"][k], res["1"][k]
+        assert np.array_equal(a.view(np.uint8 if a.dtype == np.uint8 else np.uint32), b.view(np.uint8 if b.dtype == np.uint8 else np.uint32)), k
