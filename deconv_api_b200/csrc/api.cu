@@ -523,6 +523,18 @@ static int ensure_nonneg(dcv_ctx* ctx, bool& nonneg, float* data, size_t n) {
 // block5_conv3 sweep against the reference's golden projections: rel-L2 1.8e-6 (FFMA 6.3e-6), 3.6x the throughput.
 static bool fp32_on_tc(const dcv_ctx* ctx, const Layer& l) { return ctx->fp32_tc != 0 && l.wd != nullptr; }
 
+// fp32 mode, two-plane scheme: the conv directly below conv layer j (no pool in between) can take this conv's result as
+// ready-made operand planes - the split pass between the two disappears (conv_tc.cu, tc_conv_bwd_exact).  Not when the
+// lower conv rectifies its input and this one does not (the ReLU pass in between works on the fp32 tensor).
+static const Layer* exact_fuse_target(dcv_ctx* ctx, int j, bool) {
+  if (j < 1 || !tc_bwd_exact_can_fuse_split()) return nullptr;
+  const Layer& l = ctx->net[j];
+  const Layer& nx = ctx->net[j - 1];
+  if (nx.kind != LK_CONV || nx.cout != l.cin || !fp32_on_tc(ctx, nx)) return nullptr;
+  if (nx.relu && !l.relu) return nullptr;
+  return &nx;
+}
+
 static int project_chunk(dcv_ctx* ctx, int layer, int foff, int n, int vis_mode, int precision, float* final_dst,
                          float** result) {
   enum { M_MAP, M_TENSOR, M_VEC };
@@ -530,6 +542,7 @@ static int project_chunk(dcv_ctx* ctx, int layer, int foff, int n, int vis_mode,
   int hcur = 0;
   bool rep_bf16 = false;             // TENSOR data currently lives in hb[hcur] (padded-flat bf16)
   bool exact_chain = false;          // fp32 mode: the current tensor was written by tc_conv_bwd_exact (its per-item maxima are known)
+  ctx->split_ready = -1;
   int lowest_conv = -1;
   for (int j = 0; j <= layer; ++j) if (ctx->net[j].kind == LK_CONV) { lowest_conv = j; break; }
   const int B = ctx->in_B;
@@ -625,7 +638,9 @@ static int project_chunk(dcv_ctx* ctx, int layer, int foff, int n, int vis_mode,
         Layer& cl = ctx->net[j - 1];
         if (j - 1 == 0 && final_dst) bufs[cur ^ 1] = final_dst;
         TRY(tc_prepare_backward_exact(ctx, cl));
-        TRY(tc_conv_bwd_exact_unpool(ctx, cl, bufs[cur], (const uint8_t*)l.sw.p, B, P, l.in_H, l.in_W, bufs[cur ^ 1], cl.relu, exact_chain));
+        const Layer* nx = exact_fuse_target(ctx, j - 1, final_dst != nullptr);
+        if (nx) TRY(tc_prepare_backward_exact(ctx, ctx->net[j - 2]));
+        TRY(tc_conv_bwd_exact_unpool(ctx, cl, bufs[cur], (const uint8_t*)l.sw.p, B, P, l.in_H, l.in_W, bufs[cur ^ 1], cl.relu, exact_chain, nx));
         exact_chain = true;
         cur ^= 1;
         h = l.in_H; w = l.in_W;
@@ -713,7 +728,9 @@ static int project_chunk(dcv_ctx* ctx, int layer, int foff, int n, int vis_mode,
           // fp32 mode on the tensor cores: operands split into three bf16 planes, six products (conv_tc.cu)
           if (fdst) bufs[cur ^ 1] = fdst;
           TRY(tc_prepare_backward_exact(ctx, ctx->net[j]));
-          TRY(tc_conv_bwd_exact(ctx, l, bufs[cur], P, h, w, bufs[cur ^ 1], l.relu, exact_chain));
+          const Layer* nx = exact_fuse_target(ctx, j, final_dst != nullptr);
+          if (nx) TRY(tc_prepare_backward_exact(ctx, ctx->net[j - 1]));
+          TRY(tc_conv_bwd_exact(ctx, l, bufs[cur], P, h, w, bufs[cur ^ 1], l.relu, exact_chain, nx));
           exact_chain = true;           // the next conv's input maxima come out of this one's epilogue
         } else {
           if (fdst) bufs[cur ^ 1] = fdst;

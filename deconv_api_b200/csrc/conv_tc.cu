@@ -197,6 +197,31 @@ __device__ __forceinline__ void split2h(float xs, __half& h, __half& l) {
   l = __float2half_rn(xs - __half2float(h));
 }
 
+// Largest L1 norm of an output channel's backward weights: max over n of sum over (tap, k) of |wd[tap][k][n]|, as float bits
+// (atomicMax on a zeroed word).  |conv output| <= that x the largest |input|: the scale of a fused split (tc_exact.cuh).
+__global__ void weight_l1max_kernel(const float* __restrict__ wd, int kdim, int ndim, uint32_t* __restrict__ out) {
+  const int n = blockIdx.x;
+  float s = 0.f;
+  for (int i = threadIdx.x; i < 9 * kdim; i += blockDim.x) s += fabsf(wd[(size_t)i * ndim + n]);
+  __shared__ float part[8];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int k = 0; k < (int)(blockDim.x >> 5); ++k) t += part[k];
+    atomicMax(out, __float_as_uint(t));
+  }
+}
+// scale source of a fused split: bound[item] = largest |input| of the item x the layer's L1 maximum (a little above, for
+// the rounding of both factors; pow2_scale_from_amax leaves a factor of four to spare besides)
+__global__ void split_bound_kernel(const uint32_t* __restrict__ amax_in, const uint32_t* __restrict__ l1max, int P,
+                                   uint32_t* __restrict__ bound) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < P) bound[i] = __float_as_uint(__uint_as_float(amax_in[i]) * __uint_as_float(*l1max) * 1.001f);
+}
+
 // fp32 compact (P,h,w,C) -> padded-flat fp16 with TWO planes per row: columns [hi | lo], c_pad each.
 __global__ void split2_pad_kernel(const float* __restrict__ x, int P, int h, int w, int C, int c_pad,
                                   const uint32_t* __restrict__ amax, __half* __restrict__ out) {
@@ -766,6 +791,8 @@ struct TcConvArgs {
   const uint32_t* amax_a = nullptr;
   const uint32_t* amax_b = nullptr;
   uint32_t* amax_out = nullptr;
+  uint16_t* split_out = nullptr;            // scheme 1: write the result as the next conv's fp16 planes (TcParams::split_out)
+  const uint32_t* split_scale = nullptr;
 };
 
 static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& a, const __nv_bfloat16* in, int P, int h, int w,
@@ -921,7 +948,8 @@ static int tc_prepare_backward_2h(dcv_ctx* ctx, Layer& l) {
   if (e != cudaSuccess) return ctx->fail(DCV_ERR_NOMEM, "cudaMalloc(weight maximum): %s", cudaGetErrorString(e));
   cudaMemsetAsync(l.tc.wd_amax, 0, 256, ctx->stream);
   absmax_kernel<<<grid_for(nw / 4 + 1, 256, 4), 256, 0, ctx->stream>>>(l.wd, nw, l.tc.wd_amax);
-  ctx->launches++;
+  weight_l1max_kernel<<<l.cin, 256, 0, ctx->stream>>>(l.wd, l.cout, l.cin, l.tc.wd_amax + 1);       // second word of the same block
+  ctx->launches += 2;
   const size_t n = (size_t)9 * 2 * n_pad * k_pad;
   e = cudaMalloc(&l.tc.wd2_f16, n * sizeof(__half));
   if (e != cudaSuccess) return ctx->fail(DCV_ERR_NOMEM, "cudaMalloc(two-plane backward weights): %s", cudaGetErrorString(e));
@@ -962,22 +990,37 @@ int tc_prepare_backward_exact(dcv_ctx* ctx, Layer& l) {
 // between does not raise them) - the extra pass over the input is skipped
 // up_sw != null: `in` is the pooled tensor (P,h/2,w/2,cout) and the unpool by these switches is done by the split pass
 static int tc_conv_bwd_2h(dcv_ctx* ctx, const Layer& l, const float* in, int P, int h, int w, float* out, int relu, bool chain,
-                          const uint8_t* up_sw = nullptr, int up_Bsw = 1) {
+                          const uint8_t* up_sw = nullptr, int up_Bsw = 1, const Layer* fuse_next = nullptr) {
   if (!l.tc.wd2_f16) return ctx->fail(DCV_ERR_STATE, "two-plane backward weights were not prepared for this layer");
   const int k_pad = tc_cpad(l.cout), n_pad = tc_cpad(l.cin);
-  const size_t elems = (size_t)P * (h + 1) * (w + 1) * 2 * k_pad;
-  int r = ctx->ws[4].ensure(ctx, elems * sizeof(__half));
+  // Per-item arrays, four of them: E[0], E[1] = exact maxima of |tensor| (read for this conv's input / filled by its
+  // epilogue for its output), S[0], S[1] = scale sources of fused splits (the bound this conv's input planes were scaled
+  // by when the previous conv wrote them / the bound this conv scales its output planes by).
+  const size_t slot = ((size_t)P * sizeof(uint32_t) + 255) & ~(size_t)255;
+  const bool grew = ctx->amax.cap < 4 * slot;
+  int r = ctx->amax.ensure(ctx, 4 * slot);
   if (r) return r;
-  // two arrays of per-item maxima: the one this conv reads and the one it fills for the next conv of the chain
-  const size_t half = ((size_t)P * sizeof(uint32_t) + 255) & ~(size_t)255;
-  const bool grew = ctx->amax.cap < 2 * half;
-  r = ctx->amax.ensure(ctx, 2 * half);
-  if (r) return r;
+  // input planes already written by the previous conv of the chain (fused split)?
+  const int in_planes = (chain && !grew && !up_sw && ctx->amax_cur >= 0) ? ctx->split_ready : -1;
+  ctx->split_ready = -1;
   if (grew || !chain || ctx->amax_cur < 0) { chain = false; ctx->amax_cur = 0; }
-  uint32_t* amax = (uint32_t*)((char*)ctx->amax.p + ctx->amax_cur * half);
-  uint32_t* amax_next = (uint32_t*)((char*)ctx->amax.p + (ctx->amax_cur ^ 1) * half);
+  auto arr = [&](int i) { return (uint32_t*)((char*)ctx->amax.p + (size_t)i * slot); };
+  uint32_t* amax = arr(ctx->amax_cur);                 // E of the input
+  uint32_t* amax_next = arr(ctx->amax_cur ^ 1);        // E of the output
+  const uint32_t* scale_in = in_planes >= 0 ? arr(2 + ctx->scale_cur) : amax;     // what the input planes were scaled by
+  uint32_t* scale_out = arr(2 + (in_planes >= 0 ? ctx->scale_cur ^ 1 : 0));
+  // plane buffers: ws[4] / ws[5]; the input sits in ws[4 + in_sel], a fused output goes to the other one
+  const int in_sel = in_planes >= 0 ? in_planes : 0;
+  const size_t elems = (size_t)P * (h + 1) * (w + 1) * 2 * k_pad;
+  if (in_planes < 0) { r = ctx->ws[4].ensure(ctx, elems * sizeof(__half)); if (r) return r; }
+  const bool fuse = fuse_next && fuse_next->tc.wd2_f16 && tc_cpad(fuse_next->cout) == n_pad && !(l.tc.wall2_f16);
+  if (fuse) {
+    r = ctx->ws[4 + (in_sel ^ 1)].ensure(ctx, (size_t)P * (h + 1) * (w + 1) * 2 * n_pad * sizeof(__half));
+    if (r) return r;
+  }
+  const __half* planes = (const __half*)ctx->ws[4 + in_sel].p;
   const size_t len = (size_t)(up_sw ? (h / 2) * (w / 2) : h * w) * l.cout, n_in = (size_t)P * len;   // elements actually read
-  {
+  if (in_planes < 0) {
     ProfScope ps(ctx, DCV_K_OTHER, 0.0, (chain ? 4.0 : 8.0) * n_in + (up_sw ? 1.0 * n_in : 0.0) + 4.0 * P * (h + 1) * (w + 1) * k_pad);
     if (!chain) {
       cudaMemsetAsync(amax, 0, (size_t)P * sizeof(uint32_t), ctx->stream);
@@ -985,12 +1028,16 @@ static int tc_conv_bwd_2h(dcv_ctx* ctx, const Layer& l, const float* in, int P, 
       absmax_items_kernel<<<dim3(bpi, P), 256, 0, ctx->stream>>>(in, len, amax);
       ctx->launches++;
     }
-    cudaMemsetAsync(amax_next, 0, (size_t)P * sizeof(uint32_t), ctx->stream);
     const size_t work = (size_t)P * (h + 1) * (w + 1) * (k_pad / 8);
     if (up_sw)
       split2_unpool_pad_kernel<<<grid_for(work, 256), 256, 0, ctx->stream>>>(in, up_sw, up_Bsw, P, h, w, l.cout, k_pad, amax, (__half*)ctx->ws[4].p);
     else
       split2_pad_kernel<<<grid_for(work, 256), 256, 0, ctx->stream>>>(in, P, h, w, l.cout, k_pad, amax, (__half*)ctx->ws[4].p);
+    ctx->launches++;
+  }
+  cudaMemsetAsync(amax_next, 0, (size_t)P * sizeof(uint32_t), ctx->stream);
+  if (fuse) {
+    split_bound_kernel<<<(P + 255) / 256, 256, 0, ctx->stream>>>(amax, l.tc.wd_amax + 1, P, scale_out);
     ctx->launches++;
   }
   ctx->amax_cur = -1;          // set again below once a kernel that fills amax_next has been queued
@@ -1004,9 +1051,9 @@ static int tc_conv_bwd_2h(dcv_ctx* ctx, const Layer& l, const float* in, int P, 
     p.total_tiles = (int)tt;
     p.relu = relu;
     p.out = out;
-    p.amax_a = amax; p.amax_b = l.tc.wd_amax;
+    p.amax_a = scale_in; p.amax_b = l.tc.wd_amax;
     CUtensorMap ta, tb;
-    r = make_tmap_patch(ctx, &ta, ctx->ws[4].p, (uint64_t)2 * k_pad, (uint64_t)(w + 1), (uint64_t)P * (h + 1));
+    r = make_tmap_patch(ctx, &ta, (void*)planes, (uint64_t)2 * k_pad, (uint64_t)(w + 1), (uint64_t)P * (h + 1));
     if (r) return r;
     r = make_tmap(ctx, &tb, l.tc.wall2_f16, (uint64_t)2 * LAST_N, (uint64_t)k_pad, LAST_N);
     if (r) return r;
@@ -1030,24 +1077,32 @@ static int tc_conv_bwd_2h(dcv_ctx* ctx, const Layer& l, const float* in, int P, 
   TcConvArgs a{l.tc.wd2_f16, k_pad, n_pad, l.cout, l.cin, relu, nullptr, 6};
   a.prof_class = DCV_K_CONV_TC;
   a.scheme = 1;
-  a.amax_a = amax; a.amax_b = l.tc.wd_amax;
+  a.amax_a = scale_in; a.amax_b = l.tc.wd_amax;
   a.amax_out = amax_next;
-  r = tc_conv_run(ctx, a, (const __nv_bfloat16*)ctx->ws[4].p, P, h, w, nullptr, out);
-  if (!r) ctx->amax_cur = (int)(amax_next != (uint32_t*)ctx->amax.p);
+  if (fuse) { a.split_out = (uint16_t*)ctx->ws[4 + (in_sel ^ 1)].p; a.split_scale = scale_out; }
+  r = tc_conv_run(ctx, a, (const __nv_bfloat16*)planes, P, h, w, nullptr, fuse ? nullptr : out);
+  if (!r) {
+    ctx->amax_cur = (int)(amax_next != (uint32_t*)ctx->amax.p);
+    if (fuse) { ctx->split_ready = in_sel ^ 1; ctx->scale_cur = (int)(scale_out != arr(2)); }
+  }
   return r;
 }
 
 bool tc_bwd_exact_fuses_unpool() { return fp32_scheme() == 1; }
+bool tc_bwd_exact_can_fuse_split() { return fp32_scheme() == 1; }
 
 int tc_conv_bwd_exact_unpool(dcv_ctx* ctx, const Layer& l, const float* pooled, const uint8_t* sw, int Bsw, int P, int h, int w,
-                             float* out, int relu, bool chain) {
+                             float* out, int relu, bool chain, const Layer* fuse_next) {
   if (fp32_scheme() != 1) return ctx->fail(DCV_ERR_UNSUPPORTED, "fused unpool needs the two-plane scheme");
   if ((h & 1) || (w & 1)) return ctx->fail(DCV_ERR_ARG, "fused unpool needs an even size");
-  return tc_conv_bwd_2h(ctx, l, pooled, P, h, w, out, relu, chain, sw, Bsw);
+  static const int fuse_split = getenv("DCV_FP32_FUSE_SPLIT") ? atoi(getenv("DCV_FP32_FUSE_SPLIT")) : 1;
+  return tc_conv_bwd_2h(ctx, l, pooled, P, h, w, out, relu, chain, sw, Bsw, fuse_split ? fuse_next : nullptr);
 }
 
-int tc_conv_bwd_exact(dcv_ctx* ctx, const Layer& l, const float* in, int P, int h, int w, float* out, int relu, bool chain) {
-  if (fp32_scheme() == 1) return tc_conv_bwd_2h(ctx, l, in, P, h, w, out, relu, chain);
+int tc_conv_bwd_exact(dcv_ctx* ctx, const Layer& l, const float* in, int P, int h, int w, float* out, int relu, bool chain,
+                      const Layer* fuse_next) {
+  static const int fuse_split = getenv("DCV_FP32_FUSE_SPLIT") ? atoi(getenv("DCV_FP32_FUSE_SPLIT")) : 1;
+  if (fp32_scheme() == 1) return tc_conv_bwd_2h(ctx, l, in, P, h, w, out, relu, chain, nullptr, 1, fuse_split ? fuse_next : nullptr);
   if (!l.tc.wd3_bf16) return ctx->fail(DCV_ERR_STATE, "split backward weights were not prepared for this layer");
   const int k_pad = tc_cpad(l.cout), n_pad = tc_cpad(l.cin);
   const size_t elems = (size_t)P * tc_split_elems(h, w, l.cout);
@@ -1212,7 +1267,8 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
   // fp32-accurate mode: accumulation in registers (tc_exact.cuh); DCV_TC_EXACT=2 forces N tile 64
   static const int exact_regs = getenv("DCV_TC_EXACT") ? atoi(getenv("DCV_TC_EXACT")) : 1;
   if (l.nprod == 6) {
-    if (!out_f32) return ctx->fail(DCV_ERR_UNSUPPORTED, "tc_conv: the split-operand mode writes fp32 only");
+    if (!out_f32 && !(l.split_out && l.scheme == 1))
+      return ctx->fail(DCV_ERR_UNSUPPORTED, "tc_conv: the split-operand mode writes fp32 (or, two-plane scheme, the next conv's planes)");
     int bn = l.n_real <= 16 ? 16 : (l.n_pad % 128 == 0 ? 128 : 64);
     if (bn == 128 && (long long)p.m_tiles * (l.n_pad / 128) < ctx->num_sms) bn = 64;      // few rows: more, smaller tiles
     if (exact_regs == 2 && bn == 128) bn = 64;
@@ -1224,6 +1280,7 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
     const int smem = stages * exact_stage_bytes(bn) + 1024 + 256;
     const int npl = l.scheme == 1 ? 2 : 3;
     p.amax_a = l.amax_a; p.amax_b = l.amax_b; p.amax_out = l.amax_out;
+    p.split_out = l.split_out; p.split_scale = l.split_scale;
     CUtensorMap ta, tb;
     int r = make_tmap(ctx, &ta, in, (uint64_t)p.rows, (uint64_t)npl * l.k_pad, BAND_ROWS);
     if (r) return r;

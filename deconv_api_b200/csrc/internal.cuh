@@ -67,8 +67,10 @@ struct dcv_ctx {
   DevBuf ws[6];        // projection workspace: [0],[1] ping-pong tensors, [2],[3] maps, [4],[5] bf16 ping-pong
   DevBuf feat_dev;
   DevBuf scratch;      // reduction partials
-  DevBuf amax;         // fp16 scheme: per-item float bit patterns of the largest |activation|, two arrays (read / filled)
+  DevBuf amax;         // fp16 scheme: per-item float bit patterns: two arrays of largest |activation| (read / filled), two of fused-split scale sources
   int amax_cur = -1;   // which of the two holds the maxima of the last exact conv's output (-1: none)
+  int split_ready = -1; // 0 / 1: the last exact conv wrote its result as the next conv's planes into ws[4 + split_ready]
+  int scale_cur = 0;    // which of the two scale-source arrays those planes were scaled by
   DevBuf stage;        // staging for host-buffer entry points
   // host-output projections: chunks are copied back on a second stream while the next chunk computes
   cudaStream_t copy_stream = nullptr;
@@ -134,11 +136,16 @@ int tc_conv_fwd_exact(dcv_ctx* ctx, const Layer& l, const float* in, int P, int 
 int tc_prepare_backward_exact(dcv_ctx* ctx, Layer& l);
 // chain: `in` is the output of the previous tc_conv_bwd_exact call on this context (possibly unpooled / rectified since):
 // its per-item maxima are already known
-int tc_conv_bwd_exact(dcv_ctx* ctx, const Layer& l, const float* in, int P, int h, int w, float* out, int relu, bool chain = false);
+// fuse_next (two-plane scheme): the layer whose backward conv consumes this result next, with nothing in between; the
+// result is then written as THAT conv's fp16 operand planes (no fp32 copy in `out`, no split pass in the next call,
+// which must be the next tc_conv_bwd_exact on this context, with chain = true)
+int tc_conv_bwd_exact(dcv_ctx* ctx, const Layer& l, const float* in, int P, int h, int w, float* out, int relu, bool chain = false,
+                      const Layer* fuse_next = nullptr);
+bool tc_bwd_exact_can_fuse_split();
 // the same with DPooling.down in front: `pooled` is (P,h/2,w/2,cout), unpooled by the switches inside the split pass
 bool tc_bwd_exact_fuses_unpool();
 int tc_conv_bwd_exact_unpool(dcv_ctx* ctx, const Layer& l, const float* pooled, const uint8_t* sw, int Bsw, int P, int h, int w,
-                             float* out, int relu, bool chain);
+                             float* out, int relu, bool chain, const Layer* fuse_next = nullptr);
 size_t tc_split_elems(int h, int w, int c);          // bf16 elements of one item split into three planes
 // backward conv; exactly one of out_bf16 (padded-flat, pitch l.tc.n_pad) / out_f32 (compact (P,h,w,l.cin)) is
 // non-null; relu < 0: the layer's own activation (deconvnet rule), 0/1: explicit (DeepDream uses 0)

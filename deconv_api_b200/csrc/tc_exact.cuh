@@ -177,7 +177,34 @@ conv_exact_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       const int y = q / wp, x = q % wp;
       float vmax = 0.f;                                 // largest |output| of this thread's row part (amax_out)
       const int item_of_row = r / rp;
-      if (owner && r < p.rows && x < p.w && y < p.h) {
+      if (SCHEME == 1 && p.split_out) {
+        // the result leaves as the next conv's two fp16 planes (all rows of the tile: pad rows and pad columns are zeros)
+        if (owner && r < p.rows) {
+          const bool is_pixel = x < p.w && y < p.h;
+          const float oscale = wscale_inv / pow2_scale_from_amax(__ldg(p.amax_a + item_of_row));
+          const float nscale = pow2_scale_from_amax(__ldg(p.split_scale + item_of_row));
+          uint16_t* dst = p.split_out + (size_t)r * (2 * (size_t)p.n_pad) + n0;
+#pragma unroll
+          for (int i = 0; i < COLS; i += 8) {
+            uint32_t hi[4], lo[4];
+#pragma unroll
+            for (int k = 0; k < 8; k += 2) {
+              float a0 = acc[i + k] * oscale, a1 = acc[i + k + 1] * oscale;
+              if (p.relu) { a0 = fmaxf(a0, 0.f); a1 = fmaxf(a1, 0.f); }
+              if (!is_pixel) { a0 = 0.f; a1 = 0.f; }
+              vmax = fmaxf(vmax, fmaxf(fabsf(a0), fabsf(a1)));
+              a0 *= nscale; a1 *= nscale;
+              const __half2 h2 = __floats2half2_rn(a0, a1);
+              const float2 hf = __half22float2(h2);
+              const __half2 l2 = __floats2half2_rn(a0 - hf.x, a1 - hf.y);
+              hi[k >> 1] = *reinterpret_cast<const uint32_t*>(&h2);
+              lo[k >> 1] = *reinterpret_cast<const uint32_t*>(&l2);
+            }
+            *reinterpret_cast<uint4*>(dst + i) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+            *reinterpret_cast<uint4*>(dst + p.n_pad + i) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+          }
+        }
+      } else if (owner && r < p.rows && x < p.w && y < p.h) {
         const int item = item_of_row;
         const float oscale = SCHEME == 0 ? 1.f : wscale_inv / pow2_scale_from_amax(__ldg(p.amax_a + item));   // per-item activation scale
         float* dst = p.out_f32 + (((size_t)item * p.h + y) * p.w + x) * p.n_real + n0;

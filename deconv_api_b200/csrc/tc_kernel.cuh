@@ -47,6 +47,12 @@ struct TcParams {
   const uint32_t* amax_a;
   const uint32_t* amax_b;
   uint32_t* amax_out;        // optional: per-item maximum of |output| (float bits, atomicMax; zeroed by the host): the scale of the NEXT conv
+  // conv_exact_kernel SCHEME 1, optional: instead of the fp32 result write it as the NEXT conv's operand - two fp16 planes
+  // [hi | lo] per padded-flat row, n_pad columns each, scaled by pow2_scale_from_amax(split_scale[item]); split_scale is
+  // an upper bound of the item's largest |output| that is known before this conv runs (largest |input| x the layer's
+  // largest L1 norm of an output channel's weights), so no pass over the finished output is needed to find a scale
+  uint16_t* split_out;
+  const uint32_t* split_scale;
   const float* bias;         // n_real entries added before the ReLU (forward conv), or null
   // DeepDream backward: fold the NEXT layer's gradient prep into this epilogue (bf16 plain store only):
   //   out = mask(act > 0) * (acc + prep_scale * act), act = that layer's bf16 tape in the output's layout

@@ -3,6 +3,7 @@
 // follow the PTX ISA "tcgen05 matrix descriptor" / "instruction descriptor" tables.
 #pragma once
 #include <cuda.h>
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
