@@ -253,5 +253,6 @@ conv_exact_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   if (warp == 1) tmem_dealloc(tmem_base, TMEM_COLS);
 }
 
+
 }  // namespace tc
 }  // namespace dcv

@@ -104,6 +104,9 @@ def test_conv3x3_vs_oracle(engine, fp32_kernels, B, H, W, cin, cout, bias, relu)
     (2, 9, 7, 72, 40, False),              # ragged channels, odd sizes, linear
     (300, 4, 4, 64, 64, True),
     (1, 33, 17, 8, 16, True),              # N tile 16 through the generic kernel (9 * 8 > 32)
+    (8, 56, 56, 64, 128, True),            # 64 output channels, K = 128, 204 tiles
+    (2, 120, 97, 64, 64, True),            # K = 64, odd sizes (tiles straddle image rows and the two items)
+    (40, 47, 45, 48, 64, False),           # ragged output channels (48 of 64), many items, linear
 ])
 def test_deconv3x3_fp32_vs_oracle(engine, fp32_kernels, B, H, W, cin, cout, relu):
     rng = np.random.default_rng(B * 1000 + H + cin + cout + 1)
