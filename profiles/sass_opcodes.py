@@ -4,7 +4,7 @@ import collections, os, re, subprocess, sys
 root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 lib = os.path.join(root, "deconv_api_b200", "_lib", "libdcv.so")
 out = subprocess.run(["cuobjdump", "-sass", lib], capture_output=True, text=True).stdout
-key = ("UTCHMMA", "UTCQMMA", "UTMALDG", "UTMASTG", "LDTM", "STTM", "UTCBAR", "UTCCP", "UTCATOMSWS", "SYNCS", "HMMA", "FFMA", "STS", "LDS", "SHFL")
+key = ("UTCHMMA", "UTCQMMA", "UTMALDG", "UTMASTG", "LDTM", "STTM", "UTCBAR", "UTCCP", "UTCATOMSWS", "UBLKCP", "SYNCS", "HMMA", "FFMA", "STS", "LDS", "SHFL")
 kern, hist, total = None, {}, collections.Counter()
 for line in out.splitlines():
     m = re.search(r"Function : (\S+)", line)
@@ -20,9 +20,9 @@ for line in out.splitlines():
         total[op.split(".")[0]] += 1
 print("library:", os.path.relpath(lib, root), "- opcode counts from `cuobjdump -sass` (static instruction counts)")
 print("whole library:", {k: total[k] for k in key if total[k]})
-for k in sorted(hist, key=lambda n: -sum(v for o, v in hist[n].items() if o.startswith(("UTC", "UTMA", "LDTM")))):
+for k in sorted(hist, key=lambda n: -sum(v for o, v in hist[n].items() if o.startswith(("UTC", "UTMA", "LDTM", "UBLKCP")))):
     h = hist[k]
-    tc = {o: v for o, v in sorted(h.items()) if o.startswith(("UTCHMMA", "UTMALDG", "UTMASTG", "LDTM", "UTCBAR", "SYNCS.ARRIVE", "SYNCS.PHASECHK"))}
+    tc = {o: v for o, v in sorted(h.items()) if o.startswith(("UTCHMMA", "UTMALDG", "UTMASTG", "LDTM", "UTCBAR", "UBLKCP", "SYNCS.ARRIVE", "SYNCS.PHASECHK"))}
     base = collections.Counter()
     for o, v in h.items():
         base[o.split(".")[0]] += v
