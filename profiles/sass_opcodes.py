@@ -10,7 +10,7 @@ for line in out.splitlines():
     m = re.search(r"Function : (\S+)", line)
     if m:
         kern = subprocess.run(["c++filt", m.group(1)], capture_output=True, text=True).stdout.strip()
-        kern = re.sub(r"\(.*", "", kern)
+        kern = re.sub(r"\((?!anonymous namespace\)).*", "", kern)       # drop the argument list, keep "(anonymous namespace)::"
         hist[kern] = collections.Counter()
         continue
     m = re.match(r"\s+/\*[0-9a-f]+\*/\s+(?:@!?U?P\d+\s+)?([A-Z0-9_.]+)", line)
