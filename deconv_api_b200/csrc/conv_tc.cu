@@ -1330,6 +1330,7 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
   // CTA).  A narrower tile gives more CTAs, but pays only if it does not add a wave: 65x65x512 runs one wave of 136
   // N=128 tiles instead of two waves of N=64 tiles, 129x129x256 one wave of 133 N=256 tiles instead of two of N=128.
   static const int bn_model = getenv("DCV_TC_BN_MODEL") ? atoi(getenv("DCV_TC_BN_MODEL")) : 1;
+  bool latency_pair = false;      // DeepDream: the rule below chose the CTA-pair kernel, whatever the tile count
   if (bn_model && ctx->latency_tiles) {
     auto cost = [&](int b) {
       const long long tiles = (long long)p.m_tiles * (l.n_pad / b);
@@ -1339,6 +1340,16 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
     int best = bn;
     for (int b = bn >> 1; b >= 64 && bn > 64; b >>= 1)
       if (cost(b) < cost(best)) best = b;
+    // The CTA-pair kernel (256 x 256 tiles on two SMs, tc_kernel2.cuh) is NOT a candidate here: measured with the rule
+    // extended to it (~146 on this scale per K step of a pair tile), DeepDream got slower - 512x512 0.756 -> 0.820 ms of
+    // kernels per iteration, 2048x2048 unchanged (6.63 / 6.59 ms): with the bias / gradient-prep epilogues of this path the
+    // pair kernel's four epilogue warps set its pace, not its MMAs.  DCV_TC_LATENCY_PAIR=1 switches the candidate on.
+    static const int lat_pair = getenv("DCV_TC_LATENCY_PAIR") ? atoi(getenv("DCV_TC_LATENCY_PAIR")) : 0;
+    if (lat_pair && bn == 256 && l.ntaps == 9 && l.nprod == 1 && out_bf16) {
+      const long long pairs = (long long)((p.rows + 255) / 256) * (l.n_pad / 256);
+      const long long pw = (pairs + ctx->num_sms / 2 - 1) / (ctx->num_sms / 2);
+      if (pw * 146 < cost(best)) { best = 256; latency_pair = true; }
+    }
     bn = best;
   } else {
     while (bn > 64 && (long long)p.m_tiles * (l.n_pad / bn) < ctx->num_sms) bn >>= 1;
@@ -1493,7 +1504,8 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
   const int m_tiles2 = (p.rows + 255) / 256;
   // Measured (profiles/r1_summary.md): the pair form gains 9-13 % at N tile 256 and nothing at N <= 128, where the
   // A-operand read of each SM (unchanged by pairing) sets the pace; DCV_TC_2CTA=2 forces it everywhere for tests.
-  if (l.ntaps == 9 && l.nprod == 1 && bn >= 64 && (use_pair == 2 || (use_pair == 1 && bn == 256)) && (long long)m_tiles2 * p.n_tiles >= ctx->num_sms / 2) {
+  if (l.ntaps == 9 && l.nprod == 1 && bn >= 64 && (use_pair == 2 || (use_pair == 1 && bn == 256)) &&
+      ((long long)m_tiles2 * p.n_tiles >= ctx->num_sms / 2 || latency_pair)) {
     // CTA-pair kernels (tc_kernel2.cuh): tiles of 256 rows x bn channels, each CTA stages half of the B tile
     TcParams q = p;
     q.m_tiles = m_tiles2;
