@@ -331,6 +331,15 @@ deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       const int n0 = (tile % p.n_tiles) * BLOCK_N;
       const int buf = local & 1;
       const uint32_t use = (uint32_t)(local >> 1);
+      // DeepDream backward: the gradient-prep activations of this thread's first column chunk are fetched before the wait
+      // for the MMAs (a small layer is one tile per CTA: the load's latency would otherwise sit at the end of the kernel)
+      constexpr int PRE_CHUNK = BLOCK_N >= 32 * NSUB ? 32 : 16;
+      uint4 pre_act[PRE_CHUNK / 8];
+      if (p.prep_act && crank == 0 && m0 + lg * 32 + lane < p.rows) {
+        const uint4* ap = reinterpret_cast<const uint4*>(p.prep_act + (size_t)(m0 + lg * 32 + lane) * p.n_pad + n0 + sub * PRE_CHUNK);
+#pragma unroll
+        for (int i = 0; i < PRE_CHUNK / 8; ++i) pre_act[i] = __ldg(ap + i);
+      }
       mbar_wait(&tfull_bar[buf], use & 1);
       tc_fence_after();
       if constexpr (SPLIT > 1) {
@@ -430,7 +439,7 @@ deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
               const uint4* ap = reinterpret_cast<const uint4*>(p.prep_act + (size_t)r * p.n_pad + n0 + c0);
 #pragma unroll
               for (int i = 0; i < CHUNK / 8; ++i) {
-                const uint4 t = __ldg(ap + i);
+                const uint4 t = c0 == sub * CHUNK ? pre_act[i] : __ldg(ap + i);
                 const uint32_t aw[4] = {t.x, t.y, t.z, t.w};
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
