@@ -725,7 +725,8 @@ cudaError_t launch_kc(dcv_ctx* ctx, void (*kernel)(KArgs...), dim3 grid, dim3 bl
   cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = ctx->stream;
   cudaLaunchAttribute attr[2];
   int n = 0;
-  if (use_pdl && ctx->latency_tiles) {
+  // not right after a kernel that wrote weights: deconv_tc_kernel fetches its first weight tiles BEFORE griddepcontrol.wait
+  if (use_pdl && ctx->latency_tiles && !ctx->pdl_hold) {
     attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[n].val.programmaticStreamSerializationAllowed = 1;
     ++n;
@@ -737,6 +738,7 @@ cudaError_t launch_kc(dcv_ctx* ctx, void (*kernel)(KArgs...), dim3 grid, dim3 bl
   }
   cfg.attrs = attr;
   cfg.numAttrs = n;
+  ctx->pdl_hold = 0;
   return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
 }
 template <typename... KArgs, typename... Args>
@@ -813,11 +815,13 @@ int tc_prepare_layer(dcv_ctx* ctx, Layer& l) {
   cudaError_t e = cudaMalloc(&l.tc.wd_bf16, n * sizeof(__nv_bfloat16));
   if (e != cudaSuccess) return ctx->fail(DCV_ERR_NOMEM, "cudaMalloc(bf16 weights): %s", cudaGetErrorString(e));
   pack_weights_tc_kernel<<<grid_for(n, 256), 256, 0, ctx->stream>>>(l.wd, l.cout, l.cin, l.tc.k_pad, l.tc.n_pad, l.tc.wd_bf16);
+  ctx->pdl_hold = 1;       // weights written by a kernel: the next conv must not start early (launch_kc)
   ctx->launches++;
   if (9 * l.cin <= LAST_N) {     // narrow last layer: all-tap weights for the GEMM + col2im kernel
     e = cudaMalloc(&l.tc.wall_bf16, (size_t)LAST_N * l.tc.k_pad * sizeof(__nv_bfloat16));
     if (e != cudaSuccess) return ctx->fail(DCV_ERR_NOMEM, "cudaMalloc(all-tap weights): %s", cudaGetErrorString(e));
     pack_weights_alltap_kernel<<<grid_for((size_t)LAST_N * l.tc.k_pad, 256), 256, 0, ctx->stream>>>(l.wd, l.cout, l.cin, l.tc.k_pad, l.tc.wall_bf16);
+    ctx->pdl_hold = 1;       // weights written by a kernel: the next conv must not start early (launch_kc)
     ctx->launches++;
   }
   e = cudaGetLastError();
@@ -909,6 +913,7 @@ int tc_prepare_forward_exact(dcv_ctx* ctx, Layer& l) {
   cudaError_t e = cudaMalloc(&l.tc.wf3_bf16, n * sizeof(__nv_bfloat16));
   if (e != cudaSuccess) return ctx->fail(DCV_ERR_NOMEM, "cudaMalloc(split forward weights): %s", cudaGetErrorString(e));
   pack_weights_fwd3_kernel<<<grid_for(n / 3, 256), 256, 0, ctx->stream>>>(l.w, l.cin, l.cout, l.tc.fk_pad, l.tc.fn_pad, l.tc.wf3_bf16);
+  ctx->pdl_hold = 1;       // weights written by a kernel: the next conv must not start early (launch_kc)
   ctx->launches++;
   return 0;
 }
@@ -954,11 +959,13 @@ static int tc_prepare_backward_2h(dcv_ctx* ctx, Layer& l) {
   e = cudaMalloc(&l.tc.wd2_f16, n * sizeof(__half));
   if (e != cudaSuccess) return ctx->fail(DCV_ERR_NOMEM, "cudaMalloc(two-plane backward weights): %s", cudaGetErrorString(e));
   pack_weights_2h_kernel<<<grid_for(n / 2, 256), 256, 0, ctx->stream>>>(l.wd, l.cout, l.cin, k_pad, n_pad, l.tc.wd_amax, (__half*)l.tc.wd2_f16);
+  ctx->pdl_hold = 1;       // weights written by a kernel: the next conv must not start early (launch_kc)
   ctx->launches++;
   if (9 * l.cin <= LAST_N) {
     e = cudaMalloc(&l.tc.wall2_f16, (size_t)2 * LAST_N * k_pad * sizeof(__half));
     if (e != cudaSuccess) return ctx->fail(DCV_ERR_NOMEM, "cudaMalloc(two-plane all-tap weights): %s", cudaGetErrorString(e));
     pack_weights_alltap2h_kernel<<<grid_for((size_t)LAST_N * k_pad, 256), 256, 0, ctx->stream>>>(l.wd, l.cout, l.cin, k_pad, l.tc.wd_amax, (__half*)l.tc.wall2_f16);
+    ctx->pdl_hold = 1;       // weights written by a kernel: the next conv must not start early (launch_kc)
     ctx->launches++;
   }
   e = cudaGetLastError();
@@ -975,11 +982,13 @@ int tc_prepare_backward_exact(dcv_ctx* ctx, Layer& l) {
   cudaError_t e = cudaMalloc(&l.tc.wd3_bf16, n * sizeof(__nv_bfloat16));
   if (e != cudaSuccess) return ctx->fail(DCV_ERR_NOMEM, "cudaMalloc(split backward weights): %s", cudaGetErrorString(e));
   pack_weights_fwd3_kernel<<<grid_for(n / 3, 256), 256, 0, ctx->stream>>>(l.wd, l.cout, l.cin, k_pad, n_pad, l.tc.wd3_bf16);
+  ctx->pdl_hold = 1;       // weights written by a kernel: the next conv must not start early (launch_kc)
   ctx->launches++;
   if (9 * l.cin <= LAST_N) {          // narrow last layer: all-tap weights for the exact GEMM + col2im kernel
     e = cudaMalloc(&l.tc.wall3_bf16, (size_t)3 * LAST_N * k_pad * sizeof(__nv_bfloat16));
     if (e != cudaSuccess) return ctx->fail(DCV_ERR_NOMEM, "cudaMalloc(split all-tap weights): %s", cudaGetErrorString(e));
     pack_weights_alltap3_kernel<<<grid_for((size_t)LAST_N * k_pad, 256), 256, 0, ctx->stream>>>(l.wd, l.cout, l.cin, k_pad, l.tc.wall3_bf16);
+    ctx->pdl_hold = 1;       // weights written by a kernel: the next conv must not start early (launch_kc)
     ctx->launches++;
   }
   return 0;
@@ -1161,6 +1170,7 @@ int tc_conv_first(dcv_ctx* ctx, Layer& l, const float* x, int P, int h, int w, _
     cudaError_t e = cudaMalloc(&l.tc.wf0_bf16, (size_t)n_pad * 64 * sizeof(__nv_bfloat16));
     if (e != cudaSuccess) return ctx->fail(DCV_ERR_NOMEM, "cudaMalloc(first-layer weights): %s", cudaGetErrorString(e));
     pack_first_kernel<<<grid_for((size_t)n_pad * 64, 256), 256, 0, ctx->stream>>>(l.w, l.cin, l.cout, n_pad, l.tc.wf0_bf16);
+    ctx->pdl_hold = 1;       // weights written by a kernel: the next conv must not start early (launch_kc)
     ctx->launches++;
   }
   const size_t rows = (size_t)P * (h + 1) * (w + 1);
@@ -1191,6 +1201,7 @@ int tc_prepare_forward(dcv_ctx* ctx, Layer& l) {
   if (e != cudaSuccess) return ctx->fail(DCV_ERR_NOMEM, "cudaMalloc(bf16 forward weights): %s", cudaGetErrorString(e));
   // forward conv: K = cin, N = cout; l.w is [9][cin][cout] = [tap][k][n]
   pack_weights_tc_kernel<<<grid_for(n, 256), 256, 0, ctx->stream>>>(l.w, l.cin, l.cout, l.tc.fk_pad, l.tc.fn_pad, l.tc.wf_bf16);
+  ctx->pdl_hold = 1;       // weights written by a kernel: the next conv must not start early (launch_kc)
   ctx->launches++;
   return 0;
 }

@@ -60,6 +60,7 @@ struct dcv_ctx {
   std::vector<Layer> net;
   int tape_upto = -1;
   int latency_tiles = 0;   // 1 while DeepDream runs: N tiles chosen by the wave/cycle model (conv_tc.cu)
+  int pdl_hold = 0;        // 1: a kernel that writes weights was queued; the next launch through launch_kc is a plain one
   int fwd_mode = 1;    // dcv_set_forward_mode: 0 = FFMA fp32, 1 = tcgen05 with split operands (default)
   int fp32_tc = 1;     // dcv_set_fp32_mode: backward convs of the DCV_FP32 chain, 0 = FFMA, 1 = split-operand tcgen05 (DCV_FP32_TC)
   int in_B = 0, in_H = 0, in_W = 0, in_C = 0;

@@ -225,6 +225,43 @@ deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
           for (int kc = 0; kc < p.k_blocks; ++kc)
             tma_load_2d(wres + (t * p.k_blocks + kc) * B_TILE_BYTES, &tmap_b, wres_bar, kc * BLOCK_K, t * p.n_pad);
       }
+      // One stage's loads.  which: 1 = the weight tiles (they never depend on the previous kernel), 2 = the activation box,
+      // 3 = both; the barrier is armed with the whole stage's bytes when the weights go out.
+      auto load_stage = [&](int st, int m0, int n0, int stage, int which) {
+        const int kc = kc0 + st % kcl;
+        const int gp = st / kcl;
+        const int g = gp / p.nprod, prod = gp % p.nprod;
+        // operand planes of product `prod` (hi*hi, hi*mid, mid*hi, hi*lo, lo*hi, mid*mid); plane 0 when nprod == 1
+        const int pa = (0x120100 >> (4 * prod)) & 3;       // A plane: 0,0,1,0,2,1
+        const int pb = (0x102010 >> (4 * prod)) & 3;       // B plane: 0,1,0,2,0,1
+        const int a_col = pa * kcols + kc * BLOCK_K;
+        uint8_t* a_dst = ring + stage * stage_bytes;
+        if (which & 1) mbar_arrive_expect_tx(&full_bar[stage], (uint32_t)stage_bytes);
+        if constexpr (MODE == MODE_TAP) {
+          const int shift = p.ntaps == 1 ? 0 : (g / 3 - 1) * wp + (g % 3 - 1);
+          if (which & 2) tma_load_2d(a_dst, &tmap_a, &full_bar[stage], a_col, m0 + shift);
+          if (which & 1) tma_load_2d(a_dst + A_TILE_BYTES, &tmap_b, &full_bar[stage], kc * BLOCK_K, (g * p.nprod_planes + pb) * p.n_pad + n0);
+        } else {
+          if (which & 2) tma_load_2d(a_dst, &tmap_a, &full_bar[stage], a_col, m0 + (g - 1) * wp - 1);
+          if constexpr (MODE == MODE_BAND) {
+            if (which & 1) {
+#pragma unroll
+              for (int dx = 0; dx < 3; ++dx)
+                tma_load_2d(a_dst + A_BAND_BYTES + dx * B_TILE_BYTES, &tmap_b, &full_bar[stage], kc * BLOCK_K,
+                            ((g * 3 + dx) * p.nprod_planes + pb) * p.n_pad + n0);
+            }
+          }
+        }
+      };
+      // Before the wait for the previous kernel: the weight tiles of the first stages of this CTA's first tile (the ring is
+      // empty, no slot to wait for).  Small DeepDream layers are one tile per CTA - the weights' trip from L2 then overlaps
+      // the predecessor's tail instead of following it.
+      int pre = 0;
+      if (tile0 < total_tiles) {
+        pre = total_st < p.stages ? total_st : p.stages;
+        const int m0 = (tile0 / p.n_tiles) * BLOCK_M, n0 = (tile0 % p.n_tiles) * BLOCK_N;
+        for (int st = 0; st < pre; ++st) load_stage(st, m0, n0, st, 1);
+      }
       griddep_wait();                 // the activations were written by the previous kernel of the stream
       int stage = 0;
       uint32_t phase = 0;
@@ -232,28 +269,11 @@ deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         const int m0 = (tile / p.n_tiles) * BLOCK_M;
         const int n0 = (tile % p.n_tiles) * BLOCK_N;
         for (int st = 0; st < total_st; ++st) {
-          const int kc = kc0 + st % kcl;
-          const int gp = st / kcl;
-          const int g = gp / p.nprod, prod = gp % p.nprod;
-          // operand planes of product `prod` (hi*hi, hi*mid, mid*hi, hi*lo, lo*hi, mid*mid); plane 0 when nprod == 1
-          const int pa = (0x120100 >> (4 * prod)) & 3;       // A plane: 0,0,1,0,2,1
-          const int pb = (0x102010 >> (4 * prod)) & 3;       // B plane: 0,1,0,2,0,1
-          const int a_col = pa * kcols + kc * BLOCK_K;
-          mbar_wait(&empty_bar[stage], phase ^ 1);
-          uint8_t* a_dst = ring + stage * stage_bytes;
-          mbar_arrive_expect_tx(&full_bar[stage], (uint32_t)stage_bytes);
-          if constexpr (MODE == MODE_TAP) {
-            const int shift = p.ntaps == 1 ? 0 : (g / 3 - 1) * wp + (g % 3 - 1);
-            tma_load_2d(a_dst, &tmap_a, &full_bar[stage], a_col, m0 + shift);
-            tma_load_2d(a_dst + A_TILE_BYTES, &tmap_b, &full_bar[stage], kc * BLOCK_K, (g * p.nprod_planes + pb) * p.n_pad + n0);
+          if (tile == tile0 && st < pre) {
+            load_stage(st, m0, n0, stage, 2);         // the weights of this stage are already on their way
           } else {
-            tma_load_2d(a_dst, &tmap_a, &full_bar[stage], a_col, m0 + (g - 1) * wp - 1);
-            if constexpr (MODE == MODE_BAND) {
-#pragma unroll
-              for (int dx = 0; dx < 3; ++dx)
-                tma_load_2d(a_dst + A_BAND_BYTES + dx * B_TILE_BYTES, &tmap_b, &full_bar[stage], kc * BLOCK_K,
-                            ((g * 3 + dx) * p.nprod_planes + pb) * p.n_pad + n0);
-            }
+            mbar_wait(&empty_bar[stage], phase ^ 1);
+            load_stage(st, m0, n0, stage, 3);
           }
           if (++stage == p.stages) { stage = 0; phase ^= 1; }
         }
