@@ -271,7 +271,10 @@ DCV_API int dcv_roll(dcv_ctx* ctx, const float* x, int B, int H, int W, int C, i
 /* ---- device-resident forms of the streaming operators above: x_dev / out_dev / sw_dev are device pointers owned
  * by the caller (16-byte aligned for pool / unpool), nothing is copied or allocated, and the call is asynchronous
  * on the context's stream (dcv_sync to wait).  Same arithmetic as the host-buffer forms; for pipelines that keep
- * their images on the GPU between DPooling.up / DPooling.down (deepdream.py:129-150) or DeepDream steps. --- */
+ * their images on the GPU between DPooling.up / DPooling.down (deepdream.py:129-150) or DeepDream steps.
+ * dcv_resize_bilinear_dev moves its source rows with 16-byte bulk copies: it may read the (at most 12) bytes between
+ * a row segment and the 16-byte boundaries around it, so x_dev must lie in an allocation that starts and ends on
+ * 16-byte boundaries (true of every cudaMalloc / caching-allocator block); x_dev itself needs only 4-byte alignment. --- */
 DCV_API int dcv_maxpool_switch_dev(dcv_ctx* ctx, const float* x_dev, int B, int H, int W, int C, float* pooled_dev, uint8_t* sw_dev);
 DCV_API int dcv_unpool_switch_dev(dcv_ctx* ctx, const float* x_dev, const uint8_t* sw_dev, int B, int H, int W, int C, float* out_dev);
 DCV_API int dcv_resize_bilinear_dev(dcv_ctx* ctx, const float* x_dev, int B, int H, int W, int C, int OH, int OW, float* out_dev);
