@@ -1351,15 +1351,16 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
     int best = bn;
     for (int b = bn >> 1; b >= 64 && bn > 64; b >>= 1)
       if (cost(b) < cost(best)) best = b;
-    // The CTA-pair kernel (256 x 256 tiles on two SMs, tc_kernel2.cuh) is NOT a candidate here: measured with the rule
-    // extended to it (~146 on this scale per K step of a pair tile), DeepDream got slower - 512x512 0.756 -> 0.820 ms of
-    // kernels per iteration, 2048x2048 unchanged (6.63 / 6.59 ms): with the bias / gradient-prep epilogues of this path the
-    // pair kernel's four epilogue warps set its pace, not its MMAs.  DCV_TC_LATENCY_PAIR=1 switches the candidate on.
-    static const int lat_pair = getenv("DCV_TC_LATENCY_PAIR") ? atoi(getenv("DCV_TC_LATENCY_PAIR")) : 0;
+    // The CTA-pair kernel (256 x 256 tiles on two SMs, tc_kernel2.cuh; ~146 on this scale per K step of a pair tile) is a
+    // candidate for layers of at least two waves of pairs.  Measured with eight epilogue warps per CTA (with four the
+    // bias / gradient-prep epilogues of this path set the kernel's pace): one 2048x2048 iteration 6.78 -> 6.07 ms of kernels;
+    // a single wave (129x129x256 at 512x512: 67 pairs) is slower than two waves of N = 128 tiles (0.752 -> 0.788 ms per
+    // iteration), hence the two-wave rule.  DCV_TC_LATENCY_PAIR=0 switches the candidate off.
+    static const int lat_pair = getenv("DCV_TC_LATENCY_PAIR") ? atoi(getenv("DCV_TC_LATENCY_PAIR")) : 1;
     if (lat_pair && bn == 256 && l.ntaps == 9 && l.nprod == 1 && out_bf16) {
       const long long pairs = (long long)((p.rows + 255) / 256) * (l.n_pad / 256);
       const long long pw = (pairs + ctx->num_sms / 2 - 1) / (ctx->num_sms / 2);
-      if (pw * 146 < cost(best)) { best = 256; latency_pair = true; }
+      if ((pw >= 2 || lat_pair == 2) && pw * 146 < cost(best)) { best = 256; latency_pair = true; }
     }
     bn = best;
   } else {

@@ -21,7 +21,11 @@ constexpr int BLOCK_K = 64;                 // bf16 elements = 128 bytes = one s
 constexpr int A_TILE_BYTES = BLOCK_M * 128;
 constexpr int BAND_ROWS = 136;              // 128 + 2 halo rows, rounded up to the 8-row swizzle atom
 constexpr int A_BAND_BYTES = BAND_ROWS * 128;
-constexpr int NUM_THREADS = 192;            // CTA-pair kernel (tc_kernel2.cuh): TMA warp, MMA warp, 4 epilogue warps
+#ifndef TC2_EPI_WARPS_CFG
+#define TC2_EPI_WARPS_CFG 8
+#endif
+constexpr int TC2_EPI_WARPS = TC2_EPI_WARPS_CFG;   // CTA-pair kernel (tc_kernel2.cuh): epilogue warps per CTA, 4 or 8 (two per TMEM lane quarter, interleaved column chunks)
+constexpr int NUM_THREADS = 64 + 32 * TC2_EPI_WARPS;   // + TMA warp, MMA warp
 constexpr int TC1_EPI_WARPS = 8;            // deconv_tc_kernel: two epilogue warps per TMEM lane quarter, interleaved column chunks (16 measured equal)
 constexpr int TC1_THREADS = 64 + 32 * TC1_EPI_WARPS;
 constexpr int SMEM_BUDGET = 200 * 1024;

@@ -92,7 +92,7 @@ deconv_tc2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     tma_prefetch_desc(&tmap_a);
     tma_prefetch_desc(&tmap_b);
     for (int s = 0; s < p.stages; ++s) { mbar_init(&full_bar[s], 2); mbar_init(&empty_bar[s], 1); }
-    for (int b = 0; b < 2; ++b) { mbar_init(&tfull_bar[b], 1); mbar_init(&tempty_bar[b], 8); }
+    for (int b = 0; b < 2; ++b) { mbar_init(&tfull_bar[b], 1); mbar_init(&tempty_bar[b], 2 * TC2_EPI_WARPS); }
     mbar_init(wres_bar, 2);
     fence_barrier_init();
   }
@@ -206,6 +206,8 @@ deconv_tc2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   } else {
     // ===== epilogue (both CTAs, own 128 TMEM lanes = own 128 rows of the 256-row tile) =====
     const int lg = warp & 3;
+    const int sub = (warp - 2) >> 2;                   // which of the quarter's warps: it takes every NSUB-th column chunk
+    constexpr int NSUB = TC2_EPI_WARPS / 4;
     const int rp = (p.h + 1) * wp;
     int local = 0;
     for (int tile = pair; tile < total_tiles; tile += npairs, ++local) {
@@ -222,7 +224,7 @@ deconv_tc2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       const bool is_pixel = in_range && (x < p.w) && (y < p.h);
       const uint32_t t_row = tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(buf * BLOCK_N);
 #pragma unroll 1
-      for (int c0 = 0; c0 < BLOCK_N; c0 += 32) {
+      for (int c0 = sub * 32; c0 < BLOCK_N; c0 += NSUB * 32) {
         uint32_t v[32];
         tmem_ld32(t_row + (uint32_t)c0, v);
         tmem_ld_wait();
