@@ -467,13 +467,14 @@ unpool_pad_kernel(const __nv_bfloat16* __restrict__ x, const uint8_t* __restrict
   const int owp = w + 1, orp = (h + 1) * owp;
   const int qh = (h + 2) / 2, qw = (w + 2) / 2;          // quads covering y in [0,h], x in [0,w]
   const int cg = c_pad / 8;
-  const size_t total = (size_t)P * qh * qw * cg;
-  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
-    const int g = (int)(i % cg);
-    size_t t = i / cg;
-    const int ox = (int)(t % qw); t /= qw;
-    const int oy = (int)(t % qh);
-    const int item = (int)(t / qh);
+  // grid rows (blockIdx.y) walk the items, 32-bit index arithmetic inside an item (no 64-bit divisions)
+  const unsigned per_item = (unsigned)qh * (unsigned)qw * (unsigned)cg;
+  for (int item = blockIdx.y; item < P; item += gridDim.y)
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < per_item; i += gridDim.x * blockDim.x) {
+    const int g = (int)(i % (unsigned)cg);
+    unsigned t = i / (unsigned)cg;
+    const int oy = (int)(t / (unsigned)qw);
+    const int ox = (int)(t - (unsigned)oy * (unsigned)qw);
     uint4 val = make_uint4(0u, 0u, 0u, 0u);
     uint32_t sidx[8];
 #pragma unroll
@@ -537,13 +538,14 @@ pool_pad_kernel(const __nv_bfloat16* __restrict__ x, int P, int h, int w, int C,
   const int iwp = w + 1, irp = (h + 1) * iwp;
   const int owp = pw + 1, orp = (ph + 1) * owp;
   const int cg = c_pad / 8;
-  const size_t total = (size_t)P * orp * cg;
-  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
-    const int g = (int)(i % cg);
-    const size_t r = i / cg;
-    const int q = (int)(r % orp);
-    const int item = (int)(r / orp);
-    const int oy = q / owp, ox = q % owp;
+  // grid rows (blockIdx.y) walk the items, 32-bit index arithmetic inside an item (no 64-bit divisions)
+  const unsigned per_item = (unsigned)orp * (unsigned)cg;
+  for (int item = blockIdx.y; item < P; item += gridDim.y)
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < per_item; i += gridDim.x * blockDim.x) {
+    const int g = (int)(i % (unsigned)cg);
+    const int q = (int)(i / (unsigned)cg);
+    const size_t r = (size_t)item * orp + q;
+    const int oy = q / owp, ox = q - oy * owp;
     uint4 res = make_uint4(0u, 0u, 0u, 0u);
     if (oy < ph && ox < pw) {
       const __nv_bfloat16* base = x + ((size_t)item * irp + (2 * oy) * iwp + 2 * ox) * c_pad + g * 8;
@@ -878,7 +880,10 @@ int tc_unpool(dcv_ctx* ctx, const __nv_bfloat16* x, const uint8_t* sw, int P, in
   const size_t work = (size_t)P * ((h + 2) / 2) * ((w + 2) / 2) * (c_pad / 8);
   // algorithmic bytes in this layout: 2 B/elem read at pooled size + 1 B switch, 2 B/elem written at full size
   ProfScope ps(ctx, DCV_K_UNPOOL, 0.0, (double)P * ph * pw * C * (2.0 + 1.0 + 8.0));
-  launch_k(ctx, unpool_pad_kernel, dim3(grid_for(work, 256)), dim3(256), (size_t)0, x, sw, P, Bsw, ph, pw, h, w, C, c_pad, out,
+  const size_t per_item = work / P;
+  const unsigned gx = (unsigned)std::min<size_t>((per_item + 255) / 256, (size_t)16 * kNumSMs);
+  const unsigned gy = (unsigned)std::min<size_t>((size_t)P, std::max<size_t>(1, (size_t)16 * kNumSMs / gx));
+  launch_k(ctx, unpool_pad_kernel, dim3(gx, gy), dim3(256), (size_t)0, x, sw, P, Bsw, ph, pw, h, w, C, c_pad, out,
            prep ? prep->act : (const __nv_bfloat16*)nullptr, prep ? prep->scale : 0.f, prep ? prep->relu : 0);
   ctx->launches++;
   return 0;
@@ -888,7 +893,10 @@ int tc_pool(dcv_ctx* ctx, const __nv_bfloat16* x, int P, int h, int w, int C, __
   const int c_pad = tc_cpad(C);
   const size_t work = (size_t)P * (h / 2 + 1) * (w / 2 + 1) * (c_pad / 8);
   ProfScope ps(ctx, DCV_K_POOL, 0.0, (double)P * h * w * C * (2.0 + 3.0 / 4.0));
-  launch_k(ctx, pool_pad_kernel, dim3(grid_for(work, 256)), dim3(256), (size_t)0, x, P, h, w, C, c_pad, out, sw);
+  const size_t per_item = work / P;
+  const unsigned gx = (unsigned)std::min<size_t>((per_item + 255) / 256, (size_t)16 * kNumSMs);
+  const unsigned gy = (unsigned)std::min<size_t>((size_t)P, std::max<size_t>(1, (size_t)16 * kNumSMs / gx));
+  launch_k(ctx, pool_pad_kernel, dim3(gx, gy), dim3(256), (size_t)0, x, P, h, w, C, c_pad, out, sw);
   ctx->launches++;
   return 0;
 }
