@@ -772,6 +772,26 @@ __global__ void __launch_bounds__(256) rank1_deconv_kernel(const float* __restri
   __syncthreads();
   const size_t obase = ((size_t)item * HW + p0) * cin;
   const int total = 64 * cin;
+  if ((cin & 3) == 0) {
+    // four channels per thread: one broadcast tap and one 16-byte weight read per tap and four outputs, one 16-byte store
+    // (the scalar form below spends ~40 instructions per 4-byte store and ran at 1.2 TB/s); same FMA order per output
+    const int c4 = cin >> 2;
+    const int npix = min(64, HW - p0);
+    for (int i = threadIdx.x; i < npix * c4; i += blockDim.x) {
+      const int pp = i / c4, cq = i - pp * c4;
+      const float* tp = tap + pp * 9;
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int t = 0; t < 9; ++t) {
+        const float tv = tp[t];
+        const float4 wv = *reinterpret_cast<const float4*>(wsl + t * cin + 4 * cq);
+        acc.x = fmaf(tv, wv.x, acc.x); acc.y = fmaf(tv, wv.y, acc.y); acc.z = fmaf(tv, wv.z, acc.z); acc.w = fmaf(tv, wv.w, acc.w);
+      }
+      if (relu) { acc.x = fmaxf(acc.x, 0.f); acc.y = fmaxf(acc.y, 0.f); acc.z = fmaxf(acc.z, 0.f); acc.w = fmaxf(acc.w, 0.f); }
+      *reinterpret_cast<float4*>(out + obase + (size_t)pp * cin + 4 * cq) = acc;
+    }
+    return;
+  }
   for (int i = threadIdx.x; i < total; i += blockDim.x) {
     const int pp = i / cin, ci = i % cin;
     if (p0 + pp >= HW) break;
