@@ -617,55 +617,65 @@ __global__ void __launch_bounds__(256) sumsq_bf16_kernel(const __nv_bfloat16* __
 }
 
 // Rank-1 first backward conv writing the padded-flat bf16 layout: out[r][ci] = relu(sum_tap map[p+tap] * wd[tap][f][ci]).
-// One block = RANK1_PX consecutive padded rows of one item.  A thread owns ONE channel pair for the whole block
-// (its 18 weights live in registers) and walks over the rows; the 9 map values of a row are shared-memory
-// broadcasts.  Stores are bf16x2, contiguous across the threads of a row: the kernel is bound by its HBM writes.
+// One block = RANK1_PX consecutive padded rows of one item.  A thread owns four channels for the whole block
+// (its 36 weights live in registers) and walks over the rows; the 9 map values of a row are shared-memory
+// broadcasts.  Stores are 8 bytes, contiguous across the threads of a row.
 constexpr int RANK1_PX = 128;
 __global__ void __launch_bounds__(256)
 rank1_pad_kernel(const float* __restrict__ maps, const float* __restrict__ wd, int cout, int cin, int c_pad,
                  const int* __restrict__ feat, int B, int h, int w, int relu, __nv_bfloat16* __restrict__ out) {
-  __shared__ float tap[RANK1_PX * 9];
+  __shared__ __align__(16) float tap[RANK1_PX * 12];          // 9 taps per row, padded to 12 floats: three 16-byte reads
   const int item = blockIdx.y;
   const int f = feat[item / B];
   const int wp = w + 1, rp = (h + 1) * wp;
   const int q0 = blockIdx.x * RANK1_PX;
   const float* m = maps + (size_t)item * h * w;
   for (int i = threadIdx.x; i < RANK1_PX * 9; i += blockDim.x) {
-    const int pp = i / 9, t = i % 9;
+    const int pp = i / 9, t = i - pp * 9;
     const int q = q0 + pp;
     float v = 0.f;
     if (q < rp) {
-      const int yc = q / wp, xc = q % wp;
+      const int yc = q / wp, xc = q - yc * wp;
       const int y = yc + t / 3 - 1, x = xc + t % 3 - 1;
       if (yc < h && xc < w && y >= 0 && y < h && x >= 0 && x < w) v = __ldg(m + y * w + x);
     }
-    tap[i] = v;                     // all-zero taps at pad positions -> relu(0) = 0 is written there
+    tap[pp * 12 + t] = v;           // all-zero taps at pad positions -> relu(0) = 0 is written there
   }
   __syncthreads();
-  const int cp = c_pad / 2;                         // channel pairs
-  const int lanes = blockDim.x / cp > 0 ? blockDim.x / cp : 1;     // row lanes when cp < blockDim.x
+  // A thread owns FOUR channels for the whole block (36 weights in registers) and walks over the rows: three 16-byte
+  // shared-memory broadcasts, 36 FMAs and one 8-byte store per row (two channels per thread: 62 instructions per 8
+  // bytes against 46 now - the kernel is bound by instruction issue, not by its HBM writes).  Same FMA order per output.
+  const int cq = c_pad / 4;                         // channel quads (c_pad is a multiple of 64)
   const int nrows = min(RANK1_PX, rp - q0);
-  for (int pair = threadIdx.x % cp; pair < cp; pair += (cp > (int)blockDim.x ? blockDim.x : cp)) {
-    const int c2 = pair * 2;
-    float wa[9], wb[9];
+  for (int quad = threadIdx.x % cq; quad < cq; quad += (cq > (int)blockDim.x ? blockDim.x : cq)) {
+    const int c4 = quad * 4;
+    float wv[9][4];
 #pragma unroll
     for (int t = 0; t < 9; ++t) {
       const float* wr = wd + ((size_t)t * cout + f) * cin;
-      wa[t] = c2 < cin ? __ldg(wr + c2) : 0.f;
-      wb[t] = c2 + 1 < cin ? __ldg(wr + c2 + 1) : 0.f;
-    }
-    for (int pp = (cp >= (int)blockDim.x ? 0 : threadIdx.x / cp); pp < nrows; pp += lanes) {
-      float a = 0.f, b = 0.f;
 #pragma unroll
-      for (int t = 0; t < 9; ++t) {
-        const float tv = tap[pp * 9 + t];
-        a = fmaf(tv, wa[t], a);
-        b = fmaf(tv, wb[t], b);
-      }
-      if (relu) { a = fmaxf(a, 0.f); b = fmaxf(b, 0.f); }
-      *reinterpret_cast<__nv_bfloat162*>(out + ((size_t)item * rp + q0 + pp) * c_pad + c2) = __floats2bfloat162_rn(a, b);
+      for (int e = 0; e < 4; ++e) wv[t][e] = c4 + e < cin ? __ldg(wr + c4 + e) : 0.f;
     }
-    if (cp <= (int)blockDim.x) break;
+    const int lanes = cq >= (int)blockDim.x ? 1 : (int)blockDim.x / cq;
+    for (int pp = (cq >= (int)blockDim.x ? 0 : threadIdx.x / cq); pp < nrows; pp += lanes) {
+      const float4 t0 = *reinterpret_cast<const float4*>(tap + pp * 12);
+      const float4 t1 = *reinterpret_cast<const float4*>(tap + pp * 12 + 4);
+      const float t8 = tap[pp * 12 + 8];
+      const float tv[9] = {t0.x, t0.y, t0.z, t0.w, t1.x, t1.y, t1.z, t1.w, t8};
+      float a[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int t = 0; t < 9; ++t)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) a[e] = fmaf(tv[t], wv[t][e], a[e]);
+      if (relu) {
+#pragma unroll
+        for (int e = 0; e < 4; ++e) a[e] = fmaxf(a[e], 0.f);
+      }
+      const __nv_bfloat162 p0 = __floats2bfloat162_rn(a[0], a[1]), p1 = __floats2bfloat162_rn(a[2], a[3]);
+      *reinterpret_cast<uint2*>(out + ((size_t)item * rp + q0 + pp) * c_pad + c4) =
+          make_uint2(*reinterpret_cast<const uint32_t*>(&p0), *reinterpret_cast<const uint32_t*>(&p1));
+    }
+    if (cq <= (int)blockDim.x) break;
   }
 }
 
