@@ -364,6 +364,28 @@ deconv_strip_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
             const float* p1 = ps_base + ((g + 2) % STRIP_P_SLOTS) * (128 * STRIP_PS);   // P(g-1)
             const float* p2 = ps_base + (g % STRIP_P_SLOTS) * (128 * STRIP_PS);         // P(g)
             float* orow = p.out + (((size_t)item * p.h + y) * p.w) * p.cout3;
+            if (p.cout3 == 3) {
+              // the usual case with every offset a compile-time constant (shared-memory reads with immediate offsets)
+              for (int x = xs + tt; x < xe; x += 32 * STRIP_TAIL_WARPS) {
+                const int i = x - hc0;
+                float a0 = 0.f, a1 = 0.f, a2 = 0.f;
+#pragma unroll
+                for (int dy = 0; dy < 3; ++dy) {
+                  const float* ps = (dy == 0 ? p0 : (dy == 1 ? p1 : p2)) + (i - 1) * STRIP_PS + dy * 9;
+#pragma unroll
+                  for (int dx = 0; dx < 3; ++dx) {
+                    if (dx > 0 || i > 0) {
+                      a0 += ps[dx * STRIP_PS + dx * 3];
+                      a1 += ps[dx * STRIP_PS + dx * 3 + 1];
+                      a2 += ps[dx * STRIP_PS + dx * 3 + 2];
+                    }
+                  }
+                }
+                if (p.relu_last) { a0 = fmaxf(a0, 0.f); a1 = fmaxf(a1, 0.f); a2 = fmaxf(a2, 0.f); }
+                float* o3 = orow + (size_t)x * 3;
+                o3[0] = a0; o3[1] = a1; o3[2] = a2;
+              }
+            } else
             for (int x = xs + tt; x < xe; x += 32 * STRIP_TAIL_WARPS) {
               const int i = x - hc0;                          // position inside the tile; i-1 = -1 only at x = 0 (zero pad)
               float acc[3] = {0.f, 0.f, 0.f};
