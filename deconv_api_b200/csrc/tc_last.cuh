@@ -196,6 +196,24 @@ deconv_last_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
       if (has_px && y < p.h && x < p.w) {
         float* dst = p.out + (((size_t)item * p.h + y) * p.w + x) * p.cout;
         const float* pp = ps + (ly * LAST_H + lx) * LAST_PS;
+        if (p.cout == 3) {
+          // the usual case with every offset a compile-time constant; same summation order as the loop below
+          float a3[3] = {0.f, 0.f, 0.f};
+#pragma unroll
+          for (int t = 0; t < 9; ++t) {
+#pragma unroll
+            for (int c = 0; c < 3; ++c) a3[c] += pp[((t / 3) * LAST_H + (t % 3)) * LAST_PS + t * 3 + c];
+          }
+          float sc = 1.f;
+          if (EXACT == 2) sc = wscale_inv / pow2_scale_from_amax(__ldg(p.amax_a + item));        // per-item activation scale
+#pragma unroll
+          for (int c = 0; c < 3; ++c) {
+            float acc = a3[c];
+            if (EXACT == 2) acc *= sc;
+            if (p.relu) acc = fmaxf(acc, 0.f);
+            dst[c] = acc;
+          }
+        } else
         for (int c = 0; c < p.cout; ++c) {
           float acc = 0.f;
 #pragma unroll
