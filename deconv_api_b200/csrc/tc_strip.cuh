@@ -47,6 +47,14 @@ constexpr int STRIP_NPX = 16 / STRIP_PROD_WARPS;        // pooled pixels per pro
 constexpr int STRIP_PXSTEP = 4 * STRIP_PROD_WARPS;      // distance between a thread's pooled pixels
 constexpr int STRIP_W_BYTES = 3 * STRIP_N * 128;        // resident conv weights: [dy][192][64] bf16
 constexpr int STRIP_WL_BYTES = 32 * 128;                // resident all-tap weights of the last layer: [32][64] bf16
+#ifndef STRIP_BACKOFF_NS
+#define STRIP_BACKOFF_NS 0
+#endif
+// how the waiting roles wait: 0 = try_wait with a suspend hint, N > 0 = test + nanosleep(N) (tc_ptx.cuh)
+__device__ __forceinline__ void strip_wait(uint64_t* bar, uint32_t parity) {
+  if constexpr (STRIP_BACKOFF_NS > 0) mbar_wait_backoff(bar, parity, STRIP_BACKOFF_NS);
+  else mbar_wait_parked(bar, parity);
+}
 constexpr int STRIP_PS = 29;                            // P row pitch in floats (27 used, odd: conflict-free)
 constexpr int STRIP_P_BYTES = 128 * STRIP_PS * 4;
 constexpr int STRIP_P_SLOTS = 3;
@@ -264,7 +272,7 @@ deconv_strip_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         const uint32_t buf = g & 1, use = g >> 1;
         const bool is_pixel = col_ok && tall >= 0 && tall < p.T && y < p.h;
         if (tall < 0) y = 0; else if (++y > p.h) y = 0;       // y of the next tile
-        mbar_wait_parked(&tfull_bar[buf], use & 1);
+        strip_wait(&tfull_bar[buf], use & 1);
         tc_fence_after();
         const uint32_t t_row = tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(buf * ACC_STRIDE);
         uint32_t packed[STRIP_EPI_PASSES][8];
@@ -314,7 +322,7 @@ deconv_strip_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         } else {
           // X tile (rows = positions, 128 B = 64 channels, 128-byte swizzle); no barrier among the warps: each one
           // credits the tile's mbarrier when its part is visible to the async proxy
-          mbar_wait_parked(&xempty_bar[buf], (use & 1) ^ 1);
+          strip_wait(&xempty_bar[buf], (use & 1) ^ 1);
           if (lane < STRIP_SEG) {
             const uint32_t rowp = xs_u32 + buf * A_TILE_BYTES + row_local * 128;
 #pragma unroll
@@ -343,7 +351,7 @@ deconv_strip_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
       const StripWalk k = strip_walk<LAST>(p, s);
       for (int j = 0; j < k.nt; ++j, ++g) {
         const uint32_t b = g & 1, use = g >> 1;
-        mbar_wait_parked(&pfull_bar[b], use & 1);
+        strip_wait(&pfull_bar[b], use & 1);
         tc_fence_after();
         uint32_t v[32];
         tmem_ld32(tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(b * ACC_STRIDE + PACC_OFF), v);
@@ -503,7 +511,7 @@ deconv_strip_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         const uint32_t yodd = (uint32_t)(y & 1);
         if (tin < 0) y = (tin == -1) ? 0 : p.h;              // state of the NEXT row; rows above the tensor are pad rows
         else if (++y > p.h) { y = 0; ++item; }
-        mbar_wait_parked(&in_empty[slot], (use & 1) ^ 1);
+        strip_wait(&in_empty[slot], (use & 1) ^ 1);
         const uint32_t dst = in_ring_u32 + slot * A_TILE_BYTES;
         if (key >= 0) {
           const uint32_t lq = lut_u32 + yodd * 4096u;                                  // corners (y & 1) * 2 + {0, 1}
