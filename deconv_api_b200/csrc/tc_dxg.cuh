@@ -218,11 +218,12 @@ deconv_dxg_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       if (issuer) tma_store_wait_read();                      // the previous tile's store has read the staging tile
       named_barrier_sync(1, 32 * DXG_EPI_WARPS);
       if (lane < SEG) {
+        // st.shared by 32-bit address (a generic-pointer store costs a dozen instructions of address conversion)
         const int row_local = SEG * lg + lane;
         const int j = c0 >> 3;                                // 16-byte chunk index of this thread's first 8 channels
-        uint8_t* rowp = out_tile + row_local * 128;
-        *reinterpret_cast<uint4*>(rowp + (((j) ^ (row_local & 7)) << 4)) = make_uint4(packed[0], packed[1], packed[2], packed[3]);
-        *reinterpret_cast<uint4*>(rowp + (((j + 1) ^ (row_local & 7)) << 4)) = make_uint4(packed[4], packed[5], packed[6], packed[7]);
+        const uint32_t rowp = smem_u32(out_tile) + (uint32_t)(row_local * 128);
+        sts128(rowp + (uint32_t)(((j) ^ (row_local & 7)) << 4), make_uint4(packed[0], packed[1], packed[2], packed[3]));
+        sts128(rowp + (uint32_t)(((j + 1) ^ (row_local & 7)) << 4), make_uint4(packed[4], packed[5], packed[6], packed[7]));
       }
       fence_proxy_async_smem();
       named_barrier_sync(1, 32 * DXG_EPI_WARPS);
