@@ -264,11 +264,6 @@ __device__ __forceinline__ void bulk_load_1d(void* dst_smem, unsigned long long 
                "l"(src), "r"(bytes), "r"(tc::smem_u32(bar))
                : "memory");
 }
-__device__ __forceinline__ float lds_f32(uint32_t addr) {
-  float v;
-  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
-  return v;
-}
 
 __global__ void __launch_bounds__(RT_THREADS)
 resize_bilinear_pipe_kernel(const float* __restrict__ x, int H, int W, int C, int OH, int OW, float* __restrict__ out,
@@ -366,7 +361,7 @@ resize_bilinear_pipe_kernel(const float* __restrict__ x, int H, int W, int C, in
         tc::mbar_wait(&full_bar[s], ph);
         float v[RT_U];
 #pragma unroll
-        for (int k = 0; k < RT_U; ++k) v[k] = (1.f - lx[k]) * lds_f32(base + g0[k]) + lx[k] * lds_f32(base + g1[k]);
+        for (int k = 0; k < RT_U; ++k) v[k] = (1.f - lx[k]) * tc::lds_f32(base + g0[k]) + lx[k] * tc::lds_f32(base + g1[k]);
         if (y & 1) {
 #pragma unroll
           for (int k = 0; k < RT_U; ++k) ho[k] = v[k];

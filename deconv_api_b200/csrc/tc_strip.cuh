@@ -346,6 +346,7 @@ deconv_strip_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     const int lg = warp & 3;
     const int tt = threadIdx.x - 32 * (2 + STRIP_EPI_WARPS);  // 0 .. 127
     int hj = -1, hnt = 0, ht = 0, hc0 = 0;                    // the previous tile (the middle of the col2im)
+    const uint32_t ps_u32 = smem_u32(ps_base);
     uint32_t g = 0;
     for (int s = blockIdx.x; s < p.total_strips; s += gridDim.x) {
       const StripWalk k = strip_walk<LAST>(p, s);
@@ -359,9 +360,11 @@ deconv_strip_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&pempty_bar[b]);
-        float* dst = ps_base + (g % STRIP_P_SLOTS) * (128 * STRIP_PS) + (lg * 32 + lane) * STRIP_PS;
+        // st.shared / ld.shared by 32-bit address in this role too (generic-pointer LD / ST carry 64-bit address math and
+        // take the generic path through the LSU)
+        const uint32_t dst = ps_u32 + (uint32_t)(((g % STRIP_P_SLOTS) * (128 * STRIP_PS) + (lg * 32 + lane) * STRIP_PS) * 4);
 #pragma unroll
-        for (int q = 0; q < 27; ++q) dst[q] = __uint_as_float(v[q]);
+        for (int q = 0; q < 27; ++q) sts32(dst + 4 * q, v[q]);
         named_barrier_sync(2, 32 * STRIP_TAIL_WARPS);         // P(g) complete in shared memory
         if (hj >= 1 && hj <= hnt - 2) {                       // top and bottom tiles of a strip are halo only
           const int y = ht % (p.h + 1), item = ht / (p.h + 1);
@@ -379,13 +382,13 @@ deconv_strip_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
                 float a0 = 0.f, a1 = 0.f, a2 = 0.f;
 #pragma unroll
                 for (int dy = 0; dy < 3; ++dy) {
-                  const float* ps = (dy == 0 ? p0 : (dy == 1 ? p1 : p2)) + (i - 1) * STRIP_PS + dy * 9;
+                  const uint32_t ps = ps_u32 + (uint32_t)((((g + 1 + dy) % STRIP_P_SLOTS) * (128 * STRIP_PS) + (i - 1) * STRIP_PS + dy * 9) * 4);
 #pragma unroll
                   for (int dx = 0; dx < 3; ++dx) {
                     if (dx > 0 || i > 0) {
-                      a0 += ps[dx * STRIP_PS + dx * 3];
-                      a1 += ps[dx * STRIP_PS + dx * 3 + 1];
-                      a2 += ps[dx * STRIP_PS + dx * 3 + 2];
+                      a0 += lds_f32(ps + (dx * STRIP_PS + dx * 3) * 4);
+                      a1 += lds_f32(ps + (dx * STRIP_PS + dx * 3 + 1) * 4);
+                      a2 += lds_f32(ps + (dx * STRIP_PS + dx * 3 + 2) * 4);
                     }
                   }
                 }
