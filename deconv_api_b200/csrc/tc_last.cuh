@@ -183,10 +183,11 @@ deconv_last_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
         uint32_t v[32];
         tmem_ld32(tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(buf * 64 + half * 32), v);
         tmem_ld_wait();
-        float* dst = ps + (half * 128 + lg * 32 + lane) * LAST_PS;
+        // st.shared / ld.shared by 32-bit address (generic LD / ST carry 64-bit address math and take the generic path)
+        const uint32_t dst = smem_u32(ps) + (uint32_t)((half * 128 + lg * 32 + lane) * LAST_PS * 4);
 #pragma unroll
         for (int j = 0; j < 27; ++j)
-          if (j < ncol) dst[j] = __uint_as_float(v[j]);
+          if (j < ncol) sts32(dst + 4 * j, v[j]);
       }
       tc_fence_before();
       __syncwarp();
@@ -198,11 +199,12 @@ deconv_last_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
         const float* pp = ps + (ly * LAST_H + lx) * LAST_PS;
         if (p.cout == 3) {
           // the usual case with every offset a compile-time constant; same summation order as the loop below
+          const uint32_t pp_u32 = smem_u32(pp);
           float a3[3] = {0.f, 0.f, 0.f};
 #pragma unroll
           for (int t = 0; t < 9; ++t) {
 #pragma unroll
-            for (int c = 0; c < 3; ++c) a3[c] += pp[((t / 3) * LAST_H + (t % 3)) * LAST_PS + t * 3 + c];
+            for (int c = 0; c < 3; ++c) a3[c] += lds_f32(pp_u32 + (uint32_t)((((t / 3) * LAST_H + (t % 3)) * LAST_PS + t * 3 + c) * 4));
           }
           float sc = 1.f;
           if (EXACT == 2) sc = wscale_inv / pow2_scale_from_amax(__ldg(p.amax_a + item));        // per-item activation scale
