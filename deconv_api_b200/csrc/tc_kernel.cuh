@@ -409,12 +409,12 @@ deconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         else tmem_ld16(t_row + (uint32_t)c0, v);
         tmem_ld_wait();
         if constexpr (SPLIT > 1) {               // add the peers' partial sums, in CTA order
-          const float4* rp4 = red + (size_t)(c0 / 4) * BLOCK_M + lg * 32 + lane;
+          const uint32_t rp4 = smem_u32(red) + (uint32_t)(((c0 / 4) * BLOCK_M + lg * 32 + lane) * 16);
 #pragma unroll
           for (int sp = 0; sp < SPLIT - 1; ++sp) {
 #pragma unroll
             for (int i = 0; i < CHUNK / 4; ++i) {
-              const float4 u = rp4[(size_t)(sp * (BLOCK_N / 4) + i) * BLOCK_M];
+              const float4 u = lds128_f32(rp4 + (uint32_t)((sp * (BLOCK_N / 4) + i) * BLOCK_M * 16));
               v[4 * i] = __float_as_uint(__uint_as_float(v[4 * i]) + u.x);
               v[4 * i + 1] = __float_as_uint(__uint_as_float(v[4 * i + 1]) + u.y);
               v[4 * i + 2] = __float_as_uint(__uint_as_float(v[4 * i + 2]) + u.z);
