@@ -44,6 +44,17 @@ __device__ __forceinline__ float lds_f32(uint32_t addr) {
   asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr) : "memory");
   return v;
 }
+// the same with a compile-time byte offset in the instruction (no register per address)
+template <int OFF>
+__device__ __forceinline__ float lds_f32_at(uint32_t base) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1+%2];" : "=f"(v) : "r"(base), "n"(OFF) : "memory");
+  return v;
+}
+template <int OFF>
+__device__ __forceinline__ void sts32_at(uint32_t base, uint32_t v) {
+  asm volatile("st.shared.b32 [%0+%1], %2;" ::"r"(base), "n"(OFF), "r"(v) : "memory");
+}
 __device__ __forceinline__ float4 lds128_f32(uint32_t addr) {
   float4 v;
   asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr) : "memory");

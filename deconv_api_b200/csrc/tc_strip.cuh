@@ -60,6 +60,18 @@ constexpr int STRIP_P_BYTES = 128 * STRIP_PS * 4;
 constexpr int STRIP_P_SLOTS = 3;
 
 constexpr int STRIP_TAIL_WARPS = 4;
+// tail warps: 27 floats of a P row to shared memory / the three channels of tap dx of a P row, offsets as immediates
+template <int Q>
+__device__ __forceinline__ void strip_store27(uint32_t dst, const uint32_t (&v)[32]) {
+  sts32_at<4 * Q>(dst, v[Q]);
+  if constexpr (Q + 1 < 27) strip_store27<Q + 1>(dst, v);
+}
+template <int DX>
+__device__ __forceinline__ void strip_tap3(uint32_t ps, float& a0, float& a1, float& a2) {
+  a0 += lds_f32_at<(DX * STRIP_PS + DX * 3) * 4>(ps);
+  a1 += lds_f32_at<(DX * STRIP_PS + DX * 3 + 1) * 4>(ps);
+  a2 += lds_f32_at<(DX * STRIP_PS + DX * 3 + 2) * 4>(ps);
+}
 __host__ __device__ constexpr int strip_threads(bool unpool, bool last) {
   return 64 + 32 * STRIP_EPI_WARPS + (last ? 32 * STRIP_TAIL_WARPS : 0) + (unpool ? 32 * STRIP_PROD_WARPS : 0);
 }
@@ -363,8 +375,7 @@ deconv_strip_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         // st.shared / ld.shared by 32-bit address in this role too (generic-pointer LD / ST carry 64-bit address math and
         // take the generic path through the LSU)
         const uint32_t dst = ps_u32 + (uint32_t)(((g % STRIP_P_SLOTS) * (128 * STRIP_PS) + (lg * 32 + lane) * STRIP_PS) * 4);
-#pragma unroll
-        for (int q = 0; q < 27; ++q) sts32(dst + 4 * q, v[q]);
+        strip_store27<0>(dst, v);
         named_barrier_sync(2, 32 * STRIP_TAIL_WARPS);         // P(g) complete in shared memory
         if (hj >= 1 && hj <= hnt - 2) {                       // top and bottom tiles of a strip are halo only
           const int y = ht % (p.h + 1), item = ht / (p.h + 1);
@@ -382,15 +393,11 @@ deconv_strip_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
                 float a0 = 0.f, a1 = 0.f, a2 = 0.f;
 #pragma unroll
                 for (int dy = 0; dy < 3; ++dy) {
+                  // row i-1 of P(g-2+dy), columns dy*9..: every further offset is an immediate of the load
                   const uint32_t ps = ps_u32 + (uint32_t)((((g + 1 + dy) % STRIP_P_SLOTS) * (128 * STRIP_PS) + (i - 1) * STRIP_PS + dy * 9) * 4);
-#pragma unroll
-                  for (int dx = 0; dx < 3; ++dx) {
-                    if (dx > 0 || i > 0) {
-                      a0 += lds_f32(ps + (dx * STRIP_PS + dx * 3) * 4);
-                      a1 += lds_f32(ps + (dx * STRIP_PS + dx * 3 + 1) * 4);
-                      a2 += lds_f32(ps + (dx * STRIP_PS + dx * 3 + 2) * 4);
-                    }
-                  }
+                  if (i > 0) strip_tap3<0>(ps, a0, a1, a2);
+                  strip_tap3<1>(ps, a0, a1, a2);
+                  strip_tap3<2>(ps, a0, a1, a2);
                 }
                 if (p.relu_last) { a0 = fmaxf(a0, 0.f); a1 = fmaxf(a1, 0.f); a2 = fmaxf(a2, 0.f); }
                 float* o3 = orow + (size_t)x * 3;
