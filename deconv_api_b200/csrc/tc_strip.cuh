@@ -311,8 +311,14 @@ deconv_strip_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
               sv[e] = fmaxf(t, relu_lo);
             }
             __nv_bfloat162 h2 = __floats2bfloat162_rn(sv[0], sv[1]);
-            packed[ps][c / 2] = is_pixel ? *reinterpret_cast<uint32_t*>(&h2) : 0u;
+            packed[ps][c / 2] = *reinterpret_cast<uint32_t*>(&h2);
           }
+        }
+        if (!is_pixel) {                                      // pad positions store zeros
+#pragma unroll
+          for (int ps = 0; ps < STRIP_EPI_PASSES; ++ps)
+#pragma unroll
+            for (int c = 0; c < 8; ++c) packed[ps][c] = 0u;
         }
         if constexpr (!LAST) {
           if (issuer) tma_store_wait_read();                  // the previous tile's store has read the staging tile
