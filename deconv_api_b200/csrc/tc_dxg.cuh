@@ -210,7 +210,11 @@ deconv_dxg_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         }
         if constexpr (EPI & 2) { if (in_range) prep_pair(p, actw[c / 2], s[0], s[1]); }
         __nv_bfloat162 h2 = __floats2bfloat162_rn(s[0], s[1]);
-        packed[c / 2] = is_pixel ? *reinterpret_cast<uint32_t*>(&h2) : 0u;
+        packed[c / 2] = *reinterpret_cast<uint32_t*>(&h2);
+      }
+      if (!is_pixel) {                                        // pad positions store zeros (one predicated block, not a select per pair)
+#pragma unroll
+        for (int c = 0; c < 8; ++c) packed[c] = 0u;
       }
       // Output through shared memory + ONE TMA store per tile: a direct store has every thread write 32 bytes of its
       // own 128-byte row, 32 lines per warp instruction (measured: 0.6 ms of block1_conv2's 2.4 ms).
