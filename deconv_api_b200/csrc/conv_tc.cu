@@ -810,6 +810,7 @@ struct TcConvArgs {
   const uint32_t* amax_a = nullptr;
   const uint32_t* amax_b = nullptr;
   uint32_t* amax_out = nullptr;
+  bool allow_ksplit = false;                // forward pass: few-tile layers may split K over a cluster (bits then depend on the batch's tile count, never on how feature maps are chunked)
   uint16_t* split_out = nullptr;            // scheme 1: write the result as the next conv's fp16 planes (TcParams::split_out)
   const uint32_t* split_scale = nullptr;
 };
@@ -954,6 +955,7 @@ int tc_conv_fwd_exact(dcv_ctx* ctx, const Layer& l, const float* in, int P, int 
     ctx->launches++;
   }
   TcConvArgs a{l.tc.wf3_bf16, l.tc.fk_pad, l.tc.fn_pad, l.cin, l.cout, l.relu, l.bias, 6};
+  a.allow_ksplit = true;
   return tc_conv_run(ctx, a, (const __nv_bfloat16*)ctx->ws[4].p, P, h, w, nullptr, out);
 }
 
@@ -1311,11 +1313,20 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
     if (bn == 128 && (long long)p.m_tiles * (l.n_pad / 128) < ctx->num_sms) bn = 64;      // few rows: more, smaller tiles
     if (exact_regs == 2 && bn == 128) bn = 64;
     p.n_tiles = bn == 16 ? 1 : l.n_pad / bn;
-    int stages = SMEM_BUDGET / exact_stage_bytes(bn);
+    // forward pass of few images: 14x14 .. 28x28 layers have 16 - 56 tiles; split K over clusters of 2 / 4 CTAs
+    static const int exact_split = getenv("DCV_EXACT_SPLITK") ? atoi(getenv("DCV_EXACT_SPLITK")) : 1;
+    int split = 1;
+    if (exact_split && l.allow_ksplit && l.scheme == 0 && bn == 64) {
+      const int tiles = p.m_tiles * p.n_tiles;
+      if (tiles * 4 <= ctx->num_sms && p.k_blocks % 4 == 0) split = 4;
+      else if (tiles * 2 <= ctx->num_sms && p.k_blocks % 2 == 0) split = 2;
+    }
+    const int red_bytes = (split - 1) * BLOCK_M * bn * 4;
+    int stages = (SMEM_BUDGET + (split > 1 ? 24 * 1024 : 0) - red_bytes) / exact_stage_bytes(bn);
     if (stages > 8) stages = 8;
     p.stages = stages;
     p.base_off = 0;
-    const int smem = stages * exact_stage_bytes(bn) + 1024 + 256;
+    const int smem = stages * exact_stage_bytes(bn) + 1024 + 256 + red_bytes;
     const int npl = l.scheme == 1 ? 2 : 3;
     p.amax_a = l.amax_a; p.amax_b = l.amax_b; p.amax_out = l.amax_out;
     p.split_out = l.split_out; p.split_scale = l.split_scale;
@@ -1328,6 +1339,24 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
                  2.0 * P * h * w * ((double)l.k_real + 2.0 * l.n_real));
     const int grid = std::min(p.m_tiles * p.n_tiles, ctx->num_sms);
     cudaError_t e = cudaSuccess;
+    if (split > 1) {
+      const int tiles = p.m_tiles * p.n_tiles;
+      const dim3 g2(split * std::min(tiles, ctx->num_sms / split));
+      static int smem_set2[2][64] = {};
+      if (smem_set2[split == 4][ctx->device & 63] < smem) {
+        e = split == 4 ? cudaFuncSetAttribute(conv_exact_kernel<64, 0, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)
+                       : cudaFuncSetAttribute(conv_exact_kernel<64, 0, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "cudaFuncSetAttribute(exact kernel, K split): %s", cudaGetErrorString(e));
+        smem_set2[split == 4][ctx->device & 63] = smem;
+      }
+      e = split == 4 ? launch_kc(ctx, conv_exact_kernel<64, 0, 4>, g2, dim3(EXACT_THREADS), (size_t)smem, 4, ta, tb, p)
+                     : launch_kc(ctx, conv_exact_kernel<64, 0, 2>, g2, dim3(EXACT_THREADS), (size_t)smem, 2, ta, tb, p);
+      if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "conv_exact_kernel (K split %d) launch: %s", split, cudaGetErrorString(e));
+      ctx->launches++;
+      e = cudaGetLastError();
+      if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "conv_exact_kernel (K split %d): %s", split, cudaGetErrorString(e));
+      return 0;
+    }
 #define EXACT_LAUNCH(BN)                                                                                         \
     {                                                                                                              \
       static int smem_set[64] = {};                                                                                \

@@ -31,7 +31,11 @@ constexpr int EXACT_THREADS = 320;   // TMA warp, MMA warp, 8 accumulate warps (
 // magnitude (x*s = hi + lo, 11 significand bits each), three products (hh, hl, lh): ~2^-21 per product at HALF the MMA
 // work - the backward convs of the DCV_FP32 chain (measured on the 512-map step against the oracle: see DESIGN.md §4).
 // Everything else is shared: one fresh TMEM slot per stage, fp32 register accumulation, the result rescaled once.
-template <int BLOCK_N, int SCHEME = 0>
+// SPLIT > 1 (forward pass of single images: 14x14 .. 28x28 layers are 16 - 56 tiles of 144 stages): the kernel runs as
+// clusters of SPLIT CTAs that share one tile and each take 1/SPLIT of the 64-channel blocks of K; CTAs 1.. send their
+// fp32 register accumulators to CTA 0's shared memory (st.shared::cluster), CTA 0 adds them in rank order and runs the
+// epilogue.  The partial sums are plain fp32 adds: the result differs from the unsplit kernel's in the last place only.
+template <int BLOCK_N, int SCHEME = 0, int SPLIT = 1>
 __global__ void __launch_bounds__(EXACT_THREADS, 1)
 conv_exact_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, TcParams p) {
   constexpr int B_TILE_BYTES = BLOCK_N * 128;
@@ -44,7 +48,12 @@ conv_exact_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   uint64_t* empty_bar = full_bar + MAX_STAGES;
   uint64_t* sfull_bar = empty_bar + MAX_STAGES;         // [EXACT_SLOTS] slot holds a finished stage
   uint64_t* sempty_bar = sfull_bar + EXACT_SLOTS;       // [EXACT_SLOTS] slot drained by the eight accumulate warps
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sempty_bar + EXACT_SLOTS);
+  uint64_t* red_full = sempty_bar + EXACT_SLOTS;        // SPLIT: the peers' partial sums of a tile have landed (CTA 0)
+  uint64_t* red_free = red_full + 1;                    // SPLIT: CTA 0 has read this CTA's partial sums (peers)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(red_free + 1);
+  // SPLIT: (SPLIT - 1) partial accumulators of 128 x BLOCK_N floats behind the barriers, as [peer][column / 4][row][4]
+  float4* red = reinterpret_cast<float4*>(reinterpret_cast<uint8_t*>(full_bar) + 256);
+  const uint32_t crank = SPLIT > 1 ? cluster_ctarank() : 0u;
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -54,6 +63,8 @@ conv_exact_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     tma_prefetch_desc(&tmap_b);
     for (int s = 0; s < p.stages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
     for (int s = 0; s < EXACT_SLOTS; ++s) { mbar_init(&sfull_bar[s], 1); mbar_init(&sempty_bar[s], 8); }
+    mbar_init(red_full, (SPLIT - 1) * 8);
+    mbar_init(red_free, 8);
     fence_barrier_init();
   }
   if (warp == 1) {
@@ -61,7 +72,8 @@ conv_exact_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     tmem_relinquish();
   }
   tc_fence_before();
-  __syncthreads();
+  if constexpr (SPLIT > 1) cluster_sync_all();          // the peers' barriers exist before anyone arrives on them
+  else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -69,7 +81,10 @@ conv_exact_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   const int wp = p.w + 1;
   constexpr int NPROD = SCHEME == 0 ? 6 : 3;
   constexpr int NPLANE = SCHEME == 0 ? 3 : 2;
-  const int total_st = 3 * NPROD * p.k_blocks;        // (dy, product, 64-channel block) stages per tile
+  const int kcl = p.k_blocks / SPLIT;                 // 64-channel blocks this CTA multiplies
+  const int kc0 = (int)crank * kcl;
+  const int total_st = 3 * NPROD * kcl;               // (dy, product, 64-channel block) stages per tile
+  const int tile0 = blockIdx.x / SPLIT, tile_step = gridDim.x / SPLIT;
   const int kcols = p.k_blocks * BLOCK_K;             // columns of one operand plane
 
   if (warp == 0) {
@@ -77,12 +92,12 @@ conv_exact_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      for (int tile = tile0; tile < total_tiles; tile += tile_step) {
         const int m0 = (tile / p.n_tiles) * BLOCK_M;
         const int n0 = (tile % p.n_tiles) * BLOCK_N;
         for (int st = 0; st < total_st; ++st) {
-          const int kc = st % p.k_blocks;
-          const int gp = st / p.k_blocks;
+          const int kc = kc0 + st % kcl;
+          const int gp = st / kcl;
           const int g = gp / NPROD, prod = gp % NPROD;
           const int pa = SCHEME == 0 ? (0x120100 >> (4 * prod)) & 3 : (0x100 >> (4 * prod)) & 3;   // A plane: 0,0,1,0,2,1 | 0,0,1
           const int pb = SCHEME == 0 ? (0x102010 >> (4 * prod)) & 3 : (0x010 >> (4 * prod)) & 3;   // B plane: 0,1,0,2,0,1 | 0,1,0
@@ -104,7 +119,7 @@ conv_exact_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     int stage = 0;
     uint32_t phase = 0;
     uint32_t chunk = 0;                                 // running stage count of this CTA: slot = chunk % EXACT_SLOTS
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+    for (int tile = tile0; tile < total_tiles; tile += tile_step) {
       for (int st = 0; st < total_st; ++st, ++chunk) {
         const uint32_t slot = chunk % EXACT_SLOTS, suse = chunk / EXACT_SLOTS;
         mbar_wait(&sempty_bar[slot], (suse & 1) ^ 1);   // the accumulate warps have read this slot's previous stage
@@ -140,7 +155,8 @@ conv_exact_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     // SCHEME 1: both operands carry a power-of-two scale; undo it once, on the fp32 sum (exact)
     const float wscale_inv = SCHEME == 0 ? 1.f : 1.f / pow2_scale_from_amax(__ldg(p.amax_b));
     uint32_t chunk = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+    int local = 0;
+    for (int tile = tile0; tile < total_tiles; tile += tile_step, ++local) {
       const int m0 = (tile / p.n_tiles) * BLOCK_M;
       const int n0 = (tile % p.n_tiles) * BLOCK_N + cbase;
       float acc[COLS];
@@ -170,6 +186,40 @@ conv_exact_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&sempty_bar[slot]);
+      }
+      if constexpr (SPLIT > 1) {
+        // [peer][column / 4][row][4]: one 16-byte vector per row and column quad, rows (lanes) consecutive
+        const uint32_t my_off = (uint32_t)(((cbase / 4) * BLOCK_M + lg * 32 + lane) * 16);
+        if (crank != 0) {
+          mbar_wait_cluster(red_free, (uint32_t)(local & 1) ^ 1u);       // CTA 0 has read the previous tile's
+          if (owner) {
+            const uint32_t dst = mapa_u32(smem_u32(red), 0) + (uint32_t)(((int)crank - 1) * (BLOCK_N / 4) * BLOCK_M * 16) + my_off;
+#pragma unroll
+            for (int i = 0; i < COLS; i += 4)
+              st_cluster_v4(dst + (uint32_t)((i / 4) * BLOCK_M * 16), __float_as_uint(acc[i]), __float_as_uint(acc[i + 1]),
+                            __float_as_uint(acc[i + 2]), __float_as_uint(acc[i + 3]));
+          }
+          fence_acq_rel_cluster();
+          __syncwarp();
+          if (lane == 0) mbar_arrive_remote_release(red_full, 0);
+          continue;
+        }
+        mbar_wait_cluster(red_full, (uint32_t)(local & 1));
+        if (owner) {
+          const uint32_t src = smem_u32(red) + my_off;
+#pragma unroll
+          for (int sp = 0; sp < SPLIT - 1; ++sp) {
+#pragma unroll
+            for (int i = 0; i < COLS; i += 4) {
+              const float4 u = lds128_f32(src + (uint32_t)((sp * (BLOCK_N / 4) + i / 4) * BLOCK_M * 16));
+              acc[i] += u.x; acc[i + 1] += u.y; acc[i + 2] += u.z; acc[i + 3] += u.w;
+            }
+          }
+        }
+        __syncwarp();
+        if (lane == 0) {                                   // the peers may overwrite their part of `red`
+          for (uint32_t c = 1; c < (uint32_t)SPLIT; ++c) mbar_arrive_remote_release(red_free, c);
+        }
       }
       // epilogue: bias, ReLU, fp32 compact store (P,h,w,n_real)
       const int r = m0 + lg * 32 + lane;
@@ -249,10 +299,10 @@ conv_exact_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   }
 
   tc_fence_before();
-  __syncthreads();
+  if constexpr (SPLIT > 1) cluster_sync_all();          // no CTA leaves while a peer may still write to it or arrive on it
+  else __syncthreads();
   if (warp == 1) tmem_dealloc(tmem_base, TMEM_COLS);
 }
-
 
 }  // namespace tc
 }  // namespace dcv
