@@ -1312,15 +1312,35 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
     int bn = l.n_real <= 16 ? 16 : (l.n_pad % 128 == 0 ? 128 : 64);
     if (bn == 128 && (long long)p.m_tiles * (l.n_pad / 128) < ctx->num_sms) bn = 64;      // few rows: more, smaller tiles
     if (exact_regs == 2 && bn == 128) bn = 64;
-    p.n_tiles = bn == 16 ? 1 : l.n_pad / bn;
-    // forward pass of few images: 14x14 .. 28x28 layers have 16 - 56 tiles; split K over clusters of 2 / 4 CTAs
+    // Forward pass: the layers from 112x112 down have 16 - 200 tiles per image.  Pick the N tile and the K split (clusters
+    // of 2 / 4 CTAs per tile) that minimise waves x K steps x cycles per step (85 at N = 64, 92 at N = 128; a split costs
+    // about half a 64-channel block for its reduction): 112x112x128 one wave of 100 N = 128 tiles instead of two of N = 64,
+    // 56x56x256 52 N = 128 tiles split in two, 28x28x512 56 N = 64 tiles split in two, 14x14x512 16 in four.  The SPLIT is
+    // decided on the geometry of ONE image and then used for any batch: it changes the order of the K sum, and an image's
+    // tape (its switches) must not depend on how many images share the call.  The N tile does not touch the sums.
     static const int exact_split = getenv("DCV_EXACT_SPLITK") ? atoi(getenv("DCV_EXACT_SPLITK")) : 1;
     int split = 1;
-    if (exact_split && l.allow_ksplit && l.scheme == 0 && bn == 64) {
-      const int tiles = p.m_tiles * p.n_tiles;
-      if (tiles * 4 <= ctx->num_sms && p.k_blocks % 4 == 0) split = 4;
-      else if (tiles * 2 <= ctx->num_sms && p.k_blocks % 2 == 0) split = 2;
+    if (exact_split && l.allow_ksplit && l.scheme == 0 && bn >= 64) {
+      auto choose = [&](long long m_tiles, bool with_split, int& obn, int& osplit) {
+        double best = 1e30;
+        for (int b = 64; b <= 128; b += 64) {
+          if (l.n_pad % b) continue;
+          const long long tiles = m_tiles * (l.n_pad / b);
+          for (int sp = 1; sp <= (with_split ? (b == 64 ? 4 : 2) : 1); sp *= 2) {
+            if (p.k_blocks % sp) continue;
+            if (sp > 1 && tiles * sp > ctx->num_sms) continue;
+            const long long waves = sp > 1 ? 1 : (tiles + ctx->num_sms - 1) / ctx->num_sms;
+            const double c = (double)waves * ((double)p.k_blocks / sp + (sp > 1 ? 0.5 : 0.0)) * (b == 64 ? 85.0 : 92.0);
+            if (c < best - 1e-9) { best = c; obn = b; osplit = sp; }
+          }
+        }
+      };
+      int bn1 = bn, split1 = 1;
+      choose(((long long)(h + 1) * (w + 1) + BLOCK_M - 1) / BLOCK_M, true, bn1, split1);
+      if (split1 > 1) { bn = bn1; split = split1; }
+      else { int s1 = 1; choose(p.m_tiles, false, bn, s1); }
     }
+    p.n_tiles = bn == 16 ? 1 : l.n_pad / bn;
     const int red_bytes = (split - 1) * BLOCK_M * bn * 4;
     int stages = (SMEM_BUDGET + (split > 1 ? 24 * 1024 : 0) - red_bytes) / exact_stage_bytes(bn);
     if (stages > 8) stages = 8;
@@ -1342,14 +1362,17 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
     if (split > 1) {
       const int tiles = p.m_tiles * p.n_tiles;
       const dim3 g2(split * std::min(tiles, ctx->num_sms / split));
-      static int smem_set2[2][64] = {};
-      if (smem_set2[split == 4][ctx->device & 63] < smem) {
-        e = split == 4 ? cudaFuncSetAttribute(conv_exact_kernel<64, 0, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)
+      const int which = bn == 128 ? 2 : (split == 4 ? 1 : 0);
+      static int smem_set2[3][64] = {};
+      if (smem_set2[which][ctx->device & 63] < smem) {
+        e = which == 2 ? cudaFuncSetAttribute(conv_exact_kernel<128, 0, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)
+          : which == 1 ? cudaFuncSetAttribute(conv_exact_kernel<64, 0, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)
                        : cudaFuncSetAttribute(conv_exact_kernel<64, 0, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "cudaFuncSetAttribute(exact kernel, K split): %s", cudaGetErrorString(e));
-        smem_set2[split == 4][ctx->device & 63] = smem;
+        smem_set2[which][ctx->device & 63] = smem;
       }
-      e = split == 4 ? launch_kc(ctx, conv_exact_kernel<64, 0, 4>, g2, dim3(EXACT_THREADS), (size_t)smem, 4, ta, tb, p)
+      e = which == 2 ? launch_kc(ctx, conv_exact_kernel<128, 0, 2>, g2, dim3(EXACT_THREADS), (size_t)smem, 2, ta, tb, p)
+        : which == 1 ? launch_kc(ctx, conv_exact_kernel<64, 0, 4>, g2, dim3(EXACT_THREADS), (size_t)smem, 4, ta, tb, p)
                      : launch_kc(ctx, conv_exact_kernel<64, 0, 2>, g2, dim3(EXACT_THREADS), (size_t)smem, 2, ta, tb, p);
       if (e != cudaSuccess) return ctx->fail(DCV_ERR_CUDA, "conv_exact_kernel (K split %d) launch: %s", split, cudaGetErrorString(e));
       ctx->launches++;

@@ -153,3 +153,25 @@ def test_vgg16_dense_targets_vs_oracle():
             assert a.shape == b.shape == (224, 224, 3)
             assert rel_l2(a, b) < 1e-5, name
             assert rel_l2(a16, b) < 2e-2, name
+
+
+@pytest.mark.gpu
+def test_forward_tape_does_not_depend_on_the_batch():
+    """An image's tape (activations and switches of every layer) must be the same bits whether the image is forwarded
+    alone or in a batch: the forward kernels choose tile shapes by the batch's size, but anything that changes the order
+    of a sum (the K split over a thread-block cluster for layers with few tiles) is decided on one image's geometry."""
+    from deconv_api_b200 import synth, vgg16
+    model = vgg16.VGG16(weights=None, include_top=False, input_shape=(224, 224, 3))
+    imgs = synth.image_batch(5, 224, 224, seed0=40)
+    eng = model.bound_engine(upto="block5_conv3")
+    top = eng.index["block5_conv3"]
+    eng.forward(imgs, top)
+    layers = [i for i, k in enumerate(eng.kinds) if k in ("conv", "pool") and i <= top]
+    acts = {i: eng.activation(i) for i in layers}
+    sws = {i: eng.switch_index(i) for i in layers if eng.kinds[i] == "pool"}
+    for b in (0, 4):
+        eng.forward(imgs[b:b + 1], top)
+        for i in layers:
+            assert np.array_equal(eng.activation(i)[0].view(np.uint32), acts[i][b].view(np.uint32)), (b, i)
+        for i in sws:
+            assert np.array_equal(eng.switch_index(i)[0], sws[i][b]), (b, i)
