@@ -314,8 +314,10 @@ int forward_impl(dcv_ctx* ctx, const float* img, bool on_device, int B, int H, i
   const float* cur = (const float*)ctx->input.p;
   int cb = B, ch = H, cw = W, cc = C;
   bool flat = false;
+  int fwd_planes = -1;               // workspace index holding the current tensor as split operand planes (-1: none)
   for (int j = 0; j <= upto; ++j) {
     Layer& l = ctx->net[j];
+    if (l.kind != LK_CONV) fwd_planes = -1;
     switch (l.kind) {
       case LK_CONV: {
         if (flat) return ctx->fail(DCV_ERR_UNSUPPORTED, "conv after flatten");
@@ -325,7 +327,11 @@ int forward_impl(dcv_ctx* ctx, const float* img, bool on_device, int B, int H, i
         // FFMA otherwise / when disabled (DCV_FWD_TC=0)
         if (ctx->fwd_mode == 1 && l.cin >= 16) {
           TRY(tc_prepare_forward_exact(ctx, l));
-          TRY(tc_conv_fwd_exact(ctx, l, cur, cb, ch, cw, (float*)l.act.p));
+          // a conv directly above (no pool in between) takes this result as ready-made operand planes
+          const Layer* nx = (j + 1 <= upto && ctx->net[j + 1].kind == LK_CONV && ctx->net[j + 1].cin >= 16) ? &ctx->net[j + 1] : nullptr;
+          int planes_out = -1;
+          TRY(tc_conv_fwd_exact(ctx, l, cur, cb, ch, cw, (float*)l.act.p, fwd_planes, nx, &planes_out));
+          fwd_planes = planes_out;
           cc = l.cout;
           break;
         }
@@ -335,6 +341,7 @@ int forward_impl(dcv_ctx* ctx, const float* img, bool on_device, int B, int H, i
                        4.0 * cb * ch * cw * ((double)l.cin + l.cout));
           launch_conv3x3_fp32(cur, l.w, cb, ch, cw, l.cin, l.cout, e, (float*)l.act.p, ctx->stream); ctx->launches++;
         }
+        fwd_planes = -1;
         cc = l.cout;
         break;
       }

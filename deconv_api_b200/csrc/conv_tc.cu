@@ -943,12 +943,20 @@ int tc_prepare_forward_exact(dcv_ctx* ctx, Layer& l) {
 }
 
 // in: fp32 compact (P,h,w,cin) -> out: fp32 compact (P,h,w,cout) = act(conv + bias); scratch: ctx->ws[4]
-int tc_conv_fwd_exact(dcv_ctx* ctx, const Layer& l, const float* in, int P, int h, int w, float* out) {
+// planes_in: -1 = split `in` here; 0 / 1 = the previous conv's epilogue already wrote this conv's three operand planes
+// into ws[4 + planes_in].  planes_out (optional): set to the workspace index this conv wrote the NEXT conv's planes to
+// (fuse_next: the conv that consumes this result directly, with nothing in between).
+int tc_conv_fwd_exact(dcv_ctx* ctx, const Layer& l, const float* in, int P, int h, int w, float* out, int planes_in,
+                      const Layer* fuse_next, int* planes_out) {
   if (!l.tc.wf3_bf16) return ctx->fail(DCV_ERR_STATE, "split forward weights were not prepared for this layer");
-  const size_t elems = (size_t)P * (h + 1) * (w + 1) * 3 * l.tc.fk_pad;
-  int r = ctx->ws[4].ensure(ctx, elems * sizeof(__nv_bfloat16));
-  if (r) return r;
-  {
+  static const int fuse = getenv("DCV_FWD_FUSE_SPLIT") ? atoi(getenv("DCV_FWD_FUSE_SPLIT")) : 1;
+  if (planes_out) *planes_out = -1;
+  const int sel = planes_in >= 0 ? planes_in : 0;
+  int r = 0;
+  if (planes_in < 0) {
+    const size_t elems = (size_t)P * (h + 1) * (w + 1) * 3 * l.tc.fk_pad;
+    r = ctx->ws[4].ensure(ctx, elems * sizeof(__nv_bfloat16));
+    if (r) return r;
     const size_t work = (size_t)P * (h + 1) * (w + 1) * (l.tc.fk_pad / 8);
     ProfScope ps(ctx, DCV_K_OTHER, 0.0, 4.0 * P * h * w * l.cin + 6.0 * P * (h + 1) * (w + 1) * l.tc.fk_pad);
     split3_pad_kernel<<<grid_for(work, 256), 256, 0, ctx->stream>>>(in, P, h, w, l.cin, l.tc.fk_pad, (__nv_bfloat16*)ctx->ws[4].p);
@@ -956,7 +964,13 @@ int tc_conv_fwd_exact(dcv_ctx* ctx, const Layer& l, const float* in, int P, int 
   }
   TcConvArgs a{l.tc.wf3_bf16, l.tc.fk_pad, l.tc.fn_pad, l.cin, l.cout, l.relu, l.bias, 6};
   a.allow_ksplit = true;
-  return tc_conv_run(ctx, a, (const __nv_bfloat16*)ctx->ws[4].p, P, h, w, nullptr, out);
+  if (fuse && fuse_next && planes_out && tc_cpad(fuse_next->cin) == l.tc.fn_pad && fuse_next->cin == l.cout) {
+    r = ctx->ws[4 + (sel ^ 1)].ensure(ctx, (size_t)P * (h + 1) * (w + 1) * 3 * l.tc.fn_pad * sizeof(__nv_bfloat16));
+    if (r) return r;
+    a.split_out = (uint16_t*)ctx->ws[4 + (sel ^ 1)].p;
+    *planes_out = sel ^ 1;
+  }
+  return tc_conv_run(ctx, a, (const __nv_bfloat16*)ctx->ws[4 + sel].p, P, h, w, nullptr, out);
 }
 
 size_t tc_split_elems(int h, int w, int c) { return (size_t)(h + 1) * (w + 1) * 3 * tc_cpad(c); }
@@ -1307,7 +1321,7 @@ static int tc_conv_run(dcv_ctx* ctx, const TcConvArgs& l, const __nv_bfloat16* i
   // fp32-accurate mode: accumulation in registers (tc_exact.cuh); DCV_TC_EXACT=2 forces N tile 64
   static const int exact_regs = getenv("DCV_TC_EXACT") ? atoi(getenv("DCV_TC_EXACT")) : 1;
   if (l.nprod == 6) {
-    if (!out_f32 && !(l.split_out && l.scheme == 1))
+    if (!out_f32 && !(l.split_out && l.scheme == 1))   // (scheme 0 writes the planes besides the fp32 result)
       return ctx->fail(DCV_ERR_UNSUPPORTED, "tc_conv: the split-operand mode writes fp32 (or, two-plane scheme, the next conv's planes)");
     int bn = l.n_real <= 16 ? 16 : (l.n_pad % 128 == 0 ? 128 : 64);
     if (bn == 128 && (long long)p.m_tiles * (l.n_pad / 128) < ctx->num_sms) bn = 64;      // few rows: more, smaller tiles

@@ -131,7 +131,8 @@ int tc_conv_first(dcv_ctx* ctx, Layer& l, const float* x, int P, int h, int w, _
                   const int* jit = nullptr);      // jit: device jitter table, the image is read rolled (DeepDream)
 // fp32-accurate forward conv on tcgen05 (bf16 x 3 operand split, six products); fp32 compact in and out
 int tc_prepare_forward_exact(dcv_ctx* ctx, Layer& l);
-int tc_conv_fwd_exact(dcv_ctx* ctx, const Layer& l, const float* in, int P, int h, int w, float* out);
+int tc_conv_fwd_exact(dcv_ctx* ctx, const Layer& l, const float* in, int P, int h, int w, float* out, int planes_in = -1,
+                      const Layer* fuse_next = nullptr, int* planes_out = nullptr);
 // the same for the backward (deconvnet) conv of the fp32 projection mode: in fp32 compact (P,h,w,cout) ->
 // out fp32 compact (P,h,w,cin) = relu?(conv(in, flipT(W))); scratch ctx->ws[4] sized by tc_split_elems()
 int tc_prepare_backward_exact(dcv_ctx* ctx, Layer& l);

@@ -284,6 +284,43 @@ conv_exact_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           }
         }
       }
+      if (SCHEME == 0 && p.split_out) {
+        // forward tape: besides the fp32 activation, the result goes out as the NEXT conv's operand - three bf16 planes
+        // [hi | mid | lo] per padded-flat row (the arithmetic of split3_pad_kernel, which this replaces); pad rows and
+        // pad channels are written as zeros
+        if (owner && r < p.rows) {
+          const bool is_px = x < p.w && y < p.h;
+          uint16_t* dst = p.split_out + (size_t)r * (3 * (size_t)p.n_pad) + n0;
+#pragma unroll
+          for (int i = 0; i < COLS; i += 8) {
+            uint32_t hi[4], mi[4], lo[4];
+#pragma unroll
+            for (int k = 0; k < 8; k += 2) {
+              float a2[2];
+#pragma unroll
+              for (int e2 = 0; e2 < 2; ++e2) {
+                float a = acc[i + k + e2];
+                const int c = n0 + i + k + e2;
+                if (p.bias && c < p.n_real) a += __ldg(p.bias + c);
+                if (p.relu) a = fmaxf(a, 0.f);
+                a2[e2] = (is_px && c < p.n_real) ? a : 0.f;
+              }
+              const __nv_bfloat162 h2 = __floats2bfloat162_rn(a2[0], a2[1]);
+              const float2 hf = __bfloat1622float2(h2);
+              const float r0 = a2[0] - hf.x, r1 = a2[1] - hf.y;
+              const __nv_bfloat162 m2 = __floats2bfloat162_rn(r0, r1);
+              const float2 mf = __bfloat1622float2(m2);
+              const __nv_bfloat162 l2 = __floats2bfloat162_rn(r0 - mf.x, r1 - mf.y);
+              hi[k >> 1] = *reinterpret_cast<const uint32_t*>(&h2);
+              mi[k >> 1] = *reinterpret_cast<const uint32_t*>(&m2);
+              lo[k >> 1] = *reinterpret_cast<const uint32_t*>(&l2);
+            }
+            *reinterpret_cast<uint4*>(dst + i) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+            *reinterpret_cast<uint4*>(dst + p.n_pad + i) = make_uint4(mi[0], mi[1], mi[2], mi[3]);
+            *reinterpret_cast<uint4*>(dst + 2 * p.n_pad + i) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+          }
+        }
+      }
       if (p.amax_out) {
         // one atomic per warp when the whole warp sits in one item (the rule; tiles straddle items only at their ends)
         const int item0 = __shfl_sync(0xffffffffu, item_of_row, 0);
