@@ -439,14 +439,18 @@ dream_update_kernel(float* __restrict__ img, const float* __restrict__ g, const 
   block_sum_partials(partial, np, ts, tq);
   const float rms = (float)sqrt(tq / (double)n);
   const float sc = step / fmaxf(rms, 1e-7f);
-  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
-    const int c = (int)(i % C);
-    size_t p = i / C;
-    const int xx = (int)(p % W);
-    const int y = (int)(p / W);
+  // blocks walk whole rows (two contiguous segments of the rolled gradient row per image row): 32-bit arithmetic, no
+  // division per element (the flat 64-bit index form took 20 us for a 512x512 image)
+  int sxs = ox % W; if (sxs < 0) sxs += W;
+  const unsigned wc = (unsigned)W * (unsigned)C, shift = (unsigned)sxs * (unsigned)C;    // g row index = (f + shift) mod wc
+  for (int y = blockIdx.x; y < H; y += gridDim.x) {
     int sy = (y + oy) % H; if (sy < 0) sy += H;
-    int sx = (xx + ox) % W; if (sx < 0) sx += W;
-    img[i] = fmaf(sc, __ldg(g + ((size_t)sy * W + sx) * C + c), img[i]);
+    float* irow = img + (size_t)y * wc;
+    const float* grow = g + (size_t)sy * wc;
+    for (unsigned f = threadIdx.x; f < wc; f += blockDim.x) {
+      unsigned sf = f + shift; if (sf >= wc) sf -= wc;
+      irow[f] = fmaf(sc, __ldg(grow + sf), irow[f]);
+    }
   }
 }
 
@@ -768,7 +772,7 @@ int dream_iter(dcv_ctx* ctx, float* img, int B, int H, int W, int C, const LossS
     ProfScope ps(ctx, DCV_K_OTHER, 0.0, 16.0 * per);
     launch_sum_stats(g + b * per, per, (double*)ctx->scratch.p, np, ctx->stream);
     // few, fat blocks: every block first reduces the block partials of the RMS
-    dream_update_kernel<<<(int)std::min<size_t>(std::max<size_t>((per + 4095) / 4096, 1), 4 * kNumSMs), 256, 0, ctx->stream>>>(img + b * per, g + b * per, (const double*)ctx->scratch.p, np,
+    dream_update_kernel<<<std::min(H, 4 * kNumSMs), 256, 0, ctx->stream>>>(img + b * per, g + b * per, (const double*)ctx->scratch.p, np,
                                                                          H, W, C, step, 0, 0, jit_dev);
     ctx->launches += 2;
   }
